@@ -1,0 +1,599 @@
+// oracle/nnbvh_oracle.cpp -- TEST INFRASTRUCTURE (the checker), not product code.
+//
+// CPU restatement of the reference's hot path, operation for operation in
+// IEEE binary32 (build with -ffp-contract=off; fused multiply-adds only where
+// the reference source says FMA()).  Each function cites the reference
+// file:line it follows (paths relative to /root/reference/src/pbrt).
+//
+// Parity status: PINNED against the unmodified reference built into
+// oracle/_ref/libnnbvh_ref.so (tests/test_oracle_vs_ref.py) and against the
+// golden vectors under tests/golden/ generated from that library.
+//
+// Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline /
+// --impl reference legs may use this file.
+
+#include "nnbvh_oracle.h"
+
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+#include <limits>
+#include <vector>
+
+#include <atomic>
+#include <thread>
+
+namespace {
+
+// ---- util/float.h:43,195-197 ------------------------------------------------
+constexpr float kMachineEpsilon = std::numeric_limits<float>::epsilon() * 0.5;
+constexpr float Gamma(int n) {
+    return (n * kMachineEpsilon) / (1 - n * kMachineEpsilon);
+}
+constexpr float kInfinity = std::numeric_limits<float>::infinity();
+
+// ---- util/math.h:569-575 (float instantiation; FMA = std::fma, float.h:100) --
+inline float DifferenceOfProducts(float a, float b, float c, float d) {
+    float cd = c * d;
+    float differenceOfProducts = std::fma(a, b, -cd);
+    float error = std::fma(-c, d, cd);
+    return differenceOfProducts + error;
+}
+
+struct V3 {
+    float x, y, z;
+    float operator[](int i) const { return i == 0 ? x : (i == 1 ? y : z); }
+};
+
+// util/vecmath.h:447-451 -- std::max over an initializer list (first largest).
+inline float MaxComponentValue(float a, float b, float c) {
+    return std::max({a, b, c});
+}
+
+// ---- util/vecmath.h:1254-1336 -----------------------------------------------
+struct Box {
+    float mn[3], mx[3];
+    Box() {
+        for (int i = 0; i < 3; ++i) {
+            mn[i] = std::numeric_limits<float>::max();
+            mx[i] = std::numeric_limits<float>::lowest();
+        }
+    }
+    float SurfaceArea() const {
+        float dx = mx[0] - mn[0], dy = mx[1] - mn[1], dz = mx[2] - mn[2];
+        return 2 * (dx * dy + dx * dz + dy * dz);
+    }
+    int MaxDimension() const {
+        float dx = mx[0] - mn[0], dy = mx[1] - mn[1], dz = mx[2] - mn[2];
+        if (dx > dy && dx > dz)
+            return 0;
+        else if (dy > dz)
+            return 1;
+        else
+            return 2;
+    }
+    // Bounds3::Offset (vecmath.h:1321-1330), one component.
+    float Offset(const float p[3], int dim) const {
+        float o = p[dim] - mn[dim];
+        if (mx[dim] > mn[dim])
+            o /= mx[dim] - mn[dim];
+        return o;
+    }
+};
+inline Box Union(const Box &a, const Box &b) {  // vecmath.h:1487-1492
+    Box r;
+    for (int i = 0; i < 3; ++i) {
+        r.mn[i] = std::min(a.mn[i], b.mn[i]);
+        r.mx[i] = std::max(a.mx[i], b.mx[i]);
+    }
+    return r;
+}
+inline Box Union(const Box &a, const float p[3]) {  // vecmath.h:1479-1484
+    Box r;
+    for (int i = 0; i < 3; ++i) {
+        r.mn[i] = std::min(a.mn[i], p[i]);
+        r.mx[i] = std::max(a.mx[i], p[i]);
+    }
+    return r;
+}
+
+// ---- cpu/aggregates.cpp:91-100 ----------------------------------------------
+struct BuildPrim {
+    size_t primitiveIndex;
+    Box bounds;
+    void Centroid(float c[3]) const {
+        for (int i = 0; i < 3; ++i)
+            c[i] = .5f * bounds.mn[i] + .5f * bounds.mx[i];
+    }
+    float Centroid(int dim) const { return .5f * bounds.mn[dim] + .5f * bounds.mx[dim]; }
+};
+
+struct BuildNode {  // cpu/aggregates.cpp:103-126
+    Box bounds;
+    BuildNode *children[2];
+    int splitAxis, firstPrimOffset, nPrimitives;
+};
+
+struct Builder {
+    int maxPrimsInNode;
+    int splitMethod;
+    std::vector<BuildNode *> pool;
+    int totalNodes = 0;
+    int orderedPrimsOffset = 0;
+    int32_t *orderOut;
+
+    ~Builder() {
+        for (BuildNode *n : pool)
+            delete n;
+    }
+
+    BuildNode *MakeLeaf(BuildNode *node, BuildPrim *prims, size_t n, const Box &bounds) {
+        // aggregates.cpp:207-215 / 227-234 / 342-351
+        int firstPrimOffset = orderedPrimsOffset;
+        orderedPrimsOffset += (int)n;
+        for (size_t i = 0; i < n; ++i)
+            orderOut[firstPrimOffset + i] = (int32_t)prims[i].primitiveIndex;
+        node->firstPrimOffset = firstPrimOffset;
+        node->nPrimitives = (int)n;
+        node->bounds = bounds;
+        node->children[0] = node->children[1] = nullptr;
+        return node;
+    }
+
+    // cpu/aggregates.cpp:192-387 (sequential recursion order == the
+    // reference's order when it runs on one thread).
+    BuildNode *BuildRecursive(BuildPrim *prims, size_t n) {
+        BuildNode *node = new BuildNode;
+        pool.push_back(node);
+        ++totalNodes;
+        Box bounds;
+        for (size_t i = 0; i < n; ++i)
+            bounds = Union(bounds, prims[i].bounds);
+
+        if (bounds.SurfaceArea() == 0 || n == 1)
+            return MakeLeaf(node, prims, n, bounds);
+
+        Box centroidBounds;
+        for (size_t i = 0; i < n; ++i) {
+            float c[3];
+            prims[i].Centroid(c);
+            centroidBounds = Union(centroidBounds, c);
+        }
+        int dim = centroidBounds.MaxDimension();
+        if (centroidBounds.mx[dim] == centroidBounds.mn[dim])
+            return MakeLeaf(node, prims, n, bounds);
+
+        size_t mid = n / 2;
+        auto equalCounts = [&]() {
+            mid = n / 2;
+            std::nth_element(prims, prims + mid, prims + n,
+                             [dim](const BuildPrim &a, const BuildPrim &b) {
+                                 return a.Centroid(dim) < b.Centroid(dim);
+                             });
+        };
+        switch (splitMethod) {
+        case NNBVH_ORACLE_MIDDLE: {  // :240-253
+            float pmid = (centroidBounds.mn[dim] + centroidBounds.mx[dim]) / 2;
+            BuildPrim *midIter =
+                std::partition(prims, prims + n, [dim, pmid](const BuildPrim &pi) {
+                    return pi.Centroid(dim) < pmid;
+                });
+            mid = midIter - prims;
+            if (midIter != prims && midIter != prims + n)
+                break;
+            equalCounts();  // falls through to EqualCounts in the reference
+            break;
+        }
+        case NNBVH_ORACLE_EQUAL_COUNTS:  // :254-264
+            equalCounts();
+            break;
+        case NNBVH_ORACLE_SAH:
+        default: {  // :265-355
+            if (n <= 2) {
+                equalCounts();
+            } else {
+                constexpr int nBuckets = 12;
+                struct Bucket {
+                    int count = 0;
+                    Box bounds;
+                } buckets[nBuckets];
+                for (size_t i = 0; i < n; ++i) {
+                    float c[3];
+                    prims[i].Centroid(c);
+                    int b = nBuckets * centroidBounds.Offset(c, dim);
+                    if (b == nBuckets)
+                        b = nBuckets - 1;
+                    buckets[b].count++;
+                    buckets[b].bounds = Union(buckets[b].bounds, prims[i].bounds);
+                }
+                constexpr int nSplits = nBuckets - 1;
+                float costs[nSplits] = {};
+                int countBelow = 0;
+                Box boundBelow;
+                for (int i = 0; i < nSplits; ++i) {
+                    boundBelow = Union(boundBelow, buckets[i].bounds);
+                    countBelow += buckets[i].count;
+                    costs[i] += countBelow * boundBelow.SurfaceArea();
+                }
+                int countAbove = 0;
+                Box boundAbove;
+                for (int i = nSplits; i >= 1; --i) {
+                    boundAbove = Union(boundAbove, buckets[i].bounds);
+                    countAbove += buckets[i].count;
+                    costs[i - 1] += countAbove * boundAbove.SurfaceArea();
+                }
+                int minCostSplitBucket = -1;
+                float minCost = kInfinity;
+                for (int i = 0; i < nSplits; ++i) {
+                    if (costs[i] < minCost) {
+                        minCost = costs[i];
+                        minCostSplitBucket = i;
+                    }
+                }
+                float leafCost = n;
+                minCost = 1.f / 2.f + minCost / bounds.SurfaceArea();
+                if (n > (size_t)maxPrimsInNode || minCost < leafCost) {
+                    BuildPrim *midIter =
+                        std::partition(prims, prims + n, [=](const BuildPrim &bp) {
+                            float c[3];
+                            bp.Centroid(c);
+                            int b = nBuckets * centroidBounds.Offset(c, dim);
+                            if (b == nBuckets)
+                                b = nBuckets - 1;
+                            return b <= minCostSplitBucket;
+                        });
+                    mid = midIter - prims;
+                } else {
+                    return MakeLeaf(node, prims, n, bounds);
+                }
+            }
+            break;
+        }
+        }
+        BuildNode *c0 = BuildRecursive(prims, mid);
+        BuildNode *c1 = BuildRecursive(prims + mid, n - mid);
+        // InitInterior, :113-120
+        node->children[0] = c0;
+        node->children[1] = c1;
+        node->bounds = Union(c0->bounds, c1->bounds);
+        node->splitAxis = dim;
+        node->nPrimitives = 0;
+        return node;
+    }
+
+    // cpu/aggregates.cpp:505-522
+    int Flatten(const BuildNode *node, nnbvh_oracle_node *nodes, int *offset) {
+        nnbvh_oracle_node *ln = &nodes[*offset];
+        std::memset(ln, 0, sizeof(*ln));
+        for (int i = 0; i < 3; ++i) {
+            ln->bounds[i] = node->bounds.mn[i];
+            ln->bounds[3 + i] = node->bounds.mx[i];
+        }
+        int nodeOffset = (*offset)++;
+        if (node->nPrimitives > 0) {
+            ln->offset = node->firstPrimOffset;
+            ln->nPrimitives = (uint16_t)node->nPrimitives;
+        } else {
+            ln->axis = (uint8_t)node->splitAxis;
+            ln->nPrimitives = 0;
+            Flatten(node->children[0], nodes, offset);
+            ln->offset = Flatten(node->children[1], nodes, offset);
+        }
+        return nodeOffset;
+    }
+};
+
+// ---- per-ray constants --------------------------------------------------------
+struct RayCtx {
+    float ox, oy, oz, dx, dy, dz;
+    float invx, invy, invz;
+    int neg[3];
+};
+
+inline RayCtx MakeRayCtx(const float *r) {
+    RayCtx c;
+    c.ox = r[0];
+    c.oy = r[1];
+    c.oz = r[2];
+    c.dx = r[4];
+    c.dy = r[5];
+    c.dz = r[6];
+    // cpu/aggregates.cpp:534-535
+    c.invx = 1 / c.dx;
+    c.invy = 1 / c.dy;
+    c.invz = 1 / c.dz;
+    c.neg[0] = int(c.invx < 0);
+    c.neg[1] = int(c.invy < 0);
+    c.neg[2] = int(c.invz < 0);
+    return c;
+}
+
+// ---- util/vecmath.h:1573-1608 -------------------------------------------------
+inline bool BoxIntersectP(const float *b, const RayCtx &r, float raytMax) {
+    // bounds[i] is pMin for i==0, pMax for i==1 (vecmath.h:1272-1276)
+    float tMin = (b[3 * r.neg[0] + 0] - r.ox) * r.invx;
+    float tMax = (b[3 * (1 - r.neg[0]) + 0] - r.ox) * r.invx;
+    float tyMin = (b[3 * r.neg[1] + 1] - r.oy) * r.invy;
+    float tyMax = (b[3 * (1 - r.neg[1]) + 1] - r.oy) * r.invy;
+    tMax *= 1 + 2 * Gamma(3);
+    tyMax *= 1 + 2 * Gamma(3);
+    if (tMin > tyMax || tyMin > tMax)
+        return false;
+    if (tyMin > tMin)
+        tMin = tyMin;
+    if (tyMax < tMax)
+        tMax = tyMax;
+    float tzMin = (b[3 * r.neg[2] + 2] - r.oz) * r.invz;
+    float tzMax = (b[3 * (1 - r.neg[2]) + 2] - r.oz) * r.invz;
+    tzMax *= 1 + 2 * Gamma(3);
+    if (tMin > tzMax || tzMin > tMax)
+        return false;
+    if (tzMin > tMin)
+        tMin = tzMin;
+    if (tzMax < tMax)
+        tMax = tzMax;
+    return (tMin < raytMax) && (tMax > 0);
+}
+
+// ---- shapes.cpp:172-273 ----------------------------------------------------------
+inline bool TriangleIntersect(const RayCtx &r, float tMax, const float *p, float *tOut,
+                              float *b0Out, float *b1Out, float *b2Out) {
+    V3 p0{p[0], p[1], p[2]}, p1{p[3], p[4], p[5]}, p2{p[6], p[7], p[8]};
+    // :176  LengthSquared(Cross(p2 - p0, p1 - p0)) == 0
+    {
+        V3 v{p2.x - p0.x, p2.y - p0.y, p2.z - p0.z};
+        V3 w{p1.x - p0.x, p1.y - p0.y, p1.z - p0.z};
+        float cx = DifferenceOfProducts(v.y, w.z, v.z, w.y);
+        float cy = DifferenceOfProducts(v.z, w.x, v.x, w.z);
+        float cz = DifferenceOfProducts(v.x, w.y, v.y, w.x);
+        if (cx * cx + cy * cy + cz * cz == 0)
+            return false;
+    }
+    // :181-183
+    V3 p0t{p0.x - r.ox, p0.y - r.oy, p0.z - r.oz};
+    V3 p1t{p1.x - r.ox, p1.y - r.oy, p1.z - r.oz};
+    V3 p2t{p2.x - r.ox, p2.y - r.oy, p2.z - r.oz};
+    // :186-196
+    V3 d0{r.dx, r.dy, r.dz};
+    float ax = std::abs(d0.x), ay = std::abs(d0.y), az = std::abs(d0.z);
+    int kz = (ax > ay) ? ((ax > az) ? 0 : 2) : ((ay > az) ? 1 : 2);
+    int kx = kz + 1;
+    if (kx == 3)
+        kx = 0;
+    int ky = kx + 1;
+    if (ky == 3)
+        ky = 0;
+    V3 d{d0[kx], d0[ky], d0[kz]};
+    p0t = V3{p0t[kx], p0t[ky], p0t[kz]};
+    p1t = V3{p1t[kx], p1t[ky], p1t[kz]};
+    p2t = V3{p2t[kx], p2t[ky], p2t[kz]};
+    // :199-207
+    float Sx = -d.x / d.z;
+    float Sy = -d.y / d.z;
+    float Sz = 1 / d.z;
+    p0t.x += Sx * p0t.z;
+    p0t.y += Sy * p0t.z;
+    p1t.x += Sx * p1t.z;
+    p1t.y += Sy * p1t.z;
+    p2t.x += Sx * p2t.z;
+    p2t.y += Sy * p2t.z;
+    // :210-212
+    float e0 = DifferenceOfProducts(p1t.x, p2t.y, p1t.y, p2t.x);
+    float e1 = DifferenceOfProducts(p2t.x, p0t.y, p2t.y, p0t.x);
+    float e2 = DifferenceOfProducts(p0t.x, p1t.y, p0t.y, p1t.x);
+    // :215-225
+    if (e0 == 0.0f || e1 == 0.0f || e2 == 0.0f) {
+        double p2txp1ty = (double)p2t.x * (double)p1t.y;
+        double p2typ1tx = (double)p2t.y * (double)p1t.x;
+        e0 = (float)(p2typ1tx - p2txp1ty);
+        double p0txp2ty = (double)p0t.x * (double)p2t.y;
+        double p0typ2tx = (double)p0t.y * (double)p2t.x;
+        e1 = (float)(p0typ2tx - p0txp2ty);
+        double p1txp0ty = (double)p1t.x * (double)p0t.y;
+        double p1typ0tx = (double)p1t.y * (double)p0t.x;
+        e2 = (float)(p1typ0tx - p1txp0ty);
+    }
+    // :228-232
+    if ((e0 < 0 || e1 < 0 || e2 < 0) && (e0 > 0 || e1 > 0 || e2 > 0))
+        return false;
+    float det = e0 + e1 + e2;
+    if (det == 0)
+        return false;
+    // :235-242
+    p0t.z *= Sz;
+    p1t.z *= Sz;
+    p2t.z *= Sz;
+    float tScaled = e0 * p0t.z + e1 * p1t.z + e2 * p2t.z;
+    if (det < 0 && (tScaled >= 0 || tScaled < tMax * det))
+        return false;
+    else if (det > 0 && (tScaled <= 0 || tScaled > tMax * det))
+        return false;
+    // :245-247
+    float invDet = 1 / det;
+    float b0 = e0 * invDet, b1 = e1 * invDet, b2 = e2 * invDet;
+    float t = tScaled * invDet;
+    // :250-269
+    float maxZt = MaxComponentValue(std::abs(p0t.z), std::abs(p1t.z), std::abs(p2t.z));
+    float deltaZ = Gamma(3) * maxZt;
+    float maxXt = MaxComponentValue(std::abs(p0t.x), std::abs(p1t.x), std::abs(p2t.x));
+    float maxYt = MaxComponentValue(std::abs(p0t.y), std::abs(p1t.y), std::abs(p2t.y));
+    float deltaX = Gamma(5) * (maxXt + maxZt);
+    float deltaY = Gamma(5) * (maxYt + maxZt);
+    float deltaE = 2 * (Gamma(2) * maxXt * maxYt + deltaY * maxXt + deltaX * maxYt);
+    float maxE = MaxComponentValue(std::abs(e0), std::abs(e1), std::abs(e2));
+    float deltaT =
+        3 * (Gamma(3) * maxE * maxZt + deltaE * maxZt + deltaZ * maxE) * std::abs(invDet);
+    if (t <= deltaT)
+        return false;
+    *tOut = t;
+    *b0Out = b0;
+    *b1Out = b1;
+    *b2Out = b2;
+    return true;
+}
+
+template <bool ANY>
+inline bool Traverse(const nnbvh_oracle_node *nodes, const float *tris, const float *ray8,
+                     uint32_t *hit5, uint32_t *nodesVisitedOut, uint32_t *triTestsOut) {
+    RayCtx r = MakeRayCtx(ray8);
+    float tMax = ray8[3];
+    uint32_t hitPrim = 0xFFFFFFFFu;
+    float hitT = 0, hb0 = 0, hb1 = 0, hb2 = 0;
+    bool any = false;
+    uint32_t nodesVisited = 0, triTests = 0;
+    if (nodes) {
+        int toVisitOffset = 0, currentNodeIndex = 0;
+        int nodesToVisit[64];
+        while (true) {
+            ++nodesVisited;
+            const nnbvh_oracle_node *node = &nodes[currentNodeIndex];
+            if (BoxIntersectP(node->bounds, r, tMax)) {
+                if (node->nPrimitives > 0) {
+                    for (int i = 0; i < node->nPrimitives; ++i) {
+                        ++triTests;
+                        float t, b0, b1, b2;
+                        uint32_t prim = (uint32_t)(node->offset + i);
+                        if (TriangleIntersect(r, tMax, tris + 9 * (size_t)prim, &t, &b0, &b1,
+                                              &b2)) {
+                            if (ANY) {
+                                any = true;
+                                goto done;
+                            }
+                            hitPrim = prim;
+                            hitT = t;
+                            hb0 = b0;
+                            hb1 = b1;
+                            hb2 = b2;
+                            tMax = t;
+                        }
+                    }
+                    if (toVisitOffset == 0)
+                        break;
+                    currentNodeIndex = nodesToVisit[--toVisitOffset];
+                } else {
+                    if (r.neg[node->axis]) {
+                        nodesToVisit[toVisitOffset++] = currentNodeIndex + 1;
+                        currentNodeIndex = node->offset;
+                    } else {
+                        nodesToVisit[toVisitOffset++] = node->offset;
+                        currentNodeIndex = currentNodeIndex + 1;
+                    }
+                }
+            } else {
+                if (toVisitOffset == 0)
+                    break;
+                currentNodeIndex = nodesToVisit[--toVisitOffset];
+            }
+        }
+    }
+done:
+    if (nodesVisitedOut)
+        *nodesVisitedOut = nodesVisited;
+    if (triTestsOut)
+        *triTestsOut = triTests;
+    if (ANY)
+        return any;
+    hit5[0] = hitPrim;
+    std::memcpy(&hit5[1], &hitT, 4);
+    std::memcpy(&hit5[2], &hb0, 4);
+    std::memcpy(&hit5[3], &hb1, 4);
+    std::memcpy(&hit5[4], &hb2, 4);
+    return hitPrim != 0xFFFFFFFFu;
+}
+
+// Dynamic chunked loop over [0,n) on nThreads std::threads (<=0: all cores).
+template <typename F>
+void ParallelRays(int64_t n, int nThreads, F body) {
+    int nt = nThreads > 0 ? nThreads : (int)std::thread::hardware_concurrency();
+    if (nt < 1)
+        nt = 1;
+    const int64_t chunk = 4096;
+    if (nt == 1 || n <= chunk) {
+        for (int64_t i = 0; i < n; ++i)
+            body(i);
+        return;
+    }
+    std::atomic<int64_t> next{0};
+    auto worker = [&]() {
+        for (;;) {
+            int64_t b = next.fetch_add(chunk);
+            if (b >= n)
+                return;
+            int64_t e = std::min(n, b + chunk);
+            for (int64_t i = b; i < e; ++i)
+                body(i);
+        }
+    };
+    std::vector<std::thread> th;
+    for (int t = 1; t < nt; ++t)
+        th.emplace_back(worker);
+    worker();
+    for (auto &t : th)
+        t.join();
+}
+
+}  // namespace
+
+extern "C" {
+
+int64_t nnbvh_oracle_build(const float *triVerts9, int32_t nTris, int32_t maxPrimsInNode,
+                           int32_t splitMethod, nnbvh_oracle_node *nodesOut,
+                           int32_t *orderOut) {
+    if (splitMethod == NNBVH_ORACLE_HLBVH || nTris <= 0)
+        return -1;
+    Builder b;
+    b.maxPrimsInNode = std::min(255, maxPrimsInNode);  // aggregates.cpp:142
+    b.splitMethod = splitMethod;
+    b.orderOut = orderOut;
+    std::vector<BuildPrim> prims((size_t)nTris);
+    for (int32_t i = 0; i < nTris; ++i) {
+        // Triangle::Bounds = Union(Bounds3f(p0, p1), p2)  (shapes.cpp:294-301)
+        const float *p = triVerts9 + 9 * (size_t)i;
+        Box bb;
+        for (int k = 0; k < 3; ++k) {
+            bb.mn[k] = std::min(p[k], p[3 + k]);
+            bb.mx[k] = std::max(p[k], p[3 + k]);
+        }
+        bb = Union(bb, p + 6);
+        prims[i].primitiveIndex = (size_t)i;
+        prims[i].bounds = bb;
+    }
+    BuildNode *root = b.BuildRecursive(prims.data(), prims.size());
+    int offset = 0;
+    b.Flatten(root, nodesOut, &offset);
+    return offset;
+}
+
+void nnbvh_oracle_intersect(const nnbvh_oracle_node *nodes, const float *orderedTris9,
+                            const float *rays8, int64_t n, uint32_t *hits5,
+                            uint32_t *nodesVisited, uint32_t *triTests, int32_t nThreads) {
+    ParallelRays(n, nThreads, [&](int64_t i) {
+        Traverse<false>(nodes, orderedTris9, rays8 + 8 * i, hits5 + 5 * i,
+                        nodesVisited ? nodesVisited + i : nullptr,
+                        triTests ? triTests + i : nullptr);
+    });
+}
+
+void nnbvh_oracle_intersectP(const nnbvh_oracle_node *nodes, const float *orderedTris9,
+                             const float *rays8, int64_t n, uint8_t *occluded,
+                             uint32_t *nodesVisited, uint32_t *triTests, int32_t nThreads) {
+    ParallelRays(n, nThreads, [&](int64_t i) {
+        occluded[i] = Traverse<true>(nodes, orderedTris9, rays8 + 8 * i, nullptr,
+                                     nodesVisited ? nodesVisited + i : nullptr,
+                                     triTests ? triTests + i : nullptr)
+                          ? 1
+                          : 0;
+    });
+}
+
+int32_t nnbvh_oracle_triangle(const float *ray8, const float *p9, float *out4) {
+    RayCtx r = MakeRayCtx(ray8);
+    return TriangleIntersect(r, ray8[3], p9, &out4[0], &out4[1], &out4[2], &out4[3]) ? 1 : 0;
+}
+
+int32_t nnbvh_oracle_box(const float *ray8, const float *box6) {
+    RayCtx r = MakeRayCtx(ray8);
+    return BoxIntersectP(box6, r, ray8[3]) ? 1 : 0;
+}
+
+}  // extern "C"

@@ -1,0 +1,207 @@
+"""oracle/pyoracle.py -- TEST INFRASTRUCTURE (the checker), not product code.
+
+ctypes bindings for
+  * oracle/_build/libnnbvh_oracle.so : our CPU restatement (oracle/nnbvh_oracle.cpp)
+  * oracle/_ref/libnnbvh_ref.so      : the UNMODIFIED reference translation units
+                                       behind oracle/ref_driver.cpp (optional)
+
+Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline /
+--impl reference legs may import this module.  The product package
+(nn_bvh_b200/) must never do so.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+import subprocess
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ORACLE_SO = os.path.join(HERE, "_build", "libnnbvh_oracle.so")
+REF_SO = os.path.join(HERE, "_ref", "libnnbvh_ref.so")
+MISS = 0xFFFFFFFF
+
+SPLIT = {"sah": 0, "hlbvh": 1, "middle": 2, "equal": 3}
+
+
+def build(ref: bool = True) -> None:
+    """Compile the restatement (always) and oracle/_ref (when /root/reference exists)."""
+    targets = ["oracle"] + (["ref"] if ref else [])
+    subprocess.check_call(["make", "-s", "-C", HERE, "-j8"] + targets)
+
+
+def _p(a):
+    return a.ctypes.data_as(ctypes.c_void_p)
+
+
+class Oracle:
+    """The CPU restatement."""
+
+    def __init__(self):
+        if not os.path.exists(ORACLE_SO):
+            build(ref=False)
+        L = self.lib = ctypes.CDLL(ORACLE_SO)
+        L.nnbvh_oracle_build.restype = ctypes.c_int64
+        L.nnbvh_oracle_build.argtypes = [ctypes.c_void_p, ctypes.c_int32, ctypes.c_int32,
+                                         ctypes.c_int32, ctypes.c_void_p, ctypes.c_void_p]
+        for f in (L.nnbvh_oracle_intersect, L.nnbvh_oracle_intersectP):
+            f.restype = None
+            f.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int64,
+                          ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int32]
+        L.nnbvh_oracle_triangle.argtypes = [ctypes.c_void_p] * 3
+        L.nnbvh_oracle_box.argtypes = [ctypes.c_void_p] * 2
+
+    def build_bvh(self, tris9: np.ndarray, max_prims: int = 4, split: str = "sah"):
+        """tris9: (T,9) float32 in original order -> (nodes (M,8) uint32 view, order (T,) int32)."""
+        tris9 = np.ascontiguousarray(tris9, dtype=np.float32).reshape(-1, 9)
+        T = tris9.shape[0]
+        nodes = np.zeros((2 * T, 8), dtype=np.uint32)
+        order = np.zeros(T, dtype=np.int32)
+        n = self.lib.nnbvh_oracle_build(_p(tris9), T, max_prims, SPLIT[split], _p(nodes), _p(order))
+        if n < 0:
+            raise ValueError("oracle build failed")
+        return nodes[:n].copy(), order
+
+    def intersect(self, nodes, ordered_tris9, rays8, counters=False, threads=0):
+        rays8 = np.ascontiguousarray(rays8, dtype=np.float32).reshape(-1, 8)
+        n = rays8.shape[0]
+        hits = np.zeros((n, 5), dtype=np.uint32)
+        nv = np.zeros(n, dtype=np.uint32) if counters else None
+        tt = np.zeros(n, dtype=np.uint32) if counters else None
+        self.lib.nnbvh_oracle_intersect(_p(nodes), _p(ordered_tris9), _p(rays8), n, _p(hits),
+                                        _p(nv) if counters else None,
+                                        _p(tt) if counters else None, threads)
+        return (hits, nv, tt) if counters else hits
+
+    def intersect_p(self, nodes, ordered_tris9, rays8, counters=False, threads=0):
+        rays8 = np.ascontiguousarray(rays8, dtype=np.float32).reshape(-1, 8)
+        n = rays8.shape[0]
+        occ = np.zeros(n, dtype=np.uint8)
+        nv = np.zeros(n, dtype=np.uint32) if counters else None
+        tt = np.zeros(n, dtype=np.uint32) if counters else None
+        self.lib.nnbvh_oracle_intersectP(_p(nodes), _p(ordered_tris9), _p(rays8), n, _p(occ),
+                                         _p(nv) if counters else None,
+                                         _p(tt) if counters else None, threads)
+        return (occ, nv, tt) if counters else occ
+
+    def triangle(self, ray8, p9):
+        ray8 = np.ascontiguousarray(ray8, dtype=np.float32)
+        p9 = np.ascontiguousarray(p9, dtype=np.float32)
+        out = np.zeros(4, dtype=np.float32)
+        hit = self.lib.nnbvh_oracle_triangle(_p(ray8), _p(p9), _p(out))
+        return bool(hit), out
+
+    def box(self, ray8, box6):
+        ray8 = np.ascontiguousarray(ray8, dtype=np.float32)
+        box6 = np.ascontiguousarray(box6, dtype=np.float32)
+        return bool(self.lib.nnbvh_oracle_box(_p(ray8), _p(box6)))
+
+
+def ref_available() -> bool:
+    return os.path.exists(REF_SO)
+
+
+class Reference:
+    """The unmodified reference code (oracle/_ref), when it has been built."""
+
+    _inited = False
+
+    def __init__(self, threads: int = 0):
+        if not ref_available():
+            raise FileNotFoundError(REF_SO)
+        L = self.lib = ctypes.CDLL(REF_SO)
+        L.nnbvh_ref_scene_create.restype = ctypes.c_void_p
+        L.nnbvh_ref_scene_create.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p,
+                                             ctypes.c_int, ctypes.c_int, ctypes.c_int]
+        L.nnbvh_ref_scene_num_nodes.argtypes = [ctypes.c_void_p]
+        L.nnbvh_ref_scene_export.argtypes = [ctypes.c_void_p] * 3
+        L.nnbvh_ref_intersect.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int64,
+                                          ctypes.c_void_p, ctypes.c_int]
+        L.nnbvh_ref_intersect_only.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int64,
+                                               ctypes.c_void_p]
+        L.nnbvh_ref_intersectP.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int64,
+                                           ctypes.c_void_p, ctypes.c_int]
+        L.nnbvh_ref_triangle.argtypes = [ctypes.c_void_p] * 3
+        L.nnbvh_ref_box.argtypes = [ctypes.c_void_p] * 2
+        L.nnbvh_ref_stats.argtypes = [ctypes.c_void_p] * 3
+        L.nnbvh_ref_loop_subdivide.argtypes = [ctypes.c_int, ctypes.c_void_p, ctypes.c_int,
+                                               ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p,
+                                               ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p]
+        L.nnbvh_ref_free.argtypes = [ctypes.c_void_p]
+        L.nnbvh_ref_set_threads(threads)
+
+    def set_threads(self, n: int):
+        self.lib.nnbvh_ref_set_threads(n)
+
+    @property
+    def threads(self) -> int:
+        return self.lib.nnbvh_ref_threads()
+
+    def scene(self, tris9: np.ndarray, max_prims: int = 4, split: str = "sah"):
+        """Build the reference BVHAggregate over a de-indexed triangle soup."""
+        tris9 = np.ascontiguousarray(tris9, dtype=np.float32).reshape(-1, 9)
+        T = tris9.shape[0]
+        verts = tris9.reshape(-1, 3)
+        idx = np.arange(3 * T, dtype=np.int32)
+        h = self.lib.nnbvh_ref_scene_create(_p(verts), 3 * T, _p(idx), T, max_prims, SPLIT[split])
+        return ctypes.c_void_p(h)
+
+    def export(self, scene, n_tris: int):
+        n = self.lib.nnbvh_ref_scene_num_nodes(scene)
+        nodes = np.zeros((n, 8), dtype=np.uint32)
+        order = np.zeros(n_tris, dtype=np.int32)
+        self.lib.nnbvh_ref_scene_export(scene, _p(nodes), _p(order))
+        return nodes, order
+
+    def intersect(self, scene, rays8, parallel=True):
+        rays8 = np.ascontiguousarray(rays8, dtype=np.float32).reshape(-1, 8)
+        hits = np.zeros((rays8.shape[0], 5), dtype=np.uint32)
+        self.lib.nnbvh_ref_intersect(scene, _p(rays8), rays8.shape[0], _p(hits), int(parallel))
+        return hits
+
+    def intersect_only(self, scene, rays8):
+        rays8 = np.ascontiguousarray(rays8, dtype=np.float32).reshape(-1, 8)
+        hit = np.zeros(rays8.shape[0], dtype=np.uint8)
+        self.lib.nnbvh_ref_intersect_only(scene, _p(rays8), rays8.shape[0], _p(hit))
+        return hit
+
+    def intersect_p(self, scene, rays8, parallel=True):
+        rays8 = np.ascontiguousarray(rays8, dtype=np.float32).reshape(-1, 8)
+        occ = np.zeros(rays8.shape[0], dtype=np.uint8)
+        self.lib.nnbvh_ref_intersectP(scene, _p(rays8), rays8.shape[0], _p(occ), int(parallel))
+        return occ
+
+    def triangle(self, ray8, p9):
+        ray8 = np.ascontiguousarray(ray8, dtype=np.float32)
+        p9 = np.ascontiguousarray(p9, dtype=np.float32)
+        out = np.zeros(4, dtype=np.float32)
+        hit = self.lib.nnbvh_ref_triangle(_p(ray8), _p(p9), _p(out))
+        return bool(hit), out
+
+    def box(self, ray8, box6):
+        ray8 = np.ascontiguousarray(ray8, dtype=np.float32)
+        box6 = np.ascontiguousarray(box6, dtype=np.float32)
+        return bool(self.lib.nnbvh_ref_box(_p(ray8), _p(box6)))
+
+    def stats(self):
+        """(nodesVisited, triTests, triHits) of single-threaded calls since the last read."""
+        a, b, c = ctypes.c_int64(), ctypes.c_int64(), ctypes.c_int64()
+        self.lib.nnbvh_ref_stats(ctypes.byref(a), ctypes.byref(b), ctypes.byref(c))
+        return a.value, b.value, c.value
+
+    def loop_subdivide(self, levels: int, indices: np.ndarray, verts: np.ndarray):
+        indices = np.ascontiguousarray(indices, dtype=np.int32).ravel()
+        verts = np.ascontiguousarray(verts, dtype=np.float32).reshape(-1, 3)
+        oi, ov = ctypes.c_void_p(), ctypes.c_void_p()
+        ni, nv = ctypes.c_int(), ctypes.c_int()
+        self.lib.nnbvh_ref_loop_subdivide(levels, _p(indices), indices.size, _p(verts),
+                                          verts.shape[0], ctypes.byref(oi), ctypes.byref(ni),
+                                          ctypes.byref(ov), ctypes.byref(nv))
+        idx = np.ctypeslib.as_array(ctypes.cast(oi, ctypes.POINTER(ctypes.c_int32)),
+                                    (ni.value,)).copy()
+        v = np.ctypeslib.as_array(ctypes.cast(ov, ctypes.POINTER(ctypes.c_float)),
+                                  (nv.value * 3,)).copy().reshape(-1, 3)
+        self.lib.nnbvh_ref_free(oi)
+        self.lib.nnbvh_ref_free(ov)
+        return idx, v

@@ -1,0 +1,355 @@
+// oracle/ref_driver.cpp -- TEST INFRASTRUCTURE, not product code.
+//
+// A thin extern "C" driver around the UNMODIFIED reference translation units
+// (compiled where they lie under /root/reference/src by oracle/Makefile into
+// oracle/_ref/libnnbvh_ref.so).  It runs the reference's own
+//   BVHAggregate ctor / flattenBVH     (src/pbrt/cpu/aggregates.cpp:140-190, 505-522)
+//   BVHAggregate::Intersect/IntersectP (src/pbrt/cpu/aggregates.cpp:529-624)
+//   Triangle::Intersect/IntersectP     (src/pbrt/shapes.cpp:320-358)
+//   IntersectTriangle                  (src/pbrt/shapes.cpp:172-273)
+//   Bounds3f::IntersectP               (src/pbrt/util/vecmath.h:1573-1608)
+// so that the C restatement in oracle/nnbvh_oracle.cpp and the CUDA engine can
+// be pinned against the real thing.  Nothing here is copied from the
+// reference; it only #includes its headers at build time.
+//
+// Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline /
+// --impl reference legs may load the resulting library.
+
+#include <algorithm>
+#include <atomic>
+#include <cstdint>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <functional>
+#include <map>
+#include <memory>
+#include <mutex>
+#include <sstream>
+#include <string>
+#include <thread>
+#include <vector>
+
+// BVHAggregate::nodes/primitives, SimplePrimitive::shape and
+// Triangle::triIndex are private (cpu/aggregates.h:66-69, cpu/primitive.h:76-79,
+// shapes.h:1186-1189); the reference tree is read-only, so the driver opens
+// them for itself.  Layout is unaffected by access specifiers.
+#define private public
+#include <pbrt/pbrt.h>
+#include <pbrt/cpu/aggregates.h>
+#include <pbrt/cpu/primitive.h>
+#include <pbrt/options.h>
+#include <pbrt/shapes.h>
+#include <pbrt/util/buffercache.h>
+#include <pbrt/util/log.h>
+#include <pbrt/util/loopsubdiv.h>
+#include <pbrt/util/mesh.h>
+#include <pbrt/util/parallel.h>
+#include <pbrt/util/stats.h>
+#include <pbrt/util/transform.h>
+#include <pbrt/util/vecmath.h>
+#undef private
+
+namespace {
+
+// Mirror of the 32-byte record defined in cpu/aggregates.cpp:128-137 (the
+// definition lives in the .cpp, so the driver states the layout itself and
+// static_asserts it).
+struct alignas(32) NodeMirror {
+    float bounds[6];
+    int offset;
+    uint16_t nPrimitives;
+    uint8_t axis;
+    uint8_t pad;
+};
+static_assert(sizeof(NodeMirror) == 32, "LinearBVHNode must be 32 bytes");
+
+struct RefScene {
+    pbrt::TriangleMesh *mesh = nullptr;
+    pbrt::BVHAggregate *agg = nullptr;
+    int nTris = 0;
+    int nNodes = 0;
+    std::vector<int> orderedToOrig;  // ordered prim index -> original triangle
+    std::vector<int> origToOrdered;
+};
+
+bool g_inited = false;
+
+int CountNodes(const NodeMirror *nodes) {
+    // Pre-order layout: the node count is one past the largest index reachable.
+    int maxIdx = 0;
+    std::vector<int> stack{0};
+    while (!stack.empty()) {
+        int i = stack.back();
+        stack.pop_back();
+        maxIdx = std::max(maxIdx, i);
+        if (nodes[i].nPrimitives == 0) {
+            stack.push_back(i + 1);
+            stack.push_back(nodes[i].offset);
+        }
+    }
+    return maxIdx + 1;
+}
+
+inline pbrt::Ray MakeRay(const float *r) {
+    return pbrt::Ray(pbrt::Point3f(r[0], r[1], r[2]), pbrt::Vector3f(r[4], r[5], r[6]), r[7]);
+}
+
+}  // namespace
+
+extern "C" {
+
+// nThreads <= 0 -> all cores (ParallelInit(-1) semantics, util/parallel.h:30).
+int nnbvh_ref_init(int nThreads) {
+    if (g_inited)
+        return 0;
+    pbrt::PBRTOptions opt;
+    opt.nThreads = nThreads > 0 ? nThreads : 0;
+    opt.quiet = true;
+    pbrt::Options = new pbrt::PBRTOptions(opt);
+    pbrt::InitLogging(pbrt::LogLevel::Error, "", false, false);
+    pbrt::ParallelInit(nThreads > 0 ? nThreads : pbrt::AvailableCores());
+    pbrt::Triangle::Init({});
+    pbrt::InitBufferCaches();
+    g_inited = true;
+    return 0;
+}
+
+// Re-create the reference's thread pool with n workers (n<=0: all cores).
+// One thread makes the >128K-primitive parallel build deterministic
+// (cpu/aggregates.cpp:359-370 orders leaves by an atomic fetch_add).
+int nnbvh_ref_set_threads(int nThreads) {
+    if (!g_inited)
+        return nnbvh_ref_init(nThreads);
+    pbrt::ParallelCleanup();
+    pbrt::ParallelInit(nThreads > 0 ? nThreads : pbrt::AvailableCores());
+    return 0;
+}
+
+int nnbvh_ref_threads(void) {
+    return pbrt::RunningThreads();
+}
+
+// splitMethod: 0 SAH, 1 HLBVH, 2 Middle, 3 EqualCounts (cpu/aggregates.h:31).
+void *nnbvh_ref_scene_create(const float *verts, int nVerts, const int *indices, int nTris,
+                             int maxPrimsInNode, int splitMethod) {
+    if (!g_inited)
+        nnbvh_ref_init(0);
+    auto *s = new RefScene;
+    std::vector<int> idx(indices, indices + 3 * (size_t)nTris);
+    std::vector<pbrt::Point3f> p(nVerts);
+    for (int i = 0; i < nVerts; ++i)
+        p[i] = pbrt::Point3f(verts[3 * i], verts[3 * i + 1], verts[3 * i + 2]);
+    std::vector<int> face(nTris);
+    for (int i = 0; i < nTris; ++i)
+        face[i] = i;  // faceIndex of a hit == original triangle id
+    pbrt::Allocator alloc;
+    s->mesh = alloc.new_object<pbrt::TriangleMesh>(pbrt::Transform(), false, idx, p,
+                                                   std::vector<pbrt::Vector3f>(),
+                                                   std::vector<pbrt::Normal3f>(),
+                                                   std::vector<pbrt::Point2f>(), face, alloc);
+    pstd::vector<pbrt::Shape> shapes = pbrt::Triangle::CreateTriangles(s->mesh, alloc);
+    std::vector<pbrt::Primitive> prims;
+    prims.reserve(nTris);
+    for (pbrt::Shape sh : shapes)
+        prims.push_back(pbrt::Primitive(
+            alloc.new_object<pbrt::SimplePrimitive>(sh, pbrt::Material(nullptr))));
+    s->nTris = nTris;
+    s->agg = new pbrt::BVHAggregate(std::move(prims), maxPrimsInNode,
+                                    (pbrt::BVHAggregate::SplitMethod)splitMethod);
+    s->nNodes = CountNodes(reinterpret_cast<const NodeMirror *>(s->agg->nodes));
+    s->orderedToOrig.resize(nTris);
+    s->origToOrdered.resize(nTris);
+    for (int i = 0; i < nTris; ++i) {
+        const pbrt::SimplePrimitive *sp = s->agg->primitives[i].Cast<pbrt::SimplePrimitive>();
+        const pbrt::Triangle *tri = sp->shape.Cast<pbrt::Triangle>();
+        s->orderedToOrig[i] = tri->triIndex;
+        s->origToOrdered[tri->triIndex] = i;
+    }
+    return s;
+}
+
+int nnbvh_ref_scene_num_nodes(void *scene) {
+    return ((RefScene *)scene)->nNodes;
+}
+int nnbvh_ref_scene_num_prims(void *scene) {
+    return ((RefScene *)scene)->nTris;
+}
+
+// nodesOut: nNodes*32 bytes, byte-identical LinearBVHNode records (pad zeroed).
+// orderOut: nTris ints, ordered prim -> original triangle.
+void nnbvh_ref_scene_export(void *scene, void *nodesOut, int *orderOut) {
+    RefScene *s = (RefScene *)scene;
+    const NodeMirror *src = reinterpret_cast<const NodeMirror *>(s->agg->nodes);
+    NodeMirror *dst = (NodeMirror *)nodesOut;
+    for (int i = 0; i < s->nNodes; ++i) {
+        dst[i] = src[i];
+        dst[i].pad = 0;
+        if (dst[i].nPrimitives > 0)
+            dst[i].axis = 0;  // axis is uninitialised for leaves in the reference
+    }
+    std::memcpy(orderOut, s->orderedToOrig.data(), sizeof(int) * s->nTris);
+}
+
+// rays: n * 8 floats {ox,oy,oz,tMax,dx,dy,dz,time}.  hits: n * 5 words
+// {prim (ordered index, 0xFFFFFFFF miss), t, b0, b1, b2}.
+// parallel != 0 -> ParallelFor over rays exactly as CPUAggregate::IntersectClosest
+// does (wavefront/aggregate.cpp:42-57).
+void nnbvh_ref_intersect(void *scene, const float *rays, int64_t n, uint32_t *hits,
+                         int parallel) {
+    RefScene *s = (RefScene *)scene;
+    pbrt::Primitive top(s->agg);
+    auto body = [&](int64_t i) {
+        const float *r = rays + 8 * i;
+        pbrt::Ray ray = MakeRay(r);
+        pstd::optional<pbrt::ShapeIntersection> si = top.Intersect(ray, r[3]);
+        uint32_t *h = hits + 5 * i;
+        if (!si) {
+            h[0] = 0xFFFFFFFFu;
+            h[1] = h[2] = h[3] = h[4] = 0;
+            return;
+        }
+        int orig = si->intr.faceIndex;
+        h[0] = (uint32_t)s->origToOrdered[orig];
+        // The barycentrics do not survive in SurfaceInteraction; recover them
+        // from the reference's own IntersectTriangle on the winning triangle
+        // (b and t do not depend on tMax, shapes.cpp:245-247).
+        const int *v = &s->mesh->vertexIndices[3 * orig];
+        pstd::optional<pbrt::TriangleIntersection> ti = pbrt::IntersectTriangle(
+            ray, pbrt::Infinity, s->mesh->p[v[0]], s->mesh->p[v[1]], s->mesh->p[v[2]]);
+        float t = si->tHit, b0 = 0, b1 = 0, b2 = 0;
+        if (ti) {
+            b0 = ti->b0;
+            b1 = ti->b1;
+            b2 = ti->b2;
+        }
+        std::memcpy(&h[1], &t, 4);
+        std::memcpy(&h[2], &b0, 4);
+        std::memcpy(&h[3], &b1, 4);
+        std::memcpy(&h[4], &b2, 4);
+    };
+    if (parallel)
+        pbrt::ParallelFor(0, n, body);
+    else
+        for (int64_t i = 0; i < n; ++i)
+            body(i);
+}
+
+// Timing variant: the reference as-is, nothing but the call and a 1-byte result.
+void nnbvh_ref_intersect_only(void *scene, const float *rays, int64_t n, uint8_t *hit) {
+    RefScene *s = (RefScene *)scene;
+    pbrt::Primitive top(s->agg);
+    pbrt::ParallelFor(0, n, [&](int64_t i) {
+        const float *r = rays + 8 * i;
+        hit[i] = top.Intersect(MakeRay(r), r[3]).has_value();
+    });
+}
+
+void nnbvh_ref_intersectP(void *scene, const float *rays, int64_t n, uint8_t *occluded,
+                          int parallel) {
+    RefScene *s = (RefScene *)scene;
+    pbrt::Primitive top(s->agg);
+    auto body = [&](int64_t i) {
+        const float *r = rays + 8 * i;
+        occluded[i] = top.IntersectP(MakeRay(r), r[3]) ? 1 : 0;
+    };
+    if (parallel)
+        pbrt::ParallelFor(0, n, body);
+    else
+        for (int64_t i = 0; i < n; ++i)
+            body(i);
+}
+
+// Direct known-answer hooks ---------------------------------------------------
+int nnbvh_ref_triangle(const float *ray8, const float *p9, float *out4) {
+    pstd::optional<pbrt::TriangleIntersection> ti = pbrt::IntersectTriangle(
+        MakeRay(ray8), ray8[3], pbrt::Point3f(p9[0], p9[1], p9[2]),
+        pbrt::Point3f(p9[3], p9[4], p9[5]), pbrt::Point3f(p9[6], p9[7], p9[8]));
+    if (!ti)
+        return 0;
+    out4[0] = ti->t;
+    out4[1] = ti->b0;
+    out4[2] = ti->b1;
+    out4[3] = ti->b2;
+    return 1;
+}
+
+int nnbvh_ref_box(const float *ray8, const float *box6) {
+    pbrt::Bounds3f b(pbrt::Point3f(box6[0], box6[1], box6[2]),
+                     pbrt::Point3f(box6[3], box6[4], box6[5]));
+    // Bounds3f(p1,p2) takes min/max of its arguments; callers pass pMin<=pMax.
+    pbrt::Point3f o(ray8[0], ray8[1], ray8[2]);
+    pbrt::Vector3f d(ray8[4], ray8[5], ray8[6]);
+    pbrt::Vector3f invDir(1 / d.x, 1 / d.y, 1 / d.z);
+    int dirIsNeg[3] = {int(invDir.x < 0), int(invDir.y < 0), int(invDir.z < 0)};
+    return b.IntersectP(o, d, ray8[3], invDir, dirIsNeg) ? 1 : 0;
+}
+
+// Loop subdivision through the reference (util/loopsubdiv.cpp) so that
+// config 1's killeroo geometry matches what pbrt itself would trace.
+// Returns a malloc'd mesh via out params; caller frees with nnbvh_ref_free.
+int nnbvh_ref_loop_subdivide(int nLevels, const int *indices, int nIdx, const float *verts,
+                             int nVerts, int **outIdx, int *outNIdx, float **outVerts,
+                             int *outNVerts) {
+    if (!g_inited)
+        nnbvh_ref_init(0);
+    std::vector<int> idx(indices, indices + nIdx);
+    std::vector<pbrt::Point3f> p(nVerts);
+    for (int i = 0; i < nVerts; ++i)
+        p[i] = pbrt::Point3f(verts[3 * i], verts[3 * i + 1], verts[3 * i + 2]);
+    pbrt::Transform identity;
+    pbrt::TriangleMesh *m =
+        pbrt::LoopSubdivide(&identity, false, nLevels, idx, p, pbrt::Allocator());
+    *outNIdx = 3 * m->nTriangles;
+    *outNVerts = m->nVertices;
+    *outIdx = (int *)std::malloc(sizeof(int) * *outNIdx);
+    *outVerts = (float *)std::malloc(sizeof(float) * 3 * *outNVerts);
+    std::memcpy(*outIdx, m->vertexIndices, sizeof(int) * *outNIdx);
+    for (int i = 0; i < m->nVertices; ++i) {
+        (*outVerts)[3 * i] = m->p[i].x;
+        (*outVerts)[3 * i + 1] = m->p[i].y;
+        (*outVerts)[3 * i + 2] = m->p[i].z;
+    }
+    return 0;
+}
+
+void nnbvh_ref_free(void *p) {
+    std::free(p);
+}
+
+// Counter read-out: merges the calling thread's thread-local STAT counters
+// (cpu/aggregates.cpp:27, shapes.cpp:148) into the global accumulator and
+// parses PrintStats.  Only meaningful after single-threaded (parallel=0)
+// calls made on this same thread.  Resets the counters.
+int nnbvh_ref_stats(int64_t *nodesVisited, int64_t *triTests, int64_t *triHits) {
+    pbrt::ReportThreadStats();
+    char *buf = nullptr;
+    size_t len = 0;
+    FILE *f = open_memstream(&buf, &len);
+    pbrt::PrintStats(f);
+    std::fclose(f);
+    pbrt::ClearStats();
+    *nodesVisited = 0;
+    *triTests = 0;
+    *triHits = 0;
+    std::istringstream in(std::string(buf ? buf : "", len));
+    std::free(buf);
+    std::string line;
+    while (std::getline(in, line)) {
+        if (line.find("Nodes visited") != std::string::npos) {
+            size_t p = line.find("Nodes visited") + 13;
+            *nodesVisited = std::strtoll(line.c_str() + p, nullptr, 10);
+        } else if (line.find("Ray-Triangle intersection tests") != std::string::npos) {
+            // "<hits> / <tests> (x.xx%)"
+            size_t p = line.find("tests") + 5;
+            char *end = nullptr;
+            *triHits = std::strtoll(line.c_str() + p, &end, 10);
+            while (*end && (*end == ' ' || *end == '/'))
+                ++end;
+            *triTests = std::strtoll(end, nullptr, 10);
+        }
+    }
+    return 0;
+}
+
+}  // extern "C"
