@@ -1,0 +1,374 @@
+#!/usr/bin/env python3
+"""bench.py -- Mrays/s of the closest-hit + shadow hot path on B200 (BASELINE.json metric).
+
+  python bench.py --gpus N --steps K --warmup W            (torchrun for N > 1)
+  python bench.py --impl reference ...                      (the reference's CPU path)
+
+A "step" is one pass of the hot path over one batch: `--rays` incoherent
+diffuse-bounce rays through BVHAggregate::Intersect (closest hit) plus `--rays`
+shadow rays through IntersectP (any hit) -- BASELINE.json configs[1] (default
+8M + 8M).  The conference scene is missing from the reference tree
+(.MISSING_LARGE_BLOBS:12); the workload is its stand-in, the reference's own
+bathroom scene (592k triangles) from scene_cache/, else a procedural room, and
+config.workload says which.
+
+value  : whole-job Mrays/s, rays resident in HBM, CUDA-event timed (max over ranks).
+e2e    : same metric through the C ABI with pinned HOST buffers (H2D/D2H inside).
+roofline: closest-hit traversal kernel, algorithmic bytes / event-timed duration.
+cpu_baseline / --impl reference: the unmodified reference TUs (oracle/_ref) if built,
+         else the oracle port, on the host cores.
+Only the cpu_baseline / reference legs touch oracle/; the product path never does.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "Mrays/s closest-hit+shadow"
+UNIT = "Mrays/s"
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--scene", default="bathroom")
+    ap.add_argument("--rays", type=int, default=8 << 20, help="rays per kind per step per GPU")
+    ap.add_argument("--cpu-seconds", type=float, default=12.0, help="budget of the cpu_baseline leg")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    return ap.parse_args()
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index=0):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                 "-i", str(self.index), "-lms", "100"],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+        except OSError:
+            self.proc = None
+            return
+        self.t = threading.Thread(target=self._read, daemon=True)
+        self.t.start()
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        for r in self.rows:
+            try:
+                sm.append(float(r[1]))
+                mx.append(float(r[2]))
+            except (ValueError, IndexError):
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown",
+                                "sw_power_cap"), r[4:8]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": float(np.median(sm)) if sm else None,
+                "sm_max_mhz": max(mx) if mx else None, "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+def load_workload(args, trace, rank):
+    """-> dict(tris, nodes, order, ordered, bounce, shadow, name)."""
+    import nn_bvh_b200 as nb
+    from nn_bvh_b200 import rays as R
+    from nn_bvh_b200 import scenes
+    tris, cam, name = scenes.load(args.scene)
+    nodes, order = nb.build_bvh(tris, 4, "sah")     # reference defaults (aggregates.cpp:727,742)
+    ordered = tris[order]
+    return dict(tris=tris, cam=cam, nodes=nodes, order=order, ordered=ordered, name=name)
+
+
+def make_rays(w, trace, n, rank):
+    from nn_bvh_b200 import rays as R
+    return R.bounce_and_shadow_rays(trace, w["ordered"], w["cam"], n, seed=2 + 1000 * rank)
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+# ---------------------------------------------------------------------------
+# CPU legs (the only code in this file that may touch oracle/)
+# ---------------------------------------------------------------------------
+class CpuPath:
+    """The reference's own CPU implementation: oracle/_ref (unmodified reference TUs,
+    ParallelFor over rays like CPUAggregate::IntersectClosest, wavefront/aggregate.cpp:42-68)
+    when it was built in the dev container, else the oracle port on std::threads."""
+
+    def __init__(self, w):
+        from oracle import pyoracle
+        self.w = w
+        self.cores = os.cpu_count() or 1
+        if pyoracle.ref_available():
+            self.kind = "reference"
+            self.ref = pyoracle.Reference(threads=0)
+            self.cores = self.ref.threads
+            # the reference builds its own tree from the same soup (parallel build: leaf
+            # order may differ from ours, the hit SET does not matter for timing)
+            self.scene = self.ref.scene(w["tris"], 4, "sah")
+        else:
+            self.kind = "port"
+            self.orc = pyoracle.Oracle()
+            self.nodes = np.ascontiguousarray(w["nodes"]).view(np.uint32).reshape(-1, 8)
+
+    def closest(self, rays):
+        r = np.ascontiguousarray(rays).view(np.float32).reshape(-1, 8)
+        if self.kind == "reference":
+            return self.ref.intersect_only(self.scene, r)
+        return self.orc.intersect(self.nodes, self.w["ordered"], r, threads=0)
+
+    def shadow(self, rays):
+        r = np.ascontiguousarray(rays).view(np.float32).reshape(-1, 8)
+        if self.kind == "reference":
+            return self.ref.intersect_p(self.scene, r, parallel=True)
+        return self.orc.intersect_p(self.nodes, self.w["ordered"], r, threads=0)
+
+    def timed(self, bounce, shadow, budget_s, chunk=1 << 18):
+        """Trace chunks of (closest + shadow) until ~budget_s; -> (Mrays/s, rays, seconds)."""
+        self.closest(bounce[:chunk // 8])  # warm-up
+        done, t0 = 0, time.perf_counter()
+        n = min(len(bounce), len(shadow))
+        while done < n and time.perf_counter() - t0 < budget_s:
+            e = min(n, done + chunk)
+            self.closest(bounce[done:e])
+            self.shadow(shadow[done:e])
+            done = e
+        dt = time.perf_counter() - t0
+        return 2 * done / dt / 1e6, 2 * done, dt
+
+
+def run_reference(args):
+    """--impl reference: the reference CPU path on this box's host cores; rank 0 only."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    from oracle import pyoracle
+    orc = pyoracle.Oracle()
+    w = load_workload(args, None, 0)
+    nodes32 = np.ascontiguousarray(w["nodes"]).view(np.uint32).reshape(-1, 8)
+
+    def trace(r):   # primary rays for the ray generator: oracle port, all threads
+        import nn_bvh_b200 as nb
+        h = orc.intersect(nodes32, w["ordered"], np.ascontiguousarray(r).view(np.float32).reshape(-1, 8))
+        return h.view(nb.HIT_DTYPE).reshape(-1)
+
+    cpu = CpuPath(w)
+    # bounded sample per step: sized from a short probe so the whole run ends in minutes
+    probe_b, probe_s = make_rays(w, trace, 1 << 17, 0)
+    mr, _, _ = cpu.timed(probe_b, probe_s, 2.0, chunk=1 << 16)
+    per_step = int(max(1 << 16, min(args.rays, mr * 1e6 * 1.5 / 2)))   # ~1.5 s per step
+    bounce, shadow = make_rays(w, trace, per_step, 0)
+    for _ in range(max(args.warmup, 1)):
+        cpu.closest(bounce[: per_step // 4])
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        cpu.closest(bounce)
+        cpu.shadow(shadow)
+    dt = time.perf_counter() - t0
+    val = 2 * per_step * args.steps / dt / 1e6
+    sample = f"{per_step} closest + {per_step} shadow rays per step (bounded sample of {args.rays}+{args.rays})"
+    line = {"impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+            "data": "synthetic rays over " + w["name"],
+            "config": {"workload": f"{w['name']}: incoherent diffuse-bounce closest-hit + shadow any-hit",
+                       "triangles": int(len(w["tris"])), "sample": sample},
+            "cpu_baseline": {"value": val, "unit": UNIT, "cores": cpu.cores, "kind": cpu.kind,
+                             "sample": sample},
+            "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line), flush=True)
+
+
+# ---------------------------------------------------------------------------
+# GPU arm
+# ---------------------------------------------------------------------------
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    import nn_bvh_b200 as nb
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; nn_bvh_b200 has no CPU path to time")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    w = load_workload(args, None, rank)
+    agg = nb.GPUBVHAggregate(nodes=w["nodes"], ordered_tris9=w["ordered"], order=w["order"],
+                             device=local)
+    bounce, shadow = make_rays(w, lambda r: agg.IntersectBatch(r), args.rays, rank)
+    n = args.rays
+
+    # ---- device-resident buffers; engine launches on torch's current stream ----
+    stream = torch.cuda.current_stream()
+    agg.set_stream(stream.cuda_stream)
+    d_b = torch.from_numpy(bounce.view(np.float32).reshape(-1, 8)).to(dev)
+    d_s = torch.from_numpy(shadow.view(np.float32).reshape(-1, 8)).to(dev)
+    d_hits = torch.zeros((n, 5), dtype=torch.int32, device=dev)
+    d_occ = torch.zeros(n, dtype=torch.uint8, device=dev)
+    gather_hits = gather_occ = None
+    if world > 1 and rank == 0:   # NCCL gather of hit records to rank 0
+        gather_hits = [torch.empty_like(d_hits) for _ in range(world)]
+        gather_occ = [torch.empty_like(d_occ) for _ in range(world)]
+
+    def step(ev_mid=None):
+        agg.IntersectBatch(d_b, hits=d_hits, n=n)
+        if ev_mid is not None:
+            ev_mid.record(stream)
+        agg.IntersectPBatch(d_s, occluded=d_occ, n=n)
+        if world > 1:
+            dist.gather(d_hits, gather_hits, dst=0)
+            dist.gather(d_occ, gather_occ, dst=0)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(max(args.warmup, 3)):
+        step()
+    barrier()
+    clocks = ClockSampler(local)
+    if rank == 0:
+        clocks.start()
+    l0 = agg.launch_count()
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(3 * args.steps + 1)]
+    barrier()
+    ev[0].record(stream)
+    for k in range(args.steps):
+        step(ev[3 * k + 1])
+        ev[3 * k + 3].record(stream)
+    barrier()
+    launches = agg.launch_count() - l0
+    total_ms = ev[0].elapsed_time(ev[3 * args.steps])
+    closest_ms = float(np.mean([ev[3 * k].elapsed_time(ev[3 * k + 1])
+                                for k in range(args.steps)]))
+    clk = clocks.stop() if rank == 0 else None
+    t = torch.tensor([total_ms, closest_ms], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    total_ms, closest_ms = t.tolist()
+    value = world * 2 * n * args.steps / (total_ms / 1e3) / 1e6
+
+    # ---- e2e: pinned host buffers through the C ABI, copies inside the timed region ----
+    agg.set_stream(0)   # engine's own streams for the chunked H2D / kernel / D2H pipeline
+    h_b = torch.from_numpy(bounce.view(np.float32).reshape(-1, 8)).pin_memory()
+    h_s = torch.from_numpy(shadow.view(np.float32).reshape(-1, 8)).pin_memory()
+    h_hits = torch.zeros((n, 5), dtype=torch.int32).pin_memory()
+    h_occ = torch.zeros(n, dtype=torch.uint8).pin_memory()
+    e2e_steps = max(2, min(args.steps, 5))
+    for _ in range(2):
+        agg.IntersectBatch(h_b, hits=h_hits, n=n)
+        agg.IntersectPBatch(h_s, occluded=h_occ, n=n)
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        agg.IntersectBatch(h_b, hits=h_hits, n=n)
+        agg.IntersectPBatch(h_s, occluded=h_occ, n=n)
+    torch.cuda.synchronize()
+    e2e_s = time.perf_counter() - t0
+    t = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    e2e_val = world * 2 * n * e2e_steps / t.item() / 1e6
+    # device results and e2e results must agree (same engine, same rays)
+    assert torch.equal(h_hits, d_hits.cpu()) and torch.equal(h_occ, d_occ.cpu())
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    # ---- roofline of the dominant kernel (closest-hit traversal) ----
+    # algorithmic bytes/ray = 52 + 32*nodesVisited + 36*triTests; the counts
+    # come from the engine's counting kernel, which follows the reference's rules.
+    cn = min(n, 1 << 21)
+    _, nv, tt = agg.IntersectCounters(bounce[:cn])
+    _, nvs, tts = agg.IntersectCounters(shadow[:cn], any_hit=True)
+    bytes_per_ray = 52.0 + 32.0 * float(nv.mean()) + 36.0 * float(tt.mean())
+    peak, peak_src = peaks()
+    achieved = bytes_per_ray * n / (closest_ms / 1e3) / 1e9
+    roofline = {"bound": "hbm", "kernel": "WideKernel<closest>", "achieved": achieved, "peak": peak,
+                "unit": "GB/s", "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                "algorithmic_bytes_per_ray": bytes_per_ray, "rays_per_launch": n,
+                "kernel_ms": closest_ms, "nodes_visited_per_ray": float(nv.mean()),
+                "tri_tests_per_ray": float(tt.mean()),
+                "shadow_nodes_visited_per_ray": float(nvs.mean()),
+                "shadow_tri_tests_per_ray": float(tts.mean()),
+                "note": "scene is L2-resident: algorithmic bytes are served mostly by L1/L2, "
+                        "so frac may exceed 1 of the HBM copy peak"}
+
+    cpu_baseline = None
+    if not args.no_cpu_baseline:
+        cpu = CpuPath(w)
+        mr, rays_done, secs = cpu.timed(bounce, shadow, args.cpu_seconds)
+        cpu_baseline = {"value": mr, "unit": UNIT, "cores": cpu.cores, "kind": cpu.kind,
+                        "sample": f"first {rays_done // 2} closest + {rays_done // 2} shadow rays "
+                                  f"of the same batch, {secs:.1f} s"}
+
+    line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": max(args.warmup, 3), "ms_per_step": total_ms / args.steps,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+            "data": "synthetic rays over " + w["name"],
+            "config": {"workload": f"{w['name']}: {n} incoherent diffuse-bounce closest-hit rays + "
+                                   f"{n} shadow any-hit rays per GPU per step",
+                       "triangles": int(len(w["tris"])), "bvh_nodes": int(len(w["nodes"])),
+                       "tree": "reference SAH, maxnodeprims 4", "parallelism": f"rays sharded x{world}, scene replicated"
+                       + (", NCCL gather of hit records to rank 0 inside the step" if world > 1 else ""),
+                       "l2": "ray+hit buffers (>=400 MB per step) exceed the 126 MB L2; "
+                             "scene stays cache-resident by design"},
+            "e2e": {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": 2 * n * 32,
+                    "d2h_bytes_per_step": n * 20 + n, "steps": e2e_steps},
+            "gpu_launches": int(launches), "clocks": clk, "roofline": roofline,
+            "cpu_baseline": cpu_baseline}
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    a = parse()
+    if a.impl == "reference":
+        run_reference(a)
+    else:
+        run_ours(a)

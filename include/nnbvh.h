@@ -1,0 +1,163 @@
+/* include/nnbvh.h -- C ABI of libnnbvh.so, the B200-native batch ray-query engine.
+ *
+ * Drop-in boundary for ONE path of the reference (Wil-Lee/NN_BVH = pbrt-v4 +
+ * machine_learning/): closest-hit / any-hit traversal of the flattened BVH plus
+ * the watertight ray-triangle test.  The reference has no FFI for this path
+ * (SURVEY.md section 8(b)); these entry points are what a binding would wrap.
+ * Paths below are relative to /root/reference/src/pbrt.
+ *
+ * Conventions: every function returns 0 on success or a negative nnbvh_status;
+ * nothing aborts or throws across the boundary (the reference LOG_FATALs,
+ * util/check.h:36).  nnbvh_last_error() gives the message for the calling
+ * thread.  Ray / hit / output pointers may be host (pageable or pinned) or
+ * device pointers; device pointers are detected with cudaPointerGetAttributes
+ * and used in place.  There is NO CPU fallback: without a CUDA device every
+ * compute entry point fails with NNBVH_ERR_CUDA.
+ */
+#ifndef NNBVH_H
+#define NNBVH_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum nnbvh_status {
+    NNBVH_OK = 0,
+    NNBVH_ERR_INVALID = -1,   /* bad argument / malformed tree */
+    NNBVH_ERR_CUDA = -2,      /* CUDA runtime error or no device */
+    NNBVH_ERR_NOSCENE = -3,   /* query before nnbvh_upload_scene */
+    NNBVH_ERR_DEPTH = -4,     /* traversal stack would exceed 64 entries
+                                 (cpu/aggregates.cpp:538 has no such check) */
+    NNBVH_ERR_NOMEM = -5
+} nnbvh_status;
+
+/* Byte-identical to `struct alignas(32) LinearBVHNode`
+ * (cpu/aggregates.cpp:128-137): pre-order, first child at idx+1. */
+typedef struct nnbvh_node {
+    float bounds[6];       /* pMin.xyz, pMax.xyz */
+    int32_t offset;        /* leaf: primitivesOffset; interior: secondChildOffset */
+    uint16_t nPrimitives;  /* 0 -> interior */
+    uint8_t axis;
+    uint8_t pad;
+} nnbvh_node;
+
+/* Ray {o, d, time} (ray.h:35-38) + the tMax argument of Intersect/IntersectP. */
+typedef struct nnbvh_ray {
+    float ox, oy, oz, tMax, dx, dy, dz, time;
+} nnbvh_ray;
+
+/* What survives of ShapeIntersection (shapes.h:93-97): ordered primitive index
+ * (NNBVH_MISS = no hit), tHit and the TriangleIntersection barycentrics
+ * (shapes.h:820-824).  SurfaceInteraction is rebuilt on the host from these
+ * (Triangle::InteractionFromIntersection, shapes.h:884). */
+typedef struct nnbvh_hit {
+    uint32_t prim;
+    float t, b0, b1, b2;
+} nnbvh_hit;
+
+#define NNBVH_MISS 0xFFFFFFFFu
+
+/* BVHAggregate::SplitMethod (cpu/aggregates.h:31). */
+typedef enum nnbvh_split { NNBVH_SPLIT_SAH = 0, NNBVH_SPLIT_HLBVH = 1,
+                           NNBVH_SPLIT_MIDDLE = 2, NNBVH_SPLIT_EQUAL_COUNTS = 3 } nnbvh_split;
+
+typedef enum nnbvh_kernel {
+    NNBVH_KERNEL_AUTO = 0,   /* engine default (the fast path) */
+    NNBVH_KERNEL_BASIC = 1,  /* one thread per ray over the 32-byte nodes, statement
+                                order of cpu/aggregates.cpp:529-624 */
+    NNBVH_KERNEL_WIDE = 2    /* persistent warps over 64-byte two-child nodes */
+} nnbvh_kernel;
+
+typedef struct nnbvh_options {
+    int32_t device;          /* CUDA device ordinal; -1 = current device */
+    int32_t kernel;          /* nnbvh_kernel */
+    int32_t smem_top_nodes;  /* wide kernel: top-of-tree nodes staged in shared
+                                memory; -1 = default, 0 = none */
+    int32_t reserved[5];
+} nnbvh_options;
+
+typedef struct nnbvh_engine nnbvh_engine;
+
+/* ---- host-side tree construction (no GPU needed) ------------------------- */
+
+/* Replaces BVHAggregate::BVHAggregate + buildRecursive + flattenBVH
+ * (cpu/aggregates.cpp:140-387, 505-522) for a triangle soup: same splits, same
+ * leaf order, byte-identical nodes (the reference on ONE thread; its parallel
+ * build orders leaves nondeterministically, :359-370).
+ * triVerts9: nTris*9 floats, original order.  nodesOut: capacity 2*nTris-1.
+ * orderOut[i] = original index of ordered primitive i. */
+int nnbvh_build_bvh(const float *triVerts9, uint32_t nTris, int32_t maxPrimsInNode,
+                    int32_t splitMethod, int32_t nThreads, nnbvh_node *nodesOut,
+                    uint32_t *nNodesOut, uint32_t *orderOut);
+
+/* Maximum number of simultaneously stacked nodes any ray can need on this tree
+ * (the reference's nodesToVisit[64], cpu/aggregates.cpp:538). */
+int nnbvh_tree_stack_depth(const nnbvh_node *nodes, uint32_t nNodes, uint32_t *depthOut);
+
+/* ---- engine ---------------------------------------------------------------- */
+
+int nnbvh_create(const nnbvh_options *opts /* may be NULL */, nnbvh_engine **out);
+void nnbvh_destroy(nnbvh_engine *e);
+
+/* Stream (cudaStream_t) that all later work of this engine is issued on;
+ * NULL = the engine's own stream. */
+int nnbvh_set_stream(nnbvh_engine *e, void *cudaStream);
+
+/* Replaces the reference's pointer graph (Primitive -> SimplePrimitive ->
+ * Triangle -> TriangleMesh, cpu/primitive.cpp:96-109, shapes.cpp:320-327) by
+ * device arrays.  nodes: the flattened tree; orderedTriVerts9: nPrims*9 floats in
+ * ORDERED (leaf) order.  Host or device pointers.  nNodes == 0 uploads the empty
+ * scene (`nodes == nullptr` in the reference: every ray misses). */
+int nnbvh_upload_scene(nnbvh_engine *e, const nnbvh_node *nodes, uint32_t nNodes,
+                       const float *orderedTriVerts9, uint32_t nPrims);
+
+/* BVHAggregate::Intersect (cpu/aggregates.cpp:529-579) for n rays. */
+int nnbvh_intersect_closest(nnbvh_engine *e, const nnbvh_ray *rays, uint64_t n,
+                            nnbvh_hit *hits);
+
+/* BVHAggregate::IntersectP (cpu/aggregates.cpp:581-624) for n rays: occluded[i] = 0/1. */
+int nnbvh_intersect_any(nnbvh_engine *e, const nnbvh_ray *rays, uint64_t n,
+                        uint8_t *occluded);
+
+/* SoA forms for the wavefront queues (SOA<RayWorkItem>, wavefront/workitems.soa;
+ * wavefront/aggregate.cpp:34-68).  tMax may be NULL (= Infinity). */
+int nnbvh_intersect_closest_soa(nnbvh_engine *e, const float *ox, const float *oy,
+                                const float *oz, const float *dx, const float *dy,
+                                const float *dz, const float *tMax, uint64_t n,
+                                nnbvh_hit *hits);
+int nnbvh_intersect_any_soa(nnbvh_engine *e, const float *ox, const float *oy,
+                            const float *oz, const float *dx, const float *dy,
+                            const float *dz, const float *tMax, uint64_t n,
+                            uint8_t *occluded);
+
+/* Same results plus the reference's per-ray statistics: nodesVisited counts as
+ * `++nodesVisited` does (cpu/aggregates.cpp:541,592), triTests as `++nTriTests`
+ * (shapes.cpp:322,343).  Runs the BASIC kernel.  anyHit != 0 -> IntersectP
+ * (hits may be NULL, occluded filled); else Intersect (occluded may be NULL). */
+int nnbvh_intersect_counters(nnbvh_engine *e, const nnbvh_ray *rays, uint64_t n,
+                             int32_t anyHit, nnbvh_hit *hits, uint8_t *occluded,
+                             uint32_t *nodesVisited, uint32_t *triTests);
+
+/* Device time (CUDA events on the engine's stream) of the traversal kernel(s)
+ * of the most recent intersect call, and kernels launched so far. */
+int nnbvh_last_kernel_ms(nnbvh_engine *e, float *ms);
+int nnbvh_launch_count(nnbvh_engine *e, uint64_t *launches);
+
+/* IntersectTriangle (shapes.cpp:172-273) and Bounds3f::IntersectP
+ * (util/vecmath.h:1573-1608) evaluated ON THE DEVICE for n independent
+ * (ray, triangle) / (ray, box) pairs -- known-answer hooks for the parity
+ * tests.  out4 = {t,b0,b1,b2}; hit[i] = 0/1.  Host pointers. */
+int nnbvh_test_triangles(nnbvh_engine *e, const nnbvh_ray *rays, const float *tris9,
+                         uint64_t n, uint8_t *hit, float *out4);
+int nnbvh_test_boxes(nnbvh_engine *e, const nnbvh_ray *rays, const float *boxes6,
+                     uint64_t n, uint8_t *hit);
+
+const char *nnbvh_last_error(void);
+const char *nnbvh_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* NNBVH_H */

@@ -1,0 +1,198 @@
+"""nn_bvh_b200/aggregate.py -- host-side mirror of the reference's BVHAggregate.
+
+Same surface as `class BVHAggregate` (/root/reference/src/pbrt/cpu/aggregates.h:28-70):
+constructor (primitives, maxPrimsInNode, splitMethod), `Create(prims, parameters)`,
+`Bounds()`, `Intersect(ray, tMax)`, `IntersectP(ray, tMax)` -- plus the batch
+forms the reference only has in `CPUAggregate::IntersectClosest/IntersectShadow`
+(wavefront/aggregate.cpp:34-68).  Every query runs in libnnbvh.so on the GPU;
+this file holds no intersection arithmetic.
+"""
+from __future__ import annotations
+
+import ctypes
+from typing import Optional
+
+import numpy as np
+
+from . import capi
+from .capi import HIT_DTYPE, MISS, NODE_DTYPE, RAY_DTYPE
+
+
+def build_bvh(tris9: np.ndarray, max_prims_in_node: int = 4, split_method: str = "sah",
+              threads: int = 0):
+    """BVHAggregate ctor + flattenBVH on the host (libnnbvh nnbvh_build_bvh).
+
+    tris9: (T,9) float32, original order.  Returns (nodes: NODE_DTYPE[M], order: uint32[T])
+    where order[i] is the original index of ordered primitive i."""
+    tris9 = np.ascontiguousarray(tris9, dtype=np.float32).reshape(-1, 9)
+    T = tris9.shape[0]
+    nodes = np.zeros(max(2 * T - 1, 1), dtype=NODE_DTYPE)
+    order = np.zeros(T, dtype=np.uint32)
+    n = ctypes.c_uint32(0)
+    capi.check(capi.lib().nnbvh_build_bvh(capi.ptr(tris9), T, max_prims_in_node,
+                                          capi.SPLIT[split_method], threads, capi.ptr(nodes),
+                                          ctypes.byref(n), capi.ptr(order)))
+    return nodes[:n.value].copy(), order
+
+
+def tree_stack_depth(nodes: np.ndarray) -> int:
+    d = ctypes.c_uint32(0)
+    capi.check(capi.lib().nnbvh_tree_stack_depth(capi.ptr(nodes), len(nodes), ctypes.byref(d)))
+    return d.value
+
+
+def make_rays(o, d, tmax=np.inf, time=0.0) -> np.ndarray:
+    """Pack (N,3) origins/directions into the 32-byte nnbvh_ray layout."""
+    o = np.asarray(o, dtype=np.float32).reshape(-1, 3)
+    d = np.asarray(d, dtype=np.float32).reshape(-1, 3)
+    r = np.zeros(o.shape[0], dtype=RAY_DTYPE)
+    r["o"], r["d"], r["tMax"], r["time"] = o, d, tmax, time
+    return r
+
+
+class GPUBVHAggregate:
+    """Drop-in batch backend for BVHAggregate::Intersect / IntersectP."""
+
+    SplitMethod = ("sah", "hlbvh", "middle", "equal")
+
+    def __init__(self, tris9: Optional[np.ndarray] = None, max_prims_in_node: int = 1,
+                 split_method: str = "sah", *, nodes: Optional[np.ndarray] = None,
+                 ordered_tris9: Optional[np.ndarray] = None, order: Optional[np.ndarray] = None,
+                 device: int = -1, kernel: int = capi.KERNEL_AUTO, smem_top_nodes: int = -1):
+        """Either tris9 (a soup to build over, like the reference ctor) or a ready
+        flattened tree: nodes + ordered_tris9 (e.g. an exported NN-split tree)."""
+        L = capi.lib()
+        if nodes is None:
+            if tris9 is None or len(tris9) == 0:
+                # The reference CHECK(!primitives.empty())s; an empty aggregate here misses.
+                nodes = np.zeros(0, dtype=NODE_DTYPE)
+                ordered_tris9 = np.zeros((0, 9), dtype=np.float32)
+                order = np.zeros(0, dtype=np.uint32)
+            else:
+                tris9 = np.ascontiguousarray(tris9, dtype=np.float32).reshape(-1, 9)
+                nodes, order = build_bvh(tris9, max_prims_in_node, split_method)
+                ordered_tris9 = tris9[order]
+        self.nodes = np.ascontiguousarray(nodes).view(NODE_DTYPE).reshape(-1)
+        self.ordered_tris9 = np.ascontiguousarray(ordered_tris9, dtype=np.float32).reshape(-1, 9)
+        self.order = order  # ordered prim -> caller's primitive id (None = identity)
+        opts = capi.Options(device=device, kernel=kernel, smem_top_nodes=smem_top_nodes)
+        h = ctypes.c_void_p()
+        capi.check(L.nnbvh_create(ctypes.byref(opts), ctypes.byref(h)))
+        self._h = h
+        capi.check(L.nnbvh_upload_scene(h, capi.ptr(self.nodes), len(self.nodes),
+                                        capi.ptr(self.ordered_tris9), len(self.ordered_tris9)))
+
+    @classmethod
+    def Create(cls, tris9, parameters: Optional[dict] = None, **kw):
+        """BVHAggregate::Create (cpu/aggregates.cpp:725-744): "splitmethod" (default
+        "sah"), "maxnodeprims" (default 4)."""
+        p = parameters or {}
+        name = p.get("splitmethod", "sah")
+        if name not in cls.SplitMethod:
+            name = "sah"  # the reference warns and falls back to sah (:737-740)
+        return cls(tris9, int(p.get("maxnodeprims", 4)), name, **kw)
+
+    def close(self):
+        if getattr(self, "_h", None):
+            capi.lib().nnbvh_destroy(self._h)
+            self._h = None
+
+    __del__ = close
+
+    # ---- BVHAggregate surface -------------------------------------------------
+    def Bounds(self):
+        if len(self.nodes) == 0:
+            raise RuntimeError("Bounds() of an empty aggregate (the reference CHECK(nodes)s)")
+        return self.nodes[0]["bounds"].copy()
+
+    def Intersect(self, ray, tMax=np.inf):
+        """Single ray: (o, d) -> None or (prim, t, b0, b1, b2).  One-ray batch on the GPU."""
+        h = self.IntersectBatch(make_rays(ray[0], ray[1], tMax))[0]
+        if h["prim"] == MISS:
+            return None
+        return int(h["prim"]), float(h["t"]), *map(float, h["b"])
+
+    def IntersectP(self, ray, tMax=np.inf) -> bool:
+        return bool(self.IntersectPBatch(make_rays(ray[0], ray[1], tMax))[0])
+
+    # ---- batch surface --------------------------------------------------------
+    def IntersectBatch(self, rays, hits=None, n=None):
+        """rays: RAY_DTYPE ndarray / (N,8) float32 / torch tensor (host or CUDA).
+        Returns hits (HIT_DTYPE ndarray for numpy input; the tensor passed as `hits`
+        otherwise -- a (N,5) int32/float32-viewable 20-byte-record buffer)."""
+        n = self._count(rays, n)
+        if hits is None:
+            if not isinstance(rays, np.ndarray):
+                raise ValueError("pass `hits` when rays is a tensor")
+            hits = np.zeros(n, dtype=HIT_DTYPE)
+        capi.check(capi.lib().nnbvh_intersect_closest(self._h, capi.ptr(rays), n, capi.ptr(hits)))
+        return hits
+
+    def IntersectPBatch(self, rays, occluded=None, n=None):
+        n = self._count(rays, n)
+        if occluded is None:
+            if not isinstance(rays, np.ndarray):
+                raise ValueError("pass `occluded` when rays is a tensor")
+            occluded = np.zeros(n, dtype=np.uint8)
+        capi.check(capi.lib().nnbvh_intersect_any(self._h, capi.ptr(rays), n, capi.ptr(occluded)))
+        return occluded
+
+    def IntersectBatchSoA(self, ox, oy, oz, dx, dy, dz, tMax=None, hits=None, any_hit=False):
+        n = int(ox.shape[0])
+        if hits is None:
+            hits = np.zeros(n, dtype=np.uint8 if any_hit else HIT_DTYPE)
+        f = capi.lib().nnbvh_intersect_any_soa if any_hit else capi.lib().nnbvh_intersect_closest_soa
+        capi.check(f(self._h, *(capi.ptr(a) for a in (ox, oy, oz, dx, dy, dz, tMax)), n,
+                     capi.ptr(hits)))
+        return hits
+
+    def IntersectCounters(self, rays, any_hit=False):
+        """Results plus the reference's per-ray statistics (bvhNodesVisited,
+        nTriTests).  numpy in, numpy out."""
+        n = self._count(rays, None)
+        hits = np.zeros(n, dtype=HIT_DTYPE)
+        occ = np.zeros(n, dtype=np.uint8)
+        nv = np.zeros(n, dtype=np.uint32)
+        tt = np.zeros(n, dtype=np.uint32)
+        capi.check(capi.lib().nnbvh_intersect_counters(self._h, capi.ptr(rays), n, int(any_hit),
+                                                       capi.ptr(hits), capi.ptr(occ),
+                                                       capi.ptr(nv), capi.ptr(tt)))
+        return (occ if any_hit else hits), nv, tt
+
+    def set_stream(self, cuda_stream: int):
+        capi.check(capi.lib().nnbvh_set_stream(self._h, ctypes.c_void_p(cuda_stream)))
+
+    def last_kernel_ms(self) -> float:
+        ms = ctypes.c_float(0)
+        capi.check(capi.lib().nnbvh_last_kernel_ms(self._h, ctypes.byref(ms)))
+        return ms.value
+
+    def launch_count(self) -> int:
+        c = ctypes.c_uint64(0)
+        capi.check(capi.lib().nnbvh_launch_count(self._h, ctypes.byref(c)))
+        return c.value
+
+    def test_triangles(self, rays, tris9):
+        n = len(rays)
+        tris9 = np.ascontiguousarray(tris9, dtype=np.float32).reshape(-1, 9)
+        hit = np.zeros(n, dtype=np.uint8)
+        out = np.zeros((n, 4), dtype=np.float32)
+        capi.check(capi.lib().nnbvh_test_triangles(self._h, capi.ptr(rays), capi.ptr(tris9), n,
+                                                   capi.ptr(hit), capi.ptr(out)))
+        return hit, out
+
+    def test_boxes(self, rays, boxes6):
+        n = len(rays)
+        boxes6 = np.ascontiguousarray(boxes6, dtype=np.float32).reshape(-1, 6)
+        hit = np.zeros(n, dtype=np.uint8)
+        capi.check(capi.lib().nnbvh_test_boxes(self._h, capi.ptr(rays), capi.ptr(boxes6), n,
+                                               capi.ptr(hit)))
+        return hit
+
+    @staticmethod
+    def _count(rays, n):
+        if n is not None:
+            return int(n)
+        if isinstance(rays, np.ndarray) and rays.dtype == RAY_DTYPE:
+            return rays.size
+        return int(rays.shape[0])

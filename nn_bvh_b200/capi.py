@@ -1,0 +1,102 @@
+"""nn_bvh_b200/capi.py -- ctypes binding of libnnbvh.so (include/nnbvh.h).
+
+The library is the product; this module only declares its signatures.  It fails
+loudly when the shared object is missing (run `python -c "import
+__graft_entry__ as g; g.build()"` or nn_bvh_b200/csrc/build.sh) -- there is no
+Python or CPU fallback for any compute entry point.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "libnnbvh.so")
+
+MISS = 0xFFFFFFFF
+KERNEL_AUTO, KERNEL_BASIC, KERNEL_WIDE = 0, 1, 2
+SPLIT = {"sah": 0, "hlbvh": 1, "middle": 2, "equal": 3}
+
+NODE_DTYPE = np.dtype([("bounds", "<f4", (6,)), ("offset", "<i4"), ("nPrimitives", "<u2"),
+                       ("axis", "u1"), ("pad", "u1")])
+RAY_DTYPE = np.dtype([("o", "<f4", (3,)), ("tMax", "<f4"), ("d", "<f4", (3,)), ("time", "<f4")])
+HIT_DTYPE = np.dtype([("prim", "<u4"), ("t", "<f4"), ("b", "<f4", (3,))])
+assert NODE_DTYPE.itemsize == 32 and RAY_DTYPE.itemsize == 32 and HIT_DTYPE.itemsize == 20
+
+# Every symbol include/nnbvh.h declares (tests check the .so exports all of them).
+SYMBOLS = [
+    "nnbvh_build_bvh", "nnbvh_tree_stack_depth", "nnbvh_create", "nnbvh_destroy",
+    "nnbvh_set_stream", "nnbvh_upload_scene", "nnbvh_intersect_closest", "nnbvh_intersect_any",
+    "nnbvh_intersect_closest_soa", "nnbvh_intersect_any_soa", "nnbvh_intersect_counters",
+    "nnbvh_last_kernel_ms", "nnbvh_launch_count", "nnbvh_test_triangles", "nnbvh_test_boxes",
+    "nnbvh_last_error", "nnbvh_version",
+]
+
+
+class Options(ctypes.Structure):
+    _fields_ = [("device", ctypes.c_int32), ("kernel", ctypes.c_int32),
+                ("smem_top_nodes", ctypes.c_int32), ("reserved", ctypes.c_int32 * 5)]
+
+
+class NnbvhError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__(f"libnnbvh error {code}: {msg}")
+        self.code = code
+
+
+_lib = None
+
+
+def lib() -> ctypes.CDLL:
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise ImportError(f"{LIB_PATH} is missing: build the CUDA library first "
+                          "(__graft_entry__.build()); nn_bvh_b200 has no fallback path")
+    L = ctypes.CDLL(LIB_PATH)
+    vp, u32, u64, i32 = ctypes.c_void_p, ctypes.c_uint32, ctypes.c_uint64, ctypes.c_int32
+    L.nnbvh_build_bvh.argtypes = [vp, u32, i32, i32, i32, vp, vp, vp]
+    L.nnbvh_tree_stack_depth.argtypes = [vp, u32, vp]
+    L.nnbvh_create.argtypes = [vp, vp]
+    L.nnbvh_destroy.argtypes = [vp]
+    L.nnbvh_destroy.restype = None
+    L.nnbvh_set_stream.argtypes = [vp, vp]
+    L.nnbvh_upload_scene.argtypes = [vp, vp, u32, vp, u32]
+    L.nnbvh_intersect_closest.argtypes = [vp, vp, u64, vp]
+    L.nnbvh_intersect_any.argtypes = [vp, vp, u64, vp]
+    L.nnbvh_intersect_closest_soa.argtypes = [vp] * 8 + [u64, vp]
+    L.nnbvh_intersect_any_soa.argtypes = [vp] * 8 + [u64, vp]
+    L.nnbvh_intersect_counters.argtypes = [vp, vp, u64, i32, vp, vp, vp, vp]
+    L.nnbvh_last_kernel_ms.argtypes = [vp, vp]
+    L.nnbvh_launch_count.argtypes = [vp, vp]
+    L.nnbvh_test_triangles.argtypes = [vp, vp, vp, u64, vp, vp]
+    L.nnbvh_test_boxes.argtypes = [vp, vp, vp, u64, vp]
+    L.nnbvh_last_error.restype = ctypes.c_char_p
+    L.nnbvh_version.restype = ctypes.c_char_p
+    _lib = L
+    return L
+
+
+def check(rc: int) -> None:
+    if rc != 0:
+        raise NnbvhError(rc, lib().nnbvh_last_error().decode("utf-8", "replace"))
+
+
+def ptr(a):
+    """Raw address of a numpy array, a torch tensor (host or device), an int or None."""
+    if a is None:
+        return None
+    if isinstance(a, int):
+        return ctypes.c_void_p(a)
+    if isinstance(a, np.ndarray):
+        if not a.flags["C_CONTIGUOUS"]:
+            raise ValueError("array must be C-contiguous")
+        return ctypes.c_void_p(a.ctypes.data)
+    if hasattr(a, "data_ptr"):  # torch.Tensor
+        if not a.is_contiguous():
+            raise ValueError("tensor must be contiguous")
+        return ctypes.c_void_p(a.data_ptr())
+    raise TypeError(type(a))

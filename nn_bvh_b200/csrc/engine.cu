@@ -1,0 +1,737 @@
+// nn_bvh_b200/csrc/engine.cu -- the C ABI of libnnbvh.so (include/nnbvh.h).
+//
+// Owns device memory, streams and launches.  There is no CPU path in here: if
+// CUDA is unavailable every compute entry point returns NNBVH_ERR_CUDA.
+
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <deque>
+#include <vector>
+
+#include "../../include/nnbvh.h"
+#include "internal.h"
+#include "kernels.cuh"
+
+namespace nnbvh {
+
+static thread_local char g_err[512] = "";
+
+int SetError(int code, const char *fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+    return code;
+}
+
+#define CU(call)                                                                          \
+    do {                                                                                  \
+        cudaError_t e_ = (call);                                                          \
+        if (e_ != cudaSuccess)                                                            \
+            return SetError(NNBVH_ERR_CUDA, "%s failed: %s (%s:%d)", #call,               \
+                            cudaGetErrorString(e_), __FILE__, __LINE__);                  \
+    } while (0)
+
+template <typename T>
+struct DevBuf {
+    T *p = nullptr;
+    size_t cap = 0;  // elements
+    int Reserve(size_t n) {
+        if (n <= cap) return NNBVH_OK;
+        if (p) cudaFree(p);
+        p = nullptr;
+        cap = 0;
+        CU(cudaMalloc(&p, std::max<size_t>(n, 1) * sizeof(T)));
+        cap = n;
+        return NNBVH_OK;
+    }
+    void Free() {
+        if (p) cudaFree(p);
+        p = nullptr;
+        cap = 0;
+    }
+};
+
+// One in-flight chunk of the host-pointer pipeline: H2D rays -> kernel -> D2H results.
+struct Slot {
+    cudaStream_t stream = nullptr;
+    cudaEvent_t done = nullptr;
+    DevBuf<nnbvh_ray> rays;
+    DevBuf<float> soa;       // 7 planes for the SoA entry points
+    DevBuf<nnbvh_hit> hits;
+    DevBuf<uint8_t> occ;
+    DevBuf<uint32_t> cnt;    // 2 planes (nodesVisited, triTests)
+    unsigned long long *cursor = nullptr;
+};
+
+}  // namespace nnbvh
+
+using namespace nnbvh;
+
+struct nnbvh_engine {
+    int device = 0;
+    int kernel = NNBVH_KERNEL_AUTO;
+    int smemTopNodes = -1;
+    int numSMs = 0;
+    int maxSmemOptin = 0;
+    cudaStream_t ownStream = nullptr, stream = nullptr;
+    cudaEvent_t evA = nullptr, evB = nullptr;
+    float lastMs = 0.f;
+    uint64_t launches = 0;
+    // scene
+    bool haveScene = false;
+    SceneDev sc{};
+    DevBuf<nnbvh_node> dNodes;
+    DevBuf<WideNode> dWide;
+    DevBuf<float4> dTris;
+    // device-pointer path scratch
+    unsigned long long *cursor = nullptr;
+    // host-pointer pipeline
+    static constexpr int kSlots = 3;
+    Slot slots[kSlots];
+    // tuning knobs (env overridable, see nnbvh_create)
+    int wideMinB = 2;        // CTAs/SM the WideKernel variant is compiled for
+    int refillBelow = 32;
+    uint64_t chunkRays = 1u << 20;
+};
+
+extern "C" const char *nnbvh_last_error(void) { return g_err; }
+extern "C" const char *nnbvh_version(void) { return "nnbvh-b200 0.1 (sm_100a)"; }
+
+static int EnvInt(const char *name, int dflt) {
+    const char *v = getenv(name);
+    return v && *v ? atoi(v) : dflt;
+}
+
+extern "C" int nnbvh_create(const nnbvh_options *opts, nnbvh_engine **out) {
+    if (!out) return SetError(NNBVH_ERR_INVALID, "nnbvh_create: out is NULL");
+    *out = nullptr;
+    int nDev = 0;
+    cudaError_t ce = cudaGetDeviceCount(&nDev);
+    if (ce != cudaSuccess || nDev == 0)
+        return SetError(NNBVH_ERR_CUDA, "nnbvh_create: no CUDA device (%s); this library has "
+                                        "no CPU fallback",
+                        ce == cudaSuccess ? "device count 0" : cudaGetErrorString(ce));
+    nnbvh_engine *e = new nnbvh_engine;
+    int dev = opts ? opts->device : -1;
+    if (dev < 0) CU(cudaGetDevice(&dev));
+    if (dev >= nDev) {
+        delete e;
+        return SetError(NNBVH_ERR_INVALID, "nnbvh_create: device %d of %d", dev, nDev);
+    }
+    e->device = dev;
+    CU(cudaSetDevice(dev));
+    cudaDeviceProp prop;
+    CU(cudaGetDeviceProperties(&prop, dev));
+    if (prop.major < 10) {
+        delete e;
+        return SetError(NNBVH_ERR_CUDA, "nnbvh_create: device %d is sm_%d%d; this library is "
+                                        "built for sm_100a only", dev, prop.major, prop.minor);
+    }
+    e->numSMs = prop.multiProcessorCount;
+    e->maxSmemOptin = (int)prop.sharedMemPerBlockOptin;
+    e->kernel = opts ? opts->kernel : NNBVH_KERNEL_AUTO;
+    e->smemTopNodes = opts ? opts->smem_top_nodes : -1;
+    e->kernel = EnvInt("NNBVH_KERNEL", e->kernel);
+    e->smemTopNodes = EnvInt("NNBVH_SMEM_NODES", e->smemTopNodes);
+    e->wideMinB = EnvInt("NNBVH_WIDE_MINB", e->wideMinB);
+    e->refillBelow = EnvInt("NNBVH_REFILL_BELOW", e->refillBelow);
+    e->chunkRays = (uint64_t)EnvInt("NNBVH_CHUNK_RAYS", (int)e->chunkRays);
+    CU(cudaStreamCreateWithFlags(&e->ownStream, cudaStreamNonBlocking));
+    e->stream = e->ownStream;
+    CU(cudaEventCreate(&e->evA));
+    CU(cudaEventCreate(&e->evB));
+    CU(cudaMalloc(&e->cursor, sizeof(unsigned long long)));
+    for (Slot &s : e->slots) {
+        CU(cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking));
+        CU(cudaEventCreateWithFlags(&s.done, cudaEventDisableTiming));
+        CU(cudaMalloc(&s.cursor, sizeof(unsigned long long)));
+    }
+    *out = e;
+    return NNBVH_OK;
+}
+
+extern "C" void nnbvh_destroy(nnbvh_engine *e) {
+    if (!e) return;
+    cudaSetDevice(e->device);
+    cudaDeviceSynchronize();
+    e->dNodes.Free();
+    e->dWide.Free();
+    e->dTris.Free();
+    if (e->cursor) cudaFree(e->cursor);
+    for (Slot &s : e->slots) {
+        s.rays.Free(); s.soa.Free(); s.hits.Free(); s.occ.Free(); s.cnt.Free();
+        if (s.cursor) cudaFree(s.cursor);
+        if (s.done) cudaEventDestroy(s.done);
+        if (s.stream) cudaStreamDestroy(s.stream);
+    }
+    if (e->evA) cudaEventDestroy(e->evA);
+    if (e->evB) cudaEventDestroy(e->evB);
+    if (e->ownStream) cudaStreamDestroy(e->ownStream);
+    delete e;
+}
+
+extern "C" int nnbvh_set_stream(nnbvh_engine *e, void *cudaStream) {
+    if (!e) return SetError(NNBVH_ERR_INVALID, "nnbvh_set_stream: engine is NULL");
+    e->stream = cudaStream ? (cudaStream_t)cudaStream : e->ownStream;
+    return NNBVH_OK;
+}
+
+extern "C" int nnbvh_last_kernel_ms(nnbvh_engine *e, float *ms) {
+    if (!e || !ms) return SetError(NNBVH_ERR_INVALID, "nnbvh_last_kernel_ms: NULL argument");
+    if (e->lastMs < 0.f) {  // device-pointer call: resolve the event pair now
+        CU(cudaEventSynchronize(e->evB));
+        float t = 0.f;
+        CU(cudaEventElapsedTime(&t, e->evA, e->evB));
+        e->lastMs = t;
+    }
+    *ms = e->lastMs;
+    return NNBVH_OK;
+}
+
+extern "C" int nnbvh_launch_count(nnbvh_engine *e, uint64_t *launches) {
+    if (!e || !launches) return SetError(NNBVH_ERR_INVALID, "nnbvh_launch_count: NULL argument");
+    *launches = e->launches;
+    return NNBVH_OK;
+}
+
+// ---------------------------------------------------------------------------
+// Scene upload: reference layout -> device layout
+// ---------------------------------------------------------------------------
+namespace nnbvh {
+
+static bool IsDevicePtr(const void *p) {
+    if (!p) return false;
+    cudaPointerAttributes a;
+    if (cudaPointerGetAttributes(&a, p) != cudaSuccess) {
+        cudaGetLastError();
+        return false;
+    }
+    return a.type == cudaMemoryTypeDevice || a.type == cudaMemoryTypeManaged;
+}
+
+// in9: nPrims*9 floats (ordered); last: 1 where the primitive ends its leaf.
+__global__ void PackTrisKernel(const float *__restrict__ in9, const uint8_t *__restrict__ last,
+                               uint32_t nPrims, float4 *__restrict__ out) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= nPrims) return;
+    const float *p = in9 + 9 * (size_t)i;
+    float v[9];
+#pragma unroll
+    for (int k = 0; k < 9; ++k) v[k] = p[k];
+    uint32_t flags = 0;
+    if (TriangleDegenerate(v[0], v[1], v[2], v[3], v[4], v[5], v[6], v[7], v[8]))
+        flags |= kTriDegenerate;
+    if (last[i]) flags |= kTriLast;
+    out[3 * (size_t)i + 0] = make_float4(v[0], v[1], v[2], __uint_as_float(flags));
+    out[3 * (size_t)i + 1] = make_float4(v[3], v[4], v[5], 0.f);
+    out[3 * (size_t)i + 2] = make_float4(v[6], v[7], v[8], 0.f);
+}
+
+// Validates the tree and derives the wide layout.  Returns NNBVH_OK or an error.
+static int BuildWideLayout(const std::vector<nnbvh_node> &nodes, uint32_t nPrims,
+                           uint32_t topCap, std::vector<WideNode> &wide,
+                           std::vector<uint8_t> &lastFlag, int32_t *rootRef,
+                           uint32_t *topNodes) {
+    const uint32_t M = (uint32_t)nodes.size();
+    lastFlag.assign(nPrims, 0);
+    std::vector<uint8_t> covered(nPrims, 0);
+    for (uint32_t i = 0; i < M; ++i) {
+        const nnbvh_node &nd = nodes[i];
+        if (nd.nPrimitives > 0) {
+            if (nd.offset < 0 || (uint64_t)nd.offset + nd.nPrimitives > nPrims)
+                return SetError(NNBVH_ERR_INVALID, "tree: leaf %u covers primitives [%d,%d) of %u",
+                                i, nd.offset, nd.offset + nd.nPrimitives, nPrims);
+            lastFlag[nd.offset + nd.nPrimitives - 1] = 1;
+            for (uint32_t k = 0; k < nd.nPrimitives; ++k) covered[nd.offset + k] = 1;
+        } else {
+            if (nd.axis > 2 || i + 1 >= M || nd.offset <= (int32_t)i + 1 ||
+                (uint32_t)nd.offset >= M)
+                return SetError(NNBVH_ERR_INVALID, "tree: interior node %u has axis %u, second "
+                                "child %d (of %u nodes)", i, nd.axis, nd.offset, M);
+        }
+    }
+    uint32_t depth = 0;
+    int rc = nnbvh_tree_stack_depth(nodes.data(), M, &depth);
+    if (rc) return rc;
+    if (depth > (uint32_t)kMaxStack)
+        return SetError(NNBVH_ERR_DEPTH, "tree: traversal needs %u stack entries; the reference's "
+                        "nodesToVisit[64] (cpu/aggregates.cpp:538) would overflow", depth);
+    // Number the interior nodes: BFS for the top (shared-memory resident,
+    // contiguous), pre-order for the rest (keeps subtrees local in memory).
+    std::vector<int32_t> wideOf(M, -1);
+    uint32_t nWide = 0;
+    if (nodes[0].nPrimitives == 0) {
+        std::deque<uint32_t> q{0u};
+        while (!q.empty() && nWide < topCap) {
+            uint32_t i = q.front();
+            q.pop_front();
+            wideOf[i] = (int32_t)nWide++;
+            uint32_t c0 = i + 1, c1 = (uint32_t)nodes[i].offset;
+            if (nodes[c0].nPrimitives == 0) q.push_back(c0);
+            if (nodes[c1].nPrimitives == 0) q.push_back(c1);
+        }
+        *topNodes = nWide;
+        for (uint32_t i = 0; i < M; ++i)  // array order IS pre-order
+            if (nodes[i].nPrimitives == 0 && wideOf[i] < 0) wideOf[i] = (int32_t)nWide++;
+    } else {
+        *topNodes = 0;
+    }
+    wide.assign(nWide, WideNode{});
+    auto refOf = [&](uint32_t i) -> int32_t {
+        return nodes[i].nPrimitives == 0 ? wideOf[i]
+                                         : (int32_t)(0x80000000u | (uint32_t)nodes[i].offset);
+    };
+    for (uint32_t i = 0; i < M; ++i) {
+        if (nodes[i].nPrimitives != 0) continue;
+        WideNode &w = wide[wideOf[i]];
+        const nnbvh_node &a = nodes[i + 1], &b = nodes[nodes[i].offset];
+        for (int k = 0; k < 3; ++k) {
+            w.lo0[k] = a.bounds[k];
+            w.hi0[k] = a.bounds[3 + k];
+            w.lo1[k] = b.bounds[k];
+            w.hi1[k] = b.bounds[3 + k];
+        }
+        w.ref0 = refOf(i + 1);
+        w.ref1 = refOf((uint32_t)nodes[i].offset);
+        w.axis = nodes[i].axis;
+        w.pad = 0;
+    }
+    *rootRef = refOf(0);
+    return NNBVH_OK;
+}
+
+}  // namespace nnbvh
+
+extern "C" int nnbvh_upload_scene(nnbvh_engine *e, const nnbvh_node *nodes, uint32_t nNodes,
+                                  const float *orderedTriVerts9, uint32_t nPrims) {
+    if (!e) return SetError(NNBVH_ERR_INVALID, "nnbvh_upload_scene: engine is NULL");
+    CU(cudaSetDevice(e->device));
+    e->haveScene = false;
+    if (nNodes == 0) {  // `nodes == nullptr` in the reference: every ray misses
+        e->sc = SceneDev{};
+        e->haveScene = true;
+        return NNBVH_OK;
+    }
+    if (!nodes || !orderedTriVerts9 || nPrims == 0)
+        return SetError(NNBVH_ERR_INVALID, "nnbvh_upload_scene: NULL nodes/triangles");
+    if (nPrims >= 0x80000000u)
+        return SetError(NNBVH_ERR_INVALID, "nnbvh_upload_scene: too many primitives");
+    cudaStream_t st = e->stream;
+    std::vector<nnbvh_node> h(nNodes);
+    CU(cudaMemcpyAsync(h.data(), nodes, sizeof(nnbvh_node) * (size_t)nNodes, cudaMemcpyDefault, st));
+    CU(cudaStreamSynchronize(st));
+    std::vector<WideNode> wide;
+    std::vector<uint8_t> last;
+    int32_t rootRef = 0;
+    uint32_t topNodes = 0;
+    const uint32_t topCap = 2048;  // 128 KiB of WideNodes at most in shared memory
+    int rc = BuildWideLayout(h, nPrims, topCap, wide, last, &rootRef, &topNodes);
+    if (rc) return rc;
+    rc = e->dNodes.Reserve(nNodes);
+    if (rc) return rc;
+    rc = e->dWide.Reserve(wide.size());
+    if (rc) return rc;
+    rc = e->dTris.Reserve(3 * (size_t)nPrims);
+    if (rc) return rc;
+    CU(cudaMemcpyAsync(e->dNodes.p, h.data(), sizeof(nnbvh_node) * (size_t)nNodes,
+                       cudaMemcpyHostToDevice, st));
+    if (!wide.empty())
+        CU(cudaMemcpyAsync(e->dWide.p, wide.data(), sizeof(WideNode) * wide.size(),
+                           cudaMemcpyHostToDevice, st));
+    // triangles: stage raw floats + leaf-end flags, pack on the device
+    float *dRaw = nullptr;
+    uint8_t *dLast = nullptr;
+    const float *src = orderedTriVerts9;
+    if (!IsDevicePtr(orderedTriVerts9)) {
+        CU(cudaMalloc(&dRaw, sizeof(float) * 9 * (size_t)nPrims));
+        CU(cudaMemcpyAsync(dRaw, orderedTriVerts9, sizeof(float) * 9 * (size_t)nPrims,
+                           cudaMemcpyHostToDevice, st));
+        src = dRaw;
+    }
+    CU(cudaMalloc(&dLast, nPrims));
+    CU(cudaMemcpyAsync(dLast, last.data(), nPrims, cudaMemcpyHostToDevice, st));
+    PackTrisKernel<<<(nPrims + 255) / 256, 256, 0, st>>>(src, dLast, nPrims, e->dTris.p);
+    ++e->launches;
+    CU(cudaGetLastError());
+    CU(cudaStreamSynchronize(st));
+    if (dRaw) cudaFree(dRaw);
+    cudaFree(dLast);
+    SceneDev sc{};
+    sc.nodes = e->dNodes.p;
+    sc.wide = e->dWide.p;
+    sc.tris = e->dTris.p;
+    sc.nNodes = nNodes;
+    sc.nWide = (uint32_t)wide.size();
+    sc.nPrims = nPrims;
+    for (int k = 0; k < 6; ++k) sc.rootBox[k] = h[0].bounds[k];
+    sc.rootRef = rootRef;
+    sc.topNodes = topNodes;
+    e->sc = sc;
+    e->haveScene = true;
+    return NNBVH_OK;
+}
+
+// ---------------------------------------------------------------------------
+// Launch
+// ---------------------------------------------------------------------------
+namespace nnbvh {
+
+struct Outputs {
+    nnbvh_hit *hits = nullptr;
+    uint8_t *occ = nullptr;
+    uint32_t *nodesVisited = nullptr, *triTests = nullptr;
+};
+
+template <bool ANY, int MINB>
+static int LaunchWideT(nnbvh_engine *e, cudaStream_t st, const WideParams &p, uint32_t smemBytes) {
+    static int configuredFor[16] = {};  // per device: max dynamic smem already opted in
+    if (e->device < 16 && configuredFor[e->device] < (int)smemBytes + 1) {
+        CU(cudaFuncSetAttribute(WideKernel<ANY, MINB>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                e->maxSmemOptin - 1024));
+        configuredFor[e->device] = e->maxSmemOptin;
+    }
+    int grid = e->numSMs * MINB;
+    WideKernel<ANY, MINB><<<grid, 256, smemBytes, st>>>(p);
+    return NNBVH_OK;
+}
+
+template <bool ANY>
+static int LaunchWide(nnbvh_engine *e, cudaStream_t st, const WideParams &p, uint32_t smemBytes) {
+    switch (e->wideMinB) {
+    case 1: return LaunchWideT<ANY, 1>(e, st, p, smemBytes);
+    case 3: return LaunchWideT<ANY, 3>(e, st, p, smemBytes);
+    case 4: return LaunchWideT<ANY, 4>(e, st, p, smemBytes);
+    default: return LaunchWideT<ANY, 2>(e, st, p, smemBytes);
+    }
+}
+
+// All pointers are device pointers here.
+static int LaunchTraversal(nnbvh_engine *e, cudaStream_t st, bool any, bool counters,
+                           const RayInput &in, uint64_t n, const Outputs &o,
+                           unsigned long long *cursor) {
+    if (n == 0) return NNBVH_OK;
+    const bool basic = counters || e->kernel == NNBVH_KERNEL_BASIC;
+    if (basic) {
+        if (n > (uint64_t)0x7fffffff * 128)
+            return SetError(NNBVH_ERR_INVALID, "batch too large for one launch");
+        unsigned grid = (unsigned)((n + 127) / 128);
+        if (counters) {
+            if (any) BasicKernel<true, true><<<grid, 128, 0, st>>>(e->sc, in, n, o.hits, o.occ, o.nodesVisited, o.triTests);
+            else BasicKernel<false, true><<<grid, 128, 0, st>>>(e->sc, in, n, o.hits, o.occ, o.nodesVisited, o.triTests);
+        } else {
+            if (any) BasicKernel<true, false><<<grid, 128, 0, st>>>(e->sc, in, n, o.hits, o.occ, nullptr, nullptr);
+            else BasicKernel<false, false><<<grid, 128, 0, st>>>(e->sc, in, n, o.hits, o.occ, nullptr, nullptr);
+        }
+    } else {
+        int minB = (e->wideMinB >= 1 && e->wideMinB <= 4) ? e->wideMinB : 2;
+        uint32_t budgetNodes = (uint32_t)((e->maxSmemOptin - 2048) / minB / sizeof(WideNode));
+        uint32_t want = e->smemTopNodes >= 0 ? (uint32_t)e->smemTopNodes : 2048u / minB;
+        uint32_t smemNodes = std::min(std::min(want, budgetNodes), e->sc.topNodes);
+        WideParams p;
+        p.sc = e->sc;
+        p.in = in;
+        p.n = n;
+        p.hits = o.hits;
+        p.occluded = o.occ;
+        p.cursor = cursor;
+        p.smemNodes = smemNodes;
+        p.refillBelow = (uint32_t)std::min(32, std::max(1, e->refillBelow));
+        CU(cudaMemsetAsync(cursor, 0, sizeof(unsigned long long), st));
+        int rc = any ? LaunchWide<true>(e, st, p, smemNodes * (uint32_t)sizeof(WideNode))
+                     : LaunchWide<false>(e, st, p, smemNodes * (uint32_t)sizeof(WideNode));
+        if (rc) return rc;
+    }
+    ++e->launches;
+    CU(cudaGetLastError());
+    return NNBVH_OK;
+}
+
+struct Batch {
+    bool any = false, counters = false, soa = false;
+    const nnbvh_ray *rays = nullptr;
+    const float *planes[7] = {};  // ox oy oz dx dy dz tMax
+    uint64_t n = 0;
+    Outputs out;
+};
+
+static int RunBatch(nnbvh_engine *e, const Batch &b) {
+    if (!e) return SetError(NNBVH_ERR_INVALID, "engine is NULL");
+    if (!e->haveScene) return SetError(NNBVH_ERR_NOSCENE, "no scene uploaded");
+    if (b.n == 0) return NNBVH_OK;
+    if (b.soa) {
+        for (int k = 0; k < 6; ++k)
+            if (!b.planes[k]) return SetError(NNBVH_ERR_INVALID, "SoA ray plane %d is NULL", k);
+    } else if (!b.rays) return SetError(NNBVH_ERR_INVALID, "rays is NULL");
+    if (b.any ? !b.out.occ : !b.out.hits)
+        return SetError(NNBVH_ERR_INVALID, "output buffer is NULL");
+    if (b.counters && (!b.out.nodesVisited || !b.out.triTests))
+        return SetError(NNBVH_ERR_INVALID, "counter buffer is NULL");
+    CU(cudaSetDevice(e->device));
+
+    const bool raysDev = IsDevicePtr(b.soa ? (const void *)b.planes[0] : (const void *)b.rays);
+    const bool outDev = IsDevicePtr(b.any ? (const void *)b.out.occ : (const void *)b.out.hits);
+    const bool cntDev = !b.counters || IsDevicePtr(b.out.nodesVisited);
+
+    if (raysDev && outDev && cntDev) {
+        // ---- everything resident: one launch, asynchronous on the engine's stream ----
+        RayInput in{};
+        if (b.soa) {
+            in.ox = b.planes[0]; in.oy = b.planes[1]; in.oz = b.planes[2];
+            in.dx = b.planes[3]; in.dy = b.planes[4]; in.dz = b.planes[5];
+            in.tMax = b.planes[6];
+        } else in.aos = reinterpret_cast<const float4 *>(b.rays);
+        CU(cudaEventRecord(e->evA, e->stream));
+        int rc = LaunchTraversal(e, e->stream, b.any, b.counters, in, b.n, b.out, e->cursor);
+        if (rc) return rc;
+        CU(cudaEventRecord(e->evB, e->stream));
+        e->lastMs = -1.f;  // resolved lazily by nnbvh_last_kernel_ms
+        return NNBVH_OK;
+    }
+
+    // ---- host buffers: chunked H2D -> kernel -> D2H over kSlots streams ----
+    const uint64_t chunk = std::max<uint64_t>(e->chunkRays, 1024);
+    std::vector<cudaEvent_t> k0, k1;  // kernel timing events, one pair per chunk
+    int idx = 0;
+    int rcOut = NNBVH_OK;
+    for (uint64_t off = 0; off < b.n && rcOut == NNBVH_OK; off += chunk, ++idx) {
+        Slot &s = e->slots[idx % nnbvh_engine::kSlots];
+        const uint64_t m = std::min(chunk, b.n - off);
+        CU(cudaEventSynchronize(s.done));  // slot buffers free again
+        RayInput in{};
+        if (b.soa) {
+            if (raysDev) {
+                in.ox = b.planes[0] + off; in.oy = b.planes[1] + off; in.oz = b.planes[2] + off;
+                in.dx = b.planes[3] + off; in.dy = b.planes[4] + off; in.dz = b.planes[5] + off;
+                in.tMax = b.planes[6] ? b.planes[6] + off : nullptr;
+            } else {
+                int rc = s.soa.Reserve(7 * chunk);
+                if (rc) return rc;
+                const float **dst[7] = {&in.ox, &in.oy, &in.oz, &in.dx, &in.dy, &in.dz, &in.tMax};
+                for (int k = 0; k < 7; ++k) {
+                    if (!b.planes[k]) { *dst[k] = nullptr; continue; }
+                    CU(cudaMemcpyAsync(s.soa.p + k * chunk, b.planes[k] + off, sizeof(float) * m,
+                                       cudaMemcpyHostToDevice, s.stream));
+                    *dst[k] = s.soa.p + k * chunk;
+                }
+            }
+        } else if (raysDev) {
+            in.aos = reinterpret_cast<const float4 *>(b.rays + off);
+        } else {
+            int rc = s.rays.Reserve(chunk);
+            if (rc) return rc;
+            CU(cudaMemcpyAsync(s.rays.p, b.rays + off, sizeof(nnbvh_ray) * m,
+                               cudaMemcpyHostToDevice, s.stream));
+            in.aos = reinterpret_cast<const float4 *>(s.rays.p);
+        }
+        Outputs o;
+        if (b.any || b.out.occ) {
+            if (outDev && b.any) o.occ = b.out.occ + off;
+            else if (b.any) { int rc = s.occ.Reserve(chunk); if (rc) return rc; o.occ = s.occ.p; }
+        }
+        if (!b.any) {
+            if (outDev) o.hits = b.out.hits + off;
+            else { int rc = s.hits.Reserve(chunk); if (rc) return rc; o.hits = s.hits.p; }
+        }
+        if (b.counters) {
+            if (cntDev) { o.nodesVisited = b.out.nodesVisited + off; o.triTests = b.out.triTests + off; }
+            else {
+                int rc = s.cnt.Reserve(2 * chunk);
+                if (rc) return rc;
+                o.nodesVisited = s.cnt.p;
+                o.triTests = s.cnt.p + chunk;
+            }
+        }
+        cudaEvent_t a, z;
+        CU(cudaEventCreate(&a));
+        CU(cudaEventCreate(&z));
+        k0.push_back(a);
+        k1.push_back(z);
+        CU(cudaEventRecord(a, s.stream));
+        rcOut = LaunchTraversal(e, s.stream, b.any, b.counters, in, m, o, s.cursor);
+        if (rcOut) break;
+        CU(cudaEventRecord(z, s.stream));
+        if (!outDev) {
+            if (b.any) CU(cudaMemcpyAsync(b.out.occ + off, o.occ, m, cudaMemcpyDeviceToHost, s.stream));
+            else CU(cudaMemcpyAsync(b.out.hits + off, o.hits, sizeof(nnbvh_hit) * m,
+                                    cudaMemcpyDeviceToHost, s.stream));
+        }
+        if (b.counters && !cntDev) {
+            CU(cudaMemcpyAsync(b.out.nodesVisited + off, o.nodesVisited, sizeof(uint32_t) * m,
+                               cudaMemcpyDeviceToHost, s.stream));
+            CU(cudaMemcpyAsync(b.out.triTests + off, o.triTests, sizeof(uint32_t) * m,
+                               cudaMemcpyDeviceToHost, s.stream));
+        }
+        CU(cudaEventRecord(s.done, s.stream));
+    }
+    for (Slot &s : e->slots) CU(cudaStreamSynchronize(s.stream));
+    float total = 0.f;
+    for (size_t i = 0; i < k1.size(); ++i) {
+        float ms = 0.f;
+        if (cudaEventElapsedTime(&ms, k0[i], k1[i]) == cudaSuccess) total += ms;
+        cudaEventDestroy(k0[i]);
+        cudaEventDestroy(k1[i]);
+    }
+    cudaGetLastError();
+    e->lastMs = total;
+    return rcOut;
+}
+
+}  // namespace nnbvh
+
+// ---------------------------------------------------------------------------
+// Public entry points
+// ---------------------------------------------------------------------------
+extern "C" int nnbvh_intersect_closest(nnbvh_engine *e, const nnbvh_ray *rays, uint64_t n,
+                                       nnbvh_hit *hits) {
+    Batch b;
+    b.rays = rays;
+    b.n = n;
+    b.out.hits = hits;
+    return RunBatch(e, b);
+}
+
+extern "C" int nnbvh_intersect_any(nnbvh_engine *e, const nnbvh_ray *rays, uint64_t n,
+                                   uint8_t *occluded) {
+    Batch b;
+    b.any = true;
+    b.rays = rays;
+    b.n = n;
+    b.out.occ = occluded;
+    return RunBatch(e, b);
+}
+
+static void FillPlanes(Batch &b, const float *ox, const float *oy, const float *oz,
+                       const float *dx, const float *dy, const float *dz, const float *tMax) {
+    b.soa = true;
+    b.planes[0] = ox; b.planes[1] = oy; b.planes[2] = oz;
+    b.planes[3] = dx; b.planes[4] = dy; b.planes[5] = dz;
+    b.planes[6] = tMax;
+}
+
+extern "C" int nnbvh_intersect_closest_soa(nnbvh_engine *e, const float *ox, const float *oy,
+                                           const float *oz, const float *dx, const float *dy,
+                                           const float *dz, const float *tMax, uint64_t n,
+                                           nnbvh_hit *hits) {
+    Batch b;
+    FillPlanes(b, ox, oy, oz, dx, dy, dz, tMax);
+    b.n = n;
+    b.out.hits = hits;
+    return RunBatch(e, b);
+}
+
+extern "C" int nnbvh_intersect_any_soa(nnbvh_engine *e, const float *ox, const float *oy,
+                                       const float *oz, const float *dx, const float *dy,
+                                       const float *dz, const float *tMax, uint64_t n,
+                                       uint8_t *occluded) {
+    Batch b;
+    FillPlanes(b, ox, oy, oz, dx, dy, dz, tMax);
+    b.any = true;
+    b.n = n;
+    b.out.occ = occluded;
+    return RunBatch(e, b);
+}
+
+extern "C" int nnbvh_intersect_counters(nnbvh_engine *e, const nnbvh_ray *rays, uint64_t n,
+                                        int32_t anyHit, nnbvh_hit *hits, uint8_t *occluded,
+                                        uint32_t *nodesVisited, uint32_t *triTests) {
+    Batch b;
+    b.any = anyHit != 0;
+    b.counters = true;
+    b.rays = rays;
+    b.n = n;
+    b.out.hits = hits;
+    b.out.occ = occluded;
+    b.out.nodesVisited = nodesVisited;
+    b.out.triTests = triTests;
+    return RunBatch(e, b);
+}
+
+// ---------------------------------------------------------------------------
+// Known-answer hooks: the device versions of IntersectTriangle / Bounds3f::IntersectP
+// ---------------------------------------------------------------------------
+namespace nnbvh {
+
+__global__ void TestTrianglesKernel(const float4 *__restrict__ rays, const float *__restrict__ tris9,
+                                    uint64_t n, uint8_t *__restrict__ hit, float *__restrict__ out4) {
+    uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    float4 a = rays[2 * i], b = rays[2 * i + 1];
+    RayConst rc = MakeRayConst(a.x, a.y, a.z, b.x, b.y, b.z);
+    const float *p = tris9 + 9 * i;
+    float t = 0, b0 = 0, b1 = 0, b2 = 0;
+    bool h = false;
+    if (!TriangleDegenerate(p[0], p[1], p[2], p[3], p[4], p[5], p[6], p[7], p[8]))
+        h = TriangleTest(rc, a.w, p[0], p[1], p[2], p[3], p[4], p[5], p[6], p[7], p[8], &t, &b0,
+                         &b1, &b2);
+    hit[i] = h ? 1 : 0;
+    out4[4 * i + 0] = h ? t : 0.f;
+    out4[4 * i + 1] = h ? b0 : 0.f;
+    out4[4 * i + 2] = h ? b1 : 0.f;
+    out4[4 * i + 3] = h ? b2 : 0.f;
+}
+
+__global__ void TestBoxesKernel(const float4 *__restrict__ rays, const float *__restrict__ boxes6,
+                                uint64_t n, uint8_t *__restrict__ hit) {
+    uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    float4 a = rays[2 * i], b = rays[2 * i + 1];
+    RayConst rc = MakeRayConst(a.x, a.y, a.z, b.x, b.y, b.z);
+    float box[6];
+    for (int k = 0; k < 6; ++k) box[k] = boxes6[6 * i + k];
+    hit[i] = SlabTest(rc, box, a.w) ? 1 : 0;
+}
+
+}  // namespace nnbvh
+
+extern "C" int nnbvh_test_triangles(nnbvh_engine *e, const nnbvh_ray *rays, const float *tris9,
+                                    uint64_t n, uint8_t *hit, float *out4) {
+    if (!e || !rays || !tris9 || !hit || !out4)
+        return SetError(NNBVH_ERR_INVALID, "nnbvh_test_triangles: NULL argument");
+    if (n == 0) return NNBVH_OK;
+    CU(cudaSetDevice(e->device));
+    float4 *dR = nullptr;
+    float *dT = nullptr, *dO = nullptr;
+    uint8_t *dH = nullptr;
+    CU(cudaMalloc(&dR, n * 32));
+    CU(cudaMalloc(&dT, n * 36));
+    CU(cudaMalloc(&dO, n * 16));
+    CU(cudaMalloc(&dH, n));
+    CU(cudaMemcpy(dR, rays, n * 32, cudaMemcpyHostToDevice));
+    CU(cudaMemcpy(dT, tris9, n * 36, cudaMemcpyHostToDevice));
+    TestTrianglesKernel<<<(unsigned)((n + 127) / 128), 128, 0, e->stream>>>(dR, dT, n, dH, dO);
+    ++e->launches;
+    CU(cudaGetLastError());
+    CU(cudaStreamSynchronize(e->stream));
+    CU(cudaMemcpy(hit, dH, n, cudaMemcpyDeviceToHost));
+    CU(cudaMemcpy(out4, dO, n * 16, cudaMemcpyDeviceToHost));
+    cudaFree(dR); cudaFree(dT); cudaFree(dO); cudaFree(dH);
+    return NNBVH_OK;
+}
+
+extern "C" int nnbvh_test_boxes(nnbvh_engine *e, const nnbvh_ray *rays, const float *boxes6,
+                                uint64_t n, uint8_t *hit) {
+    if (!e || !rays || !boxes6 || !hit)
+        return SetError(NNBVH_ERR_INVALID, "nnbvh_test_boxes: NULL argument");
+    if (n == 0) return NNBVH_OK;
+    CU(cudaSetDevice(e->device));
+    float4 *dR = nullptr;
+    float *dB = nullptr;
+    uint8_t *dH = nullptr;
+    CU(cudaMalloc(&dR, n * 32));
+    CU(cudaMalloc(&dB, n * 24));
+    CU(cudaMalloc(&dH, n));
+    CU(cudaMemcpy(dR, rays, n * 32, cudaMemcpyHostToDevice));
+    CU(cudaMemcpy(dB, boxes6, n * 24, cudaMemcpyHostToDevice));
+    TestBoxesKernel<<<(unsigned)((n + 127) / 128), 128, 0, e->stream>>>(dR, dB, n, dH);
+    ++e->launches;
+    CU(cudaGetLastError());
+    CU(cudaStreamSynchronize(e->stream));
+    CU(cudaMemcpy(hit, dH, n, cudaMemcpyDeviceToHost));
+    cudaFree(dR); cudaFree(dB); cudaFree(dH);
+    return NNBVH_OK;
+}

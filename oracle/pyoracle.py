@@ -98,6 +98,14 @@ class Oracle:
         return bool(self.lib.nnbvh_oracle_box(_p(ray8), _p(box6)))
 
 
+def as_pbrt_stores(tris9: np.ndarray) -> np.ndarray:
+    """Vertex positions as the reference's TriangleMesh holds them.  Its constructor
+    pushes every vertex through renderFromObject (util/mesh.cpp:36-39); even for the
+    identity that computes 0*x + 0*y + 1*z + 0, which turns -0.0 into +0.0.  Parity is
+    on the geometry the reference actually traces, so fixtures store this form."""
+    return (np.asarray(tris9, dtype=np.float32) + np.float32(0.0)).astype(np.float32)
+
+
 def ref_available() -> bool:
     return os.path.exists(REF_SO)
 
@@ -141,6 +149,8 @@ class Reference:
     def scene(self, tris9: np.ndarray, max_prims: int = 4, split: str = "sah"):
         """Build the reference BVHAggregate over a de-indexed triangle soup."""
         tris9 = np.ascontiguousarray(tris9, dtype=np.float32).reshape(-1, 9)
+        if np.any(np.signbit(tris9) & (tris9 == 0)):
+            raise ValueError("triangle soup holds -0.0: pass as_pbrt_stores(tris) to both sides")
         T = tris9.shape[0]
         verts = tris9.reshape(-1, 3)
         idx = np.arange(3 * T, dtype=np.int32)

@@ -1,0 +1,98 @@
+"""CPU: the C-ABI library loads, exports what include/nnbvh.h declares, the host
+builder reproduces the reference tree, and compute fails loudly without a GPU."""
+import ctypes
+import os
+import re
+
+import numpy as np
+import pytest
+
+from conftest import ROOT, soup
+
+
+def test_library_exports_every_declared_symbol():
+    from nn_bvh_b200 import capi
+    L = capi.lib()
+    hdr = open(os.path.join(ROOT, "include", "nnbvh.h")).read()
+    declared = set(re.findall(r"\b(nnbvh_[a-z_0-9]+)\s*\(", hdr))
+    assert declared == set(capi.SYMBOLS), declared ^ set(capi.SYMBOLS)
+    for s in declared:
+        assert hasattr(L, s), s
+    assert b"sm_100a" in L.nnbvh_version()
+
+
+def test_struct_sizes_match_header():
+    from nn_bvh_b200 import capi
+    assert capi.NODE_DTYPE.itemsize == 32   # sizeof(LinearBVHNode), aggregates.cpp:129
+    assert capi.RAY_DTYPE.itemsize == 32
+    assert capi.HIT_DTYPE.itemsize == 20
+    assert ctypes.sizeof(capi.Options) == 32
+
+
+@pytest.mark.parametrize("split", ["sah", "middle", "equal"])
+def test_host_builder_matches_golden_reference_tree(golden, split):
+    import nn_bvh_b200 as nb
+    g = golden["scene_small"]
+    nodes, order = nb.build_bvh(g["tris"], 4, split)
+    assert np.array_equal(nodes.view(np.uint32).reshape(-1, 8), g[f"{split}_nodes"])
+    assert np.array_equal(order, g[f"{split}_order"].astype(np.uint32))
+
+
+def test_host_builder_matches_oracle_and_threads(oracle):
+    import nn_bvh_b200 as nb
+    rng = np.random.default_rng(5)
+    tris = soup(rng, 200_000, 0.01)   # > 64K spans: exercises the threaded path
+    n1, o1 = nb.build_bvh(tris, 4, "sah", threads=1)
+    n8, o8 = nb.build_bvh(tris, 4, "sah", threads=8)
+    on, oo = oracle.build_bvh(tris, 4, "sah")
+    assert np.array_equal(n1, n8) and np.array_equal(o1, o8)
+    assert np.array_equal(n1.view(np.uint32).reshape(-1, 8), on)
+    assert np.array_equal(o1, oo.astype(np.uint32))
+    assert nb.tree_stack_depth(n1) <= 64
+
+
+def test_builder_edge_cases():
+    import nn_bvh_b200 as nb
+    one = np.array([[0, 0, 0, 1, 0, 0, 0, 1, 0]], np.float32)
+    nodes, order = nb.build_bvh(one, 4, "sah")
+    assert len(nodes) == 1 and nodes[0]["nPrimitives"] == 1 and order[0] == 0
+    same = np.tile(one, (7, 1))   # identical centroids -> one leaf of 7 (aggregates.cpp:225)
+    nodes, _ = nb.build_bvh(same, 4, "sah")
+    assert len(nodes) == 1 and nodes[0]["nPrimitives"] == 7
+    with pytest.raises(nb.NnbvhError):
+        nb.build_bvh(np.zeros((0, 9), np.float32), 4, "sah")
+    with pytest.raises(nb.NnbvhError):
+        nb.build_bvh(one, 4, "hlbvh")
+
+
+def test_stack_depth_of_chain():
+    import nn_bvh_b200 as nb
+    # left-deep chain of k interior nodes
+    k = 70
+    nodes = np.zeros(2 * k + 1, dtype=nb.NODE_DTYPE)
+    # pre-order: interior i at index i (i<k), its first child i+1, second child = leaf at 2k-i
+    for i in range(k):
+        nodes[i]["offset"] = 2 * k - i
+    for j in range(k, 2 * k + 1):
+        nodes[j]["nPrimitives"] = 1
+        nodes[j]["offset"] = j - k
+    assert nb.tree_stack_depth(nodes) == k
+
+
+def test_no_gpu_fails_loudly():
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    import nn_bvh_b200 as nb
+    with pytest.raises(nb.NnbvhError) as ei:
+        nb.GPUBVHAggregate(np.array([[0, 0, 0, 1, 0, 0, 0, 1, 0]], np.float32), 4)
+    assert ei.value.code == -2 and "no CPU fallback" in str(ei.value)
+
+
+def test_product_never_imports_oracle():
+    pkg = os.path.join(ROOT, "nn_bvh_b200")
+    for dp, _, fs in os.walk(pkg):
+        for f in fs:
+            if f.endswith((".py", ".cu", ".cuh", ".cpp", ".h", ".sh")):
+                txt = open(os.path.join(dp, f), errors="replace").read()
+                assert "pyoracle" not in txt and "nnbvh_oracle" not in txt and "_ref/" not in txt, f

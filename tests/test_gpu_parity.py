@@ -1,0 +1,195 @@
+"""GPU: the CUDA engine (through libnnbvh.so's C ABI) against the oracle and the
+committed golden vectors.  Bit-exact: hit/miss, primitive index, t, b0..b2 (the
+north star allows 2 ulp on t/b; the engine is held to 0), counters included."""
+import numpy as np
+import pytest
+
+from conftest import rand_rays, soup
+
+pytestmark = pytest.mark.gpu
+
+KERNELS = {"basic": 1, "wide": 2}
+
+
+def _agg(tris=None, kernel="wide", **kw):
+    import nn_bvh_b200 as nb
+    return nb.GPUBVHAggregate(tris, kernel=KERNELS[kernel], **kw)
+
+
+def _as_words(h):
+    return np.ascontiguousarray(h).view(np.uint32).reshape(-1, 5)
+
+
+def test_device_triangle_golden(golden):
+    g = golden["tri_vectors"]
+    agg = _agg(np.array([[0, 0, 0, 1, 0, 0, 0, 1, 0]], np.float32), max_prims_in_node=4)
+    hit, out = agg.test_triangles(g["rays"], g["tris"])
+    assert np.array_equal(hit, g["hit"])
+    assert np.array_equal(out.view(np.uint32), g["out"].view(np.uint32))
+    assert hit[0] == 0   # Triangle.BadCases, shapes_test.cpp:435-449
+
+
+def test_device_box_golden(golden):
+    g = golden["box_vectors"]
+    agg = _agg(np.array([[0, 0, 0, 1, 0, 0, 0, 1, 0]], np.float32), max_prims_in_node=4)
+    assert np.array_equal(agg.test_boxes(g["rays"], g["boxes"]), g["hit"])
+
+
+@pytest.mark.parametrize("kernel", ["basic", "wide"])
+@pytest.mark.parametrize("split", ["sah", "middle", "equal"])
+def test_scene_golden(golden, kernel, split):
+    g = golden["scene_small"]
+    agg = _agg(g["tris"], kernel, max_prims_in_node=4, split_method=split)
+    assert np.array_equal(agg.nodes.view(np.uint32).reshape(-1, 8), g[f"{split}_nodes"])
+    hits = agg.IntersectBatch(g["rays"])
+    assert np.array_equal(_as_words(hits), g[f"{split}_hits"])
+    assert np.array_equal(agg.IntersectPBatch(g["rays"]), g[f"{split}_occ"])
+    st = g[f"{split}_stats"]
+    h2, nv, tt = agg.IntersectCounters(g["rays"])
+    assert np.array_equal(_as_words(h2), g[f"{split}_hits"])
+    assert (int(nv.sum()), int(tt.sum())) == (st[0], st[1])
+    o2, nv, tt = agg.IntersectCounters(g["rays"], any_hit=True)
+    assert np.array_equal(o2, g[f"{split}_occ"])
+    assert (int(nv.sum()), int(tt.sum())) == (st[2], st[3])
+
+
+@pytest.mark.parametrize("kernel", ["basic", "wide"])
+@pytest.mark.parametrize("T,s,mp", [(1, 0.3, 4), (2, 0.3, 4), (37, 0.2, 4), (20000, 0.02, 4),
+                                     (20000, 0.05, 1), (60000, 0.01, 255)])
+def test_random_soups_vs_oracle(oracle, kernel, T, s, mp):
+    rng = np.random.default_rng(T * 7 + mp)
+    tris = soup(rng, T, s)
+    agg = _agg(tris, kernel, max_prims_in_node=mp)
+    nodes = agg.nodes.view(np.uint32).reshape(-1, 8)
+    rays = rand_rays(rng, 100_000)
+    rays[50_000:, 3] = rng.random(50_000)
+    want, wnv, wtt = oracle.intersect(nodes, agg.ordered_tris9, rays, counters=True)
+    assert np.array_equal(_as_words(agg.IntersectBatch(rays)), want)
+    assert np.array_equal(agg.IntersectPBatch(rays), oracle.intersect_p(nodes, agg.ordered_tris9, rays))
+    _, nv, tt = agg.IntersectCounters(rays)
+    assert np.array_equal(nv, wnv) and np.array_equal(tt, wtt)
+
+
+@pytest.mark.parametrize("kernel", ["basic", "wide"])
+def test_edge_inputs(oracle, kernel):
+    rng = np.random.default_rng(3)
+    tris = soup(rng, 5000, 0.05)
+    agg = _agg(tris, kernel, max_prims_in_node=4)
+    nodes = agg.nodes.view(np.uint32).reshape(-1, 8)
+    # empty batch
+    assert len(agg.IntersectBatch(np.zeros((0, 8), np.float32))) == 0
+    # ragged sizes around the warp / block / chunk boundaries
+    for n in (1, 31, 32, 33, 255, 257, 4097):
+        rays = rand_rays(rng, n)
+        assert np.array_equal(_as_words(agg.IntersectBatch(rays)),
+                              oracle.intersect(nodes, agg.ordered_tris9, rays)), n
+    # axis-aligned directions incl. -0.0, origins on box planes, tMax = 0, inf, tiny
+    rays = rand_rays(rng, 6000)
+    rays[:2000, 4:7] = 0
+    rays[np.arange(2000), 4 + np.arange(2000) % 3] = np.where(np.arange(2000) % 2, 1.0, -1.0)
+    rays[1000:2000, 4:7] = np.where(rays[1000:2000, 4:7] == 0, np.float32(-0.0), rays[1000:2000, 4:7])
+    rays[2000:3000, 0] = nodes[0, 0:1].view(np.float32)   # origin.x on the root's pMin.x plane
+    rays[3000:3500, 3] = 0.0
+    rays[3500:4000, 3] = 1e-30
+    want = oracle.intersect(nodes, agg.ordered_tris9, rays)
+    assert np.array_equal(_as_words(agg.IntersectBatch(rays)), want)
+    assert np.array_equal(agg.IntersectPBatch(rays), oracle.intersect_p(nodes, agg.ordered_tris9, rays))
+
+
+@pytest.mark.parametrize("kernel", ["basic", "wide"])
+def test_empty_scene_misses(kernel):
+    import nn_bvh_b200 as nb
+    agg = _agg(None, kernel)
+    rays = rand_rays(np.random.default_rng(0), 100)
+    h = agg.IntersectBatch(rays)
+    assert np.all(h["prim"] == nb.MISS) and not agg.IntersectPBatch(rays).any()
+    with pytest.raises(RuntimeError):
+        agg.Bounds()
+
+
+def test_deep_tree_rejected():
+    import nn_bvh_b200 as nb
+    k = 70
+    nodes = np.zeros(2 * k + 1, dtype=nb.NODE_DTYPE)
+    for i in range(k):
+        nodes[i]["offset"] = 2 * k - i
+        nodes[i]["bounds"] = [0, 0, 0, 1, 1, 1]
+    for j in range(k, 2 * k + 1):
+        nodes[j]["nPrimitives"] = 1
+        nodes[j]["offset"] = j - k
+        nodes[j]["bounds"] = [0, 0, 0, 1, 1, 1]
+    tris = np.tile(np.array([[0, 0, 0, 1, 0, 0, 0, 1, 0]], np.float32), (k + 1, 1))
+    with pytest.raises(nb.NnbvhError) as ei:
+        nb.GPUBVHAggregate(nodes=nodes, ordered_tris9=tris)
+    assert ei.value.code == -4
+
+
+def test_watertight_sphere(oracle):
+    """Triangle.Watertight (shapes_test.cpp:31-131, disabled upstream): rays from inside a
+    jittered triangulated sphere, many aimed exactly at vertices, must always hit."""
+    rng = np.random.default_rng(12111)
+    nt, npk = 16, 16
+    th = np.linspace(0, np.pi, nt + 1)
+    ph = np.linspace(0, 2 * np.pi, npk + 1)[:-1]
+    P = np.array([[np.sin(t) * np.cos(p), np.sin(t) * np.sin(p), np.cos(t)] for t in th for p in ph])
+    P = (P * (1 + 0.05 * rng.random((len(P), 1)))).astype(np.float32)
+    P[:npk] = P[0]
+    P[-npk:] = P[-1]
+    idx = []
+    for i in range(nt):
+        for j in range(npk):
+            a, b = i * npk + j, i * npk + (j + 1) % npk
+            c, d = a + npk, b + npk
+            idx += [[a, c, b], [b, c, d]]
+    tris = P[np.array(idx)].reshape(-1, 9) + np.float32(0)
+    agg = _agg(tris, "wide", max_prims_in_node=4)
+    n = 100_000
+    rays = np.zeros((n, 8), np.float32)
+    rays[:, :3] = rng.random((n, 3)) * 0.2 - 0.1
+    d = rng.normal(size=(n, 3))
+    aim = rng.integers(0, len(P), size=n)
+    d[: n // 2] = P[aim[: n // 2]] - rays[: n // 2, :3]
+    rays[:, 4:7] = d
+    rays[:, 3] = np.inf
+    h = agg.IntersectBatch(rays)
+    import nn_bvh_b200 as nb
+    assert np.all(h["prim"] != nb.MISS)
+    nodes = agg.nodes.view(np.uint32).reshape(-1, 8)
+    assert np.array_equal(_as_words(h), oracle.intersect(nodes, agg.ordered_tris9, rays))
+
+
+def test_single_ray_surface_and_tensors(oracle):
+    import torch
+    import nn_bvh_b200 as nb
+    rng = np.random.default_rng(8)
+    tris = soup(rng, 3000, 0.05)
+    agg = nb.GPUBVHAggregate.Create(tris, {"maxnodeprims": 4, "splitmethod": "sah"})
+    nodes = agg.nodes.view(np.uint32).reshape(-1, 8)
+    rays = rand_rays(rng, 50_000)
+    want = oracle.intersect(nodes, agg.ordered_tris9, rays)
+    # single-ray BVHAggregate::Intersect / IntersectP surface
+    for i in range(20):
+        r = agg.Intersect((rays[i, :3], rays[i, 4:7]), rays[i, 3])
+        if want[i, 0] == nb.MISS:
+            assert r is None and not agg.IntersectP((rays[i, :3], rays[i, 4:7]))
+        else:
+            assert r[0] == want[i, 0] and np.float32(r[1]).view(np.uint32) == want[i, 1]
+            assert agg.IntersectP((rays[i, :3], rays[i, 4:7]))
+    # device-resident tensors (no copies inside the call) and pinned host tensors
+    dr = torch.from_numpy(rays).cuda()
+    dh = torch.zeros((len(rays), 5), dtype=torch.int32, device="cuda")
+    agg.IntersectBatch(dr, hits=dh)
+    torch.cuda.synchronize()
+    assert agg.last_kernel_ms() > 0
+    assert np.array_equal(dh.cpu().numpy().view(np.uint32), want)
+    pr = torch.from_numpy(rays).pin_memory()
+    ph = torch.zeros((len(rays), 5), dtype=torch.int32).pin_memory()
+    agg.IntersectBatch(pr, hits=ph)
+    assert np.array_equal(ph.numpy().view(np.uint32), want)
+    # SoA entry points (wavefront queue layout)
+    cols = [np.ascontiguousarray(rays[:, k]) for k in (0, 1, 2, 4, 5, 6, 3)]
+    hs = agg.IntersectBatchSoA(*cols)
+    assert np.array_equal(_as_words(hs), want)
+    occ = agg.IntersectBatchSoA(*cols, any_hit=True)
+    assert np.array_equal(occ, oracle.intersect_p(nodes, agg.ordered_tris9, rays))
+    assert agg.launch_count() > 0

@@ -1,0 +1,175 @@
+#!/usr/bin/env python3
+"""tools/make_golden.py -- generate tests/golden/*.npz from the UNMODIFIED reference.
+
+Runs only in this container (needs oracle/_ref built from /root/reference).
+Every array below is produced by the reference's own code through
+oracle/ref_driver.cpp; the fixtures are small so they can be committed.
+
+  tri_vectors.npz   IntersectTriangle known answers: the reference's one golden
+                    vector (Triangle.BadCases, shapes_test.cpp:435-449), the
+                    Reintersect-style random triangles with coordinates
+                    10^U(-8,8) (shapes_test.cpp:22-25,133-154), edge/vertex hits
+                    that take the double-precision fallback, degenerate triangles.
+  box_vectors.npz   Bounds3f::IntersectP answers incl. zero direction components,
+                    origins on slab planes (0*inf = NaN), negative zero.
+  scene_small.npz   a 3000-triangle soup: reference SAH/Middle/EqualCounts trees
+                    (nodes + order), closest-hit records, IntersectP results,
+                    counter totals, for 4096 rays.
+"""
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+from oracle.pyoracle import Reference, as_pbrt_stores  # noqa: E402
+
+OUT = os.path.join(ROOT, "tests", "golden")
+
+
+def p_exp(rng, n):
+    """pExp of shapes_test.cpp:22-25: sign * 10^U(-8,8)."""
+    logu = rng.uniform(-8, 8, size=n)
+    sign = np.where(rng.random(n) < 0.5, -1.0, 1.0)
+    return (sign * 10.0 ** logu).astype(np.float32)
+
+
+def tri_vectors(ref, rng):
+    rays, tris = [], []
+    # (1) Triangle.BadCases, shapes_test.cpp:435-449 (expects a miss)
+    rays.append([-0.36098, 3.2618, 2.6918, np.inf, 0.0061, -0.0014, -0.9999, 0.0])  # placeholder 0
+    tris.append([5.0, 8.0, 9.0, 5.0, 8.0, 9.0, 5.0, 8.0, 9.0])
+    # (2) random triangles over 16 orders of magnitude, rays aimed at interior points
+    n = 3000
+    p = p_exp(rng, n * 9).reshape(n, 3, 3)
+    b = rng.dirichlet([1, 1, 1], size=n)
+    target = (p.astype(np.float64) * b[:, :, None]).sum(1)
+    o = p_exp(rng, n * 3).reshape(n, 3).astype(np.float64)
+    d = target - o
+    for i in range(n):
+        tm = np.inf if i % 3 else 1.0
+        dd = d[i] / (np.linalg.norm(d[i]) if i % 2 else 1.0)
+        rays.append([*o[i], tm, *dd, 0.0])
+        tris.append(p[i].ravel())
+    # (3) rays through vertices / edge midpoints of well-conditioned triangles (e == 0 paths)
+    n = 2000
+    p = rng.integers(-8, 9, size=(n, 3, 3)).astype(np.float32)
+    for i in range(n):
+        k = i % 6
+        tgt = p[i, k] if k < 3 else 0.5 * (p[i, k - 3] + p[i, (k - 2) % 3])
+        o = rng.integers(-20, 21, size=3).astype(np.float32)
+        rays.append([*o, np.inf, *(tgt - o), 0.0])
+        tris.append(p[i].ravel())
+    # (4) axis-aligned rays (zero direction components), small random scenes
+    n = 1000
+    p = rng.random((n, 3, 3)).astype(np.float32)
+    for i in range(n):
+        d = np.zeros(3, np.float32)
+        d[i % 3] = 1.0 if (i // 3) % 2 else -1.0
+        c = p[i].mean(0)
+        o = c - d * 2
+        if i % 5 == 0:
+            o = o + rng.normal(size=3).astype(np.float32) * 0.3
+        rays.append([*o, np.inf, *d, 0.0])
+        tris.append(p[i].ravel())
+    # (5) degenerate triangles
+    for i in range(50):
+        a = rng.random(3).astype(np.float32)
+        bb = rng.random(3).astype(np.float32)
+        tri = [a, bb, a + (bb - a) * np.float32(0.5)] if i % 2 else [a, a, bb]
+        rays.append([0, 0, -5, np.inf, *(a - np.array([0, 0, -5], np.float32)), 0.0])
+        tris.append(np.concatenate(tri))
+    rays = np.array(rays, dtype=np.float32)
+    tris = np.array(tris, dtype=np.float32)
+    # the real BadCases vector (shapes_test.cpp:438-446)
+    tris[0] = [-1113.45459, -79.049614, -56.2431908, -1113.45459, -87.0922699, -56.2431908,
+               -1113.45459, -79.2090149, -56.2431908]
+    rays[0] = [-1081.47925, 99.9999542, 87.7701111, np.inf, -32.1072998, -183.355865,
+               -144.607635, 0.014]
+    hit = np.zeros(len(rays), np.uint8)
+    out = np.zeros((len(rays), 4), np.float32)
+    for i in range(len(rays)):
+        h, o4 = ref.triangle(rays[i], tris[i])
+        hit[i] = h
+        out[i] = o4 if h else 0
+    assert hit[0] == 0, "reference BadCases vector must miss"
+    np.savez_compressed(os.path.join(OUT, "tri_vectors.npz"), rays=rays, tris=tris, hit=hit, out=out)
+    print("tri_vectors", len(rays), "hits", int(hit.sum()))
+
+
+def box_vectors(ref, rng):
+    n = 6000
+    lo = rng.integers(-4, 4, size=(n, 3)).astype(np.float32)
+    hi = lo + rng.integers(0, 4, size=(n, 3)).astype(np.float32)  # some flat boxes
+    o = rng.integers(-6, 7, size=(n, 3)).astype(np.float32)       # often ON a slab plane
+    d = rng.integers(-2, 3, size=(n, 3)).astype(np.float32)       # many zero components
+    d[np.all(d == 0, axis=1)] = [0, 0, 1]
+    neg0 = rng.random((n, 3)) < 0.15
+    d = np.where((d == 0) & neg0, np.float32(-0.0), d)
+    tmax = np.where(rng.random(n) < 0.5, np.inf, rng.random(n) * 8).astype(np.float32)
+    # second half: generic floats
+    h = n // 2
+    lo[h:] = rng.normal(size=(n - h, 3)).astype(np.float32)
+    hi[h:] = lo[h:] + np.abs(rng.normal(size=(n - h, 3))).astype(np.float32)
+    o[h:] = rng.normal(size=(n - h, 3)).astype(np.float32) * 3
+    d[h:] = rng.normal(size=(n - h, 3)).astype(np.float32)
+    aim = rng.random(n) < 0.6   # aim most rays at a point of (or on the surface of) the box
+    w = rng.integers(0, 3, size=(n, 3)).astype(np.float32) / 2   # 0, .5, 1 -> faces/edges/corners
+    tgt = lo + (hi - lo) * w
+    d = np.where(aim[:, None] & np.any(tgt != o, axis=1)[:, None], tgt - o, d).astype(np.float32)
+    rays = np.zeros((n, 8), np.float32)
+    rays[:, :3], rays[:, 3], rays[:, 4:7] = o, tmax, d
+    boxes = np.concatenate([lo, hi], 1)
+    hit = np.array([ref.box(rays[i], boxes[i]) for i in range(n)], dtype=np.uint8)
+    np.savez_compressed(os.path.join(OUT, "box_vectors.npz"), rays=rays, boxes=boxes, hit=hit)
+    print("box_vectors", n, "hits", int(hit.sum()))
+
+
+def scene_small(ref, rng):
+    T = 3000
+    # clustered soup with shared vertices (grid patches) + duplicates -> ties, leaves of 1-4
+    g = 20
+    u, v = np.meshgrid(np.arange(g + 1), np.arange(g + 1), indexing="ij")
+    P = np.stack([u, v, np.sin(u * 0.7) * np.cos(v * 0.5) * 2], -1).astype(np.float32) / 10
+    q = np.stack([P[:-1, :-1], P[1:, :-1], P[1:, 1:], P[:-1, 1:]], 2).reshape(-1, 4, 3)
+    grid = np.concatenate([q[:, [0, 1, 2]], q[:, [2, 3, 0]]], 0).reshape(-1, 9)   # 800 tris
+    c = rng.random((T - 2 * len(grid), 1, 3), dtype=np.float32) * 2
+    soup = (c + 0.15 * (rng.random((len(c), 3, 3), dtype=np.float32) * 2 - 1)).reshape(-1, 9)
+    tris = as_pbrt_stores(np.concatenate([grid, grid, soup], 0))   # grid twice: exact ties
+    N = 4096
+    rays = np.zeros((N, 8), np.float32)
+    rays[:, :3] = rng.random((N, 3)) * 3 - 0.5
+    d = rng.normal(size=(N, 3))
+    rays[:, 4:7] = d / np.linalg.norm(d, axis=1, keepdims=True)
+    rays[:, 3] = np.inf
+    # a block of straight-down rays through grid vertices (shared edges/vertices, duplicates)
+    k = 600
+    rays[:k, 0] = rng.integers(0, g + 1, size=k) / 10
+    rays[:k, 1] = rng.integers(0, g + 1, size=k) / 10
+    rays[:k, 2] = 3.0
+    rays[:k, 4:7] = [0, 0, -1]
+    rays[N // 2:, 3] = rng.random(N - N // 2) * 1.5   # finite tMax on half
+    out = {"tris": tris, "rays": rays}
+    for split in ("sah", "middle", "equal"):
+        sc = ref.scene(tris, 4, split)
+        nodes, order = ref.export(sc, len(tris))
+        ref.stats()
+        hits = ref.intersect(sc, rays, parallel=False)
+        st_c = ref.stats()
+        occ = ref.intersect_p(sc, rays, parallel=False)
+        st_p = ref.stats()
+        out.update({f"{split}_nodes": nodes, f"{split}_order": order, f"{split}_hits": hits,
+                    f"{split}_occ": occ,
+                    f"{split}_stats": np.array([st_c[0], st_c[1], st_p[0], st_p[1]], np.int64)})
+        print(split, "nodes", len(nodes), "hit frac", (hits[:, 0] != 0xFFFFFFFF).mean(), st_c, st_p)
+    np.savez_compressed(os.path.join(OUT, "scene_small.npz"), **out)
+
+
+if __name__ == "__main__":
+    os.makedirs(OUT, exist_ok=True)
+    ref = Reference(threads=1)
+    rng = np.random.default_rng(20261104)
+    tri_vectors(ref, rng)
+    box_vectors(ref, rng)
+    scene_small(ref, rng)
