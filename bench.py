@@ -240,7 +240,9 @@ def run_ours(args):
     n = args.rays
 
     # ---- device-resident buffers; engine launches on torch's current stream ----
-    stream = torch.cuda.current_stream()
+    # a non-default torch stream: handle 0 would mean "engine's own stream" to the C ABI
+    stream = torch.cuda.Stream(device=dev)
+    torch.cuda.set_stream(stream)
     agg.set_stream(stream.cuda_stream)
     d_b = torch.from_numpy(bounce.view(np.float32).reshape(-1, 8)).to(dev)
     d_s = torch.from_numpy(shadow.view(np.float32).reshape(-1, 8)).to(dev)

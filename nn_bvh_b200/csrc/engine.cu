@@ -94,8 +94,9 @@ struct nnbvh_engine {
     static constexpr int kSlots = 3;
     Slot slots[kSlots];
     // tuning knobs (env overridable, see nnbvh_create)
-    int wideMinB = 2;        // CTAs/SM the WideKernel variant is compiled for
-    int refillBelow = 32;
+    int wideMinB = 4;        // CTAs/SM the WideKernel variant is compiled for
+    int refillBelow = 24;
+    int leafQuorum = 16;
     uint64_t chunkRays = 1u << 20;
 };
 
@@ -140,6 +141,7 @@ extern "C" int nnbvh_create(const nnbvh_options *opts, nnbvh_engine **out) {
     e->smemTopNodes = EnvInt("NNBVH_SMEM_NODES", e->smemTopNodes);
     e->wideMinB = EnvInt("NNBVH_WIDE_MINB", e->wideMinB);
     e->refillBelow = EnvInt("NNBVH_REFILL_BELOW", e->refillBelow);
+    e->leafQuorum = EnvInt("NNBVH_LEAF_QUORUM", e->leafQuorum);
     e->chunkRays = (uint64_t)EnvInt("NNBVH_CHUNK_RAYS", (int)e->chunkRays);
     CU(cudaStreamCreateWithFlags(&e->ownStream, cudaStreamNonBlocking));
     e->stream = e->ownStream;
@@ -430,7 +432,7 @@ static int LaunchTraversal(nnbvh_engine *e, cudaStream_t st, bool any, bool coun
     } else {
         int minB = (e->wideMinB >= 1 && e->wideMinB <= 4) ? e->wideMinB : 2;
         uint32_t budgetNodes = (uint32_t)((e->maxSmemOptin - 2048) / minB / sizeof(WideNode));
-        uint32_t want = e->smemTopNodes >= 0 ? (uint32_t)e->smemTopNodes : 2048u / minB;
+        uint32_t want = e->smemTopNodes >= 0 ? (uint32_t)e->smemTopNodes : 0u;  // measured: L1 beats explicit staging
         uint32_t smemNodes = std::min(std::min(want, budgetNodes), e->sc.topNodes);
         WideParams p;
         p.sc = e->sc;
@@ -441,6 +443,7 @@ static int LaunchTraversal(nnbvh_engine *e, cudaStream_t st, bool any, bool coun
         p.cursor = cursor;
         p.smemNodes = smemNodes;
         p.refillBelow = (uint32_t)std::min(32, std::max(1, e->refillBelow));
+        p.leafQuorum = (uint32_t)std::min(32, std::max(1, e->leafQuorum));
         CU(cudaMemsetAsync(cursor, 0, sizeof(unsigned long long), st));
         int rc = any ? LaunchWide<true>(e, st, p, smemNodes * (uint32_t)sizeof(WideNode))
                      : LaunchWide<false>(e, st, p, smemNodes * (uint32_t)sizeof(WideNode));

@@ -212,6 +212,7 @@ struct WideParams {
     unsigned long long *cursor;  // global ray cursor (zeroed before launch)
     uint32_t smemNodes;          // WideNodes staged in shared memory (<= sc.topNodes)
     uint32_t refillBelow;        // refill finished lanes when fewer than this many are live
+    uint32_t leafQuorum;         // run the leaf phase once this many lanes wait at a leaf
 };
 
 struct NodeRegs {
@@ -276,6 +277,13 @@ __global__ void __launch_bounds__(256, MINB) WideKernel(WideParams p) {
     bool exhausted = false;  // the global cursor ran past n (warp-uniform)
     uint32_t dummy = 0;
 
+    // Phase-separated loop.  An if/else "node or leaf" body runs both bodies
+    // almost every iteration (some lane of 32 is nearly always at a leaf), which
+    // measured at 8.7 active lanes per instruction.  Instead: lanes that reach a
+    // leaf PARK (no speculation -- the reference's order is kept exactly) while the
+    // others keep descending, until `leafQuorum` lanes are parked or nobody is
+    // descending; then the leaf body runs once for all parked lanes.
+    const unsigned leafQuorum = p.leafQuorum;
     while (true) {
         // ---- refill: finished lanes take the next rays from the global cursor ----
         unsigned liveMask = __ballot_sync(0xffffffffu, alive);
@@ -296,17 +304,13 @@ __global__ void __launch_bounds__(256, MINB) WideKernel(WideParams p) {
                     hit.prim = NNBVH_MISS;
                     hit.t = hit.b0 = hit.b1 = hit.b2 = 0.f;
                     sp = 0;
-                    alive = true;
                     // Root: the reference tests the root's own box first
                     // (aggregates.cpp:543); nodes == nullptr -> miss (:531).
-                    bool rootHit = false;
-                    if (sc.nNodes) rootHit = SlabTest(rc, sc.rootBox, tMax);
-                    if (rootHit) cur = sc.rootRef;
-                    else {
-                        alive = false;
-                        if (ANY) p.occluded[idx] = 0;
-                        else StoreHit(p.hits, idx, hit);
-                    }
+                    if (sc.nNodes && SlabTest(rc, sc.rootBox, tMax)) {
+                        cur = sc.rootRef;
+                        alive = true;
+                    } else if (ANY) p.occluded[idx] = 0;
+                    else StoreHit(p.hits, idx, hit);
                 }
             }
             liveMask = __ballot_sync(0xffffffffu, alive);
@@ -315,70 +319,87 @@ __global__ void __launch_bounds__(256, MINB) WideKernel(WideParams p) {
             if (exhausted) break;
             continue;
         }
-        if (!alive) continue;
 
-        bool finished = false;
-        bool doPop = false;
-        if (cur >= 0) {
-            // ---- interior: one fetch, both children's boxes ----
-            NodeRegs nd = LoadWide(sc.wide, top, p.smemNodes, cur);
-            const float lo0x = nd.q0.x, lo0y = nd.q0.y, lo0z = nd.q0.z;
-            const float hi0x = nd.q0.w, hi0y = nd.q1.x, hi0z = nd.q1.y;
-            const float lo1x = nd.q1.z, lo1y = nd.q1.w, lo1z = nd.q2.x;
-            const float hi1x = nd.q2.y, hi1y = nd.q2.z, hi1z = nd.q2.w;
-            float t0, t1;
-            bool ok0 = SlabStatic(rc, rc.negx ? hi0x : lo0x, rc.negx ? lo0x : hi0x,
-                                  rc.negy ? hi0y : lo0y, rc.negy ? lo0y : hi0y,
-                                  rc.negz ? hi0z : lo0z, rc.negz ? lo0z : hi0z, &t0);
-            bool ok1 = SlabStatic(rc, rc.negx ? hi1x : lo1x, rc.negx ? lo1x : hi1x,
-                                  rc.negy ? hi1y : lo1y, rc.negy ? lo1y : hi1y,
-                                  rc.negz ? hi1z : lo1z, rc.negz ? lo1z : hi1z, &t1);
-            ok0 = ok0 && (t0 < tMax);
-            ok1 = ok1 && (t1 < tMax);
-            const int axis = nd.q3.z;
-            const bool secondFirst = axis == 0 ? rc.negx : (axis == 1 ? rc.negy : rc.negz);
-            const bool okNear = secondFirst ? ok1 : ok0, okFar = secondFirst ? ok0 : ok1;
-            const int refNear = secondFirst ? nd.q3.y : nd.q3.x;
-            const int refFar = secondFirst ? nd.q3.x : nd.q3.y;
-            const float tFar = secondFirst ? t0 : t1;
-            if (okNear) {
-                if (okFar) {
-                    stackRef[sp] = refFar;
-                    stackT[sp] = tFar;
-                    ++sp;
+        // ---- phase A: interior nodes ----
+        while (true) {
+            const bool atNode = alive && cur >= 0;
+            const unsigned nodeMask = __ballot_sync(0xffffffffu, atNode);
+            const unsigned leafMask = __ballot_sync(0xffffffffu, alive && cur < 0);
+            if (nodeMask == 0 || (unsigned)__popc(leafMask) >= leafQuorum) break;
+            if (atNode) {
+                NodeRegs nd = LoadWide(sc.wide, top, p.smemNodes, cur);
+                const float lo0x = nd.q0.x, lo0y = nd.q0.y, lo0z = nd.q0.z;
+                const float hi0x = nd.q0.w, hi0y = nd.q1.x, hi0z = nd.q1.y;
+                const float lo1x = nd.q1.z, lo1y = nd.q1.w, lo1z = nd.q2.x;
+                const float hi1x = nd.q2.y, hi1y = nd.q2.z, hi1z = nd.q2.w;
+                float t0, t1;
+                const bool ok0 = SlabStatic(rc, rc.negx ? hi0x : lo0x, rc.negx ? lo0x : hi0x,
+                                            rc.negy ? hi0y : lo0y, rc.negy ? lo0y : hi0y,
+                                            rc.negz ? hi0z : lo0z, rc.negz ? lo0z : hi0z, &t0);
+                const bool ok1 = SlabStatic(rc, rc.negx ? hi1x : lo1x, rc.negx ? lo1x : hi1x,
+                                            rc.negy ? hi1y : lo1y, rc.negy ? lo1y : hi1y,
+                                            rc.negz ? hi1z : lo1z, rc.negz ? lo1z : hi1z, &t1);
+                const int axis = nd.q3.z;
+                const bool secondFirst = axis == 0 ? rc.negx : (axis == 1 ? rc.negy : rc.negz);
+                // "static" = every part of the box test that does not involve tMax.
+                const bool stNear = secondFirst ? ok1 : ok0, stFar = secondFirst ? ok0 : ok1;
+                const int refNear = secondFirst ? nd.q3.y : nd.q3.x;
+                const int refFar = secondFirst ? nd.q3.x : nd.q3.y;
+                const float tNear = secondFirst ? t1 : t0, tFar = secondFirst ? t0 : t1;
+                if (stNear && tNear < tMax) {
+                    // The far child is stacked whenever its static test passes, NOT only
+                    // when tFar < tMax now: the reference's tMax can GROW by an ulp (a
+                    // later primitive is accepted in scaled space, tScaled <= tMax*det,
+                    // with a rounded t above tMax; shapes.cpp:239-247), so a box that
+                    // fails `tMin < tMax` now may pass when the reference pops it.
+                    if (stFar) {
+                        stackRef[sp] = refFar;
+                        stackT[sp] = tFar;
+                        ++sp;
+                    }
+                    cur = refNear;
+                } else if (stFar && tFar < tMax) {
+                    cur = refFar;
+                } else {
+                    // pop until an entry whose box beats the current tMax (:570-574)
+                    while (true) {
+                        if (sp == 0) {
+                            alive = false;
+                            if (ANY) p.occluded[rayIdx] = 0;
+                            else StoreHit(p.hits, rayIdx, hit);
+                            break;
+                        }
+                        --sp;
+                        if (stackT[sp] < tMax) {
+                            cur = stackRef[sp];
+                            break;
+                        }
+                    }
                 }
-                cur = refNear;
-            } else if (okFar) {
-                cur = refFar;
-            } else {
-                doPop = true;
             }
-        } else {
-            // ---- leaf ----
+        }
+
+        // ---- phase B: leaves (all parked lanes together) ----
+        if (alive && cur < 0) {
             if (LeafTest<ANY, false>(tris, (uint32_t)cur & 0x7fffffffu, rc, tMax, hit, dummy)) {
-                finished = true;  // ANY: first accepted primitive ends the ray (:598-601)
+                alive = false;  // ANY: first accepted primitive ends the ray (:598-601)
                 p.occluded[rayIdx] = 1;
             } else {
-                doPop = true;
-            }
-        }
-        if (doPop) {
-            // pop until an entry whose box still beats the current tMax (:556-558, :570-574)
-            while (true) {
-                if (sp == 0) {
-                    finished = true;
-                    if (ANY) p.occluded[rayIdx] = 0;
-                    else StoreHit(p.hits, rayIdx, hit);
-                    break;
-                }
-                --sp;
-                if (stackT[sp] < tMax) {
-                    cur = stackRef[sp];
-                    break;
+                while (true) {  // :556-558
+                    if (sp == 0) {
+                        alive = false;
+                        if (ANY) p.occluded[rayIdx] = 0;
+                        else StoreHit(p.hits, rayIdx, hit);
+                        break;
+                    }
+                    --sp;
+                    if (stackT[sp] < tMax) {
+                        cur = stackRef[sp];
+                        break;
+                    }
                 }
             }
         }
-        if (finished) alive = false;
     }
 }
 
