@@ -1,0 +1,190 @@
+// include/nnbvh.hpp -- C++ host mirror of the reference's BVHAggregate over the C ABI (nnbvh.h).
+//
+// Header-only; link against libnnbvh.so.  Same surface as `class BVHAggregate`
+// (/root/reference/src/pbrt/cpu/aggregates.h:28-70): a constructor taking the
+// primitives, maxPrimsInNode and SplitMethod; Bounds(); Intersect(ray, tMax);
+// IntersectP(ray, tMax) -- plus the batch forms the reference only has in
+// CPUAggregate::IntersectClosest / IntersectShadow (wavefront/aggregate.cpp:34-68).
+// No intersection arithmetic lives here: every query runs in libnnbvh.so on the GPU,
+// and every failure becomes a nnbvh::Error (the reference LOG_FATALs instead).
+//
+// What pbrt would pass in: `tris` = the 9 floats of each Triangle's vertices in
+// render space (Triangle::GetMesh()->p[v[k]], shapes.cpp:325-327) in the order
+// of the std::vector<Primitive> given to BVHAggregate; `PrimitiveIndex(i)` maps a
+// hit record back to that order, where the caller re-attaches material / area
+// light (SimplePrimitive / GeometricPrimitive, cpu/primitive.cpp:50-109) and
+// rebuilds the SurfaceInteraction with Triangle::InteractionFromIntersection
+// (shapes.h:884) from {t, b0, b1, b2}.
+#ifndef NNBVH_HPP
+#define NNBVH_HPP
+
+#include <cstddef>
+#include <cstdint>
+#include <limits>
+#include <optional>
+#include <stdexcept>
+#include <string>
+#include <utility>
+#include <vector>
+
+#include "nnbvh.h"
+
+namespace nnbvh {
+
+struct Error : std::runtime_error {
+    int code;
+    Error(int c, const std::string &what) : std::runtime_error(what), code(c) {}
+};
+
+inline void Check(int rc) {
+    if (rc != NNBVH_OK) throw Error(rc, std::string("libnnbvh: ") + nnbvh_last_error());
+}
+
+// Ray{o, d, time} (ray.h:35-38).
+struct Ray {
+    float o[3];
+    float d[3];
+    float time = 0.f;
+};
+
+// What survives of ShapeIntersection (shapes.h:93-97) + TriangleIntersection (shapes.h:820-824).
+struct Hit {
+    uint32_t prim;  // ORDERED primitive index; PrimitiveIndex() maps it back
+    float tHit, b0, b1, b2;
+};
+
+struct Bounds3f {
+    float pMin[3], pMax[3];
+};
+
+inline nnbvh_ray MakeRay(const Ray &r, float tMax) {
+    return nnbvh_ray{r.o[0], r.o[1], r.o[2], tMax, r.d[0], r.d[1], r.d[2], r.time};
+}
+
+class GPUBVHAggregate {
+  public:
+    enum class SplitMethod { SAH = NNBVH_SPLIT_SAH, HLBVH = NNBVH_SPLIT_HLBVH,
+                             Middle = NNBVH_SPLIT_MIDDLE, EqualCounts = NNBVH_SPLIT_EQUAL_COUNTS };
+
+    // BVHAggregate(std::vector<Primitive> p, int maxPrimsInNode = 1, SplitMethod = SAH),
+    // cpu/aggregates.cpp:140-190.  tris9: 9 floats per triangle, caller's primitive order.
+    GPUBVHAggregate(const std::vector<float> &tris9, int maxPrimsInNode = 1,
+                    SplitMethod splitMethod = SplitMethod::SAH, int device = -1,
+                    int buildThreads = 0) {
+        const uint32_t nTris = (uint32_t)(tris9.size() / 9);
+        if (nTris) {
+            nodes_.resize(2 * (size_t)nTris - 1);
+            order_.resize(nTris);
+            uint32_t nNodes = 0;
+            Check(nnbvh_build_bvh(tris9.data(), nTris, maxPrimsInNode, (int)splitMethod,
+                                  buildThreads, nodes_.data(), &nNodes, order_.data()));
+            nodes_.resize(nNodes);
+            ordered_.resize(9 * (size_t)nTris);
+            for (uint32_t i = 0; i < nTris; ++i)
+                for (int k = 0; k < 9; ++k)
+                    ordered_[9 * (size_t)i + k] = tris9[9 * (size_t)order_[i] + k];
+        }
+        Open(device);
+    }
+
+    // A ready flattened tree (e.g. an NN-split tree exported in LinearBVHNode layout).
+    GPUBVHAggregate(std::vector<nnbvh_node> nodes, std::vector<float> orderedTris9,
+                    std::vector<uint32_t> order = {}, int device = -1)
+        : nodes_(std::move(nodes)), ordered_(std::move(orderedTris9)), order_(std::move(order)) {
+        Open(device);
+    }
+
+    GPUBVHAggregate(const GPUBVHAggregate &) = delete;
+    GPUBVHAggregate &operator=(const GPUBVHAggregate &) = delete;
+    ~GPUBVHAggregate() { nnbvh_destroy(e_); }
+
+    // Bounds3f BVHAggregate::Bounds() const, cpu/aggregates.cpp:524-527 (CHECK(nodes) there).
+    Bounds3f Bounds() const {
+        if (nodes_.empty()) throw Error(NNBVH_ERR_NOSCENE, "Bounds() of an empty aggregate");
+        const float *b = nodes_[0].bounds;
+        return Bounds3f{{b[0], b[1], b[2]}, {b[3], b[4], b[5]}};
+    }
+
+    // pstd::optional<ShapeIntersection> Intersect(const Ray&, Float tMax) const (:529-579).
+    std::optional<Hit> Intersect(const Ray &ray,
+                                 float tMax = std::numeric_limits<float>::infinity()) const {
+        nnbvh_ray r = MakeRay(ray, tMax);
+        nnbvh_hit h;
+        Check(nnbvh_intersect_closest(e_, &r, 1, &h));
+        if (h.prim == NNBVH_MISS) return std::nullopt;
+        return Hit{h.prim, h.t, h.b0, h.b1, h.b2};
+    }
+
+    // bool IntersectP(const Ray&, Float tMax) const (:581-624).
+    bool IntersectP(const Ray &ray,
+                    float tMax = std::numeric_limits<float>::infinity()) const {
+        nnbvh_ray r = MakeRay(ray, tMax);
+        uint8_t occ = 0;
+        Check(nnbvh_intersect_any(e_, &r, 1, &occ));
+        return occ != 0;
+    }
+
+    // Batch forms: n rays in, n results out; pointers may be host or device memory.
+    void IntersectBatch(const nnbvh_ray *rays, uint64_t n, nnbvh_hit *hits) const {
+        Check(nnbvh_intersect_closest(e_, rays, n, hits));
+    }
+    void IntersectPBatch(const nnbvh_ray *rays, uint64_t n, uint8_t *occluded) const {
+        Check(nnbvh_intersect_any(e_, rays, n, occluded));
+    }
+    // The wavefront queues' SoA layout (SOA<RayWorkItem>, wavefront/workitems.soa); tMax may be null.
+    void IntersectBatchSoA(const float *ox, const float *oy, const float *oz, const float *dx,
+                           const float *dy, const float *dz, const float *tMax, uint64_t n,
+                           nnbvh_hit *hits) const {
+        Check(nnbvh_intersect_closest_soa(e_, ox, oy, oz, dx, dy, dz, tMax, n, hits));
+    }
+    void IntersectPBatchSoA(const float *ox, const float *oy, const float *oz, const float *dx,
+                            const float *dy, const float *dz, const float *tMax, uint64_t n,
+                            uint8_t *occluded) const {
+        Check(nnbvh_intersect_any_soa(e_, ox, oy, oz, dx, dy, dz, tMax, n, occluded));
+    }
+    // With the reference's per-ray statistics (bvhNodesVisited, nTriTests).
+    void IntersectCounters(const nnbvh_ray *rays, uint64_t n, bool anyHit, nnbvh_hit *hits,
+                           uint8_t *occluded, uint32_t *nodesVisited, uint32_t *triTests) const {
+        Check(nnbvh_intersect_counters(e_, rays, n, anyHit, hits, occluded, nodesVisited, triTests));
+    }
+
+    // ordered primitive index -> index in the constructor's primitive list.
+    uint32_t PrimitiveIndex(uint32_t ordered) const {
+        return order_.empty() ? ordered : order_[ordered];
+    }
+    const std::vector<nnbvh_node> &Nodes() const { return nodes_; }
+    const std::vector<float> &OrderedTriangles() const { return ordered_; }
+    void SetStream(void *cudaStream) { Check(nnbvh_set_stream(e_, cudaStream)); }
+    float LastKernelMs() const {
+        float ms = 0;
+        Check(nnbvh_last_kernel_ms(e_, &ms));
+        return ms;
+    }
+    nnbvh_engine *Handle() const { return e_; }
+
+  private:
+    void Open(int device) {
+        nnbvh_options o{};
+        o.device = device;
+        o.kernel = NNBVH_KERNEL_AUTO;
+        o.smem_top_nodes = -1;
+        Check(nnbvh_create(&o, &e_));
+        int rc = nnbvh_upload_scene(e_, nodes_.data(), (uint32_t)nodes_.size(), ordered_.data(),
+                                    (uint32_t)(ordered_.size() / 9));
+        if (rc != NNBVH_OK) {
+            std::string msg = nnbvh_last_error();
+            nnbvh_destroy(e_);
+            e_ = nullptr;
+            throw Error(rc, "libnnbvh: " + msg);
+        }
+    }
+
+    std::vector<nnbvh_node> nodes_;
+    std::vector<float> ordered_;
+    std::vector<uint32_t> order_;
+    nnbvh_engine *e_ = nullptr;
+};
+
+}  // namespace nnbvh
+
+#endif  // NNBVH_HPP

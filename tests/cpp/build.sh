@@ -1,0 +1,10 @@
+#!/bin/sh
+# tests/cpp/build.sh -- compile the C++ host-mirror test against libnnbvh.so and the oracle.
+set -e
+HERE="$(cd "$(dirname "$0")" && pwd)"
+ROOT="$HERE/../.."
+make -s -C "$ROOT/oracle" oracle
+g++ -std=c++17 -O2 -ffp-contract=off -o "$HERE/host_mirror_test" "$HERE/host_mirror_test.cpp" \
+    -L"$ROOT/nn_bvh_b200" -lnnbvh -L"$ROOT/oracle/_build" -lnnbvh_oracle \
+    -Wl,-rpath,'$ORIGIN/../../nn_bvh_b200' -Wl,-rpath,'$ORIGIN/../../oracle/_build' -pthread
+echo "built $HERE/host_mirror_test"

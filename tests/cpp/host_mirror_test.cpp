@@ -1,0 +1,86 @@
+// tests/cpp/host_mirror_test.cpp -- the C++ host mirror (include/nnbvh.hpp) against the oracle.
+//
+// Reads like a reference-side test of BVHAggregate: build over a triangle soup,
+// Bounds(), single-ray Intersect/IntersectP, then a batch, each checked bit for
+// bit against the CPU restatement (oracle/nnbvh_oracle.h -- tests may link it).
+// Usage: host_mirror_test [--compile-only-check]
+//   exit 0 = pass; prints the first mismatch otherwise.  Needs a CUDA device
+//   (the pytest wrapper runs it under -m gpu; the CPU suite only compiles it and
+//   checks that it fails loudly with NNBVH_ERR_CUDA when no device is present).
+#include <cstdio>
+#include <cstring>
+#include <random>
+#include <vector>
+
+#include "../../include/nnbvh.hpp"
+#include "../../oracle/nnbvh_oracle.h"
+
+int main(int argc, char **argv) {
+    const uint32_t T = 20000, N = 100000;
+    std::mt19937 rng(1234);
+    std::uniform_real_distribution<float> U(0.f, 1.f);
+    std::vector<float> tris(9 * (size_t)T);
+    for (uint32_t i = 0; i < T; ++i) {
+        float c[3] = {U(rng), U(rng), U(rng)};
+        for (int v = 0; v < 3; ++v)
+            for (int k = 0; k < 3; ++k) tris[9 * (size_t)i + 3 * v + k] = c[k] + 0.02f * (2 * U(rng) - 1);
+    }
+    try {
+        nnbvh::GPUBVHAggregate agg(tris, 4, nnbvh::GPUBVHAggregate::SplitMethod::SAH);
+
+        // the tree must be the reference's, byte for byte
+        std::vector<nnbvh_oracle_node> onodes(2 * (size_t)T);
+        std::vector<int32_t> oorder(T);
+        int64_t m = nnbvh_oracle_build(tris.data(), (int32_t)T, 4, NNBVH_ORACLE_SAH, onodes.data(), oorder.data());
+        if (m != (int64_t)agg.Nodes().size() ||
+            std::memcmp(onodes.data(), agg.Nodes().data(), sizeof(nnbvh_node) * (size_t)m) != 0) {
+            std::printf("FAIL: tree differs from the oracle's (%lld vs %zu nodes)\n", (long long)m, agg.Nodes().size());
+            return 1;
+        }
+        for (uint32_t i = 0; i < T; ++i)
+            if ((uint32_t)oorder[i] != agg.PrimitiveIndex(i)) { std::printf("FAIL: leaf order differs at %u\n", i); return 1; }
+        nnbvh::Bounds3f b = agg.Bounds();
+        if (std::memcmp(&b, onodes[0].bounds, 24) != 0) { std::printf("FAIL: Bounds()\n"); return 1; }
+
+        std::vector<nnbvh_ray> rays(N);
+        std::normal_distribution<float> G(0.f, 1.f);
+        for (uint32_t i = 0; i < N; ++i) {
+            nnbvh_ray &r = rays[i];
+            r.ox = -0.25f + 1.5f * U(rng); r.oy = -0.25f + 1.5f * U(rng); r.oz = -0.25f + 1.5f * U(rng);
+            r.dx = G(rng); r.dy = G(rng); r.dz = G(rng);
+            r.tMax = (i & 1) ? U(rng) : std::numeric_limits<float>::infinity();
+            r.time = 0.f;
+        }
+        std::vector<nnbvh_hit> hits(N);
+        std::vector<uint8_t> occ(N);
+        agg.IntersectBatch(rays.data(), N, hits.data());
+        agg.IntersectPBatch(rays.data(), N, occ.data());
+        std::vector<uint32_t> want(5 * (size_t)N);
+        std::vector<uint8_t> wocc(N);
+        nnbvh_oracle_intersect(onodes.data(), agg.OrderedTriangles().data(), &rays[0].ox, N, want.data(), nullptr, nullptr, 0);
+        nnbvh_oracle_intersectP(onodes.data(), agg.OrderedTriangles().data(), &rays[0].ox, N, wocc.data(), nullptr, nullptr, 0);
+        static_assert(sizeof(nnbvh_hit) == 20, "hit record is 20 bytes");
+        if (std::memcmp(hits.data(), want.data(), 20 * (size_t)N) != 0) { std::printf("FAIL: closest-hit records differ\n"); return 1; }
+        if (std::memcmp(occ.data(), wocc.data(), N) != 0) { std::printf("FAIL: any-hit results differ\n"); return 1; }
+
+        // single-ray surface
+        uint32_t nHit = 0;
+        for (uint32_t i = 0; i < 64; ++i) {
+            nnbvh::Ray r{{rays[i].ox, rays[i].oy, rays[i].oz}, {rays[i].dx, rays[i].dy, rays[i].dz}, 0.f};
+            auto h = agg.Intersect(r, rays[i].tMax);
+            bool p = agg.IntersectP(r, rays[i].tMax);
+            const uint32_t *w = &want[5 * (size_t)i];
+            if (h.has_value() != (w[0] != NNBVH_MISS) || p != (wocc[i] != 0)) { std::printf("FAIL: single ray %u\n", i); return 1; }
+            if (h) {
+                ++nHit;
+                if (h->prim != w[0] || std::memcmp(&h->tHit, &w[1], 16) != 0) { std::printf("FAIL: single-ray record %u\n", i); return 1; }
+            }
+        }
+        std::printf("PASS: %u triangles, %zu nodes, %u rays bit-exact vs oracle (%u/64 single rays hit), kernel %.3f ms\n",
+                    T, agg.Nodes().size(), N, nHit, agg.LastKernelMs());
+        return 0;
+    } catch (const nnbvh::Error &e) {
+        std::printf("nnbvh::Error %d: %s\n", e.code, e.what());
+        return e.code == NNBVH_ERR_CUDA ? 3 : 2;
+    }
+}

@@ -96,3 +96,29 @@ def test_product_never_imports_oracle():
             if f.endswith((".py", ".cu", ".cuh", ".cpp", ".h", ".sh")):
                 txt = open(os.path.join(dp, f), errors="replace").read()
                 assert "pyoracle" not in txt and "nnbvh_oracle" not in txt and "_ref/" not in txt, f
+
+
+def _build_cpp_test():
+    import subprocess
+    subprocess.check_call(["sh", os.path.join(ROOT, "tests", "cpp", "build.sh")],
+                          stdout=subprocess.DEVNULL)
+    return os.path.join(ROOT, "tests", "cpp", "host_mirror_test")
+
+
+def test_cpp_host_mirror_compiles_and_fails_loudly_without_gpu():
+    """include/nnbvh.hpp (the C++ mirror of BVHAggregate) compiles against the C ABI;
+    without a device the program reports NNBVH_ERR_CUDA (exit 3), never a CPU answer."""
+    import subprocess
+    import torch
+    exe = _build_cpp_test()
+    if torch.cuda.is_available():
+        pytest.skip("GPU present: covered by test_cpp_host_mirror_gpu")
+    r = subprocess.run([exe], capture_output=True, text=True)
+    assert r.returncode == 3 and "no CPU fallback" in r.stdout, r.stdout + r.stderr
+
+
+@pytest.mark.gpu
+def test_cpp_host_mirror_gpu():
+    import subprocess
+    r = subprocess.run([_build_cpp_test()], capture_output=True, text=True)
+    assert r.returncode == 0 and r.stdout.startswith("PASS"), r.stdout + r.stderr
