@@ -67,7 +67,9 @@ typedef enum nnbvh_kernel {
     NNBVH_KERNEL_AUTO = 0,   /* engine default (the fast path) */
     NNBVH_KERNEL_BASIC = 1,  /* one thread per ray over the 32-byte nodes, statement
                                 order of cpu/aggregates.cpp:529-624 */
-    NNBVH_KERNEL_WIDE = 2    /* persistent warps over 64-byte two-child nodes */
+    NNBVH_KERNEL_WIDE = 2,   /* persistent warps over 64-byte two-child nodes (first version) */
+    NNBVH_KERNEL_STEP = 3    /* persistent warps, one straight-line step per lane per
+                                iteration, 256-bit node loads (the default) */
 } nnbvh_kernel;
 
 typedef struct nnbvh_options {

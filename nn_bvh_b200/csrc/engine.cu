@@ -6,6 +6,7 @@
 #include <cuda_runtime.h>
 
 #include <algorithm>
+#include <cmath>
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
@@ -15,6 +16,8 @@
 #include "../../include/nnbvh.h"
 #include "internal.h"
 #include "kernels.cuh"
+#include "binning.cuh"
+#include "traverse.cuh"
 
 namespace nnbvh {
 
@@ -56,6 +59,19 @@ struct DevBuf {
     }
 };
 
+// Per-launch device scratch: the persistent kernel's ray cursor and the binning buffers.
+struct Scratch {
+    // cursor[0], cursor[1]: ray cursors of the fast and the exact launch; cursor[2] (low
+    // 32 bits): number of deferred rays.  Zeroed together before each batch.
+    unsigned long long *cursor = nullptr;
+    DevBuf<uint32_t> keys, perm, hist, tileSums, deferred;
+    void Free() {
+        if (cursor) cudaFree(cursor);
+        cursor = nullptr;
+        keys.Free(); perm.Free(); hist.Free(); tileSums.Free(); deferred.Free();
+    }
+};
+
 // One in-flight chunk of the host-pointer pipeline: H2D rays -> kernel -> D2H results.
 struct Slot {
     cudaStream_t stream = nullptr;
@@ -65,7 +81,7 @@ struct Slot {
     DevBuf<nnbvh_hit> hits;
     DevBuf<uint8_t> occ;
     DevBuf<uint32_t> cnt;    // 2 planes (nodesVisited, triTests)
-    unsigned long long *cursor = nullptr;
+    Scratch scratch;
 };
 
 }  // namespace nnbvh
@@ -84,12 +100,13 @@ struct nnbvh_engine {
     uint64_t launches = 0;
     // scene
     bool haveScene = false;
+    bool boxesRegular = true;  // every node box finite with lo <= hi: the fast slab test is exact
     SceneDev sc{};
     DevBuf<nnbvh_node> dNodes;
     DevBuf<WideNode> dWide;
     DevBuf<float4> dTris;
     // device-pointer path scratch
-    unsigned long long *cursor = nullptr;
+    Scratch scratch;
     // host-pointer pipeline
     static constexpr int kSlots = 3;
     Slot slots[kSlots];
@@ -98,6 +115,12 @@ struct nnbvh_engine {
     int refillBelow = 24;
     int leafQuorum = 16;
     uint64_t chunkRays = 1u << 20;
+    // ray binning pre-pass (binning.cuh)
+    int exactOnly = 0;       // StepKernel: skip the fast-slab launch (debug / A-B knob)
+    int binMode = 0;         // 0 = off, 1 = on for batches >= binMinRays
+    int binCellBits = 5;     // origin grid (1<<bits)^3
+    int binDirBits = 2;      // octahedral direction grid (1<<bits)^2
+    uint64_t binMinRays = 1u << 16;
 };
 
 extern "C" const char *nnbvh_last_error(void) { return g_err; }
@@ -143,15 +166,20 @@ extern "C" int nnbvh_create(const nnbvh_options *opts, nnbvh_engine **out) {
     e->refillBelow = EnvInt("NNBVH_REFILL_BELOW", e->refillBelow);
     e->leafQuorum = EnvInt("NNBVH_LEAF_QUORUM", e->leafQuorum);
     e->chunkRays = (uint64_t)EnvInt("NNBVH_CHUNK_RAYS", (int)e->chunkRays);
+    e->binMode = EnvInt("NNBVH_BIN", e->binMode);
+    e->exactOnly = EnvInt("NNBVH_EXACT_ONLY", e->exactOnly);
+    e->binCellBits = std::min(8, std::max(0, EnvInt("NNBVH_BIN_CELL_BITS", e->binCellBits)));
+    e->binDirBits = std::min(4, std::max(0, EnvInt("NNBVH_BIN_DIR_BITS", e->binDirBits)));
+    e->binMinRays = (uint64_t)EnvInt("NNBVH_BIN_MIN_RAYS", (int)e->binMinRays);
     CU(cudaStreamCreateWithFlags(&e->ownStream, cudaStreamNonBlocking));
     e->stream = e->ownStream;
     CU(cudaEventCreate(&e->evA));
     CU(cudaEventCreate(&e->evB));
-    CU(cudaMalloc(&e->cursor, sizeof(unsigned long long)));
+    CU(cudaMalloc(&e->scratch.cursor, 4 * sizeof(unsigned long long)));
     for (Slot &s : e->slots) {
         CU(cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking));
         CU(cudaEventCreateWithFlags(&s.done, cudaEventDisableTiming));
-        CU(cudaMalloc(&s.cursor, sizeof(unsigned long long)));
+        CU(cudaMalloc(&s.scratch.cursor, 4 * sizeof(unsigned long long)));
     }
     *out = e;
     return NNBVH_OK;
@@ -164,10 +192,10 @@ extern "C" void nnbvh_destroy(nnbvh_engine *e) {
     e->dNodes.Free();
     e->dWide.Free();
     e->dTris.Free();
-    if (e->cursor) cudaFree(e->cursor);
+    e->scratch.Free();
     for (Slot &s : e->slots) {
         s.rays.Free(); s.soa.Free(); s.hits.Free(); s.occ.Free(); s.cnt.Free();
-        if (s.cursor) cudaFree(s.cursor);
+        s.scratch.Free();
         if (s.done) cudaEventDestroy(s.done);
         if (s.stream) cudaStreamDestroy(s.stream);
     }
@@ -327,6 +355,12 @@ extern "C" int nnbvh_upload_scene(nnbvh_engine *e, const nnbvh_node *nodes, uint
     std::vector<nnbvh_node> h(nNodes);
     CU(cudaMemcpyAsync(h.data(), nodes, sizeof(nnbvh_node) * (size_t)nNodes, cudaMemcpyDefault, st));
     CU(cudaStreamSynchronize(st));
+    e->boxesRegular = true;
+    for (const nnbvh_node &nd : h)
+        for (int k = 0; k < 3; ++k) {
+            float lo = nd.bounds[k], hi = nd.bounds[3 + k];
+            if (!(std::isfinite(lo) && std::isfinite(hi) && lo <= hi)) e->boxesRegular = false;
+        }
     std::vector<WideNode> wide;
     std::vector<uint8_t> last;
     int32_t rootRef = 0;
@@ -412,10 +446,20 @@ static int LaunchWide(nnbvh_engine *e, cudaStream_t st, const WideParams &p, uin
     }
 }
 
+template <bool ANY, bool EXACT>
+static void LaunchStep(nnbvh_engine *e, cudaStream_t st, const StepParams &p) {
+    switch (e->wideMinB) {
+    case 1: StepKernel<ANY, EXACT, 1><<<e->numSMs * 1, 256, 0, st>>>(p); break;
+    case 2: StepKernel<ANY, EXACT, 2><<<e->numSMs * 2, 256, 0, st>>>(p); break;
+    case 3: StepKernel<ANY, EXACT, 3><<<e->numSMs * 3, 256, 0, st>>>(p); break;
+    default: StepKernel<ANY, EXACT, 4><<<e->numSMs * 4, 256, 0, st>>>(p); break;
+    }
+}
+
 // All pointers are device pointers here.
 static int LaunchTraversal(nnbvh_engine *e, cudaStream_t st, bool any, bool counters,
                            const RayInput &in, uint64_t n, const Outputs &o,
-                           unsigned long long *cursor) {
+                           Scratch &scr) {
     if (n == 0) return NNBVH_OK;
     const bool basic = counters || e->kernel == NNBVH_KERNEL_BASIC;
     if (basic) {
@@ -434,7 +478,73 @@ static int LaunchTraversal(nnbvh_engine *e, cudaStream_t st, bool any, bool coun
         uint32_t budgetNodes = (uint32_t)((e->maxSmemOptin - 2048) / minB / sizeof(WideNode));
         uint32_t want = e->smemTopNodes >= 0 ? (uint32_t)e->smemTopNodes : 0u;  // measured: L1 beats explicit staging
         uint32_t smemNodes = std::min(std::min(want, budgetNodes), e->sc.topNodes);
+        // ---- optional binning pre-pass: a ray order that keeps warps coherent ----
+        const uint32_t *perm = nullptr;
+        if (e->binMode && n >= e->binMinRays && n < 0xffffffffull && e->sc.nNodes) {
+            BinParams bp;
+            bp.cellBits = (uint32_t)e->binCellBits;
+            bp.dirBits = (uint32_t)e->binDirBits;
+            for (int k = 0; k < 3; ++k) {
+                float ext = e->sc.rootBox[3 + k] - e->sc.rootBox[k];
+                bp.lo[k] = e->sc.rootBox[k];
+                bp.scale[k] = ext > 0.f ? (float)(1u << bp.cellBits) / ext : 0.f;
+            }
+            const uint32_t nBins = 1u << (3 * bp.cellBits + 2 * bp.dirBits);
+            const uint32_t nTiles = (nBins + kScanTile - 1) / kScanTile;
+            int rc = scr.keys.Reserve(n);
+            if (!rc) rc = scr.perm.Reserve(n);
+            if (!rc) rc = scr.hist.Reserve(nBins);
+            if (!rc) rc = scr.tileSums.Reserve(nTiles);
+            if (rc) return rc;
+            CU(cudaMemsetAsync(scr.hist.p, 0, sizeof(uint32_t) * (size_t)nBins, st));
+            const unsigned g = (unsigned)((n + 255) / 256);
+            BinCountKernel<<<g, 256, 0, st>>>(bp, in, n, scr.keys.p, scr.hist.p);
+            BinTileSumKernel<<<nTiles, 1024, 0, st>>>(scr.hist.p, nBins, scr.tileSums.p);
+            BinTileScanKernel<<<nTiles, 1024, 0, st>>>(scr.hist.p, nBins, scr.tileSums.p);
+            BinScatterKernel<<<g, 256, 0, st>>>(scr.keys.p, n, scr.hist.p, scr.perm.p);
+            e->launches += 4;
+            CU(cudaGetLastError());
+            perm = scr.perm.p;
+        }
+        unsigned long long *cursor = scr.cursor;
+        CU(cudaMemsetAsync(cursor, 0, 4 * sizeof(unsigned long long), st));
+        if (e->kernel != NNBVH_KERNEL_WIDE) {
+            // ---- StepKernel: fast-slab launch, then the exact launch over the deferred rays ----
+            if (n > 0xffffffffull)
+                return SetError(NNBVH_ERR_INVALID, "batch too large for one launch");
+            StepParams sp{};
+            sp.sc = e->sc;
+            sp.in = in;
+            sp.n = n;
+            sp.hits = o.hits;
+            sp.occluded = o.occ;
+            sp.perm = perm;
+            sp.refillBelow = (uint32_t)std::min(32, std::max(1, e->refillBelow));
+            sp.leafQuorum = (uint32_t)std::min(32, std::max(1, e->leafQuorum));
+            uint32_t *nDef = reinterpret_cast<uint32_t *>(cursor + 2);
+            if (e->boxesRegular && !e->exactOnly) {
+                int rc = scr.deferred.Reserve(n);
+                if (rc) return rc;
+                sp.cursor = cursor;
+                sp.deferred = scr.deferred.p;
+                sp.nDeferred = nDef;
+                if (any) LaunchStep<true, false>(e, st, sp);
+                else LaunchStep<false, false>(e, st, sp);
+                ++e->launches;
+                sp.perm = scr.deferred.p;
+                sp.nPtr = nDef;
+                sp.deferred = nullptr;
+                sp.nDeferred = nullptr;
+            }
+            sp.cursor = cursor + 1;
+            if (any) LaunchStep<true, true>(e, st, sp);
+            else LaunchStep<false, true>(e, st, sp);
+            ++e->launches;
+            CU(cudaGetLastError());
+            return NNBVH_OK;
+        }
         WideParams p;
+        p.perm = perm;
         p.sc = e->sc;
         p.in = in;
         p.n = n;
@@ -444,7 +554,6 @@ static int LaunchTraversal(nnbvh_engine *e, cudaStream_t st, bool any, bool coun
         p.smemNodes = smemNodes;
         p.refillBelow = (uint32_t)std::min(32, std::max(1, e->refillBelow));
         p.leafQuorum = (uint32_t)std::min(32, std::max(1, e->leafQuorum));
-        CU(cudaMemsetAsync(cursor, 0, sizeof(unsigned long long), st));
         int rc = any ? LaunchWide<true>(e, st, p, smemNodes * (uint32_t)sizeof(WideNode))
                      : LaunchWide<false>(e, st, p, smemNodes * (uint32_t)sizeof(WideNode));
         if (rc) return rc;
@@ -489,7 +598,7 @@ static int RunBatch(nnbvh_engine *e, const Batch &b) {
             in.tMax = b.planes[6];
         } else in.aos = reinterpret_cast<const float4 *>(b.rays);
         CU(cudaEventRecord(e->evA, e->stream));
-        int rc = LaunchTraversal(e, e->stream, b.any, b.counters, in, b.n, b.out, e->cursor);
+        int rc = LaunchTraversal(e, e->stream, b.any, b.counters, in, b.n, b.out, e->scratch);
         if (rc) return rc;
         CU(cudaEventRecord(e->evB, e->stream));
         e->lastMs = -1.f;  // resolved lazily by nnbvh_last_kernel_ms
@@ -555,7 +664,7 @@ static int RunBatch(nnbvh_engine *e, const Batch &b) {
         k0.push_back(a);
         k1.push_back(z);
         CU(cudaEventRecord(a, s.stream));
-        rcOut = LaunchTraversal(e, s.stream, b.any, b.counters, in, m, o, s.cursor);
+        rcOut = LaunchTraversal(e, s.stream, b.any, b.counters, in, m, o, s.scratch);
         if (rcOut) break;
         CU(cudaEventRecord(z, s.stream));
         if (!outDev) {

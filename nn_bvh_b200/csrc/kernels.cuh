@@ -210,6 +210,7 @@ struct WideParams {
     nnbvh_hit *hits;
     uint8_t *occluded;
     unsigned long long *cursor;  // global ray cursor (zeroed before launch)
+    const uint32_t *perm;        // optional ray order (binning.cuh); results go to slot perm[j]
     uint32_t smemNodes;          // WideNodes staged in shared memory (<= sc.topNodes)
     uint32_t refillBelow;        // refill finished lanes when fewer than this many are live
     uint32_t leafQuorum;         // run the leaf phase once this many lanes wait at a leaf
@@ -297,6 +298,7 @@ __global__ void __launch_bounds__(256, MINB) WideKernel(WideParams p) {
             if (!alive) {
                 uint64_t idx = base + __popc(want & ((1u << lane) - 1));
                 if (idx < p.n) {
+                    if (p.perm) idx = __ldg(p.perm + idx);
                     rayIdx = idx;
                     RayRegs rr = LoadRay(p.in, idx);
                     rc = MakeRayConst(rr.ox, rr.oy, rr.oz, rr.dx, rr.dy, rr.dz);

@@ -1,0 +1,303 @@
+// nn_bvh_b200/csrc/traverse.cuh -- StepKernel: the product traversal kernel (sm_100a).
+//
+// Same results, bit for bit, as BasicKernel / the reference (cpu/aggregates.cpp:529-624),
+// organised for the resource that actually binds on B200 once the scene sits in L1/L2:
+// warp issue slots and L1 wavefronts (profiles/r01a_*: 70 % issue utilisation at 13 of 32
+// lanes active, L1 at 75 %).
+//
+//  * Persistent warps pull rays from a global cursor; finished lanes are refilled.
+//  * Every lane carries (cur, curT): the node or leaf it is AT and the box-entry distance
+//    that was computed when its parent was fetched.  `curT < tMax` -- the only part of
+//    Bounds3f::IntersectP that depends on the shrinking tMax (util/vecmath.h:1607) -- is
+//    evaluated when the lane steps onto `cur`, which is the moment the reference tests it.
+//  * One step per lane per iteration, straight-line: a lane whose entry fails the test, or
+//    whose node has no passing child, pops ONE entry and re-validates next iteration, so no
+//    lane ever loops while its 31 neighbours wait.
+//  * A 64-byte node is fetched with two 256-bit loads (LDG.E.ENL2.256): half the L1
+//    wavefronts of four LDG.128.
+//  * Fast slab (EXACT=false): for rays whose invDir is finite and non-zero and whose origin
+//    is finite -- no 0*inf NaN can arise -- the compare/select cascade of vecmath.h:1587-1605
+//    equals  max3(tx0,ty0,tz0) <= min3(tx1',ty1',tz1')  &&  min3 > 0  with the entry distance
+//    max3 (proof in DESIGN.md section 5.1; needs lo <= hi and finite boxes, validated at
+//    upload).  Rays that do not qualify are appended to a deferred list and traced by the
+//    EXACT=true instantiation, which runs the reference's cascade verbatim (SlabStatic).
+//  * Leaves: lanes park at a leaf until `leafQuorum` lanes wait (or nobody is at an interior
+//    node); then every parked lane tests ONE triangle.  A lane stays parked for the next
+//    triangle of its leaf, so the triangle body always starts with many lanes.
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "exact_math.cuh"
+#include "internal.h"
+#include "kernels.cuh"
+
+namespace nnbvh {
+
+struct StepParams {
+    SceneDev sc;
+    RayInput in;
+    uint64_t n;                   // rays (or capacity of `perm` when nPtr is used)
+    const uint32_t *nPtr;         // if set: number of entries of `perm` to process, on the device
+    nnbvh_hit *hits;
+    uint8_t *occluded;
+    unsigned long long *cursor;   // zeroed before launch
+    const uint32_t *perm;         // optional ray order; results go to slot perm[j]
+    uint32_t *deferred;           // EXACT=false: indices of rays needing the exact slab test
+    uint32_t *nDeferred;
+    uint32_t refillBelow, leafQuorum;
+};
+
+struct F8 {
+    float v[8];
+};
+
+// 256-bit read-only global load (PTX ISA 8.8, sm_100+): SASS LDG.E.ENL2.256.CONSTANT.
+__device__ __forceinline__ F8 Ldg256(const void *p) {
+    F8 r;
+    asm volatile("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=f"(r.v[0]), "=f"(r.v[1]), "=f"(r.v[2]), "=f"(r.v[3]), "=f"(r.v[4]),
+                   "=f"(r.v[5]), "=f"(r.v[6]), "=f"(r.v[7])
+                 : "l"(p));
+    return r;
+}
+
+// The per-ray constants the step loop keeps in registers (no d: it is folded into inv / S).
+struct StepRay {
+    float ox, oy, oz;
+    float ix, iy, iz;
+    float Sx, Sy, Sz;
+    int kz;         // MaxComponentIndex(Abs(d)), shapes.cpp:186
+    unsigned neg;   // bit k = dirIsNeg[k], cpu/aggregates.cpp:535
+};
+
+__device__ __forceinline__ RayConst ToRayConst(const StepRay &s) {
+    RayConst r;
+    r.ox = s.ox; r.oy = s.oy; r.oz = s.oz;
+    r.dx = r.dy = r.dz = 0.f;  // unused by SlabStatic / TriangleTest
+    r.ix = s.ix; r.iy = s.iy; r.iz = s.iz;
+    r.negx = s.neg & 1; r.negy = (s.neg >> 1) & 1; r.negz = (s.neg >> 2) & 1;
+    r.kz = s.kz;
+    r.kx = s.kz == 2 ? 0 : s.kz + 1;
+    r.ky = r.kx == 2 ? 0 : r.kx + 1;
+    r.Sx = s.Sx; r.Sy = s.Sy; r.Sz = s.Sz;
+    return r;
+}
+
+constexpr float kNegInf = -__builtin_huge_valf();
+
+template <bool ANY, bool EXACT, int MINB>
+__global__ void __launch_bounds__(256, MINB) StepKernel(StepParams p) {
+    const SceneDev &sc = p.sc;
+    const unsigned lane = threadIdx.x & 31;
+    const float4 *__restrict__ tris = sc.tris;
+    const unsigned char *__restrict__ wideBase = reinterpret_cast<const unsigned char *>(sc.wide);
+    const uint64_t nRays = p.nPtr ? (uint64_t)__ldg(p.nPtr) : p.n;
+
+    uint32_t rayIdx = 0;
+    bool alive = false;
+    StepRay ry{};
+    float tMax = 0.f;
+    HitRegs hit{NNBVH_MISS, 0.f, 0.f, 0.f, 0.f};
+    int cur = 0, sp = 0;
+    float curT = 0.f;
+    // stack entry = {ref, tEntry} packed into 64 bits (one STL.64 / LDL.64 per push / pop)
+    unsigned long long stack[kMaxStack];
+    bool exhausted = false;
+
+    const unsigned leafQuorum = p.leafQuorum;
+
+    while (true) {
+        // ---- refill: finished lanes take the next rays from the global cursor ----
+        unsigned liveMask = __ballot_sync(0xffffffffu, alive);
+        if (!exhausted && (unsigned)__popc(liveMask) < p.refillBelow) {
+            unsigned want = ~liveMask;
+            unsigned nWant = __popc(want);
+            unsigned long long base = 0;
+            if (lane == 0) base = atomicAdd(p.cursor, (unsigned long long)nWant);
+            base = __shfl_sync(0xffffffffu, base, 0);
+            if (base + nWant >= nRays) exhausted = true;
+            if (!alive) {
+                uint64_t j = base + __popc(want & ((1u << lane) - 1));
+                if (j < nRays) {
+                    uint32_t idx = p.perm ? __ldg(p.perm + j) : (uint32_t)j;
+                    RayRegs rr = LoadRay(p.in, idx);
+                    RayConst rc = MakeRayConst(rr.ox, rr.oy, rr.oz, rr.dx, rr.dy, rr.dz);
+                    bool defer = false;
+                    if (!EXACT) {
+                        // finite, non-zero invDir and finite origin <=> the fast slab is exact
+                        const float big = __int_as_float(0x7f800000);
+                        bool okInv = fabsf(rc.ix) < big && fabsf(rc.iy) < big && fabsf(rc.iz) < big &&
+                                     rc.ix != 0.f && rc.iy != 0.f && rc.iz != 0.f;
+                        bool okOrg = fabsf(rc.ox) < big && fabsf(rc.oy) < big && fabsf(rc.oz) < big;
+                        defer = !(okInv && okOrg);
+                    }
+                    if (defer) {
+                        uint32_t pos = atomicAdd(p.nDeferred, 1u);
+                        p.deferred[pos] = idx;
+                    } else {
+                        rayIdx = idx;
+                        ry.ox = rc.ox; ry.oy = rc.oy; ry.oz = rc.oz;
+                        ry.ix = rc.ix; ry.iy = rc.iy; ry.iz = rc.iz;
+                        ry.Sx = rc.Sx; ry.Sy = rc.Sy; ry.Sz = rc.Sz;
+                        ry.kz = rc.kz;
+                        ry.neg = (unsigned)rc.negx | ((unsigned)rc.negy << 1) | ((unsigned)rc.negz << 2);
+                        tMax = rr.tMax;
+                        hit.prim = NNBVH_MISS;
+                        hit.t = hit.b0 = hit.b1 = hit.b2 = 0.f;
+                        sp = 0;
+                        // Root: the reference tests the root's own box first (aggregates.cpp:543);
+                        // nodes == nullptr -> miss (:531).  Exact cascade, once per ray.
+                        float tRoot = 0.f;
+                        bool rootOk = false;
+                        if (sc.nNodes) {
+                            const float *b = sc.rootBox;
+                            rootOk = SlabStatic(rc, rc.negx ? b[3] : b[0], rc.negx ? b[0] : b[3],
+                                                rc.negy ? b[4] : b[1], rc.negy ? b[1] : b[4],
+                                                rc.negz ? b[5] : b[2], rc.negz ? b[2] : b[5], &tRoot);
+                        }
+                        if (rootOk && tRoot < tMax) {
+                            cur = sc.rootRef;
+                            curT = tRoot;
+                            alive = true;
+                        } else if (ANY) p.occluded[idx] = 0;
+                        else StoreHit(p.hits, idx, hit);
+                    }
+                }
+            }
+            liveMask = __ballot_sync(0xffffffffu, alive);
+        }
+        if (liveMask == 0) {
+            if (exhausted) break;
+            continue;
+        }
+
+        // ---- phase A: interior nodes, one step per lane per iteration ----
+        while (true) {
+            const bool atNode = alive && cur >= 0;
+            const unsigned nodeMask = __ballot_sync(0xffffffffu, atNode);
+            const unsigned leafMask = __ballot_sync(0xffffffffu, alive && cur < 0);
+            if (nodeMask == 0 || (unsigned)__popc(leafMask) >= leafQuorum) break;
+            if (atNode) {
+                bool needPop = true;
+                if (curT < tMax) {  // the reference's `tMin < raytMax` for this node, made now
+                    const unsigned char *np = wideBase + (size_t)(unsigned)cur * sizeof(WideNode);
+                    const F8 a = Ldg256(np), b = Ldg256(np + 32);
+                    // WideNode: lo0 xyz, hi0 xyz, lo1 xy | lo1 z, hi1 xyz, ref0, ref1, axis, pad
+                    const bool nx = ry.neg & 1, ny = ry.neg & 2, nz = ry.neg & 4;
+                    const float n0x = nx ? a.v[3] : a.v[0], f0x = nx ? a.v[0] : a.v[3];
+                    const float n0y = ny ? a.v[4] : a.v[1], f0y = ny ? a.v[1] : a.v[4];
+                    const float n0z = nz ? a.v[5] : a.v[2], f0z = nz ? a.v[2] : a.v[5];
+                    const float n1x = nx ? b.v[1] : a.v[6], f1x = nx ? a.v[6] : b.v[1];
+                    const float n1y = ny ? b.v[2] : a.v[7], f1y = ny ? a.v[7] : b.v[2];
+                    const float n1z = nz ? b.v[3] : b.v[0], f1z = nz ? b.v[0] : b.v[3];
+                    float t0, t1;
+                    bool ok0, ok1;
+                    if (EXACT) {
+                        RayConst rc = ToRayConst(ry);
+                        ok0 = SlabStatic(rc, n0x, f0x, n0y, f0y, n0z, f0z, &t0);
+                        ok1 = SlabStatic(rc, n1x, f1x, n1y, f1y, n1z, f1z, &t1);
+                    } else {
+                        const float pad = SlabPad();
+                        const float ax0 = Mul(Sub(n0x, ry.ox), ry.ix), bx0 = Mul(Mul(Sub(f0x, ry.ox), ry.ix), pad);
+                        const float ay0 = Mul(Sub(n0y, ry.oy), ry.iy), by0 = Mul(Mul(Sub(f0y, ry.oy), ry.iy), pad);
+                        const float az0 = Mul(Sub(n0z, ry.oz), ry.iz), bz0 = Mul(Mul(Sub(f0z, ry.oz), ry.iz), pad);
+                        const float ax1 = Mul(Sub(n1x, ry.ox), ry.ix), bx1 = Mul(Mul(Sub(f1x, ry.ox), ry.ix), pad);
+                        const float ay1 = Mul(Sub(n1y, ry.oy), ry.iy), by1 = Mul(Mul(Sub(f1y, ry.oy), ry.iy), pad);
+                        const float az1 = Mul(Sub(n1z, ry.oz), ry.iz), bz1 = Mul(Mul(Sub(f1z, ry.oz), ry.iz), pad);
+                        t0 = fmaxf(fmaxf(ax0, ay0), az0);
+                        t1 = fmaxf(fmaxf(ax1, ay1), az1);
+                        const float x0 = fminf(fminf(bx0, by0), bz0);
+                        const float x1 = fminf(fminf(bx1, by1), bz1);
+                        ok0 = (t0 <= x0) && (x0 > 0.f);
+                        ok1 = (t1 <= x1) && (x1 > 0.f);
+                    }
+                    const int ref0 = __float_as_int(b.v[4]), ref1 = __float_as_int(b.v[5]);
+                    const unsigned axis = __float_as_uint(b.v[6]);
+                    const bool secondFirst = (ry.neg >> axis) & 1u;  // aggregates.cpp:561
+                    const bool stNear = secondFirst ? ok1 : ok0, stFar = secondFirst ? ok0 : ok1;
+                    const int refNear = secondFirst ? ref1 : ref0, refFar = secondFirst ? ref0 : ref1;
+                    const float tNear = secondFirst ? t1 : t0, tFar = secondFirst ? t0 : t1;
+                    const bool goNear = stNear && (tNear < tMax);
+                    if (goNear) {
+                        // The far child is stacked whenever its tMax-independent test passes: tMax
+                        // can GROW by an ulp before the pop (shapes.cpp:239-247), see DESIGN.md.
+                        if (stFar) {
+                            stack[sp] = ((unsigned long long)__float_as_uint(tFar) << 32) | (unsigned)refFar;
+                            ++sp;
+                        }
+                        cur = refNear;
+                        curT = tNear;  // tNear < tMax already established: next step passes
+                        needPop = false;
+                    } else if (stFar && (tFar < tMax)) {
+                        cur = refFar;
+                        curT = tFar;
+                        needPop = false;
+                    }
+                }
+                if (needPop) {  // aggregates.cpp:570-574, one entry per step
+                    if (sp == 0) {
+                        alive = false;
+                        if (ANY) p.occluded[rayIdx] = 0;
+                        else StoreHit(p.hits, rayIdx, hit);
+                    } else {
+                        --sp;
+                        unsigned long long e = stack[sp];
+                        cur = (int)(unsigned)e;
+                        curT = __uint_as_float((unsigned)(e >> 32));
+                    }
+                }
+            }
+        }
+
+        // ---- phase B: every parked lane tests ONE triangle of its leaf ----
+        if (alive && cur < 0) {
+            bool needPop = true;
+            if (curT < tMax) {  // box test of the leaf node, made when the lane steps onto it
+                curT = kNegInf;  // ... and only then: later triangles of this leaf skip it (:547-555)
+                const uint32_t prim = (uint32_t)cur & 0x7fffffffu;
+                const float4 *tp = tris + 3 * (size_t)prim;
+                const float4 v0 = __ldg(tp), v1 = __ldg(tp + 1), v2 = __ldg(tp + 2);
+                const uint32_t flags = __float_as_uint(v0.w);
+                bool found = false;
+                if (!(flags & kTriDegenerate)) {
+                    RayConst rc = ToRayConst(ry);
+                    float t, b0, b1, b2;
+                    if (TriangleTest(rc, tMax, v0.x, v0.y, v0.z, v1.x, v1.y, v1.z, v2.x, v2.y, v2.z,
+                                     &t, &b0, &b1, &b2)) {
+                        found = true;
+                        hit.prim = prim;
+                        hit.t = t;
+                        hit.b0 = b0;
+                        hit.b1 = b1;
+                        hit.b2 = b2;
+                        tMax = t;
+                    }
+                }
+                if (ANY && found) {  // first accepted primitive ends the ray (:598-601)
+                    alive = false;
+                    needPop = false;
+                    p.occluded[rayIdx] = 1;
+                } else if (!(flags & kTriLast)) {
+                    cur = cur + 1;  // next primitive of the same leaf (bit 31 stays set)
+                    needPop = false;
+                }
+            }
+            if (needPop) {  // :556-558
+                if (sp == 0) {
+                    alive = false;
+                    if (ANY) p.occluded[rayIdx] = 0;
+                    else StoreHit(p.hits, rayIdx, hit);
+                } else {
+                    --sp;
+                    unsigned long long e = stack[sp];
+                    cur = (int)(unsigned)e;
+                    curT = __uint_as_float((unsigned)(e >> 32));
+                }
+            }
+        }
+    }
+}
+
+}  // namespace nnbvh

@@ -8,7 +8,7 @@ from conftest import rand_rays, soup
 
 pytestmark = pytest.mark.gpu
 
-KERNELS = {"basic": 1, "wide": 2}
+KERNELS = {"basic": 1, "wide": 2, "step": 3}
 
 
 def _agg(tris=None, kernel="wide", **kw):
@@ -35,7 +35,7 @@ def test_device_box_golden(golden):
     assert np.array_equal(agg.test_boxes(g["rays"], g["boxes"]), g["hit"])
 
 
-@pytest.mark.parametrize("kernel", ["basic", "wide"])
+@pytest.mark.parametrize("kernel", ["basic", "wide", "step"])
 @pytest.mark.parametrize("split", ["sah", "middle", "equal"])
 def test_scene_golden(golden, kernel, split):
     g = golden["scene_small"]
@@ -53,7 +53,7 @@ def test_scene_golden(golden, kernel, split):
     assert (int(nv.sum()), int(tt.sum())) == (st[2], st[3])
 
 
-@pytest.mark.parametrize("kernel", ["basic", "wide"])
+@pytest.mark.parametrize("kernel", ["basic", "wide", "step"])
 @pytest.mark.parametrize("T,s,mp", [(1, 0.3, 4), (2, 0.3, 4), (37, 0.2, 4), (20000, 0.02, 4),
                                      (20000, 0.05, 1), (60000, 0.01, 255)])
 def test_random_soups_vs_oracle(oracle, kernel, T, s, mp):
@@ -70,7 +70,7 @@ def test_random_soups_vs_oracle(oracle, kernel, T, s, mp):
     assert np.array_equal(nv, wnv) and np.array_equal(tt, wtt)
 
 
-@pytest.mark.parametrize("kernel", ["basic", "wide"])
+@pytest.mark.parametrize("kernel", ["basic", "wide", "step"])
 def test_edge_inputs(oracle, kernel):
     rng = np.random.default_rng(3)
     tris = soup(rng, 5000, 0.05)
@@ -96,7 +96,7 @@ def test_edge_inputs(oracle, kernel):
     assert np.array_equal(agg.IntersectPBatch(rays), oracle.intersect_p(nodes, agg.ordered_tris9, rays))
 
 
-@pytest.mark.parametrize("kernel", ["basic", "wide"])
+@pytest.mark.parametrize("kernel", ["basic", "wide", "step"])
 def test_empty_scene_misses(kernel):
     import nn_bvh_b200 as nb
     agg = _agg(None, kernel)
@@ -142,7 +142,7 @@ def test_watertight_sphere(oracle):
             c, d = a + npk, b + npk
             idx += [[a, c, b], [b, c, d]]
     tris = P[np.array(idx)].reshape(-1, 9) + np.float32(0)
-    agg = _agg(tris, "wide", max_prims_in_node=4)
+    agg = _agg(tris, "step", max_prims_in_node=4)
     n = 100_000
     rays = np.zeros((n, 8), np.float32)
     rays[:, :3] = rng.random((n, 3)) * 0.2 - 0.1
