@@ -68,8 +68,10 @@ typedef enum nnbvh_kernel {
     NNBVH_KERNEL_BASIC = 1,  /* one thread per ray over the 32-byte nodes, statement
                                 order of cpu/aggregates.cpp:529-624 */
     NNBVH_KERNEL_WIDE = 2,   /* persistent warps over 64-byte two-child nodes (first version) */
-    NNBVH_KERNEL_STEP = 3    /* persistent warps, one straight-line step per lane per
+    NNBVH_KERNEL_STEP = 3,   /* persistent warps, one straight-line step per lane per
                                 iteration, 256-bit node loads (the default) */
+    NNBVH_KERNEL_SPEC = 4    /* STEP + one postponed leaf per lane (speculative traversal;
+                                measured slower on B200, kept for A/B runs) */
 } nnbvh_kernel;
 
 typedef struct nnbvh_options {

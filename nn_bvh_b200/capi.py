@@ -16,7 +16,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(HERE, "libnnbvh.so")
 
 MISS = 0xFFFFFFFF
-KERNEL_AUTO, KERNEL_BASIC, KERNEL_WIDE, KERNEL_STEP = 0, 1, 2, 3
+KERNEL_AUTO, KERNEL_BASIC, KERNEL_WIDE, KERNEL_STEP, KERNEL_SPEC = 0, 1, 2, 3, 4
 SPLIT = {"sah": 0, "hlbvh": 1, "middle": 2, "equal": 3}
 
 NODE_DTYPE = np.dtype([("bounds", "<f4", (6,)), ("offset", "<i4"), ("nPrimitives", "<u2"),

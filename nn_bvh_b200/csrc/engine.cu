@@ -18,6 +18,7 @@
 #include "kernels.cuh"
 #include "binning.cuh"
 #include "traverse.cuh"
+#include "spec.cuh"
 
 namespace nnbvh {
 
@@ -101,6 +102,7 @@ struct nnbvh_engine {
     // scene
     bool haveScene = false;
     bool boxesRegular = true;  // every node box finite with lo <= hi: the fast slab test is exact
+    bool boxesNested = true;   // every child box lies inside its parent's: speculation is exact
     SceneDev sc{};
     DevBuf<nnbvh_node> dNodes;
     DevBuf<WideNode> dWide;
@@ -116,7 +118,8 @@ struct nnbvh_engine {
     int leafQuorum = 16;
     uint64_t chunkRays = 1u << 20;
     // ray binning pre-pass (binning.cuh)
-    int exactOnly = 0;       // StepKernel: skip the fast-slab launch (debug / A-B knob)
+    int exactOnly = 0;       // skip the fast-slab launch (debug / A-B knob)
+    int noSpec = 0;          // SpecKernel without postponed leaves (debug / A-B knob)
     int binMode = 0;         // 0 = off, 1 = on for batches >= binMinRays
     int binCellBits = 5;     // origin grid (1<<bits)^3
     int binDirBits = 2;      // octahedral direction grid (1<<bits)^2
@@ -168,6 +171,7 @@ extern "C" int nnbvh_create(const nnbvh_options *opts, nnbvh_engine **out) {
     e->chunkRays = (uint64_t)EnvInt("NNBVH_CHUNK_RAYS", (int)e->chunkRays);
     e->binMode = EnvInt("NNBVH_BIN", e->binMode);
     e->exactOnly = EnvInt("NNBVH_EXACT_ONLY", e->exactOnly);
+    e->noSpec = EnvInt("NNBVH_NO_SPEC", e->noSpec);
     e->binCellBits = std::min(8, std::max(0, EnvInt("NNBVH_BIN_CELL_BITS", e->binCellBits)));
     e->binDirBits = std::min(4, std::max(0, EnvInt("NNBVH_BIN_DIR_BITS", e->binDirBits)));
     e->binMinRays = (uint64_t)EnvInt("NNBVH_BIN_MIN_RAYS", (int)e->binMinRays);
@@ -361,6 +365,16 @@ extern "C" int nnbvh_upload_scene(nnbvh_engine *e, const nnbvh_node *nodes, uint
             float lo = nd.bounds[k], hi = nd.bounds[3 + k];
             if (!(std::isfinite(lo) && std::isfinite(hi) && lo <= hi)) e->boxesRegular = false;
         }
+    e->boxesNested = true;
+    for (uint32_t i = 0; i < nNodes; ++i) {
+        const nnbvh_node &nd = h[i];
+        if (nd.nPrimitives != 0 || i + 1 >= nNodes || nd.offset <= 0 || (uint32_t)nd.offset >= nNodes)
+            continue;  // leaves; malformed interiors are rejected by BuildWideLayout below
+        for (const nnbvh_node *c : {&h[i + 1], &h[nd.offset]})
+            for (int k = 0; k < 3; ++k)
+                if (!(c->bounds[k] >= nd.bounds[k] && c->bounds[3 + k] <= nd.bounds[3 + k]))
+                    e->boxesNested = false;
+    }
     std::vector<WideNode> wide;
     std::vector<uint8_t> last;
     int32_t rootRef = 0;
@@ -456,6 +470,16 @@ static void LaunchStep(nnbvh_engine *e, cudaStream_t st, const StepParams &p) {
     }
 }
 
+template <bool ANY, bool EXACT, bool SPEC>
+static void LaunchSpec(nnbvh_engine *e, cudaStream_t st, const StepParams &p) {
+    switch (e->wideMinB) {
+    case 1: SpecKernel<ANY, EXACT, SPEC, 1><<<e->numSMs * 1, 256, 0, st>>>(p); break;
+    case 2: SpecKernel<ANY, EXACT, SPEC, 2><<<e->numSMs * 2, 256, 0, st>>>(p); break;
+    case 3: SpecKernel<ANY, EXACT, SPEC, 3><<<e->numSMs * 3, 256, 0, st>>>(p); break;
+    default: SpecKernel<ANY, EXACT, SPEC, 4><<<e->numSMs * 4, 256, 0, st>>>(p); break;
+    }
+}
+
 // All pointers are device pointers here.
 static int LaunchTraversal(nnbvh_engine *e, cudaStream_t st, bool any, bool counters,
                            const RayInput &in, uint64_t n, const Outputs &o,
@@ -528,8 +552,16 @@ static int LaunchTraversal(nnbvh_engine *e, cudaStream_t st, bool any, bool coun
                 sp.cursor = cursor;
                 sp.deferred = scr.deferred.p;
                 sp.nDeferred = nDef;
-                if (any) LaunchStep<true, false>(e, st, sp);
-                else LaunchStep<false, false>(e, st, sp);
+                if (e->kernel != NNBVH_KERNEL_SPEC) {
+                    if (any) LaunchStep<true, false>(e, st, sp);
+                    else LaunchStep<false, false>(e, st, sp);
+                } else if (e->boxesNested && !e->noSpec) {
+                    if (any) LaunchSpec<true, false, true>(e, st, sp);
+                    else LaunchSpec<false, false, true>(e, st, sp);
+                } else {
+                    if (any) LaunchSpec<true, false, false>(e, st, sp);
+                    else LaunchSpec<false, false, false>(e, st, sp);
+                }
                 ++e->launches;
                 sp.perm = scr.deferred.p;
                 sp.nPtr = nDef;
@@ -537,8 +569,13 @@ static int LaunchTraversal(nnbvh_engine *e, cudaStream_t st, bool any, bool coun
                 sp.nDeferred = nullptr;
             }
             sp.cursor = cursor + 1;
-            if (any) LaunchStep<true, true>(e, st, sp);
-            else LaunchStep<false, true>(e, st, sp);
+            if (e->kernel != NNBVH_KERNEL_SPEC) {
+                if (any) LaunchStep<true, true>(e, st, sp);
+                else LaunchStep<false, true>(e, st, sp);
+            } else {
+                if (any) LaunchSpec<true, true, false>(e, st, sp);
+                else LaunchSpec<false, true, false>(e, st, sp);
+            }
             ++e->launches;
             CU(cudaGetLastError());
             return NNBVH_OK;

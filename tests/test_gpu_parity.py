@@ -8,7 +8,7 @@ from conftest import rand_rays, soup
 
 pytestmark = pytest.mark.gpu
 
-KERNELS = {"basic": 1, "wide": 2, "step": 3}
+KERNELS = {"basic": 1, "wide": 2, "step": 3, "spec": 4}
 
 
 def _agg(tris=None, kernel="wide", **kw):
@@ -35,7 +35,7 @@ def test_device_box_golden(golden):
     assert np.array_equal(agg.test_boxes(g["rays"], g["boxes"]), g["hit"])
 
 
-@pytest.mark.parametrize("kernel", ["basic", "wide", "step"])
+@pytest.mark.parametrize("kernel", ["basic", "wide", "step", "spec"])
 @pytest.mark.parametrize("split", ["sah", "middle", "equal"])
 def test_scene_golden(golden, kernel, split):
     g = golden["scene_small"]
@@ -53,7 +53,7 @@ def test_scene_golden(golden, kernel, split):
     assert (int(nv.sum()), int(tt.sum())) == (st[2], st[3])
 
 
-@pytest.mark.parametrize("kernel", ["basic", "wide", "step"])
+@pytest.mark.parametrize("kernel", ["basic", "wide", "step", "spec"])
 @pytest.mark.parametrize("T,s,mp", [(1, 0.3, 4), (2, 0.3, 4), (37, 0.2, 4), (20000, 0.02, 4),
                                      (20000, 0.05, 1), (60000, 0.01, 255)])
 def test_random_soups_vs_oracle(oracle, kernel, T, s, mp):
@@ -70,7 +70,7 @@ def test_random_soups_vs_oracle(oracle, kernel, T, s, mp):
     assert np.array_equal(nv, wnv) and np.array_equal(tt, wtt)
 
 
-@pytest.mark.parametrize("kernel", ["basic", "wide", "step"])
+@pytest.mark.parametrize("kernel", ["basic", "wide", "step", "spec"])
 def test_edge_inputs(oracle, kernel):
     rng = np.random.default_rng(3)
     tris = soup(rng, 5000, 0.05)
@@ -96,7 +96,7 @@ def test_edge_inputs(oracle, kernel):
     assert np.array_equal(agg.IntersectPBatch(rays), oracle.intersect_p(nodes, agg.ordered_tris9, rays))
 
 
-@pytest.mark.parametrize("kernel", ["basic", "wide", "step"])
+@pytest.mark.parametrize("kernel", ["basic", "wide", "step", "spec"])
 def test_empty_scene_misses(kernel):
     import nn_bvh_b200 as nb
     agg = _agg(None, kernel)
@@ -142,7 +142,7 @@ def test_watertight_sphere(oracle):
             c, d = a + npk, b + npk
             idx += [[a, c, b], [b, c, d]]
     tris = P[np.array(idx)].reshape(-1, 9) + np.float32(0)
-    agg = _agg(tris, "step", max_prims_in_node=4)
+    agg = _agg(tris, "spec", max_prims_in_node=4)
     n = 100_000
     rays = np.zeros((n, 8), np.float32)
     rays[:, :3] = rng.random((n, 3)) * 0.2 - 0.1
@@ -193,3 +193,41 @@ def test_single_ray_surface_and_tensors(oracle):
     occ = agg.IntersectBatchSoA(*cols, any_hit=True)
     assert np.array_equal(occ, oracle.intersect_p(nodes, agg.ordered_tris9, rays))
     assert agg.launch_count() > 0
+
+
+@pytest.mark.parametrize("kernel", ["wide", "step", "spec"])
+@pytest.mark.parametrize("mp", [1, 4, 32])
+def test_axis_aligned_room_near_ties(oracle, kernel, mp):
+    """Flat axis-aligned geometry: leaf boxes are flat, so box-entry distances tie with hit
+    distances to the ulp, and rays aimed at grid vertices / edges hit several triangles at the
+    same t (shared edges).  This is where 'tMax grows by an ulp' (shapes.cpp:239-247) and the
+    in-leaf order matter; results must still be bit-identical."""
+    from nn_bvh_b200 import scenes
+    tris, _ = scenes.procedural_room(n_objects=6, sphere_level=3, seed=7)
+    agg = _agg(tris, kernel, max_prims_in_node=mp)
+    nodes = agg.nodes.view(np.uint32).reshape(-1, 8)
+    rng = np.random.default_rng(11 + mp)
+    n = 300_000
+    rays = np.zeros((n, 8), np.float32)
+    o = np.stack([rng.uniform(-2.9, 2.9, n), rng.uniform(0.1, 2.9, n), rng.uniform(-2.9, 2.9, n)], 1)
+    # targets: wall grid vertices (64x64 grid over [-3,3]x[0,3]x[-3,3]) on a random wall
+    g = np.linspace(0.0, 1.0, 65)
+    u, v = rng.integers(0, 65, n), rng.integers(0, 65, n)
+    axis, side = rng.integers(0, 3, n), rng.integers(0, 2, n)
+    lo, hi = np.array([-3.0, 0.0, -3.0]), np.array([3.0, 3.0, 3.0])
+    tgt = np.zeros((n, 3))
+    for a in range(3):
+        oth = [k for k in range(3) if k != a]
+        m = axis == a
+        tgt[m, oth[0]] = lo[oth[0]] + g[u[m]] * (hi[oth[0]] - lo[oth[0]])
+        tgt[m, oth[1]] = lo[oth[1]] + g[v[m]] * (hi[oth[1]] - lo[oth[1]])
+        tgt[m, a] = np.where(side[m] == 1, hi[a], lo[a])
+    tgt[n // 2:] += rng.normal(scale=1e-3, size=(n - n // 2, 3)) * (rng.random((n - n // 2, 1)) < 0.5)
+    rays[:, :3] = o
+    rays[:, 4:7] = (tgt - o)
+    rays[: n // 4, 4:7] /= np.linalg.norm(rays[: n // 4, 4:7], axis=1, keepdims=True)
+    rays[:, 3] = np.inf
+    rays[n // 3: n // 2, 3] = 1.0    # shadow-style: d = target - origin, tMax = 1 (hit exactly at tMax)
+    want = oracle.intersect(nodes, agg.ordered_tris9, rays)
+    assert np.array_equal(_as_words(agg.IntersectBatch(rays)), want)
+    assert np.array_equal(agg.IntersectPBatch(rays), oracle.intersect_p(nodes, agg.ordered_tris9, rays))
