@@ -39,7 +39,7 @@ UNIT = "Mrays/s"
 def parse():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--steps", type=int, default=30)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--scene", default="bathroom")
@@ -248,19 +248,24 @@ def run_ours(args):
     d_s = torch.from_numpy(shadow.view(np.float32).reshape(-1, 8)).to(dev)
     d_hits = torch.zeros((n, 5), dtype=torch.int32, device=dev)
     d_occ = torch.zeros(n, dtype=torch.uint8, device=dev)
-    gather_hits = gather_occ = None
-    if world > 1 and rank == 0:   # NCCL gather of hit records to rank 0
-        gather_hits = [torch.empty_like(d_hits) for _ in range(world)]
-        gather_occ = [torch.empty_like(d_occ) for _ in range(world)]
+    from nn_bvh_b200 import sharding
+    g_hits = g_occ = None
+    if world > 1 and rank == 0:   # hit records of all ranks, global ray order
+        g_hits = torch.empty((world * n, 5), dtype=torch.int32, device=dev)
+        g_occ = torch.empty(world * n, dtype=torch.uint8, device=dev)
 
     def step(ev_mid=None):
         agg.IntersectBatch(d_b, hits=d_hits, n=n)
         if ev_mid is not None:
             ev_mid.record(stream)
+        w1 = None
+        if world > 1:   # NCCL gather of the closest-hit records overlaps the shadow kernel
+            _, w1 = sharding.gather_records(d_hits, world * n, dst=0, out=g_hits, async_op=True)
         agg.IntersectPBatch(d_s, occluded=d_occ, n=n)
         if world > 1:
-            dist.gather(d_hits, gather_hits, dst=0)
-            dist.gather(d_occ, gather_occ, dst=0)
+            _, w2 = sharding.gather_records(d_occ, world * n, dst=0, out=g_occ, async_op=True)
+            w1.wait()
+            w2.wait()
 
     def barrier():
         if world > 1:
@@ -286,6 +291,17 @@ def run_ours(args):
     closest_ms = float(np.mean([ev[3 * k].elapsed_time(ev[3 * k + 1])
                                 for k in range(args.steps)]))
     clk = clocks.stop() if rank == 0 else None
+    if world > 1:
+        # the gathered records must be every rank's own records, in global ray order
+        mine = torch.stack([d_hits.to(torch.int64).sum(), d_occ.to(torch.int64).sum()])
+        sums = [torch.empty_like(mine) for _ in range(world)]
+        dist.all_gather(sums, mine)
+        if rank == 0:
+            assert torch.equal(g_hits[:n], d_hits) and torch.equal(g_occ[:n], d_occ)
+            for r in range(world):
+                got = torch.stack([g_hits[r * n:(r + 1) * n].to(torch.int64).sum(),
+                                   g_occ[r * n:(r + 1) * n].to(torch.int64).sum()])
+                assert torch.equal(got, sums[r]), f"gathered records of rank {r} differ"
     t = torch.tensor([total_ms, closest_ms], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)

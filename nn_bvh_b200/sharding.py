@@ -1,0 +1,107 @@
+"""nn_bvh_b200/sharding.py -- ray-batch sharding across ranks (one process per GPU).
+
+The reference has no multi-device path at all (no NCCL/MPI; `--gpu-device`
+picks one GPU, /root/reference/src/pbrt/pbrt.cpp:68).  Rays are independent, so the path
+shards with no data-path collective: the scene is replicated on every rank, rank g of G
+traces the contiguous slice [g*N/G, (g+1)*N/G) of the batch, and the one
+exchange step is returning the 20-byte hit records / occlusion bytes to the caller's rank
+(an NCCL gather over NVLink on GPUs; gloo in the CPU tests).
+
+Nothing here intersects anything: `trace` callables are injected (GPUBVHAggregate methods in
+bench.py, anything with the same contract in tests).
+"""
+from __future__ import annotations
+
+from typing import Callable, Optional
+
+import torch
+import torch.distributed as dist
+
+
+def shard_range(n: int, rank: int, world: int) -> tuple[int, int]:
+    """Contiguous slice of rank `rank`: [rank*n//world, (rank+1)*n//world).  Slices tile
+    [0, n) exactly, differ in size by at most one, and may be empty when n < world."""
+    if not (0 <= rank < world):
+        raise ValueError(f"rank {rank} outside world of {world}")
+    return (rank * n) // world, ((rank + 1) * n) // world
+
+
+def max_shard(n: int, world: int) -> int:
+    return max(shard_range(n, r, world)[1] - shard_range(n, r, world)[0] for r in range(world))
+
+
+def gather_records(local: torch.Tensor, n_total: int, dst: int = 0, group=None,
+                   out: Optional[torch.Tensor] = None, async_op: bool = False):
+    """Gather per-rank result rows (hit records (m,5) int32 or occlusion bytes (m,)) into one
+    (n_total, ...) tensor on rank `dst`, in global ray order; returns it on `dst`, None elsewhere.
+
+    Equal shards (n_total % world == 0) are received straight into slices of `out` -- no
+    staging copy -- and with async_op=True the call returns (out_or_None, work) without
+    waiting, so the caller can overlap the transfer with its next kernel.  Ragged shards are
+    padded to the largest shard (NCCL gather needs same-shape contributions); the padding is
+    dropped on `dst`."""
+    world = dist.get_world_size(group)
+    rank = dist.get_rank(group)
+    m = max_shard(n_total, world)
+    a, b = shard_range(n_total, rank, world)
+    if local.shape[0] != b - a:
+        raise ValueError(f"rank {rank}: local result has {local.shape[0]} rows, shard has {b - a}")
+    tail = tuple(local.shape[1:])
+    if rank == dst and out is None:
+        out = local.new_empty((n_total,) + tail)
+    if m == 0:
+        return ((out if rank == dst else None), None) if async_op else (out if rank == dst else None)
+    if n_total % world == 0:
+        parts = list(out.view((world, m) + tail).unbind(0)) if rank == dst else None
+        work = dist.gather(local.contiguous(), parts, dst=dst, group=group, async_op=async_op)
+        res = out if rank == dst else None
+        return (res, work) if async_op else res
+    if async_op:
+        raise ValueError("async gather needs equal shards (n_total % world == 0)")
+    send = local.new_zeros((m,) + tail)
+    send[: b - a] = local
+    parts = [torch.empty_like(send) for _ in range(world)] if rank == dst else None
+    dist.gather(send, parts, dst=dst, group=group)
+    if rank != dst:
+        return None
+    for r, part in enumerate(parts):
+        ra, rb = shard_range(n_total, r, world)
+        out[ra:rb] = part[: rb - ra]
+    return out
+
+
+def scatter_rays(rays: Optional[torch.Tensor], n_total: int, src: int = 0, group=None,
+                 device=None) -> torch.Tensor:
+    """Distribute an (n_total, 8) float32 ray batch held by rank `src` so that each rank
+    ends up with its shard_range slice (padded scatter, padding dropped)."""
+    world = dist.get_world_size(group)
+    rank = dist.get_rank(group)
+    m = max_shard(n_total, world)
+    a, b = shard_range(n_total, rank, world)
+    if device is None:
+        device = rays.device if rays is not None else torch.device("cpu")
+    recv = torch.zeros((m, 8), dtype=torch.float32, device=device)
+    if m == 0:
+        return recv
+    parts = None
+    if rank == src:
+        parts = []
+        for r in range(world):
+            ra, rb = shard_range(n_total, r, world)
+            part = torch.zeros((m, 8), dtype=torch.float32, device=device)
+            part[: rb - ra] = rays[ra:rb]
+            parts.append(part)
+    dist.scatter(recv, parts, src=src, group=group)
+    return recv[: b - a]
+
+
+def trace_sharded(trace: Callable[[torch.Tensor], torch.Tensor], rays_full: torch.Tensor,
+                  dst: int = 0, group=None) -> Optional[torch.Tensor]:
+    """Every rank holds (or can regenerate) the full batch: trace the own slice with `trace`
+    (rays (m,8) -> result rows (m,...)) and gather the records to `dst` in global order."""
+    world = dist.get_world_size(group)
+    rank = dist.get_rank(group)
+    n = rays_full.shape[0]
+    a, b = shard_range(n, rank, world)
+    local = trace(rays_full[a:b])
+    return gather_records(local, n, dst=dst, group=group)
