@@ -19,7 +19,9 @@ tris, cam, name = scenes.load(scene)
 nodes, order = nb.build_bvh(tris, 4, "sah")
 ordered = tris[order]
 agg = nb.GPUBVHAggregate(nodes=nodes, ordered_tris9=ordered)
-if kind == "primary":
+if kind == "random":
+    r = R.random_rays(n)
+elif kind == "primary":
     res = int(np.ceil(np.sqrt(n)))
     r = R.camera_rays(cam, res, res)[:n]
 else:
@@ -36,4 +38,12 @@ for _ in range(iters):
         agg.IntersectBatch(d, hits=d_hits, n=n)
     ms = agg.last_kernel_ms()
     print(f"{name} {kind} {n} rays: {ms:.3f} ms  {n / ms / 1e3:.1f} Mrays/s", flush=True)
+if os.environ.get("PROF_COUNTERS"):
+    m = min(n, 1 << 20)
+    _, nv, tt = agg.IntersectCounters(r[:m], any_hit=(kind == "shadow"))
+    io = 33 if kind == "shadow" else 52
+    bpr = io + 32.0 * nv.mean() + 36.0 * tt.mean()
+    print(f"nodesVisited {nv.mean():.2f} triTests {tt.mean():.2f} algorithmic B/ray {bpr:.0f} -> "
+          f"{bpr * n / ms / 1e6:.0f} GB/s algorithmic; scene {len(nodes) * 32 / 1e6:.0f} MB nodes32 + "
+          f"{len(ordered) * 48 / 1e6:.0f} MB tris48 + {(len(nodes) // 2) * 64 / 1e6:.0f} MB wide", flush=True)
 agg.close()
