@@ -110,13 +110,15 @@ struct nnbvh_engine {
     // device-pointer path scratch
     Scratch scratch;
     // host-pointer pipeline
-    static constexpr int kSlots = 3;
-    Slot slots[kSlots];
+    static constexpr int kMaxSlots = 8;
+    int nSlots = 4;          // chunks in flight (NNBVH_SLOTS); 512K x 4 measured best on PCIe Gen5
+    Slot slots[kMaxSlots];
     // tuning knobs (env overridable, see nnbvh_create)
     int wideMinB = 4;        // CTAs/SM the WideKernel variant is compiled for
     int refillBelow = 24;
     int leafQuorum = 16;
-    uint64_t chunkRays = 1u << 20;
+    uint64_t chunkRays = 1u << 19;
+    uint64_t chunkRaysSoa = 1u << 20;  // SoA planes are 4 bytes per ray each: larger chunks per copy
     // ray binning pre-pass (binning.cuh)
     int exactOnly = 0;       // skip the fast-slab launch (debug / A-B knob)
     int noSpec = 0;          // SpecKernel without postponed leaves (debug / A-B knob)
@@ -169,6 +171,8 @@ extern "C" int nnbvh_create(const nnbvh_options *opts, nnbvh_engine **out) {
     e->refillBelow = EnvInt("NNBVH_REFILL_BELOW", e->refillBelow);
     e->leafQuorum = EnvInt("NNBVH_LEAF_QUORUM", e->leafQuorum);
     e->chunkRays = (uint64_t)EnvInt("NNBVH_CHUNK_RAYS", (int)e->chunkRays);
+    e->chunkRaysSoa = (uint64_t)EnvInt("NNBVH_CHUNK_RAYS_SOA", (int)e->chunkRaysSoa);
+    e->nSlots = std::min((int)nnbvh_engine::kMaxSlots, std::max(1, EnvInt("NNBVH_SLOTS", e->nSlots)));
     e->binMode = EnvInt("NNBVH_BIN", e->binMode);
     e->exactOnly = EnvInt("NNBVH_EXACT_ONLY", e->exactOnly);
     e->noSpec = EnvInt("NNBVH_NO_SPEC", e->noSpec);
@@ -643,12 +647,12 @@ static int RunBatch(nnbvh_engine *e, const Batch &b) {
     }
 
     // ---- host buffers: chunked H2D -> kernel -> D2H over kSlots streams ----
-    const uint64_t chunk = std::max<uint64_t>(e->chunkRays, 1024);
+    const uint64_t chunk = std::max<uint64_t>(b.soa ? e->chunkRaysSoa : e->chunkRays, 1024);
     std::vector<cudaEvent_t> k0, k1;  // kernel timing events, one pair per chunk
     int idx = 0;
     int rcOut = NNBVH_OK;
     for (uint64_t off = 0; off < b.n && rcOut == NNBVH_OK; off += chunk, ++idx) {
-        Slot &s = e->slots[idx % nnbvh_engine::kSlots];
+        Slot &s = e->slots[idx % e->nSlots];
         const uint64_t m = std::min(chunk, b.n - off);
         CU(cudaEventSynchronize(s.done));  // slot buffers free again
         RayInput in{};
