@@ -114,7 +114,7 @@ struct nnbvh_engine {
     int nSlots = 4;          // chunks in flight (NNBVH_SLOTS); 512K x 4 measured best on PCIe Gen5
     Slot slots[kMaxSlots];
     // tuning knobs (env overridable, see nnbvh_create)
-    int wideMinB = 4;        // CTAs/SM the WideKernel variant is compiled for
+    int wideMinB = 5;        // CTAs/SM the traversal kernel is compiled for
     int refillBelow = 24;
     int leafQuorum = 16;
     uint64_t chunkRays = 1u << 19;
@@ -459,8 +459,8 @@ static int LaunchWide(nnbvh_engine *e, cudaStream_t st, const WideParams &p, uin
     switch (e->wideMinB) {
     case 1: return LaunchWideT<ANY, 1>(e, st, p, smemBytes);
     case 3: return LaunchWideT<ANY, 3>(e, st, p, smemBytes);
-    case 4: return LaunchWideT<ANY, 4>(e, st, p, smemBytes);
-    default: return LaunchWideT<ANY, 2>(e, st, p, smemBytes);
+    case 2: return LaunchWideT<ANY, 2>(e, st, p, smemBytes);
+    default: return LaunchWideT<ANY, 4>(e, st, p, smemBytes);
     }
 }
 
@@ -470,7 +470,9 @@ static void LaunchStep(nnbvh_engine *e, cudaStream_t st, const StepParams &p) {
     case 1: StepKernel<ANY, EXACT, 1><<<e->numSMs * 1, 256, 0, st>>>(p); break;
     case 2: StepKernel<ANY, EXACT, 2><<<e->numSMs * 2, 256, 0, st>>>(p); break;
     case 3: StepKernel<ANY, EXACT, 3><<<e->numSMs * 3, 256, 0, st>>>(p); break;
-    default: StepKernel<ANY, EXACT, 4><<<e->numSMs * 4, 256, 0, st>>>(p); break;
+    case 4: StepKernel<ANY, EXACT, 4><<<e->numSMs * 4, 256, 0, st>>>(p); break;
+    case 6: StepKernel<ANY, EXACT, 6><<<e->numSMs * 6, 256, 0, st>>>(p); break;
+    default: StepKernel<ANY, EXACT, 5><<<e->numSMs * 5, 256, 0, st>>>(p); break;
     }
 }
 
@@ -502,7 +504,7 @@ static int LaunchTraversal(nnbvh_engine *e, cudaStream_t st, bool any, bool coun
             else BasicKernel<false, false><<<grid, 128, 0, st>>>(e->sc, in, n, o.hits, o.occ, nullptr, nullptr);
         }
     } else {
-        int minB = (e->wideMinB >= 1 && e->wideMinB <= 4) ? e->wideMinB : 2;
+        int minB = (e->wideMinB >= 1 && e->wideMinB <= 3) ? e->wideMinB : 4;
         uint32_t budgetNodes = (uint32_t)((e->maxSmemOptin - 2048) / minB / sizeof(WideNode));
         uint32_t want = e->smemTopNodes >= 0 ? (uint32_t)e->smemTopNodes : 0u;  // measured: L1 beats explicit staging
         uint32_t smemNodes = std::min(std::min(want, budgetNodes), e->sc.topNodes);
