@@ -1,0 +1,127 @@
+#!/usr/bin/env python3
+"""tools/config5.py -- BASELINE.json configs[4]: synthetic 10M-triangle mesh, 256M random rays,
+sharded over the ranks it is launched with (torchrun), NCCL gather of a per-rank checksum.
+
+Ray i is a pure function of its GLOBAL index (counter-based hash), so every world size traces the
+same 256M rays; rank g takes the contiguous slice shard_range(N, g, G).  The
+run prints Mrays/s (device timed, max over ranks) and three checksums of the hit records that
+must be identical for every G:  number of hits, sum of primitive indices, xor of the t bit
+patterns.  A strided subset is checked against the oracle on rank 0 (tools may use the oracle).
+usage: [torchrun ...] config5.py [--tris 10000000] [--rays 268435456] [--oracle 200000]
+"""
+import argparse
+import os
+import sys
+import time
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+
+
+def hash01(idx: torch.Tensor, stream: int) -> torch.Tensor:
+    """splitmix64-style hash of (global index, stream) -> float32 in [0,1) with 24 random bits."""
+    def w(v):   # python int -> the int64 with the same low 64 bits
+        v &= (1 << 64) - 1
+        return v - (1 << 64) if v >= (1 << 63) else v
+    x = idx * -7046029254386353131 + w((stream + 1) * 0xBF58476D1CE4E5B9)   # wraps mod 2^64
+    def lsr(v, k):   # logical shift right on int64
+        return (v >> k) & ((1 << (64 - k)) - 1)
+    x = (x ^ lsr(x, 30)) * -4658895280553007687
+    x = (x ^ lsr(x, 27)) * -7723592293110705685
+    x = x ^ lsr(x, 31)
+    return (lsr(x, 40) & 0xFFFFFF).to(torch.float32) * (1.0 / 16777216.0)
+
+
+def gen_rays(a: int, b: int, dev) -> torch.Tensor:
+    """rays [a, b): o ~ U[-0.25,1.25)^3, d uniform on the sphere, tMax = inf."""
+    out = torch.empty((b - a, 8), dtype=torch.float32, device=dev)
+    step = 1 << 24
+    for s in range(a, b, step):
+        e = min(b, s + step)
+        idx = torch.arange(s, e, dtype=torch.int64, device=dev)
+        o = out[s - a:e - a]
+        for k in range(3):
+            o[:, k] = hash01(idx, k) * 1.5 - 0.25
+        z = 1 - 2 * hash01(idx, 3)
+        phi = (2 * np.pi) * hash01(idx, 4)
+        rad = torch.sqrt(torch.clamp(1 - z * z, min=0))
+        o[:, 4], o[:, 5], o[:, 6] = rad * torch.cos(phi), rad * torch.sin(phi), z
+        o[:, 3] = float("inf")
+        o[:, 7] = 0
+    return out
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--tris", type=int, default=10_000_000)
+    ap.add_argument("--rays", type=int, default=256 << 20)
+    ap.add_argument("--oracle", type=int, default=200_000)
+    ap.add_argument("--reps", type=int, default=3)
+    a = ap.parse_args()
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    import nn_bvh_b200 as nb
+    from nn_bvh_b200 import scenes, sharding
+    tris = scenes.synthetic_soup(a.tris)
+    t0 = time.time()
+    nodes, order = nb.build_bvh(tris, 4, "sah")
+    t_build = time.time() - t0
+    agg = nb.GPUBVHAggregate(nodes=nodes, ordered_tris9=tris[order], order=order, device=local)
+    lo, hi = sharding.shard_range(a.rays, rank, world)
+    rays = gen_rays(lo, hi, dev)
+    hits = torch.zeros((hi - lo, 5), dtype=torch.int32, device=dev)
+    stream = torch.cuda.Stream(device=dev)
+    torch.cuda.set_stream(stream)
+    agg.set_stream(stream.cuda_stream)
+    best = 1e30
+    for _ in range(a.reps):
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        agg.IntersectBatch(rays, hits=hits, n=hi - lo)
+        torch.cuda.synchronize()
+        t = torch.tensor([agg.last_kernel_ms()], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        best = min(best, t.item())
+    hit = hits[:, 0] != -1
+    xor = torch.tensor(0, dtype=torch.int64, device=dev)
+    tb = hits[:, 1].to(torch.int64)
+    while tb.numel() > 1:   # xor-reduce
+        if tb.numel() % 2:
+            tb = torch.cat([tb, tb.new_zeros(1)])
+        tb = tb[0::2] ^ tb[1::2]
+    xor = tb[0]
+    cs = torch.stack([hit.sum(), hits[:, 0].to(torch.int64)[hit].sum(), xor])
+    if world > 1:
+        parts = [torch.empty_like(cs) for _ in range(world)]
+        dist.all_gather(parts, cs)
+        tot = torch.stack(parts)
+        cs = torch.stack([tot[:, 0].sum(), tot[:, 1].sum(), torch.tensor(
+            int(np.bitwise_xor.reduce(tot[:, 2].cpu().numpy())), device=dev)])
+    if rank == 0:
+        ok = None
+        if a.oracle:
+            from oracle.pyoracle import Oracle
+            stepn = max(1, (hi - lo) // a.oracle)
+            sub = rays[::stepn].cpu().numpy()
+            want = Oracle().intersect(agg.nodes.view(np.uint32).reshape(-1, 8), agg.ordered_tris9, sub)
+            ok = bool(np.array_equal(hits[::stepn].cpu().numpy().view(np.uint32), want))
+        print({"config": f"synthetic {a.tris} triangles, {a.rays} random rays", "n_gpus": world,
+               "bvh_nodes": int(len(nodes)), "build_s": round(t_build, 1), "kernel_ms": round(best, 2),
+               "Mrays_s": round(a.rays / best / 1e3, 1), "hits": int(cs[0]), "sum_prim": int(cs[1]),
+               "xor_t_bits": int(cs[2]), "oracle_subset_bit_exact": ok}, flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()
