@@ -33,6 +33,7 @@
 
 #include "../../include/nnbvh.h"
 #include "internal.h"
+#include "hlbvh_emit.h"
 
 namespace nnbvh {
 namespace {
@@ -224,6 +225,196 @@ uint32_t BuildSpan(const Ctx &c, size_t s, size_t n, uint32_t at, int par) {
 }  // namespace
 }  // namespace nnbvh
 
+
+// ---------------------------------------------------------------------------
+// HLBVH (aggregates.cpp:389-503, 626-723).  Morton codes -> stable sort -> independent treelets
+// (hlbvh_emit.h) -> upper SAH over the treelet roots, emitted straight into pre-order.
+// ---------------------------------------------------------------------------
+namespace nnbvh {
+namespace {
+
+struct UpperCtx {
+    const nnbvh_node *slab;
+    TreeletRef *tr;
+    nnbvh_node *out;
+    int error;  // 1: the reference's CHECK_NE(centroidBounds...) / CHECK_GT(mid, start) would fire
+};
+
+Aabb BoxOf(const nnbvh_node &nd) {
+    Aabb b;
+    for (int k = 0; k < 3; ++k) {
+        b.lo[k] = nd.bounds[k];
+        b.hi[k] = nd.bounds[3 + k];
+    }
+    return b;
+}
+
+// Writes the subtree over treelets [s, e) at out[at...]; returns the number of nodes written.
+uint32_t EmitUpper(UpperCtx &c, uint32_t s, uint32_t e, uint32_t at) {
+    if (c.error) return 0;
+    if (e - s == 1) {  // :633-634: the treelet itself; rebase its interior offsets
+        const TreeletRef &t = c.tr[s];
+        std::memcpy(c.out + at, c.slab + t.slabAt, sizeof(nnbvh_node) * (size_t)t.nNodes);
+        for (uint32_t i = at; i < at + t.nNodes; ++i)
+            if (c.out[i].nPrimitives == 0) c.out[i].offset += (int32_t)at;
+        return t.nNodes;
+    }
+    Aabb bounds, cb;
+    for (uint32_t i = s; i < e; ++i) {
+        Aabb b = BoxOf(c.slab[c.tr[i].slabAt]);
+        bounds.Grow(b);
+        float m[3];
+        for (int k = 0; k < 3; ++k) m[k] = (b.lo[k] + b.hi[k]) * 0.5f;  // :645-646
+        cb.Grow(m);
+    }
+    const int dim = cb.WidestAxis();
+    if (cb.hi[dim] == cb.lo[dim]) {  // CHECK_NE, :652
+        c.error = 1;
+        return 0;
+    }
+    auto bucketOf = [&](const TreeletRef &t) {
+        const nnbvh_node &r = c.slab[t.slabAt];
+        float centroid = (r.bounds[dim] + r.bounds[3 + dim]) * 0.5f;
+        int b = kBuckets * ((centroid - cb.lo[dim]) / (cb.hi[dim] - cb.lo[dim]));
+        return b == kBuckets ? kBuckets - 1 : b;
+    };
+    int count[kBuckets] = {};
+    Aabb bb[kBuckets];
+    for (uint32_t i = s; i < e; ++i) {
+        int b = bucketOf(c.tr[i]);
+        ++count[b];
+        bb[b].Grow(BoxOf(c.slab[c.tr[i].slabAt]));
+    }
+    float best = 0;
+    int bestBucket = -1;
+    for (int i = 0; i < kBuckets - 1; ++i) {  // :679-692, O(buckets^2) there; same sums here
+        Aabb b0, b1;
+        int c0 = 0, c1 = 0;
+        for (int j = 0; j <= i; ++j) {
+            b0.Grow(bb[j]);
+            c0 += count[j];
+        }
+        for (int j = i + 1; j < kBuckets; ++j) {
+            b1.Grow(bb[j]);
+            c1 += count[j];
+        }
+        float cost = .125f + (c0 * b0.Area() + c1 * b1.Area()) / bounds.Area();
+        if (bestBucket < 0 || cost < best) {
+            best = cost;
+            bestBucket = i;
+        }
+    }
+    TreeletRef *m = std::partition(c.tr + s, c.tr + e,
+                                   [&](const TreeletRef &t) { return bucketOf(t) <= bestBucket; });
+    const uint32_t mid = (uint32_t)(m - c.tr);
+    if (!(mid > s && mid < e)) {  // CHECK_GT / CHECK_LT, :716-717
+        c.error = 1;
+        return 0;
+    }
+    const uint32_t nl = EmitUpper(c, s, mid, at + 1);
+    const uint32_t nr = EmitUpper(c, mid, e, at + 1 + nl);
+    if (c.error) return 0;
+    nnbvh_node &nd = c.out[at];
+    std::memset(&nd, 0, sizeof(nd));
+    const nnbvh_node &L = c.out[at + 1], &R = c.out[at + 1 + nl];
+    for (int k = 0; k < 3; ++k) {
+        nd.bounds[k] = std::min(L.bounds[k], R.bounds[k]);
+        nd.bounds[3 + k] = std::max(L.bounds[3 + k], R.bounds[3 + k]);
+    }
+    nd.axis = (uint8_t)dim;
+    nd.offset = (int32_t)(at + 1 + nl);
+    return 1 + nl + nr;
+}
+
+}  // namespace
+
+int AssembleHLBVH(const nnbvh_node *slab, TreeletRef *treelets, uint32_t nTreelets,
+                  nnbvh_node *nodesOut, uint32_t *nNodesOut) {
+    UpperCtx c{slab, treelets, nodesOut, 0};
+    uint32_t total = EmitUpper(c, 0, nTreelets, 0);
+    if (c.error)
+        return SetError(NNBVH_ERR_INVALID, "hlbvh: treelet roots cannot be split (the reference "
+                                           "CHECKs centroidBounds / mid in buildUpperSAH, "
+                                           "cpu/aggregates.cpp:652,716)");
+    *nNodesOut = total;
+    return NNBVH_OK;
+}
+
+namespace {
+
+// Triangle::Bounds = Union(Bounds3f(p0,p1), p2), shapes.cpp:294-301
+void TriBox(const float *p, float *b6) {
+    for (int k = 0; k < 3; ++k) {
+        b6[k] = std::min(std::min(p[k], p[3 + k]), p[6 + k]);
+        b6[3 + k] = std::max(std::max(p[k], p[3 + k]), p[6 + k]);
+    }
+}
+
+int BuildHLBVHHost(const float *tris9, uint32_t nTris, int maxLeaf, int nThreads,
+                   nnbvh_node *nodesOut, uint32_t *nNodesOut, uint32_t *orderOut) {
+    std::vector<float> box(6 * (size_t)nTris);
+    Aabb cb;
+    for (uint32_t i = 0; i < nTris; ++i) {
+        float *b = &box[6 * (size_t)i];
+        TriBox(tris9 + 9 * (size_t)i, b);
+        float m[3] = {.5f * b[0] + .5f * b[3], .5f * b[1] + .5f * b[4], .5f * b[2] + .5f * b[5]};
+        cb.Grow(m);
+    }
+    std::vector<uint32_t> code(nTris), prim(nTris), code2(nTris), prim2(nTris);
+    for (uint32_t i = 0; i < nTris; ++i) {
+        const float *b = &box[6 * (size_t)i];
+        float o[3];
+        for (int k = 0; k < 3; ++k) o[k] = cb.Rel(.5f * b[k] + .5f * b[3 + k], k) * 1024;  // :404-408
+        code[i] = EncodeMorton3(o[0], o[1], o[2]);
+        prim[i] = i;
+    }
+    // stable LSD radix sort on the 30 code bits, 3 passes of 10 (the reference does 5 of 6, :41-82;
+    // every stable sort by the same key yields the same permutation)
+    for (int pass = 0; pass < 3; ++pass) {
+        const int shift = 10 * pass;
+        std::vector<uint32_t> cnt(1025, 0);
+        for (uint32_t i = 0; i < nTris; ++i) ++cnt[((code[i] >> shift) & 1023u) + 1];
+        for (int d = 0; d < 1024; ++d) cnt[d + 1] += cnt[d];
+        for (uint32_t i = 0; i < nTris; ++i) {
+            uint32_t at = cnt[(code[i] >> shift) & 1023u]++;
+            code2[at] = code[i];
+            prim2[at] = prim[i];
+        }
+        code.swap(code2);
+        prim.swap(prim2);
+    }
+    std::vector<TreeletRef> tr;
+    for (uint32_t start = 0, end = 1; end <= nTris; ++end)
+        if (end == nTris || ((code[start] ^ code[end]) & kTreeletMask)) {
+            tr.push_back(TreeletRef{start, end - start, 2 * start, 0});
+            start = end;
+        }
+    std::vector<nnbvh_node> slab(2 * (size_t)nTris);
+    std::atomic<uint32_t> next{0};
+    std::atomic<int> overflow{0};
+    auto work = [&] {
+        for (uint32_t t; (t = next.fetch_add(1)) < tr.size();) {
+            int ov = 0;
+            tr[t].nNodes = EmitTreelet(code.data(), prim.data(), box.data(), tr[t].start, tr[t].n,
+                                       maxLeaf, slab.data() + tr[t].slabAt, &ov);
+            if (ov) overflow.store(1);
+        }
+    };
+    int nt = std::max(1, std::min(nThreads, 64));
+    std::vector<std::thread> pool;
+    for (int k = 1; k < nt; ++k) pool.emplace_back(work);
+    work();
+    for (std::thread &t : pool) t.join();
+    if (overflow.load())
+        return SetError(NNBVH_ERR_INVALID, "nnbvh_build_bvh: a leaf holds >= 65536 primitives "
+                                           "(the reference CHECKs nPrimitives < 65536)");
+    for (uint32_t i = 0; i < nTris; ++i) orderOut[i] = prim[i];
+    return AssembleHLBVH(slab.data(), tr.data(), (uint32_t)tr.size(), nodesOut, nNodesOut);
+}
+
+}  // namespace
+}  // namespace nnbvh
+
 using namespace nnbvh;
 
 extern "C" int nnbvh_build_bvh(const float *triVerts9, uint32_t nTris, int32_t maxPrimsInNode,
@@ -232,12 +423,15 @@ extern "C" int nnbvh_build_bvh(const float *triVerts9, uint32_t nTris, int32_t m
     if (!triVerts9 || !nodesOut || !nNodesOut || !orderOut || nTris == 0)
         return SetError(NNBVH_ERR_INVALID, "nnbvh_build_bvh: null argument or empty soup "
                                            "(the reference CHECKs !primitives.empty())");
-    if (splitMethod != NNBVH_SPLIT_SAH && splitMethod != NNBVH_SPLIT_MIDDLE &&
-        splitMethod != NNBVH_SPLIT_EQUAL_COUNTS)
-        return SetError(NNBVH_ERR_INVALID, "nnbvh_build_bvh: split method %d not supported on "
-                                           "the host (HLBVH is built on the device)", splitMethod);
+    if (splitMethod < NNBVH_SPLIT_SAH || splitMethod > NNBVH_SPLIT_EQUAL_COUNTS)
+        return SetError(NNBVH_ERR_INVALID, "nnbvh_build_bvh: unknown split method %d", splitMethod);
     if (nTris > (1u << 30))
         return SetError(NNBVH_ERR_INVALID, "nnbvh_build_bvh: too many triangles");
+    if (splitMethod == NNBVH_SPLIT_HLBVH) {
+        int nt = nThreads > 0 ? nThreads : (int)std::thread::hardware_concurrency();
+        return BuildHLBVHHost(triVerts9, nTris, std::min(255, (int)maxPrimsInNode), nt, nodesOut,
+                              nNodesOut, orderOut);
+    }
     std::vector<Item> items(nTris);
     for (uint32_t i = 0; i < nTris; ++i) {
         // Triangle::Bounds = Union(Bounds3f(p0,p1), p2), shapes.cpp:294-301

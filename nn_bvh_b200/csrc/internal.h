@@ -38,4 +38,16 @@ constexpr uint32_t kTriDegenerate = 1u;  // shapes.cpp:176 reject, evaluated at 
 constexpr uint32_t kTriLast = 2u;        // last primitive of its leaf
 constexpr int kMaxStack = 64;            // cpu/aggregates.cpp:538
 
+
+// ---- HLBVH assembly, shared by the host builder and the device builder (build_host.cpp) ----
+struct TreeletRef {
+    uint32_t start, n;  // range of the Morton-sorted primitive array
+    uint32_t slabAt;    // its nodes are slab[slabAt .. slabAt + nNodes), pre-order, interior
+    uint32_t nNodes;    // offsets relative to slabAt
+};
+// buildUpperSAH (cpu/aggregates.cpp:626-723) over the treelet roots, then the final pre-order
+// layout of flattenBVH (:505-522) written straight into nodesOut.  treelets[] is permuted.
+int AssembleHLBVH(const nnbvh_node *slab, TreeletRef *treelets, uint32_t nTreelets,
+                  nnbvh_node *nodesOut, uint32_t *nNodesOut);
+
 }  // namespace nnbvh

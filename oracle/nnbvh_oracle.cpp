@@ -261,6 +261,175 @@ struct Builder {
         return node;
     }
 
+
+    // ---- HLBVH: cpu/aggregates.cpp:29-82 (RadixSort), 389-449 (buildHLBVH), 451-503 (emitLBVH),
+    //      626-723 (buildUpperSAH); util/math.h:99-119 (LeftShift3 / EncodeMorton3) ----------
+    struct MortonPrim {
+        int primitiveIndex;
+        uint32_t mortonCode;
+    };
+    static uint32_t LeftShift3(uint32_t x) {
+        if (x == (1 << 10)) --x;
+        x = (x | (x << 16)) & 0x30000ffu;
+        x = (x | (x << 8)) & 0x300f00fu;
+        x = (x | (x << 4)) & 0x30c30c3u;
+        x = (x | (x << 2)) & 0x9249249u;
+        return x;
+    }
+    static uint32_t EncodeMorton3(float x, float y, float z) {
+        return (LeftShift3((uint32_t)z) << 2) | (LeftShift3((uint32_t)y) << 1) | LeftShift3((uint32_t)x);
+    }
+    static void RadixSort(std::vector<MortonPrim> *v) {
+        std::vector<MortonPrim> temp(v->size());
+        const int bitsPerPass = 6, nBits = 30, nPasses = nBits / bitsPerPass;
+        for (int pass = 0; pass < nPasses; ++pass) {
+            int lowBit = pass * bitsPerPass;
+            std::vector<MortonPrim> &in = (pass & 1) ? temp : *v;
+            std::vector<MortonPrim> &out = (pass & 1) ? *v : temp;
+            const int nBuckets = 1 << bitsPerPass, bitMask = nBuckets - 1;
+            int bucketCount[1 << 6] = {0};
+            for (const MortonPrim &mp : in) ++bucketCount[(mp.mortonCode >> lowBit) & bitMask];
+            int outIndex[1 << 6];
+            outIndex[0] = 0;
+            for (int i = 1; i < nBuckets; ++i) outIndex[i] = outIndex[i - 1] + bucketCount[i - 1];
+            for (const MortonPrim &mp : in) out[outIndex[(mp.mortonCode >> lowBit) & bitMask]++] = mp;
+        }
+        if (nPasses & 1) std::swap(*v, temp);
+    }
+
+    BuildNode *NewNode() {
+        BuildNode *n = new BuildNode();
+        pool.push_back(n);
+        ++totalNodes;
+        return n;
+    }
+
+    BuildNode *EmitLBVH(const std::vector<BuildPrim> &prims, MortonPrim *mp, int n, int bitIndex) {
+        if (bitIndex == -1 || n < maxPrimsInNode) {
+            BuildNode *node = NewNode();
+            Box bounds;
+            int first = orderedPrimsOffset;
+            orderedPrimsOffset += n;
+            for (int i = 0; i < n; ++i) {
+                orderOut[first + i] = mp[i].primitiveIndex;
+                bounds = Union(bounds, prims[mp[i].primitiveIndex].bounds);
+            }
+            node->firstPrimOffset = first;
+            node->nPrimitives = n;
+            node->bounds = bounds;
+            node->children[0] = node->children[1] = nullptr;
+            return node;
+        }
+        uint32_t mask = 1u << bitIndex;
+        if ((mp[0].mortonCode & mask) == (mp[n - 1].mortonCode & mask))
+            return EmitLBVH(prims, mp, n, bitIndex - 1);
+        // FindInterval (util/math.h:518-534): last index in [0, n-2] whose predicate holds
+        int size = n - 2, first = 1;
+        while (size > 0) {
+            int half = size >> 1, middle = first + half;
+            bool pred = (mp[0].mortonCode & mask) == (mp[middle].mortonCode & mask);
+            first = pred ? middle + 1 : first;
+            size = pred ? size - (half + 1) : half;
+        }
+        int splitOffset = std::min(std::max(first - 1, 0), n - 2) + 1;
+        BuildNode *node = NewNode();   // created BEFORE its children (pre-order slot in the treelet)
+        BuildNode *c0 = EmitLBVH(prims, mp, splitOffset, bitIndex - 1);
+        BuildNode *c1 = EmitLBVH(prims, mp + splitOffset, n - splitOffset, bitIndex - 1);
+        node->children[0] = c0;
+        node->children[1] = c1;
+        node->bounds = Union(c0->bounds, c1->bounds);
+        node->splitAxis = bitIndex % 3;
+        node->nPrimitives = 0;
+        return node;
+    }
+
+    static float SurfaceArea(const Box &b) {
+        float dx = b.mx[0] - b.mn[0], dy = b.mx[1] - b.mn[1], dz = b.mx[2] - b.mn[2];
+        return 2 * (dx * dy + dx * dz + dy * dz);
+    }
+
+    BuildNode *BuildUpperSAH(std::vector<BuildNode *> &roots, int start, int end) {
+        int nNodes = end - start;
+        if (nNodes == 1) return roots[start];
+        BuildNode *node = NewNode();
+        Box bounds, cb;
+        for (int i = start; i < end; ++i) bounds = Union(bounds, roots[i]->bounds);
+        for (int i = start; i < end; ++i) {
+            float c[3];
+            for (int k = 0; k < 3; ++k) c[k] = (roots[i]->bounds.mn[k] + roots[i]->bounds.mx[k]) * 0.5f;
+            cb = Union(cb, c);
+        }
+        float ex = cb.mx[0] - cb.mn[0], ey = cb.mx[1] - cb.mn[1], ez = cb.mx[2] - cb.mn[2];
+        int dim = (ex > ey && ex > ez) ? 0 : (ey > ez ? 1 : 2);   // MaxDimension, vecmath.h:1307-1315
+        const int nBuckets = 12;
+        auto bucketOf = [&](const BuildNode *nd) {
+            float centroid = (nd->bounds.mn[dim] + nd->bounds.mx[dim]) * 0.5f;
+            int b = nBuckets * ((centroid - cb.mn[dim]) / (cb.mx[dim] - cb.mn[dim]));
+            return b == nBuckets ? nBuckets - 1 : b;
+        };
+        int count[12] = {0};
+        Box bb[12];
+        for (int i = start; i < end; ++i) {
+            int b = bucketOf(roots[i]);
+            count[b]++;
+            bb[b] = Union(bb[b], roots[i]->bounds);
+        }
+        float cost[11];
+        for (int i = 0; i < nBuckets - 1; ++i) {
+            Box b0, b1;
+            int c0 = 0, c1 = 0;
+            for (int j = 0; j <= i; ++j) { b0 = Union(b0, bb[j]); c0 += count[j]; }
+            for (int j = i + 1; j < nBuckets; ++j) { b1 = Union(b1, bb[j]); c1 += count[j]; }
+            cost[i] = .125f + (c0 * SurfaceArea(b0) + c1 * SurfaceArea(b1)) / SurfaceArea(bounds);
+        }
+        float minCost = cost[0];
+        int minBucket = 0;
+        for (int i = 1; i < nBuckets - 1; ++i)
+            if (cost[i] < minCost) { minCost = cost[i]; minBucket = i; }
+        BuildNode **pmid = std::partition(&roots[start], &roots[end - 1] + 1,
+                                          [&](const BuildNode *nd) { return bucketOf(nd) <= minBucket; });
+        int mid = (int)(pmid - &roots[0]);
+        BuildNode *c0 = BuildUpperSAH(roots, start, mid);
+        BuildNode *c1 = BuildUpperSAH(roots, mid, end);
+        node->children[0] = c0;
+        node->children[1] = c1;
+        node->bounds = Union(c0->bounds, c1->bounds);
+        node->splitAxis = dim;
+        node->nPrimitives = 0;
+        return node;
+    }
+
+    BuildNode *BuildHLBVH(const std::vector<BuildPrim> &prims) {
+        Box bounds;
+        for (const BuildPrim &p : prims) {
+            float c[3];
+            p.Centroid(c);
+            bounds = Union(bounds, c);
+        }
+        std::vector<MortonPrim> mp(prims.size());
+        for (size_t i = 0; i < prims.size(); ++i) {
+            float c[3], o[3];
+            prims[i].Centroid(c);
+            for (int k = 0; k < 3; ++k) {   // Bounds3::Offset, vecmath.h:1323-1330
+                o[k] = c[k] - bounds.mn[k];
+                if (bounds.mx[k] > bounds.mn[k]) o[k] /= bounds.mx[k] - bounds.mn[k];
+                o[k] = o[k] * 1024;
+            }
+            mp[i].primitiveIndex = (int)prims[i].primitiveIndex;
+            mp[i].mortonCode = EncodeMorton3(o[0], o[1], o[2]);
+        }
+        RadixSort(&mp);
+        std::vector<BuildNode *> roots;
+        const uint32_t mask = 0x3ffc0000u;   // 0b00111111111111000000000000000000
+        for (size_t start = 0, end = 1; end <= mp.size(); ++end) {
+            if (end == mp.size() || ((mp[start].mortonCode & mask) != (mp[end].mortonCode & mask))) {
+                roots.push_back(EmitLBVH(prims, &mp[start], (int)(end - start), 29 - 12));
+                start = end;
+            }
+        }
+        return BuildUpperSAH(roots, 0, (int)roots.size());
+    }
+
     // cpu/aggregates.cpp:505-522
     int Flatten(const BuildNode *node, nnbvh_oracle_node *nodes, int *offset) {
         nnbvh_oracle_node *ln = &nodes[*offset];
@@ -539,7 +708,7 @@ extern "C" {
 int64_t nnbvh_oracle_build(const float *triVerts9, int32_t nTris, int32_t maxPrimsInNode,
                            int32_t splitMethod, nnbvh_oracle_node *nodesOut,
                            int32_t *orderOut) {
-    if (splitMethod == NNBVH_ORACLE_HLBVH || nTris <= 0)
+    if (nTris <= 0)
         return -1;
     Builder b;
     b.maxPrimsInNode = std::min(255, maxPrimsInNode);  // aggregates.cpp:142
@@ -558,7 +727,8 @@ int64_t nnbvh_oracle_build(const float *triVerts9, int32_t nTris, int32_t maxPri
         prims[i].primitiveIndex = (size_t)i;
         prims[i].bounds = bb;
     }
-    BuildNode *root = b.BuildRecursive(prims.data(), prims.size());
+    BuildNode *root = splitMethod == NNBVH_ORACLE_HLBVH ? b.BuildHLBVH(prims)
+                                                        : b.BuildRecursive(prims.data(), prims.size());
     int offset = 0;
     b.Flatten(root, nodesOut, &offset);
     return offset;

@@ -36,7 +36,7 @@ def reference():
 @pytest.fixture(scope="session")
 def golden():
     return {n: np.load(os.path.join(GOLDEN, n + ".npz"))
-            for n in ("tri_vectors", "box_vectors", "scene_small")}
+            for n in ("tri_vectors", "box_vectors", "scene_small", "hlbvh")}
 
 
 @pytest.fixture(scope="session", autouse=True)

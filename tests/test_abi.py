@@ -61,8 +61,36 @@ def test_builder_edge_cases():
     assert len(nodes) == 1 and nodes[0]["nPrimitives"] == 7
     with pytest.raises(nb.NnbvhError):
         nb.build_bvh(np.zeros((0, 9), np.float32), 4, "sah")
-    with pytest.raises(nb.NnbvhError):
-        nb.build_bvh(one, 4, "hlbvh")
+    nodes, order = nb.build_bvh(one, 4, "hlbvh")   # one treelet, one leaf
+    assert len(nodes) == 1 and nodes[0]["nPrimitives"] == 1 and order[0] == 0
+    # identical primitives share one Morton code: a single leaf however large maxPrims is not
+    # reached by bit splits (emitLBVH bitIndex == -1, aggregates.cpp:458)
+    nodes, _ = nb.build_bvh(same, 4, "hlbvh")
+    assert len(nodes) == 1 and nodes[0]["nPrimitives"] == 7
+
+
+@pytest.mark.parametrize("name,mp", [("small4", 4), ("soup4", 4), ("soup1", 1), ("soup255", 255)])
+def test_host_hlbvh_matches_reference_golden(golden, name, mp):
+    """The host HLBVH builder against trees the unmodified reference produced
+    (tools/make_golden.py: hlbvh), byte for byte, at any thread count."""
+    import nn_bvh_b200 as nb
+    g = golden["hlbvh"]
+    tris = golden["scene_small"]["tris"] if name == "small4" else g["soup"]
+    for threads in (1, 5):
+        nodes, order = nb.build_bvh(tris, mp, "hlbvh", threads=threads)
+        assert np.array_equal(nodes.view(np.uint32).reshape(-1, 8), g[f"{name}_nodes"])
+        assert np.array_equal(order, g[f"{name}_order"].astype(np.uint32))
+    assert nb.tree_stack_depth(nodes) <= 64
+
+
+def test_host_hlbvh_matches_oracle_large(oracle):
+    import nn_bvh_b200 as nb
+    rng = np.random.default_rng(6)
+    tris = soup(rng, 250_000, 0.004)
+    nodes, order = nb.build_bvh(tris, 4, "hlbvh")
+    on, oo = oracle.build_bvh(tris, 4, "hlbvh")
+    assert np.array_equal(nodes.view(np.uint32).reshape(-1, 8), on)
+    assert np.array_equal(order, oo.astype(np.uint32))
 
 
 def test_stack_depth_of_chain():

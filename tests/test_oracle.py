@@ -42,11 +42,28 @@ def test_oracle_scene_golden(oracle, golden, split):
     assert (int(nv.sum()), int(tt.sum()), int(nvp.sum()), int(ttp.sum())) == tuple(st)
 
 
+HLBVH_CASES = [("small4", 4), ("soup4", 4), ("soup1", 1), ("soup255", 255)]
+
+
+@pytest.mark.parametrize("name,mp", HLBVH_CASES)
+def test_oracle_hlbvh_golden(oracle, golden, name, mp):
+    """buildHLBVH / emitLBVH / buildUpperSAH, cpu/aggregates.cpp:389-503, 626-723."""
+    g = golden["hlbvh"]
+    tris = golden["scene_small"]["tris"] if name == "small4" else g["soup"]
+    nodes, order = oracle.build_bvh(tris, mp, "hlbvh")
+    assert np.array_equal(nodes, g[f"{name}_nodes"])
+    assert np.array_equal(order, g[f"{name}_order"])
+    if name == "small4":
+        rays = golden["scene_small"]["rays"]
+        assert np.array_equal(oracle.intersect(nodes, tris[order], rays), g["small4_hits"])
+        assert np.array_equal(oracle.intersect_p(nodes, tris[order], rays), g["small4_occ"])
+
+
 def test_oracle_vs_reference_live(oracle, reference):
     """Fresh seeded inputs through both (only where oracle/_ref exists)."""
     rng = np.random.default_rng(99)
     for T, s, mp, split in [(5000, 0.03, 4, "sah"), (5000, 0.03, 1, "sah"), (4000, 0.05, 8, "middle"),
-                            (4000, 0.05, 4, "equal")]:
+                            (4000, 0.05, 4, "equal"), (30000, 0.004, 4, "hlbvh"), (37, 0.3, 1, "hlbvh")]:
         tris = soup(rng, T, s)
         sc = reference.scene(tris, mp, split)
         rn, ro = reference.export(sc, T)

@@ -166,10 +166,35 @@ def scene_small(ref, rng):
     np.savez_compressed(os.path.join(OUT, "scene_small.npz"), **out)
 
 
+def hlbvh(ref):
+    """HLBVH trees of the unmodified reference (cpu/aggregates.cpp:389-503, 626-723): the
+    scene_small triangles (duplicates -> equal Morton codes) and a soup wide enough for a few
+    thousand treelets, at two leaf sizes.  Own seed, own file, so the other goldens stay put."""
+    rng = np.random.default_rng(20261105)
+    small = np.load(os.path.join(OUT, "scene_small.npz"))
+    c = rng.random((12000, 1, 3), dtype=np.float32)
+    soup = as_pbrt_stores((c + 0.01 * (rng.random((12000, 3, 3), dtype=np.float32) * 2 - 1)).reshape(-1, 9))
+    out = {"soup": soup}
+    for name, tris, mp in (("small4", small["tris"], 4), ("soup4", soup, 4), ("soup1", soup, 1),
+                           ("soup255", soup, 255)):
+        sc = ref.scene(tris, mp, "hlbvh")
+        nodes, order = ref.export(sc, len(tris))
+        out[f"{name}_nodes"], out[f"{name}_order"] = nodes, order
+        if name == "small4":
+            out["small4_hits"] = ref.intersect(sc, small["rays"], parallel=False)
+            out["small4_occ"] = ref.intersect_p(sc, small["rays"], parallel=False)
+        print("hlbvh", name, "nodes", len(nodes))
+    np.savez_compressed(os.path.join(OUT, "hlbvh.npz"), **out)
+
+
 if __name__ == "__main__":
     os.makedirs(OUT, exist_ok=True)
     ref = Reference(threads=1)
+    if "--only-hlbvh" in sys.argv:
+        hlbvh(ref)
+        sys.exit(0)
     rng = np.random.default_rng(20261104)
     tri_vectors(ref, rng)
     box_vectors(ref, rng)
     scene_small(ref, rng)
+    hlbvh(ref)
