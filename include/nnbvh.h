@@ -109,6 +109,15 @@ void nnbvh_destroy(nnbvh_engine *e);
  * NULL = the engine's own stream. */
 int nnbvh_set_stream(nnbvh_engine *e, void *cudaStream);
 
+/* nnbvh_build_bvh(..., NNBVH_SPLIT_HLBVH, ...) with the data-parallel stages of
+ * BVHAggregate::buildHLBVH (cpu/aggregates.cpp:389-449: primitive and centroid
+ * bounds, Morton codes, the radix sort, treelet emission) run on the engine's GPU;
+ * buildUpperSAH (:626-723) over the <= 4096 treelet roots stays on the host.
+ * Same arguments, byte-identical output.  triVerts9 is a HOST pointer. */
+int nnbvh_build_hlbvh_device(nnbvh_engine *e, const float *triVerts9, uint32_t nTris,
+                             uint32_t maxPrimsInNode, nnbvh_node *nodesOut,
+                             uint32_t *nNodesOut, uint32_t *orderOut);
+
 /* Replaces the reference's pointer graph (Primitive -> SimplePrimitive ->
  * Triangle -> TriangleMesh, cpu/primitive.cpp:96-109, shapes.cpp:320-327) by
  * device arrays.  nodes: the flattened tree; orderedTriVerts9: nPrims*9 floats in

@@ -8,4 +8,5 @@ Package layout (only what the hot path needs):
   rays.py       deterministic ray batches for those configs
 """
 from .capi import HIT_DTYPE, MISS, NODE_DTYPE, RAY_DTYPE, NnbvhError  # noqa: F401
-from .aggregate import GPUBVHAggregate, build_bvh, make_rays, tree_stack_depth  # noqa: F401
+from .aggregate import (GPUBVHAggregate, build_bvh, build_hlbvh_device, make_rays,  # noqa: F401
+                        tree_stack_depth)  # noqa: F401

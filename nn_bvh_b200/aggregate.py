@@ -35,6 +35,33 @@ def build_bvh(tris9: np.ndarray, max_prims_in_node: int = 4, split_method: str =
     return nodes[:n.value].copy(), order
 
 
+def build_hlbvh_device(tris9: np.ndarray, max_prims_in_node: int = 4, *, engine=None,
+                       device: int = -1):
+    """build_bvh(..., "hlbvh") with Morton codes, the radix sort and treelet emission on the GPU
+    (libnnbvh nnbvh_build_hlbvh_device); byte-identical to the host builder.  `engine`: an engine
+    handle to run on (a temporary one is created otherwise).  Returns (nodes, order, device_ms)."""
+    L = capi.lib()
+    tris9 = np.ascontiguousarray(tris9, dtype=np.float32).reshape(-1, 9)
+    T = tris9.shape[0]
+    own = engine is None
+    if own:
+        engine = ctypes.c_void_p()
+        opts = capi.Options(device=device, kernel=capi.KERNEL_AUTO, smem_top_nodes=-1)
+        capi.check(L.nnbvh_create(ctypes.byref(opts), ctypes.byref(engine)))
+    try:
+        nodes = np.zeros(max(2 * T - 1, 1), dtype=NODE_DTYPE)
+        order = np.zeros(T, dtype=np.uint32)
+        n = ctypes.c_uint32(0)
+        capi.check(L.nnbvh_build_hlbvh_device(engine, capi.ptr(tris9), T, max_prims_in_node,
+                                              capi.ptr(nodes), ctypes.byref(n), capi.ptr(order)))
+        ms = ctypes.c_float(0)
+        capi.check(L.nnbvh_last_kernel_ms(engine, ctypes.byref(ms)))
+    finally:
+        if own:
+            L.nnbvh_destroy(engine)
+    return nodes[:n.value].copy(), order, ms.value
+
+
 def tree_stack_depth(nodes: np.ndarray) -> int:
     d = ctypes.c_uint32(0)
     capi.check(capi.lib().nnbvh_tree_stack_depth(capi.ptr(nodes), len(nodes), ctypes.byref(d)))
@@ -62,6 +89,10 @@ class GPUBVHAggregate:
         """Either tris9 (a soup to build over, like the reference ctor) or a ready
         flattened tree: nodes + ordered_tris9 (e.g. an exported NN-split tree)."""
         L = capi.lib()
+        opts = capi.Options(device=device, kernel=kernel, smem_top_nodes=smem_top_nodes)
+        h = ctypes.c_void_p()
+        capi.check(L.nnbvh_create(ctypes.byref(opts), ctypes.byref(h)))
+        self._h = h
         if nodes is None:
             if tris9 is None or len(tris9) == 0:
                 # The reference CHECK(!primitives.empty())s; an empty aggregate here misses.
@@ -70,15 +101,14 @@ class GPUBVHAggregate:
                 order = np.zeros(0, dtype=np.uint32)
             else:
                 tris9 = np.ascontiguousarray(tris9, dtype=np.float32).reshape(-1, 9)
-                nodes, order = build_bvh(tris9, max_prims_in_node, split_method)
+                if split_method == "hlbvh":   # the one builder with device stages
+                    nodes, order, _ = build_hlbvh_device(tris9, max_prims_in_node, engine=h)
+                else:
+                    nodes, order = build_bvh(tris9, max_prims_in_node, split_method)
                 ordered_tris9 = tris9[order]
         self.nodes = np.ascontiguousarray(nodes).view(NODE_DTYPE).reshape(-1)
         self.ordered_tris9 = np.ascontiguousarray(ordered_tris9, dtype=np.float32).reshape(-1, 9)
         self.order = order  # ordered prim -> caller's primitive id (None = identity)
-        opts = capi.Options(device=device, kernel=kernel, smem_top_nodes=smem_top_nodes)
-        h = ctypes.c_void_p()
-        capi.check(L.nnbvh_create(ctypes.byref(opts), ctypes.byref(h)))
-        self._h = h
         capi.check(L.nnbvh_upload_scene(h, capi.ptr(self.nodes), len(self.nodes),
                                         capi.ptr(self.ordered_tris9), len(self.ordered_tris9)))
 

@@ -31,7 +31,7 @@ SYMBOLS = [
     "nnbvh_set_stream", "nnbvh_upload_scene", "nnbvh_intersect_closest", "nnbvh_intersect_any",
     "nnbvh_intersect_closest_soa", "nnbvh_intersect_any_soa", "nnbvh_intersect_counters",
     "nnbvh_last_kernel_ms", "nnbvh_launch_count", "nnbvh_test_triangles", "nnbvh_test_boxes",
-    "nnbvh_last_error", "nnbvh_version",
+    "nnbvh_last_error", "nnbvh_version", "nnbvh_build_hlbvh_device",
 ]
 
 
@@ -60,6 +60,7 @@ def lib() -> ctypes.CDLL:
     vp, u32, u64, i32 = ctypes.c_void_p, ctypes.c_uint32, ctypes.c_uint64, ctypes.c_int32
     L.nnbvh_build_bvh.argtypes = [vp, u32, i32, i32, i32, vp, vp, vp]
     L.nnbvh_tree_stack_depth.argtypes = [vp, u32, vp]
+    L.nnbvh_build_hlbvh_device.argtypes = [vp, vp, u32, u32, vp, vp, vp]
     L.nnbvh_create.argtypes = [vp, vp]
     L.nnbvh_destroy.argtypes = [vp]
     L.nnbvh_destroy.restype = None

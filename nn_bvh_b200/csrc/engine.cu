@@ -19,6 +19,7 @@
 #include "binning.cuh"
 #include "traverse.cuh"
 #include "spec.cuh"
+#include "hlbvh.cuh"
 
 namespace nnbvh {
 
@@ -889,4 +890,114 @@ extern "C" int nnbvh_test_boxes(nnbvh_engine *e, const nnbvh_ray *rays, const fl
     CU(cudaMemcpy(hit, dH, n, cudaMemcpyDeviceToHost));
     cudaFree(dR); cudaFree(dB); cudaFree(dH);
     return NNBVH_OK;
+}
+
+// ---------------------------------------------------------------------------
+// HLBVH with the data-parallel stages on the device (hlbvh.cuh)
+// ---------------------------------------------------------------------------
+namespace {
+struct HlbvhBufs {
+    float *tris = nullptr, *box = nullptr;
+    uint32_t *u32 = nullptr;  // one arena, see the layout in nnbvh_build_hlbvh_device
+    nnbvh_node *nodes = nullptr;
+    ~HlbvhBufs() {
+        cudaFree(tris); cudaFree(box); cudaFree(u32); cudaFree(nodes);
+    }
+};
+}  // namespace
+
+extern "C" int nnbvh_build_hlbvh_device(nnbvh_engine *e, const float *triVerts9, uint32_t nTris,
+                                        uint32_t maxPrimsInNode, nnbvh_node *nodesOut,
+                                        uint32_t *nNodesOut, uint32_t *orderOut) {
+    if (!e) return SetError(NNBVH_ERR_INVALID, "nnbvh_build_hlbvh_device: engine is NULL");
+    if (!triVerts9 || !nodesOut || !nNodesOut || !orderOut)
+        return SetError(NNBVH_ERR_INVALID, "nnbvh_build_hlbvh_device: NULL argument");
+    if (nTris == 0) return SetError(NNBVH_ERR_INVALID, "nnbvh_build_hlbvh_device: no primitives");
+    if (nTris > (1u << 30))
+        return SetError(NNBVH_ERR_INVALID, "nnbvh_build_hlbvh_device: too many primitives");
+    const uint32_t maxLeaf = std::min<uint32_t>(255u, maxPrimsInNode);  // aggregates.cpp:149
+    CU(cudaSetDevice(e->device));
+    cudaStream_t st = e->stream;
+    const uint32_t n = nTris;
+    const uint32_t nBlk = (n + 255) / 256, nSortBlk = (n + kSortTile - 1) / kSortTile;
+    const size_t nHist = 256 * (size_t)nSortBlk;
+    const size_t nTiles = (std::max<size_t>(nHist, (size_t)n + 1) + kScanTile - 1) / kScanTile;
+    // layout of the u32 arena
+    size_t at = 0;
+    auto take = [&](size_t k) { size_t r = at; at += (k + 3) & ~(size_t)3; return r; };
+    const size_t oCb = take(8), oHead = take(kMaxTreelets), oStarts = take(kMaxTreelets),
+                 oOffs = take(kMaxTreelets + 1), oCount = take(1), oOv = take(1), oCodeA = take(n),
+                 oCodeB = take(n), oPrimA = take(n), oPrimB = take(n), oHist = take(nHist),
+                 oTile = take(nTiles), oMask = take(n), oLeafN = take(n), oRangeL = take(n),
+                 oS = take((size_t)n + 1), oParent = take(2 * (size_t)n), oVisit = take(2 * (size_t)n);
+    HlbvhBufs b;
+    CU(cudaMalloc(&b.tris, 36 * (size_t)n));
+    CU(cudaMalloc(&b.box, 24 * (size_t)n));
+    CU(cudaMalloc(&b.u32, 4 * at));
+    CU(cudaMalloc(&b.nodes, sizeof(nnbvh_node) * 2 * (size_t)n));  // a tree over n leaves: < 2n nodes
+    uint32_t *u = b.u32;
+    CU(cudaMemcpyAsync(b.tris, triVerts9, 36 * (size_t)n, cudaMemcpyHostToDevice, st));
+    CU(cudaEventRecord(e->evA, st));
+    CU(cudaMemsetAsync(u + oCb, 0xff, 12, st));
+    CU(cudaMemsetAsync(u + oCb + 3, 0, 12, st));
+    CU(cudaMemsetAsync(u + oHead, 0xff, 4 * kMaxTreelets, st));
+    CU(cudaMemsetAsync(u + oOv, 0, 4, st));
+    CU(cudaMemsetAsync(u + oMask, 0, 4 * (size_t)n, st));
+    CU(cudaMemsetAsync(u + oVisit, 0, 8 * (size_t)n, st));
+    PrimBoundsKernel<<<nBlk, 256, 0, st>>>(b.tris, n, b.box, u + oCb);
+    MortonKernel<<<nBlk, 256, 0, st>>>(b.box, n, u + oCb, u + oCodeA, u + oPrimA);
+    e->launches += 2;
+    uint32_t *cIn = u + oCodeA, *cOut = u + oCodeB, *pIn = u + oPrimA, *pOut = u + oPrimB;
+    const unsigned nHistTiles = (unsigned)((nHist + kScanTile - 1) / kScanTile);
+    for (int shift = 0; shift < 30; shift += 8) {
+        RadixPassKernel<false><<<nSortBlk, 256, 0, st>>>(cIn, pIn, n, shift, u + oHist, cOut, pOut);
+        BinTileSumKernel<<<nHistTiles, 1024, 0, st>>>(u + oHist, (uint32_t)nHist, u + oTile);
+        BinTileScanKernel<<<nHistTiles, 1024, 0, st>>>(u + oHist, (uint32_t)nHist, u + oTile);
+        RadixPassKernel<true><<<nSortBlk, 256, 0, st>>>(cIn, pIn, n, shift, u + oHist, cOut, pOut);
+        e->launches += 4;
+        std::swap(cIn, cOut);
+        std::swap(pIn, pOut);
+    }
+    TreeletHeadKernel<<<nBlk, 256, 0, st>>>(cIn, n, u + oHead);
+    TreeletListKernel<<<1, 32, 0, st>>>(u + oHead, u + oStarts, u + oCount);
+    LbvhTopologyKernel<<<nBlk, 256, 0, st>>>(cIn, n, maxLeaf, u + oMask, u + oLeafN, u + oRangeL,
+                                             reinterpret_cast<int *>(u + oOv));
+    const unsigned nSTiles = (unsigned)(((size_t)n + 1 + kScanTile - 1) / kScanTile);
+    LbvhCountKernel<<<(n + 1 + 255) / 256, 256, 0, st>>>(u + oMask, n, u + oS);
+    BinTileSumKernel<<<nSTiles, 1024, 0, st>>>(u + oS, n + 1, u + oTile);
+    BinTileScanKernel<<<nSTiles, 1024, 0, st>>>(u + oS, n + 1, u + oTile);
+    LbvhNodesKernel<<<nBlk, 256, 0, st>>>(cIn, n, u + oMask, u + oLeafN, u + oRangeL, u + oS,
+                                          u + oHead, b.nodes, u + oParent);
+    LbvhBoundsKernel<<<nBlk, 256, 0, st>>>(cIn, pIn, b.box, n, u + oMask, u + oLeafN, u + oS,
+                                           u + oHead, u + oParent, u + oVisit, b.nodes);
+    TreeletOffsetsKernel<<<(kMaxTreelets + 1 + 255) / 256, 256, 0, st>>>(u + oStarts, u + oCount,
+                                                                        u + oS, n, u + oOffs);
+    e->launches += 9;
+    CU(cudaGetLastError());
+    CU(cudaEventRecord(e->evB, st));
+    // control block back: count, overflow, then starts and offs
+    uint32_t hCount = 0;
+    int hOv = 0;
+    CU(cudaMemcpyAsync(&hCount, u + oCount, 4, cudaMemcpyDeviceToHost, st));
+    CU(cudaMemcpyAsync(&hOv, u + oOv, 4, cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    CU(cudaEventElapsedTime(&e->lastMs, e->evA, e->evB));
+    if (hOv)
+        return SetError(NNBVH_ERR_INVALID, "nnbvh_build_hlbvh_device: a leaf holds >= 65536 "
+                                           "primitives (the reference CHECKs nPrimitives < 65536)");
+    std::vector<uint32_t> starts(hCount), offs(hCount + 1);
+    CU(cudaMemcpyAsync(starts.data(), u + oStarts, 4 * (size_t)hCount, cudaMemcpyDeviceToHost, st));
+    CU(cudaMemcpyAsync(offs.data(), u + oOffs, 4 * (size_t)(hCount + 1), cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    const uint32_t total = offs[hCount];
+    std::vector<nnbvh_node> dense(total);
+    CU(cudaMemcpyAsync(dense.data(), b.nodes, sizeof(nnbvh_node) * (size_t)total,
+                       cudaMemcpyDeviceToHost, st));
+    CU(cudaMemcpyAsync(orderOut, pIn, 4 * (size_t)n, cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    std::vector<TreeletRef> tr(hCount);
+    for (uint32_t k = 0; k < hCount; ++k)
+        tr[k] = TreeletRef{starts[k], (k + 1 < hCount ? starts[k + 1] : n) - starts[k], offs[k],
+                           offs[k + 1] - offs[k]};
+    return AssembleHLBVH(dense.data(), tr.data(), hCount, nodesOut, nNodesOut);
 }
