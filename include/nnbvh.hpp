@@ -72,19 +72,25 @@ class GPUBVHAggregate {
                     SplitMethod splitMethod = SplitMethod::SAH, int device = -1,
                     int buildThreads = 0) {
         const uint32_t nTris = (uint32_t)(tris9.size() / 9);
+        CreateEngine(device);
         if (nTris) {
             nodes_.resize(2 * (size_t)nTris - 1);
             order_.resize(nTris);
             uint32_t nNodes = 0;
-            Check(nnbvh_build_bvh(tris9.data(), nTris, maxPrimsInNode, (int)splitMethod,
-                                  buildThreads, nodes_.data(), &nNodes, order_.data()));
+            // HLBVH is the builder with device stages (buildHLBVH, cpu/aggregates.cpp:389-449)
+            int rc = splitMethod == SplitMethod::HLBVH
+                         ? nnbvh_build_hlbvh_device(e_, tris9.data(), nTris, (uint32_t)maxPrimsInNode,
+                                                    nodes_.data(), &nNodes, order_.data())
+                         : nnbvh_build_bvh(tris9.data(), nTris, maxPrimsInNode, (int)splitMethod,
+                                           buildThreads, nodes_.data(), &nNodes, order_.data());
+            if (rc != NNBVH_OK) Fail(rc);
             nodes_.resize(nNodes);
             ordered_.resize(9 * (size_t)nTris);
             for (uint32_t i = 0; i < nTris; ++i)
                 for (int k = 0; k < 9; ++k)
                     ordered_[9 * (size_t)i + k] = tris9[9 * (size_t)order_[i] + k];
         }
-        Open(device);
+        Upload();
     }
 
     // A ready flattened tree (e.g. an NN-split tree exported in LinearBVHNode layout).
@@ -163,20 +169,27 @@ class GPUBVHAggregate {
     nnbvh_engine *Handle() const { return e_; }
 
   private:
-    void Open(int device) {
+    void CreateEngine(int device) {
         nnbvh_options o{};
         o.device = device;
         o.kernel = NNBVH_KERNEL_AUTO;
         o.smem_top_nodes = -1;
         Check(nnbvh_create(&o, &e_));
+    }
+    [[noreturn]] void Fail(int rc) {  // constructor failure: the destructor will not run
+        std::string msg = nnbvh_last_error();
+        nnbvh_destroy(e_);
+        e_ = nullptr;
+        throw Error(rc, "libnnbvh: " + msg);
+    }
+    void Upload() {
         int rc = nnbvh_upload_scene(e_, nodes_.data(), (uint32_t)nodes_.size(), ordered_.data(),
                                     (uint32_t)(ordered_.size() / 9));
-        if (rc != NNBVH_OK) {
-            std::string msg = nnbvh_last_error();
-            nnbvh_destroy(e_);
-            e_ = nullptr;
-            throw Error(rc, "libnnbvh: " + msg);
-        }
+        if (rc != NNBVH_OK) Fail(rc);
+    }
+    void Open(int device) {
+        CreateEngine(device);
+        Upload();
     }
 
     std::vector<nnbvh_node> nodes_;

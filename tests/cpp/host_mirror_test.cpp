@@ -15,7 +15,9 @@
 #include "../../include/nnbvh.hpp"
 #include "../../oracle/nnbvh_oracle.h"
 
-int main(int argc, char **argv) {
+using Split = nnbvh::GPUBVHAggregate::SplitMethod;
+
+static int RunCase(Split split, int oracleSplit, const char *name) {
     const uint32_t T = 20000, N = 100000;
     std::mt19937 rng(1234);
     std::uniform_real_distribution<float> U(0.f, 1.f);
@@ -26,12 +28,12 @@ int main(int argc, char **argv) {
             for (int k = 0; k < 3; ++k) tris[9 * (size_t)i + 3 * v + k] = c[k] + 0.02f * (2 * U(rng) - 1);
     }
     try {
-        nnbvh::GPUBVHAggregate agg(tris, 4, nnbvh::GPUBVHAggregate::SplitMethod::SAH);
+        nnbvh::GPUBVHAggregate agg(tris, 4, split);  // HLBVH: built on the device
 
         // the tree must be the reference's, byte for byte
         std::vector<nnbvh_oracle_node> onodes(2 * (size_t)T);
         std::vector<int32_t> oorder(T);
-        int64_t m = nnbvh_oracle_build(tris.data(), (int32_t)T, 4, NNBVH_ORACLE_SAH, onodes.data(), oorder.data());
+        int64_t m = nnbvh_oracle_build(tris.data(), (int32_t)T, 4, oracleSplit, onodes.data(), oorder.data());
         if (m != (int64_t)agg.Nodes().size() ||
             std::memcmp(onodes.data(), agg.Nodes().data(), sizeof(nnbvh_node) * (size_t)m) != 0) {
             std::printf("FAIL: tree differs from the oracle's (%lld vs %zu nodes)\n", (long long)m, agg.Nodes().size());
@@ -76,11 +78,17 @@ int main(int argc, char **argv) {
                 if (h->prim != w[0] || std::memcmp(&h->tHit, &w[1], 16) != 0) { std::printf("FAIL: single-ray record %u\n", i); return 1; }
             }
         }
-        std::printf("PASS: %u triangles, %zu nodes, %u rays bit-exact vs oracle (%u/64 single rays hit), kernel %.3f ms\n",
-                    T, agg.Nodes().size(), N, nHit, agg.LastKernelMs());
+        std::printf("PASS %s: %u triangles, %zu nodes, %u rays bit-exact vs oracle (%u/64 single rays hit), kernel %.3f ms\n",
+                    name, T, agg.Nodes().size(), N, nHit, agg.LastKernelMs());
         return 0;
     } catch (const nnbvh::Error &e) {
         std::printf("nnbvh::Error %d: %s\n", e.code, e.what());
         return e.code == NNBVH_ERR_CUDA ? 3 : 2;
     }
+}
+
+int main(int, char **) {
+    int rc = RunCase(Split::SAH, NNBVH_ORACLE_SAH, "sah");
+    if (rc) return rc;
+    return RunCase(Split::HLBVH, NNBVH_ORACLE_HLBVH, "hlbvh");
 }
