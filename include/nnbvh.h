@@ -68,10 +68,8 @@ typedef enum nnbvh_kernel {
     NNBVH_KERNEL_BASIC = 1,  /* one thread per ray over the 32-byte nodes, statement
                                 order of cpu/aggregates.cpp:529-624 */
     NNBVH_KERNEL_WIDE = 2,   /* persistent warps over 64-byte two-child nodes (first version) */
-    NNBVH_KERNEL_STEP = 3,   /* persistent warps, one straight-line step per lane per
+    NNBVH_KERNEL_STEP = 3    /* persistent warps, one straight-line step per lane per
                                 iteration, 256-bit node loads (the default) */
-    NNBVH_KERNEL_SPEC = 4    /* STEP + one postponed leaf per lane (speculative traversal;
-                                measured slower on B200, kept for A/B runs) */
 } nnbvh_kernel;
 
 typedef struct nnbvh_options {
@@ -117,6 +115,18 @@ int nnbvh_set_stream(nnbvh_engine *e, void *cudaStream);
 int nnbvh_build_hlbvh_device(nnbvh_engine *e, const float *triVerts9, uint32_t nTris,
                              uint32_t maxPrimsInNode, nnbvh_node *nodesOut,
                              uint32_t *nNodesOut, uint32_t *orderOut);
+
+/* Device time of the traversal launches alone (fast-slab launch + exact launch over the
+ * deferred rays) of the last device-pointer batch: nnbvh_last_kernel_ms minus the ray
+ * ordering pre-pass.  Blocks until that batch has finished. */
+int nnbvh_last_traversal_ms(nnbvh_engine *e, float *ms);
+
+/* Diagnostic: lane-occupancy counters of the traversal kernel, accumulated since the
+ * last call, when the engine was created with NNBVH_STEP_STATS=1 in the environment
+ * (a counting instantiation of the kernel runs then).  out8: phase-A iterations, lanes
+ * at a node, lanes parked at a leaf, lanes without a ray, phase-B passes, lanes parked
+ * there, lanes that ran a triangle test, refills (all summed over warps). */
+int nnbvh_debug_step_stats(nnbvh_engine *e, uint64_t *out8);
 
 /* Replaces the reference's pointer graph (Primitive -> SimplePrimitive ->
  * Triangle -> TriangleMesh, cpu/primitive.cpp:96-109, shapes.cpp:320-327) by

@@ -197,6 +197,20 @@ class GPUBVHAggregate:
         capi.check(capi.lib().nnbvh_last_kernel_ms(self._h, ctypes.byref(ms)))
         return ms.value
 
+    def last_traversal_ms(self) -> float:
+        """Device time of the traversal launches of the last device-pointer batch (no pre-pass)."""
+        ms = ctypes.c_float(0)
+        capi.check(capi.lib().nnbvh_last_traversal_ms(self._h, ctypes.byref(ms)))
+        return ms.value
+
+    def step_stats(self) -> dict:
+        """Lane-occupancy counters of the traversal kernel (engine created under NNBVH_STEP_STATS=1)."""
+        out = (ctypes.c_uint64 * 8)()
+        capi.check(capi.lib().nnbvh_debug_step_stats(self._h, out))
+        names = ("iters_a", "lanes_node", "lanes_parked", "lanes_empty", "iters_b", "lanes_b_parked",
+                 "lanes_b_testing", "refills")
+        return dict(zip(names, (int(v) for v in out)))
+
     def launch_count(self) -> int:
         c = ctypes.c_uint64(0)
         capi.check(capi.lib().nnbvh_launch_count(self._h, ctypes.byref(c)))

@@ -16,7 +16,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(HERE, "libnnbvh.so")
 
 MISS = 0xFFFFFFFF
-KERNEL_AUTO, KERNEL_BASIC, KERNEL_WIDE, KERNEL_STEP, KERNEL_SPEC = 0, 1, 2, 3, 4
+KERNEL_AUTO, KERNEL_BASIC, KERNEL_WIDE, KERNEL_STEP = 0, 1, 2, 3
 SPLIT = {"sah": 0, "hlbvh": 1, "middle": 2, "equal": 3}
 
 NODE_DTYPE = np.dtype([("bounds", "<f4", (6,)), ("offset", "<i4"), ("nPrimitives", "<u2"),
@@ -31,7 +31,7 @@ SYMBOLS = [
     "nnbvh_set_stream", "nnbvh_upload_scene", "nnbvh_intersect_closest", "nnbvh_intersect_any",
     "nnbvh_intersect_closest_soa", "nnbvh_intersect_any_soa", "nnbvh_intersect_counters",
     "nnbvh_last_kernel_ms", "nnbvh_launch_count", "nnbvh_test_triangles", "nnbvh_test_boxes",
-    "nnbvh_last_error", "nnbvh_version", "nnbvh_build_hlbvh_device",
+    "nnbvh_last_error", "nnbvh_version", "nnbvh_build_hlbvh_device", "nnbvh_debug_step_stats", "nnbvh_last_traversal_ms",
 ]
 
 
@@ -73,6 +73,8 @@ def lib() -> ctypes.CDLL:
     L.nnbvh_intersect_counters.argtypes = [vp, vp, u64, i32, vp, vp, vp, vp]
     L.nnbvh_last_kernel_ms.argtypes = [vp, vp]
     L.nnbvh_launch_count.argtypes = [vp, vp]
+    L.nnbvh_debug_step_stats.argtypes = [vp, vp]
+    L.nnbvh_last_traversal_ms.argtypes = [vp, vp]
     L.nnbvh_test_triangles.argtypes = [vp, vp, vp, u64, vp, vp]
     L.nnbvh_test_boxes.argtypes = [vp, vp, vp, u64, vp]
     L.nnbvh_last_error.restype = ctypes.c_char_p

@@ -10,9 +10,12 @@
 // the permutation and writes each result back to the ray's ORIGINAL slot, so the
 // caller sees exactly the reference's semantics: hits[i] belongs to rays[i].
 //
-// One-pass counting sort: keys + histogram (warp-aggregated atomics) -> exclusive
-// scan -> scatter.  The order of rays inside a bin is arbitrary (atomic arrival
-// order); no result depends on it.
+// Keys (BinKeyKernel) -> stable LSD radix sort of (key, ray index), 8 bits per pass
+// (RadixCount/RadixScatterKernel in hlbvh.cuh, the HLBVH builder's sort) -> the permutation.  A
+// device-side flag skips the sort for batches that arrive coherent (camera rays):
+// BinSampleKernel measures the number of distinct keys per warp of consecutive rays
+// on a sample of the batch; every later kernel of the pre-pass returns at once when
+// the flag is 0, and the traversal kernel then ignores the permutation.
 #pragma once
 
 #include <cuda_runtime.h>
@@ -63,29 +66,52 @@ __device__ __forceinline__ uint32_t RayKey(const BinParams &bp, const RayRegs &r
     return (cell << (2 * bp.dirBits)) | dir;
 }
 
-// keys[i] and the bin histogram.  One atomic per distinct key per warp.
-__global__ void __launch_bounds__(256)
-BinCountKernel(BinParams bp, RayInput in, uint64_t n, uint32_t *__restrict__ keys,
-               uint32_t *__restrict__ hist) {
-    uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+// How incoherent the batch already is: kBinSamples warps' worth of consecutive rays, spread evenly
+// over the batch; each counts the different keys among its 32 rays (1 = all in one cell, 32 =
+// all different).  stats[0] accumulates the counts, stats[1] the number of warps sampled.
+constexpr int kBinSamples = 256;
+
+__global__ void __launch_bounds__(32)
+BinSampleKernel(BinParams bp, RayInput in, uint64_t n, unsigned long long *__restrict__ stats) {
+    const uint64_t warps = (n + 31) / 32;
+    const uint64_t w = warps * blockIdx.x / kBinSamples;  // distinct for warps >= kBinSamples
+    if (blockIdx.x > 0 && w == warps * (blockIdx.x - 1) / kBinSamples) return;
+    const uint64_t i = w * 32 + threadIdx.x;
     const bool valid = i < n;
     uint32_t key = 0xffffffffu;
-    if (valid) {
-        RayRegs r = LoadRay(in, i);
-        key = RayKey(bp, r);
-        keys[i] = key;
+    if (valid) key = RayKey(bp, LoadRay(in, i));
+    const unsigned peers = __match_any_sync(0xffffffffu, key);
+    const unsigned leaders =
+        __ballot_sync(0xffffffffu, valid && (unsigned)(__ffs(peers) - 1) == threadIdx.x);
+    if (threadIdx.x == 0) {
+        atomicAdd(stats, (unsigned long long)__popc(leaders));
+        atomicAdd(stats + 1, 1ull);
     }
-    const unsigned lane = threadIdx.x & 31;
-    unsigned peers = __match_any_sync(0xffffffffu, key);
-    if (valid && (unsigned)(__ffs(peers) - 1) == lane) atomicAdd(hist + key, (uint32_t)__popc(peers));
+}
+
+// One thread: sort only batches whose warps are incoherent as they come.  *flag = 1 when the
+// average sampled warp holds more than `threshold` distinct keys (or when forced).
+__global__ void BinDecideKernel(const unsigned long long *__restrict__ stats, uint32_t threshold,
+                                uint32_t force, uint32_t *__restrict__ flag) {
+    *flag = (force || stats[0] > stats[1] * threshold) ? 1u : 0u;
+}
+
+__global__ void __launch_bounds__(256)
+BinKeyKernel(BinParams bp, RayInput in, uint64_t n, uint32_t *__restrict__ keys,
+             const uint32_t *__restrict__ enable) {
+    if (*enable == 0u) return;
+    const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) keys[i] = RayKey(bp, LoadRay(in, i));
 }
 
 // Exclusive scan of hist[0..nBins) in place, two launches over tiles of kScanTile entries.
 constexpr int kScanTile = 4096;  // 1024 threads x 4
 
 __global__ void __launch_bounds__(1024)
-BinTileSumKernel(const uint32_t *__restrict__ hist, uint32_t nBins, uint32_t *__restrict__ tileSums) {
+BinTileSumKernel(const uint32_t *__restrict__ hist, uint32_t nBins, uint32_t *__restrict__ tileSums,
+                 const uint32_t *__restrict__ enable = nullptr) {
     __shared__ uint32_t warpSum[32];
+    if (enable && *enable == 0u) return;
     uint32_t base = blockIdx.x * kScanTile + threadIdx.x * 4;
     uint32_t s = 0;
     if (base + 3 < nBins) {
@@ -106,9 +132,11 @@ BinTileSumKernel(const uint32_t *__restrict__ hist, uint32_t nBins, uint32_t *__
 }
 
 __global__ void __launch_bounds__(1024)
-BinTileScanKernel(uint32_t *__restrict__ hist, uint32_t nBins, const uint32_t *__restrict__ tileSums) {
+BinTileScanKernel(uint32_t *__restrict__ hist, uint32_t nBins, const uint32_t *__restrict__ tileSums,
+                  const uint32_t *__restrict__ enable = nullptr) {
     __shared__ uint32_t warpSum[32];
     __shared__ uint32_t tileBase;
+    if (enable && *enable == 0u) return;
     // prefix of the tiles before this one (<= a few hundred values)
     uint32_t pre = 0;
     for (uint32_t t = threadIdx.x; t < blockIdx.x; t += blockDim.x) pre += tileSums[t];
@@ -150,22 +178,6 @@ BinTileScanKernel(uint32_t *__restrict__ hist, uint32_t nBins, const uint32_t *_
         if (base + k < nBins) hist[base + k] = ex;
         ex += v[k];
     }
-}
-
-// perm[pos] = i, pos taken from the scanned histogram (which becomes the bins' end offsets).
-__global__ void __launch_bounds__(256)
-BinScatterKernel(const uint32_t *__restrict__ keys, uint64_t n, uint32_t *__restrict__ offsets,
-                 uint32_t *__restrict__ perm) {
-    uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    const bool valid = i < n;
-    uint32_t key = valid ? keys[i] : 0xffffffffu;
-    const unsigned lane = threadIdx.x & 31;
-    unsigned peers = __match_any_sync(0xffffffffu, key);
-    unsigned leader = (unsigned)(__ffs(peers) - 1);
-    uint32_t base = 0;
-    if (valid && leader == lane) base = atomicAdd(offsets + key, (uint32_t)__popc(peers));
-    base = __shfl_sync(0xffffffffu, base, leader);
-    if (valid) perm[base + __popc(peers & ((1u << lane) - 1))] = (uint32_t)i;
 }
 
 }  // namespace nnbvh

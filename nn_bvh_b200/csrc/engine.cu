@@ -17,9 +17,8 @@
 #include "internal.h"
 #include "kernels.cuh"
 #include "binning.cuh"
-#include "traverse.cuh"
-#include "spec.cuh"
 #include "hlbvh.cuh"
+#include "traverse.cuh"
 
 namespace nnbvh {
 
@@ -62,15 +61,26 @@ struct DevBuf {
 };
 
 // Per-launch device scratch: the persistent kernel's ray cursor and the binning buffers.
+constexpr int kCursorWords = 8;
 struct Scratch {
     // cursor[0], cursor[1]: ray cursors of the fast and the exact launch; cursor[2] (low
-    // 32 bits): number of deferred rays.  Zeroed together before each batch.
+    // 32 bits): number of deferred rays; cursor[3], cursor[4]: binning's distinct-keys / warps
+    // sampled; cursor[5] (low 32 bits): binning's "sorted" flag.  Zeroed together before each batch.
     unsigned long long *cursor = nullptr;
-    DevBuf<uint32_t> keys, perm, hist, tileSums, deferred;
+    DevBuf<uint32_t> keys, keys2, perm, perm2, hist, tileSums, deferred;
+    // Binning mode 2: the device decides per batch, but only the host can skip LAUNCHES.  The flag
+    // of every batch is copied here (pinned, asynchronously, never waited for); after two batches
+    // in a row that arrived coherent the sort kernels are no longer enqueued, until a batch
+    // decides otherwise.  Affects launch overhead only, never results.
+    uint32_t *hFlag = nullptr;
+    int coherentRun = 0;
     void Free() {
         if (cursor) cudaFree(cursor);
         cursor = nullptr;
-        keys.Free(); perm.Free(); hist.Free(); tileSums.Free(); deferred.Free();
+        if (hFlag) cudaFreeHost(hFlag);
+        hFlag = nullptr;
+        keys.Free(); keys2.Free(); perm.Free(); perm2.Free(); hist.Free(); tileSums.Free();
+        deferred.Free();
     }
 };
 
@@ -97,13 +107,14 @@ struct nnbvh_engine {
     int numSMs = 0;
     int maxSmemOptin = 0;
     cudaStream_t ownStream = nullptr, stream = nullptr;
-    cudaEvent_t evA = nullptr, evB = nullptr;
+    cudaEvent_t evA = nullptr, evB = nullptr;  // around a whole batch call (device-pointer path)
+    cudaEvent_t evC = nullptr, evD = nullptr;  // around its traversal launches only
+    bool haveTraversalEvents = false;
     float lastMs = 0.f;
     uint64_t launches = 0;
     // scene
     bool haveScene = false;
     bool boxesRegular = true;  // every node box finite with lo <= hi: the fast slab test is exact
-    bool boxesNested = true;   // every child box lies inside its parent's: speculation is exact
     SceneDev sc{};
     DevBuf<nnbvh_node> dNodes;
     DevBuf<WideNode> dWide;
@@ -116,17 +127,21 @@ struct nnbvh_engine {
     Slot slots[kMaxSlots];
     // tuning knobs (env overridable, see nnbvh_create)
     int wideMinB = 5;        // CTAs/SM the traversal kernel is compiled for
-    int refillBelow = 24;
-    int leafQuorum = 16;
+    int refillBelow = 20;
+    int leafQuorum = 12;
+    int stepStats = 0;       // NNBVH_STEP_STATS=1: run the counting instantiation of StepKernel
+    unsigned long long *dStats = nullptr;
+    int popLoop = 1;         // StepKernel: discard culled stack entries inside the pop
     uint64_t chunkRays = 1u << 19;
     uint64_t chunkRaysSoa = 1u << 20;  // SoA planes are 4 bytes per ray each: larger chunks per copy
     // ray binning pre-pass (binning.cuh)
     int exactOnly = 0;       // skip the fast-slab launch (debug / A-B knob)
-    int noSpec = 0;          // SpecKernel without postponed leaves (debug / A-B knob)
-    int binMode = 0;         // 0 = off, 1 = on for batches >= binMinRays
+    int binMode = 2;         // 0 = off, 1 = always, 2 = per batch, decided on the device (>= binMinRays)
+    int binThreshold = 8;    // mode 2: sort when the average warp holds more distinct keys than this
     int binCellBits = 5;     // origin grid (1<<bits)^3
-    int binDirBits = 2;      // octahedral direction grid (1<<bits)^2
-    uint64_t binMinRays = 1u << 16;
+    int binDirBits = 3;      // octahedral direction grid (1<<bits)^2
+    uint64_t binMinRays = 1u << 21;  // the pre-pass is ~17 launches: not worth it under ~2 Mi rays
+    uint32_t binMinNodes = 1u << 18; // nor for scenes the L1s hold anyway (measured: killeroos loses 11-14 %)
 };
 
 extern "C" const char *nnbvh_last_error(void) { return g_err; }
@@ -167,28 +182,38 @@ extern "C" int nnbvh_create(const nnbvh_options *opts, nnbvh_engine **out) {
     e->kernel = opts ? opts->kernel : NNBVH_KERNEL_AUTO;
     e->smemTopNodes = opts ? opts->smem_top_nodes : -1;
     e->kernel = EnvInt("NNBVH_KERNEL", e->kernel);
+    if (e->kernel < NNBVH_KERNEL_AUTO || e->kernel > NNBVH_KERNEL_STEP) {
+        int k = e->kernel;
+        delete e;
+        return SetError(NNBVH_ERR_INVALID, "nnbvh_create: unknown kernel %d", k);
+    }
     e->smemTopNodes = EnvInt("NNBVH_SMEM_NODES", e->smemTopNodes);
     e->wideMinB = EnvInt("NNBVH_WIDE_MINB", e->wideMinB);
     e->refillBelow = EnvInt("NNBVH_REFILL_BELOW", e->refillBelow);
     e->leafQuorum = EnvInt("NNBVH_LEAF_QUORUM", e->leafQuorum);
+    e->popLoop = EnvInt("NNBVH_POP_LOOP", e->popLoop);
+    e->stepStats = EnvInt("NNBVH_STEP_STATS", 0);
     e->chunkRays = (uint64_t)EnvInt("NNBVH_CHUNK_RAYS", (int)e->chunkRays);
     e->chunkRaysSoa = (uint64_t)EnvInt("NNBVH_CHUNK_RAYS_SOA", (int)e->chunkRaysSoa);
     e->nSlots = std::min((int)nnbvh_engine::kMaxSlots, std::max(1, EnvInt("NNBVH_SLOTS", e->nSlots)));
     e->binMode = EnvInt("NNBVH_BIN", e->binMode);
+    e->binThreshold = EnvInt("NNBVH_BIN_THRESHOLD", e->binThreshold);
     e->exactOnly = EnvInt("NNBVH_EXACT_ONLY", e->exactOnly);
-    e->noSpec = EnvInt("NNBVH_NO_SPEC", e->noSpec);
     e->binCellBits = std::min(8, std::max(0, EnvInt("NNBVH_BIN_CELL_BITS", e->binCellBits)));
     e->binDirBits = std::min(4, std::max(0, EnvInt("NNBVH_BIN_DIR_BITS", e->binDirBits)));
     e->binMinRays = (uint64_t)EnvInt("NNBVH_BIN_MIN_RAYS", (int)e->binMinRays);
+    e->binMinNodes = (uint32_t)EnvInt("NNBVH_BIN_MIN_NODES", (int)e->binMinNodes);
     CU(cudaStreamCreateWithFlags(&e->ownStream, cudaStreamNonBlocking));
     e->stream = e->ownStream;
     CU(cudaEventCreate(&e->evA));
     CU(cudaEventCreate(&e->evB));
-    CU(cudaMalloc(&e->scratch.cursor, 4 * sizeof(unsigned long long)));
+    CU(cudaEventCreate(&e->evC));
+    CU(cudaEventCreate(&e->evD));
+    CU(cudaMalloc(&e->scratch.cursor, kCursorWords * sizeof(unsigned long long)));
     for (Slot &s : e->slots) {
         CU(cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking));
         CU(cudaEventCreateWithFlags(&s.done, cudaEventDisableTiming));
-        CU(cudaMalloc(&s.scratch.cursor, 4 * sizeof(unsigned long long)));
+        CU(cudaMalloc(&s.scratch.cursor, kCursorWords * sizeof(unsigned long long)));
     }
     *out = e;
     return NNBVH_OK;
@@ -201,6 +226,7 @@ extern "C" void nnbvh_destroy(nnbvh_engine *e) {
     e->dNodes.Free();
     e->dWide.Free();
     e->dTris.Free();
+    if (e->dStats) cudaFree(e->dStats);
     e->scratch.Free();
     for (Slot &s : e->slots) {
         s.rays.Free(); s.soa.Free(); s.hits.Free(); s.occ.Free(); s.cnt.Free();
@@ -210,6 +236,8 @@ extern "C" void nnbvh_destroy(nnbvh_engine *e) {
     }
     if (e->evA) cudaEventDestroy(e->evA);
     if (e->evB) cudaEventDestroy(e->evB);
+    if (e->evC) cudaEventDestroy(e->evC);
+    if (e->evD) cudaEventDestroy(e->evD);
     if (e->ownStream) cudaStreamDestroy(e->ownStream);
     delete e;
 }
@@ -229,6 +257,27 @@ extern "C" int nnbvh_last_kernel_ms(nnbvh_engine *e, float *ms) {
         e->lastMs = t;
     }
     *ms = e->lastMs;
+    return NNBVH_OK;
+}
+
+extern "C" int nnbvh_last_traversal_ms(nnbvh_engine *e, float *ms) {
+    if (!e || !ms) return SetError(NNBVH_ERR_INVALID, "nnbvh_last_traversal_ms: NULL argument");
+    if (!e->haveTraversalEvents)
+        return SetError(NNBVH_ERR_INVALID, "nnbvh_last_traversal_ms: no device-pointer batch has run "
+                                           "through the StepKernel path yet");
+    CU(cudaSetDevice(e->device));
+    CU(cudaEventSynchronize(e->evD));
+    CU(cudaEventElapsedTime(ms, e->evC, e->evD));
+    return NNBVH_OK;
+}
+
+extern "C" int nnbvh_debug_step_stats(nnbvh_engine *e, uint64_t *out8) {
+    if (!e || !out8) return SetError(NNBVH_ERR_INVALID, "nnbvh_debug_step_stats: NULL argument");
+    if (!e->dStats) return SetError(NNBVH_ERR_INVALID, "nnbvh_debug_step_stats: NNBVH_STEP_STATS was not set");
+    CU(cudaSetDevice(e->device));
+    CU(cudaStreamSynchronize(e->stream));
+    CU(cudaMemcpy(out8, e->dStats, 8 * sizeof(uint64_t), cudaMemcpyDeviceToHost));
+    CU(cudaMemset(e->dStats, 0, 8 * sizeof(uint64_t)));
     return NNBVH_OK;
 }
 
@@ -370,16 +419,6 @@ extern "C" int nnbvh_upload_scene(nnbvh_engine *e, const nnbvh_node *nodes, uint
             float lo = nd.bounds[k], hi = nd.bounds[3 + k];
             if (!(std::isfinite(lo) && std::isfinite(hi) && lo <= hi)) e->boxesRegular = false;
         }
-    e->boxesNested = true;
-    for (uint32_t i = 0; i < nNodes; ++i) {
-        const nnbvh_node &nd = h[i];
-        if (nd.nPrimitives != 0 || i + 1 >= nNodes || nd.offset <= 0 || (uint32_t)nd.offset >= nNodes)
-            continue;  // leaves; malformed interiors are rejected by BuildWideLayout below
-        for (const nnbvh_node *c : {&h[i + 1], &h[nd.offset]})
-            for (int k = 0; k < 3; ++k)
-                if (!(c->bounds[k] >= nd.bounds[k] && c->bounds[3 + k] <= nd.bounds[3 + k]))
-                    e->boxesNested = false;
-    }
     std::vector<WideNode> wide;
     std::vector<uint8_t> last;
     int32_t rootRef = 0;
@@ -467,6 +506,10 @@ static int LaunchWide(nnbvh_engine *e, cudaStream_t st, const WideParams &p, uin
 
 template <bool ANY, bool EXACT>
 static void LaunchStep(nnbvh_engine *e, cudaStream_t st, const StepParams &p) {
+    if (p.stats && !EXACT) {  // NNBVH_STEP_STATS=1: lane-occupancy counters (diagnostic build of the kernel)
+        StepKernel<ANY, false, 5, true><<<e->numSMs * 5, 256, 0, st>>>(p);
+        return;
+    }
     switch (e->wideMinB) {
     case 1: StepKernel<ANY, EXACT, 1><<<e->numSMs * 1, 256, 0, st>>>(p); break;
     case 2: StepKernel<ANY, EXACT, 2><<<e->numSMs * 2, 256, 0, st>>>(p); break;
@@ -477,15 +520,6 @@ static void LaunchStep(nnbvh_engine *e, cudaStream_t st, const StepParams &p) {
     }
 }
 
-template <bool ANY, bool EXACT, bool SPEC>
-static void LaunchSpec(nnbvh_engine *e, cudaStream_t st, const StepParams &p) {
-    switch (e->wideMinB) {
-    case 1: SpecKernel<ANY, EXACT, SPEC, 1><<<e->numSMs * 1, 256, 0, st>>>(p); break;
-    case 2: SpecKernel<ANY, EXACT, SPEC, 2><<<e->numSMs * 2, 256, 0, st>>>(p); break;
-    case 3: SpecKernel<ANY, EXACT, SPEC, 3><<<e->numSMs * 3, 256, 0, st>>>(p); break;
-    default: SpecKernel<ANY, EXACT, SPEC, 4><<<e->numSMs * 4, 256, 0, st>>>(p); break;
-    }
-}
 
 // All pointers are device pointers here.
 static int LaunchTraversal(nnbvh_engine *e, cudaStream_t st, bool any, bool counters,
@@ -509,9 +543,15 @@ static int LaunchTraversal(nnbvh_engine *e, cudaStream_t st, bool any, bool coun
         uint32_t budgetNodes = (uint32_t)((e->maxSmemOptin - 2048) / minB / sizeof(WideNode));
         uint32_t want = e->smemTopNodes >= 0 ? (uint32_t)e->smemTopNodes : 0u;  // measured: L1 beats explicit staging
         uint32_t smemNodes = std::min(std::min(want, budgetNodes), e->sc.topNodes);
-        // ---- optional binning pre-pass: a ray order that keeps warps coherent ----
-        const uint32_t *perm = nullptr;
-        if (e->binMode && n >= e->binMinRays && n < 0xffffffffull && e->sc.nNodes) {
+        unsigned long long *cursor = scr.cursor;
+        CU(cudaMemsetAsync(cursor, 0, kCursorWords * sizeof(unsigned long long), st));
+        // ---- binning pre-pass: a ray order that keeps warps coherent (binning.cuh) ----
+        // binMode 1: always sort; 2: the device decides per batch (StepKernel only, which reads
+        // the flag); 0: off.
+        const uint32_t *perm = nullptr, *permOn = nullptr;
+        const bool stepKernel = e->kernel != NNBVH_KERNEL_WIDE;
+        if ((e->binMode == 1 || (e->binMode == 2 && stepKernel && e->sc.nNodes >= e->binMinNodes)) &&
+            n >= e->binMinRays && n < 0xffffffffull && e->sc.nNodes) {
             BinParams bp;
             bp.cellBits = (uint32_t)e->binCellBits;
             bp.dirBits = (uint32_t)e->binDirBits;
@@ -520,25 +560,52 @@ static int LaunchTraversal(nnbvh_engine *e, cudaStream_t st, bool any, bool coun
                 bp.lo[k] = e->sc.rootBox[k];
                 bp.scale[k] = ext > 0.f ? (float)(1u << bp.cellBits) / ext : 0.f;
             }
-            const uint32_t nBins = 1u << (3 * bp.cellBits + 2 * bp.dirBits);
-            const uint32_t nTiles = (nBins + kScanTile - 1) / kScanTile;
+            const int keyBits = (int)(3 * bp.cellBits + 2 * bp.dirBits);
+            const uint32_t nSortBlk = (uint32_t)((n + kSortTile - 1) / kSortTile);
+            constexpr int kBinRadixBits = 7;  // 21-bit default key = 3 passes; runs of 16 pairs per digit
+            const uint32_t nHist = (1u << kBinRadixBits) * nSortBlk, nTiles = (nHist + kScanTile - 1) / kScanTile;
             int rc = scr.keys.Reserve(n);
+            if (!rc) rc = scr.keys2.Reserve(n);
             if (!rc) rc = scr.perm.Reserve(n);
-            if (!rc) rc = scr.hist.Reserve(nBins);
+            if (!rc) rc = scr.perm2.Reserve(n);
+            if (!rc) rc = scr.hist.Reserve(nHist);
             if (!rc) rc = scr.tileSums.Reserve(nTiles);
             if (rc) return rc;
-            CU(cudaMemsetAsync(scr.hist.p, 0, sizeof(uint32_t) * (size_t)nBins, st));
-            const unsigned g = (unsigned)((n + 255) / 256);
-            BinCountKernel<<<g, 256, 0, st>>>(bp, in, n, scr.keys.p, scr.hist.p);
-            BinTileSumKernel<<<nTiles, 1024, 0, st>>>(scr.hist.p, nBins, scr.tileSums.p);
-            BinTileScanKernel<<<nTiles, 1024, 0, st>>>(scr.hist.p, nBins, scr.tileSums.p);
-            BinScatterKernel<<<g, 256, 0, st>>>(scr.keys.p, n, scr.hist.p, scr.perm.p);
-            e->launches += 4;
+            uint32_t *flag = reinterpret_cast<uint32_t *>(cursor + 5);
+            if (!scr.hFlag) {
+                CU(cudaHostAlloc(&scr.hFlag, sizeof(uint32_t), cudaHostAllocDefault));
+                *scr.hFlag = 1u;
+            }
+            const uint32_t lastFlag = *const_cast<volatile uint32_t *>(scr.hFlag);
+            scr.coherentRun = lastFlag ? 0 : std::min(scr.coherentRun + 1, 1 << 20);
+            const bool enqueueSort = e->binMode == 1 || scr.coherentRun < 2;
+            BinSampleKernel<<<kBinSamples, 32, 0, st>>>(bp, in, n, cursor + 3);
+            BinDecideKernel<<<1, 1, 0, st>>>(cursor + 3, (uint32_t)e->binThreshold,
+                                             e->binMode == 1 ? 1u : 0u, flag);
+            CU(cudaMemcpyAsync(scr.hFlag, flag, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+            e->launches += 2;
+            uint32_t *kIn = scr.keys.p, *kOut = scr.keys2.p, *vIn = nullptr, *vOut = scr.perm.p;
+            if (enqueueSort) {
+                BinKeyKernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(bp, in, n, scr.keys.p, flag);
+                ++e->launches;
+            }
+            for (int shift = 0; enqueueSort && shift < keyBits; shift += kBinRadixBits) {
+                RadixCountKernel<kBinRadixBits><<<nSortBlk, 256, 0, st>>>(kIn, (uint32_t)n, shift, scr.hist.p, flag);
+                BinTileSumKernel<<<nTiles, 1024, 0, st>>>(scr.hist.p, nHist, scr.tileSums.p, flag);
+                BinTileScanKernel<<<nTiles, 1024, 0, st>>>(scr.hist.p, nHist, scr.tileSums.p, flag);
+                RadixScatterKernel<kBinRadixBits><<<nSortBlk, 256, 0, st>>>(kIn, vIn, (uint32_t)n, shift, scr.hist.p, kOut, vOut, flag);
+                e->launches += 4;
+                std::swap(kIn, kOut);
+                uint32_t *done = vOut;
+                vOut = (done == scr.perm.p) ? scr.perm2.p : scr.perm.p;
+                vIn = done;
+            }
             CU(cudaGetLastError());
-            perm = scr.perm.p;
+            if (enqueueSort) {
+                perm = vIn;
+                permOn = flag;
+            }
         }
-        unsigned long long *cursor = scr.cursor;
-        CU(cudaMemsetAsync(cursor, 0, 4 * sizeof(unsigned long long), st));
         if (e->kernel != NNBVH_KERNEL_WIDE) {
             // ---- StepKernel: fast-slab launch, then the exact launch over the deferred rays ----
             if (n > 0xffffffffull)
@@ -550,41 +617,44 @@ static int LaunchTraversal(nnbvh_engine *e, cudaStream_t st, bool any, bool coun
             sp.hits = o.hits;
             sp.occluded = o.occ;
             sp.perm = perm;
+            sp.permOn = permOn;
             sp.refillBelow = (uint32_t)std::min(32, std::max(1, e->refillBelow));
             sp.leafQuorum = (uint32_t)std::min(32, std::max(1, e->leafQuorum));
+            sp.popLoop = (uint32_t)(e->popLoop != 0);
+            if (e->stepStats) {
+                if (!e->dStats) {
+                    CU(cudaMalloc(&e->dStats, 8 * sizeof(unsigned long long)));
+                    CU(cudaMemsetAsync(e->dStats, 0, 8 * sizeof(unsigned long long), st));
+                }
+                sp.stats = e->dStats;
+            }
             uint32_t *nDef = reinterpret_cast<uint32_t *>(cursor + 2);
+            const bool timed = st == e->stream;  // the device-pointer path; chunk streams are not timed
+            if (timed) CU(cudaEventRecord(e->evC, st));
             if (e->boxesRegular && !e->exactOnly) {
                 int rc = scr.deferred.Reserve(n);
                 if (rc) return rc;
                 sp.cursor = cursor;
                 sp.deferred = scr.deferred.p;
                 sp.nDeferred = nDef;
-                if (e->kernel != NNBVH_KERNEL_SPEC) {
-                    if (any) LaunchStep<true, false>(e, st, sp);
-                    else LaunchStep<false, false>(e, st, sp);
-                } else if (e->boxesNested && !e->noSpec) {
-                    if (any) LaunchSpec<true, false, true>(e, st, sp);
-                    else LaunchSpec<false, false, true>(e, st, sp);
-                } else {
-                    if (any) LaunchSpec<true, false, false>(e, st, sp);
-                    else LaunchSpec<false, false, false>(e, st, sp);
-                }
+                if (any) LaunchStep<true, false>(e, st, sp);
+                else LaunchStep<false, false>(e, st, sp);
                 ++e->launches;
                 sp.perm = scr.deferred.p;
+                sp.permOn = nullptr;
                 sp.nPtr = nDef;
                 sp.deferred = nullptr;
                 sp.nDeferred = nullptr;
             }
             sp.cursor = cursor + 1;
-            if (e->kernel != NNBVH_KERNEL_SPEC) {
-                if (any) LaunchStep<true, true>(e, st, sp);
-                else LaunchStep<false, true>(e, st, sp);
-            } else {
-                if (any) LaunchSpec<true, true, false>(e, st, sp);
-                else LaunchSpec<false, true, false>(e, st, sp);
-            }
+            if (any) LaunchStep<true, true>(e, st, sp);
+            else LaunchStep<false, true>(e, st, sp);
             ++e->launches;
             CU(cudaGetLastError());
+            if (timed) {
+                CU(cudaEventRecord(e->evD, st));
+                e->haveTraversalEvents = true;
+            }
             return NNBVH_OK;
         }
         WideParams p;
@@ -950,10 +1020,10 @@ extern "C" int nnbvh_build_hlbvh_device(nnbvh_engine *e, const float *triVerts9,
     uint32_t *cIn = u + oCodeA, *cOut = u + oCodeB, *pIn = u + oPrimA, *pOut = u + oPrimB;
     const unsigned nHistTiles = (unsigned)((nHist + kScanTile - 1) / kScanTile);
     for (int shift = 0; shift < 30; shift += 8) {
-        RadixPassKernel<false><<<nSortBlk, 256, 0, st>>>(cIn, pIn, n, shift, u + oHist, cOut, pOut);
+        RadixCountKernel<8><<<nSortBlk, 256, 0, st>>>(cIn, n, shift, u + oHist);
         BinTileSumKernel<<<nHistTiles, 1024, 0, st>>>(u + oHist, (uint32_t)nHist, u + oTile);
         BinTileScanKernel<<<nHistTiles, 1024, 0, st>>>(u + oHist, (uint32_t)nHist, u + oTile);
-        RadixPassKernel<true><<<nSortBlk, 256, 0, st>>>(cIn, pIn, n, shift, u + oHist, cOut, pOut);
+        RadixScatterKernel<8><<<nSortBlk, 256, 0, st>>>(cIn, pIn, n, shift, u + oHist, cOut, pOut);
         e->launches += 4;
         std::swap(cIn, cOut);
         std::swap(pIn, pOut);

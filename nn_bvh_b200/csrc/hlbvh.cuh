@@ -4,7 +4,7 @@
 // (/root/reference/src/pbrt/cpu/aggregates.cpp:389-449):
 //   :392-394  centroid bounds            -> PrimBoundsKernel (warp min/max + ordered-uint atomics)
 //   :398-409  Morton codes               -> MortonKernel
-//   :412      RadixSort (:41-82)         -> RadixPassKernel<false/true> + the generic tile scan of
+//   :412      RadixSort (:41-82)         -> RadixCountKernel / RadixScatterKernel + the generic tile scan of
 //                                           binning.cuh; 4 stable passes of 8 bits over the 30 code bits
 //   :415-431  treelet boundaries         -> TreeletHeadKernel + TreeletListKernel
 //   :434-449  emitLBVH per treelet       -> one thread per NODE: LbvhTopologyKernel, a prefix sum,
@@ -89,59 +89,120 @@ MortonKernel(const float *__restrict__ box6, uint32_t n, const uint32_t *__restr
     prim[i] = i;
 }
 
-// ---- stable LSD radix sort, 8 bits per pass ------------------------------------------------
+// ---- stable LSD radix sort, BITS (<= 8) bits per pass ------------------------------------------
 // A block owns a tile of 2048 consecutive keys; warp w owns the tile's keys [256w, 256w+256) in 8
-// rounds of 32 consecutive keys.  The rank of a key among the tile's keys with the same digit is
-// (digit count of earlier warps) + (count of earlier rounds of this warp) + (earlier lanes of this
-// round), i.e. input order: the scatter is stable.  SCATTER=false only writes the tile's digit
-// counts to hist[digit * nBlocks + block]; after an exclusive scan of hist the SCATTER=true launch
-// recomputes the same ranks and moves the pairs.
+// rounds of 32 consecutive keys.
+//   RadixCountKernel: hist[digit * nBlocks + block] = the tile's digit counts.  An exclusive scan
+//     of hist (digit-major) then holds, per (digit, block), the first output position.
+//   RadixScatterKernel: the rank of a key among the tile's keys with the same digit is (count in
+//     earlier warps) + (count in earlier rounds of this warp) + (earlier lanes of this round), i.e.
+//     input order, so the pass is stable.  Pairs are first placed in shared memory in digit order
+//     and written out from there, so consecutive threads write consecutive addresses (runs of
+//     tile/2^BITS pairs per digit) instead of 32 scattered 4-byte stores per instruction.
+// Also the sort of the ray binning pre-pass (binning.cuh), which passes `enable`.
 constexpr int kSortTile = 2048;
 
-template <bool SCATTER>
+template <int BITS>
 __global__ void __launch_bounds__(256)
-RadixPassKernel(const uint32_t *__restrict__ keysIn, const uint32_t *__restrict__ valsIn, uint32_t n,
-                int shift, uint32_t *__restrict__ hist, uint32_t *__restrict__ keysOut,
-                uint32_t *__restrict__ valsOut) {
-    __shared__ uint32_t cnt[8][256];
-    const unsigned tid = threadIdx.x, w = tid >> 5, lane = tid & 31;
-    for (int k = 0; k < 8; ++k) cnt[k][tid] = 0;
+RadixCountKernel(const uint32_t *__restrict__ keysIn, uint32_t n, int shift,
+                 uint32_t *__restrict__ hist, const uint32_t *__restrict__ enable = nullptr) {
+    constexpr uint32_t R = 1u << BITS;
+    __shared__ uint32_t cnt[8][R];
+    if (enable && *enable == 0u) return;  // uniform: the binning pre-pass decided not to sort
+    const unsigned tid = threadIdx.x, w = tid >> 5;
+    for (uint32_t k = tid; k < 8 * R; k += 256) (&cnt[0][0])[k] = 0;
     __syncthreads();
-    const uint64_t base = (uint64_t)blockIdx.x * kSortTile + w * 256u;
-    uint32_t key[8], rank[8];
+    const uint64_t base = (uint64_t)blockIdx.x * kSortTile;
+#pragma unroll
+    for (int r = 0; r < 8; ++r) {
+        const uint64_t i = base + r * 256u + tid;  // order is irrelevant for counting: coalesced
+        if (i < n) atomicAdd(&cnt[w][(keysIn[i] >> shift) & (R - 1)], 1u);
+    }
+    __syncthreads();
+    for (uint32_t d = tid; d < R; d += 256) {
+        uint32_t t = 0;
+        for (int k = 0; k < 8; ++k) t += cnt[k][d];
+        hist[(size_t)d * gridDim.x + blockIdx.x] = t;
+    }
+}
+
+template <int BITS>
+__global__ void __launch_bounds__(256)
+RadixScatterKernel(const uint32_t *__restrict__ keysIn, const uint32_t *__restrict__ valsIn,
+                   uint32_t n, int shift, const uint32_t *__restrict__ hist,
+                   uint32_t *__restrict__ keysOut, uint32_t *__restrict__ valsOut,
+                   const uint32_t *__restrict__ enable = nullptr) {
+    constexpr uint32_t R = 1u << BITS;
+    static_assert(R <= 256, "one thread per digit in the prefix stages");
+    __shared__ uint32_t cnt[8][R];
+    __shared__ uint32_t digitStart[R];  // tile-local exclusive prefix of the digit totals
+    __shared__ uint32_t outBase[R];     // global position of the tile's first pair with this digit - digitStart
+    __shared__ uint32_t warpTot[8];
+    __shared__ uint32_t sKey[kSortTile], sVal[kSortTile];
+    if (enable && *enable == 0u) return;
+    const unsigned tid = threadIdx.x, w = tid >> 5, lane = tid & 31;
+    for (uint32_t k = tid; k < 8 * R; k += 256) (&cnt[0][0])[k] = 0;
+    __syncthreads();
+    const uint64_t tile = (uint64_t)blockIdx.x * kSortTile, base = tile + w * 256u;
+    uint32_t key[8], val[8], rank[8];
 #pragma unroll
     for (int r = 0; r < 8; ++r) {
         const uint64_t i = base + r * 32u + lane;
         const bool valid = i < n;
         key[r] = valid ? keysIn[i] : 0u;
-        const uint32_t digit = valid ? ((key[r] >> shift) & 255u) : 256u;
+        val[r] = valid ? (valsIn ? valsIn[i] : (uint32_t)i) : 0u;  // no valsIn: first pass, identity
+        const uint32_t digit = valid ? ((key[r] >> shift) & (R - 1)) : R;
         const unsigned peers = __match_any_sync(0xffffffffu, digit);
-        uint32_t before = valid ? cnt[w][digit] : 0u;
+        const uint32_t before = valid ? cnt[w][digit] : 0u;
         rank[r] = before + __popc(peers & ((1u << lane) - 1u));
         __syncwarp();
         if (valid && (unsigned)(__ffs(peers) - 1) == lane) cnt[w][digit] = before + __popc(peers);
         __syncwarp();
     }
     __syncthreads();
-    {   // thread d: exclusive prefix of digit d's counts over the 8 warps (+ the global base)
-        uint32_t run = 0;
-        if (SCATTER) run = hist[(size_t)tid * gridDim.x + blockIdx.x];
+    // thread d: exclusive prefix of digit d's counts over the 8 warps, then over the digits
+    uint32_t total = 0;
+    if (tid < R) {
         for (int k = 0; k < 8; ++k) {
-            uint32_t t = cnt[k][tid];
-            cnt[k][tid] = run;
-            run += t;
+            const uint32_t t = cnt[k][tid];
+            cnt[k][tid] = total;
+            total += t;
         }
-        if (!SCATTER) hist[(size_t)tid * gridDim.x + blockIdx.x] = run;
     }
-    if (!SCATTER) return;
+    uint32_t inc = total;
+    for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t t = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= (unsigned)o) inc += t;
+    }
+    if (lane == 31) warpTot[w] = inc;
+    __syncthreads();
+    if (tid < R) {
+        uint32_t pre = 0;
+        for (unsigned k = 0; k < w; ++k) pre += warpTot[k];
+        const uint32_t start = pre + inc - total;
+        digitStart[tid] = start;
+        outBase[tid] = hist[(size_t)tid * gridDim.x + blockIdx.x] - start;
+    }
     __syncthreads();
 #pragma unroll
     for (int r = 0; r < 8; ++r) {
-        const uint64_t i = base + r * 32u + lane;
-        if (i < n) {
-            const uint32_t pos = cnt[w][(key[r] >> shift) & 255u] + rank[r];
-            keysOut[pos] = key[r];
-            valsOut[pos] = valsIn[i];
+        if (base + r * 32u + lane < n) {
+            const uint32_t d = (key[r] >> shift) & (R - 1);
+            const uint32_t at = digitStart[d] + cnt[w][d] + rank[r];
+            sKey[at] = key[r];
+            sVal[at] = val[r];
+        }
+    }
+    __syncthreads();
+    const uint32_t count = (uint32_t)(n - tile < (uint64_t)kSortTile ? n - tile : (uint64_t)kSortTile);
+#pragma unroll
+    for (int r = 0; r < 8; ++r) {
+        const uint32_t j = r * 256u + tid;
+        if (j < count) {
+            const uint32_t k = sKey[j];
+            const uint32_t pos = outBase[(k >> shift) & (R - 1)] + j;
+            keysOut[pos] = k;
+            valsOut[pos] = sVal[j];
         }
     }
 }

@@ -44,9 +44,12 @@ struct StepParams {
     uint8_t *occluded;
     unsigned long long *cursor;   // zeroed before launch
     const uint32_t *perm;         // optional ray order; results go to slot perm[j]
+    const uint32_t *permOn;       // optional device flag: 0 = ignore perm (binning decided not to sort)
     uint32_t *deferred;           // EXACT=false: indices of rays needing the exact slab test
     uint32_t *nDeferred;
     uint32_t refillBelow, leafQuorum;
+    uint32_t popLoop;             // 1: discard culled stack entries inside the pop (default)
+    unsigned long long *stats;    // STATS instantiation only: 8 lane-occupancy counters
 };
 
 struct F8 {
@@ -87,13 +90,17 @@ __device__ __forceinline__ RayConst ToRayConst(const StepRay &s) {
 
 constexpr float kNegInf = -__builtin_huge_valf();
 
-template <bool ANY, bool EXACT, int MINB>
+template <bool ANY, bool EXACT, int MINB, bool STATS = false>
 __global__ void __launch_bounds__(256, MINB) StepKernel(StepParams p) {
+    // STATS: [0] phase-A iterations, [1] lanes at a node, [2] lanes parked at a leaf, [3] lanes without
+    // a ray, [4] phase-B passes, [5] lanes parked there, [6] lanes that ran a triangle test, [7] refills
+    unsigned long long st[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     const SceneDev &sc = p.sc;
     const unsigned lane = threadIdx.x & 31;
     const float4 *__restrict__ tris = sc.tris;
     const unsigned char *__restrict__ wideBase = reinterpret_cast<const unsigned char *>(sc.wide);
     const uint64_t nRays = p.nPtr ? (uint64_t)__ldg(p.nPtr) : p.n;
+    const uint32_t *__restrict__ perm = (p.perm && (!p.permOn || __ldg(p.permOn))) ? p.perm : nullptr;
 
     uint32_t rayIdx = 0;
     bool alive = false;
@@ -118,10 +125,11 @@ __global__ void __launch_bounds__(256, MINB) StepKernel(StepParams p) {
             if (lane == 0) base = atomicAdd(p.cursor, (unsigned long long)nWant);
             base = __shfl_sync(0xffffffffu, base, 0);
             if (base + nWant >= nRays) exhausted = true;
+            if (STATS) st[7] += 1;
             if (!alive) {
                 uint64_t j = base + __popc(want & ((1u << lane) - 1));
                 if (j < nRays) {
-                    uint32_t idx = p.perm ? __ldg(p.perm + j) : (uint32_t)j;
+                    uint32_t idx = perm ? __ldg(perm + j) : (uint32_t)j;
                     RayRegs rr = LoadRay(p.in, idx);
                     RayConst rc = MakeRayConst(rr.ox, rr.oy, rr.oz, rr.dx, rr.dy, rr.dz);
                     bool defer = false;
@@ -179,6 +187,12 @@ __global__ void __launch_bounds__(256, MINB) StepKernel(StepParams p) {
             const unsigned nodeMask = __ballot_sync(0xffffffffu, atNode);
             const unsigned leafMask = __ballot_sync(0xffffffffu, alive && cur < 0);
             if (nodeMask == 0 || (unsigned)__popc(leafMask) >= leafQuorum) break;
+            if (STATS) {
+                st[0] += 1;
+                st[1] += __popc(nodeMask);
+                st[2] += __popc(leafMask);
+                st[3] += 32 - __popc(nodeMask | leafMask);
+            }
             if (atNode) {
                 bool needPop = true;
                 if (curT < tMax) {  // the reference's `tMin < raytMax` for this node, made now
@@ -192,12 +206,21 @@ __global__ void __launch_bounds__(256, MINB) StepKernel(StepParams p) {
                     const float n1x = nx ? b.v[1] : a.v[6], f1x = nx ? a.v[6] : b.v[1];
                     const float n1y = ny ? b.v[2] : a.v[7], f1y = ny ? a.v[7] : b.v[2];
                     const float n1z = nz ? b.v[3] : b.v[0], f1z = nz ? b.v[0] : b.v[3];
-                    float t0, t1;
-                    bool ok0, ok1;
+                    const int ref0 = __float_as_int(b.v[4]), ref1 = __float_as_int(b.v[5]);
+                    const unsigned axis = __float_as_uint(b.v[6]);
+                    const bool secondFirst = (ry.neg >> axis) & 1u;  // aggregates.cpp:561
+                    const int refNear = secondFirst ? ref1 : ref0, refFar = secondFirst ? ref0 : ref1;
+                    float tNear, tFar;
+                    bool stNear, stFar;
                     if (EXACT) {
                         RayConst rc = ToRayConst(ry);
-                        ok0 = SlabStatic(rc, n0x, f0x, n0y, f0y, n0z, f0z, &t0);
-                        ok1 = SlabStatic(rc, n1x, f1x, n1y, f1y, n1z, f1z, &t1);
+                        float t0, t1;
+                        const bool ok0 = SlabStatic(rc, n0x, f0x, n0y, f0y, n0z, f0z, &t0);
+                        const bool ok1 = SlabStatic(rc, n1x, f1x, n1y, f1y, n1z, f1z, &t1);
+                        stNear = secondFirst ? ok1 : ok0;
+                        stFar = secondFirst ? ok0 : ok1;
+                        tNear = secondFirst ? t1 : t0;
+                        tFar = secondFirst ? t0 : t1;
                     } else {
                         const float pad = SlabPad();
                         const float ax0 = Mul(Sub(n0x, ry.ox), ry.ix), bx0 = Mul(Mul(Sub(f0x, ry.ox), ry.ix), pad);
@@ -206,19 +229,17 @@ __global__ void __launch_bounds__(256, MINB) StepKernel(StepParams p) {
                         const float ax1 = Mul(Sub(n1x, ry.ox), ry.ix), bx1 = Mul(Mul(Sub(f1x, ry.ox), ry.ix), pad);
                         const float ay1 = Mul(Sub(n1y, ry.oy), ry.iy), by1 = Mul(Mul(Sub(f1y, ry.oy), ry.iy), pad);
                         const float az1 = Mul(Sub(n1z, ry.oz), ry.iz), bz1 = Mul(Mul(Sub(f1z, ry.oz), ry.iz), pad);
-                        t0 = fmaxf(fmaxf(ax0, ay0), az0);
-                        t1 = fmaxf(fmaxf(ax1, ay1), az1);
+                        const float t0 = fmaxf(fmaxf(ax0, ay0), az0);
+                        const float t1 = fmaxf(fmaxf(ax1, ay1), az1);
                         const float x0 = fminf(fminf(bx0, by0), bz0);
                         const float x1 = fminf(fminf(bx1, by1), bz1);
-                        ok0 = (t0 <= x0) && (x0 > 0.f);
-                        ok1 = (t1 <= x1) && (x1 > 0.f);
+                        // order the VALUES, then compare: the predicates never live in registers
+                        tNear = secondFirst ? t1 : t0;
+                        tFar = secondFirst ? t0 : t1;
+                        const float xNear = secondFirst ? x1 : x0, xFar = secondFirst ? x0 : x1;
+                        stNear = (tNear <= xNear) && (xNear > 0.f);
+                        stFar = (tFar <= xFar) && (xFar > 0.f);
                     }
-                    const int ref0 = __float_as_int(b.v[4]), ref1 = __float_as_int(b.v[5]);
-                    const unsigned axis = __float_as_uint(b.v[6]);
-                    const bool secondFirst = (ry.neg >> axis) & 1u;  // aggregates.cpp:561
-                    const bool stNear = secondFirst ? ok1 : ok0, stFar = secondFirst ? ok0 : ok1;
-                    const int refNear = secondFirst ? ref1 : ref0, refFar = secondFirst ? ref0 : ref1;
-                    const float tNear = secondFirst ? t1 : t0, tFar = secondFirst ? t0 : t1;
                     const bool goNear = stNear && (tNear < tMax);
                     if (goNear) {
                         // The far child is stacked whenever its tMax-independent test passes: tMax
@@ -236,22 +257,39 @@ __global__ void __launch_bounds__(256, MINB) StepKernel(StepParams p) {
                         needPop = false;
                     }
                 }
-                if (needPop) {  // aggregates.cpp:570-574, one entry per step
-                    if (sp == 0) {
+                if (needPop) {
+                    // aggregates.cpp:570-574.  Entries whose box test fails against the current tMax
+                    // (`curT < tMax` false) are discarded here rather than one per iteration: the
+                    // reference pops them one by one with the same outcome, and tMax cannot change
+                    // between this pop and the lane's next step.
+                    bool got = false;
+                    while (sp > 0) {
+                        --sp;
+                        const unsigned long long e = stack[sp];
+                        cur = (int)(unsigned)e;
+                        curT = __uint_as_float((unsigned)(e >> 32));
+                        if (curT < tMax || !p.popLoop) {
+                            got = true;
+                            break;
+                        }
+                    }
+                    if (!got) {
                         alive = false;
                         if (ANY) p.occluded[rayIdx] = 0;
                         else StoreHit(p.hits, rayIdx, hit);
-                    } else {
-                        --sp;
-                        unsigned long long e = stack[sp];
-                        cur = (int)(unsigned)e;
-                        curT = __uint_as_float((unsigned)(e >> 32));
                     }
                 }
             }
         }
 
         // ---- phase B: every parked lane tests ONE triangle of its leaf ----
+        if (STATS) {
+            const unsigned parked = __ballot_sync(0xffffffffu, alive && cur < 0);
+            const unsigned testing = __ballot_sync(0xffffffffu, alive && cur < 0 && curT < tMax);
+            st[4] += 1;
+            st[5] += __popc(parked);
+            st[6] += __popc(testing);
+        }
         if (alive && cur < 0) {
             bool needPop = true;
             if (curT < tMax) {  // box test of the leaf node, made when the lane steps onto it
@@ -284,20 +322,28 @@ __global__ void __launch_bounds__(256, MINB) StepKernel(StepParams p) {
                     needPop = false;
                 }
             }
-            if (needPop) {  // :556-558
-                if (sp == 0) {
+            if (needPop) {  // :556-558; culled entries are skipped as in phase A
+                bool got = false;
+                while (sp > 0) {
+                    --sp;
+                    const unsigned long long e = stack[sp];
+                    cur = (int)(unsigned)e;
+                    curT = __uint_as_float((unsigned)(e >> 32));
+                    if (curT < tMax || !p.popLoop) {
+                        got = true;
+                        break;
+                    }
+                }
+                if (!got) {
                     alive = false;
                     if (ANY) p.occluded[rayIdx] = 0;
                     else StoreHit(p.hits, rayIdx, hit);
-                } else {
-                    --sp;
-                    unsigned long long e = stack[sp];
-                    cur = (int)(unsigned)e;
-                    curT = __uint_as_float((unsigned)(e >> 32));
                 }
             }
         }
     }
+    if (STATS && lane == 0)
+        for (int k = 0; k < 8; ++k) atomicAdd(p.stats + k, st[k]);
 }
 
 }  // namespace nnbvh

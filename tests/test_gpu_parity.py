@@ -8,7 +8,7 @@ from conftest import rand_rays, soup
 
 pytestmark = pytest.mark.gpu
 
-KERNELS = {"basic": 1, "wide": 2, "step": 3, "spec": 4}
+KERNELS = {"basic": 1, "wide": 2, "step": 3}
 
 
 def _agg(tris=None, kernel="wide", **kw):
@@ -35,7 +35,7 @@ def test_device_box_golden(golden):
     assert np.array_equal(agg.test_boxes(g["rays"], g["boxes"]), g["hit"])
 
 
-@pytest.mark.parametrize("kernel", ["basic", "wide", "step", "spec"])
+@pytest.mark.parametrize("kernel", ["basic", "wide", "step"])
 @pytest.mark.parametrize("split", ["sah", "middle", "equal"])
 def test_scene_golden(golden, kernel, split):
     g = golden["scene_small"]
@@ -53,7 +53,7 @@ def test_scene_golden(golden, kernel, split):
     assert (int(nv.sum()), int(tt.sum())) == (st[2], st[3])
 
 
-@pytest.mark.parametrize("kernel", ["basic", "wide", "step", "spec"])
+@pytest.mark.parametrize("kernel", ["basic", "wide", "step"])
 @pytest.mark.parametrize("T,s,mp", [(1, 0.3, 4), (2, 0.3, 4), (37, 0.2, 4), (20000, 0.02, 4),
                                      (20000, 0.05, 1), (60000, 0.01, 255)])
 def test_random_soups_vs_oracle(oracle, kernel, T, s, mp):
@@ -70,7 +70,7 @@ def test_random_soups_vs_oracle(oracle, kernel, T, s, mp):
     assert np.array_equal(nv, wnv) and np.array_equal(tt, wtt)
 
 
-@pytest.mark.parametrize("kernel", ["basic", "wide", "step", "spec"])
+@pytest.mark.parametrize("kernel", ["basic", "wide", "step"])
 def test_edge_inputs(oracle, kernel):
     rng = np.random.default_rng(3)
     tris = soup(rng, 5000, 0.05)
@@ -96,7 +96,7 @@ def test_edge_inputs(oracle, kernel):
     assert np.array_equal(agg.IntersectPBatch(rays), oracle.intersect_p(nodes, agg.ordered_tris9, rays))
 
 
-@pytest.mark.parametrize("kernel", ["basic", "wide", "step", "spec"])
+@pytest.mark.parametrize("kernel", ["basic", "wide", "step"])
 def test_empty_scene_misses(kernel):
     import nn_bvh_b200 as nb
     agg = _agg(None, kernel)
@@ -142,7 +142,7 @@ def test_watertight_sphere(oracle):
             c, d = a + npk, b + npk
             idx += [[a, c, b], [b, c, d]]
     tris = P[np.array(idx)].reshape(-1, 9) + np.float32(0)
-    agg = _agg(tris, "spec", max_prims_in_node=4)
+    agg = _agg(tris, "step", max_prims_in_node=4)
     n = 100_000
     rays = np.zeros((n, 8), np.float32)
     rays[:, :3] = rng.random((n, 3)) * 0.2 - 0.1
@@ -195,7 +195,7 @@ def test_single_ray_surface_and_tensors(oracle):
     assert agg.launch_count() > 0
 
 
-@pytest.mark.parametrize("kernel", ["wide", "step", "spec"])
+@pytest.mark.parametrize("kernel", ["wide", "step"])
 @pytest.mark.parametrize("mp", [1, 4, 32])
 def test_axis_aligned_room_near_ties(oracle, kernel, mp):
     """Flat axis-aligned geometry: leaf boxes are flat, so box-entry distances tie with hit
@@ -231,3 +231,44 @@ def test_axis_aligned_room_near_ties(oracle, kernel, mp):
     want = oracle.intersect(nodes, agg.ordered_tris9, rays)
     assert np.array_equal(_as_words(agg.IntersectBatch(rays)), want)
     assert np.array_equal(agg.IntersectPBatch(rays), oracle.intersect_p(nodes, agg.ordered_tris9, rays))
+
+
+@pytest.mark.parametrize("any_hit", [False, True])
+def test_binning_prepass_never_changes_results(oracle, any_hit, monkeypatch):
+    """The ray-ordering pre-pass (binning.cuh) is invisible: forced on, off, or decided per batch on
+    the device (threshold 0 = always sort, 33 = never), hits[i] still belongs to rays[i], bit for bit.
+    Batch sizes straddle the radix tile (2048) and the 64 Ki-ray minimum."""
+    import nn_bvh_b200 as nb
+    rng = np.random.default_rng(31)
+    tris = soup(rng, 30_000, 0.02)
+    nodes, order = nb.build_bvh(tris, 4, "sah")
+    ot = tris[order]
+    n = 65_536 + 2048 + 77
+    incoherent = rand_rays(rng, n)
+    incoherent[n // 2:, 3] = rng.random(n - n // 2)
+    coherent = np.zeros((n, 8), np.float32)            # a pinhole: one origin, slowly varying direction
+    coherent[:, :3] = [0.5, 0.5, -1.0]
+    u = (np.arange(n) % 512) / 512 - 0.5
+    v = (np.arange(n) // 512) / (n // 512 + 1) - 0.5
+    coherent[:, 4:7] = np.stack([u, v, np.ones(n)], 1)
+    coherent[:, 3] = np.inf
+    for rays in (incoherent, coherent):
+        want = (oracle.intersect_p if any_hit else oracle.intersect)(nodes.view(np.uint32).reshape(-1, 8), ot, rays)
+        for env in ({"NNBVH_BIN": "0"}, {"NNBVH_BIN": "1"}, {"NNBVH_BIN": "2"},
+                    {"NNBVH_BIN": "2", "NNBVH_BIN_THRESHOLD": "0"},
+                    {"NNBVH_BIN": "2", "NNBVH_BIN_THRESHOLD": "33"},
+                    {"NNBVH_BIN": "1", "NNBVH_BIN_CELL_BITS": "8", "NNBVH_BIN_DIR_BITS": "4"},
+                    {"NNBVH_BIN": "1", "NNBVH_BIN_CELL_BITS": "2", "NNBVH_BIN_DIR_BITS": "0"}):
+            for k in ("NNBVH_BIN", "NNBVH_BIN_THRESHOLD", "NNBVH_BIN_CELL_BITS", "NNBVH_BIN_DIR_BITS"):
+                monkeypatch.delenv(k, raising=False)
+            monkeypatch.setenv("NNBVH_BIN_MIN_RAYS", "65536")   # defaults skip batches / scenes this small
+            monkeypatch.setenv("NNBVH_BIN_MIN_NODES", "1")
+            for k, val in env.items():
+                monkeypatch.setenv(k, val)
+            agg = nb.GPUBVHAggregate(nodes=nodes, ordered_tris9=ot)
+            if any_hit:
+                got = agg.IntersectPBatch(rays)
+            else:
+                got = np.ascontiguousarray(agg.IntersectBatch(rays)).view(np.uint32).reshape(-1, 5)
+            assert np.array_equal(got, want), env
+            agg.close()
