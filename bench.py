@@ -395,8 +395,9 @@ def run_ours(args):
                 "shadow_nodes_visited_per_ray": float(nvs.mean()),
                 "shadow_tri_tests_per_ray": float(tts.mean()),
                 "note": "scene (94 MB) is L2-resident: the algorithmic bytes are served by L1/L2, DRAM "
-                        "traffic is the compulsory ray+hit I/O; the kernel is co-limited by issue slots "
-                        "(75%) and the L1 data pipe (76%), see DESIGN.md 5.1 and profiles/r01e_*"}
+                        "traffic is ray+hit I/O (hit records go to scattered slots once rays are ordered); "
+                        "the kernel is co-limited by issue slots (77%) and the L1 data pipe (65%), see "
+                        "DESIGN.md 5.1 and profiles/r01h_*"}
 
     cpu_baseline = None
     if not args.no_cpu_baseline:
