@@ -593,7 +593,9 @@ static int LaunchTraversal(nnbvh_engine *e, cudaStream_t st, bool any, bool coun
                 RadixCountKernel<kBinRadixBits><<<nSortBlk, 256, 0, st>>>(kIn, (uint32_t)n, shift, scr.hist.p, flag);
                 BinTileSumKernel<<<nTiles, 1024, 0, st>>>(scr.hist.p, nHist, scr.tileSums.p, flag);
                 BinTileScanKernel<<<nTiles, 1024, 0, st>>>(scr.hist.p, nHist, scr.tileSums.p, flag);
-                RadixScatterKernel<kBinRadixBits><<<nSortBlk, 256, 0, st>>>(kIn, vIn, (uint32_t)n, shift, scr.hist.p, kOut, vOut, flag);
+                const bool lastPass = shift + kBinRadixBits >= keyBits;  // only the permutation is read afterwards
+                RadixScatterKernel<kBinRadixBits><<<nSortBlk, 256, 0, st>>>(kIn, vIn, (uint32_t)n, shift, scr.hist.p,
+                                                                           lastPass ? nullptr : kOut, vOut, flag);
                 e->launches += 4;
                 std::swap(kIn, kOut);
                 uint32_t *done = vOut;

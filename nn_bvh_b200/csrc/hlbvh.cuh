@@ -113,11 +113,15 @@ RadixCountKernel(const uint32_t *__restrict__ keysIn, uint32_t n, int shift,
     for (uint32_t k = tid; k < 8 * R; k += 256) (&cnt[0][0])[k] = 0;
     __syncthreads();
     const uint64_t base = (uint64_t)blockIdx.x * kSortTile;
+    uint32_t key[8];
 #pragma unroll
-    for (int r = 0; r < 8; ++r) {
+    for (int r = 0; r < 8; ++r) {  // all eight loads in flight before the first shared atomic
         const uint64_t i = base + r * 256u + tid;  // order is irrelevant for counting: coalesced
-        if (i < n) atomicAdd(&cnt[w][(keysIn[i] >> shift) & (R - 1)], 1u);
+        key[r] = i < n ? keysIn[i] : 0u;
     }
+#pragma unroll
+    for (int r = 0; r < 8; ++r)
+        if (base + r * 256u + tid < n) atomicAdd(&cnt[w][(key[r] >> shift) & (R - 1)], 1u);
     __syncthreads();
     for (uint32_t d = tid; d < R; d += 256) {
         uint32_t t = 0;
@@ -127,7 +131,7 @@ RadixCountKernel(const uint32_t *__restrict__ keysIn, uint32_t n, int shift,
 }
 
 template <int BITS>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, 5)
 RadixScatterKernel(const uint32_t *__restrict__ keysIn, const uint32_t *__restrict__ valsIn,
                    uint32_t n, int shift, const uint32_t *__restrict__ hist,
                    uint32_t *__restrict__ keysOut, uint32_t *__restrict__ valsOut,
@@ -144,15 +148,24 @@ RadixScatterKernel(const uint32_t *__restrict__ keysIn, const uint32_t *__restri
     for (uint32_t k = tid; k < 8 * R; k += 256) (&cnt[0][0])[k] = 0;
     __syncthreads();
     const uint64_t tile = (uint64_t)blockIdx.x * kSortTile, base = tile + w * 256u;
-    uint32_t key[8], val[8], rank[8];
+    uint32_t key[8], rank[8];
 #pragma unroll
     for (int r = 0; r < 8; ++r) {
         const uint64_t i = base + r * 32u + lane;
-        const bool valid = i < n;
-        key[r] = valid ? keysIn[i] : 0u;
-        val[r] = valid ? (valsIn ? valsIn[i] : (uint32_t)i) : 0u;  // no valsIn: first pass, identity
-        const uint32_t digit = valid ? ((key[r] >> shift) & (R - 1)) : R;
-        const unsigned peers = __match_any_sync(0xffffffffu, digit);
+        key[r] = i < n ? keysIn[i] : 0u;
+    }
+    // the eight MATCH instructions are independent of each other and of the counters: issue them
+    // together, then run the short dependent chain over the shared counters
+#pragma unroll
+    for (int r = 0; r < 8; ++r) {
+        const bool valid = base + r * 32u + lane < n;
+        rank[r] = __match_any_sync(0xffffffffu, valid ? ((key[r] >> shift) & (R - 1)) : R);
+    }
+#pragma unroll
+    for (int r = 0; r < 8; ++r) {
+        const bool valid = base + r * 32u + lane < n;
+        const uint32_t digit = (key[r] >> shift) & (R - 1);
+        const unsigned peers = rank[r];
         const uint32_t before = valid ? cnt[w][digit] : 0u;
         rank[r] = before + __popc(peers & ((1u << lane) - 1u));
         __syncwarp();
@@ -190,7 +203,8 @@ RadixScatterKernel(const uint32_t *__restrict__ keysIn, const uint32_t *__restri
             const uint32_t d = (key[r] >> shift) & (R - 1);
             const uint32_t at = digitStart[d] + cnt[w][d] + rank[r];
             sKey[at] = key[r];
-            sVal[at] = val[r];
+            const uint64_t i = base + r * 32u + lane;
+            sVal[at] = valsIn ? valsIn[i] : (uint32_t)i;  // no valsIn: first pass, identity
         }
     }
     __syncthreads();
@@ -201,7 +215,7 @@ RadixScatterKernel(const uint32_t *__restrict__ keysIn, const uint32_t *__restri
         if (j < count) {
             const uint32_t k = sKey[j];
             const uint32_t pos = outBase[(k >> shift) & (R - 1)] + j;
-            keysOut[pos] = k;
+            if (keysOut) keysOut[pos] = k;  // the last pass of a sort that only wants the permutation
             valsOut[pos] = sVal[j];
         }
     }
