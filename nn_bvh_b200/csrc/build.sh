@@ -9,6 +9,6 @@ NVCC="${NVCC:-/usr/local/cuda/bin/nvcc}"
 "$NVCC" -std=c++17 -O3 -lineinfo --fmad=false -prec-div=true -prec-sqrt=true -ftz=false \
     -gencode arch=compute_100a,code=sm_100a \
     -Xcompiler -fPIC,-ffp-contract=off,-O2,-pthread -shared \
-    ${NNBVH_PTXAS_V:+-Xptxas -v} \
+    ${NNBVH_PTXAS_V:+-Xptxas -v} ${NNBVH_EXTRA_FLAGS} \
     -o "$OUT" "$HERE/engine.cu" "$HERE/build_host.cpp" -lcudart
 echo "built $OUT"
