@@ -150,3 +150,37 @@ def test_cpp_host_mirror_gpu():
     import subprocess
     r = subprocess.run([_build_cpp_test()], capture_output=True, text=True)
     assert r.returncode == 0 and r.stdout.startswith("PASS"), r.stdout + r.stderr
+
+
+def test_host_builders_match_oracle_on_many_small_inputs(oracle):
+    """Every split method on 300 tiny soups (1..40 triangles, duplicates, flat and collinear sets, huge
+    and tiny coordinates): nodes and primitive order byte for byte."""
+    import nn_bvh_b200 as nb
+    rng = np.random.default_rng(2026)
+    for case in range(300):
+        T = int(rng.integers(1, 41))
+        scale = np.float32(10.0 ** rng.integers(-6, 7))
+        tris = (rng.random((T, 9), dtype=np.float32) * scale).astype(np.float32)
+        kind = case % 6
+        if kind == 1:
+            tris[T // 2:] = tris[: T - T // 2]            # duplicates
+        elif kind == 2:
+            tris[:, 2::3] = tris[0, 2]                    # planar
+        elif kind == 3:
+            tris[:, 1::3] = tris[0, 1]
+            tris[:, 2::3] = tris[0, 2]                    # collinear centroids
+        elif kind == 4:
+            tris[:] = tris[0]                             # all identical
+        mp = int(rng.choice([1, 2, 4, 8, 255]))
+        for split in ("sah", "hlbvh", "middle", "equal"):
+            try:
+                n, o = nb.build_bvh(tris, mp, split)
+            except nb.NnbvhError:
+                # only HLBVH may refuse: treelet roots with one shared centroid (the reference CHECKs)
+                assert split == "hlbvh", (case, split)
+                with pytest.raises(Exception):
+                    oracle.build_bvh(tris, mp, split)
+                continue
+            on, oo = oracle.build_bvh(tris, mp, split)
+            assert np.array_equal(n.view(np.uint32).reshape(-1, 8), on), (case, split, T, mp)
+            assert np.array_equal(o, oo.astype(np.uint32)), (case, split, T, mp)

@@ -82,3 +82,35 @@ def test_device_hlbvh_errors():
         nb.build_hlbvh_device(np.tile(one, (70_000, 1)), 4)
     with pytest.raises(nb.NnbvhError):
         nb.build_bvh(np.tile(one, (70_000, 1)), 4, "hlbvh")
+
+
+def test_device_hlbvh_many_small_inputs():
+    """200 tiny soups (1..300 triangles; duplicates, planar, collinear, identical, 1e-6..1e6 scales) at
+    several leaf sizes: device == host, byte for byte; where the host refuses (the reference's CHECKs)
+    the device refuses too."""
+    import nn_bvh_b200 as nb
+    rng = np.random.default_rng(4052)
+    for case in range(200):
+        T = int(rng.integers(1, 301))
+        scale = np.float32(10.0 ** rng.integers(-6, 7))
+        tris = (rng.random((T, 9), dtype=np.float32) * scale).astype(np.float32)
+        kind = case % 6
+        if kind == 1:
+            tris[T // 2:] = tris[: T - T // 2]
+        elif kind == 2:
+            tris[:, 2::3] = tris[0, 2]
+        elif kind == 3:
+            tris[:, 1::3] = tris[0, 1]
+            tris[:, 2::3] = tris[0, 2]
+        elif kind == 4:
+            tris[:] = tris[0]
+        mp = int(rng.choice([1, 2, 4, 8, 255]))
+        try:
+            hn, ho = nb.build_bvh(tris, mp, "hlbvh")
+        except nb.NnbvhError:
+            with pytest.raises(nb.NnbvhError):
+                nb.build_hlbvh_device(tris, mp)
+            continue
+        dn, do, _ = nb.build_hlbvh_device(tris, mp)
+        assert np.array_equal(_words(dn), _words(hn)), (case, T, mp)
+        assert np.array_equal(do, ho), (case, T, mp)

@@ -272,3 +272,43 @@ def test_binning_prepass_never_changes_results(oracle, any_hit, monkeypatch):
                 got = np.ascontiguousarray(agg.IntersectBatch(rays)).view(np.uint32).reshape(-1, 5)
             assert np.array_equal(got, want), env
             agg.close()
+
+
+def test_binning_decision_is_made_on_the_device(monkeypatch):
+    """Mode 2 sorts incoherent batches and leaves coherent ones alone; after two coherent batches in a
+    row the host stops enqueueing the sort kernels (launch counts: 2 decision kernels + 2 traversal
+    launches instead of 2 + key + 3 x 4 + 2)."""
+    import nn_bvh_b200 as nb
+    rng = np.random.default_rng(32)
+    tris = soup(rng, 30_000, 0.02)
+    nodes, order = nb.build_bvh(tris, 4, "sah")
+    n = 1 << 17
+    incoherent = rand_rays(rng, n)
+    coherent = np.zeros((n, 8), np.float32)
+    coherent[:, :3] = [0.5, 0.5, -1.0]
+    coherent[:, 4:7] = np.stack([(np.arange(n) % 512) / 512 - 0.5, (np.arange(n) // 512) / 256 - 0.5, np.ones(n)], 1)
+    coherent[:, 3] = np.inf
+    monkeypatch.setenv("NNBVH_BIN", "2")
+    monkeypatch.setenv("NNBVH_BIN_MIN_RAYS", "65536")
+    monkeypatch.setenv("NNBVH_BIN_MIN_NODES", "1")
+    import torch
+    agg = nb.GPUBVHAggregate(nodes=nodes, ordered_tris9=tris[order])
+    hits = torch.zeros((n, 5), dtype=torch.int32, device="cuda")
+
+    def launches(rays):
+        d = torch.from_numpy(rays).cuda()
+        c0 = agg.launch_count()
+        agg.IntersectBatch(d, hits=hits, n=n)
+        torch.cuda.synchronize()
+        return agg.launch_count() - c0
+
+    full = 2 + 1 + 3 * 4 + 2
+    assert launches(incoherent) == full
+    assert launches(incoherent) == full
+    assert launches(coherent) == full            # last decision seen by the host: "sort"
+    assert launches(coherent) == full            # one coherent batch seen
+    assert launches(coherent) == 4               # two in a row: sort kernels no longer enqueued
+    assert launches(coherent) == 4
+    assert launches(incoherent) == 4             # the device says "sort", the host learns it afterwards
+    assert launches(incoherent) == full
+    agg.close()
