@@ -46,6 +46,8 @@ def parse():
     ap.add_argument("--rays", type=int, default=8 << 20, help="rays per kind per step per GPU")
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="budget of the cpu_baseline leg")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--exchange", default="peer", choices=["peer", "nccl"],
+                    help="N>1: how hit records reach rank 0: copy engines into a peer-mapped window, or an NCCL gather")
     return ap.parse_args()
 
 
@@ -251,20 +253,37 @@ def run_ours(args):
     d_hits = torch.zeros((n, 5), dtype=torch.int32, device=dev)
     d_occ = torch.zeros(n, dtype=torch.uint8, device=dev)
     from nn_bvh_b200 import sharding
-    g_hits = g_occ = None
-    if world > 1 and rank == 0:   # hit records of all ranks, global ray order
+    # N>1: hit records of all ranks on rank 0, global ray order, inside the timed step.
+    # "peer": rank 0 owns the array, every rank copies its slice into it with a copy engine over
+    # NVLink while its shadow kernel runs (sharding.PeerWindow); "nccl": an NCCL gather -- its
+    # kernel needs SMs the persistent traversal CTAs hold, so it only starts when they drain.
+    g_hits = g_occ = win_hits = win_occ = None
+    if world > 1 and args.exchange == "peer":
+        win_hits = sharding.PeerWindow(world * n, (5,), torch.int32, dst=0)
+        win_occ = sharding.PeerWindow(world * n, (), torch.uint8, dst=0)
+        g_hits, g_occ = win_hits.tensor, win_occ.tensor
+    elif world > 1 and rank == 0:
         g_hits = torch.empty((world * n, 5), dtype=torch.int32, device=dev)
         g_occ = torch.empty(world * n, dtype=torch.uint8, device=dev)
 
     def step(ev_mid=None):
+        if win_hits is not None:   # the previous step's delivery must not be overtaken by this step's writes
+            win_hits.wait_on(stream)
+            win_occ.wait_on(stream)
         agg.IntersectBatch(d_b, hits=d_hits, n=n)
         if ev_mid is not None:
             ev_mid.record(stream)
         w1 = None
-        if world > 1:   # NCCL gather of the closest-hit records overlaps the shadow kernel
+        if win_hits is not None:
+            win_hits.deliver(d_hits, stream)
+        elif world > 1:
             _, w1 = sharding.gather_records(d_hits, world * n, dst=0, out=g_hits, async_op=True)
         agg.IntersectPBatch(d_s, occluded=d_occ, n=n)
-        if world > 1:
+        if win_hits is not None:
+            win_occ.deliver(d_occ, stream)
+            win_hits.wait_on(stream)   # the step ends when its records are on rank 0
+            win_occ.wait_on(stream)
+        elif world > 1:
             _, w2 = sharding.gather_records(d_occ, world * n, dst=0, out=g_occ, async_op=True)
             w1.wait()
             w2.wait()
@@ -417,7 +436,9 @@ def run_ours(args):
                                    f"{n} shadow any-hit rays per GPU per step",
                        "triangles": int(len(w["tris"])), "bvh_nodes": int(len(w["nodes"])),
                        "tree": "reference SAH, maxnodeprims 4", "parallelism": f"rays sharded x{world}, scene replicated"
-                       + (", NCCL gather of hit records to rank 0 inside the step" if world > 1 else ""),
+                       + ("" if world == 1 else ", hit records to rank 0 inside the step by " +
+                          ("copy engines into a peer-mapped window (NVLink)" if args.exchange == "peer"
+                           else "an NCCL gather")),
                        "l2": "ray+hit buffers (>=400 MB per step) exceed the 126 MB L2; "
                              "scene stays cache-resident by design"},
             "e2e": {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": n * 24 + n * 28,

@@ -121,6 +121,18 @@ int nnbvh_build_hlbvh_device(nnbvh_engine *e, const float *triVerts9, uint32_t n
  * ordering pre-pass.  Blocks until that batch has finished. */
 int nnbvh_last_traversal_ms(nnbvh_engine *e, float *ms);
 
+/* ---- sharded runs: result window on the caller's GPU -------------------------
+ * One process per GPU.  The rank that wants the results allocates the global array
+ * (nnbvh_peer_alloc: device memory + a 64-byte CUDA IPC handle to send to the other
+ * processes); every other rank maps it (nnbvh_peer_open) and delivers its slice with
+ * nnbvh_peer_copy, a copy-engine transfer over NVLink ordered on `cudaStream` -- no
+ * SM is taken from the traversal kernels.  All on the calling thread's current device. */
+int nnbvh_peer_alloc(uint64_t bytes, void **devPtr, void *handle64);
+int nnbvh_peer_open(const void *handle64, void **devPtr);
+int nnbvh_peer_close(void *devPtr);
+int nnbvh_peer_free(void *devPtr);
+int nnbvh_peer_copy(void *dst, const void *src, uint64_t bytes, void *cudaStream);
+
 /* Diagnostic: lane-occupancy counters of the traversal kernel, accumulated since the
  * last call, when the engine was created with NNBVH_STEP_STATS=1 in the environment
  * (a counting instantiation of the kernel runs then).  out8: phase-A iterations, lanes

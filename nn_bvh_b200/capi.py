@@ -31,7 +31,8 @@ SYMBOLS = [
     "nnbvh_set_stream", "nnbvh_upload_scene", "nnbvh_intersect_closest", "nnbvh_intersect_any",
     "nnbvh_intersect_closest_soa", "nnbvh_intersect_any_soa", "nnbvh_intersect_counters",
     "nnbvh_last_kernel_ms", "nnbvh_launch_count", "nnbvh_test_triangles", "nnbvh_test_boxes",
-    "nnbvh_last_error", "nnbvh_version", "nnbvh_build_hlbvh_device", "nnbvh_debug_step_stats", "nnbvh_last_traversal_ms",
+    "nnbvh_last_error", "nnbvh_version", "nnbvh_build_hlbvh_device", "nnbvh_debug_step_stats", "nnbvh_last_traversal_ms", "nnbvh_peer_alloc", "nnbvh_peer_open",
+    "nnbvh_peer_close", "nnbvh_peer_free", "nnbvh_peer_copy",
 ]
 
 
@@ -75,6 +76,11 @@ def lib() -> ctypes.CDLL:
     L.nnbvh_launch_count.argtypes = [vp, vp]
     L.nnbvh_debug_step_stats.argtypes = [vp, vp]
     L.nnbvh_last_traversal_ms.argtypes = [vp, vp]
+    L.nnbvh_peer_alloc.argtypes = [u64, vp, vp]
+    L.nnbvh_peer_open.argtypes = [vp, vp]
+    L.nnbvh_peer_close.argtypes = [vp]
+    L.nnbvh_peer_free.argtypes = [vp]
+    L.nnbvh_peer_copy.argtypes = [vp, vp, u64, vp]
     L.nnbvh_test_triangles.argtypes = [vp, vp, vp, u64, vp, vp]
     L.nnbvh_test_boxes.argtypes = [vp, vp, vp, u64, vp]
     L.nnbvh_last_error.restype = ctypes.c_char_p

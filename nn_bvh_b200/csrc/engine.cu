@@ -1073,3 +1073,50 @@ extern "C" int nnbvh_build_hlbvh_device(nnbvh_engine *e, const float *triVerts9,
                            offs[k + 1] - offs[k]};
     return AssembleHLBVH(dense.data(), tr.data(), hCount, nodesOut, nNodesOut);
 }
+
+// ---------------------------------------------------------------------------
+// Result window on a peer GPU (the exchange step of the sharded path): the caller's
+// rank allocates the global result array, the other ranks map it through CUDA IPC and deliver
+// their slice with a copy engine over NVLink -- no SM is taken from the traversal kernels, which
+// fill the GPU with persistent CTAs and would otherwise serialise with a collective's kernel.
+// ---------------------------------------------------------------------------
+extern "C" int nnbvh_peer_alloc(uint64_t bytes, void **devPtr, void *handle64) {
+    if (!devPtr || !handle64) return SetError(NNBVH_ERR_INVALID, "nnbvh_peer_alloc: NULL argument");
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle is 64 bytes");
+    void *p = nullptr;
+    CU(cudaMalloc(&p, std::max<uint64_t>(bytes, 1)));
+    cudaIpcMemHandle_t h;
+    cudaError_t ce = cudaIpcGetMemHandle(&h, p);
+    if (ce != cudaSuccess) {
+        cudaFree(p);
+        return SetError(NNBVH_ERR_CUDA, "cudaIpcGetMemHandle failed: %s", cudaGetErrorString(ce));
+    }
+    std::memcpy(handle64, &h, 64);
+    *devPtr = p;
+    return NNBVH_OK;
+}
+
+extern "C" int nnbvh_peer_open(const void *handle64, void **devPtr) {
+    if (!devPtr || !handle64) return SetError(NNBVH_ERR_INVALID, "nnbvh_peer_open: NULL argument");
+    cudaIpcMemHandle_t h;
+    std::memcpy(&h, handle64, 64);
+    CU(cudaIpcOpenMemHandle(devPtr, h, cudaIpcMemLazyEnablePeerAccess));
+    return NNBVH_OK;
+}
+
+extern "C" int nnbvh_peer_close(void *devPtr) {
+    if (devPtr) CU(cudaIpcCloseMemHandle(devPtr));
+    return NNBVH_OK;
+}
+
+extern "C" int nnbvh_peer_free(void *devPtr) {
+    if (devPtr) CU(cudaFree(devPtr));
+    return NNBVH_OK;
+}
+
+extern "C" int nnbvh_peer_copy(void *dst, const void *src, uint64_t bytes, void *cudaStream) {
+    if (bytes == 0) return NNBVH_OK;
+    if (!dst || !src) return SetError(NNBVH_ERR_INVALID, "nnbvh_peer_copy: NULL argument");
+    CU(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDefault, static_cast<cudaStream_t>(cudaStream)));
+    return NNBVH_OK;
+}
