@@ -259,10 +259,24 @@ def run_ours(args):
     # kernel needs SMs the persistent traversal CTAs hold, so it only starts when they drain.
     g_hits = g_occ = win_hits = win_occ = None
     if world > 1 and args.exchange == "peer":
-        win_hits = sharding.PeerWindow(world * n, (5,), torch.int32, dst=0)
-        win_occ = sharding.PeerWindow(world * n, (), torch.uint8, dst=0)
-        g_hits, g_occ = win_hits.tensor, win_occ.tensor
-    elif world > 1 and rank == 0:
+        ok = 1
+        try:
+            win_hits = sharding.PeerWindow(world * n, (5,), torch.int32, dst=0)
+            win_occ = sharding.PeerWindow(world * n, (), torch.uint8, dst=0)
+        except Exception as e:   # noqa: BLE001 -- e.g. CUDA IPC not permitted in this container
+            print(f"bench.py rank {rank}: peer window unavailable ({e}); using the NCCL gather", file=sys.stderr)
+            ok = 0
+        flag = torch.tensor([ok], dtype=torch.int32, device=dev)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)   # every rank takes the same path
+        if flag.item() == 0:
+            for wdw in (win_hits, win_occ):
+                if wdw is not None:
+                    wdw.close()
+            win_hits = win_occ = None
+            args.exchange = "nccl"
+        else:
+            g_hits, g_occ = win_hits.tensor, win_occ.tensor
+    if world > 1 and args.exchange == "nccl" and rank == 0:
         g_hits = torch.empty((world * n, 5), dtype=torch.int32, device=dev)
         g_occ = torch.empty(world * n, dtype=torch.uint8, device=dev)
 

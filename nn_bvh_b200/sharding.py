@@ -132,11 +132,19 @@ class PeerWindow:
         handle = (ctypes.c_ubyte * 64)()
         p = ctypes.c_void_p()
         box = [None]
-        if self.rank == dst:
-            capi.check(L.nnbvh_peer_alloc(nbytes, ctypes.byref(p), handle))
-            box[0] = bytes(handle)
-        dist.broadcast_object_list(box, src=dst, group=group)
+        self.base = 0
         self._owner = self.rank == dst
+        err = None
+        if self._owner:   # whatever happens here, the broadcast below must still be reached
+            try:
+                capi.check(L.nnbvh_peer_alloc(nbytes, ctypes.byref(p), handle))
+                box[0] = bytes(handle)
+                self.base = p.value
+            except Exception as e:   # noqa: BLE001
+                err = e
+        dist.broadcast_object_list(box, src=dst, group=group)
+        if box[0] is None:
+            raise RuntimeError(f"PeerWindow: rank {dst} could not allocate / export the window") from err
         if not self._owner:
             handle = (ctypes.c_ubyte * 64).from_buffer_copy(box[0])
             capi.check(L.nnbvh_peer_open(handle, ctypes.byref(p)))
