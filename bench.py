@@ -418,10 +418,17 @@ def run_ours(args):
             tj = json.load(f)
         traffic = (tj["dram_bytes_read"] + tj["dram_bytes_write"]) / 1e9   # GB per launch, from ncu
         traffic_src = tj["source"]
+    # for an L2-resident scene also state the L2 figure, from the library's own read probe
+    scene_bytes = 64 * (len(w["nodes"]) // 2 + 1) + 48 * len(w["tris"])
+    l2_gbs = agg.read_bandwidth_probe(min(max(scene_bytes, 16 << 20), 96 << 20), 40)
+    hbm_probe_gbs = agg.read_bandwidth_probe(4 << 30, 2)
     roofline = {"bound": "hbm", "kernel": "StepKernel<closest>", "achieved": achieved, "peak": peak,
                 "unit": "GB/s", "frac": achieved / peak, "traffic": traffic, "traffic_unit": "GB per launch",
                 "traffic_source": traffic_src, "algorithmic_gb_per_launch": bytes_per_ray * n / 1e9,
                 "peak_source": peak_src,
+                "l2": {"peak": l2_gbs, "unit": "GB/s", "frac": achieved / l2_gbs,
+                       "source": f"nnbvh_read_bandwidth_probe over a scene-sized ({scene_bytes >> 20} MB) L2-resident "
+                                 "buffer, 256-bit read-only loads", "hbm_same_probe": hbm_probe_gbs},
                 "algorithmic_bytes_per_ray": bytes_per_ray, "rays_per_launch": n,
                 "kernel_ms": traversal_ms, "closest_batch_ms": closest_ms,
                 "prepass": "closest_batch_ms - kernel_ms = ray-ordering pre-pass (sample, keys, 3 radix passes)",

@@ -133,6 +133,10 @@ int nnbvh_peer_close(void *devPtr);
 int nnbvh_peer_free(void *devPtr);
 int nnbvh_peer_copy(void *dst, const void *src, uint64_t bytes, void *cudaStream);
 
+/* Measurement: read bandwidth (GB/s) of a `bytes`-sized device buffer streamed `iters` times with
+ * the traversal kernel's 256-bit read-only loads: L2 for buffers that fit it, HBM beyond. */
+int nnbvh_read_bandwidth_probe(nnbvh_engine *e, uint64_t bytes, uint32_t iters, float *gbs);
+
 /* Diagnostic: lane-occupancy counters of the traversal kernel, accumulated since the
  * last call, when the engine was created with NNBVH_STEP_STATS=1 in the environment
  * (a counting instantiation of the kernel runs then).  out8: phase-A iterations, lanes

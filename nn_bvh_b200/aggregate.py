@@ -203,6 +203,12 @@ class GPUBVHAggregate:
         capi.check(capi.lib().nnbvh_last_traversal_ms(self._h, ctypes.byref(ms)))
         return ms.value
 
+    def read_bandwidth_probe(self, nbytes: int, iters: int = 20) -> float:
+        """GB/s of streaming an nbytes device buffer `iters` times with 256-bit loads (L2 if it fits)."""
+        g = ctypes.c_float(0)
+        capi.check(capi.lib().nnbvh_read_bandwidth_probe(self._h, nbytes, iters, ctypes.byref(g)))
+        return g.value
+
     def step_stats(self) -> dict:
         """Lane-occupancy counters of the traversal kernel (engine created under NNBVH_STEP_STATS=1)."""
         out = (ctypes.c_uint64 * 8)()

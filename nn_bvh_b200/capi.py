@@ -32,7 +32,7 @@ SYMBOLS = [
     "nnbvh_intersect_closest_soa", "nnbvh_intersect_any_soa", "nnbvh_intersect_counters",
     "nnbvh_last_kernel_ms", "nnbvh_launch_count", "nnbvh_test_triangles", "nnbvh_test_boxes",
     "nnbvh_last_error", "nnbvh_version", "nnbvh_build_hlbvh_device", "nnbvh_debug_step_stats", "nnbvh_last_traversal_ms", "nnbvh_peer_alloc", "nnbvh_peer_open",
-    "nnbvh_peer_close", "nnbvh_peer_free", "nnbvh_peer_copy",
+    "nnbvh_peer_close", "nnbvh_peer_free", "nnbvh_peer_copy", "nnbvh_read_bandwidth_probe",
 ]
 
 
@@ -81,6 +81,7 @@ def lib() -> ctypes.CDLL:
     L.nnbvh_peer_close.argtypes = [vp]
     L.nnbvh_peer_free.argtypes = [vp]
     L.nnbvh_peer_copy.argtypes = [vp, vp, u64, vp]
+    L.nnbvh_read_bandwidth_probe.argtypes = [vp, u64, u32, vp]
     L.nnbvh_test_triangles.argtypes = [vp, vp, vp, u64, vp, vp]
     L.nnbvh_test_boxes.argtypes = [vp, vp, vp, u64, vp]
     L.nnbvh_last_error.restype = ctypes.c_char_p

@@ -1120,3 +1120,48 @@ extern "C" int nnbvh_peer_copy(void *dst, const void *src, uint64_t bytes, void 
     CU(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDefault, static_cast<cudaStream_t>(cudaStream)));
     return NNBVH_OK;
 }
+
+// ---------------------------------------------------------------------------
+// Read-bandwidth probe: the denominator SURVEY 8(d) asks for next to the HBM figure when the scene
+// is L2-resident.  A persistent grid streams a `bytes`-sized buffer `iters` times with the same
+// 256-bit read-only loads the traversal kernel uses; small buffers measure L2, large ones HBM.
+// ---------------------------------------------------------------------------
+namespace nnbvh {
+__global__ void __launch_bounds__(256)
+ReadProbeKernel(const unsigned char *__restrict__ buf, uint64_t nChunks, uint32_t iters,
+                float *__restrict__ sink) {
+    float acc = 0.f;
+    const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+    for (uint32_t it = 0; it < iters; ++it)
+        for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nChunks; i += stride) {
+            const F8 v = Ldg256(buf + 32 * i);
+            acc += v.v[0] + v.v[7];
+        }
+    if (acc == 123.456f) *sink = acc;  // keeps the loads alive
+}
+}  // namespace nnbvh
+
+extern "C" int nnbvh_read_bandwidth_probe(nnbvh_engine *e, uint64_t bytes, uint32_t iters, float *gbs) {
+    if (!e || !gbs) return SetError(NNBVH_ERR_INVALID, "nnbvh_read_bandwidth_probe: NULL argument");
+    if (bytes < 32 || iters == 0) return SetError(NNBVH_ERR_INVALID, "nnbvh_read_bandwidth_probe: empty probe");
+    CU(cudaSetDevice(e->device));
+    unsigned char *buf = nullptr;
+    float *sink = nullptr;
+    CU(cudaMalloc(&buf, bytes));
+    CU(cudaMalloc(&sink, sizeof(float)));
+    CU(cudaMemsetAsync(buf, 0, bytes, e->stream));
+    const uint64_t nChunks = bytes / 32;
+    ReadProbeKernel<<<e->numSMs * 8, 256, 0, e->stream>>>(buf, nChunks, 1, sink);  // warm-up (fills L2)
+    CU(cudaEventRecord(e->evA, e->stream));
+    ReadProbeKernel<<<e->numSMs * 8, 256, 0, e->stream>>>(buf, nChunks, iters, sink);
+    CU(cudaEventRecord(e->evB, e->stream));
+    e->launches += 2;
+    CU(cudaGetLastError());
+    CU(cudaEventSynchronize(e->evB));
+    float ms = 0.f;
+    CU(cudaEventElapsedTime(&ms, e->evA, e->evB));
+    cudaFree(buf);
+    cudaFree(sink);
+    *gbs = (float)((double)nChunks * 32.0 * iters / (ms * 1e-3) / 1e9);
+    return NNBVH_OK;
+}

@@ -312,3 +312,16 @@ def test_binning_decision_is_made_on_the_device(monkeypatch):
     assert launches(incoherent) == 4             # the device says "sort", the host learns it afterwards
     assert launches(incoherent) == full
     agg.close()
+
+
+def test_read_bandwidth_probe_orders_l2_above_hbm():
+    """The roofline denominators bench.py reports next to the HBM peak: an L2-resident buffer streams
+    faster than one far larger than L2, and both are in the range a B200 can produce."""
+    import nn_bvh_b200 as nb
+    agg = nb.GPUBVHAggregate(np.array([[0, 0, 0, 1, 0, 0, 0, 1, 0]], np.float32), 4)
+    l2 = agg.read_bandwidth_probe(32 << 20, 20)
+    hbm = agg.read_bandwidth_probe(2 << 30, 2)
+    assert 1000 < hbm < 9000 and l2 > hbm
+    with pytest.raises(nb.NnbvhError):
+        agg.read_bandwidth_probe(0, 1)
+    agg.close()
