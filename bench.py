@@ -436,10 +436,10 @@ def run_ours(args):
                 "tri_tests_per_ray": float(tt.mean()),
                 "shadow_nodes_visited_per_ray": float(nvs.mean()),
                 "shadow_tri_tests_per_ray": float(tts.mean()),
-                "note": "scene (94 MB) is L2-resident: the algorithmic bytes are served by L1/L2, DRAM "
+                "note": f"scene ({scene_bytes >> 20} MB of 64-byte wide nodes + 48-byte triangles) is L2-resident: the algorithmic bytes are served by L1/L2, DRAM "
                         "traffic is ray+hit I/O (hit records go to scattered slots once rays are ordered); "
                         "the kernel is co-limited by issue slots (77%) and the L1 data pipe (65%), see "
-                        "DESIGN.md 5.1 and profiles/r01h_*"}
+                        "DESIGN.md 5.1 and profiles/r01j_step_metrics.txt"}
 
     cpu_baseline = None
     if not args.no_cpu_baseline:
