@@ -133,6 +133,15 @@ int nnbvh_peer_close(void *devPtr);
 int nnbvh_peer_free(void *devPtr);
 int nnbvh_peer_copy(void *dst, const void *src, uint64_t bytes, void *cudaStream);
 
+/* Where a caller's buffer lives (cudaPointerGetAttributes): *kind = 0 host memory (pageable or
+ * pinned), 1 device memory, 2 managed memory.  The wavefront backend (nnbvh_wavefront.hpp) uses
+ * it to decide whether the host loop after a batch can read a queue's planes in place
+ * (the reference's queues are host memory on --wavefront and managed memory on --gpu,
+ * wavefront/integrator.cpp:231-234). */
+int nnbvh_pointer_kind(const void *p, int *kind);
+/* Blocking copy of `bytes` from device (or managed) memory to host memory. */
+int nnbvh_copy_to_host(void *dstHost, const void *src, uint64_t bytes);
+
 /* Measurement: read bandwidth (GB/s) of a `bytes`-sized device buffer streamed `iters` times with
  * the traversal kernel's 256-bit read-only loads: L2 for buffers that fit it, HBM beyond. */
 int nnbvh_read_bandwidth_probe(nnbvh_engine *e, uint64_t bytes, uint32_t iters, float *gbs);

@@ -33,6 +33,7 @@ SYMBOLS = [
     "nnbvh_last_kernel_ms", "nnbvh_launch_count", "nnbvh_test_triangles", "nnbvh_test_boxes",
     "nnbvh_last_error", "nnbvh_version", "nnbvh_build_hlbvh_device", "nnbvh_debug_step_stats", "nnbvh_last_traversal_ms", "nnbvh_peer_alloc", "nnbvh_peer_open",
     "nnbvh_peer_close", "nnbvh_peer_free", "nnbvh_peer_copy", "nnbvh_read_bandwidth_probe",
+    "nnbvh_pointer_kind", "nnbvh_copy_to_host",
 ]
 
 
@@ -82,6 +83,8 @@ def lib() -> ctypes.CDLL:
     L.nnbvh_peer_free.argtypes = [vp]
     L.nnbvh_peer_copy.argtypes = [vp, vp, u64, vp]
     L.nnbvh_read_bandwidth_probe.argtypes = [vp, u64, u32, vp]
+    L.nnbvh_pointer_kind.argtypes = [vp, vp]
+    L.nnbvh_copy_to_host.argtypes = [vp, vp, u64]
     L.nnbvh_test_triangles.argtypes = [vp, vp, vp, u64, vp, vp]
     L.nnbvh_test_boxes.argtypes = [vp, vp, vp, u64, vp]
     L.nnbvh_last_error.restype = ctypes.c_char_p

@@ -1121,6 +1121,26 @@ extern "C" int nnbvh_peer_copy(void *dst, const void *src, uint64_t bytes, void 
     return NNBVH_OK;
 }
 
+extern "C" int nnbvh_pointer_kind(const void *p, int *kind) {
+    if (!kind) return SetError(NNBVH_ERR_INVALID, "nnbvh_pointer_kind: kind is NULL");
+    *kind = 0;
+    if (!p) return NNBVH_OK;
+    cudaPointerAttributes a;
+    if (cudaPointerGetAttributes(&a, p) != cudaSuccess) {
+        cudaGetLastError();  // no device, or a pointer CUDA has never seen: host memory
+        return NNBVH_OK;
+    }
+    *kind = a.type == cudaMemoryTypeDevice ? 1 : a.type == cudaMemoryTypeManaged ? 2 : 0;
+    return NNBVH_OK;
+}
+
+extern "C" int nnbvh_copy_to_host(void *dstHost, const void *src, uint64_t bytes) {
+    if (bytes == 0) return NNBVH_OK;
+    if (!dstHost || !src) return SetError(NNBVH_ERR_INVALID, "nnbvh_copy_to_host: NULL argument");
+    CU(cudaMemcpy(dstHost, src, bytes, cudaMemcpyDefault));
+    return NNBVH_OK;
+}
+
 // ---------------------------------------------------------------------------
 // Read-bandwidth probe: the denominator SURVEY 8(d) asks for next to the HBM figure when the scene
 // is L2-resident.  A persistent grid streams a `bytes`-sized buffer `iters` times with the same

@@ -194,6 +194,25 @@ class Reference:
         box6 = np.ascontiguousarray(box6, dtype=np.float32)
         return bool(self.lib.nnbvh_ref_box(_p(ray8), _p(box6)))
 
+    def triangle_interaction(self, verts, indices, tri, b, wo_time, normals=None, tangents=None,
+                             uvs=None, reverse_orientation=False):
+        """Triangle::InteractionFromIntersection (shapes.h:884-1010) for queries (tri[i], b[i],
+        wo_time[i]) on an indexed mesh; 39 words per query (see oracle/ref_driver.cpp)."""
+        f32 = lambda a: None if a is None else np.ascontiguousarray(a, dtype=np.float32)
+        verts, normals, tangents, uvs = f32(verts), f32(normals), f32(tangents), f32(uvs)
+        indices = np.ascontiguousarray(indices, dtype=np.int32)
+        tri = np.ascontiguousarray(tri, dtype=np.int32)
+        b, wo_time = f32(b), f32(wo_time)
+        out = np.zeros((tri.shape[0], 39), dtype=np.uint32)
+        fn = self.lib.nnbvh_ref_triangle_interaction
+        fn.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_int] + \
+            [ctypes.c_void_p] * 3 + [ctypes.c_int] + [ctypes.c_void_p] * 3 + [ctypes.c_int64,
+                                                                            ctypes.c_void_p]
+        q = lambda a: None if a is None else _p(a)
+        fn(_p(verts), verts.shape[0], _p(indices), indices.size // 3, q(normals), q(tangents),
+           q(uvs), int(reverse_orientation), _p(tri), _p(b), _p(wo_time), tri.shape[0], _p(out))
+        return out
+
     def stats(self):
         """(nodesVisited, triTests, triHits) of single-threaded calls since the last read."""
         a, b, c = ctypes.c_int64(), ctypes.c_int64(), ctypes.c_int64()

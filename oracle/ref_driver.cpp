@@ -8,6 +8,7 @@
 //   Triangle::Intersect/IntersectP     (src/pbrt/shapes.cpp:320-358)
 //   IntersectTriangle                  (src/pbrt/shapes.cpp:172-273)
 //   Bounds3f::IntersectP               (src/pbrt/util/vecmath.h:1573-1608)
+//   Triangle::InteractionFromIntersection (src/pbrt/shapes.h:884-1010)
 // so that the C restatement in oracle/nnbvh_oracle.cpp and the CUDA engine can
 // be pinned against the real thing.  Nothing here is copied from the
 // reference; it only #includes its headers at build time.
@@ -283,6 +284,66 @@ int nnbvh_ref_box(const float *ray8, const float *box6) {
     pbrt::Vector3f invDir(1 / d.x, 1 / d.y, 1 / d.z);
     int dirIsNeg[3] = {int(invDir.x < 0), int(invDir.y < 0), int(invDir.z < 0)};
     return b.IntersectP(o, d, ray8[3], invDir, dirIsNeg) ? 1 : 0;
+}
+
+// Triangle::InteractionFromIntersection (shapes.h:884-1010) on a caller-supplied mesh: the host
+// step that turns an engine hit record {prim,t,b0,b1,b2} back into a SurfaceInteraction
+// (pins include/nnbvh_wavefront.hpp).  normals / tangents / uvs may be NULL.
+// query i: triangle tri[i], barycentrics b[3i..], wo_time[4i..] = {wo.xyz, time}.
+// out: 39 words per query = pi.low xyz, pi.high xyz, n, uv, dpdu, dpdv, dndu, dndv,
+// shading.{n, dpdu, dpdv, dndu, dndv}, faceIndex (int).
+int nnbvh_ref_triangle_interaction(const float *verts, int nVerts, const int *indices, int nTris,
+                                   const float *normals, const float *tangents, const float *uvs,
+                                   int reverseOrientation, const int *tri, const float *b,
+                                   const float *wo_time, int64_t n, float *out) {
+    if (!g_inited)
+        nnbvh_ref_init(0);
+    std::vector<int> idx(indices, indices + 3 * (size_t)nTris);
+    std::vector<pbrt::Point3f> p(nVerts);
+    std::vector<pbrt::Normal3f> nn;
+    std::vector<pbrt::Vector3f> ss;
+    std::vector<pbrt::Point2f> uv;
+    for (int i = 0; i < nVerts; ++i)
+        p[i] = pbrt::Point3f(verts[3 * i], verts[3 * i + 1], verts[3 * i + 2]);
+    if (normals)
+        for (int i = 0; i < nVerts; ++i)
+            nn.push_back(pbrt::Normal3f(normals[3 * i], normals[3 * i + 1], normals[3 * i + 2]));
+    if (tangents)
+        for (int i = 0; i < nVerts; ++i)
+            ss.push_back(pbrt::Vector3f(tangents[3 * i], tangents[3 * i + 1], tangents[3 * i + 2]));
+    if (uvs)
+        for (int i = 0; i < nVerts; ++i)
+            uv.push_back(pbrt::Point2f(uvs[2 * i], uvs[2 * i + 1]));
+    std::vector<int> face(nTris);
+    for (int i = 0; i < nTris; ++i)
+        face[i] = i;
+    pbrt::Allocator alloc;
+    pbrt::TriangleMesh *mesh = alloc.new_object<pbrt::TriangleMesh>(
+        pbrt::Transform(), reverseOrientation != 0, idx, p, ss, nn, uv, face, alloc);
+    for (int64_t i = 0; i < n; ++i) {
+        pbrt::TriangleIntersection ti{b[3 * i], b[3 * i + 1], b[3 * i + 2], 1.f};
+        const float *w = wo_time + 4 * i;
+        pbrt::SurfaceInteraction si = pbrt::Triangle::InteractionFromIntersection(
+            mesh, tri[i], ti, w[3], pbrt::Vector3f(w[0], w[1], w[2]));
+        float *o = out + 39 * i;
+        auto put3 = [&o](float x, float y, float z) { *o++ = x, *o++ = y, *o++ = z; };
+        put3(si.pi.x.LowerBound(), si.pi.y.LowerBound(), si.pi.z.LowerBound());
+        put3(si.pi.x.UpperBound(), si.pi.y.UpperBound(), si.pi.z.UpperBound());
+        put3(si.n.x, si.n.y, si.n.z);
+        *o++ = si.uv.x, *o++ = si.uv.y;
+        put3(si.dpdu.x, si.dpdu.y, si.dpdu.z);
+        put3(si.dpdv.x, si.dpdv.y, si.dpdv.z);
+        put3(si.dndu.x, si.dndu.y, si.dndu.z);
+        put3(si.dndv.x, si.dndv.y, si.dndv.z);
+        put3(si.shading.n.x, si.shading.n.y, si.shading.n.z);
+        put3(si.shading.dpdu.x, si.shading.dpdu.y, si.shading.dpdu.z);
+        put3(si.shading.dpdv.x, si.shading.dpdv.y, si.shading.dpdv.z);
+        put3(si.shading.dndu.x, si.shading.dndu.y, si.shading.dndu.z);
+        put3(si.shading.dndv.x, si.shading.dndv.y, si.shading.dndv.z);
+        int fi = si.faceIndex;
+        std::memcpy(o, &fi, 4);
+    }
+    return 0;
 }
 
 // Loop subdivision through the reference (util/loopsubdiv.cpp) so that

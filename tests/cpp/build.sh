@@ -8,3 +8,7 @@ g++ -std=c++17 -O2 -ffp-contract=off -o "$HERE/host_mirror_test" "$HERE/host_mir
     -L"$ROOT/nn_bvh_b200" -lnnbvh -L"$ROOT/oracle/_build" -lnnbvh_oracle \
     -Wl,-rpath,'$ORIGIN/../../nn_bvh_b200' -Wl,-rpath,'$ORIGIN/../../oracle/_build' -pthread
 echo "built $HERE/host_mirror_test"
+g++ -std=c++17 -O2 -ffp-contract=off -fPIC -shared -I"$ROOT/include" \
+    -o "$HERE/libwavefront_shim.so" "$HERE/wavefront_shim.cpp" \
+    -L"$ROOT/nn_bvh_b200" -lnnbvh -Wl,-rpath,'$ORIGIN/../../nn_bvh_b200' -pthread
+echo "built $HERE/libwavefront_shim.so"

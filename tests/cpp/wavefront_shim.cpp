@@ -1,0 +1,159 @@
+// tests/cpp/wavefront_shim.cpp -- a C-callable consumer of include/nnbvh_wavefront.hpp for the tests.
+//
+// Plays the integrator's part around nnbvh::wavefront::GPUBVHWavefrontAggregate: owns SoA ray
+// queues (the layout of the reference's SOA<RayWorkItem>, wavefront/workitems.soa) and a sink that
+// records what EnqueueWorkAfterMiss / EnqueueWorkAfterIntersection / RecordShadowRayResult
+// (wavefront/intersect.h:16-163) would be handed.  wf_interaction() exposes the host-side
+// Triangle::InteractionFromIntersection restatement on its own (no GPU needed).
+#include <cstring>
+#include <mutex>
+
+#include "nnbvh_wavefront.hpp"
+
+using namespace nnbvh::wavefront;
+
+namespace {
+thread_local std::string g_what;
+
+struct Mesh {
+    std::vector<float> p, n, s, uv;
+    std::vector<int> idx, face;
+    TriangleMeshView View(bool reverseOrientation) const {
+        TriangleMeshView v;
+        v.vertexIndices = idx.data();
+        v.p = p.data();
+        v.n = n.empty() ? nullptr : n.data();
+        v.s = s.empty() ? nullptr : s.data();
+        v.uv = uv.empty() ? nullptr : uv.data();
+        v.faceIndices = face.data();
+        v.reverseOrientation = reverseOrientation;
+        return v;
+    }
+};
+
+Mesh MakeMesh(const float *verts, int nVerts, const int *indices, int nTris, const float *normals,
+              const float *tangents, const float *uvs, bool reverseOrientation = false) {
+    Mesh m;
+    m.p.assign(verts, verts + 3 * (size_t)nVerts);
+    m.idx.assign(indices, indices + 3 * (size_t)nTris);
+    if (normals) m.n.assign(normals, normals + 3 * (size_t)nVerts);
+    // TriangleMesh stores the normals negated when reverseOrientation is set (util/mesh.cpp:51-55)
+    if (reverseOrientation)
+        for (float &x : m.n) x = -x;
+    if (tangents) m.s.assign(tangents, tangents + 3 * (size_t)nVerts);
+    if (uvs) m.uv.assign(uvs, uvs + 2 * (size_t)nVerts);
+    m.face.resize(nTris);
+    for (int i = 0; i < nTris; ++i) m.face[i] = i;
+    return m;
+}
+
+// 39 words, the order oracle/ref_driver.cpp nnbvh_ref_triangle_interaction writes
+void Pack(const SurfaceHit &h, float *o) {
+    auto put = [&o](const float *v, int k) { std::memcpy(o, v, 4 * k); o += k; };
+    put(h.piLow, 3), put(h.piHigh, 3), put(h.n, 3), put(h.uv, 2), put(h.dpdu, 3), put(h.dpdv, 3);
+    put(h.dndu, 3), put(h.dndv, 3), put(h.shading.n, 3), put(h.shading.dpdu, 3);
+    put(h.shading.dpdv, 3), put(h.shading.dndu, 3), put(h.shading.dndv, 3);
+    std::memcpy(o, &h.faceIndex, 4);
+}
+
+struct Scene {
+    Mesh mesh;
+    std::unique_ptr<GPUBVHWavefrontAggregate> agg;
+};
+
+// what the reference's queues would receive, by ray index
+struct Sink {
+    int8_t *kind;     // 0 EnqueueWorkAfterMiss, 1 EnqueueWorkAfterIntersection
+    uint32_t *prim;   // index in the constructor's primitive list
+    float *tHit;
+    float *surf39;
+    float *woTime;    // 4 per ray
+    uint8_t *shadow;  // RecordShadowRayResult(foundIntersection)
+    std::atomic<int> calls{0};
+    void EnqueueWorkAfterMiss(int i) { kind[i] = 0, ++calls; }
+    void EnqueueWorkAfterIntersection(int i, uint32_t p, float t, const SurfaceHit &h) {
+        kind[i] = 1, prim[i] = p, tHit[i] = t;
+        Pack(h, surf39 + 39 * (size_t)i);
+        std::memcpy(woTime + 4 * (size_t)i, h.wo, 12);
+        woTime[4 * (size_t)i + 3] = h.time;
+        ++calls;
+    }
+    void RecordShadowRayResult(int i, bool found) { shadow[i] = found, ++calls; }
+};
+}  // namespace
+
+extern "C" {
+
+const char *wf_last_error(void) { return g_what.c_str(); }
+
+int wf_interaction(const float *verts, int nVerts, const int *indices, int nTris,
+                   const float *normals, const float *tangents, const float *uvs,
+                   int reverseOrientation, const int *tri, const float *b, const float *woTime,
+                   int64_t n, float *out39) {
+    Mesh m = MakeMesh(verts, nVerts, indices, nTris, normals, tangents, uvs, reverseOrientation != 0);
+    TriangleMeshView v = m.View(reverseOrientation != 0);
+    for (int64_t i = 0; i < n; ++i) {
+        SurfaceHit h;
+        if (!InteractionFromIntersection(v, tri[i], b[3 * i], b[3 * i + 1], b[3 * i + 2],
+                                         woTime[4 * i + 3], woTime + 4 * i, &h))
+            return -1;
+        Pack(h, out39 + 39 * i);
+    }
+    return 0;
+}
+
+void *wf_create(const float *verts, int nVerts, const int *indices, int nTris, const float *normals,
+                const float *uvs, int maxPrimsInNode, int splitMethod, int hostThreads) {
+    try {
+        auto *s = new Scene;
+        s->mesh = MakeMesh(verts, nVerts, indices, nTris, normals, nullptr, uvs);
+        std::vector<GPUBVHWavefrontAggregate::PrimitiveRef> prims(nTris);
+        for (int i = 0; i < nTris; ++i) prims[i] = {0, i};
+        s->agg.reset(new GPUBVHWavefrontAggregate(
+            {s->mesh.View(false)}, prims, maxPrimsInNode,
+            (nnbvh::GPUBVHAggregate::SplitMethod)splitMethod, -1, hostThreads));
+        return s;
+    } catch (const nnbvh::Error &e) {
+        g_what = e.what();
+        return nullptr;
+    }
+}
+
+void wf_destroy(void *scene) { delete (Scene *)scene; }
+
+// planes: ox oy oz dx dy dz time (7 pointers; host or device memory).  Returns the number of sink
+// calls (== n) or a negative nnbvh_status.
+int wf_intersect_closest(void *scene, int maxRays, const float *const *planes, int n, int8_t *kind,
+                         uint32_t *prim, float *tHit, float *surf39, float *woTime) {
+    try {
+        RayQueueView q{planes[0], planes[1], planes[2], planes[3], planes[4], planes[5], planes[6], n};
+        Sink sink;
+        sink.kind = kind, sink.prim = prim, sink.tHit = tHit, sink.surf39 = surf39, sink.woTime = woTime;
+        ((Scene *)scene)->agg->IntersectClosest(maxRays, q, sink);
+        return sink.calls;
+    } catch (const nnbvh::Error &e) {
+        g_what = e.what();
+        return e.code;
+    }
+}
+
+// planes: ox oy oz dx dy dz time tMax (8 pointers).
+int wf_intersect_shadow(void *scene, int maxRays, const float *const *planes, int n, uint8_t *found,
+                        int transmittance) {
+    try {
+        ShadowRayQueueView q{planes[0], planes[1], planes[2], planes[3], planes[4],
+                             planes[5], planes[6], planes[7], n};
+        Sink sink;
+        sink.shadow = found;
+        if (transmittance)
+            ((Scene *)scene)->agg->IntersectShadowTr(maxRays, q, sink);
+        else
+            ((Scene *)scene)->agg->IntersectShadow(maxRays, q, sink);
+        return sink.calls;
+    } catch (const nnbvh::Error &e) {
+        g_what = e.what();
+        return e.code;
+    }
+}
+
+}  // extern "C"

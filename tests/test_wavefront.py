@@ -1,0 +1,172 @@
+"""tests/test_wavefront.py -- the wavefront batch backend (include/nnbvh_wavefront.hpp).
+
+CPU part: the host-side restatement of Triangle::InteractionFromIntersection
+(/root/reference/src/pbrt/shapes.h:884-1010) against golden answers produced by the reference's own
+function (tools/make_golden.py -> tests/golden/interaction.npz) and, where oracle/_ref is built,
+against the reference live on fresh inputs.  Bit-exact: every one of the 39 words.
+
+GPU part: GPUBVHWavefrontAggregate::IntersectClosest / IntersectShadow over SoA ray queues
+(CPUAggregate::IntersectClosest / IntersectShadow, wavefront/aggregate.cpp:34-68): every ray reaches
+the sink exactly once, as a miss or with the oracle's primitive / tHit and the reference's surface
+geometry, for queues in host memory and in device memory.
+"""
+import ctypes
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+from conftest import GOLDEN, ROOT, rand_rays
+
+CASES = ("plain", "uv", "uv_n", "n_only", "uv_n_s", "reversed", "degenerate_uv", "zero_ns")
+
+
+def _p(a):
+    return None if a is None else a.ctypes.data_as(ctypes.c_void_p)
+
+
+@pytest.fixture(scope="module")
+def shim():
+    subprocess.check_call(["sh", os.path.join(ROOT, "tests", "cpp", "build.sh")], stdout=subprocess.DEVNULL)
+    L = ctypes.CDLL(os.path.join(ROOT, "tests", "cpp", "libwavefront_shim.so"))
+    L.wf_last_error.restype = ctypes.c_char_p
+    L.wf_create.restype = ctypes.c_void_p
+    L.wf_create.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p,
+                            ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_int]
+    L.wf_destroy.argtypes = [ctypes.c_void_p]
+    L.wf_interaction.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_int] + \
+        [ctypes.c_void_p] * 3 + [ctypes.c_int] + [ctypes.c_void_p] * 3 + [ctypes.c_int64, ctypes.c_void_p]
+    L.wf_intersect_closest.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_int] + \
+        [ctypes.c_void_p] * 5
+    L.wf_intersect_shadow.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_int,
+                                      ctypes.c_void_p, ctypes.c_int]
+    return L
+
+
+def _interaction(L, c):
+    f = lambda k: np.ascontiguousarray(c[k]) if c.get(k) is not None else None
+    verts, idx, tri, b, wt = f("verts"), f("idx"), f("tri"), f("b"), f("wo_time")
+    n, s, uv = f("n"), f("s"), f("uv")
+    out = np.zeros((tri.shape[0], 39), dtype=np.uint32)
+    rc = L.wf_interaction(_p(verts), verts.shape[0], _p(idx), idx.shape[0], _p(n), _p(s), _p(uv),
+                          int(bool(c["reverse"])), _p(tri), _p(b), _p(wt), tri.shape[0], _p(out))
+    assert rc == 0
+    return out
+
+
+NAMES39 = (["pi.low"] * 3 + ["pi.high"] * 3 + ["n"] * 3 + ["uv"] * 2 + ["dpdu"] * 3 + ["dpdv"] * 3 +
+           ["dndu"] * 3 + ["dndv"] * 3 + ["shading.n"] * 3 + ["shading.dpdu"] * 3 + ["shading.dpdv"] * 3 +
+           ["shading.dndu"] * 3 + ["shading.dndv"] * 3 + ["faceIndex"])
+
+
+def _same(got, want, what):
+    bad = np.argwhere(got != want)
+    assert bad.size == 0, f"{what}: {len(bad)} words differ, first at query {bad[0][0]} field {NAMES39[bad[0][1]]}"
+
+
+@pytest.mark.parametrize("name", CASES)
+def test_interaction_matches_reference_golden(shim, name):
+    g = np.load(os.path.join(GOLDEN, "interaction.npz"))
+    c = {k: (g[f"{name}_{k}"] if f"{name}_{k}" in g else None)
+         for k in ("verts", "idx", "uv", "n", "s", "tri", "b", "wo_time", "reverse")}
+    _same(_interaction(shim, c), g[name + "_want"], name)
+
+
+def test_interaction_matches_reference_live(shim, reference):
+    from tools.make_golden import interaction_cases
+    for seed in (1, 2, 3):
+        for name, c in interaction_cases(np.random.default_rng(seed)).items():
+            want = reference.triangle_interaction(c["verts"], c["idx"], c["tri"], c["b"], c["wo_time"],
+                                                  normals=c["n"], tangents=c["s"], uvs=c["uv"],
+                                                  reverse_orientation=c["reverse"])
+            _same(_interaction(shim, c), want, f"{name} seed {seed}")
+
+
+def test_backend_fails_loudly_without_gpu(shim):
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    verts = np.array([[0, 0, 0], [1, 0, 0], [0, 1, 0]], dtype=np.float32)
+    idx = np.array([[0, 1, 2]], dtype=np.int32)
+    h = shim.wf_create(_p(verts), 3, _p(idx), 1, None, None, 4, 0, 1)
+    assert not h and b"no CPU fallback" in shim.wf_last_error()
+
+
+def _mesh(rng, V=4000, T=12000):
+    """An indexed mesh of small triangles (shared vertices) with uv and normals."""
+    verts = rng.random((V, 3)).astype(np.float32)
+    a = rng.integers(0, V, T)
+    # neighbours in a spatial sort keep triangles small
+    order = np.lexsort((verts[:, 2], verts[:, 1], (verts[:, 0] * 16).astype(int)))
+    inv = np.empty(V, dtype=np.int64)
+    inv[order] = np.arange(V)
+    b = order[np.clip(inv[a] + rng.integers(1, 6, T), 0, V - 1)]
+    c = order[np.clip(inv[a] - rng.integers(1, 6, T), 0, V - 1)]
+    idx = np.stack([a, b, c], axis=1).astype(np.int32)
+    idx = idx[(idx[:, 0] != idx[:, 1]) & (idx[:, 1] != idx[:, 2]) & (idx[:, 0] != idx[:, 2])]
+    uv = rng.random((V, 2)).astype(np.float32)
+    n = rng.normal(size=(V, 3)).astype(np.float32)
+    n = (n / np.linalg.norm(n, axis=1, keepdims=True)).astype(np.float32) + np.float32(0)
+    return verts, np.ascontiguousarray(idx), uv, n
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("where", ["host", "device"])
+def test_wavefront_queues_closest_and_shadow(shim, oracle, reference, where):
+    import torch
+    rng = np.random.default_rng(34)
+    verts, idx, uv, nrm = _mesh(rng)
+    T = idx.shape[0]
+    h = shim.wf_create(_p(verts), verts.shape[0], _p(idx), T, _p(nrm), _p(uv), 4, 0, 4)
+    assert h, shim.wf_last_error()
+    try:
+        N = 200_000
+        rays = rand_rays(rng, N)
+        rays[:, 7] = rng.random(N)                     # ray.time travels to the interaction
+        rays[N // 2:, 3] = rng.random(N - N // 2)      # shadow tMax
+        planes_np = [np.ascontiguousarray(rays[:, k]) for k in (0, 1, 2, 4, 5, 6, 7, 3)]
+        if where == "device":
+            keep = [torch.from_numpy(p).cuda() for p in planes_np]
+            ptrs = [t.data_ptr() for t in keep]
+        else:
+            ptrs = [p.ctypes.data for p in planes_np]
+        arr = (ctypes.c_void_p * 8)(*ptrs)
+
+        kind = np.full(N, -1, dtype=np.int8)
+        prim = np.zeros(N, dtype=np.uint32)
+        t_hit = np.zeros(N, dtype=np.float32)
+        surf = np.zeros((N, 39), dtype=np.uint32)
+        wo_t = np.zeros((N, 4), dtype=np.float32)
+        # a queue larger than maxRays is the caller's error (queues are allocated for maxQueueSize)
+        assert shim.wf_intersect_closest(h, N - 1, arr, N, _p(kind), _p(prim), _p(t_hit), _p(surf), _p(wo_t)) < 0
+        calls = shim.wf_intersect_closest(h, N, arr, N, _p(kind), _p(prim), _p(t_hit), _p(surf), _p(wo_t))
+        assert calls == N, shim.wf_last_error()
+
+        # the same rays through the oracle on the tree the reference builds (tMax = inf for closest)
+        tris9 = verts[idx].reshape(T, 9)
+        sc = reference.scene(tris9, 4, "sah")
+        nodes, order = reference.export(sc, T)
+        r_inf = rays.copy()
+        r_inf[:, 3] = np.inf
+        want = oracle.intersect(nodes, tris9[order], r_inf)
+        miss = want[:, 0] == 0xFFFFFFFF
+        assert np.array_equal(kind == 0, miss) and np.array_equal(kind == 1, ~miss)
+        hit = np.nonzero(~miss)[0]
+        assert len(hit) > N // 20
+        assert np.array_equal(prim[hit], order[want[hit, 0]].astype(np.uint32))      # caller's primitive index
+        assert np.array_equal(t_hit[hit].view(np.uint32), want[hit, 1])
+        assert np.array_equal(wo_t[hit, :3], -rays[hit, 4:7]) and np.array_equal(wo_t[hit, 3], rays[hit, 7])
+        b = want[hit, 2:5].view(np.float32)
+        ref_surf = reference.triangle_interaction(verts, idx, prim[hit].astype(np.int32), b, wo_t[hit],
+                                                  normals=nrm, uvs=uv)
+        _same(surf[hit], ref_surf, "EnqueueWorkAfterIntersection geometry")
+
+        found = np.full(N, 7, dtype=np.uint8)
+        for tr in (0, 1):
+            assert shim.wf_intersect_shadow(h, N, arr, N, _p(found), tr) == N, shim.wf_last_error()
+            assert np.array_equal(found, oracle.intersect_p(nodes, tris9[order], rays))
+        # an empty queue is a no-op
+        assert shim.wf_intersect_shadow(h, N, arr, 0, _p(found), 0) == 0
+    finally:
+        shim.wf_destroy(h)

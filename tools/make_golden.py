@@ -15,6 +15,10 @@ oracle/ref_driver.cpp; the fixtures are small so they can be committed.
   scene_small.npz   a 3000-triangle soup: reference SAH/Middle/EqualCounts trees
                     (nodes + order), closest-hit records, IntersectP results,
                     counter totals, for 4096 rays.
+  interaction.npz   Triangle::InteractionFromIntersection (shapes.h:884-1010) answers on
+                    indexed meshes with / without uv, normals, tangents, reversed
+                    orientation, degenerate uv and zero shading normals
+                    (--only-interaction regenerates just this file).
 """
 import os
 import sys
@@ -187,9 +191,57 @@ def hlbvh(ref):
     np.savez_compressed(os.path.join(OUT, "hlbvh.npz"), **out)
 
 
+def interaction_cases(rng):
+    """Meshes + queries for InteractionFromIntersection; shared with tests/test_wavefront.py."""
+    cases = {}
+    V, T, Q = 60, 100, 400
+    for name in ("plain", "uv", "uv_n", "n_only", "uv_n_s", "reversed", "degenerate_uv", "zero_ns"):
+        verts = as_pbrt_stores((rng.random((V, 3)) * 4 - 2).astype(np.float32))
+        idx = np.stack([rng.permutation(V)[:3] for _ in range(T)]).astype(np.int32)
+        uv = n = s = None
+        if "uv" in name:
+            uv = rng.random((V, 2)).astype(np.float32)
+        if name == "degenerate_uv":
+            uv = np.repeat(rng.random((1, 2)).astype(np.float32), V, axis=0)   # all equal: determinant 0
+            uv[::7] += np.float32(1e-6)                                         # and almost equal
+        if "_n" in name or name in ("n_only", "reversed", "degenerate_uv", "zero_ns"):
+            n = rng.normal(size=(V, 3)).astype(np.float32)
+            n /= np.linalg.norm(n, axis=1, keepdims=True).astype(np.float32)
+            n = as_pbrt_stores(n.astype(np.float32))
+        if name == "zero_ns":
+            n[::3] = 0                                                          # LengthSquared(ns) == 0 paths
+        if "_s" in name:
+            s = as_pbrt_stores(rng.normal(size=(V, 3)).astype(np.float32))
+            s[::5] = 0                                                          # ss falls back to dpdu
+        tri = rng.integers(0, T, Q).astype(np.int32)
+        b = rng.random((Q, 3)).astype(np.float32)
+        b /= b.sum(axis=1, keepdims=True)
+        b[::11] = [1, 0, 0]
+        wo_time = rng.normal(size=(Q, 4)).astype(np.float32)
+        cases[name] = dict(verts=verts, idx=idx, uv=uv, n=n, s=s, tri=tri, b=b.astype(np.float32),
+                           wo_time=wo_time, reverse=(name == "reversed"))
+    return cases
+
+
+def interaction(ref):
+    out = {}
+    for name, c in interaction_cases(np.random.default_rng(884)).items():
+        out[name + "_want"] = ref.triangle_interaction(c["verts"], c["idx"], c["tri"], c["b"], c["wo_time"],
+                                                       normals=c["n"], tangents=c["s"], uvs=c["uv"],
+                                                       reverse_orientation=c["reverse"])
+        for k, v in c.items():   # the inputs travel with the answers
+            if v is not None:
+                out[name + "_" + k] = np.asarray(v)
+        print("interaction", name, out[name + "_want"].shape)
+    np.savez_compressed(os.path.join(OUT, "interaction.npz"), **out)
+
+
 if __name__ == "__main__":
     os.makedirs(OUT, exist_ok=True)
     ref = Reference(threads=1)
+    if "--only-interaction" in sys.argv:
+        interaction(ref)
+        sys.exit(0)
     if "--only-hlbvh" in sys.argv:
         hlbvh(ref)
         sys.exit(0)
@@ -198,3 +250,4 @@ if __name__ == "__main__":
     box_vectors(ref, rng)
     scene_small(ref, rng)
     hlbvh(ref)
+    interaction(ref)
