@@ -94,6 +94,29 @@ int nnbvh_build_bvh(const float *triVerts9, uint32_t nTris, int32_t maxPrimsInNo
                     int32_t splitMethod, int32_t nThreads, nnbvh_node *nodesOut,
                     uint32_t *nNodesOut, uint32_t *orderOut);
 
+/* The same builder over arbitrary primitives: bounds6 = nPrims * {pMin xyz, pMax xyz}, i.e. what
+ * Primitive::Bounds() returns for each entry of the std::vector<Primitive> handed to
+ * BVHAggregate (cpu/aggregates.cpp:150-153).  Triangles: Triangle::Bounds (shapes.cpp:294-301);
+ * spheres: nnbvh_sphere_bounds. */
+int nnbvh_build_bvh_bounds(const float *bounds6, uint32_t nPrims, int32_t maxPrimsInNode,
+                           int32_t splitMethod, int32_t nThreads, nnbvh_node *nodesOut,
+                           uint32_t *nNodesOut, uint32_t *orderOut);
+
+/* ---- sphere leaves (Sphere, shapes.h:107-340) ---------------------------------------------
+ * What `Shape "sphere"` hands to Sphere::Sphere (shapes.h:117-128): both transforms (rows 0..2 of
+ * the 4x4 matrices, row-major; row 3 must be 0 0 0 1) and radius / zmin / zmax / phimax as the
+ * scene file gives them (the constructor's clamping is applied by the library).  Spheres with
+ * phimax < 360 are rejected (NNBVH_ERR_INVALID): their clipping test compares std::atan2's
+ * result (shapes.h:194-203), which the device cannot reproduce bit for bit. */
+typedef struct nnbvh_sphere {
+    float renderFromObject[12];
+    float objectFromRender[12];
+    float radius, zMin, zMax, phiMax; /* phiMax in degrees */
+} nnbvh_sphere;
+
+/* Sphere::Bounds() (shapes.cpp:37-40), on the host: bounds6 = {pMin xyz, pMax xyz}. */
+int nnbvh_sphere_bounds(const nnbvh_sphere *s, float *bounds6);
+
 /* Maximum number of simultaneously stacked nodes any ray can need on this tree
  * (the reference's nodesToVisit[64], cpu/aggregates.cpp:538). */
 int nnbvh_tree_stack_depth(const nnbvh_node *nodes, uint32_t nNodes, uint32_t *depthOut);
@@ -161,6 +184,18 @@ int nnbvh_debug_step_stats(nnbvh_engine *e, uint64_t *out8);
 int nnbvh_upload_scene(nnbvh_engine *e, const nnbvh_node *nodes, uint32_t nNodes,
                        const float *orderedTriVerts9, uint32_t nPrims);
 
+/* nnbvh_upload_scene for a primitive list that mixes triangles and spheres (the killeroos scene's
+ * spherical light, crown's environment shell).  orderedSphereIndex[i] = -1 when ordered primitive
+ * i is a triangle (its 9 floats are read from orderedTriVerts9 as usual), else the index of its
+ * sphere in `spheres` (its 9 floats are ignored).  A hit on a sphere is reported as
+ * {prim, t = tHit, b0,b1,b2 = pObj.xyz}: QuadricIntersection (shapes.h:100-104) without phi,
+ * which is atan2(pObj.y, pObj.x) (+2*Pi when negative) on the host;
+ * Sphere::InteractionFromIntersection (shapes.h:239-300) takes it from there.  The per-ray
+ * counter triTests counts triangle tests only, as the reference's nTriTests does. */
+int nnbvh_upload_scene_mixed(nnbvh_engine *e, const nnbvh_node *nodes, uint32_t nNodes,
+                             const float *orderedTriVerts9, const int32_t *orderedSphereIndex,
+                             uint32_t nPrims, const nnbvh_sphere *spheres, uint32_t nSpheres);
+
 /* BVHAggregate::Intersect (cpu/aggregates.cpp:529-579) for n rays. */
 int nnbvh_intersect_closest(nnbvh_engine *e, const nnbvh_ray *rays, uint64_t n,
                             nnbvh_hit *hits);
@@ -201,6 +236,10 @@ int nnbvh_test_triangles(nnbvh_engine *e, const nnbvh_ray *rays, const float *tr
                          uint64_t n, uint8_t *hit, float *out4);
 int nnbvh_test_boxes(nnbvh_engine *e, const nnbvh_ray *rays, const float *boxes6,
                      uint64_t n, uint8_t *hit);
+/* Sphere::BasicIntersect (shapes.h:147-232) on n independent (ray, sphere) pairs.
+ * out4[i] = {tHit, pObj.x, pObj.y, pObj.z} where hit[i] != 0. */
+int nnbvh_test_spheres(nnbvh_engine *e, const nnbvh_ray *rays, const nnbvh_sphere *spheres,
+                       uint64_t n, uint8_t *hit, float *out4);
 
 const char *nnbvh_last_error(void);
 const char *nnbvh_version(void);

@@ -35,6 +35,59 @@ def build_bvh(tris9: np.ndarray, max_prims_in_node: int = 4, split_method: str =
     return nodes[:n.value].copy(), order
 
 
+SPHERE_DTYPE = np.dtype([("renderFromObject", "<f4", (12,)), ("objectFromRender", "<f4", (12,)),
+                         ("radius", "<f4"), ("zMin", "<f4"), ("zMax", "<f4"), ("phiMax", "<f4")])
+assert SPHERE_DTYPE.itemsize == 112   # nnbvh_sphere
+
+
+def make_spheres(render_from_object, radius, z_min=None, z_max=None, phi_max=360.0) -> np.ndarray:
+    """nnbvh_sphere records from (S,4,4) or (S,3,4) renderFromObject matrices and radii: what
+    `Shape "sphere"` under a CTM hands to Sphere::Sphere (shapes.h:117-128).  objectFromRender is
+    the float32 rounding of the float64 inverse (pbrt computes its own Inverse(m) in float; a caller
+    that needs pbrt's exact matrices fills the records itself)."""
+    m = np.asarray(render_from_object, dtype=np.float64).reshape(-1, *np.shape(render_from_object)[-2:])
+    full = np.tile(np.eye(4), (m.shape[0], 1, 1))
+    full[:, :m.shape[1], :] = m
+    radius = np.broadcast_to(np.asarray(radius, dtype=np.float32), (m.shape[0],))
+    s = np.zeros(m.shape[0], dtype=SPHERE_DTYPE)
+    s["renderFromObject"] = full[:, :3, :].reshape(-1, 12)
+    s["objectFromRender"] = np.linalg.inv(full)[:, :3, :].reshape(-1, 12)
+    s["radius"] = radius
+    s["zMin"] = -radius if z_min is None else z_min
+    s["zMax"] = radius if z_max is None else z_max
+    s["phiMax"] = phi_max
+    return s
+
+
+def sphere_bounds(spheres: np.ndarray) -> np.ndarray:
+    """Sphere::Bounds() (shapes.cpp:37-40) for each record: (S,6) float32."""
+    spheres = np.ascontiguousarray(spheres).view(SPHERE_DTYPE).reshape(-1)
+    out = np.zeros((len(spheres), 6), dtype=np.float32)
+    for i in range(len(spheres)):
+        capi.check(capi.lib().nnbvh_sphere_bounds(capi.ptr(spheres[i:i + 1]), capi.ptr(out[i])))
+    return out
+
+
+def triangle_bounds(tris9: np.ndarray) -> np.ndarray:
+    """Triangle::Bounds() (shapes.cpp:294-301): (T,6) float32."""
+    v = np.asarray(tris9, dtype=np.float32).reshape(-1, 3, 3)
+    return np.concatenate([v.min(axis=1), v.max(axis=1)], axis=1)
+
+
+def build_bvh_bounds(bounds6: np.ndarray, max_prims_in_node: int = 4, split_method: str = "sah",
+                     threads: int = 0):
+    """build_bvh over arbitrary primitives given their Bounds() (libnnbvh nnbvh_build_bvh_bounds)."""
+    bounds6 = np.ascontiguousarray(bounds6, dtype=np.float32).reshape(-1, 6)
+    P = bounds6.shape[0]
+    nodes = np.zeros(max(2 * P - 1, 1), dtype=NODE_DTYPE)
+    order = np.zeros(P, dtype=np.uint32)
+    n = ctypes.c_uint32(0)
+    capi.check(capi.lib().nnbvh_build_bvh_bounds(capi.ptr(bounds6), P, max_prims_in_node,
+                                                 capi.SPLIT[split_method], threads, capi.ptr(nodes),
+                                                 ctypes.byref(n), capi.ptr(order)))
+    return nodes[:n.value].copy(), order
+
+
 def build_hlbvh_device(tris9: np.ndarray, max_prims_in_node: int = 4, *, engine=None,
                        device: int = -1):
     """build_bvh(..., "hlbvh") with Morton codes, the radix sort and treelet emission on the GPU
@@ -85,14 +138,36 @@ class GPUBVHAggregate:
     def __init__(self, tris9: Optional[np.ndarray] = None, max_prims_in_node: int = 1,
                  split_method: str = "sah", *, nodes: Optional[np.ndarray] = None,
                  ordered_tris9: Optional[np.ndarray] = None, order: Optional[np.ndarray] = None,
-                 device: int = -1, kernel: int = capi.KERNEL_AUTO, smem_top_nodes: int = -1):
+                 device: int = -1, kernel: int = capi.KERNEL_AUTO, smem_top_nodes: int = -1,
+                 spheres: Optional[np.ndarray] = None,
+                 ordered_sphere_index: Optional[np.ndarray] = None):
         """Either tris9 (a soup to build over, like the reference ctor) or a ready
-        flattened tree: nodes + ordered_tris9 (e.g. an exported NN-split tree)."""
+        flattened tree: nodes + ordered_tris9 (e.g. an exported NN-split tree).
+
+        spheres (SPHERE_DTYPE records, see make_spheres): sphere primitives appended to the
+        primitive list after the triangles, i.e. caller primitive T + k is sphere k.  A hit on
+        one is reported as {prim, t, b = pObj} (include/nnbvh.h nnbvh_upload_scene_mixed).  With
+        a ready tree pass ordered_sphere_index (-1 = triangle) as well."""
         L = capi.lib()
         opts = capi.Options(device=device, kernel=kernel, smem_top_nodes=smem_top_nodes)
         h = ctypes.c_void_p()
         capi.check(L.nnbvh_create(ctypes.byref(opts), ctypes.byref(h)))
         self._h = h
+        self.spheres = None
+        self.ordered_sphere_index = None
+        if spheres is not None and len(spheres):
+            self.spheres = np.ascontiguousarray(spheres).view(SPHERE_DTYPE).reshape(-1)
+            if nodes is None:
+                tris9 = (np.zeros((0, 9), dtype=np.float32) if tris9 is None
+                         else np.ascontiguousarray(tris9, dtype=np.float32).reshape(-1, 9))
+                T = tris9.shape[0]
+                bounds = np.concatenate([triangle_bounds(tris9), sphere_bounds(self.spheres)])
+                nodes, order = build_bvh_bounds(bounds, max_prims_in_node, split_method)
+                ordered_sphere_index = np.where(order >= T, order.astype(np.int64) - T, -1).astype(np.int32)
+                ordered_tris9 = np.zeros((len(order), 9), dtype=np.float32)
+                is_tri = order < T
+                ordered_tris9[is_tri] = tris9[order[is_tri]]
+            self.ordered_sphere_index = np.ascontiguousarray(ordered_sphere_index, dtype=np.int32)
         if nodes is None:
             if tris9 is None or len(tris9) == 0:
                 # The reference CHECK(!primitives.empty())s; an empty aggregate here misses.
@@ -109,8 +184,13 @@ class GPUBVHAggregate:
         self.nodes = np.ascontiguousarray(nodes).view(NODE_DTYPE).reshape(-1)
         self.ordered_tris9 = np.ascontiguousarray(ordered_tris9, dtype=np.float32).reshape(-1, 9)
         self.order = order  # ordered prim -> caller's primitive id (None = identity)
-        capi.check(L.nnbvh_upload_scene(h, capi.ptr(self.nodes), len(self.nodes),
-                                        capi.ptr(self.ordered_tris9), len(self.ordered_tris9)))
+        if self.spheres is not None:
+            capi.check(L.nnbvh_upload_scene_mixed(h, capi.ptr(self.nodes), len(self.nodes),
+                                                  capi.ptr(self.ordered_tris9), capi.ptr(self.ordered_sphere_index),
+                                                  len(self.ordered_tris9), capi.ptr(self.spheres), len(self.spheres)))
+        else:
+            capi.check(L.nnbvh_upload_scene(h, capi.ptr(self.nodes), len(self.nodes),
+                                            capi.ptr(self.ordered_tris9), len(self.ordered_tris9)))
 
     @classmethod
     def Create(cls, tris9, parameters: Optional[dict] = None, **kw):

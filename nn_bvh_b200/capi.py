@@ -33,7 +33,8 @@ SYMBOLS = [
     "nnbvh_last_kernel_ms", "nnbvh_launch_count", "nnbvh_test_triangles", "nnbvh_test_boxes",
     "nnbvh_last_error", "nnbvh_version", "nnbvh_build_hlbvh_device", "nnbvh_debug_step_stats", "nnbvh_last_traversal_ms", "nnbvh_peer_alloc", "nnbvh_peer_open",
     "nnbvh_peer_close", "nnbvh_peer_free", "nnbvh_peer_copy", "nnbvh_read_bandwidth_probe",
-    "nnbvh_pointer_kind", "nnbvh_copy_to_host",
+    "nnbvh_pointer_kind", "nnbvh_copy_to_host", "nnbvh_build_bvh_bounds", "nnbvh_sphere_bounds",
+    "nnbvh_upload_scene_mixed", "nnbvh_test_spheres",
 ]
 
 
@@ -84,6 +85,10 @@ def lib() -> ctypes.CDLL:
     L.nnbvh_peer_copy.argtypes = [vp, vp, u64, vp]
     L.nnbvh_read_bandwidth_probe.argtypes = [vp, u64, u32, vp]
     L.nnbvh_pointer_kind.argtypes = [vp, vp]
+    L.nnbvh_build_bvh_bounds.argtypes = [vp, u32, i32, i32, i32, vp, vp, vp]
+    L.nnbvh_sphere_bounds.argtypes = [vp, vp]
+    L.nnbvh_upload_scene_mixed.argtypes = [vp, vp, u32, vp, vp, u32, vp, u32]
+    L.nnbvh_test_spheres.argtypes = [vp, vp, vp, u64, vp, vp]
     L.nnbvh_copy_to_host.argtypes = [vp, vp, u64]
     L.nnbvh_test_triangles.argtypes = [vp, vp, vp, u64, vp, vp]
     L.nnbvh_test_boxes.argtypes = [vp, vp, vp, u64, vp]

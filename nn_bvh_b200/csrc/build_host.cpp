@@ -350,13 +350,12 @@ void TriBox(const float *p, float *b6) {
     }
 }
 
-int BuildHLBVHHost(const float *tris9, uint32_t nTris, int maxLeaf, int nThreads,
+// box: 6 floats per primitive (Primitive::Bounds()), original order
+int BuildHLBVHHost(const std::vector<float> &box, uint32_t nTris, int maxLeaf, int nThreads,
                    nnbvh_node *nodesOut, uint32_t *nNodesOut, uint32_t *orderOut) {
-    std::vector<float> box(6 * (size_t)nTris);
     Aabb cb;
     for (uint32_t i = 0; i < nTris; ++i) {
-        float *b = &box[6 * (size_t)i];
-        TriBox(tris9 + 9 * (size_t)i, b);
+        const float *b = &box[6 * (size_t)i];
         float m[3] = {.5f * b[0] + .5f * b[3], .5f * b[1] + .5f * b[4], .5f * b[2] + .5f * b[5]};
         cb.Grow(m);
     }
@@ -417,31 +416,26 @@ int BuildHLBVHHost(const float *tris9, uint32_t nTris, int maxLeaf, int nThreads
 
 using namespace nnbvh;
 
-extern "C" int nnbvh_build_bvh(const float *triVerts9, uint32_t nTris, int32_t maxPrimsInNode,
-                               int32_t splitMethod, int32_t nThreads, nnbvh_node *nodesOut,
-                               uint32_t *nNodesOut, uint32_t *orderOut) {
-    if (!triVerts9 || !nodesOut || !nNodesOut || !orderOut || nTris == 0)
-        return SetError(NNBVH_ERR_INVALID, "nnbvh_build_bvh: null argument or empty soup "
-                                           "(the reference CHECKs !primitives.empty())");
+static int BuildFromBoxes(const std::vector<float> &box, uint32_t nPrims, int32_t maxPrimsInNode,
+                          int32_t splitMethod, int32_t nThreads, nnbvh_node *nodesOut,
+                          uint32_t *nNodesOut, uint32_t *orderOut) {
     if (splitMethod < NNBVH_SPLIT_SAH || splitMethod > NNBVH_SPLIT_EQUAL_COUNTS)
         return SetError(NNBVH_ERR_INVALID, "nnbvh_build_bvh: unknown split method %d", splitMethod);
-    if (nTris > (1u << 30))
-        return SetError(NNBVH_ERR_INVALID, "nnbvh_build_bvh: too many triangles");
+    if (nPrims > (1u << 30))
+        return SetError(NNBVH_ERR_INVALID, "nnbvh_build_bvh: too many primitives");
     if (splitMethod == NNBVH_SPLIT_HLBVH) {
         int nt = nThreads > 0 ? nThreads : (int)std::thread::hardware_concurrency();
-        return BuildHLBVHHost(triVerts9, nTris, std::min(255, (int)maxPrimsInNode), nt, nodesOut,
+        return BuildHLBVHHost(box, nPrims, std::min(255, (int)maxPrimsInNode), nt, nodesOut,
                               nNodesOut, orderOut);
     }
-    std::vector<Item> items(nTris);
-    for (uint32_t i = 0; i < nTris; ++i) {
-        // Triangle::Bounds = Union(Bounds3f(p0,p1), p2), shapes.cpp:294-301
-        const float *p = triVerts9 + 9 * (size_t)i;
+    std::vector<Item> items(nPrims);
+    for (uint32_t i = 0; i < nPrims; ++i) {
+        const float *b6 = &box[6 * (size_t)i];
         Aabb b;
         for (int k = 0; k < 3; ++k) {
-            b.lo[k] = std::min(p[k], p[3 + k]);
-            b.hi[k] = std::max(p[k], p[3 + k]);
+            b.lo[k] = b6[k];
+            b.hi[k] = b6[3 + k];
         }
-        b.Grow(p + 6);
         items[i].index = i;
         items[i].box = b;
     }
@@ -455,12 +449,69 @@ extern "C" int nnbvh_build_bvh(const float *triVerts9, uint32_t nTris, int32_t m
     int nt = nThreads > 0 ? nThreads : (int)std::thread::hardware_concurrency();
     int par = 0;
     while ((1 << par) < nt) ++par;
-    uint32_t total = BuildSpan(c, 0, nTris, 0, par);
+    uint32_t total = BuildSpan(c, 0, nPrims, 0, par);
     if (overflow.load())
         return SetError(NNBVH_ERR_INVALID, "nnbvh_build_bvh: a leaf holds >= 65536 primitives "
                                            "(the reference CHECKs nPrimitives < 65536)");
-    for (uint32_t i = 0; i < nTris; ++i) orderOut[i] = (uint32_t)items[i].index;
+    for (uint32_t i = 0; i < nPrims; ++i) orderOut[i] = (uint32_t)items[i].index;
     *nNodesOut = total;
+    return NNBVH_OK;
+}
+
+extern "C" int nnbvh_build_bvh(const float *triVerts9, uint32_t nTris, int32_t maxPrimsInNode,
+                               int32_t splitMethod, int32_t nThreads, nnbvh_node *nodesOut,
+                               uint32_t *nNodesOut, uint32_t *orderOut) {
+    if (!triVerts9 || !nodesOut || !nNodesOut || !orderOut || nTris == 0)
+        return SetError(NNBVH_ERR_INVALID, "nnbvh_build_bvh: null argument or empty soup "
+                                           "(the reference CHECKs !primitives.empty())");
+    if (nTris > (1u << 30))
+        return SetError(NNBVH_ERR_INVALID, "nnbvh_build_bvh: too many triangles");
+    std::vector<float> box(6 * (size_t)nTris);
+    for (uint32_t i = 0; i < nTris; ++i) TriBox(triVerts9 + 9 * (size_t)i, &box[6 * (size_t)i]);
+    return BuildFromBoxes(box, nTris, maxPrimsInNode, splitMethod, nThreads, nodesOut, nNodesOut, orderOut);
+}
+
+extern "C" int nnbvh_build_bvh_bounds(const float *bounds6, uint32_t nPrims, int32_t maxPrimsInNode,
+                                      int32_t splitMethod, int32_t nThreads, nnbvh_node *nodesOut,
+                                      uint32_t *nNodesOut, uint32_t *orderOut) {
+    if (!bounds6 || !nodesOut || !nNodesOut || !orderOut || nPrims == 0)
+        return SetError(NNBVH_ERR_INVALID, "nnbvh_build_bvh_bounds: null argument or no primitives "
+                                           "(the reference CHECKs !primitives.empty())");
+    if (nPrims > (1u << 30))
+        return SetError(NNBVH_ERR_INVALID, "nnbvh_build_bvh_bounds: too many primitives");
+    std::vector<float> box(bounds6, bounds6 + 6 * (size_t)nPrims);
+    return BuildFromBoxes(box, nPrims, maxPrimsInNode, splitMethod, nThreads, nodesOut, nNodesOut, orderOut);
+}
+
+// Sphere::Bounds (shapes.cpp:37-40) = renderFromObject(Bounds3f((-r,-r,zMin), (r,r,zMax))):
+// Transform::operator()(Bounds3f) unions the eight transformed corners (util/transform.cpp:134-139),
+// each through Transform::operator()(Point3f) (util/transform.h:310-319, w == 1 for an affine matrix).
+extern "C" int nnbvh_sphere_bounds(const nnbvh_sphere *s, float *bounds6) {
+    if (!s || !bounds6) return SetError(NNBVH_ERR_INVALID, "nnbvh_sphere_bounds: NULL argument");
+    const float r = s->radius;
+    // the constructor's clamp, shapes.h:124-125 (Clamp: util/math.h, `val < low ? low : val > high ? high : val`)
+    auto clamp = [](float v, float lo, float hi) { return v < lo ? lo : (v > hi ? hi : v); };
+    const float zMin = clamp(std::min(s->zMin, s->zMax), -r, r), zMax = clamp(std::max(s->zMin, s->zMax), -r, r);
+    const float lo[3] = {-r, -r, zMin}, hi[3] = {r, r, zMax};
+    // Bounds3f(p1, p2) takes Min / Max of its arguments (vecmath.h:1268-1270)
+    const float bl[3] = {std::min(lo[0], hi[0]), std::min(lo[1], hi[1]), std::min(lo[2], hi[2])};
+    const float bh[3] = {std::max(lo[0], hi[0]), std::max(lo[1], hi[1]), std::max(lo[2], hi[2])};
+    float mn[3], mx[3];
+    for (int k = 0; k < 3; ++k) {  // Bounds3(): pMin = max float, pMax = lowest (vecmath.h:1259-1264)
+        mn[k] = std::numeric_limits<float>::max();
+        mx[k] = std::numeric_limits<float>::lowest();
+    }
+    const float *m = s->renderFromObject;
+    for (int c = 0; c < 8; ++c) {  // Corner(c), vecmath.h:1284-1288
+        const float x = (c & 1) ? bh[0] : bl[0], y = (c & 2) ? bh[1] : bl[1], z = (c & 4) ? bh[2] : bl[2];
+        const float q[3] = {m[0] * x + m[1] * y + m[2] * z + m[3], m[4] * x + m[5] * y + m[6] * z + m[7],
+                            m[8] * x + m[9] * y + m[10] * z + m[11]};
+        for (int k = 0; k < 3; ++k) {
+            mn[k] = std::min(mn[k], q[k]);
+            mx[k] = std::max(mx[k], q[k]);
+        }
+    }
+    for (int k = 0; k < 3; ++k) bounds6[k] = mn[k], bounds6[3 + k] = mx[k];
     return NNBVH_OK;
 }
 

@@ -119,6 +119,8 @@ struct nnbvh_engine {
     DevBuf<nnbvh_node> dNodes;
     DevBuf<WideNode> dWide;
     DevBuf<float4> dTris;
+    DevBuf<SphereDev> dSpheres;
+    bool hasSpheres = false;  // scene uploaded with spheres: the SPHERES instantiations run
     // device-pointer path scratch
     Scratch scratch;
     // host-pointer pipeline
@@ -226,6 +228,7 @@ extern "C" void nnbvh_destroy(nnbvh_engine *e) {
     e->dNodes.Free();
     e->dWide.Free();
     e->dTris.Free();
+    e->dSpheres.Free();
     if (e->dStats) cudaFree(e->dStats);
     e->scratch.Free();
     for (Slot &s : e->slots) {
@@ -303,10 +306,19 @@ static bool IsDevicePtr(const void *p) {
 }
 
 // in9: nPrims*9 floats (ordered); last: 1 where the primitive ends its leaf.
+// sphereOf (optional): >= 0 marks a sphere slot, the value is its index in the sphere table.
 __global__ void PackTrisKernel(const float *__restrict__ in9, const uint8_t *__restrict__ last,
-                               uint32_t nPrims, float4 *__restrict__ out) {
+                               const int32_t *__restrict__ sphereOf, uint32_t nPrims,
+                               float4 *__restrict__ out) {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= nPrims) return;
+    if (sphereOf && sphereOf[i] >= 0) {
+        out[3 * (size_t)i + 0] = make_float4(__uint_as_float((uint32_t)sphereOf[i]), 0.f, 0.f,
+                                             __uint_as_float(kPrimSphere | (last[i] ? kTriLast : 0u)));
+        out[3 * (size_t)i + 1] = make_float4(0.f, 0.f, 0.f, 0.f);
+        out[3 * (size_t)i + 2] = make_float4(0.f, 0.f, 0.f, 0.f);
+        return;
+    }
     const float *p = in9 + 9 * (size_t)i;
     float v[9];
 #pragma unroll
@@ -395,11 +407,53 @@ static int BuildWideLayout(const std::vector<nnbvh_node> &nodes, uint32_t nPrims
 
 }  // namespace nnbvh
 
+// Sphere::Sphere (shapes.h:117-128): the clamped zMin / zMax the intersection routine uses.
+static int MakeSphereDev(const nnbvh_sphere &s, uint32_t index, SphereDev *out) {
+    for (int k = 0; k < 12; ++k)
+        if (!std::isfinite(s.objectFromRender[k]) || !std::isfinite(s.renderFromObject[k]))
+            return SetError(NNBVH_ERR_INVALID, "sphere %u: non-finite transform", index);
+    if (!(s.radius > 0.f) || !std::isfinite(s.radius))
+        return SetError(NNBVH_ERR_INVALID, "sphere %u: radius %g", index, (double)s.radius);
+    // Clamp(phiMax, 0, 360) < 360 clips by std::atan2's value (shapes.h:194-203): not reproducible here
+    if (!(s.phiMax >= 360.f))
+        return SetError(NNBVH_ERR_INVALID, "sphere %u: phimax %g < 360 is not supported (the clipping "
+                                           "test depends on std::atan2 bit for bit)", index, (double)s.phiMax);
+    auto clamp = [](float v, float lo, float hi) { return v < lo ? lo : (v > hi ? hi : v); };
+    for (int k = 0; k < 12; ++k) out->m[k] = s.objectFromRender[k];
+    out->radius = s.radius;
+    out->zMin = clamp(std::min(s.zMin, s.zMax), -s.radius, s.radius);
+    out->zMax = clamp(std::max(s.zMin, s.zMax), -s.radius, s.radius);
+    out->pad = 0.f;
+    return NNBVH_OK;
+}
+
+static int UploadScene(nnbvh_engine *e, const nnbvh_node *nodes, uint32_t nNodes,
+                       const float *orderedTriVerts9, uint32_t nPrims, const int32_t *sphereOf,
+                       const nnbvh_sphere *spheres, uint32_t nSpheres);
+
 extern "C" int nnbvh_upload_scene(nnbvh_engine *e, const nnbvh_node *nodes, uint32_t nNodes,
                                   const float *orderedTriVerts9, uint32_t nPrims) {
+    return UploadScene(e, nodes, nNodes, orderedTriVerts9, nPrims, nullptr, nullptr, 0);
+}
+
+extern "C" int nnbvh_upload_scene_mixed(nnbvh_engine *e, const nnbvh_node *nodes, uint32_t nNodes,
+                                        const float *orderedTriVerts9, const int32_t *orderedSphereIndex,
+                                        uint32_t nPrims, const nnbvh_sphere *spheres, uint32_t nSpheres) {
+    if (nSpheres && (!spheres || !orderedSphereIndex))
+        return SetError(NNBVH_ERR_INVALID, "nnbvh_upload_scene_mixed: NULL sphere table / index");
+    if (IsDevicePtr(orderedSphereIndex) || IsDevicePtr(spheres))
+        return SetError(NNBVH_ERR_INVALID, "nnbvh_upload_scene_mixed: the sphere table and index are host arrays");
+    return UploadScene(e, nodes, nNodes, orderedTriVerts9, nPrims, nSpheres ? orderedSphereIndex : nullptr,
+                       spheres, nSpheres);
+}
+
+static int UploadScene(nnbvh_engine *e, const nnbvh_node *nodes, uint32_t nNodes,
+                       const float *orderedTriVerts9, uint32_t nPrims, const int32_t *sphereOf,
+                       const nnbvh_sphere *spheres, uint32_t nSpheres) {
     if (!e) return SetError(NNBVH_ERR_INVALID, "nnbvh_upload_scene: engine is NULL");
     CU(cudaSetDevice(e->device));
     e->haveScene = false;
+    e->hasSpheres = false;
     if (nNodes == 0) {  // `nodes == nullptr` in the reference: every ray misses
         e->sc = SceneDev{};
         e->haveScene = true;
@@ -449,12 +503,34 @@ extern "C" int nnbvh_upload_scene(nnbvh_engine *e, const nnbvh_node *nodes, uint
     }
     CU(cudaMalloc(&dLast, nPrims));
     CU(cudaMemcpyAsync(dLast, last.data(), nPrims, cudaMemcpyHostToDevice, st));
-    PackTrisKernel<<<(nPrims + 255) / 256, 256, 0, st>>>(src, dLast, nPrims, e->dTris.p);
+    int32_t *dSphereOf = nullptr;
+    if (sphereOf) {
+        std::vector<SphereDev> sd(nSpheres);
+        for (uint32_t i = 0; i < nSpheres; ++i) {
+            rc = MakeSphereDev(spheres[i], i, &sd[i]);
+            if (rc) break;
+        }
+        for (uint32_t i = 0; !rc && i < nPrims; ++i)
+            if (sphereOf[i] >= (int32_t)nSpheres)
+                rc = SetError(NNBVH_ERR_INVALID, "primitive %u refers to sphere %d of %u", i, sphereOf[i], nSpheres);
+        if (!rc) rc = e->dSpheres.Reserve(nSpheres);
+        if (rc) {
+            if (dRaw) cudaFree(dRaw);
+            cudaFree(dLast);
+            return rc;
+        }
+        CU(cudaMemcpyAsync(e->dSpheres.p, sd.data(), sizeof(SphereDev) * nSpheres, cudaMemcpyHostToDevice, st));
+        CU(cudaMalloc(&dSphereOf, sizeof(int32_t) * (size_t)nPrims));
+        CU(cudaMemcpyAsync(dSphereOf, sphereOf, sizeof(int32_t) * (size_t)nPrims, cudaMemcpyHostToDevice, st));
+        CU(cudaStreamSynchronize(st));  // sd goes out of scope
+    }
+    PackTrisKernel<<<(nPrims + 255) / 256, 256, 0, st>>>(src, dLast, dSphereOf, nPrims, e->dTris.p);
     ++e->launches;
     CU(cudaGetLastError());
     CU(cudaStreamSynchronize(st));
     if (dRaw) cudaFree(dRaw);
     cudaFree(dLast);
+    if (dSphereOf) cudaFree(dSphereOf);
     SceneDev sc{};
     sc.nodes = e->dNodes.p;
     sc.wide = e->dWide.p;
@@ -465,7 +541,9 @@ extern "C" int nnbvh_upload_scene(nnbvh_engine *e, const nnbvh_node *nodes, uint
     for (int k = 0; k < 6; ++k) sc.rootBox[k] = h[0].bounds[k];
     sc.rootRef = rootRef;
     sc.topNodes = topNodes;
+    sc.spheres = sphereOf ? e->dSpheres.p : nullptr;
     e->sc = sc;
+    e->hasSpheres = sphereOf != nullptr;
     e->haveScene = true;
     return NNBVH_OK;
 }
@@ -506,6 +584,10 @@ static int LaunchWide(nnbvh_engine *e, cudaStream_t st, const WideParams &p, uin
 
 template <bool ANY, bool EXACT>
 static void LaunchStep(nnbvh_engine *e, cudaStream_t st, const StepParams &p) {
+    if (e->hasSpheres) {  // sphere leaves: one instantiation, 4 CTAs/SM (the sphere test wants registers)
+        StepKernel<ANY, EXACT, 4, false, true><<<e->numSMs * 4, 256, 0, st>>>(p);
+        return;
+    }
     if (p.stats && !EXACT) {  // NNBVH_STEP_STATS=1: lane-occupancy counters (diagnostic build of the kernel)
         StepKernel<ANY, false, 5, true><<<e->numSMs * 5, 256, 0, st>>>(p);
         return;
@@ -531,7 +613,15 @@ static int LaunchTraversal(nnbvh_engine *e, cudaStream_t st, bool any, bool coun
         if (n > (uint64_t)0x7fffffff * 128)
             return SetError(NNBVH_ERR_INVALID, "batch too large for one launch");
         unsigned grid = (unsigned)((n + 127) / 128);
-        if (counters) {
+        if (e->hasSpheres) {
+            if (counters) {
+                if (any) BasicKernel<true, true, true><<<grid, 128, 0, st>>>(e->sc, in, n, o.hits, o.occ, o.nodesVisited, o.triTests);
+                else BasicKernel<false, true, true><<<grid, 128, 0, st>>>(e->sc, in, n, o.hits, o.occ, o.nodesVisited, o.triTests);
+            } else {
+                if (any) BasicKernel<true, false, true><<<grid, 128, 0, st>>>(e->sc, in, n, o.hits, o.occ, nullptr, nullptr);
+                else BasicKernel<false, false, true><<<grid, 128, 0, st>>>(e->sc, in, n, o.hits, o.occ, nullptr, nullptr);
+            }
+        } else if (counters) {
             if (any) BasicKernel<true, true><<<grid, 128, 0, st>>>(e->sc, in, n, o.hits, o.occ, o.nodesVisited, o.triTests);
             else BasicKernel<false, true><<<grid, 128, 0, st>>>(e->sc, in, n, o.hits, o.occ, o.nodesVisited, o.triTests);
         } else {
@@ -549,7 +639,7 @@ static int LaunchTraversal(nnbvh_engine *e, cudaStream_t st, bool any, bool coun
         // binMode 1: always sort; 2: the device decides per batch (StepKernel only, which reads
         // the flag); 0: off.
         const uint32_t *perm = nullptr, *permOn = nullptr;
-        const bool stepKernel = e->kernel != NNBVH_KERNEL_WIDE;
+        const bool stepKernel = e->kernel != NNBVH_KERNEL_WIDE || e->hasSpheres;  // WideKernel has no sphere leaves
         if ((e->binMode == 1 || (e->binMode == 2 && stepKernel && e->sc.nNodes >= e->binMinNodes)) &&
             n >= e->binMinRays && n < 0xffffffffull && e->sc.nNodes) {
             BinParams bp;
@@ -608,7 +698,7 @@ static int LaunchTraversal(nnbvh_engine *e, cudaStream_t st, bool any, bool coun
                 permOn = flag;
             }
         }
-        if (e->kernel != NNBVH_KERNEL_WIDE) {
+        if (stepKernel) {
             // ---- StepKernel: fast-slab launch, then the exact launch over the deferred rays ----
             if (n > 0xffffffffull)
                 return SetError(NNBVH_ERR_INVALID, "batch too large for one launch");
@@ -961,6 +1051,49 @@ extern "C" int nnbvh_test_boxes(nnbvh_engine *e, const nnbvh_ray *rays, const fl
     CU(cudaStreamSynchronize(e->stream));
     CU(cudaMemcpy(hit, dH, n, cudaMemcpyDeviceToHost));
     cudaFree(dR); cudaFree(dB); cudaFree(dH);
+    return NNBVH_OK;
+}
+
+namespace nnbvh {
+__global__ void TestSpheresKernel(const float4 *__restrict__ rays, const SphereDev *__restrict__ spheres,
+                                  uint64_t n, uint8_t *__restrict__ hit, float4 *__restrict__ out) {
+    uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float4 a = rays[2 * i], b = rays[2 * i + 1];
+    SphereHit sh{0.f, 0.f, 0.f, 0.f};
+    const bool ok = SphereTest(spheres + i, a.x, a.y, a.z, b.x, b.y, b.z, a.w, &sh);
+    hit[i] = ok ? 1 : 0;
+    out[i] = ok ? make_float4(sh.t, sh.px, sh.py, sh.pz) : make_float4(0.f, 0.f, 0.f, 0.f);
+}
+}  // namespace nnbvh
+
+extern "C" int nnbvh_test_spheres(nnbvh_engine *e, const nnbvh_ray *rays, const nnbvh_sphere *spheres,
+                                  uint64_t n, uint8_t *hit, float *out4) {
+    if (!e || !rays || !spheres || !hit || !out4)
+        return SetError(NNBVH_ERR_INVALID, "nnbvh_test_spheres: NULL argument");
+    if (n == 0) return NNBVH_OK;
+    CU(cudaSetDevice(e->device));
+    std::vector<SphereDev> sd(n);
+    for (uint64_t i = 0; i < n; ++i) {
+        int rc = MakeSphereDev(spheres[i], (uint32_t)i, &sd[i]);
+        if (rc) return rc;
+    }
+    float4 *dR = nullptr, *dO = nullptr;
+    SphereDev *dS = nullptr;
+    uint8_t *dH = nullptr;
+    CU(cudaMalloc(&dR, n * 32));
+    CU(cudaMalloc(&dS, n * sizeof(SphereDev)));
+    CU(cudaMalloc(&dH, n));
+    CU(cudaMalloc(&dO, n * 16));
+    CU(cudaMemcpy(dR, rays, n * 32, cudaMemcpyHostToDevice));
+    CU(cudaMemcpy(dS, sd.data(), n * sizeof(SphereDev), cudaMemcpyHostToDevice));
+    TestSpheresKernel<<<(unsigned)((n + 127) / 128), 128, 0, e->stream>>>(dR, dS, n, dH, dO);
+    ++e->launches;
+    CU(cudaGetLastError());
+    CU(cudaStreamSynchronize(e->stream));
+    CU(cudaMemcpy(hit, dH, n, cudaMemcpyDeviceToHost));
+    CU(cudaMemcpy(out4, dO, n * 16, cudaMemcpyDeviceToHost));
+    cudaFree(dR); cudaFree(dS); cudaFree(dH); cudaFree(dO);
     return NNBVH_OK;
 }
 

@@ -36,6 +36,7 @@ static_assert(sizeof(WideNode) == 64, "WideNode must be 64 bytes");
 // PackedTri: 48 bytes = 3 x float4 {p0.xyz, flags}, {p1.xyz, 0}, {p2.xyz, 0}.
 constexpr uint32_t kTriDegenerate = 1u;  // shapes.cpp:176 reject, evaluated at upload
 constexpr uint32_t kTriLast = 2u;        // last primitive of its leaf
+constexpr uint32_t kPrimSphere = 4u;     // the slot is a sphere: .x of the first float4 = index into the sphere table
 constexpr int kMaxStack = 64;            // cpu/aggregates.cpp:538
 
 

@@ -25,6 +25,7 @@
 
 #include "exact_math.cuh"
 #include "internal.h"
+#include "sphere.cuh"
 
 namespace nnbvh {
 
@@ -37,6 +38,7 @@ struct SceneDev {
     float rootBox[6];
     int32_t rootRef;          // WideNode index (>=0) or leaf ref (<0) of the root
     uint32_t topNodes;        // WideNodes [0, topNodes) are the BFS top of the tree
+    const SphereDev *spheres; // sphere table (scenes uploaded with nnbvh_upload_scene_mixed), else NULL
 };
 
 struct RayInput {
@@ -78,15 +80,32 @@ __device__ __forceinline__ void StoreHit(nnbvh_hit *hits, uint64_t i, const HitR
 
 // Tests the primitives of one leaf in order, each against the CURRENT tMax
 // (aggregates.cpp:547-555).  Returns true as soon as ANY finds a hit.
-template <bool ANY, bool COUNT>
+template <bool ANY, bool COUNT, bool SPHERES>
 __device__ __forceinline__ bool LeafTest(const float4 *__restrict__ tris, uint32_t first,
                                          const RayConst &rc, float &tMax, HitRegs &hit,
-                                         uint32_t &triTests) {
+                                         uint32_t &triTests, const SphereDev *__restrict__ spheres) {
     uint32_t prim = first;
     while (true) {
         const float4 *tp = tris + 3 * (size_t)prim;
         float4 v0 = __ldg(tp), v1 = __ldg(tp + 1), v2 = __ldg(tp + 2);
         uint32_t flags = __float_as_uint(v0.w);
+        if (SPHERES && (flags & kPrimSphere)) {
+            // Sphere::Intersect / IntersectP (shapes.h:137-145, 234-236); nTriTests counts triangles only
+            SphereHit sh;
+            if (SphereTest(spheres + __float_as_uint(v0.x), rc.ox, rc.oy, rc.oz, rc.dx, rc.dy, rc.dz,
+                           tMax, &sh)) {
+                if (ANY) return true;
+                hit.prim = prim;
+                hit.t = sh.t;
+                hit.b0 = sh.px;
+                hit.b1 = sh.py;
+                hit.b2 = sh.pz;
+                tMax = sh.t;
+            }
+            if (flags & kTriLast) break;
+            ++prim;
+            continue;
+        }
         if (COUNT) ++triTests;
         if (!(flags & kTriDegenerate)) {
             float t, b0, b1, b2;
@@ -110,7 +129,7 @@ __device__ __forceinline__ bool LeafTest(const float4 *__restrict__ tris, uint32
 // ---------------------------------------------------------------------------
 // BasicKernel: cpu/aggregates.cpp:529-624 per thread.
 // ---------------------------------------------------------------------------
-template <bool ANY, bool COUNT>
+template <bool ANY, bool COUNT, bool SPHERES = false>
 __global__ void __launch_bounds__(128)
 BasicKernel(SceneDev sc, RayInput in, uint64_t n, nnbvh_hit *__restrict__ hits,
             uint8_t *__restrict__ occluded, uint32_t *__restrict__ nodesVisitedOut,
@@ -137,7 +156,7 @@ BasicKernel(SceneDev sc, RayInput in, uint64_t n, nnbvh_hit *__restrict__ hits,
             uint32_t nPrims = meta & 0xffffu, axis = (meta >> 16) & 0xffu;
             if (SlabTest(rc, box, tMax)) {
                 if (nPrims > 0) {
-                    if (LeafTest<ANY, COUNT>(sc.tris, (uint32_t)offset, rc, tMax, hit, triTests)) {
+                    if (LeafTest<ANY, COUNT, SPHERES>(sc.tris, (uint32_t)offset, rc, tMax, hit, triTests, sc.spheres)) {
                         any = true;
                         break;
                     }
@@ -383,7 +402,7 @@ __global__ void __launch_bounds__(256, MINB) WideKernel(WideParams p) {
 
         // ---- phase B: leaves (all parked lanes together) ----
         if (alive && cur < 0) {
-            if (LeafTest<ANY, false>(tris, (uint32_t)cur & 0x7fffffffu, rc, tMax, hit, dummy)) {
+            if (LeafTest<ANY, false, false>(tris, (uint32_t)cur & 0x7fffffffu, rc, tMax, hit, dummy, nullptr)) {
                 alive = false;  // ANY: first accepted primitive ends the ray (:598-601)
                 p.occluded[rayIdx] = 1;
             } else {

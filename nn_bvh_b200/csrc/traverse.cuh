@@ -94,7 +94,7 @@ __device__ __forceinline__ RayConst ToRayConst(const StepRay &s) {
 
 constexpr float kNegInf = -__builtin_huge_valf();
 
-template <bool ANY, bool EXACT, int MINB, bool STATS = false>
+template <bool ANY, bool EXACT, int MINB, bool STATS = false, bool SPHERES = false>
 __global__ void __launch_bounds__(256, MINB) StepKernel(StepParams p) {
     // STATS: [0] phase-A iterations, [1] lanes at a node, [2] lanes parked at a leaf, [3] lanes without
     // a ray, [4] phase-B passes, [5] lanes parked there, [6] lanes that ran a triangle test, [7] refills
@@ -311,7 +311,22 @@ __global__ void __launch_bounds__(256, MINB) StepKernel(StepParams p) {
                 const float4 v0 = __ldg(tp), v1 = __ldg(tp + 1), v2 = __ldg(tp + 2);
                 const uint32_t flags = __float_as_uint(v0.w);
                 bool found = false;
-                if (!(flags & kTriDegenerate)) {
+                if (SPHERES && (flags & kPrimSphere)) {
+                    // Sphere::Intersect / IntersectP (shapes.h:137-145, 234-236).  The lane keeps no
+                    // direction (it is folded into invDir and the shear): the ray is read again.
+                    const RayRegs rr = LoadRay(p.in, rayIdx);
+                    SphereHit sh;
+                    if (SphereTest(sc.spheres + __float_as_uint(v0.x), rr.ox, rr.oy, rr.oz, rr.dx, rr.dy,
+                                   rr.dz, tMax, &sh)) {
+                        found = true;
+                        hit.prim = prim;
+                        hit.t = sh.t;
+                        hit.b0 = sh.px;
+                        hit.b1 = sh.py;
+                        hit.b2 = sh.pz;
+                        tMax = sh.t;
+                    }
+                } else if (!(flags & kTriDegenerate)) {
                     RayConst rc = ToRayConst(ry);
                     float t, b0, b1, b2;
                     if (TriangleTest(rc, tMax, v0.x, v0.y, v0.z, v1.x, v1.y, v1.z, v2.x, v2.y, v2.z,

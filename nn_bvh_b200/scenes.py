@@ -108,6 +108,24 @@ def _camera_from_meta(meta: dict, tris: np.ndarray) -> dict:
     return out
 
 
+def load_spheres(name: str):
+    """The scene's `Shape "sphere"` primitives (killeroos: the spherical light; crown: the
+    environment shell) as nnbvh_sphere records, or None.  They are NOT part of load()'s soup."""
+    mp = os.path.join(CACHE, name + ".json")
+    if not os.path.exists(mp):
+        return None
+    with open(mp) as f:
+        sph = json.load(f).get("spheres") or []
+    if not sph:
+        return None
+    from .aggregate import make_spheres
+    return make_spheres(np.array([s["render_from_object"] for s in sph]),
+                        np.array([s["radius"] for s in sph], dtype=np.float32),
+                        np.array([s["zmin"] for s in sph], dtype=np.float32),
+                        np.array([s["zmax"] for s in sph], dtype=np.float32),
+                        np.array([s["phimax"] for s in sph], dtype=np.float32))
+
+
 def load(name: str, allow_procedural: bool = True):
     """-> (tris9 float32 (T,9), camera dict, workload name actually loaded)."""
     path = os.path.join(CACHE, name + ".tris.npy")

@@ -601,9 +601,217 @@ inline bool TriangleIntersect(const RayCtx &r, float tMax, const float *p, float
     return true;
 }
 
+// ---- Sphere::BasicIntersect, shapes.h:147-232 ---------------------------------------------------
+// Interval as the reference's HOST build evaluates it: outward rounding is one float step past
+// the round-to-nearest result (util/float.h:199-320, the non-GPU branches).
+inline float NextFloatUp(float v) {  // util/float.h:164-177
+    if (std::isinf(v) && v > 0.f)
+        return v;
+    if (v == -0.f)
+        v = 0.f;
+    uint32_t ui;
+    std::memcpy(&ui, &v, 4);
+    if (v >= 0)
+        ++ui;
+    else
+        --ui;
+    std::memcpy(&v, &ui, 4);
+    return v;
+}
+inline float NextFloatDown(float v) {  // util/float.h:179-193
+    if (std::isinf(v) && v < 0.f)
+        return v;
+    if (v == 0.f)
+        v = -0.f;
+    uint32_t ui;
+    std::memcpy(&ui, &v, 4);
+    if (v > 0)
+        --ui;
+    else
+        ++ui;
+    std::memcpy(&v, &ui, 4);
+    return v;
+}
+inline float AddRoundUp(float a, float b) { return NextFloatUp(a + b); }
+inline float AddRoundDown(float a, float b) { return NextFloatDown(a + b); }
+inline float SubRoundUp(float a, float b) { return AddRoundUp(a, -b); }
+inline float SubRoundDown(float a, float b) { return AddRoundDown(a, -b); }
+inline float MulRoundUp(float a, float b) { return NextFloatUp(a * b); }
+inline float MulRoundDown(float a, float b) { return NextFloatDown(a * b); }
+inline float DivRoundUp(float a, float b) { return NextFloatUp(a / b); }
+inline float DivRoundDown(float a, float b) { return NextFloatDown(a / b); }
+inline float SqrtRoundUp(float a) { return NextFloatUp(std::sqrt(a)); }
+inline float SqrtRoundDown(float a) { return std::max<float>(0, NextFloatDown(std::sqrt(a))); }
+
+struct Interval {  // util/math.h:819-935
+    float low, high;
+    Interval() : low(0), high(0) {}
+    explicit Interval(float v) : low(v), high(v) {}
+    Interval(float l, float h) : low(std::min(l, h)), high(std::max(l, h)) {}
+    static Interval FromValueAndError(float v, float err) {
+        Interval i;
+        if (err == 0)
+            i.low = i.high = v;
+        else {
+            i.low = SubRoundDown(v, err);
+            i.high = AddRoundUp(v, err);
+        }
+        return i;
+    }
+    float Midpoint() const { return (low + high) / 2; }
+    Interval operator+(Interval i) const { return {AddRoundDown(low, i.low), AddRoundUp(high, i.high)}; }
+    Interval operator-(Interval i) const { return {SubRoundDown(low, i.high), SubRoundUp(high, i.low)}; }
+    Interval operator*(Interval i) const {
+        float lp[4] = {MulRoundDown(low, i.low), MulRoundDown(high, i.low), MulRoundDown(low, i.high),
+                       MulRoundDown(high, i.high)};
+        float hp[4] = {MulRoundUp(low, i.low), MulRoundUp(high, i.low), MulRoundUp(low, i.high),
+                       MulRoundUp(high, i.high)};
+        return {std::min({lp[0], lp[1], lp[2], lp[3]}), std::max({hp[0], hp[1], hp[2], hp[3]})};
+    }
+    Interval operator/(Interval i) const {  // :961-973
+        if (0 >= i.low && 0 <= i.high)
+            return Interval(-kInfinity, kInfinity);
+        float lq[4] = {DivRoundDown(low, i.low), DivRoundDown(high, i.low), DivRoundDown(low, i.high),
+                       DivRoundDown(high, i.high)};
+        float hq[4] = {DivRoundUp(low, i.low), DivRoundUp(high, i.low), DivRoundUp(low, i.high),
+                       DivRoundUp(high, i.high)};
+        return {std::min({lq[0], lq[1], lq[2], lq[3]}), std::max({hq[0], hq[1], hq[2], hq[3]})};
+    }
+    bool operator==(Interval i) const { return low == i.low && high == i.high; }
+};
+inline Interval Sqr(Interval i) {  // :975-982
+    float alow = std::abs(i.low), ahigh = std::abs(i.high);
+    if (alow > ahigh)
+        std::swap(alow, ahigh);
+    if (0 >= i.low && 0 <= i.high)
+        return Interval(0, MulRoundUp(ahigh, ahigh));
+    return Interval(MulRoundDown(alow, alow), MulRoundUp(ahigh, ahigh));
+}
+inline Interval operator*(float f, Interval i) {  // :995-1000
+    if (f > 0)
+        return Interval(MulRoundDown(f, i.low), MulRoundUp(f, i.high));
+    return Interval(MulRoundDown(f, i.high), MulRoundUp(f, i.low));
+}
+inline Interval Sqrt(Interval i) { return {SqrtRoundDown(i.low), SqrtRoundUp(i.high)}; }  // :1070-1072
+
+// nnbvh_sphere as 28 floats: renderFromObject[12], objectFromRender[12], radius, zMin, zMax, phiMax.
+struct SphereCtx {
+    const float *m;  // objectFromRender rows 0..2 (row 3 = 0 0 0 1)
+    float radius, zMin, zMax;
+};
+inline float Clamp(float v, float lo, float hi) { return v < lo ? lo : (v > hi ? hi : v); }
+inline SphereCtx MakeSphereCtx(const float *s28) {  // Sphere::Sphere, shapes.h:117-128
+    SphereCtx c;
+    c.m = s28 + 12;
+    c.radius = s28[24];
+    c.zMin = Clamp(std::min(s28[25], s28[26]), -c.radius, c.radius);
+    c.zMax = Clamp(std::max(s28[25], s28[26]), -c.radius, c.radius);
+    return c;
+}
+
+// phiMax is 360 for every sphere this restatement accepts: `phi > phiMax` (shapes.h:203) is then
+// never true -- Radians(360) rounds to the float 2*Pi and phi <= 2*Pi by construction.
+inline bool SphereBasicIntersect(const SphereCtx &sp, const float *ray8, float tMax, float *tOut, float *pObj) {
+    const float *m = sp.m;
+    const float g3 = Gamma(3);
+    Interval oi[3], di[3];
+    {   // Transform::operator()(Point3fi) on an exact point, util/transform.h:133-176
+        float x = Interval(ray8[0]).Midpoint(), y = Interval(ray8[1]).Midpoint(), z = Interval(ray8[2]).Midpoint();
+        for (int k = 0; k < 3; ++k) {
+            const float *r = m + 4 * k;
+            float v = (r[0] * x + r[1] * y) + (r[2] * z + r[3]);
+            float e = g3 * (std::abs(r[0] * x) + std::abs(r[1] * y) + std::abs(r[2] * z) + std::abs(r[3]));
+            oi[k] = Interval::FromValueAndError(v, e);
+        }
+    }
+    {   // Transform::operator()(Vector3fi) on an exact vector, util/transform.h:272-306
+        float x = Interval(ray8[4]).Midpoint(), y = Interval(ray8[5]).Midpoint(), z = Interval(ray8[6]).Midpoint();
+        for (int k = 0; k < 3; ++k) {
+            const float *r = m + 4 * k;
+            float e = g3 * (std::abs(r[0] * x) + std::abs(r[1] * y) + std::abs(r[2] * z));
+            float v = r[0] * x + r[1] * y + r[2] * z;
+            di[k] = Interval::FromValueAndError(v, e);
+        }
+    }
+    const Interval radius(sp.radius);
+    Interval a = Sqr(di[0]) + Sqr(di[1]) + Sqr(di[2]);
+    Interval b = 2 * (di[0] * oi[0] + di[1] * oi[1] + di[2] * oi[2]);
+    Interval c = Sqr(oi[0]) + Sqr(oi[1]) + Sqr(oi[2]) - Sqr(radius);
+    Interval f = b / (2 * a);
+    Interval v[3] = {oi[0] - f * di[0], oi[1] - f * di[1], oi[2] - f * di[2]};
+    Interval length = Sqrt(Sqr(v[0]) + Sqr(v[1]) + Sqr(v[2]));
+    Interval discrim = 4 * a * (radius + length) * (radius - length);
+    if (discrim.low < 0)
+        return false;
+    Interval rootDiscrim = Sqrt(discrim);
+    Interval q;
+    if (b.Midpoint() < 0)
+        q = -.5f * (b - rootDiscrim);
+    else
+        q = -.5f * (b + rootDiscrim);
+    Interval t0 = q / a, t1 = c / q;
+    if (t0.low > t1.low)
+        std::swap(t0, t1);
+    if (t0.high > tMax || t1.low <= 0)
+        return false;
+    Interval tShapeHit = t0;
+    if (tShapeHit.low <= 0) {
+        tShapeHit = t1;
+        if (tShapeHit.high > tMax)
+            return false;
+    }
+    auto point = [&](Interval t, float *p) {  // shapes.h:189-195
+        float tm = t.Midpoint();
+        for (int k = 0; k < 3; ++k)
+            p[k] = oi[k].Midpoint() + tm * di[k].Midpoint();
+        float d[3] = {p[0] - 0.f, p[1] - 0.f, p[2] - 0.f};
+        float s = sp.radius / std::sqrt(d[0] * d[0] + d[1] * d[1] + d[2] * d[2]);
+        p[0] *= s, p[1] *= s, p[2] *= s;
+        if (p[0] == 0 && p[1] == 0)
+            p[0] = 1e-5f * sp.radius;
+    };
+    auto clipped = [&](const float *p) {
+        return (sp.zMin > -sp.radius && p[2] < sp.zMin) || (sp.zMax < sp.radius && p[2] > sp.zMax);
+    };
+    float pHit[3];
+    point(tShapeHit, pHit);
+    if (clipped(pHit)) {
+        if (tShapeHit == t1)
+            return false;
+        if (t1.high > tMax)
+            return false;
+        tShapeHit = t1;
+        point(tShapeHit, pHit);
+        if (clipped(pHit))
+            return false;
+    }
+    *tOut = tShapeHit.Midpoint();
+    pObj[0] = pHit[0], pObj[1] = pHit[1], pObj[2] = pHit[2];
+    return true;
+}
+
+// Sphere::Bounds, shapes.cpp:37-40 with util/transform.cpp:134-139 and util/transform.h:310-319
+inline void SphereBounds(const float *s28, float *out6) {
+    SphereCtx sp = MakeSphereCtx(s28);
+    const float *m = s28;  // renderFromObject
+    Box bt;                // Bounds3(): pMin = max, pMax = lowest
+    const float r = sp.radius;
+    float lo[3] = {std::min(-r, r), std::min(-r, r), std::min(sp.zMin, sp.zMax)};
+    float hi[3] = {std::max(-r, r), std::max(-r, r), std::max(sp.zMin, sp.zMax)};
+    for (int c = 0; c < 8; ++c) {
+        float x = (c & 1) ? hi[0] : lo[0], y = (c & 2) ? hi[1] : lo[1], z = (c & 4) ? hi[2] : lo[2];
+        float p[3] = {m[0] * x + m[1] * y + m[2] * z + m[3], m[4] * x + m[5] * y + m[6] * z + m[7],
+                      m[8] * x + m[9] * y + m[10] * z + m[11]};
+        bt = Union(bt, p);
+    }
+    for (int k = 0; k < 3; ++k)
+        out6[k] = bt.mn[k], out6[3 + k] = bt.mx[k];
+}
+
 template <bool ANY>
 inline bool Traverse(const nnbvh_oracle_node *nodes, const float *tris, const float *ray8,
-                     uint32_t *hit5, uint32_t *nodesVisitedOut, uint32_t *triTestsOut) {
+                     uint32_t *hit5, uint32_t *nodesVisitedOut, uint32_t *triTestsOut,
+                     const int32_t *sphereOf = nullptr, const float *spheres28 = nullptr) {
     RayCtx r = MakeRayCtx(ray8);
     float tMax = ray8[3];
     uint32_t hitPrim = 0xFFFFFFFFu;
@@ -619,9 +827,27 @@ inline bool Traverse(const nnbvh_oracle_node *nodes, const float *tris, const fl
             if (BoxIntersectP(node->bounds, r, tMax)) {
                 if (node->nPrimitives > 0) {
                     for (int i = 0; i < node->nPrimitives; ++i) {
-                        ++triTests;
                         float t, b0, b1, b2;
                         uint32_t prim = (uint32_t)(node->offset + i);
+                        if (sphereOf && sphereOf[prim] >= 0) {
+                            // Sphere::Intersect / IntersectP (shapes.h:137-145, 234-236): no nTriTests
+                            float pObj[3];
+                            if (SphereBasicIntersect(MakeSphereCtx(spheres28 + 28 * (size_t)sphereOf[prim]),
+                                                     ray8, tMax, &t, pObj)) {
+                                if (ANY) {
+                                    any = true;
+                                    goto done;
+                                }
+                                hitPrim = prim;
+                                hitT = t;
+                                hb0 = pObj[0];
+                                hb1 = pObj[1];
+                                hb2 = pObj[2];
+                                tMax = t;
+                            }
+                            continue;
+                        }
+                        ++triTests;
                         if (TriangleIntersect(r, tMax, tris + 9 * (size_t)prim, &t, &b0, &b1,
                                               &b2)) {
                             if (ANY) {
@@ -704,6 +930,63 @@ void ParallelRays(int64_t n, int nThreads, F body) {
 }  // namespace
 
 extern "C" {
+
+int64_t nnbvh_oracle_build_bounds(const float *bounds6, int32_t nPrims, int32_t maxPrimsInNode,
+                                  int32_t splitMethod, nnbvh_oracle_node *nodesOut, int32_t *orderOut) {
+    if (nPrims <= 0)
+        return -1;
+    Builder b;
+    b.maxPrimsInNode = std::min(255, maxPrimsInNode);  // aggregates.cpp:142
+    b.splitMethod = splitMethod;
+    b.orderOut = orderOut;
+    std::vector<BuildPrim> prims((size_t)nPrims);
+    for (int32_t i = 0; i < nPrims; ++i) {
+        Box bb;
+        for (int k = 0; k < 3; ++k) {
+            bb.mn[k] = bounds6[6 * (size_t)i + k];
+            bb.mx[k] = bounds6[6 * (size_t)i + 3 + k];
+        }
+        prims[i].primitiveIndex = (size_t)i;
+        prims[i].bounds = bb;
+    }
+    BuildNode *root = splitMethod == NNBVH_ORACLE_HLBVH ? b.BuildHLBVH(prims)
+                                                        : b.BuildRecursive(prims.data(), prims.size());
+    int offset = 0;
+    b.Flatten(root, nodesOut, &offset);
+    return offset;
+}
+
+void nnbvh_oracle_intersect_mixed(const nnbvh_oracle_node *nodes, const float *orderedTris9,
+                                  const int32_t *orderedSphereIndex, const float *spheres28,
+                                  const float *rays8, int64_t n, uint32_t *hits5, uint32_t *nodesVisited,
+                                  uint32_t *triTests, int32_t nThreads) {
+    ParallelRays(n, nThreads, [&](int64_t i) {
+        Traverse<false>(nodes, orderedTris9, rays8 + 8 * i, hits5 + 5 * i,
+                        nodesVisited ? nodesVisited + i : nullptr, triTests ? triTests + i : nullptr,
+                        orderedSphereIndex, spheres28);
+    });
+}
+
+void nnbvh_oracle_intersectP_mixed(const nnbvh_oracle_node *nodes, const float *orderedTris9,
+                                   const int32_t *orderedSphereIndex, const float *spheres28,
+                                   const float *rays8, int64_t n, uint8_t *occluded, uint32_t *nodesVisited,
+                                   uint32_t *triTests, int32_t nThreads) {
+    ParallelRays(n, nThreads, [&](int64_t i) {
+        occluded[i] = Traverse<true>(nodes, orderedTris9, rays8 + 8 * i, nullptr,
+                                     nodesVisited ? nodesVisited + i : nullptr,
+                                     triTests ? triTests + i : nullptr, orderedSphereIndex, spheres28)
+                          ? 1
+                          : 0;
+    });
+}
+
+int32_t nnbvh_oracle_sphere(const float *ray8, const float *sphere28, float *out4) {
+    return SphereBasicIntersect(MakeSphereCtx(sphere28), ray8, ray8[3], &out4[0], &out4[1]) ? 1 : 0;
+}
+
+void nnbvh_oracle_sphere_bounds(const float *sphere28, float *out6) {
+    SphereBounds(sphere28, out6);
+}
 
 int64_t nnbvh_oracle_build(const float *triVerts9, int32_t nTris, int32_t maxPrimsInNode,
                            int32_t splitMethod, nnbvh_oracle_node *nodesOut,

@@ -85,6 +85,63 @@ class Oracle:
                                          _p(tt) if counters else None, threads)
         return (occ, nv, tt) if counters else occ
 
+    # ---- primitive lists that mix triangles and spheres ----
+    def build_bounds(self, bounds6, max_prims: int = 4, split: str = "sah"):
+        bounds6 = np.ascontiguousarray(bounds6, dtype=np.float32).reshape(-1, 6)
+        P = bounds6.shape[0]
+        nodes = np.zeros((2 * P, 8), dtype=np.uint32)
+        order = np.zeros(P, dtype=np.int32)
+        f = self.lib.nnbvh_oracle_build_bounds
+        f.restype = ctypes.c_int64
+        f.argtypes = [ctypes.c_void_p, ctypes.c_int32, ctypes.c_int32, ctypes.c_int32, ctypes.c_void_p,
+                      ctypes.c_void_p]
+        n = f(_p(bounds6), P, max_prims, SPLIT[split], _p(nodes), _p(order))
+        if n < 0:
+            raise ValueError("oracle build failed")
+        return nodes[:n].copy(), order
+
+    def _mixed(self, fn, out, nodes, ordered_tris9, sphere_of, spheres28, rays8, counters, threads):
+        n = rays8.shape[0]
+        nv = np.zeros(n, dtype=np.uint32) if counters else None
+        tt = np.zeros(n, dtype=np.uint32) if counters else None
+        fn.restype = None
+        fn.argtypes = [ctypes.c_void_p] * 5 + [ctypes.c_int64] + [ctypes.c_void_p] * 3 + [ctypes.c_int32]
+        fn(_p(nodes), _p(ordered_tris9), _p(sphere_of), _p(spheres28), _p(rays8), n, _p(out),
+           _p(nv) if counters else None, _p(tt) if counters else None, threads)
+        return (out, nv, tt) if counters else out
+
+    def intersect_mixed(self, nodes, ordered_tris9, sphere_of, spheres28, rays8, counters=False, threads=0):
+        rays8 = np.ascontiguousarray(rays8, dtype=np.float32).reshape(-1, 8)
+        sphere_of = np.ascontiguousarray(sphere_of, dtype=np.int32)
+        spheres28 = np.ascontiguousarray(spheres28, dtype=np.float32).reshape(-1, 28)
+        return self._mixed(self.lib.nnbvh_oracle_intersect_mixed, np.zeros((rays8.shape[0], 5), dtype=np.uint32),
+                           nodes, np.ascontiguousarray(ordered_tris9, dtype=np.float32), sphere_of, spheres28,
+                           rays8, counters, threads)
+
+    def intersect_p_mixed(self, nodes, ordered_tris9, sphere_of, spheres28, rays8, counters=False, threads=0):
+        rays8 = np.ascontiguousarray(rays8, dtype=np.float32).reshape(-1, 8)
+        sphere_of = np.ascontiguousarray(sphere_of, dtype=np.int32)
+        spheres28 = np.ascontiguousarray(spheres28, dtype=np.float32).reshape(-1, 28)
+        return self._mixed(self.lib.nnbvh_oracle_intersectP_mixed, np.zeros(rays8.shape[0], dtype=np.uint8),
+                           nodes, np.ascontiguousarray(ordered_tris9, dtype=np.float32), sphere_of, spheres28,
+                           rays8, counters, threads)
+
+    def sphere(self, ray8, sphere28):
+        ray8 = np.ascontiguousarray(ray8, dtype=np.float32)
+        sphere28 = np.ascontiguousarray(sphere28, dtype=np.float32)
+        out = np.zeros(4, dtype=np.float32)
+        self.lib.nnbvh_oracle_sphere.argtypes = [ctypes.c_void_p] * 3
+        hit = self.lib.nnbvh_oracle_sphere(_p(ray8), _p(sphere28), _p(out))
+        return bool(hit), out
+
+    def sphere_bounds(self, sphere28):
+        sphere28 = np.ascontiguousarray(sphere28, dtype=np.float32)
+        out = np.zeros(6, dtype=np.float32)
+        self.lib.nnbvh_oracle_sphere_bounds.argtypes = [ctypes.c_void_p] * 2
+        self.lib.nnbvh_oracle_sphere_bounds.restype = None
+        self.lib.nnbvh_oracle_sphere_bounds(_p(sphere28), _p(out))
+        return out
+
     def triangle(self, ray8, p9):
         ray8 = np.ascontiguousarray(ray8, dtype=np.float32)
         p9 = np.ascontiguousarray(p9, dtype=np.float32)
@@ -156,6 +213,39 @@ class Reference:
         idx = np.arange(3 * T, dtype=np.int32)
         h = self.lib.nnbvh_ref_scene_create(_p(verts), 3 * T, _p(idx), T, max_prims, SPLIT[split])
         return ctypes.c_void_p(h)
+
+    def scene_mixed(self, tris9, spheres28, max_prims: int = 4, split: str = "sah"):
+        """BVHAggregate over [triangles..., spheres...] (SimplePrimitive each)."""
+        tris9 = np.ascontiguousarray(tris9, dtype=np.float32).reshape(-1, 9)
+        spheres28 = np.ascontiguousarray(spheres28, dtype=np.float32).reshape(-1, 28)
+        if np.any(np.signbit(tris9) & (tris9 == 0)):
+            raise ValueError("triangle soup holds -0.0: pass as_pbrt_stores(tris) to both sides")
+        T = tris9.shape[0]
+        verts = np.ascontiguousarray(tris9.reshape(-1, 3))
+        idx = np.arange(3 * T, dtype=np.int32)
+        f = self.lib.nnbvh_ref_scene_create_mixed
+        f.restype = ctypes.c_void_p
+        f.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p,
+                      ctypes.c_int, ctypes.c_int, ctypes.c_int]
+        self.lib.nnbvh_ref_scene_num_prims.argtypes = [ctypes.c_void_p]
+        return ctypes.c_void_p(f(_p(verts), 3 * T, _p(idx), T, _p(spheres28), spheres28.shape[0],
+                                 max_prims, SPLIT[split]))
+
+    def sphere(self, ray8, sphere28):
+        ray8 = np.ascontiguousarray(ray8, dtype=np.float32)
+        sphere28 = np.ascontiguousarray(sphere28, dtype=np.float32)
+        out = np.zeros(4, dtype=np.float32)
+        self.lib.nnbvh_ref_sphere.argtypes = [ctypes.c_void_p] * 3
+        hit = self.lib.nnbvh_ref_sphere(_p(ray8), _p(sphere28), _p(out))
+        return bool(hit), out
+
+    def sphere_bounds(self, sphere28):
+        sphere28 = np.ascontiguousarray(sphere28, dtype=np.float32)
+        out = np.zeros(6, dtype=np.float32)
+        self.lib.nnbvh_ref_sphere_bounds.argtypes = [ctypes.c_void_p] * 2
+        self.lib.nnbvh_ref_sphere_bounds.restype = None
+        self.lib.nnbvh_ref_sphere_bounds(_p(sphere28), _p(out))
+        return out
 
     def export(self, scene, n_tris: int):
         n = self.lib.nnbvh_ref_scene_num_nodes(scene)

@@ -39,6 +39,7 @@
 #include <pbrt/pbrt.h>
 #include <pbrt/cpu/aggregates.h>
 #include <pbrt/cpu/primitive.h>
+#include <pbrt/materials.h>
 #include <pbrt/options.h>
 #include <pbrt/shapes.h>
 #include <pbrt/util/buffercache.h>
@@ -65,7 +66,36 @@ struct alignas(32) NodeMirror {
 };
 static_assert(sizeof(NodeMirror) == 32, "LinearBVHNode must be 32 bytes");
 
+struct RefSphere {
+    pbrt::Transform renderFromObject, objectFromRender;
+    pbrt::Sphere *shape = nullptr;
+};
+
+// nnbvh_sphere (include/nnbvh.h): renderFromObject[12], objectFromRender[12], radius, zMin, zMax, phiMax.
+pbrt::SquareMatrix<4> Matrix12(const float *m) {
+    float a[4][4] = {{m[0], m[1], m[2], m[3]}, {m[4], m[5], m[6], m[7]}, {m[8], m[9], m[10], m[11]}, {0, 0, 0, 1}};
+    return pbrt::SquareMatrix<4>(a);
+}
+RefSphere *MakeSphere(const float *s28) {
+    auto *rs = new RefSphere;
+    pbrt::SquareMatrix<4> r = Matrix12(s28), o = Matrix12(s28 + 12);
+    rs->renderFromObject = pbrt::Transform(r, o);
+    rs->objectFromRender = pbrt::Transform(o, r);
+    rs->shape = new pbrt::Sphere(&rs->renderFromObject, &rs->objectFromRender, false, s28[24], s28[25],
+                                 s28[26], s28[27]);
+    return rs;
+}
+// SimplePrimitive::Intersect copies its Material handle into the interaction without looking at it
+// (cpu/primitive.cpp:105-108): a fake pointer value carries the primitive's index through.
+pbrt::Material TagMaterial(int index) {
+    return pbrt::Material((pbrt::DiffuseMaterial *)(uintptr_t)(16 * (uintptr_t)(index + 1)));
+}
+int TagOf(pbrt::Material m) {
+    return (int)((uintptr_t)m.ptr() / 16) - 1;
+}
+
 struct RefScene {
+    std::vector<RefSphere *> spheres;  // primitives nTris .. nTris + spheres.size() - 1 of the list
     pbrt::TriangleMesh *mesh = nullptr;
     pbrt::BVHAggregate *agg = nullptr;
     int nTris = 0;
@@ -132,8 +162,21 @@ int nnbvh_ref_threads(void) {
 }
 
 // splitMethod: 0 SAH, 1 HLBVH, 2 Middle, 3 EqualCounts (cpu/aggregates.h:31).
+void *nnbvh_ref_scene_create_mixed(const float *verts, int nVerts, const int *indices, int nTris,
+                                   const float *spheres28, int nSpheres, int maxPrimsInNode,
+                                   int splitMethod);
+
 void *nnbvh_ref_scene_create(const float *verts, int nVerts, const int *indices, int nTris,
                              int maxPrimsInNode, int splitMethod) {
+    return nnbvh_ref_scene_create_mixed(verts, nVerts, indices, nTris, nullptr, 0, maxPrimsInNode,
+                                        splitMethod);
+}
+
+// The primitive list is: triangles 0..nTris-1 (SimplePrimitive over Triangle), then the spheres
+// (SimplePrimitive over Sphere).  nTris may be 0 when there are spheres.
+void *nnbvh_ref_scene_create_mixed(const float *verts, int nVerts, const int *indices, int nTris,
+                                   const float *spheres28, int nSpheres, int maxPrimsInNode,
+                                   int splitMethod) {
     if (!g_inited)
         nnbvh_ref_init(0);
     auto *s = new RefScene;
@@ -155,17 +198,24 @@ void *nnbvh_ref_scene_create(const float *verts, int nVerts, const int *indices,
     for (pbrt::Shape sh : shapes)
         prims.push_back(pbrt::Primitive(
             alloc.new_object<pbrt::SimplePrimitive>(sh, pbrt::Material(nullptr))));
+    for (int k = 0; k < nSpheres; ++k) {
+        s->spheres.push_back(MakeSphere(spheres28 + 28 * (size_t)k));
+        prims.push_back(pbrt::Primitive(alloc.new_object<pbrt::SimplePrimitive>(
+            pbrt::Shape(s->spheres.back()->shape), TagMaterial(nTris + k))));
+    }
     s->nTris = nTris;
+    const int nPrims = nTris + nSpheres;
     s->agg = new pbrt::BVHAggregate(std::move(prims), maxPrimsInNode,
                                     (pbrt::BVHAggregate::SplitMethod)splitMethod);
     s->nNodes = CountNodes(reinterpret_cast<const NodeMirror *>(s->agg->nodes));
-    s->orderedToOrig.resize(nTris);
-    s->origToOrdered.resize(nTris);
-    for (int i = 0; i < nTris; ++i) {
+    s->orderedToOrig.resize(nPrims);
+    s->origToOrdered.resize(nPrims);
+    for (int i = 0; i < nPrims; ++i) {
         const pbrt::SimplePrimitive *sp = s->agg->primitives[i].Cast<pbrt::SimplePrimitive>();
-        const pbrt::Triangle *tri = sp->shape.Cast<pbrt::Triangle>();
-        s->orderedToOrig[i] = tri->triIndex;
-        s->origToOrdered[tri->triIndex] = i;
+        int orig = sp->shape.Is<pbrt::Triangle>() ? sp->shape.Cast<pbrt::Triangle>()->triIndex
+                                                  : TagOf(sp->material);
+        s->orderedToOrig[i] = orig;
+        s->origToOrdered[orig] = i;
     }
     return s;
 }
@@ -174,7 +224,7 @@ int nnbvh_ref_scene_num_nodes(void *scene) {
     return ((RefScene *)scene)->nNodes;
 }
 int nnbvh_ref_scene_num_prims(void *scene) {
-    return ((RefScene *)scene)->nTris;
+    return ((RefScene *)scene)->nTris + (int)((RefScene *)scene)->spheres.size();
 }
 
 // nodesOut: nNodes*32 bytes, byte-identical LinearBVHNode records (pad zeroed).
@@ -189,7 +239,7 @@ void nnbvh_ref_scene_export(void *scene, void *nodesOut, int *orderOut) {
         if (dst[i].nPrimitives > 0)
             dst[i].axis = 0;  // axis is uninitialised for leaves in the reference
     }
-    std::memcpy(orderOut, s->orderedToOrig.data(), sizeof(int) * s->nTris);
+    std::memcpy(orderOut, s->orderedToOrig.data(), sizeof(int) * s->orderedToOrig.size());
 }
 
 // rays: n * 8 floats {ox,oy,oz,tMax,dx,dy,dz,time}.  hits: n * 5 words
@@ -208,6 +258,19 @@ void nnbvh_ref_intersect(void *scene, const float *rays, int64_t n, uint32_t *hi
         if (!si) {
             h[0] = 0xFFFFFFFFu;
             h[1] = h[2] = h[3] = h[4] = 0;
+            return;
+        }
+        if (int tag = TagOf(si->intr.material); tag >= 0) {
+            // a sphere: {prim, tHit, pObj}.  pObj does not survive in SurfaceInteraction either; the
+            // accepted hit is the one BasicIntersect returns for tMax = Infinity (shapes.h:183-222).
+            h[0] = (uint32_t)s->origToOrdered[tag];
+            pstd::optional<pbrt::QuadricIntersection> qi =
+                s->spheres[tag - s->nTris]->shape->BasicIntersect(ray, pbrt::Infinity);
+            float t = si->tHit, q[3] = {0, 0, 0};
+            if (qi)
+                q[0] = qi->pObj.x, q[1] = qi->pObj.y, q[2] = qi->pObj.z;
+            std::memcpy(&h[1], &t, 4);
+            std::memcpy(&h[2], q, 12);
             return;
         }
         int orig = si->intr.faceIndex;
@@ -284,6 +347,31 @@ int nnbvh_ref_box(const float *ray8, const float *box6) {
     pbrt::Vector3f invDir(1 / d.x, 1 / d.y, 1 / d.z);
     int dirIsNeg[3] = {int(invDir.x < 0), int(invDir.y < 0), int(invDir.z < 0)};
     return b.IntersectP(o, d, ray8[3], invDir, dirIsNeg) ? 1 : 0;
+}
+
+// Sphere::BasicIntersect (shapes.h:147-232) and Sphere::Bounds (shapes.cpp:37-40) on one sphere
+// given as 28 floats (nnbvh_sphere).  out4 = {tHit, pObj.xyz}.
+int nnbvh_ref_sphere(const float *ray8, const float *sphere28, float *out4) {
+    RefSphere *rs = MakeSphere(sphere28);
+    pstd::optional<pbrt::QuadricIntersection> qi = rs->shape->BasicIntersect(MakeRay(ray8), ray8[3]);
+    int hit = qi.has_value();
+    if (hit) {
+        out4[0] = qi->tHit;
+        out4[1] = qi->pObj.x;
+        out4[2] = qi->pObj.y;
+        out4[3] = qi->pObj.z;
+    }
+    delete rs->shape;
+    delete rs;
+    return hit;
+}
+void nnbvh_ref_sphere_bounds(const float *sphere28, float *out6) {
+    RefSphere *rs = MakeSphere(sphere28);
+    pbrt::Bounds3f b = rs->shape->Bounds();
+    out6[0] = b.pMin.x, out6[1] = b.pMin.y, out6[2] = b.pMin.z;
+    out6[3] = b.pMax.x, out6[4] = b.pMax.y, out6[5] = b.pMax.z;
+    delete rs->shape;
+    delete rs;
 }
 
 // Triangle::InteractionFromIntersection (shapes.h:884-1010) on a caller-supplied mesh: the host

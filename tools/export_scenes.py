@@ -42,7 +42,7 @@ def main(names):
         if "camera_from_world" in cam:
             cam["camera_from_world"] = np.asarray(cam["camera_from_world"]).tolist()
         meta = {"source": SCENES[name], "triangles": int(tris.shape[0]),
-                "skipped_shapes": sc.skipped, "camera": cam}
+                "skipped_shapes": sc.skipped, "camera": cam, "spheres": sc.spheres}
         with open(os.path.join(out, name + ".json"), "w") as f:
             json.dump(meta, f, indent=1)
         print(name, tris.shape, sc.skipped)

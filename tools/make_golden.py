@@ -19,6 +19,11 @@ oracle/ref_driver.cpp; the fixtures are small so they can be committed.
                     indexed meshes with / without uv, normals, tangents, reversed
                     orientation, degenerate uv and zero shading normals
                     (--only-interaction regenerates just this file).
+  sphere_vectors.npz  Sphere::BasicIntersect (shapes.h:147-232) and Sphere::Bounds answers for
+                    4000 (ray, sphere) pairs -- rotated / scaled / translated, full and
+                    z-clipped, rays from inside and outside, grazing, short tMax -- and a
+                    mixed scene (3000 triangles + 40 spheres): reference tree, hit records,
+                    IntersectP results (--only-spheres).
 """
 import os
 import sys
@@ -236,9 +241,94 @@ def interaction(ref):
     np.savez_compressed(os.path.join(OUT, "interaction.npz"), **out)
 
 
+def random_spheres(rng, n, clip_every=3, scale=1.0, center_box=2.0):
+    """n nnbvh_sphere records (28 floats): rotation * uniform scale + translation."""
+    out = np.zeros((n, 28), dtype=np.float32)
+    for i in range(n):
+        q, _ = np.linalg.qr(rng.normal(size=(3, 3)))
+        m = np.eye(4)
+        m[:3, :3] = q * np.exp(rng.uniform(-1, 1))
+        m[:3, 3] = rng.uniform(-center_box, center_box, 3)
+        rad = scale * np.exp(rng.uniform(-2, 1))
+        out[i, :12] = m[:3].ravel()
+        out[i, 12:24] = np.linalg.inv(m)[:3].ravel()
+        out[i, 24] = rad
+        if clip_every and i % clip_every == 0:
+            out[i, 25], out[i, 26] = -rad * rng.uniform(0.2, 1.2), rad * rng.uniform(0.2, 1.2)
+        else:
+            out[i, 25], out[i, 26] = -rad, rad
+        out[i, 27] = 360
+    return out
+
+
+def sphere_rays(rng, spheres):
+    """One ray per sphere: aimed near it from outside / inside, normalised or not, grazing, short tMax."""
+    n = len(spheres)
+    rays = np.zeros((n, 8), dtype=np.float32)
+    for i, s in enumerate(spheres):
+        c = s[[3, 7, 11]].astype(np.float64)
+        k = abs(np.linalg.det(s[:12].reshape(3, 4)[:, :3].astype(np.float64))) ** (1 / 3)
+        r_world = s[24] * k
+        o = c + rng.normal(size=3) * r_world * np.exp(rng.uniform(-1, 1.5))
+        aim = 1.0 if i % 7 else 1.0 + rng.normal() * 1e-3            # grazing every 7th
+        tgt = c + (lambda v: v / np.linalg.norm(v))(rng.normal(size=3)) * r_world * aim * (rng.uniform(0, 1) if i % 7 else 1)
+        d = tgt - o
+        if i % 2:
+            d /= np.linalg.norm(d)
+        rays[i, :3], rays[i, 4:7] = o, d
+        rays[i, 3] = np.inf if i % 5 else rng.uniform(0, 3)
+        rays[i, 7] = rng.random()
+    return rays
+
+
+def sphere_vectors(ref, rng):
+    n = 4000
+    spheres = random_spheres(rng, n)
+    rays = sphere_rays(rng, spheres)
+    hit = np.zeros(n, dtype=np.uint8)
+    out = np.zeros((n, 4), dtype=np.float32)
+    bounds = np.zeros((n, 6), dtype=np.float32)
+    for i in range(n):
+        h, o4 = ref.sphere(rays[i], spheres[i])
+        hit[i] = h
+        out[i] = o4 if h else 0
+        bounds[i] = ref.sphere_bounds(spheres[i])
+    # a mixed primitive list: 3000 small triangles in [0,1]^3 and 40 spheres among them
+    T = 3000
+    c = rng.random((T, 1, 3), dtype=np.float32)
+    tris = as_pbrt_stores((c + np.float32(0.03) * (rng.random((T, 3, 3), dtype=np.float32) * 2 - 1)).reshape(T, 9))
+    msph = random_spheres(rng, 40, scale=0.08, center_box=0.0)
+    for k in range(40):                      # centres inside the soup
+        m = np.eye(4)
+        m[:3] = msph[k, :12].reshape(3, 4)
+        m[:3, 3] = rng.random(3)
+        msph[k, :12] = m[:3].astype(np.float32).ravel()
+        msph[k, 12:24] = np.linalg.inv(m)[:3].astype(np.float32).ravel()
+    N = 4096
+    mr = np.zeros((N, 8), dtype=np.float32)
+    mr[:, :3] = rng.random((N, 3)) * 1.5 - 0.25
+    tgt = msph[rng.integers(0, 40, N)][:, [3, 7, 11]] + rng.normal(size=(N, 3)) * 0.05
+    d = np.where((np.arange(N) % 2 == 0)[:, None], tgt - mr[:, :3], rng.normal(size=(N, 3)))
+    mr[:, 4:7] = d / np.linalg.norm(d, axis=1, keepdims=True)
+    mr[:, 3] = np.inf
+    mr[N // 2:, 3] = rng.random(N - N // 2) * 1.5
+    sc = ref.scene_mixed(tris, msph, 4, "sah")
+    nodes, order = ref.export(sc, T + 40)
+    hits = ref.intersect(sc, mr, parallel=False)
+    occ = ref.intersect_p(sc, mr, parallel=False)
+    print("sphere_vectors: pair hits", int(hit.sum()), "of", n, "| mixed scene nodes", len(nodes),
+          "sphere hits", int((order[hits[hits[:, 0] != 0xFFFFFFFF, 0]] >= T).sum()), "occluded", int(occ.sum()))
+    np.savez_compressed(os.path.join(OUT, "sphere_vectors.npz"), rays=rays, spheres=spheres, hit=hit, out=out,
+                        bounds=bounds, mixed_tris=tris, mixed_spheres=msph, mixed_rays=mr, mixed_nodes=nodes,
+                        mixed_order=order, mixed_hits=hits, mixed_occ=occ)
+
+
 if __name__ == "__main__":
     os.makedirs(OUT, exist_ok=True)
     ref = Reference(threads=1)
+    if "--only-spheres" in sys.argv:
+        sphere_vectors(ref, np.random.default_rng(147))
+        sys.exit(0)
     if "--only-interaction" in sys.argv:
         interaction(ref)
         sys.exit(0)
@@ -251,3 +341,4 @@ if __name__ == "__main__":
     scene_small(ref, rng)
     hlbvh(ref)
     interaction(ref)
+    sphere_vectors(ref, np.random.default_rng(147))

@@ -136,6 +136,7 @@ class Scene:
     def __init__(self):
         self.tris = []       # list of (T,9) float32 world-space soups
         self.skipped = {}    # shape type -> count
+        self.spheres = []    # Shape "sphere": dicts {render_from_object (3x4), radius, zmin, zmax, phimax}
         self.camera = {}     # eye/look/up or matrix, fov, res
 
     def soup(self):
@@ -247,6 +248,14 @@ def _walk(path, sc, ctm_box, stack, subdivide):
                         raise RuntimeError("loopsubdiv shape needs a subdivide callback")
                     fi, verts = subdivide(levels, idx, verts)
                     idx = np.asarray(fi, dtype=np.int32).reshape(-1, 3)
+            elif kind == "sphere":
+                # Sphere::Create (shapes.cpp): radius 1, zmin -radius, zmax radius, phimax 360 by default
+                f1 = lambda k, d: float(p[k][1][0]) if k in p else d
+                radius = f1("radius", 1.0)
+                sc.spheres.append({"render_from_object": ctm_box[0][:3, :].tolist(), "radius": radius,
+                                   "zmin": f1("zmin", -radius), "zmax": f1("zmax", radius),
+                                   "phimax": f1("phimax", 360.0)})
+                sc.skipped[kind] = sc.skipped.get(kind, 0) + 1   # not part of the triangle soup
             else:
                 sc.skipped[kind] = sc.skipped.get(kind, 0) + 1
             if verts is not None and len(idx):
