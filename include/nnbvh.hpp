@@ -18,6 +18,7 @@
 #ifndef NNBVH_HPP
 #define NNBVH_HPP
 
+#include <algorithm>
 #include <cstddef>
 #include <cstdint>
 #include <limits>
@@ -93,6 +94,47 @@ class GPUBVHAggregate {
         Upload();
     }
 
+    // A primitive list that mixes triangles and spheres (SimplePrimitive over Triangle / Sphere,
+    // shapes.h:107-236): caller primitive i < nTris is triangle i, primitive nTris + k is sphere k.
+    // A hit on a sphere comes back as Hit{prim, tHit, b0,b1,b2 = pObj.xyz} (QuadricIntersection,
+    // shapes.h:100-104; phi = atan2(pObj.y, pObj.x)); IsSphere() tells the two apart.
+    GPUBVHAggregate(const std::vector<float> &tris9, const std::vector<nnbvh_sphere> &spheres,
+                    int maxPrimsInNode = 1, SplitMethod splitMethod = SplitMethod::SAH,
+                    int device = -1, int buildThreads = 0) {
+        const uint32_t nTris = (uint32_t)(tris9.size() / 9), nSph = (uint32_t)spheres.size();
+        const uint32_t nPrims = nTris + nSph;
+        CreateEngine(device);
+        if (nPrims) {
+            std::vector<float> bounds(6 * (size_t)nPrims);
+            for (uint32_t i = 0; i < nTris; ++i)  // Triangle::Bounds, shapes.cpp:294-301
+                for (int k = 0; k < 3; ++k) {
+                    const float *p = &tris9[9 * (size_t)i];
+                    bounds[6 * (size_t)i + k] = std::min(std::min(p[k], p[3 + k]), p[6 + k]);
+                    bounds[6 * (size_t)i + 3 + k] = std::max(std::max(p[k], p[3 + k]), p[6 + k]);
+                }
+            for (uint32_t k = 0; k < nSph; ++k)  // Sphere::Bounds, shapes.cpp:37-40
+                if (int rc = nnbvh_sphere_bounds(&spheres[k], &bounds[6 * (size_t)(nTris + k)])) Fail(rc);
+            nodes_.resize(2 * (size_t)nPrims - 1);
+            order_.resize(nPrims);
+            uint32_t nNodes = 0;
+            int rc = nnbvh_build_bvh_bounds(bounds.data(), nPrims, maxPrimsInNode, (int)splitMethod,
+                                            buildThreads, nodes_.data(), &nNodes, order_.data());
+            if (rc != NNBVH_OK) Fail(rc);
+            nodes_.resize(nNodes);
+            ordered_.assign(9 * (size_t)nPrims, 0.f);
+            sphereOf_.assign(nPrims, -1);
+            for (uint32_t i = 0; i < nPrims; ++i) {
+                if (order_[i] >= nTris) {
+                    sphereOf_[i] = (int32_t)(order_[i] - nTris);
+                    continue;
+                }
+                for (int k = 0; k < 9; ++k) ordered_[9 * (size_t)i + k] = tris9[9 * (size_t)order_[i] + k];
+            }
+        }
+        spheres_ = spheres;
+        Upload();
+    }
+
     // A ready flattened tree (e.g. an NN-split tree exported in LinearBVHNode layout).
     GPUBVHAggregate(std::vector<nnbvh_node> nodes, std::vector<float> orderedTris9,
                     std::vector<uint32_t> order = {}, int device = -1)
@@ -158,6 +200,8 @@ class GPUBVHAggregate {
     uint32_t PrimitiveIndex(uint32_t ordered) const {
         return order_.empty() ? ordered : order_[ordered];
     }
+    // ordered primitive index (Hit::prim) -> is it a sphere?
+    bool IsSphere(uint32_t ordered) const { return !sphereOf_.empty() && sphereOf_[ordered] >= 0; }
     const std::vector<nnbvh_node> &Nodes() const { return nodes_; }
     const std::vector<float> &OrderedTriangles() const { return ordered_; }
     void SetStream(void *cudaStream) { Check(nnbvh_set_stream(e_, cudaStream)); }
@@ -183,8 +227,12 @@ class GPUBVHAggregate {
         throw Error(rc, "libnnbvh: " + msg);
     }
     void Upload() {
-        int rc = nnbvh_upload_scene(e_, nodes_.data(), (uint32_t)nodes_.size(), ordered_.data(),
-                                    (uint32_t)(ordered_.size() / 9));
+        int rc = spheres_.empty()
+                     ? nnbvh_upload_scene(e_, nodes_.data(), (uint32_t)nodes_.size(), ordered_.data(),
+                                          (uint32_t)(ordered_.size() / 9))
+                     : nnbvh_upload_scene_mixed(e_, nodes_.data(), (uint32_t)nodes_.size(), ordered_.data(),
+                                                sphereOf_.data(), (uint32_t)(ordered_.size() / 9),
+                                                spheres_.data(), (uint32_t)spheres_.size());
         if (rc != NNBVH_OK) Fail(rc);
     }
     void Open(int device) {
@@ -195,6 +243,8 @@ class GPUBVHAggregate {
     std::vector<nnbvh_node> nodes_;
     std::vector<float> ordered_;
     std::vector<uint32_t> order_;
+    std::vector<int32_t> sphereOf_;       // per ordered primitive: -1 triangle, else sphere index
+    std::vector<nnbvh_sphere> spheres_;
     nnbvh_engine *e_ = nullptr;
 };
 

@@ -7,6 +7,7 @@
 //   exit 0 = pass; prints the first mismatch otherwise.  Needs a CUDA device
 //   (the pytest wrapper runs it under -m gpu; the CPU suite only compiles it and
 //   checks that it fails loudly with NNBVH_ERR_CUDA when no device is present).
+#include <algorithm>
 #include <cstdio>
 #include <cstring>
 #include <random>
@@ -87,8 +88,89 @@ static int RunCase(Split split, int oracleSplit, const char *name) {
     }
 }
 
+// Triangles and spheres in one primitive list (SimplePrimitive over Triangle / Sphere).
+static int RunSphereCase() {
+    const uint32_t T = 8000, S = 60, N = 60000;
+    std::mt19937 rng(77);
+    std::uniform_real_distribution<float> U(0.f, 1.f);
+    std::normal_distribution<float> G(0.f, 1.f);
+    std::vector<float> tris(9 * (size_t)T);
+    for (uint32_t i = 0; i < T; ++i) {
+        float c[3] = {U(rng), U(rng), U(rng)};
+        for (int v = 0; v < 3; ++v)
+            for (int k = 0; k < 3; ++k) tris[9 * (size_t)i + 3 * v + k] = c[k] + 0.02f * (2 * U(rng) - 1);
+    }
+    std::vector<nnbvh_sphere> sph(S);
+    for (nnbvh_sphere &s : sph) {  // a uniform scale and a translation: the inverse is exact enough to state by hand
+        const float k = 0.5f + U(rng), c[3] = {U(rng), U(rng), U(rng)};
+        const float r[12] = {k, 0, 0, c[0], 0, k, 0, c[1], 0, 0, k, c[2]};
+        const float o[12] = {1 / k, 0, 0, -c[0] / k, 0, 1 / k, 0, -c[1] / k, 0, 0, 1 / k, -c[2] / k};
+        std::memcpy(s.renderFromObject, r, sizeof r);
+        std::memcpy(s.objectFromRender, o, sizeof o);
+        s.radius = 0.02f + 0.05f * U(rng);
+        s.zMin = (&s - sph.data()) % 3 ? -s.radius : -0.5f * s.radius;
+        s.zMax = s.radius;
+        s.phiMax = 360.f;
+    }
+    try {
+        nnbvh::GPUBVHAggregate agg(tris, sph, 4, Split::SAH);
+        const uint32_t P = T + S;
+        std::vector<float> bounds(6 * (size_t)P);
+        for (uint32_t i = 0; i < T; ++i)
+            for (int k = 0; k < 3; ++k) {
+                const float *p = &tris[9 * (size_t)i];
+                bounds[6 * (size_t)i + k] = std::min(std::min(p[k], p[3 + k]), p[6 + k]);
+                bounds[6 * (size_t)i + 3 + k] = std::max(std::max(p[k], p[3 + k]), p[6 + k]);
+            }
+        static_assert(sizeof(nnbvh_sphere) == 28 * sizeof(float), "nnbvh_sphere is 28 floats");
+        for (uint32_t k = 0; k < S; ++k) nnbvh_oracle_sphere_bounds(sph[k].renderFromObject, &bounds[6 * (size_t)(T + k)]);
+        std::vector<nnbvh_oracle_node> onodes(2 * (size_t)P);
+        std::vector<int32_t> oorder(P), sphereOf(P);
+        int64_t m = nnbvh_oracle_build_bounds(bounds.data(), (int32_t)P, 4, NNBVH_ORACLE_SAH, onodes.data(), oorder.data());
+        if (m != (int64_t)agg.Nodes().size() ||
+            std::memcmp(onodes.data(), agg.Nodes().data(), sizeof(nnbvh_node) * (size_t)m) != 0) {
+            std::printf("FAIL: mixed tree differs from the oracle's\n");
+            return 1;
+        }
+        for (uint32_t i = 0; i < P; ++i) {
+            if ((uint32_t)oorder[i] != agg.PrimitiveIndex(i)) { std::printf("FAIL: mixed leaf order differs at %u\n", i); return 1; }
+            sphereOf[i] = oorder[i] >= (int32_t)T ? oorder[i] - (int32_t)T : -1;
+            if (agg.IsSphere(i) != (sphereOf[i] >= 0)) { std::printf("FAIL: IsSphere(%u)\n", i); return 1; }
+        }
+        std::vector<nnbvh_ray> rays(N);
+        for (uint32_t i = 0; i < N; ++i) {
+            nnbvh_ray &r = rays[i];
+            r.ox = -0.25f + 1.5f * U(rng); r.oy = -0.25f + 1.5f * U(rng); r.oz = -0.25f + 1.5f * U(rng);
+            r.dx = G(rng); r.dy = G(rng); r.dz = G(rng);
+            r.tMax = (i & 1) ? U(rng) : std::numeric_limits<float>::infinity();
+            r.time = 0.f;
+        }
+        std::vector<nnbvh_hit> hits(N);
+        std::vector<uint8_t> occ(N), wocc(N);
+        std::vector<uint32_t> want(5 * (size_t)N);
+        agg.IntersectBatch(rays.data(), N, hits.data());
+        agg.IntersectPBatch(rays.data(), N, occ.data());
+        nnbvh_oracle_intersect_mixed(onodes.data(), agg.OrderedTriangles().data(), sphereOf.data(),
+                                     sph[0].renderFromObject, &rays[0].ox, N, want.data(), nullptr, nullptr, 0);
+        nnbvh_oracle_intersectP_mixed(onodes.data(), agg.OrderedTriangles().data(), sphereOf.data(),
+                                      sph[0].renderFromObject, &rays[0].ox, N, wocc.data(), nullptr, nullptr, 0);
+        if (std::memcmp(hits.data(), want.data(), 20 * (size_t)N) != 0) { std::printf("FAIL: mixed closest-hit records differ\n"); return 1; }
+        if (std::memcmp(occ.data(), wocc.data(), N) != 0) { std::printf("FAIL: mixed any-hit results differ\n"); return 1; }
+        uint32_t onSphere = 0;
+        for (uint32_t i = 0; i < N; ++i) onSphere += hits[i].prim != NNBVH_MISS && agg.IsSphere(hits[i].prim);
+        if (onSphere < 100) { std::printf("FAIL: only %u sphere hits\n", onSphere); return 1; }
+        std::printf("PASS spheres: %u triangles + %u spheres, %u rays bit-exact vs oracle (%u sphere hits)\n", T, S, N, onSphere);
+        return 0;
+    } catch (const nnbvh::Error &e) {
+        std::printf("nnbvh::Error %d: %s\n", e.code, e.what());
+        return e.code == NNBVH_ERR_CUDA ? 3 : 2;
+    }
+}
+
 int main(int, char **) {
     int rc = RunCase(Split::SAH, NNBVH_ORACLE_SAH, "sah");
     if (rc) return rc;
-    return RunCase(Split::HLBVH, NNBVH_ORACLE_HLBVH, "hlbvh");
+    rc = RunCase(Split::HLBVH, NNBVH_ORACLE_HLBVH, "hlbvh");
+    if (rc) return rc;
+    return RunSphereCase();
 }
