@@ -196,6 +196,41 @@ int nnbvh_upload_scene_mixed(nnbvh_engine *e, const nnbvh_node *nodes, uint32_t 
                              const float *orderedTriVerts9, const int32_t *orderedSphereIndex,
                              uint32_t nPrims, const nnbvh_sphere *spheres, uint32_t nSpheres);
 
+/* ---- instances: TransformedPrimitive over per-object BVHAggregates ---------------------------
+ * (cpu/primitive.cpp:112-130; pbrt creates them for ObjectInstance, scene.cpp:1541-1571).  An object
+ * is a BVHAggregate over triangles in ITS OWN space (tree + ordered triangles, as nnbvh_upload_scene
+ * takes them); an instance places one object with renderFromPrimitive.  The top-level primitive list
+ * mixes triangles and instances: orderedInstanceIndex[i] = -1 for a triangle, else the instance.
+ * Each ray is moved into the instance's space exactly as Transform::ApplyInverse(Ray, &tMax) does
+ * (interval error bound of the origin, origin pushed along d, tMax shortened) and the object's tree is
+ * traversed there.  A hit on an instance is {prim = the instance's top-level slot, t and b0,b1,b2 of
+ * the inner triangle in the instance ray's parametrisation} -- what TransformedPrimitive::Intersect
+ * returns -- plus, from nnbvh_intersect_closest_instanced, the ordered primitive inside the object.
+ * First version: such scenes run the one-thread-per-ray kernel (nested traversal), and a scene holds
+ * either spheres or instances. */
+typedef struct nnbvh_object {
+    const nnbvh_node *nodes;
+    uint32_t nNodes;
+    const float *orderedTriVerts9;
+    uint32_t nPrims;
+} nnbvh_object;
+typedef struct nnbvh_instance {
+    float renderFromPrimitive[12]; /* rows 0..2 of the 4x4, row 3 = 0 0 0 1 */
+    float primitiveFromRender[12]; /* its inverse, as Transform caches it (mInv) */
+    uint32_t object;
+    uint32_t reserved[3];
+} nnbvh_instance;
+/* TransformedPrimitive::Bounds() given the object's root bounds (its nodes[0].bounds). */
+int nnbvh_instance_bounds(const nnbvh_instance *in, const float *objectBounds6, float *bounds6);
+int nnbvh_upload_scene_instanced(nnbvh_engine *e, const nnbvh_node *nodes, uint32_t nNodes,
+                                 const float *orderedTriVerts9, const int32_t *orderedInstanceIndex,
+                                 uint32_t nPrims, const nnbvh_instance *instances, uint32_t nInstances,
+                                 const nnbvh_object *objects, uint32_t nObjects);
+/* nnbvh_intersect_closest on an instanced scene, also returning innerPrim[i] = ordered primitive
+ * inside the hit object (NNBVH_MISS for a top-level triangle or a miss).  innerPrim may be NULL. */
+int nnbvh_intersect_closest_instanced(nnbvh_engine *e, const nnbvh_ray *rays, uint64_t n,
+                                      nnbvh_hit *hits, uint32_t *innerPrim);
+
 /* BVHAggregate::Intersect (cpu/aggregates.cpp:529-579) for n rays. */
 int nnbvh_intersect_closest(nnbvh_engine *e, const nnbvh_ray *rays, uint64_t n,
                             nnbvh_hit *hits);

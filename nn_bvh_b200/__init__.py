@@ -10,4 +10,5 @@ Package layout (only what the hot path needs):
 from .capi import HIT_DTYPE, MISS, NODE_DTYPE, RAY_DTYPE, NnbvhError  # noqa: F401
 from .aggregate import (GPUBVHAggregate, build_bvh, build_hlbvh_device, make_rays,  # noqa: F401
                         tree_stack_depth, make_spheres, sphere_bounds, triangle_bounds,  # noqa: F401
-                        build_bvh_bounds, SPHERE_DTYPE)  # noqa: F401
+                        build_bvh_bounds, SPHERE_DTYPE, INSTANCE_DTYPE, make_instances,  # noqa: F401
+                        instance_bounds)  # noqa: F401

@@ -59,6 +59,47 @@ def make_spheres(render_from_object, radius, z_min=None, z_max=None, phi_max=360
     return s
 
 
+INSTANCE_DTYPE = np.dtype([("renderFromPrimitive", "<f4", (12,)), ("primitiveFromRender", "<f4", (12,)),
+                           ("object", "<u4"), ("reserved", "<u4", (3,))])
+assert INSTANCE_DTYPE.itemsize == 112   # nnbvh_instance
+
+
+class _Object(ctypes.Structure):          # nnbvh_object
+    _fields_ = [("nodes", ctypes.c_void_p), ("nNodes", ctypes.c_uint32),
+                ("orderedTriVerts9", ctypes.c_void_p), ("nPrims", ctypes.c_uint32)]
+
+
+def make_instances(render_from_primitive, objects, primitive_from_render=None) -> np.ndarray:
+    """nnbvh_instance records from (K,4,4) / (K,3,4) matrices and the object index of each
+    (TransformedPrimitive(object aggregate, renderFromInstance), scene.cpp:1541-1571).
+    primitive_from_render: the inverse matrices as the caller's Transform caches them; by default
+    the float32 rounding of the float64 inverse."""
+    m = np.asarray(render_from_primitive, dtype=np.float64)
+    m = m.reshape(-1, *m.shape[-2:])
+    full = np.tile(np.eye(4), (m.shape[0], 1, 1))
+    full[:, :m.shape[1], :] = m
+    out = np.zeros(m.shape[0], dtype=INSTANCE_DTYPE)
+    out["renderFromPrimitive"] = full[:, :3, :].reshape(-1, 12)
+    if primitive_from_render is not None:
+        inv = np.asarray(primitive_from_render, dtype=np.float32).reshape(m.shape[0], -1)[:, :12]
+    else:
+        inv = np.linalg.inv(full)[:, :3, :].reshape(-1, 12)
+    out["primitiveFromRender"] = inv
+    out["object"] = np.asarray(objects, dtype=np.uint32)
+    return out
+
+
+def instance_bounds(instances: np.ndarray, object_bounds6: np.ndarray) -> np.ndarray:
+    """TransformedPrimitive::Bounds() (cpu/primitive.h:94): (K,6); object_bounds6[k] = root box of
+    instance k's object."""
+    instances = np.ascontiguousarray(instances).view(INSTANCE_DTYPE).reshape(-1)
+    ob = np.ascontiguousarray(object_bounds6, dtype=np.float32).reshape(-1, 6)
+    out = np.zeros((len(instances), 6), dtype=np.float32)
+    for k in range(len(instances)):
+        capi.check(capi.lib().nnbvh_instance_bounds(capi.ptr(instances[k:k + 1]), capi.ptr(ob[k]), capi.ptr(out[k])))
+    return out
+
+
 def sphere_bounds(spheres: np.ndarray) -> np.ndarray:
     """Sphere::Bounds() (shapes.cpp:37-40) for each record: (S,6) float32."""
     spheres = np.ascontiguousarray(spheres).view(SPHERE_DTYPE).reshape(-1)
@@ -140,14 +181,20 @@ class GPUBVHAggregate:
                  ordered_tris9: Optional[np.ndarray] = None, order: Optional[np.ndarray] = None,
                  device: int = -1, kernel: int = capi.KERNEL_AUTO, smem_top_nodes: int = -1,
                  spheres: Optional[np.ndarray] = None,
-                 ordered_sphere_index: Optional[np.ndarray] = None):
+                 ordered_sphere_index: Optional[np.ndarray] = None,
+                 objects: Optional[list] = None, instances: Optional[np.ndarray] = None):
         """Either tris9 (a soup to build over, like the reference ctor) or a ready
         flattened tree: nodes + ordered_tris9 (e.g. an exported NN-split tree).
 
         spheres (SPHERE_DTYPE records, see make_spheres): sphere primitives appended to the
         primitive list after the triangles, i.e. caller primitive T + k is sphere k.  A hit on
         one is reported as {prim, t, b = pObj} (include/nnbvh.h nnbvh_upload_scene_mixed).  With
-        a ready tree pass ordered_sphere_index (-1 = triangle) as well."""
+        a ready tree pass ordered_sphere_index (-1 = triangle) as well.
+
+        objects (list of (T_j,9) soups in object space) + instances (INSTANCE_DTYPE records, see
+        make_instances): each object gets its own tree; caller primitive T + k is instance k, a
+        TransformedPrimitive over its object's aggregate (nnbvh_upload_scene_instanced).  Use
+        IntersectBatchInstanced to get the primitive inside the object as well."""
         L = capi.lib()
         opts = capi.Options(device=device, kernel=kernel, smem_top_nodes=smem_top_nodes)
         h = ctypes.c_void_p()
@@ -155,6 +202,26 @@ class GPUBVHAggregate:
         self._h = h
         self.spheres = None
         self.ordered_sphere_index = None
+        self.instances = None
+        if instances is not None and len(instances):
+            if spheres is not None and len(spheres):
+                raise ValueError("a scene holds either spheres or instances")
+            self.instances = np.ascontiguousarray(instances).view(INSTANCE_DTYPE).reshape(-1)
+            self.objects = []
+            for soup in objects:
+                soup = np.ascontiguousarray(soup, dtype=np.float32).reshape(-1, 9)
+                on, oo = build_bvh(soup, max_prims_in_node, split_method)
+                self.objects.append(dict(nodes=on, order=oo, ordered_tris9=np.ascontiguousarray(soup[oo])))
+            tris9 = (np.zeros((0, 9), dtype=np.float32) if tris9 is None
+                     else np.ascontiguousarray(tris9, dtype=np.float32).reshape(-1, 9))
+            T = tris9.shape[0]
+            roots = np.stack([self.objects[j]["nodes"][0]["bounds"] for j in self.instances["object"]])
+            bounds = np.concatenate([triangle_bounds(tris9), instance_bounds(self.instances, roots)])
+            nodes, order = build_bvh_bounds(bounds, max_prims_in_node, split_method)
+            self.ordered_instance_index = np.where(order >= T, order.astype(np.int64) - T, -1).astype(np.int32)
+            ordered_tris9 = np.zeros((len(order), 9), dtype=np.float32)
+            is_tri = order < T
+            ordered_tris9[is_tri] = tris9[order[is_tri]]
         if spheres is not None and len(spheres):
             self.spheres = np.ascontiguousarray(spheres).view(SPHERE_DTYPE).reshape(-1)
             if nodes is None:
@@ -184,7 +251,17 @@ class GPUBVHAggregate:
         self.nodes = np.ascontiguousarray(nodes).view(NODE_DTYPE).reshape(-1)
         self.ordered_tris9 = np.ascontiguousarray(ordered_tris9, dtype=np.float32).reshape(-1, 9)
         self.order = order  # ordered prim -> caller's primitive id (None = identity)
-        if self.spheres is not None:
+        if self.instances is not None:
+            objs = (_Object * len(self.objects))()
+            for j, o in enumerate(self.objects):
+                objs[j] = _Object(o["nodes"].ctypes.data, len(o["nodes"]), o["ordered_tris9"].ctypes.data,
+                                  len(o["ordered_tris9"]))
+            capi.check(L.nnbvh_upload_scene_instanced(h, capi.ptr(self.nodes), len(self.nodes),
+                                                      capi.ptr(self.ordered_tris9), capi.ptr(self.ordered_instance_index),
+                                                      len(self.ordered_tris9), capi.ptr(self.instances),
+                                                      len(self.instances), ctypes.cast(objs, ctypes.c_void_p),
+                                                      len(self.objects)))
+        elif self.spheres is not None:
             capi.check(L.nnbvh_upload_scene_mixed(h, capi.ptr(self.nodes), len(self.nodes),
                                                   capi.ptr(self.ordered_tris9), capi.ptr(self.ordered_sphere_index),
                                                   len(self.ordered_tris9), capi.ptr(self.spheres), len(self.spheres)))
@@ -237,6 +314,16 @@ class GPUBVHAggregate:
             hits = np.zeros(n, dtype=HIT_DTYPE)
         capi.check(capi.lib().nnbvh_intersect_closest(self._h, capi.ptr(rays), n, capi.ptr(hits)))
         return hits
+
+    def IntersectBatchInstanced(self, rays, hits=None, inner=None, n=None):
+        """Instanced scenes: (hits, inner) with inner[i] = ordered primitive inside the hit object
+        (MISS for a top-level triangle or a miss)."""
+        n = self._count(rays, n)
+        if hits is None:
+            hits, inner = np.zeros(n, dtype=HIT_DTYPE), np.zeros(n, dtype=np.uint32)
+        capi.check(capi.lib().nnbvh_intersect_closest_instanced(self._h, capi.ptr(rays), n, capi.ptr(hits),
+                                                                capi.ptr(inner)))
+        return hits, inner
 
     def IntersectPBatch(self, rays, occluded=None, n=None):
         n = self._count(rays, n)

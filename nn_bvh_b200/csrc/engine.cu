@@ -93,6 +93,7 @@ struct Slot {
     DevBuf<nnbvh_hit> hits;
     DevBuf<uint8_t> occ;
     DevBuf<uint32_t> cnt;    // 2 planes (nodesVisited, triTests)
+    DevBuf<uint32_t> inner;  // instanced scenes: primitive inside the hit object
     Scratch scratch;
 };
 
@@ -120,6 +121,10 @@ struct nnbvh_engine {
     DevBuf<WideNode> dWide;
     DevBuf<float4> dTris;
     DevBuf<SphereDev> dSpheres;
+    DevBuf<InstanceDev> dInstances;
+    DevBuf<nnbvh_node> dObjNodes;
+    DevBuf<float4> dObjTris;
+    bool hasInstances = false;  // instanced scene: BasicKernel with nested traversal runs
     bool hasSpheres = false;  // scene uploaded with spheres: the SPHERES instantiations run
     // device-pointer path scratch
     Scratch scratch;
@@ -229,10 +234,13 @@ extern "C" void nnbvh_destroy(nnbvh_engine *e) {
     e->dWide.Free();
     e->dTris.Free();
     e->dSpheres.Free();
+    e->dInstances.Free();
+    e->dObjNodes.Free();
+    e->dObjTris.Free();
     if (e->dStats) cudaFree(e->dStats);
     e->scratch.Free();
     for (Slot &s : e->slots) {
-        s.rays.Free(); s.soa.Free(); s.hits.Free(); s.occ.Free(); s.cnt.Free();
+        s.rays.Free(); s.soa.Free(); s.hits.Free(); s.occ.Free(); s.cnt.Free(); s.inner.Free();
         s.scratch.Free();
         if (s.done) cudaEventDestroy(s.done);
         if (s.stream) cudaStreamDestroy(s.stream);
@@ -306,15 +314,16 @@ static bool IsDevicePtr(const void *p) {
 }
 
 // in9: nPrims*9 floats (ordered); last: 1 where the primitive ends its leaf.
-// sphereOf (optional): >= 0 marks a sphere slot, the value is its index in the sphere table.
+// special (optional): >= 0 marks a sphere / instance slot (specialFlag says which), the value is its
+// index in the sphere / instance table.
 __global__ void PackTrisKernel(const float *__restrict__ in9, const uint8_t *__restrict__ last,
-                               const int32_t *__restrict__ sphereOf, uint32_t nPrims,
+                               const int32_t *__restrict__ special, uint32_t specialFlag, uint32_t nPrims,
                                float4 *__restrict__ out) {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= nPrims) return;
-    if (sphereOf && sphereOf[i] >= 0) {
-        out[3 * (size_t)i + 0] = make_float4(__uint_as_float((uint32_t)sphereOf[i]), 0.f, 0.f,
-                                             __uint_as_float(kPrimSphere | (last[i] ? kTriLast : 0u)));
+    if (special && special[i] >= 0) {
+        out[3 * (size_t)i + 0] = make_float4(__uint_as_float((uint32_t)special[i]), 0.f, 0.f,
+                                             __uint_as_float(specialFlag | (last[i] ? kTriLast : 0u)));
         out[3 * (size_t)i + 1] = make_float4(0.f, 0.f, 0.f, 0.f);
         out[3 * (size_t)i + 2] = make_float4(0.f, 0.f, 0.f, 0.f);
         return;
@@ -429,7 +438,8 @@ static int MakeSphereDev(const nnbvh_sphere &s, uint32_t index, SphereDev *out) 
 
 static int UploadScene(nnbvh_engine *e, const nnbvh_node *nodes, uint32_t nNodes,
                        const float *orderedTriVerts9, uint32_t nPrims, const int32_t *sphereOf,
-                       const nnbvh_sphere *spheres, uint32_t nSpheres);
+                       const nnbvh_sphere *spheres, uint32_t nSpheres,
+                       const int32_t *instanceOf = nullptr, uint32_t nInstances = 0);
 
 extern "C" int nnbvh_upload_scene(nnbvh_engine *e, const nnbvh_node *nodes, uint32_t nNodes,
                                   const float *orderedTriVerts9, uint32_t nPrims) {
@@ -449,11 +459,13 @@ extern "C" int nnbvh_upload_scene_mixed(nnbvh_engine *e, const nnbvh_node *nodes
 
 static int UploadScene(nnbvh_engine *e, const nnbvh_node *nodes, uint32_t nNodes,
                        const float *orderedTriVerts9, uint32_t nPrims, const int32_t *sphereOf,
-                       const nnbvh_sphere *spheres, uint32_t nSpheres) {
+                       const nnbvh_sphere *spheres, uint32_t nSpheres, const int32_t *instanceOf,
+                       uint32_t nInstances) {
     if (!e) return SetError(NNBVH_ERR_INVALID, "nnbvh_upload_scene: engine is NULL");
     CU(cudaSetDevice(e->device));
     e->haveScene = false;
     e->hasSpheres = false;
+    e->hasInstances = false;
     if (nNodes == 0) {  // `nodes == nullptr` in the reference: every ray misses
         e->sc = SceneDev{};
         e->haveScene = true;
@@ -523,8 +535,18 @@ static int UploadScene(nnbvh_engine *e, const nnbvh_node *nodes, uint32_t nNodes
         CU(cudaMalloc(&dSphereOf, sizeof(int32_t) * (size_t)nPrims));
         CU(cudaMemcpyAsync(dSphereOf, sphereOf, sizeof(int32_t) * (size_t)nPrims, cudaMemcpyHostToDevice, st));
         CU(cudaStreamSynchronize(st));  // sd goes out of scope
+    } else if (instanceOf) {
+        for (uint32_t i = 0; i < nPrims; ++i)
+            if (instanceOf[i] >= (int32_t)nInstances) {
+                if (dRaw) cudaFree(dRaw);
+                cudaFree(dLast);
+                return SetError(NNBVH_ERR_INVALID, "primitive %u refers to instance %d of %u", i, instanceOf[i], nInstances);
+            }
+        CU(cudaMalloc(&dSphereOf, sizeof(int32_t) * (size_t)nPrims));
+        CU(cudaMemcpyAsync(dSphereOf, instanceOf, sizeof(int32_t) * (size_t)nPrims, cudaMemcpyHostToDevice, st));
     }
-    PackTrisKernel<<<(nPrims + 255) / 256, 256, 0, st>>>(src, dLast, dSphereOf, nPrims, e->dTris.p);
+    PackTrisKernel<<<(nPrims + 255) / 256, 256, 0, st>>>(src, dLast, dSphereOf, instanceOf ? kPrimInstance : kPrimSphere,
+                                                        nPrims, e->dTris.p);
     ++e->launches;
     CU(cudaGetLastError());
     CU(cudaStreamSynchronize(st));
@@ -548,6 +570,103 @@ static int UploadScene(nnbvh_engine *e, const nnbvh_node *nodes, uint32_t nNodes
     return NNBVH_OK;
 }
 
+// TransformedPrimitive::Bounds() (cpu/primitive.h:94) = renderFromPrimitive(primitive.Bounds()):
+// the eight transformed corners (util/transform.cpp:134-139, util/transform.h:310-319).
+extern "C" int nnbvh_instance_bounds(const nnbvh_instance *in, const float *objectBounds6, float *bounds6) {
+    if (!in || !objectBounds6 || !bounds6) return SetError(NNBVH_ERR_INVALID, "nnbvh_instance_bounds: NULL argument");
+    float mn[3], mx[3];
+    for (int k = 0; k < 3; ++k) {
+        mn[k] = std::numeric_limits<float>::max();
+        mx[k] = std::numeric_limits<float>::lowest();
+    }
+    const float *m = in->renderFromPrimitive;
+    for (int c = 0; c < 8; ++c) {
+        const float x = objectBounds6[(c & 1) ? 3 : 0], y = objectBounds6[(c & 2) ? 4 : 1], z = objectBounds6[(c & 4) ? 5 : 2];
+        const float q[3] = {m[0] * x + m[1] * y + m[2] * z + m[3], m[4] * x + m[5] * y + m[6] * z + m[7],
+                            m[8] * x + m[9] * y + m[10] * z + m[11]};
+        for (int k = 0; k < 3; ++k) {
+            mn[k] = std::min(mn[k], q[k]);
+            mx[k] = std::max(mx[k], q[k]);
+        }
+    }
+    for (int k = 0; k < 3; ++k) bounds6[k] = mn[k], bounds6[3 + k] = mx[k];
+    return NNBVH_OK;
+}
+
+extern "C" int nnbvh_upload_scene_instanced(nnbvh_engine *e, const nnbvh_node *nodes, uint32_t nNodes,
+                                            const float *orderedTriVerts9, const int32_t *orderedInstanceIndex,
+                                            uint32_t nPrims, const nnbvh_instance *instances, uint32_t nInstances,
+                                            const nnbvh_object *objects, uint32_t nObjects) {
+    if (!e) return SetError(NNBVH_ERR_INVALID, "nnbvh_upload_scene_instanced: engine is NULL");
+    if (!instances || !objects || !orderedInstanceIndex || nInstances == 0 || nObjects == 0)
+        return SetError(NNBVH_ERR_INVALID, "nnbvh_upload_scene_instanced: NULL / empty instance or object table");
+    CU(cudaSetDevice(e->device));
+    cudaStream_t st = e->stream;
+    // the objects: validate each tree, lay trees and triangles back to back
+    std::vector<nnbvh_node> allNodes;
+    std::vector<float> allTris;
+    std::vector<uint8_t> allLast;
+    std::vector<uint32_t> nodeBase(nObjects), primBase(nObjects);
+    for (uint32_t j = 0; j < nObjects; ++j) {
+        const nnbvh_object &o = objects[j];
+        if (!o.nodes || !o.orderedTriVerts9 || o.nNodes == 0 || o.nPrims == 0)
+            return SetError(NNBVH_ERR_INVALID, "object %u is empty", j);
+        std::vector<nnbvh_node> h(o.nodes, o.nodes + o.nNodes);
+        std::vector<WideNode> wide;
+        std::vector<uint8_t> last;
+        int32_t rootRef;
+        uint32_t topNodes;
+        int rc = BuildWideLayout(h, o.nPrims, 0, wide, last, &rootRef, &topNodes);  // validation + leaf-end flags
+        if (rc) return rc;
+        nodeBase[j] = (uint32_t)allNodes.size();
+        primBase[j] = (uint32_t)allLast.size();
+        allNodes.insert(allNodes.end(), h.begin(), h.end());
+        allTris.insert(allTris.end(), o.orderedTriVerts9, o.orderedTriVerts9 + 9 * (size_t)o.nPrims);
+        allLast.insert(allLast.end(), last.begin(), last.end());
+    }
+    std::vector<InstanceDev> id(nInstances);
+    for (uint32_t k = 0; k < nInstances; ++k) {
+        const nnbvh_instance &in = instances[k];
+        if (in.object >= nObjects) return SetError(NNBVH_ERR_INVALID, "instance %u refers to object %u of %u", k, in.object, nObjects);
+        for (int c = 0; c < 12; ++c) {
+            if (!std::isfinite(in.primitiveFromRender[c]) || !std::isfinite(in.renderFromPrimitive[c]))
+                return SetError(NNBVH_ERR_INVALID, "instance %u: non-finite transform", k);
+            id[k].mInv[c] = in.primitiveFromRender[c];
+        }
+        id[k].nodeBase = nodeBase[in.object];
+        id[k].primBase = primBase[in.object];
+        id[k].nNodes = objects[in.object].nNodes;
+        id[k].pad = 0;
+    }
+    const uint32_t nObjPrims = (uint32_t)allLast.size();
+    int rc = e->dObjNodes.Reserve(allNodes.size());
+    if (!rc) rc = e->dObjTris.Reserve(3 * (size_t)nObjPrims);
+    if (!rc) rc = e->dInstances.Reserve(nInstances);
+    if (rc) return rc;
+    float *dRaw = nullptr;
+    uint8_t *dLast = nullptr;
+    CU(cudaMalloc(&dRaw, sizeof(float) * allTris.size()));
+    CU(cudaMalloc(&dLast, nObjPrims));
+    CU(cudaMemcpyAsync(dRaw, allTris.data(), sizeof(float) * allTris.size(), cudaMemcpyHostToDevice, st));
+    CU(cudaMemcpyAsync(dLast, allLast.data(), nObjPrims, cudaMemcpyHostToDevice, st));
+    CU(cudaMemcpyAsync(e->dObjNodes.p, allNodes.data(), sizeof(nnbvh_node) * allNodes.size(), cudaMemcpyHostToDevice, st));
+    CU(cudaMemcpyAsync(e->dInstances.p, id.data(), sizeof(InstanceDev) * nInstances, cudaMemcpyHostToDevice, st));
+    PackTrisKernel<<<(nObjPrims + 255) / 256, 256, 0, st>>>(dRaw, dLast, nullptr, 0u, nObjPrims, e->dObjTris.p);
+    ++e->launches;
+    CU(cudaGetLastError());
+    CU(cudaStreamSynchronize(st));
+    cudaFree(dRaw);
+    cudaFree(dLast);
+    // the top level: triangles and instance slots
+    rc = UploadScene(e, nodes, nNodes, orderedTriVerts9, nPrims, nullptr, nullptr, 0, orderedInstanceIndex, nInstances);
+    if (rc) return rc;
+    e->sc.instances = e->dInstances.p;
+    e->sc.objNodes = e->dObjNodes.p;
+    e->sc.objTris = e->dObjTris.p;
+    e->hasInstances = true;
+    return NNBVH_OK;
+}
+
 // ---------------------------------------------------------------------------
 // Launch
 // ---------------------------------------------------------------------------
@@ -557,6 +676,7 @@ struct Outputs {
     nnbvh_hit *hits = nullptr;
     uint8_t *occ = nullptr;
     uint32_t *nodesVisited = nullptr, *triTests = nullptr;
+    uint32_t *inner = nullptr;  // instanced scenes, closest hit: primitive inside the object (optional)
 };
 
 template <bool ANY, int MINB>
@@ -608,12 +728,22 @@ static int LaunchTraversal(nnbvh_engine *e, cudaStream_t st, bool any, bool coun
                            const RayInput &in, uint64_t n, const Outputs &o,
                            Scratch &scr) {
     if (n == 0) return NNBVH_OK;
-    const bool basic = counters || e->kernel == NNBVH_KERNEL_BASIC;
+    // instanced scenes: nested traversal lives in BasicKernel only (one thread per ray)
+    const bool basic = counters || e->kernel == NNBVH_KERNEL_BASIC || e->hasInstances;
     if (basic) {
         if (n > (uint64_t)0x7fffffff * 128)
             return SetError(NNBVH_ERR_INVALID, "batch too large for one launch");
         unsigned grid = (unsigned)((n + 127) / 128);
-        if (e->hasSpheres) {
+        if (e->hasInstances) {
+            uint32_t *nv = counters ? o.nodesVisited : nullptr, *tt = counters ? o.triTests : nullptr;
+            if (counters) {
+                if (any) BasicKernel<true, true, false, true><<<grid, 128, 0, st>>>(e->sc, in, n, o.hits, o.occ, nv, tt, o.inner);
+                else BasicKernel<false, true, false, true><<<grid, 128, 0, st>>>(e->sc, in, n, o.hits, o.occ, nv, tt, o.inner);
+            } else {
+                if (any) BasicKernel<true, false, false, true><<<grid, 128, 0, st>>>(e->sc, in, n, o.hits, o.occ, nv, tt, o.inner);
+                else BasicKernel<false, false, false, true><<<grid, 128, 0, st>>>(e->sc, in, n, o.hits, o.occ, nv, tt, o.inner);
+            }
+        } else if (e->hasSpheres) {
             if (counters) {
                 if (any) BasicKernel<true, true, true><<<grid, 128, 0, st>>>(e->sc, in, n, o.hits, o.occ, o.nodesVisited, o.triTests);
                 else BasicKernel<false, true, true><<<grid, 128, 0, st>>>(e->sc, in, n, o.hits, o.occ, o.nodesVisited, o.triTests);
@@ -855,6 +985,10 @@ static int RunBatch(nnbvh_engine *e, const Batch &b) {
             if (outDev) o.hits = b.out.hits + off;
             else { int rc = s.hits.Reserve(chunk); if (rc) return rc; o.hits = s.hits.p; }
         }
+        if (b.out.inner && !b.any) {
+            if (outDev) o.inner = b.out.inner + off;
+            else { int rc = s.inner.Reserve(chunk); if (rc) return rc; o.inner = s.inner.p; }
+        }
         if (b.counters) {
             if (cntDev) { o.nodesVisited = b.out.nodesVisited + off; o.triTests = b.out.triTests + off; }
             else {
@@ -878,6 +1012,8 @@ static int RunBatch(nnbvh_engine *e, const Batch &b) {
             else CU(cudaMemcpyAsync(b.out.hits + off, o.hits, sizeof(nnbvh_hit) * m,
                                     cudaMemcpyDeviceToHost, s.stream));
         }
+        if (!outDev && !b.any && b.out.inner)
+            CU(cudaMemcpyAsync(b.out.inner + off, o.inner, sizeof(uint32_t) * m, cudaMemcpyDeviceToHost, s.stream));
         if (b.counters && !cntDev) {
             CU(cudaMemcpyAsync(b.out.nodesVisited + off, o.nodesVisited, sizeof(uint32_t) * m,
                                cudaMemcpyDeviceToHost, s.stream));
@@ -910,6 +1046,20 @@ extern "C" int nnbvh_intersect_closest(nnbvh_engine *e, const nnbvh_ray *rays, u
     b.rays = rays;
     b.n = n;
     b.out.hits = hits;
+    return RunBatch(e, b);
+}
+
+extern "C" int nnbvh_intersect_closest_instanced(nnbvh_engine *e, const nnbvh_ray *rays, uint64_t n,
+                                                 nnbvh_hit *hits, uint32_t *innerPrim) {
+    if (e && !e->hasInstances)
+        return SetError(NNBVH_ERR_INVALID, "nnbvh_intersect_closest_instanced: the scene has no instances");
+    Batch b;
+    b.rays = rays;
+    b.n = n;
+    b.out.hits = hits;
+    b.out.inner = innerPrim;
+    if (innerPrim && IsDevicePtr(innerPrim) != IsDevicePtr(hits))
+        return SetError(NNBVH_ERR_INVALID, "nnbvh_intersect_closest_instanced: hits and innerPrim must live on the same side");
     return RunBatch(e, b);
 }
 

@@ -37,6 +37,7 @@ static_assert(sizeof(WideNode) == 64, "WideNode must be 64 bytes");
 constexpr uint32_t kTriDegenerate = 1u;  // shapes.cpp:176 reject, evaluated at upload
 constexpr uint32_t kTriLast = 2u;        // last primitive of its leaf
 constexpr uint32_t kPrimSphere = 4u;     // the slot is a sphere: .x of the first float4 = index into the sphere table
+constexpr uint32_t kPrimInstance = 8u;   // the slot is a TransformedPrimitive: .x = index into the instance table
 constexpr int kMaxStack = 64;            // cpu/aggregates.cpp:538
 
 

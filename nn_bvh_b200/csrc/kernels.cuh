@@ -39,6 +39,10 @@ struct SceneDev {
     int32_t rootRef;          // WideNode index (>=0) or leaf ref (<0) of the root
     uint32_t topNodes;        // WideNodes [0, topNodes) are the BFS top of the tree
     const SphereDev *spheres; // sphere table (scenes uploaded with nnbvh_upload_scene_mixed), else NULL
+    // instanced scenes (nnbvh_upload_scene_instanced): instance table and the objects' trees / triangles
+    const InstanceDev *instances;
+    const nnbvh_node *objNodes;
+    const float4 *objTris;
 };
 
 struct RayInput {
@@ -67,6 +71,7 @@ __device__ __forceinline__ RayRegs LoadRay(const RayInput &in, uint64_t i) {
 struct HitRegs {
     uint32_t prim;
     float t, b0, b1, b2;
+    uint32_t inner = NNBVH_MISS;  // instanced scenes: ordered primitive inside the hit object
 };
 
 __device__ __forceinline__ void StoreHit(nnbvh_hit *hits, uint64_t i, const HitRegs &h) {
@@ -80,15 +85,31 @@ __device__ __forceinline__ void StoreHit(nnbvh_hit *hits, uint64_t i, const HitR
 
 // Tests the primitives of one leaf in order, each against the CURRENT tMax
 // (aggregates.cpp:547-555).  Returns true as soon as ANY finds a hit.
-template <bool ANY, bool COUNT, bool SPHERES>
+template <bool ANY, bool COUNT>
+__device__ __noinline__ bool InnerTraverse(const SceneDev &sc, uint32_t instance, const RayConst &outer, float tMaxOuter,
+                              HitRegs &hit, uint32_t prim, float &tMax, uint32_t &nodesVisited,
+                              uint32_t &triTests);
+
+template <bool ANY, bool COUNT, bool SPHERES, bool INST = false>
 __device__ __forceinline__ bool LeafTest(const float4 *__restrict__ tris, uint32_t first,
                                          const RayConst &rc, float &tMax, HitRegs &hit,
-                                         uint32_t &triTests, const SphereDev *__restrict__ spheres) {
+                                         uint32_t &triTests, const SphereDev *__restrict__ spheres,
+                                         const SceneDev *sc = nullptr, uint32_t *nodesVisited = nullptr) {
     uint32_t prim = first;
     while (true) {
         const float4 *tp = tris + 3 * (size_t)prim;
         float4 v0 = __ldg(tp), v1 = __ldg(tp + 1), v2 = __ldg(tp + 2);
         uint32_t flags = __float_as_uint(v0.w);
+        if (INST && (flags & kPrimInstance)) {
+            // TransformedPrimitive::Intersect / IntersectP (cpu/primitive.cpp:112-130)
+            uint32_t nv = 0;
+            const bool got = InnerTraverse<ANY, COUNT>(*sc, __float_as_uint(v0.x), rc, tMax, hit, prim, tMax, nv, triTests);
+            if (COUNT) *nodesVisited += nv;
+            if (ANY && got) return true;
+            if (flags & kTriLast) break;
+            ++prim;
+            continue;
+        }
         if (SPHERES && (flags & kPrimSphere)) {
             // Sphere::Intersect / IntersectP (shapes.h:137-145, 234-236); nTriTests counts triangles only
             SphereHit sh;
@@ -96,6 +117,7 @@ __device__ __forceinline__ bool LeafTest(const float4 *__restrict__ tris, uint32
                            tMax, &sh)) {
                 if (ANY) return true;
                 hit.prim = prim;
+                hit.inner = NNBVH_MISS;
                 hit.t = sh.t;
                 hit.b0 = sh.px;
                 hit.b1 = sh.py;
@@ -113,6 +135,7 @@ __device__ __forceinline__ bool LeafTest(const float4 *__restrict__ tris, uint32
                              &b0, &b1, &b2)) {
                 if (ANY) return true;
                 hit.prim = prim;
+                hit.inner = NNBVH_MISS;
                 hit.t = t;
                 hit.b0 = b0;
                 hit.b1 = b1;
@@ -126,14 +149,78 @@ __device__ __forceinline__ bool LeafTest(const float4 *__restrict__ tris, uint32
     return false;
 }
 
+// BVHAggregate::Intersect / IntersectP (cpu/aggregates.cpp:529-624) over 32-byte reference nodes, in
+// the reference's statement order.  primBase: added to leaf offsets (objects' triangles lie back to
+// back).  Returns true when ANY found a hit.
+template <bool ANY, bool COUNT, bool SPHERES, bool INST>
+__device__ __forceinline__ bool TraverseRef(const nnbvh_node *__restrict__ nodes, const float4 *__restrict__ tris,
+                                            uint32_t primBase, const SceneDev &sc, const RayConst &rc, float &tMax,
+                                            HitRegs &hit, uint32_t &nodesVisited, uint32_t &triTests) {
+    int stack[kMaxStack];
+    int sp = 0, cur = 0;
+    const int neg[3] = {rc.negx, rc.negy, rc.negz};
+    while (true) {
+        if (COUNT) ++nodesVisited;
+        const float4 *np = reinterpret_cast<const float4 *>(nodes + cur);
+        float4 a = __ldg(np), b = __ldg(np + 1);
+        float box[6] = {a.x, a.y, a.z, a.w, b.x, b.y};
+        int offset = __float_as_int(b.z);
+        uint32_t meta = __float_as_uint(b.w);
+        uint32_t nPrims = meta & 0xffffu, axis = (meta >> 16) & 0xffu;
+        if (SlabTest(rc, box, tMax)) {
+            if (nPrims > 0) {
+                if (LeafTest<ANY, COUNT, SPHERES, INST>(tris + 3 * (size_t)primBase, (uint32_t)offset, rc, tMax, hit,
+                                                        triTests, sc.spheres, &sc, &nodesVisited))
+                    return true;
+                if (sp == 0) break;
+                cur = stack[--sp];
+            } else if (neg[axis]) {
+                stack[sp++] = cur + 1;
+                cur = offset;
+            } else {
+                stack[sp++] = offset;
+                cur = cur + 1;
+            }
+        } else {
+            if (sp == 0) break;
+            cur = stack[--sp];
+        }
+    }
+    return false;
+}
+
+template <bool ANY, bool COUNT>
+__device__ __noinline__ bool InnerTraverse(const SceneDev &sc, uint32_t instance, const RayConst &outer,
+                                           float tMaxOuter, HitRegs &hit, uint32_t prim, float &tMax,
+                                           uint32_t &nodesVisited, uint32_t &triTests) {
+    const InstanceDev *in = sc.instances + instance;
+    float o[3], d[3], tLocal;
+    InstanceRay(in, outer.ox, outer.oy, outer.oz, outer.dx, outer.dy, outer.dz, tMaxOuter, o, d, &tLocal);
+    const RayConst rc = MakeRayConst(o[0], o[1], o[2], d[0], d[1], d[2]);
+    const uint32_t nodeBase = __ldg(&in->nodeBase), primBase = __ldg(&in->primBase);
+    HitRegs h{NNBVH_MISS, 0.f, 0.f, 0.f, 0.f};
+    const bool any = TraverseRef<ANY, COUNT, false, false>(sc.objNodes + nodeBase, sc.objTris, primBase, sc, rc,
+                                                           tLocal, h, nodesVisited, triTests);
+    if (ANY) return any;
+    if (h.prim == NNBVH_MISS) return false;
+    hit.prim = prim;          // the top-level slot of the instance
+    hit.inner = h.prim;       // ordered primitive inside the object (LeafTest numbers them from primBase 0)
+    hit.t = h.t;              // in the instance ray's parametrisation, as the reference returns it
+    hit.b0 = h.b0;
+    hit.b1 = h.b1;
+    hit.b2 = h.b2;
+    tMax = h.t;               // BVHAggregate::Intersect: tMax = si->tHit (aggregates.cpp:552)
+    return true;
+}
+
 // ---------------------------------------------------------------------------
 // BasicKernel: cpu/aggregates.cpp:529-624 per thread.
 // ---------------------------------------------------------------------------
-template <bool ANY, bool COUNT, bool SPHERES = false>
+template <bool ANY, bool COUNT, bool SPHERES = false, bool INST = false>
 __global__ void __launch_bounds__(128)
 BasicKernel(SceneDev sc, RayInput in, uint64_t n, nnbvh_hit *__restrict__ hits,
             uint8_t *__restrict__ occluded, uint32_t *__restrict__ nodesVisitedOut,
-            uint32_t *__restrict__ triTestsOut) {
+            uint32_t *__restrict__ triTestsOut, uint32_t *__restrict__ innerOut = nullptr) {
     uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     RayRegs rr = LoadRay(in, i);
@@ -142,41 +229,13 @@ BasicKernel(SceneDev sc, RayInput in, uint64_t n, nnbvh_hit *__restrict__ hits,
     HitRegs hit{NNBVH_MISS, 0.f, 0.f, 0.f, 0.f};
     bool any = false;
     uint32_t nodesVisited = 0, triTests = 0;
-    if (sc.nNodes) {
-        int stack[kMaxStack];
-        int sp = 0, cur = 0;
-        const int neg[3] = {rc.negx, rc.negy, rc.negz};
-        while (true) {
-            if (COUNT) ++nodesVisited;
-            const float4 *np = reinterpret_cast<const float4 *>(sc.nodes + cur);
-            float4 a = __ldg(np), b = __ldg(np + 1);
-            float box[6] = {a.x, a.y, a.z, a.w, b.x, b.y};
-            int offset = __float_as_int(b.z);
-            uint32_t meta = __float_as_uint(b.w);
-            uint32_t nPrims = meta & 0xffffu, axis = (meta >> 16) & 0xffu;
-            if (SlabTest(rc, box, tMax)) {
-                if (nPrims > 0) {
-                    if (LeafTest<ANY, COUNT, SPHERES>(sc.tris, (uint32_t)offset, rc, tMax, hit, triTests, sc.spheres)) {
-                        any = true;
-                        break;
-                    }
-                    if (sp == 0) break;
-                    cur = stack[--sp];
-                } else if (neg[axis]) {
-                    stack[sp++] = cur + 1;
-                    cur = offset;
-                } else {
-                    stack[sp++] = offset;
-                    cur = cur + 1;
-                }
-            } else {
-                if (sp == 0) break;
-                cur = stack[--sp];
-            }
-        }
-    }
+    if (sc.nNodes)
+        any = TraverseRef<ANY, COUNT, SPHERES, INST>(sc.nodes, sc.tris, 0u, sc, rc, tMax, hit, nodesVisited, triTests);
     if (ANY) occluded[i] = any ? 1 : 0;
-    else StoreHit(hits, i, hit);
+    else {
+        StoreHit(hits, i, hit);
+        if (INST && innerOut) innerOut[i] = hit.inner;
+    }
     if (COUNT) {
         nodesVisitedOut[i] = nodesVisited;
         triTestsOut[i] = triTests;

@@ -205,4 +205,45 @@ __device__ __noinline__ bool SphereTest(const SphereDev *__restrict__ sp, float 
     return true;
 }
 
+// ---- instances: TransformedPrimitive (cpu/primitive.cpp:112-130) -------------------------------
+// InstanceDev: 64 bytes: rows 0..2 of primitiveFromRender (the mInv of renderFromPrimitive), then where
+// the object's tree and ordered triangles start in the concatenated object arrays.
+struct alignas(64) InstanceDev {
+    float mInv[12];
+    uint32_t nodeBase, primBase, nNodes, pad;
+};
+static_assert(sizeof(InstanceDev) == 64, "InstanceDev must be 64 bytes");
+
+// Ray Transform::ApplyInverse(const Ray &r, Float *tMax) (util/transform.h:416-430) with
+// Point3fi Transform::ApplyInverse(const Point3fi &) on an exact point (util/transform.cpp:263-303).
+__device__ __noinline__ void InstanceRay(const InstanceDev *__restrict__ in, float rox, float roy, float roz,
+                                         float rdx, float rdy, float rdz, float tMax, float *o3, float *d3,
+                                         float *tMaxOut) {
+    const float4 r0 = __ldg(reinterpret_cast<const float4 *>(in)), r1 = __ldg(reinterpret_cast<const float4 *>(in) + 1),
+                 r2 = __ldg(reinterpret_cast<const float4 *>(in) + 2);
+    const float g3 = GammaF(3);
+    const float x = Mid(Exact(rox)), y = Mid(Exact(roy)), z = Mid(Exact(roz));
+    Ival ox = FromValueAndError(Add(Add(Mul(r0.x, x), Mul(r0.y, y)), Add(Mul(r0.z, z), r0.w)),
+                                Mul(g3, Add(Add(fabsf(Mul(r0.x, x)), fabsf(Mul(r0.y, y))), fabsf(Mul(r0.z, z)))));
+    Ival oy = FromValueAndError(Add(Add(Mul(r1.x, x), Mul(r1.y, y)), Add(Mul(r1.z, z), r1.w)),
+                                Mul(g3, Add(Add(fabsf(Mul(r1.x, x)), fabsf(Mul(r1.y, y))), fabsf(Mul(r1.z, z)))));
+    Ival oz = FromValueAndError(Add(Add(Mul(r2.x, x), Mul(r2.y, y)), Add(Mul(r2.z, z), r2.w)),
+                                Mul(g3, Add(Add(fabsf(Mul(r2.x, x)), fabsf(Mul(r2.y, y))), fabsf(Mul(r2.z, z)))));
+    const float dx = Add(Add(Mul(r0.x, rdx), Mul(r0.y, rdy)), Mul(r0.z, rdz));
+    const float dy = Add(Add(Mul(r1.x, rdx), Mul(r1.y, rdy)), Mul(r1.z, rdz));
+    const float dz = Add(Add(Mul(r2.x, rdx), Mul(r2.y, rdy)), Mul(r2.z, rdz));
+    const float lengthSquared = Add(Add(Mul(dx, dx), Mul(dy, dy)), Mul(dz, dz));
+    if (lengthSquared > 0) {
+        const float ex = Div(Sub(ox.hi, ox.lo), 2.f), ey = Div(Sub(oy.hi, oy.lo), 2.f), ez = Div(Sub(oz.hi, oz.lo), 2.f);
+        const float dt = Div(Add(Add(Mul(fabsf(dx), ex), Mul(fabsf(dy), ey)), Mul(fabsf(dz), ez)), lengthSquared);
+        ox = ox + Exact(Mul(dt, dx));  // Point3fi += Vector3f: Interval += Float (math.h:916-917)
+        oy = oy + Exact(Mul(dt, dy));
+        oz = oz + Exact(Mul(dt, dz));
+        tMax = Sub(tMax, dt);
+    }
+    o3[0] = Mid(ox), o3[1] = Mid(oy), o3[2] = Mid(oz);
+    d3[0] = dx, d3[1] = dy, d3[2] = dz;
+    *tMaxOut = tMax;
+}
+
 }  // namespace nnbvh

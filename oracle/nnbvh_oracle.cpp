@@ -808,13 +808,60 @@ inline void SphereBounds(const float *s28, float *out6) {
         out6[k] = bt.mn[k], out6[3 + k] = bt.mx[k];
 }
 
+// ---- TransformedPrimitive (cpu/primitive.cpp:112-130) ------------------------------------------
+// Ray Transform::ApplyInverse(const Ray &r, Float *tMax), util/transform.h:416-430, with
+// Point3fi Transform::ApplyInverse(const Point3fi &) on an exact point (util/transform.cpp:263-303) and
+// Vector3<T> Transform::ApplyInverse(Vector3<T>) (util/transform.h:398-406).  mInv: rows 0..2 of the
+// inverse matrix (row 3 = 0 0 0 1, so wp == 1).
+inline void InstanceRay(const float *mInv, const float *ray8, float *local8) {
+    const float g3 = Gamma(3);
+    float x = Interval(ray8[0]).Midpoint(), y = Interval(ray8[1]).Midpoint(), z = Interval(ray8[2]).Midpoint();
+    Interval o[3];
+    for (int k = 0; k < 3; ++k) {
+        const float *r = mInv + 4 * k;
+        float v = (r[0] * x + r[1] * y) + (r[2] * z + r[3]);
+        float e = g3 * (std::abs(r[0] * x) + std::abs(r[1] * y) + std::abs(r[2] * z));
+        o[k] = Interval::FromValueAndError(v, e);
+    }
+    float dx = ray8[4], dy = ray8[5], dz = ray8[6], d[3];
+    for (int k = 0; k < 3; ++k) {
+        const float *r = mInv + 4 * k;
+        d[k] = r[0] * dx + r[1] * dy + r[2] * dz;
+    }
+    float tMax = ray8[3];
+    float lengthSquared = d[0] * d[0] + d[1] * d[1] + d[2] * d[2];
+    if (lengthSquared > 0) {
+        float oErr[3] = {(o[0].high - o[0].low) / 2, (o[1].high - o[1].low) / 2, (o[2].high - o[2].low) / 2};
+        float dt = (std::abs(d[0]) * oErr[0] + std::abs(d[1]) * oErr[1] + std::abs(d[2]) * oErr[2]) / lengthSquared;
+        for (int k = 0; k < 3; ++k)
+            o[k] = o[k] + Interval(dt * d[k]);  // Point3fi += Vector3f: Interval += Float (math.h:916-917)
+        tMax -= dt;
+    }
+    local8[0] = o[0].Midpoint(), local8[1] = o[1].Midpoint(), local8[2] = o[2].Midpoint();
+    local8[3] = tMax;
+    local8[4] = d[0], local8[5] = d[1], local8[6] = d[2];
+    local8[7] = ray8[7];
+}
+
+// Objects' trees and ordered triangles back to back; instance k = (inst24 + 24k, instObject[k]).
+struct InstancedScene {
+    const int32_t *instanceOf;  // per ordered top-level primitive: -1 triangle, else instance index
+    const float *inst24;        // renderFromPrimitive[12], primitiveFromRender[12]
+    const int32_t *instObject;
+    const nnbvh_oracle_node *objNodes;
+    const int32_t *objNodeBase;  // first node of object j
+    const float *objTris;        // ordered, 9 floats each
+    const int32_t *objPrimBase;  // first ordered primitive of object j
+};
+
 template <bool ANY>
 inline bool Traverse(const nnbvh_oracle_node *nodes, const float *tris, const float *ray8,
                      uint32_t *hit5, uint32_t *nodesVisitedOut, uint32_t *triTestsOut,
-                     const int32_t *sphereOf = nullptr, const float *spheres28 = nullptr) {
+                     const int32_t *sphereOf = nullptr, const float *spheres28 = nullptr,
+                     const InstancedScene *inst = nullptr, uint32_t *innerOut = nullptr) {
     RayCtx r = MakeRayCtx(ray8);
     float tMax = ray8[3];
-    uint32_t hitPrim = 0xFFFFFFFFu;
+    uint32_t hitPrim = 0xFFFFFFFFu, hitInner = 0xFFFFFFFFu;
     float hitT = 0, hb0 = 0, hb1 = 0, hb2 = 0;
     bool any = false;
     uint32_t nodesVisited = 0, triTests = 0;
@@ -829,6 +876,37 @@ inline bool Traverse(const nnbvh_oracle_node *nodes, const float *tris, const fl
                     for (int i = 0; i < node->nPrimitives; ++i) {
                         float t, b0, b1, b2;
                         uint32_t prim = (uint32_t)(node->offset + i);
+                        if (inst && inst->instanceOf[prim] >= 0) {
+                            // TransformedPrimitive::Intersect / IntersectP: the object's own BVHAggregate is
+                            // traversed with the transformed ray; its visits and tests land in the same
+                            // counters (one STAT_COUNTER each, aggregates.cpp:27, shapes.cpp:148)
+                            const int k = inst->instanceOf[prim], j = inst->instObject[k];
+                            float local8[8];
+                            float r8[8];
+                            std::memcpy(r8, ray8, sizeof r8);
+                            r8[3] = tMax;
+                            InstanceRay(inst->inst24 + 24 * (size_t)k + 12, r8, local8);
+                            uint32_t h5[5], nv = 0, tt = 0;
+                            bool got = Traverse<ANY>(inst->objNodes + inst->objNodeBase[j],
+                                                     inst->objTris + 9 * (size_t)inst->objPrimBase[j], local8, h5,
+                                                     &nv, &tt);
+                            nodesVisited += nv;
+                            triTests += tt;
+                            if (got) {
+                                if (ANY) {
+                                    any = true;
+                                    goto done;
+                                }
+                                hitPrim = prim;
+                                hitInner = h5[0];
+                                std::memcpy(&hitT, &h5[1], 4);
+                                std::memcpy(&hb0, &h5[2], 4);
+                                std::memcpy(&hb1, &h5[3], 4);
+                                std::memcpy(&hb2, &h5[4], 4);
+                                tMax = hitT;
+                            }
+                            continue;
+                        }
                         if (sphereOf && sphereOf[prim] >= 0) {
                             // Sphere::Intersect / IntersectP (shapes.h:137-145, 234-236): no nTriTests
                             float pObj[3];
@@ -855,6 +933,7 @@ inline bool Traverse(const nnbvh_oracle_node *nodes, const float *tris, const fl
                                 goto done;
                             }
                             hitPrim = prim;
+                            hitInner = 0xFFFFFFFFu;
                             hitT = t;
                             hb0 = b0;
                             hb1 = b1;
@@ -888,6 +967,8 @@ done:
         *triTestsOut = triTests;
     if (ANY)
         return any;
+    if (innerOut)
+        *innerOut = hitInner;
     hit5[0] = hitPrim;
     std::memcpy(&hit5[1], &hitT, 4);
     std::memcpy(&hit5[2], &hb0, 4);
@@ -978,6 +1059,42 @@ void nnbvh_oracle_intersectP_mixed(const nnbvh_oracle_node *nodes, const float *
                           ? 1
                           : 0;
     });
+}
+
+void nnbvh_oracle_intersect_instanced(const nnbvh_oracle_node *nodes, const float *orderedTris9,
+                                      const int32_t *instanceOf, const float *inst24,
+                                      const int32_t *instObject, const nnbvh_oracle_node *objNodes,
+                                      const int32_t *objNodeBase, const float *objTris,
+                                      const int32_t *objPrimBase, const float *rays8, int64_t n,
+                                      uint32_t *hits5, uint32_t *inner, uint8_t *occluded,
+                                      uint32_t *nodesVisited, uint32_t *triTests, int32_t nThreads) {
+    InstancedScene sc{instanceOf, inst24, instObject, objNodes, objNodeBase, objTris, objPrimBase};
+    ParallelRays(n, nThreads, [&](int64_t i) {
+        if (occluded)
+            occluded[i] = Traverse<true>(nodes, orderedTris9, rays8 + 8 * i, nullptr,
+                                         nodesVisited ? nodesVisited + i : nullptr,
+                                         triTests ? triTests + i : nullptr, nullptr, nullptr, &sc, nullptr)
+                              ? 1
+                              : 0;
+        else
+            Traverse<false>(nodes, orderedTris9, rays8 + 8 * i, hits5 + 5 * i,
+                            nodesVisited ? nodesVisited + i : nullptr, triTests ? triTests + i : nullptr,
+                            nullptr, nullptr, &sc, inner ? inner + i : nullptr);
+    });
+}
+
+// TransformedPrimitive::Bounds (cpu/primitive.h:94): renderFromPrimitive(objectBounds), eight corners.
+void nnbvh_oracle_instance_bounds(const float *renderFromPrimitive12, const float *objectBounds6, float *out6) {
+    const float *m = renderFromPrimitive12;
+    Box bt;
+    for (int c = 0; c < 8; ++c) {
+        float x = objectBounds6[(c & 1) ? 3 : 0], y = objectBounds6[(c & 2) ? 4 : 1], z = objectBounds6[(c & 4) ? 5 : 2];
+        float p[3] = {m[0] * x + m[1] * y + m[2] * z + m[3], m[4] * x + m[5] * y + m[6] * z + m[7],
+                      m[8] * x + m[9] * y + m[10] * z + m[11]};
+        bt = Union(bt, p);
+    }
+    for (int k = 0; k < 3; ++k)
+        out6[k] = bt.mn[k], out6[3 + k] = bt.mx[k];
 }
 
 int32_t nnbvh_oracle_sphere(const float *ray8, const float *sphere28, float *out4) {

@@ -126,6 +126,36 @@ class Oracle:
                            nodes, np.ascontiguousarray(ordered_tris9, dtype=np.float32), sphere_of, spheres28,
                            rays8, counters, threads)
 
+    # ---- instanced scenes (TransformedPrimitive over per-object BVHAggregates) ----
+    def intersect_instanced(self, sc: dict, rays8, any_hit=False, counters=False, threads=0):
+        """sc: dict with nodes, ordered_tris9, instance_of, inst24, inst_object, obj_nodes, obj_node_base,
+        obj_tris, obj_prim_base (numpy arrays).  -> (hits5, inner) or occluded [, nodesVisited, triTests]."""
+        rays8 = np.ascontiguousarray(rays8, dtype=np.float32).reshape(-1, 8)
+        n = rays8.shape[0]
+        hits = np.zeros((n, 5), dtype=np.uint32)
+        inner = np.zeros(n, dtype=np.uint32)
+        occ = np.zeros(n, dtype=np.uint8)
+        nv = np.zeros(n, dtype=np.uint32)
+        tt = np.zeros(n, dtype=np.uint32)
+        f = self.lib.nnbvh_oracle_intersect_instanced
+        f.restype = None
+        f.argtypes = [ctypes.c_void_p] * 10 + [ctypes.c_int64] + [ctypes.c_void_p] * 5 + [ctypes.c_int32]
+        a = {k: np.ascontiguousarray(v) for k, v in sc.items()}
+        f(_p(a["nodes"]), _p(a["ordered_tris9"]), _p(a["instance_of"]), _p(a["inst24"]), _p(a["inst_object"]),
+          _p(a["obj_nodes"]), _p(a["obj_node_base"]), _p(a["obj_tris"]), _p(a["obj_prim_base"]), _p(rays8), n,
+          _p(hits), _p(inner), _p(occ) if any_hit else None, _p(nv), _p(tt), threads)
+        res = (occ,) if any_hit else (hits, inner)
+        return res + (nv, tt) if counters else (res[0] if any_hit else res)
+
+    def instance_bounds(self, render_from_primitive12, object_bounds6):
+        m = np.ascontiguousarray(render_from_primitive12, dtype=np.float32)
+        b = np.ascontiguousarray(object_bounds6, dtype=np.float32)
+        out = np.zeros(6, dtype=np.float32)
+        self.lib.nnbvh_oracle_instance_bounds.argtypes = [ctypes.c_void_p] * 3
+        self.lib.nnbvh_oracle_instance_bounds.restype = None
+        self.lib.nnbvh_oracle_instance_bounds(_p(m), _p(b), _p(out))
+        return out
+
     def sphere(self, ray8, sphere28):
         ray8 = np.ascontiguousarray(ray8, dtype=np.float32)
         sphere28 = np.ascontiguousarray(sphere28, dtype=np.float32)
@@ -230,6 +260,66 @@ class Reference:
         self.lib.nnbvh_ref_scene_num_prims.argtypes = [ctypes.c_void_p]
         return ctypes.c_void_p(f(_p(verts), 3 * T, _p(idx), T, _p(spheres28), spheres28.shape[0],
                                  max_prims, SPLIT[split]))
+
+    def scene_instanced(self, tris9, obj_soups, inst24, inst_object, max_prims: int = 4, split: str = "sah"):
+        """BVHAggregate over [top-level triangles..., TransformedPrimitive(object BVHAggregate) per instance].
+        Returns a dict with the reference's trees in the layout Oracle.intersect_instanced takes."""
+        tris9 = np.ascontiguousarray(tris9, dtype=np.float32).reshape(-1, 9)
+        T = tris9.shape[0]
+        obj_soups = [np.ascontiguousarray(o, dtype=np.float32).reshape(-1, 9) for o in obj_soups]
+        obj_all = np.ascontiguousarray(np.concatenate(obj_soups))
+        start = np.concatenate([[0], np.cumsum([len(o) for o in obj_soups])]).astype(np.int32)
+        inst24 = np.ascontiguousarray(inst24, dtype=np.float32).reshape(-1, 24)
+        inst_object = np.ascontiguousarray(inst_object, dtype=np.int32)
+        K = len(inst24)
+        L = self.lib
+        L.nnbvh_ref_scene_create_instanced.restype = ctypes.c_void_p
+        L.nnbvh_ref_scene_create_instanced.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p,
+                                                       ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int,
+                                                       ctypes.c_int, ctypes.c_int]
+        h = ctypes.c_void_p(L.nnbvh_ref_scene_create_instanced(_p(tris9), T, _p(obj_all), _p(start), len(obj_soups),
+                                                               _p(inst24), _p(inst_object), K, max_prims, SPLIT[split]))
+        L.nnbvh_ref_scene_num_prims.argtypes = [ctypes.c_void_p]
+        nodes, order = self.export(h, T + K)
+        L.nnbvh_ref_scene_object_num_nodes.argtypes = [ctypes.c_void_p, ctypes.c_int]
+        L.nnbvh_ref_scene_export_object.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p]
+        L.nnbvh_ref_instance_bounds.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p]
+        L.nnbvh_ref_instance_bounds.restype = None
+        obj_nodes, obj_tris, obj_orders, nbase, pbase = [], [], [], [0], [0]
+        for j, soup in enumerate(obj_soups):
+            m = L.nnbvh_ref_scene_object_num_nodes(h, j)
+            nd = np.zeros((m, 8), dtype=np.uint32)
+            od = np.zeros(len(soup), dtype=np.int32)
+            L.nnbvh_ref_scene_export_object(h, j, _p(nd), _p(od))
+            obj_nodes.append(nd)
+            obj_tris.append(soup[od])
+            obj_orders.append(od)
+            nbase.append(nbase[-1] + m)
+            pbase.append(pbase[-1] + len(soup))
+        ib = np.zeros((K, 6), dtype=np.float32)
+        for k in range(K):
+            L.nnbvh_ref_instance_bounds(h, k, _p(ib[k]))
+        ordered = np.zeros((T + K, 9), dtype=np.float32)
+        is_tri = order < T
+        ordered[is_tri] = tris9[order[is_tri]]
+        return dict(handle=h, order=order, obj_orders=obj_orders, instance_bounds=ib,
+                    data=dict(nodes=nodes, ordered_tris9=ordered,
+                              instance_of=np.where(order >= T, order - T, -1).astype(np.int32),
+                              inst24=inst24, inst_object=inst_object,
+                              obj_nodes=np.concatenate(obj_nodes), obj_node_base=np.array(nbase[:-1], dtype=np.int32),
+                              obj_tris=np.ascontiguousarray(np.concatenate(obj_tris)),
+                              obj_prim_base=np.array(pbase[:-1], dtype=np.int32)))
+
+    def intersect_instanced(self, handle, rays8):
+        rays8 = np.ascontiguousarray(rays8, dtype=np.float32).reshape(-1, 8)
+        n = rays8.shape[0]
+        hits = np.zeros((n, 5), dtype=np.uint32)
+        inner = np.zeros(n, dtype=np.uint32)
+        self.lib.nnbvh_ref_intersect_instanced.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int64,
+                                                           ctypes.c_void_p, ctypes.c_void_p]
+        self.lib.nnbvh_ref_intersect_instanced.restype = None
+        self.lib.nnbvh_ref_intersect_instanced(handle, _p(rays8), n, _p(hits), _p(inner))
+        return hits, inner
 
     def sphere(self, ray8, sphere28):
         ray8 = np.ascontiguousarray(ray8, dtype=np.float32)

@@ -94,7 +94,22 @@ int TagOf(pbrt::Material m) {
     return (int)((uintptr_t)m.ptr() / 16) - 1;
 }
 
+// An ObjectInstance prototype: its own mesh and BVHAggregate, in object space (scene.cpp:1541-1571).
+struct RefObject {
+    pbrt::TriangleMesh *mesh = nullptr;
+    pbrt::BVHAggregate *agg = nullptr;
+    int nTris = 0, nNodes = 0;
+    std::vector<int> orderedToOrig, origToOrdered;
+};
+struct RefInstance {
+    pbrt::Transform renderFromPrimitive;
+    pbrt::TransformedPrimitive *prim = nullptr;
+    int object = 0;
+};
+
 struct RefScene {
+    std::vector<RefObject *> objects;
+    std::vector<RefInstance *> instances;  // primitives nTris .. of the list (after the triangles)
     std::vector<RefSphere *> spheres;  // primitives nTris .. nTris + spheres.size() - 1 of the list
     pbrt::TriangleMesh *mesh = nullptr;
     pbrt::BVHAggregate *agg = nullptr;
@@ -224,7 +239,8 @@ int nnbvh_ref_scene_num_nodes(void *scene) {
     return ((RefScene *)scene)->nNodes;
 }
 int nnbvh_ref_scene_num_prims(void *scene) {
-    return ((RefScene *)scene)->nTris + (int)((RefScene *)scene)->spheres.size();
+    RefScene *s = (RefScene *)scene;
+    return s->nTris + (int)s->spheres.size() + (int)s->instances.size();
 }
 
 // nodesOut: nNodes*32 bytes, byte-identical LinearBVHNode records (pad zeroed).
@@ -347,6 +363,159 @@ int nnbvh_ref_box(const float *ray8, const float *box6) {
     pbrt::Vector3f invDir(1 / d.x, 1 / d.y, 1 / d.z);
     int dirIsNeg[3] = {int(invDir.x < 0), int(invDir.y < 0), int(invDir.z < 0)};
     return b.IntersectP(o, d, ray8[3], invDir, dirIsNeg) ? 1 : 0;
+}
+
+// ---- instances: TransformedPrimitive over per-object BVHAggregates (cpu/primitive.cpp:112-130) ----
+// Primitive list: top-level triangles 0..nTris-1, then instance k as primitive nTris + k.
+// objTris9: the objects' soups back to back, object j = triangles [objStart[j], objStart[j+1]).
+// inst24: renderFromPrimitive[12], primitiveFromRender[12] per instance; instObject: its object.
+void *nnbvh_ref_scene_create_instanced(const float *tris9, int nTris, const float *objTris9,
+                                       const int *objStart, int nObjects, const float *inst24,
+                                       const int *instObject, int nInstances, int maxPrimsInNode,
+                                       int splitMethod) {
+    if (!g_inited)
+        nnbvh_ref_init(0);
+    auto *s = new RefScene;
+    pbrt::Allocator alloc;
+    auto makeMesh = [&](const float *t9, int n) {
+        std::vector<int> idx(3 * (size_t)n), face(n);
+        std::vector<pbrt::Point3f> p(3 * (size_t)n);
+        for (int i = 0; i < 3 * n; ++i) {
+            idx[i] = i;
+            p[i] = pbrt::Point3f(t9[3 * i], t9[3 * i + 1], t9[3 * i + 2]);
+        }
+        for (int i = 0; i < n; ++i)
+            face[i] = i;
+        return alloc.new_object<pbrt::TriangleMesh>(pbrt::Transform(), false, idx, p,
+                                                    std::vector<pbrt::Vector3f>(),
+                                                    std::vector<pbrt::Normal3f>(),
+                                                    std::vector<pbrt::Point2f>(), face, alloc);
+    };
+    for (int j = 0; j < nObjects; ++j) {
+        auto *o = new RefObject;
+        o->nTris = objStart[j + 1] - objStart[j];
+        o->mesh = makeMesh(objTris9 + 9 * (size_t)objStart[j], o->nTris);
+        std::vector<pbrt::Primitive> prims;
+        for (pbrt::Shape sh : pbrt::Triangle::CreateTriangles(o->mesh, alloc))
+            prims.push_back(pbrt::Primitive(alloc.new_object<pbrt::SimplePrimitive>(sh, TagMaterial(j))));
+        o->agg = new pbrt::BVHAggregate(std::move(prims), maxPrimsInNode,
+                                        (pbrt::BVHAggregate::SplitMethod)splitMethod);
+        o->nNodes = CountNodes(reinterpret_cast<const NodeMirror *>(o->agg->nodes));
+        o->orderedToOrig.resize(o->nTris);
+        o->origToOrdered.resize(o->nTris);
+        for (int i = 0; i < o->nTris; ++i) {
+            const pbrt::SimplePrimitive *sp = o->agg->primitives[i].Cast<pbrt::SimplePrimitive>();
+            int orig = sp->shape.Cast<pbrt::Triangle>()->triIndex;
+            o->orderedToOrig[i] = orig;
+            o->origToOrdered[orig] = i;
+        }
+        s->objects.push_back(o);
+    }
+    s->mesh = makeMesh(tris9, nTris);
+    std::vector<pbrt::Primitive> prims;
+    for (pbrt::Shape sh : pbrt::Triangle::CreateTriangles(s->mesh, alloc))
+        prims.push_back(pbrt::Primitive(alloc.new_object<pbrt::SimplePrimitive>(sh, pbrt::Material(nullptr))));
+    std::map<const void *, int> instIndex;
+    for (int k = 0; k < nInstances; ++k) {
+        auto *in = new RefInstance;
+        in->renderFromPrimitive = pbrt::Transform(Matrix12(inst24 + 24 * (size_t)k), Matrix12(inst24 + 24 * (size_t)k + 12));
+        in->object = instObject[k];
+        in->prim = new pbrt::TransformedPrimitive(pbrt::Primitive(s->objects[in->object]->agg), &in->renderFromPrimitive);
+        instIndex[in->prim] = k;
+        prims.push_back(pbrt::Primitive(in->prim));
+        s->instances.push_back(in);
+    }
+    s->nTris = nTris;
+    const int nPrims = nTris + nInstances;
+    s->agg = new pbrt::BVHAggregate(std::move(prims), maxPrimsInNode,
+                                    (pbrt::BVHAggregate::SplitMethod)splitMethod);
+    s->nNodes = CountNodes(reinterpret_cast<const NodeMirror *>(s->agg->nodes));
+    s->orderedToOrig.resize(nPrims);
+    s->origToOrdered.resize(nPrims);
+    for (int i = 0; i < nPrims; ++i) {
+        pbrt::Primitive p = s->agg->primitives[i];
+        int orig = p.Is<pbrt::TransformedPrimitive>()
+                       ? nTris + instIndex[p.Cast<pbrt::TransformedPrimitive>()]
+                       : p.Cast<pbrt::SimplePrimitive>()->shape.Cast<pbrt::Triangle>()->triIndex;
+        s->orderedToOrig[i] = orig;
+        s->origToOrdered[orig] = i;
+    }
+    return s;
+}
+
+int nnbvh_ref_scene_object_num_nodes(void *scene, int j) {
+    return ((RefScene *)scene)->objects[j]->nNodes;
+}
+void nnbvh_ref_scene_export_object(void *scene, int j, void *nodesOut, int *orderOut) {
+    RefObject *o = ((RefScene *)scene)->objects[j];
+    const NodeMirror *src = reinterpret_cast<const NodeMirror *>(o->agg->nodes);
+    NodeMirror *dst = (NodeMirror *)nodesOut;
+    for (int i = 0; i < o->nNodes; ++i) {
+        dst[i] = src[i];
+        dst[i].pad = 0;
+        if (dst[i].nPrimitives > 0)
+            dst[i].axis = 0;
+    }
+    std::memcpy(orderOut, o->orderedToOrig.data(), sizeof(int) * o->nTris);
+}
+
+// Closest hits of an instanced scene: hits5 as nnbvh_ref_intersect (prim = ordered TOP-LEVEL
+// primitive; for an instance t/b are the inner triangle's, in the instance's ray parametrisation,
+// exactly what TransformedPrimitive::Intersect returns) and inner[i] = ordered primitive inside the
+// object (0xFFFFFFFF for a top-level triangle or a miss).  SurfaceInteraction does not say WHICH
+// instance was hit: it is found by asking each instance of the hit object on its own.
+void nnbvh_ref_intersect_instanced(void *scene, const float *rays, int64_t n, uint32_t *hits,
+                                   uint32_t *inner) {
+    RefScene *s = (RefScene *)scene;
+    pbrt::Primitive top(s->agg);
+    for (int64_t i = 0; i < n; ++i) {
+        const float *r = rays + 8 * i;
+        pbrt::Ray ray = MakeRay(r);
+        pstd::optional<pbrt::ShapeIntersection> si = top.Intersect(ray, r[3]);
+        uint32_t *h = hits + 5 * i;
+        inner[i] = 0xFFFFFFFFu;
+        h[0] = 0xFFFFFFFFu;
+        h[1] = h[2] = h[3] = h[4] = 0;
+        if (!si)
+            continue;
+        float t = si->tHit, b[3] = {0, 0, 0};
+        int obj = TagOf(si->intr.material), face = si->intr.faceIndex;
+        if (obj < 0) {
+            h[0] = (uint32_t)s->origToOrdered[face];
+            const int *v = &s->mesh->vertexIndices[3 * face];
+            if (auto ti = pbrt::IntersectTriangle(ray, pbrt::Infinity, s->mesh->p[v[0]], s->mesh->p[v[1]], s->mesh->p[v[2]]))
+                b[0] = ti->b0, b[1] = ti->b1, b[2] = ti->b2;
+        } else {
+            int found = -1;
+            for (size_t k = 0; k < s->instances.size() && found < 0; ++k) {
+                if (s->instances[k]->object != obj)
+                    continue;
+                auto sk = s->instances[k]->prim->Intersect(ray, pbrt::Infinity);
+                if (sk && sk->tHit == t && sk->intr.faceIndex == face)
+                    found = (int)k;
+            }
+            if (found < 0) {
+                h[0] = 0xFFFFFFFEu;  // cannot happen; makes a test fail loudly
+                continue;
+            }
+            RefObject *o = s->objects[obj];
+            h[0] = (uint32_t)s->origToOrdered[s->nTris + found];
+            inner[i] = (uint32_t)o->origToOrdered[face];
+            pbrt::Ray local = s->instances[found]->renderFromPrimitive.ApplyInverse(ray, nullptr);
+            const int *v = &o->mesh->vertexIndices[3 * face];
+            if (auto ti = pbrt::IntersectTriangle(local, pbrt::Infinity, o->mesh->p[v[0]], o->mesh->p[v[1]], o->mesh->p[v[2]]))
+                b[0] = ti->b0, b[1] = ti->b1, b[2] = ti->b2;
+        }
+        std::memcpy(&h[1], &t, 4);
+        std::memcpy(&h[2], b, 12);
+    }
+}
+
+// TransformedPrimitive::Bounds() of instance k (cpu/primitive.h:94).
+void nnbvh_ref_instance_bounds(void *scene, int k, float *out6) {
+    pbrt::Bounds3f b = ((RefScene *)scene)->instances[k]->prim->Bounds();
+    out6[0] = b.pMin.x, out6[1] = b.pMin.y, out6[2] = b.pMin.z;
+    out6[3] = b.pMax.x, out6[4] = b.pMax.y, out6[5] = b.pMax.z;
 }
 
 // Sphere::BasicIntersect (shapes.h:147-232) and Sphere::Bounds (shapes.cpp:37-40) on one sphere

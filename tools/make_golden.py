@@ -24,6 +24,10 @@ oracle/ref_driver.cpp; the fixtures are small so they can be committed.
                     z-clipped, rays from inside and outside, grazing, short tMax -- and a
                     mixed scene (3000 triangles + 40 spheres): reference tree, hit records,
                     IntersectP results (--only-spheres).
+  instanced.npz     TransformedPrimitive instances (cpu/primitive.cpp:112-130): 1500 top-level
+                    triangles + 30 instances of 3 objects (one a single triangle): the reference's
+                    top-level and per-object trees, TransformedPrimitive::Bounds, closest hits
+                    (with the primitive inside the object), IntersectP (--only-instances).
 """
 import os
 import sys
@@ -323,9 +327,56 @@ def sphere_vectors(ref, rng):
                         mixed_order=order, mixed_hits=hits, mixed_occ=occ)
 
 
+def instanced_scene(rng, T=1500, K=30, obj_sizes=(400, 1, 900)):
+    """(top-level soup, object soups, inst24 (K,24), inst_object (K,)): rotations, uniform scales,
+    translations into the unit cube."""
+    def soup(n, s, lo, hi):
+        c = lo + (hi - lo) * rng.random((n, 1, 3))
+        return as_pbrt_stores((c + s * (rng.random((n, 3, 3)) * 2 - 1)).reshape(n, 9).astype(np.float32))
+    top = soup(T, 0.03, 0.0, 1.0)
+    objs = [soup(n, 0.05 if n < 600 else 0.03, -0.2, 0.2) for n in obj_sizes]
+    inst = np.zeros((K, 24), dtype=np.float32)
+    for k in range(K):
+        q, _ = np.linalg.qr(rng.normal(size=(3, 3)))
+        if np.linalg.det(q) < 0:
+            q[:, 0] = -q[:, 0]
+        m = np.eye(4)
+        m[:3, :3] = q * np.exp(rng.uniform(-1, 0.3))
+        m[:3, 3] = rng.random(3)
+        inst[k, :12] = m[:3].ravel()
+        inst[k, 12:] = np.linalg.inv(m)[:3].ravel()
+    return top, objs, inst, rng.integers(0, len(objs), K).astype(np.int32)
+
+
+def instanced(ref, rng):
+    top, objs, inst, io = instanced_scene(rng)
+    sc = ref.scene_instanced(top, objs, inst, io, 4, "sah")
+    N = 4096
+    rays = np.zeros((N, 8), dtype=np.float32)
+    rays[:, :3] = rng.random((N, 3)) * 1.5 - 0.25
+    d = rng.normal(size=(N, 3))
+    rays[:, 4:7] = d / np.linalg.norm(d, axis=1, keepdims=True)
+    rays[:, 3] = np.inf
+    rays[N // 2:, 3] = rng.random(N - N // 2)
+    hits, inner = ref.intersect_instanced(sc["handle"], rays)
+    occ = ref.intersect_p(sc["handle"], rays, parallel=False)
+    print("instanced: nodes", len(sc["data"]["nodes"]), "instance hits", int((inner != 0xFFFFFFFF).sum()),
+          "triangle hits", int(((hits[:, 0] != 0xFFFFFFFF) & (inner == 0xFFFFFFFF)).sum()), "occluded", int(occ.sum()))
+    out = dict(top=top, inst24=inst, inst_object=io, rays=rays, hits=hits, inner=inner, occ=occ, order=sc["order"],
+               instance_bounds=sc["instance_bounds"], n_objects=np.int32(len(objs)))
+    for j, o in enumerate(objs):
+        out[f"obj{j}"] = o
+        out[f"obj{j}_order"] = sc["obj_orders"][j]
+    out.update({"sc_" + k: v for k, v in sc["data"].items()})
+    np.savez_compressed(os.path.join(OUT, "instanced.npz"), **out)
+
+
 if __name__ == "__main__":
     os.makedirs(OUT, exist_ok=True)
     ref = Reference(threads=1)
+    if "--only-instances" in sys.argv:
+        instanced(ref, np.random.default_rng(112))
+        sys.exit(0)
     if "--only-spheres" in sys.argv:
         sphere_vectors(ref, np.random.default_rng(147))
         sys.exit(0)
@@ -342,3 +393,4 @@ if __name__ == "__main__":
     hlbvh(ref)
     interaction(ref)
     sphere_vectors(ref, np.random.default_rng(147))
+    instanced(ref, np.random.default_rng(112))
