@@ -139,6 +139,7 @@ struct nnbvh_engine {
     int stepStats = 0;       // NNBVH_STEP_STATS=1: run the counting instantiation of StepKernel
     unsigned long long *dStats = nullptr;
     int popLoop = 1;         // StepKernel: discard culled stack entries inside the pop
+    int sphereQuorum = 12;   // StepKernel with sphere leaves: lanes waiting at spheres before their tests run
     uint64_t chunkRays = 1u << 19;
     uint64_t chunkRaysSoa = 1u << 20;  // SoA planes are 4 bytes per ray each: larger chunks per copy
     // ray binning pre-pass (binning.cuh)
@@ -199,6 +200,7 @@ extern "C" int nnbvh_create(const nnbvh_options *opts, nnbvh_engine **out) {
     e->refillBelow = EnvInt("NNBVH_REFILL_BELOW", e->refillBelow);
     e->leafQuorum = EnvInt("NNBVH_LEAF_QUORUM", e->leafQuorum);
     e->popLoop = EnvInt("NNBVH_POP_LOOP", e->popLoop);
+    e->sphereQuorum = EnvInt("NNBVH_SPHERE_QUORUM", e->sphereQuorum);
     e->stepStats = EnvInt("NNBVH_STEP_STATS", 0);
     e->chunkRays = (uint64_t)EnvInt("NNBVH_CHUNK_RAYS", (int)e->chunkRays);
     e->chunkRaysSoa = (uint64_t)EnvInt("NNBVH_CHUNK_RAYS_SOA", (int)e->chunkRaysSoa);
@@ -843,6 +845,7 @@ static int LaunchTraversal(nnbvh_engine *e, cudaStream_t st, bool any, bool coun
             sp.refillBelow = (uint32_t)std::min(32, std::max(1, e->refillBelow));
             sp.leafQuorum = (uint32_t)std::min(32, std::max(1, e->leafQuorum));
             sp.popLoop = (uint32_t)(e->popLoop != 0);
+            sp.sphereQuorum = (uint32_t)std::min(32, std::max(1, e->sphereQuorum));
             if (e->stepStats) {
                 if (!e->dStats) {
                     CU(cudaMalloc(&e->dStats, 8 * sizeof(unsigned long long)));

@@ -53,6 +53,7 @@ struct StepParams {
     uint32_t *nDeferred;
     uint32_t refillBelow, leafQuorum;
     uint32_t popLoop;             // 1: discard culled stack entries inside the pop (default)
+    uint32_t sphereQuorum;        // SPHERES: run the sphere tests when this many lanes wait at sphere slots
     unsigned long long *stats;    // STATS instantiation only: 8 lane-occupancy counters
 };
 
@@ -116,6 +117,11 @@ __global__ void __launch_bounds__(256, MINB) StepKernel(StepParams p) {
     // stack entry = {ref, tEntry} packed into 64 bits (one STL.64 / LDL.64 per push / pop)
     unsigned long long stack[kMaxStack];
     bool exhausted = false;
+    // SPHERES: a lane that steps onto a sphere slot waits (sphWait) until `sphereQuorum` lanes of its warp
+    // wait at spheres or no lane can do anything else: Sphere::BasicIntersect is ~20x a triangle test, and
+    // run for one or two lanes at a time it was most of the kernel (crown's environment shell: every
+    // escaping ray tests it once).  Waiting changes nothing a ray can observe: its own state is frozen.
+    bool sphWait = false;
 
     const unsigned leafQuorum = p.leafQuorum;
 
@@ -189,7 +195,7 @@ __global__ void __launch_bounds__(256, MINB) StepKernel(StepParams p) {
         while (true) {
             const bool atNode = alive && cur >= 0;
             const unsigned nodeMask = __ballot_sync(0xffffffffu, atNode);
-            const unsigned leafMask = __ballot_sync(0xffffffffu, alive && cur < 0);
+            const unsigned leafMask = __ballot_sync(0xffffffffu, alive && cur < 0 && !(SPHERES && sphWait));
             if (nodeMask == 0 || (unsigned)__popc(leafMask) >= leafQuorum) break;
             // NNBVH_SPC node steps between two looks at the leaf quorum: the two ballots, the popc
             // and the compares were 7 % of the issued instructions at one step per look.  A lane that
@@ -302,16 +308,28 @@ __global__ void __launch_bounds__(256, MINB) StepKernel(StepParams p) {
             st[5] += __popc(parked);
             st[6] += __popc(testing);
         }
-        if (alive && cur < 0) {
+        bool doSphere = false;
+        if (SPHERES) {
+            const unsigned sphMask = __ballot_sync(0xffffffffu, sphWait);
+            if (sphMask) {
+                const unsigned other = __ballot_sync(0xffffffffu, alive && !sphWait);
+                doSphere = (unsigned)__popc(sphMask) >= p.sphereQuorum || other == 0;
+            }
+        }
+        if (alive && cur < 0 && (!(SPHERES && sphWait) || doSphere)) {
             bool needPop = true;
-            if (curT < tMax) {  // box test of the leaf node, made when the lane steps onto it
+            if ((SPHERES && sphWait) || curT < tMax) {  // box test of the leaf node, made when the lane steps onto it
                 curT = kNegInf;  // ... and only then: later triangles of this leaf skip it (:547-555)
                 const uint32_t prim = (uint32_t)cur & 0x7fffffffu;
                 const float4 *tp = tris + 3 * (size_t)prim;
                 const float4 v0 = __ldg(tp), v1 = __ldg(tp + 1), v2 = __ldg(tp + 2);
                 const uint32_t flags = __float_as_uint(v0.w);
                 bool found = false;
-                if (SPHERES && (flags & kPrimSphere)) {
+                if (SPHERES && (flags & kPrimSphere) && !sphWait) {
+                    sphWait = true;  // first arrival: wait for company (see above); nothing else moves
+                    needPop = false;
+                } else if (SPHERES && (flags & kPrimSphere)) {
+                    sphWait = false;
                     // Sphere::Intersect / IntersectP (shapes.h:137-145, 234-236).  The lane keeps no
                     // direction (it is folded into invDir and the shear): the ray is read again.
                     const RayRegs rr = LoadRay(p.in, rayIdx);
@@ -340,7 +358,9 @@ __global__ void __launch_bounds__(256, MINB) StepKernel(StepParams p) {
                         tMax = t;
                     }
                 }
-                if (ANY && found) {  // first accepted primitive ends the ray (:598-601)
+                if (SPHERES && sphWait) {
+                    // parked at the sphere slot: `cur` stays
+                } else if (ANY && found) {  // first accepted primitive ends the ray (:598-601)
                     alive = false;
                     needPop = false;
                     p.occluded[rayIdx] = 1;

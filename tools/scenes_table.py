@@ -4,7 +4,9 @@
 For each cached scene (reference SAH tree, maxnodeprims 4): 8 Mi camera / diffuse-bounce / shadow rays,
 best of 3 timed batches (ms from the engine's CUDA events, ray-ordering pre-pass included), the
 reference's counting rules for nodesVisited / triTests on a 1 Mi-ray subset, and the algorithmic
-bytes per ray of SURVEY 8(d)."""
+bytes per ray of SURVEY 8(d).
+--spheres: the scene's `Shape "sphere"` primitives join the primitive list (killeroos: the spherical
+light, crown: the environment shell); the same rays (generated on the triangle-only scene) are traced."""
 import os
 import sys
 
@@ -16,7 +18,9 @@ import nn_bvh_b200 as nb  # noqa: E402
 from nn_bvh_b200 import rays as R, scenes  # noqa: E402
 
 N = 8 << 20
-for scene in sys.argv[1:] or ["killeroos", "coffee_maker", "bathroom", "crown"]:
+WITH_SPHERES = "--spheres" in sys.argv
+ARGS = [a for a in sys.argv[1:] if not a.startswith("--")]
+for scene in ARGS or ["killeroos", "coffee_maker", "bathroom", "crown"]:
     tris, cam, name = scenes.load(scene, allow_procedural=False)
     nodes, order = nb.build_bvh(tris, 4, "sah")
     ordered = tris[order]
@@ -24,6 +28,12 @@ for scene in sys.argv[1:] or ["killeroos", "coffee_maker", "bathroom", "crown"]:
     bounce, shadow = R.bounce_and_shadow_rays(lambda r: agg.IntersectBatch(r), ordered, cam, N)
     res = int(np.ceil(np.sqrt(N)))
     sets = {"primary": R.camera_rays(cam, res, res)[:N], "bounce": bounce, "shadow": shadow}
+    sph = scenes.load_spheres(scene) if WITH_SPHERES else None
+    if sph is not None:
+        agg.close()
+        agg = nb.GPUBVHAggregate(tris, 4, "sah", spheres=sph)
+        nodes = agg.nodes
+        name += f"+{len(sph)}sphere"
     for kind, r in sets.items():
         n = len(r)
         d = torch.from_numpy(r.view(np.float32).reshape(-1, 8)).cuda()
