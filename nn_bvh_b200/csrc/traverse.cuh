@@ -216,13 +216,6 @@ __global__ void __launch_bounds__(256, MINB) StepKernel(StepParams p) {
                     const unsigned char *np = wideBase + (size_t)(unsigned)cur * sizeof(WideNode);
                     const F8 a = Ldg256(np), b = Ldg256(np + 32);
                     // WideNode: lo0 xyz, hi0 xyz, lo1 xy | lo1 z, hi1 xyz, ref0, ref1, axis, pad
-                    const bool nx = ry.neg & 1, ny = ry.neg & 2, nz = ry.neg & 4;
-                    const float n0x = nx ? a.v[3] : a.v[0], f0x = nx ? a.v[0] : a.v[3];
-                    const float n0y = ny ? a.v[4] : a.v[1], f0y = ny ? a.v[1] : a.v[4];
-                    const float n0z = nz ? a.v[5] : a.v[2], f0z = nz ? a.v[2] : a.v[5];
-                    const float n1x = nx ? b.v[1] : a.v[6], f1x = nx ? a.v[6] : b.v[1];
-                    const float n1y = ny ? b.v[2] : a.v[7], f1y = ny ? a.v[7] : b.v[2];
-                    const float n1z = nz ? b.v[3] : b.v[0], f1z = nz ? b.v[0] : b.v[3];
                     const int ref0 = __float_as_int(b.v[4]), ref1 = __float_as_int(b.v[5]);
                     const unsigned axis = __float_as_uint(b.v[6]);
                     const bool secondFirst = (ry.neg >> axis) & 1u;  // aggregates.cpp:561
@@ -230,6 +223,13 @@ __global__ void __launch_bounds__(256, MINB) StepKernel(StepParams p) {
                     float tNear, tFar;
                     bool stNear, stFar;
                     if (EXACT) {
+                        const bool nx = ry.neg & 1, ny = ry.neg & 2, nz = ry.neg & 4;
+                        const float n0x = nx ? a.v[3] : a.v[0], f0x = nx ? a.v[0] : a.v[3];
+                        const float n0y = ny ? a.v[4] : a.v[1], f0y = ny ? a.v[1] : a.v[4];
+                        const float n0z = nz ? a.v[5] : a.v[2], f0z = nz ? a.v[2] : a.v[5];
+                        const float n1x = nx ? b.v[1] : a.v[6], f1x = nx ? a.v[6] : b.v[1];
+                        const float n1y = ny ? b.v[2] : a.v[7], f1y = ny ? a.v[7] : b.v[2];
+                        const float n1z = nz ? b.v[3] : b.v[0], f1z = nz ? b.v[0] : b.v[3];
                         RayConst rc = ToRayConst(ry);
                         float t0, t1;
                         const bool ok0 = SlabStatic(rc, n0x, f0x, n0y, f0y, n0z, f0z, &t0);
@@ -239,17 +239,22 @@ __global__ void __launch_bounds__(256, MINB) StepKernel(StepParams p) {
                         tNear = secondFirst ? t1 : t0;
                         tFar = secondFirst ? t0 : t1;
                     } else {
+                        // Both planes of every slab, then min / max: with lo <= hi, finite non-zero invDir and
+                        // a finite origin (the fast path's preconditions) rounding is monotone, so the near
+                        // plane's distance -- bounds[dirIsNeg] in the reference -- IS the smaller of the two,
+                        // whatever the sign of invDir; and the far distances are padded after the min3
+                        // (min_k fl(t_k * c) = fl((min_k t_k) * c) for c > 0): one multiply per box, not three.
                         const float pad = SlabPad();
-                        const float ax0 = Mul(Sub(n0x, ry.ox), ry.ix), bx0 = Mul(Mul(Sub(f0x, ry.ox), ry.ix), pad);
-                        const float ay0 = Mul(Sub(n0y, ry.oy), ry.iy), by0 = Mul(Mul(Sub(f0y, ry.oy), ry.iy), pad);
-                        const float az0 = Mul(Sub(n0z, ry.oz), ry.iz), bz0 = Mul(Mul(Sub(f0z, ry.oz), ry.iz), pad);
-                        const float ax1 = Mul(Sub(n1x, ry.ox), ry.ix), bx1 = Mul(Mul(Sub(f1x, ry.ox), ry.ix), pad);
-                        const float ay1 = Mul(Sub(n1y, ry.oy), ry.iy), by1 = Mul(Mul(Sub(f1y, ry.oy), ry.iy), pad);
-                        const float az1 = Mul(Sub(n1z, ry.oz), ry.iz), bz1 = Mul(Mul(Sub(f1z, ry.oz), ry.iz), pad);
-                        const float t0 = fmaxf(fmaxf(ax0, ay0), az0);
-                        const float t1 = fmaxf(fmaxf(ax1, ay1), az1);
-                        const float x0 = fminf(fminf(bx0, by0), bz0);
-                        const float x1 = fminf(fminf(bx1, by1), bz1);
+                        const float lx0 = Mul(Sub(a.v[0], ry.ox), ry.ix), hx0 = Mul(Sub(a.v[3], ry.ox), ry.ix);
+                        const float ly0 = Mul(Sub(a.v[1], ry.oy), ry.iy), hy0 = Mul(Sub(a.v[4], ry.oy), ry.iy);
+                        const float lz0 = Mul(Sub(a.v[2], ry.oz), ry.iz), hz0 = Mul(Sub(a.v[5], ry.oz), ry.iz);
+                        const float lx1 = Mul(Sub(a.v[6], ry.ox), ry.ix), hx1 = Mul(Sub(b.v[1], ry.ox), ry.ix);
+                        const float ly1 = Mul(Sub(a.v[7], ry.oy), ry.iy), hy1 = Mul(Sub(b.v[2], ry.oy), ry.iy);
+                        const float lz1 = Mul(Sub(b.v[0], ry.oz), ry.iz), hz1 = Mul(Sub(b.v[3], ry.oz), ry.iz);
+                        const float t0 = fmaxf(fmaxf(fminf(lx0, hx0), fminf(ly0, hy0)), fminf(lz0, hz0));
+                        const float t1 = fmaxf(fmaxf(fminf(lx1, hx1), fminf(ly1, hy1)), fminf(lz1, hz1));
+                        const float x0 = Mul(fminf(fminf(fmaxf(lx0, hx0), fmaxf(ly0, hy0)), fmaxf(lz0, hz0)), pad);
+                        const float x1 = Mul(fminf(fminf(fmaxf(lx1, hx1), fmaxf(ly1, hy1)), fmaxf(lz1, hz1)), pad);
                         // order the VALUES, then compare: the predicates never live in registers
                         tNear = secondFirst ? t1 : t0;
                         tFar = secondFirst ? t0 : t1;
