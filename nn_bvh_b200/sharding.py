@@ -160,17 +160,23 @@ class PeerWindow:
         self._ready = torch.cuda.Event()
         self._done = torch.cuda.Event()
 
-    def deliver(self, local: torch.Tensor, producer: "torch.cuda.Stream"):
+    def deliver(self, local: torch.Tensor, producer: "torch.cuda.Stream", at: int = None):
         """Enqueue the copy of this rank's slice, ordered after everything `producer` holds now.
-        Returns at once; wait_on(stream) makes a stream wait for the delivery."""
+        Returns at once; wait_on(stream) makes a stream wait for the delivery.
+        at: deliver `local` as rows [at, at + len(local)) of this rank's shard (a batch traced in chunks
+        delivers each chunk while the next one is traced); None = the whole shard."""
         a, b = shard_range(self.n_total, self.rank, self.world)
-        if local.shape[0] != b - a:
-            raise ValueError(f"rank {self.rank}: local result has {local.shape[0]} rows, shard has {b - a}")
+        if at is None:
+            if local.shape[0] != b - a:
+                raise ValueError(f"rank {self.rank}: local result has {local.shape[0]} rows, shard has {b - a}")
+            at = 0
+        elif at < 0 or at + local.shape[0] > b - a:
+            raise ValueError(f"rank {self.rank}: rows [{at}, {at + local.shape[0]}) outside a shard of {b - a}")
         self._ready.record(producer)
         self.stream.wait_event(self._ready)
         self._capi.check(self._capi.lib().nnbvh_peer_copy(
-            self._ct.c_void_p(self.base + a * self.row_bytes), self._capi.ptr(local.contiguous()),
-            (b - a) * self.row_bytes, self._ct.c_void_p(self.stream.cuda_stream)))
+            self._ct.c_void_p(self.base + (a + at) * self.row_bytes), self._capi.ptr(local.contiguous()),
+            local.shape[0] * self.row_bytes, self._ct.c_void_p(self.stream.cuda_stream)))
         self._done.record(self.stream)
 
     def wait_on(self, stream: "torch.cuda.Stream"):

@@ -1,6 +1,8 @@
 #!/usr/bin/env python3
 """tools/config5.py -- BASELINE.json configs[4]: synthetic 10M-triangle mesh, 256M random rays,
-sharded over the ranks it is launched with (torchrun), NCCL gather of a per-rank checksum.
+sharded over the ranks it is launched with (torchrun); the hit records are returned to rank 0 inside
+the timed region (--gather peer: copy engines into a peer-mapped window over NVLink, chunk by chunk while
+the next chunk is traced; --gather nccl: one NCCL gather after the kernel; none: kernel only).
 
 Ray i is a pure function of its GLOBAL index (counter-based hash), so every world size traces the
 same 256M rays; rank g takes the contiguous slice shard_range(N, g, G).  The
@@ -60,6 +62,8 @@ def main():
     ap.add_argument("--rays", type=int, default=256 << 20)
     ap.add_argument("--oracle", type=int, default=200_000)
     ap.add_argument("--reps", type=int, default=3)
+    ap.add_argument("--gather", default="peer", choices=["peer", "nccl", "none"])
+    ap.add_argument("--chunks", type=int, default=8, help="chunks per rank (delivery overlaps the next chunk)")
     a = ap.parse_args()
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -81,17 +85,39 @@ def main():
     stream = torch.cuda.Stream(device=dev)
     torch.cuda.set_stream(stream)
     agg.set_stream(stream.cuda_stream)
-    best = 1e30
+    best = best_step = 1e30
+    gather = a.gather if world > 1 else "none"
+    win = sharding.PeerWindow(a.rays, (5,), torch.int32, dst=0) if gather == "peer" else None
+    glob = torch.zeros((a.rays, 5), dtype=torch.int32, device=dev) if (gather == "nccl" and rank == 0) else None
+    n_loc = hi - lo
+    bounds = [n_loc * c // a.chunks for c in range(a.chunks + 1)] if gather == "peer" else [0, n_loc]
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     for _ in range(a.reps):
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
-        agg.IntersectBatch(rays, hits=hits, n=hi - lo)
+        ev0.record(stream)
+        kms = 0.0
+        for c in range(len(bounds) - 1):
+            s0, s1 = bounds[c], bounds[c + 1]
+            if s1 == s0:
+                continue
+            agg.IntersectBatch(rays[s0:s1], hits=hits[s0:s1], n=s1 - s0)
+            if win is not None:
+                win.deliver(hits[s0:s1], stream, at=s0)
+        if win is not None:
+            win.wait_on(stream)
+        elif gather == "nccl":
+            sharding.gather_records(hits, a.rays, dst=0, out=glob)
+        ev1.record(stream)
         torch.cuda.synchronize()
-        t = torch.tensor([agg.last_kernel_ms()], dtype=torch.float64, device=dev)
+        t = torch.tensor([agg.last_kernel_ms() if len(bounds) == 2 else 0.0, ev0.elapsed_time(ev1)],
+                         dtype=torch.float64, device=dev)
         if world > 1:
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        best = min(best, t.item())
+        best, best_step = min(best, t[0].item()), min(best_step, t[1].item())
+    if len(bounds) != 2:
+        best = best_step   # chunked: the kernels' own time is not separable from the overlapped delivery
     hit = hits[:, 0] != -1
     xor = torch.tensor(0, dtype=torch.int64, device=dev)
     tb = hits[:, 1].to(torch.int64)
@@ -107,6 +133,13 @@ def main():
         tot = torch.stack(parts)
         cs = torch.stack([tot[:, 0].sum(), tot[:, 1].sum(), torch.tensor(
             int(np.bitwise_xor.reduce(tot[:, 2].cpu().numpy())), device=dev)])
+    gathered_ok = None
+    if rank == 0 and gather != "none":
+        g = win.tensor if win is not None else glob
+        ghit = g[:, 0] != -1
+        gathered_ok = bool(int(ghit.sum()) == int(cs[0]) and
+                           int(g[:, 0].to(torch.int64)[ghit].sum()) == int(cs[1]) and
+                           bool(torch.equal(g[lo:hi], hits)))
     if rank == 0:
         ok = None
         if a.oracle:
@@ -117,8 +150,11 @@ def main():
             ok = bool(np.array_equal(hits[::stepn].cpu().numpy().view(np.uint32), want))
         print({"config": f"synthetic {a.tris} triangles, {a.rays} random rays", "n_gpus": world,
                "bvh_nodes": int(len(nodes)), "build_s": round(t_build, 1), "kernel_ms": round(best, 2),
-               "Mrays_s": round(a.rays / best / 1e3, 1), "hits": int(cs[0]), "sum_prim": int(cs[1]),
+               "step_ms_with_gather": round(best_step, 2), "gather": gather,
+               "gathered_records_match": gathered_ok, "Mrays_s": round(a.rays / best_step / 1e3, 1), "hits": int(cs[0]), "sum_prim": int(cs[1]),
                "xor_t_bits": int(cs[2]), "oracle_subset_bit_exact": ok}, flush=True)
+    if win is not None:
+        win.close()
     if world > 1:
         dist.destroy_process_group()
 
