@@ -135,6 +135,83 @@ class GPUBVHAggregate {
         Upload();
     }
 
+    // TransformedPrimitive instances over per-object BVHAggregates (cpu/primitive.cpp:112-130; what pbrt
+    // builds for ObjectInstance, scene.cpp:1541-1571).  objectTris9[j]: object j's triangles in its own
+    // space; caller primitive i < nTris is top-level triangle i, primitive nTris + k is instance k.
+    // Every tree (each object's and the top level) comes from the library's host builder.
+    struct ObjectTree {
+        std::vector<nnbvh_node> nodes;
+        std::vector<float> orderedTris9;
+        std::vector<uint32_t> order;
+    };
+    GPUBVHAggregate(const std::vector<float> &tris9, const std::vector<std::vector<float>> &objectTris9,
+                    const std::vector<nnbvh_instance> &instances, int maxPrimsInNode = 1,
+                    SplitMethod splitMethod = SplitMethod::SAH, int device = -1, int buildThreads = 0) {
+        const uint32_t nTris = (uint32_t)(tris9.size() / 9), nInst = (uint32_t)instances.size();
+        const uint32_t nPrims = nTris + nInst;
+        CreateEngine(device);
+        if (nInst == 0) FailWith(NNBVH_ERR_INVALID, "GPUBVHAggregate: no instances given");
+        objects_.resize(objectTris9.size());
+        for (size_t j = 0; j < objectTris9.size(); ++j) {
+            const std::vector<float> &src = objectTris9[j];
+            const uint32_t n = (uint32_t)(src.size() / 9);
+            ObjectTree &o = objects_[j];
+            o.nodes.resize(2 * (size_t)std::max(n, 1u));
+            o.order.resize(n);
+            uint32_t nNodes = 0;
+            if (int rc = nnbvh_build_bvh(src.data(), n, maxPrimsInNode, (int)splitMethod, buildThreads,
+                                         o.nodes.data(), &nNodes, o.order.data())) Fail(rc);
+            o.nodes.resize(nNodes);
+            o.orderedTris9.resize(9 * (size_t)n);
+            for (uint32_t i = 0; i < n; ++i)
+                for (int k = 0; k < 9; ++k) o.orderedTris9[9 * (size_t)i + k] = src[9 * (size_t)o.order[i] + k];
+        }
+        std::vector<float> bounds(6 * (size_t)nPrims);
+        for (uint32_t i = 0; i < nTris; ++i)
+            for (int k = 0; k < 3; ++k) {
+                const float *p = &tris9[9 * (size_t)i];
+                bounds[6 * (size_t)i + k] = std::min(std::min(p[k], p[3 + k]), p[6 + k]);
+                bounds[6 * (size_t)i + 3 + k] = std::max(std::max(p[k], p[3 + k]), p[6 + k]);
+            }
+        for (uint32_t k = 0; k < nInst; ++k) {  // TransformedPrimitive::Bounds, cpu/primitive.h:94
+            if (instances[k].object >= objects_.size()) FailWith(NNBVH_ERR_INVALID, "GPUBVHAggregate: instance refers to a missing object");
+            if (int rc = nnbvh_instance_bounds(&instances[k], objects_[instances[k].object].nodes[0].bounds,
+                                               &bounds[6 * (size_t)(nTris + k)])) Fail(rc);
+        }
+        nodes_.resize(2 * (size_t)nPrims - 1);
+        order_.resize(nPrims);
+        uint32_t nNodes = 0;
+        if (int rc = nnbvh_build_bvh_bounds(bounds.data(), nPrims, maxPrimsInNode, (int)splitMethod, buildThreads,
+                                            nodes_.data(), &nNodes, order_.data())) Fail(rc);
+        nodes_.resize(nNodes);
+        ordered_.assign(9 * (size_t)nPrims, 0.f);
+        instanceOf_.assign(nPrims, -1);
+        for (uint32_t i = 0; i < nPrims; ++i) {
+            if (order_[i] >= nTris) {
+                instanceOf_[i] = (int32_t)(order_[i] - nTris);
+                continue;
+            }
+            for (int k = 0; k < 9; ++k) ordered_[9 * (size_t)i + k] = tris9[9 * (size_t)order_[i] + k];
+        }
+        instances_ = instances;
+        std::vector<nnbvh_object> objs(objects_.size());
+        for (size_t j = 0; j < objects_.size(); ++j)
+            objs[j] = nnbvh_object{objects_[j].nodes.data(), (uint32_t)objects_[j].nodes.size(),
+                                   objects_[j].orderedTris9.data(), (uint32_t)(objects_[j].orderedTris9.size() / 9)};
+        if (int rc = nnbvh_upload_scene_instanced(e_, nodes_.data(), (uint32_t)nodes_.size(), ordered_.data(),
+                                                  instanceOf_.data(), nPrims, instances_.data(), nInst, objs.data(),
+                                                  (uint32_t)objs.size())) Fail(rc);
+    }
+    // Closest hits of an instanced scene with the primitive inside the object (ordered within the object;
+    // Objects()[j].order maps it to the caller's triangle) as a second plane.
+    void IntersectBatchInstanced(const nnbvh_ray *rays, uint64_t n, nnbvh_hit *hits, uint32_t *innerPrim) const {
+        Check(nnbvh_intersect_closest_instanced(e_, rays, n, hits, innerPrim));
+    }
+    // ordered top-level primitive (Hit::prim) -> instance index, or -1
+    int32_t InstanceOf(uint32_t ordered) const { return instanceOf_.empty() ? -1 : instanceOf_[ordered]; }
+    const std::vector<ObjectTree> &Objects() const { return objects_; }
+    const std::vector<int32_t> &OrderedInstanceIndex() const { return instanceOf_; }
+
     // A ready flattened tree (e.g. an NN-split tree exported in LinearBVHNode layout).
     GPUBVHAggregate(std::vector<nnbvh_node> nodes, std::vector<float> orderedTris9,
                     std::vector<uint32_t> order = {}, int device = -1)
@@ -220,6 +297,11 @@ class GPUBVHAggregate {
         o.smem_top_nodes = -1;
         Check(nnbvh_create(&o, &e_));
     }
+    [[noreturn]] void FailWith(int rc, const char *what) {
+        nnbvh_destroy(e_);
+        e_ = nullptr;
+        throw Error(rc, what);
+    }
     [[noreturn]] void Fail(int rc) {  // constructor failure: the destructor will not run
         std::string msg = nnbvh_last_error();
         nnbvh_destroy(e_);
@@ -245,6 +327,9 @@ class GPUBVHAggregate {
     std::vector<uint32_t> order_;
     std::vector<int32_t> sphereOf_;       // per ordered primitive: -1 triangle, else sphere index
     std::vector<nnbvh_sphere> spheres_;
+    std::vector<int32_t> instanceOf_;     // per ordered top-level primitive: -1 triangle, else instance index
+    std::vector<nnbvh_instance> instances_;
+    std::vector<ObjectTree> objects_;
     nnbvh_engine *e_ = nullptr;
 };
 

@@ -8,6 +8,7 @@
 //   (the pytest wrapper runs it under -m gpu; the CPU suite only compiles it and
 //   checks that it fails loudly with NNBVH_ERR_CUDA when no device is present).
 #include <algorithm>
+#include <cmath>
 #include <cstdio>
 #include <cstring>
 #include <random>
@@ -167,10 +168,93 @@ static int RunSphereCase() {
     }
 }
 
+// TransformedPrimitive instances: top-level triangles + instances of two objects.
+static int RunInstanceCase() {
+    const uint32_t T = 5000, K = 80, N = 60000;
+    std::mt19937 rng(5);
+    std::uniform_real_distribution<float> U(0.f, 1.f);
+    std::normal_distribution<float> G(0.f, 1.f);
+    auto soup = [&](uint32_t n, float lo, float hi, float s) {
+        std::vector<float> t(9 * (size_t)n);
+        for (uint32_t i = 0; i < n; ++i) {
+            float c[3] = {lo + (hi - lo) * U(rng), lo + (hi - lo) * U(rng), lo + (hi - lo) * U(rng)};
+            for (int v = 0; v < 3; ++v)
+                for (int k = 0; k < 3; ++k) t[9 * (size_t)i + 3 * v + k] = c[k] + s * (2 * U(rng) - 1);
+        }
+        return t;
+    };
+    std::vector<float> tris = soup(T, 0.f, 1.f, 0.02f);
+    std::vector<std::vector<float>> objs = {soup(600, -0.2f, 0.2f, 0.03f), soup(1, -0.1f, 0.1f, 0.1f)};
+    std::vector<nnbvh_instance> inst(K);
+    for (uint32_t k = 0; k < K; ++k) {  // rotation about z, uniform scale, translation; inverse written out by hand
+        const float a = 6.2831853f * U(rng), c = std::cos(a), s = std::sin(a), sc = 0.2f + 0.3f * U(rng);
+        const float t[3] = {U(rng), U(rng), U(rng)};
+        const float r[12] = {sc * c, -sc * s, 0, t[0], sc * s, sc * c, 0, t[1], 0, 0, sc, t[2]};
+        const float ic = c / sc, is = s / sc;
+        const float o[12] = {ic, is, 0, -(ic * t[0] + is * t[1]), -is, ic, 0, -(-is * t[0] + ic * t[1]), 0, 0, 1 / sc, -t[2] / sc};
+        std::memcpy(inst[k].renderFromPrimitive, r, sizeof r);
+        std::memcpy(inst[k].primitiveFromRender, o, sizeof o);
+        inst[k].object = k % 2;
+        inst[k].reserved[0] = inst[k].reserved[1] = inst[k].reserved[2] = 0;
+    }
+    try {
+        nnbvh::GPUBVHAggregate agg(tris, objs, inst, 4, Split::SAH);
+        // the oracle's view of the same trees
+        std::vector<nnbvh_oracle_node> objNodes;
+        std::vector<float> objTris;
+        std::vector<int32_t> nodeBase, primBase, instObject(K);
+        for (const auto &o : agg.Objects()) {
+            nodeBase.push_back((int32_t)objNodes.size());
+            primBase.push_back((int32_t)(objTris.size() / 9));
+            const nnbvh_oracle_node *nd = reinterpret_cast<const nnbvh_oracle_node *>(o.nodes.data());
+            objNodes.insert(objNodes.end(), nd, nd + o.nodes.size());
+            objTris.insert(objTris.end(), o.orderedTris9.begin(), o.orderedTris9.end());
+        }
+        std::vector<float> inst24(24 * (size_t)K);
+        for (uint32_t k = 0; k < K; ++k) {
+            std::memcpy(&inst24[24 * (size_t)k], inst[k].renderFromPrimitive, 96);
+            instObject[k] = (int32_t)inst[k].object;
+        }
+        std::vector<nnbvh_ray> rays(N);
+        for (uint32_t i = 0; i < N; ++i) {
+            nnbvh_ray &r = rays[i];
+            r.ox = -0.25f + 1.5f * U(rng); r.oy = -0.25f + 1.5f * U(rng); r.oz = -0.25f + 1.5f * U(rng);
+            r.dx = G(rng); r.dy = G(rng); r.dz = G(rng);
+            r.tMax = (i & 1) ? U(rng) : std::numeric_limits<float>::infinity();
+            r.time = 0.f;
+        }
+        std::vector<nnbvh_hit> hits(N);
+        std::vector<uint32_t> inner(N), want(5 * (size_t)N), winner(N);
+        std::vector<uint8_t> occ(N), wocc(N);
+        agg.IntersectBatchInstanced(rays.data(), N, hits.data(), inner.data());
+        agg.IntersectPBatch(rays.data(), N, occ.data());
+        const nnbvh_oracle_node *top = reinterpret_cast<const nnbvh_oracle_node *>(agg.Nodes().data());
+        nnbvh_oracle_intersect_instanced(top, agg.OrderedTriangles().data(), agg.OrderedInstanceIndex().data(), inst24.data(),
+                                         instObject.data(), objNodes.data(), nodeBase.data(), objTris.data(), primBase.data(),
+                                         &rays[0].ox, N, want.data(), winner.data(), nullptr, nullptr, nullptr, 0);
+        nnbvh_oracle_intersect_instanced(top, agg.OrderedTriangles().data(), agg.OrderedInstanceIndex().data(), inst24.data(),
+                                         instObject.data(), objNodes.data(), nodeBase.data(), objTris.data(), primBase.data(),
+                                         &rays[0].ox, N, nullptr, nullptr, wocc.data(), nullptr, nullptr, 0);
+        if (std::memcmp(hits.data(), want.data(), 20 * (size_t)N) != 0) { std::printf("FAIL: instanced closest-hit records differ\n"); return 1; }
+        if (std::memcmp(inner.data(), winner.data(), 4 * (size_t)N) != 0) { std::printf("FAIL: inner primitives differ\n"); return 1; }
+        if (std::memcmp(occ.data(), wocc.data(), N) != 0) { std::printf("FAIL: instanced any-hit results differ\n"); return 1; }
+        uint32_t onInst = 0;
+        for (uint32_t i = 0; i < N; ++i) onInst += inner[i] != NNBVH_MISS;
+        if (onInst < 500) { std::printf("FAIL: only %u instance hits\n", onInst); return 1; }
+        std::printf("PASS instances: %u triangles + %u instances of 2 objects, %u rays bit-exact vs oracle (%u instance hits)\n", T, K, N, onInst);
+        return 0;
+    } catch (const nnbvh::Error &e) {
+        std::printf("nnbvh::Error %d: %s\n", e.code, e.what());
+        return e.code == NNBVH_ERR_CUDA ? 3 : 2;
+    }
+}
+
 int main(int, char **) {
     int rc = RunCase(Split::SAH, NNBVH_ORACLE_SAH, "sah");
     if (rc) return rc;
     rc = RunCase(Split::HLBVH, NNBVH_ORACLE_HLBVH, "hlbvh");
     if (rc) return rc;
-    return RunSphereCase();
+    rc = RunSphereCase();
+    if (rc) return rc;
+    return RunInstanceCase();
 }
