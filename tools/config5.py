@@ -2,7 +2,9 @@
 """tools/config5.py -- BASELINE.json configs[4]: synthetic 10M-triangle mesh, 256M random rays,
 sharded over the ranks it is launched with (torchrun); the hit records are returned to rank 0 inside
 the timed region (--gather peer: copy engines into a peer-mapped window over NVLink, chunk by chunk while
-the next chunk is traced; --gather nccl: one NCCL gather after the kernel; none: kernel only).
+the next chunk is traced; --gather direct: the traversal kernel itself stores each hit record into
+rank 0's window through the peer mapping (SM stores over NVLink, no copy at all); --gather nccl: one
+NCCL gather after the kernel; none: kernel only).
 
 Ray i is a pure function of its GLOBAL index (counter-based hash), so every world size traces the
 same 256M rays; rank g takes the contiguous slice shard_range(N, g, G).  The
@@ -62,7 +64,7 @@ def main():
     ap.add_argument("--rays", type=int, default=256 << 20)
     ap.add_argument("--oracle", type=int, default=200_000)
     ap.add_argument("--reps", type=int, default=3)
-    ap.add_argument("--gather", default="peer", choices=["peer", "nccl", "none"])
+    ap.add_argument("--gather", default="peer", choices=["peer", "direct", "nccl", "none"])
     ap.add_argument("--chunks", type=int, default=8, help="chunks per rank (delivery overlaps the next chunk)")
     a = ap.parse_args()
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -87,10 +89,12 @@ def main():
     agg.set_stream(stream.cuda_stream)
     best = best_step = 1e30
     gather = a.gather if world > 1 else "none"
-    win = sharding.PeerWindow(a.rays, (5,), torch.int32, dst=0) if gather == "peer" else None
+    win = sharding.PeerWindow(a.rays, (5,), torch.int32, dst=0) if gather in ("peer", "direct") else None
+    direct = gather == "direct"
     glob = torch.zeros((a.rays, 5), dtype=torch.int32, device=dev) if (gather == "nccl" and rank == 0) else None
     n_loc = hi - lo
-    bounds = [n_loc * c // a.chunks for c in range(a.chunks + 1)] if gather == "peer" else [0, n_loc]
+    nch = a.chunks if gather == "peer" else 1
+    bounds = [n_loc * c // nch for c in range(nch + 1)]
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     for _ in range(a.reps):
         if world > 1:
@@ -102,10 +106,13 @@ def main():
             s0, s1 = bounds[c], bounds[c + 1]
             if s1 == s0:
                 continue
+            if direct:   # the kernel's StoreHit goes straight into rank 0's memory (peer mapping)
+                agg.IntersectBatch(rays[s0:s1], hits=win.base + (lo + s0) * win.row_bytes, n=s1 - s0)
+                continue
             agg.IntersectBatch(rays[s0:s1], hits=hits[s0:s1], n=s1 - s0)
             if win is not None:
                 win.deliver(hits[s0:s1], stream, at=s0)
-        if win is not None:
+        if win is not None and not direct:
             win.wait_on(stream)
         elif gather == "nccl":
             sharding.gather_records(hits, a.rays, dst=0, out=glob)
@@ -116,6 +123,14 @@ def main():
         if world > 1:
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
         best, best_step = min(best, t[0].item()), min(best_step, t[1].item())
+    if direct:   # checksums below read this rank's records: fetch them back from the window (untimed)
+        from nn_bvh_b200 import capi
+        import ctypes
+        if world > 1:
+            dist.barrier()
+        capi.check(capi.lib().nnbvh_peer_copy(capi.ptr(hits), ctypes.c_void_p(win.base + lo * win.row_bytes),
+                                              n_loc * win.row_bytes, ctypes.c_void_p(stream.cuda_stream)))
+        torch.cuda.synchronize()
     if len(bounds) != 2:
         best = best_step   # chunked: the kernels' own time is not separable from the overlapped delivery
     hit = hits[:, 0] != -1
