@@ -65,7 +65,7 @@ def main():
     ap.add_argument("--oracle", type=int, default=200_000)
     ap.add_argument("--reps", type=int, default=3)
     ap.add_argument("--gather", default="peer", choices=["peer", "direct", "nccl", "none"])
-    ap.add_argument("--chunks", type=int, default=8, help="chunks per rank (delivery overlaps the next chunk)")
+    ap.add_argument("--chunks", type=int, default=3, help="chunks per rank (delivery overlaps the next chunk)")
     a = ap.parse_args()
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
