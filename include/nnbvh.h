@@ -258,6 +258,15 @@ int nnbvh_intersect_counters(nnbvh_engine *e, const nnbvh_ray *rays, uint64_t n,
                              int32_t anyHit, nnbvh_hit *hits, uint8_t *occluded,
                              uint32_t *nodesVisited, uint32_t *triTests);
 
+/* A second engine on the same device that SHARES src's uploaded scene (no copy; the device arrays live
+ * until the last engine holding them is destroyed) and has its own stream, scratch and host-pointer
+ * pipeline.  One engine serialises its batches; an integrator that has independent batches in flight --
+ * the shadow rays of bounce k and the closest-hit rays of bounce k+1 -- gives each its own clone and
+ * stream: the second batch's ray-ordering pre-pass and first CTAs fill the SMs the first batch's
+ * persistent CTAs leave as it drains (+5 % on the bench workload, tools/overlap_probe.py).  A later upload
+ * into either engine leaves the other with the old scene. */
+int nnbvh_clone(nnbvh_engine *src, nnbvh_engine **out);
+
 /* Device time (CUDA events on the engine's stream) of the traversal kernel(s)
  * of the most recent intersect call, and kernels launched so far. */
 int nnbvh_last_kernel_ms(nnbvh_engine *e, float *ms);

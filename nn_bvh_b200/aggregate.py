@@ -279,8 +279,18 @@ class GPUBVHAggregate:
             name = "sah"  # the reference warns and falls back to sah (:737-740)
         return cls(tris9, int(p.get("maxnodeprims", 4)), name, **kw)
 
+    def clone(self) -> "GPUBVHAggregate":
+        """A second aggregate on the same device sharing this one's uploaded scene (nnbvh_clone), with its
+        own stream and scratch: independent batches (closest-hit and shadow) can be in flight together."""
+        other = object.__new__(GPUBVHAggregate)
+        other.__dict__.update({k: v for k, v in self.__dict__.items() if k != "_h"})
+        h = ctypes.c_void_p()
+        capi.check(capi.lib().nnbvh_clone(self._h, ctypes.byref(h)))
+        other._h = h
+        return other
+
     def close(self):
-        if getattr(self, "_h", None):
+        if getattr(self, "_h", None) and capi is not None and getattr(capi, "lib", None) is not None:
             capi.lib().nnbvh_destroy(self._h)
             self._h = None
 

@@ -11,6 +11,7 @@
 #include <cstdio>
 #include <cstring>
 #include <deque>
+#include <memory>
 #include <vector>
 
 #include "../../include/nnbvh.h"
@@ -101,6 +102,20 @@ struct Slot {
 
 using namespace nnbvh;
 
+struct SceneStore {
+    DevBuf<nnbvh_node> dNodes;
+    DevBuf<WideNode> dWide;
+    DevBuf<float4> dTris;
+    DevBuf<SphereDev> dSpheres;
+    DevBuf<InstanceDev> dInstances;
+    DevBuf<nnbvh_node> dObjNodes;
+    DevBuf<float4> dObjTris;
+    ~SceneStore() {
+        dNodes.Free(); dWide.Free(); dTris.Free(); dSpheres.Free();
+        dInstances.Free(); dObjNodes.Free(); dObjTris.Free();
+    }
+};
+
 struct nnbvh_engine {
     int device = 0;
     int kernel = NNBVH_KERNEL_AUTO;
@@ -117,13 +132,8 @@ struct nnbvh_engine {
     bool haveScene = false;
     bool boxesRegular = true;  // every node box finite with lo <= hi: the fast slab test is exact
     SceneDev sc{};
-    DevBuf<nnbvh_node> dNodes;
-    DevBuf<WideNode> dWide;
-    DevBuf<float4> dTris;
-    DevBuf<SphereDev> dSpheres;
-    DevBuf<InstanceDev> dInstances;
-    DevBuf<nnbvh_node> dObjNodes;
-    DevBuf<float4> dObjTris;
+    // device copy of the scene: shared by an engine and its clones (nnbvh_clone), freed with the last of them
+    std::shared_ptr<SceneStore> store = std::make_shared<SceneStore>();
     bool hasInstances = false;  // instanced scene: BasicKernel with nested traversal runs
     bool hasSpheres = false;  // scene uploaded with spheres: the SPHERES instantiations run
     // device-pointer path scratch
@@ -232,13 +242,7 @@ extern "C" void nnbvh_destroy(nnbvh_engine *e) {
     if (!e) return;
     cudaSetDevice(e->device);
     cudaDeviceSynchronize();
-    e->dNodes.Free();
-    e->dWide.Free();
-    e->dTris.Free();
-    e->dSpheres.Free();
-    e->dInstances.Free();
-    e->dObjNodes.Free();
-    e->dObjTris.Free();
+    e->store.reset();  // frees the device scene unless a clone still holds it
     if (e->dStats) cudaFree(e->dStats);
     e->scratch.Free();
     for (Slot &s : e->slots) {
@@ -258,6 +262,25 @@ extern "C" void nnbvh_destroy(nnbvh_engine *e) {
 extern "C" int nnbvh_set_stream(nnbvh_engine *e, void *cudaStream) {
     if (!e) return SetError(NNBVH_ERR_INVALID, "nnbvh_set_stream: engine is NULL");
     e->stream = cudaStream ? (cudaStream_t)cudaStream : e->ownStream;
+    return NNBVH_OK;
+}
+
+extern "C" int nnbvh_clone(nnbvh_engine *src, nnbvh_engine **out) {
+    if (!src || !out) return SetError(NNBVH_ERR_INVALID, "nnbvh_clone: NULL argument");
+    nnbvh_options o{};
+    o.device = src->device;
+    o.kernel = src->kernel;
+    o.smem_top_nodes = src->smemTopNodes;
+    nnbvh_engine *e = nullptr;
+    int rc = nnbvh_create(&o, &e);
+    if (rc) return rc;
+    e->store = src->store;  // the scene stays where it is
+    e->sc = src->sc;
+    e->haveScene = src->haveScene;
+    e->boxesRegular = src->boxesRegular;
+    e->hasSpheres = src->hasSpheres;
+    e->hasInstances = src->hasInstances;
+    *out = e;
     return NNBVH_OK;
 }
 
@@ -418,6 +441,11 @@ static int BuildWideLayout(const std::vector<nnbvh_node> &nodes, uint32_t nPrims
 
 }  // namespace nnbvh
 
+// An upload into an engine that shares its scene with clones gets a fresh store: the clones keep theirs.
+static void DetachStore(nnbvh_engine *e) {
+    if (e && e->store.use_count() > 1) e->store = std::make_shared<SceneStore>();
+}
+
 // Sphere::Sphere (shapes.h:117-128): the clamped zMin / zMax the intersection routine uses.
 static int MakeSphereDev(const nnbvh_sphere &s, uint32_t index, SphereDev *out) {
     for (int k = 0; k < 12; ++k)
@@ -445,6 +473,7 @@ static int UploadScene(nnbvh_engine *e, const nnbvh_node *nodes, uint32_t nNodes
 
 extern "C" int nnbvh_upload_scene(nnbvh_engine *e, const nnbvh_node *nodes, uint32_t nNodes,
                                   const float *orderedTriVerts9, uint32_t nPrims) {
+    DetachStore(e);
     return UploadScene(e, nodes, nNodes, orderedTriVerts9, nPrims, nullptr, nullptr, 0);
 }
 
@@ -455,6 +484,7 @@ extern "C" int nnbvh_upload_scene_mixed(nnbvh_engine *e, const nnbvh_node *nodes
         return SetError(NNBVH_ERR_INVALID, "nnbvh_upload_scene_mixed: NULL sphere table / index");
     if (IsDevicePtr(orderedSphereIndex) || IsDevicePtr(spheres))
         return SetError(NNBVH_ERR_INVALID, "nnbvh_upload_scene_mixed: the sphere table and index are host arrays");
+    DetachStore(e);
     return UploadScene(e, nodes, nNodes, orderedTriVerts9, nPrims, nSpheres ? orderedSphereIndex : nullptr,
                        spheres, nSpheres);
 }
@@ -494,16 +524,16 @@ static int UploadScene(nnbvh_engine *e, const nnbvh_node *nodes, uint32_t nNodes
     const uint32_t topCap = 2048;  // 128 KiB of WideNodes at most in shared memory
     int rc = BuildWideLayout(h, nPrims, topCap, wide, last, &rootRef, &topNodes);
     if (rc) return rc;
-    rc = e->dNodes.Reserve(nNodes);
+    rc = e->store->dNodes.Reserve(nNodes);
     if (rc) return rc;
-    rc = e->dWide.Reserve(wide.size());
+    rc = e->store->dWide.Reserve(wide.size());
     if (rc) return rc;
-    rc = e->dTris.Reserve(3 * (size_t)nPrims);
+    rc = e->store->dTris.Reserve(3 * (size_t)nPrims);
     if (rc) return rc;
-    CU(cudaMemcpyAsync(e->dNodes.p, h.data(), sizeof(nnbvh_node) * (size_t)nNodes,
+    CU(cudaMemcpyAsync(e->store->dNodes.p, h.data(), sizeof(nnbvh_node) * (size_t)nNodes,
                        cudaMemcpyHostToDevice, st));
     if (!wide.empty())
-        CU(cudaMemcpyAsync(e->dWide.p, wide.data(), sizeof(WideNode) * wide.size(),
+        CU(cudaMemcpyAsync(e->store->dWide.p, wide.data(), sizeof(WideNode) * wide.size(),
                            cudaMemcpyHostToDevice, st));
     // triangles: stage raw floats + leaf-end flags, pack on the device
     float *dRaw = nullptr;
@@ -527,13 +557,13 @@ static int UploadScene(nnbvh_engine *e, const nnbvh_node *nodes, uint32_t nNodes
         for (uint32_t i = 0; !rc && i < nPrims; ++i)
             if (sphereOf[i] >= (int32_t)nSpheres)
                 rc = SetError(NNBVH_ERR_INVALID, "primitive %u refers to sphere %d of %u", i, sphereOf[i], nSpheres);
-        if (!rc) rc = e->dSpheres.Reserve(nSpheres);
+        if (!rc) rc = e->store->dSpheres.Reserve(nSpheres);
         if (rc) {
             if (dRaw) cudaFree(dRaw);
             cudaFree(dLast);
             return rc;
         }
-        CU(cudaMemcpyAsync(e->dSpheres.p, sd.data(), sizeof(SphereDev) * nSpheres, cudaMemcpyHostToDevice, st));
+        CU(cudaMemcpyAsync(e->store->dSpheres.p, sd.data(), sizeof(SphereDev) * nSpheres, cudaMemcpyHostToDevice, st));
         CU(cudaMalloc(&dSphereOf, sizeof(int32_t) * (size_t)nPrims));
         CU(cudaMemcpyAsync(dSphereOf, sphereOf, sizeof(int32_t) * (size_t)nPrims, cudaMemcpyHostToDevice, st));
         CU(cudaStreamSynchronize(st));  // sd goes out of scope
@@ -548,7 +578,7 @@ static int UploadScene(nnbvh_engine *e, const nnbvh_node *nodes, uint32_t nNodes
         CU(cudaMemcpyAsync(dSphereOf, instanceOf, sizeof(int32_t) * (size_t)nPrims, cudaMemcpyHostToDevice, st));
     }
     PackTrisKernel<<<(nPrims + 255) / 256, 256, 0, st>>>(src, dLast, dSphereOf, instanceOf ? kPrimInstance : kPrimSphere,
-                                                        nPrims, e->dTris.p);
+                                                        nPrims, e->store->dTris.p);
     ++e->launches;
     CU(cudaGetLastError());
     CU(cudaStreamSynchronize(st));
@@ -556,16 +586,16 @@ static int UploadScene(nnbvh_engine *e, const nnbvh_node *nodes, uint32_t nNodes
     cudaFree(dLast);
     if (dSphereOf) cudaFree(dSphereOf);
     SceneDev sc{};
-    sc.nodes = e->dNodes.p;
-    sc.wide = e->dWide.p;
-    sc.tris = e->dTris.p;
+    sc.nodes = e->store->dNodes.p;
+    sc.wide = e->store->dWide.p;
+    sc.tris = e->store->dTris.p;
     sc.nNodes = nNodes;
     sc.nWide = (uint32_t)wide.size();
     sc.nPrims = nPrims;
     for (int k = 0; k < 6; ++k) sc.rootBox[k] = h[0].bounds[k];
     sc.rootRef = rootRef;
     sc.topNodes = topNodes;
-    sc.spheres = sphereOf ? e->dSpheres.p : nullptr;
+    sc.spheres = sphereOf ? e->store->dSpheres.p : nullptr;
     e->sc = sc;
     e->hasSpheres = sphereOf != nullptr;
     e->haveScene = true;
@@ -603,6 +633,7 @@ extern "C" int nnbvh_upload_scene_instanced(nnbvh_engine *e, const nnbvh_node *n
     if (!instances || !objects || !orderedInstanceIndex || nInstances == 0 || nObjects == 0)
         return SetError(NNBVH_ERR_INVALID, "nnbvh_upload_scene_instanced: NULL / empty instance or object table");
     CU(cudaSetDevice(e->device));
+    DetachStore(e);
     cudaStream_t st = e->stream;
     // the objects: validate each tree, lay trees and triangles back to back
     std::vector<nnbvh_node> allNodes;
@@ -641,9 +672,9 @@ extern "C" int nnbvh_upload_scene_instanced(nnbvh_engine *e, const nnbvh_node *n
         id[k].pad = 0;
     }
     const uint32_t nObjPrims = (uint32_t)allLast.size();
-    int rc = e->dObjNodes.Reserve(allNodes.size());
-    if (!rc) rc = e->dObjTris.Reserve(3 * (size_t)nObjPrims);
-    if (!rc) rc = e->dInstances.Reserve(nInstances);
+    int rc = e->store->dObjNodes.Reserve(allNodes.size());
+    if (!rc) rc = e->store->dObjTris.Reserve(3 * (size_t)nObjPrims);
+    if (!rc) rc = e->store->dInstances.Reserve(nInstances);
     if (rc) return rc;
     float *dRaw = nullptr;
     uint8_t *dLast = nullptr;
@@ -651,9 +682,9 @@ extern "C" int nnbvh_upload_scene_instanced(nnbvh_engine *e, const nnbvh_node *n
     CU(cudaMalloc(&dLast, nObjPrims));
     CU(cudaMemcpyAsync(dRaw, allTris.data(), sizeof(float) * allTris.size(), cudaMemcpyHostToDevice, st));
     CU(cudaMemcpyAsync(dLast, allLast.data(), nObjPrims, cudaMemcpyHostToDevice, st));
-    CU(cudaMemcpyAsync(e->dObjNodes.p, allNodes.data(), sizeof(nnbvh_node) * allNodes.size(), cudaMemcpyHostToDevice, st));
-    CU(cudaMemcpyAsync(e->dInstances.p, id.data(), sizeof(InstanceDev) * nInstances, cudaMemcpyHostToDevice, st));
-    PackTrisKernel<<<(nObjPrims + 255) / 256, 256, 0, st>>>(dRaw, dLast, nullptr, 0u, nObjPrims, e->dObjTris.p);
+    CU(cudaMemcpyAsync(e->store->dObjNodes.p, allNodes.data(), sizeof(nnbvh_node) * allNodes.size(), cudaMemcpyHostToDevice, st));
+    CU(cudaMemcpyAsync(e->store->dInstances.p, id.data(), sizeof(InstanceDev) * nInstances, cudaMemcpyHostToDevice, st));
+    PackTrisKernel<<<(nObjPrims + 255) / 256, 256, 0, st>>>(dRaw, dLast, nullptr, 0u, nObjPrims, e->store->dObjTris.p);
     ++e->launches;
     CU(cudaGetLastError());
     CU(cudaStreamSynchronize(st));
@@ -662,9 +693,9 @@ extern "C" int nnbvh_upload_scene_instanced(nnbvh_engine *e, const nnbvh_node *n
     // the top level: triangles and instance slots
     rc = UploadScene(e, nodes, nNodes, orderedTriVerts9, nPrims, nullptr, nullptr, 0, orderedInstanceIndex, nInstances);
     if (rc) return rc;
-    e->sc.instances = e->dInstances.p;
-    e->sc.objNodes = e->dObjNodes.p;
-    e->sc.objTris = e->dObjTris.p;
+    e->sc.instances = e->store->dInstances.p;
+    e->sc.objNodes = e->store->dObjNodes.p;
+    e->sc.objTris = e->store->dObjTris.p;
     e->hasInstances = true;
     return NNBVH_OK;
 }

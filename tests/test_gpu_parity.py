@@ -325,3 +325,45 @@ def test_read_bandwidth_probe_orders_l2_above_hbm():
     with pytest.raises(nb.NnbvhError):
         agg.read_bandwidth_probe(0, 1)
     agg.close()
+
+
+@pytest.mark.gpu
+def test_clone_shares_the_scene_and_runs_concurrently(oracle):
+    """nnbvh_clone: a second engine on the same uploaded scene with its own stream; batches issued on both at
+    once give the oracle's records; the clone survives the original and a re-upload into the original."""
+    import torch
+    import nn_bvh_b200 as nb
+    from conftest import rand_rays, soup
+    rng = np.random.default_rng(77)
+    tris = soup(rng, 30_000, 0.02)
+    a = nb.GPUBVHAggregate(tris, 4, "sah")
+    b = a.clone()
+    N = 300_000
+    rays = rand_rays(rng, N)
+    rays[N // 2:, 3] = rng.random(N - N // 2)
+    nodes = a.nodes.view(np.uint32).reshape(-1, 8)
+    want = oracle.intersect(nodes, a.ordered_tris9, rays)
+    wocc = oracle.intersect_p(nodes, a.ordered_tris9, rays)
+    sa, sb = torch.cuda.Stream(), torch.cuda.Stream()
+    a.set_stream(sa.cuda_stream)
+    b.set_stream(sb.cuda_stream)
+    d = torch.from_numpy(rays).cuda()
+    hits = torch.zeros((N, 5), dtype=torch.int32, device="cuda")
+    occ = torch.zeros(N, dtype=torch.uint8, device="cuda")
+    torch.cuda.synchronize()
+    for _ in range(3):
+        a.IntersectBatch(d, hits=hits, n=N)
+        b.IntersectPBatch(d, occluded=occ, n=N)
+    torch.cuda.synchronize()
+    assert np.array_equal(hits.cpu().numpy().view(np.uint32), want)
+    assert np.array_equal(occ.cpu().numpy(), wocc)
+    # a new scene in the original leaves the clone on the old one; then the original goes away
+    a2 = nb.GPUBVHAggregate(tris[:1000], 4, "sah")
+    from nn_bvh_b200 import capi
+    capi.check(capi.lib().nnbvh_upload_scene(a._h, capi.ptr(a2.nodes), len(a2.nodes), capi.ptr(a2.ordered_tris9),
+                                             len(a2.ordered_tris9)))
+    small = oracle.intersect(a2.nodes.view(np.uint32).reshape(-1, 8), a2.ordered_tris9, rays[:50_000])
+    assert np.array_equal(np.ascontiguousarray(a.IntersectBatch(rays[:50_000])).view(np.uint32).reshape(-1, 5), small)
+    a.close()
+    assert np.array_equal(np.ascontiguousarray(b.IntersectBatch(rays)).view(np.uint32).reshape(-1, 5), want)
+    b.close()
