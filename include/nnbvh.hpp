@@ -22,6 +22,7 @@
 #include <cstddef>
 #include <cstdint>
 #include <limits>
+#include <memory>
 #include <optional>
 #include <stdexcept>
 #include <string>
@@ -219,6 +220,12 @@ class GPUBVHAggregate {
         Open(device);
     }
 
+    // A second aggregate on the same uploaded scene (nnbvh_clone: nothing is copied on the device) with its
+    // own stream and scratch, so that independent batches can be in flight together.
+    std::unique_ptr<GPUBVHAggregate> Clone() const {
+        return std::unique_ptr<GPUBVHAggregate>(new GPUBVHAggregate(CloneTag{}, *this));
+    }
+
     GPUBVHAggregate(const GPUBVHAggregate &) = delete;
     GPUBVHAggregate &operator=(const GPUBVHAggregate &) = delete;
     ~GPUBVHAggregate() { nnbvh_destroy(e_); }
@@ -290,6 +297,12 @@ class GPUBVHAggregate {
     nnbvh_engine *Handle() const { return e_; }
 
   private:
+    struct CloneTag {};
+    GPUBVHAggregate(CloneTag, const GPUBVHAggregate &o)
+        : nodes_(o.nodes_), ordered_(o.ordered_), order_(o.order_), sphereOf_(o.sphereOf_), spheres_(o.spheres_),
+          instanceOf_(o.instanceOf_), instances_(o.instances_), objects_(o.objects_) {
+        Check(nnbvh_clone(o.e_, &e_));
+    }
     void CreateEngine(int device) {
         nnbvh_options o{};
         o.device = device;

@@ -67,6 +67,14 @@ static int RunCase(Split split, int oracleSplit, const char *name) {
         if (std::memcmp(hits.data(), want.data(), 20 * (size_t)N) != 0) { std::printf("FAIL: closest-hit records differ\n"); return 1; }
         if (std::memcmp(occ.data(), wocc.data(), N) != 0) { std::printf("FAIL: any-hit results differ\n"); return 1; }
 
+        // a clone shares the uploaded scene and answers the same
+        {
+            auto twin = agg.Clone();
+            std::vector<uint8_t> occ2(N);
+            twin->IntersectPBatch(rays.data(), N, occ2.data());
+            if (std::memcmp(occ2.data(), wocc.data(), N) != 0) { std::printf("FAIL: clone's any-hit results differ\n"); return 1; }
+        }
+
         // single-ray surface
         uint32_t nHit = 0;
         for (uint32_t i = 0; i < 64; ++i) {
