@@ -383,6 +383,9 @@ def run_ours(args):
     # wavefront/aggregate.cpp:34-68) -> nnbvh_intersect_{closest,any}_soa.  The 32-byte AoS form
     # is timed too and reported as e2e.aos_value.
     agg.set_stream(0)   # engine's own streams for the chunked H2D / kernel / D2H pipeline
+    agg2.set_stream(0)
+    from concurrent.futures import ThreadPoolExecutor
+    pool = ThreadPoolExecutor(2)   # the two lanes again: two host threads, one engine each (ctypes drops the GIL)
     bf = bounce.view(np.float32).reshape(-1, 8)
     sf = shadow.view(np.float32).reshape(-1, 8)
     pb = [torch.from_numpy(np.ascontiguousarray(bf[:, k])).pin_memory() for k in (0, 1, 2, 4, 5, 6)]
@@ -394,7 +397,15 @@ def run_ours(args):
     e2e_steps = max(2, min(args.steps, 10))
 
     def e2e_soa():
-        agg.IntersectBatchSoA(*pb, None, hits=h_hits)           # tMax plane NULL = Infinity
+        # closest and shadow batches in flight together: the shadow lane's uploads fill the link while the
+        # closest lane's hit records come back, and neither pipeline's start-up / drain leaves it idle
+        f1 = pool.submit(agg.IntersectBatchSoA, *pb, None, hits=h_hits)           # tMax plane NULL = Infinity
+        f2 = pool.submit(agg2.IntersectBatchSoA, *ps, hits=h_occ, any_hit=True)
+        f1.result()
+        f2.result()
+
+    def e2e_soa_one_lane():
+        agg.IntersectBatchSoA(*pb, None, hits=h_hits)
         agg.IntersectBatchSoA(*ps, hits=h_occ, any_hit=True)
 
     def e2e_aos():
@@ -415,6 +426,9 @@ def run_ours(args):
         return world * 2 * n * e2e_steps / tt.item() / 1e6
 
     e2e_aos_val = time_e2e(e2e_aos)
+    assert torch.equal(h_hits, d_hits.cpu()) and torch.equal(h_occ, d_occ.cpu())
+    h_hits.zero_(); h_occ.zero_()
+    e2e_one_lane_val = time_e2e(e2e_soa_one_lane)
     assert torch.equal(h_hits, d_hits.cpu()) and torch.equal(h_occ, d_occ.cpu())
     h_hits.zero_(); h_occ.zero_()
     e2e_val = time_e2e(e2e_soa)
@@ -491,6 +505,9 @@ def run_ours(args):
                     "d2h_bytes_per_step": n * 20 + n, "steps": e2e_steps,
                     "layout": "SoA planes (wavefront queue layout): 6 float planes closest, 7 shadow; "
                               "20-byte hit records + occlusion bytes back",
+                    "lanes": "closest and shadow batches issued together from two host threads, one engine each "
+                             "(nnbvh_clone: one uploaded scene)",
+                    "one_lane_value": e2e_one_lane_val,
                     "aos_value": e2e_aos_val, "aos_h2d_bytes_per_step": 2 * n * 32},
             "gpu_launches": int(launches), "clocks": clk, "roofline": roofline,
             "cpu_baseline": cpu_baseline}
