@@ -213,7 +213,7 @@ inline bool InteractionFromIntersection(const TriangleMeshView &mesh, int triInd
     FromValueAndError(pHit.y, pError.y, &out->piLow[1], &out->piHigh[1]);
     FromValueAndError(pHit.z, pError.z, &out->piLow[2], &out->piHigh[2]);
     out->uv[0] = uvHit[0], out->uv[1] = uvHit[1];
-    Store3(out->wo, V3{wo[0], wo[1], wo[2]});
+    Store3(out->wo, Normalize(V3{wo[0], wo[1], wo[2]}));  // Interaction(pi, n, uv, wo, time), interaction.h:30-32
     out->time = time;
     Store3(out->dpdu, dpdu);
     Store3(out->dpdv, dpdv);
@@ -280,6 +280,153 @@ inline bool InteractionFromIntersection(const TriangleMeshView &mesh, int triInd
     Store3(out->shading.dndu, sdndu);
     Store3(out->shading.dndv, sdndv);
     return true;
+}
+
+// ---- sphere hits ---------------------------------------------------------------------------
+// What Sphere keeps beside nnbvh_sphere (shapes.h:117-128): the clamped z range's polar angles, phiMax
+// in radians, the two orientation flags.  The same libm (std::acos, std::atan2) as the reference
+// build uses is the one linked here: the host side of a drop-in is compiled with the reference.
+struct SphereShape {
+    const float *renderFromObject;  // 12 floats each, rows 0..2 of the 4x4 (row 3 = 0 0 0 1)
+    const float *objectFromRender;
+    float radius, thetaZMin, thetaZMax, phiMax;
+    bool reverseOrientation, transformSwapsHandedness;
+};
+
+namespace detail {
+inline float Clamp(float v, float lo, float hi) { return v < lo ? lo : (v > hi ? hi : v); }  // math.h:236-244
+// Transform::SwapsHandedness (transform.cpp:145-152) over Determinant(SquareMatrix<3>), math.h:1420-1426
+inline bool SwapsHandedness(const float *m) {
+    float minor12 = DoP(m[5], m[10], m[6], m[9]);
+    float minor02 = DoP(m[4], m[10], m[6], m[8]);
+    float minor01 = DoP(m[4], m[9], m[5], m[8]);
+    float det = std::fma(m[2], minor01, DoP(m[0], minor12, m[1], minor02));
+    return det < 0;
+}
+// Transform::operator()(Vector3<T>), transform.h:322-326
+inline V3 XfVector(const float *m, V3 v) {
+    return V3{m[0] * v.x + m[1] * v.y + m[2] * v.z, m[4] * v.x + m[5] * v.y + m[6] * v.z,
+              m[8] * v.x + m[9] * v.y + m[10] * v.z};
+}
+// Transform::operator()(Normal3<T>): the inverse's transpose, transform.h:329-334
+inline V3 XfNormal(const float *mInv, V3 n) {
+    return V3{mInv[0] * n.x + mInv[4] * n.y + mInv[8] * n.z, mInv[1] * n.x + mInv[5] * n.y + mInv[9] * n.z,
+              mInv[2] * n.x + mInv[6] * n.y + mInv[10] * n.z};
+}
+inline float DotV(V3 v, V3 w) { return v.x * w.x + v.y * w.y + v.z * w.z; }  // vecmath.h:964-967
+}  // namespace detail
+
+inline SphereShape MakeSphereShape(const nnbvh_sphere &s, bool reverseOrientation) {
+    using namespace detail;
+    SphereShape o;
+    o.renderFromObject = s.renderFromObject, o.objectFromRender = s.objectFromRender;
+    o.radius = s.radius;
+    o.thetaZMin = std::acos(Clamp(std::min(s.zMin, s.zMax) / s.radius, -1, 1));
+    o.thetaZMax = std::acos(Clamp(std::max(s.zMin, s.zMax) / s.radius, -1, 1));
+    o.phiMax = (3.14159265358979323846f / 180) * Clamp(s.phiMax, 0, 360);  // Radians(), math.h:261-263
+    o.reverseOrientation = reverseOrientation;
+    o.transformSwapsHandedness = SwapsHandedness(s.renderFromObject);
+    return o;
+}
+
+// Transform::operator()(const SurfaceInteraction &), util/transform.cpp:229-261, for the fields
+// SurfaceHit carries.  m / mInv: rows 0..2 of the transform and of its inverse.
+inline void TransformSurfaceHit(const float *m, const float *mInv, SurfaceHit *h) {
+    using namespace detail;
+    // ret.pi = t(si.pi): Transform::operator()(const Point3fi &), transform.h:133-176
+    float x = (h->piLow[0] + h->piHigh[0]) / 2, y = (h->piLow[1] + h->piHigh[1]) / 2,
+          z = (h->piLow[2] + h->piHigh[2]) / 2;  // Interval::Midpoint, math.h:851
+    float wx = h->piHigh[0] - h->piLow[0], wy = h->piHigh[1] - h->piLow[1], wz = h->piHigh[2] - h->piLow[2];
+    bool exact = wx == 0 && wy == 0 && wz == 0;
+    float ex = wx / 2, ey = wy / 2, ez = wz / 2;  // Point3fi::Error(), vecmath.h:757
+    float pp[3], pe[3];
+    for (int r = 0; r < 3; ++r) {
+        const float *a = m + 4 * r;
+        pp[r] = (a[0] * x + a[1] * y) + (a[2] * z + a[3]);
+        float mag = Gamma(3) * (std::fabs(a[0] * x) + std::fabs(a[1] * y) + std::fabs(a[2] * z) + std::fabs(a[3]));
+        if (exact)
+            pe[r] = mag;
+        else
+            pe[r] = (Gamma(3) + 1) * (std::fabs(a[0]) * ex + std::fabs(a[1]) * ey + std::fabs(a[2]) * ez) + mag;
+    }
+    // row 3 is 0 0 0 1: wp == 1 whenever x, y, z are finite
+    for (int r = 0; r < 3; ++r) {
+        h->p[r] = pp[r], h->pError[r] = pe[r];
+        FromValueAndError(pp[r], pe[r], &h->piLow[r], &h->piHigh[r]);
+    }
+    V3 n = Normalize(XfNormal(mInv, V3{h->n[0], h->n[1], h->n[2]}));
+    Store3(h->n, n);
+    Store3(h->wo, Normalize(XfVector(m, V3{h->wo[0], h->wo[1], h->wo[2]})));
+    Store3(h->dpdu, XfVector(m, V3{h->dpdu[0], h->dpdu[1], h->dpdu[2]}));
+    Store3(h->dpdv, XfVector(m, V3{h->dpdv[0], h->dpdv[1], h->dpdv[2]}));
+    Store3(h->dndu, XfNormal(mInv, V3{h->dndu[0], h->dndu[1], h->dndu[2]}));
+    Store3(h->dndv, XfNormal(mInv, V3{h->dndv[0], h->dndv[1], h->dndv[2]}));
+    auto &s = h->shading;
+    V3 sn = Normalize(XfNormal(mInv, V3{s.n[0], s.n[1], s.n[2]}));
+    Store3(s.dpdu, XfVector(m, V3{s.dpdu[0], s.dpdu[1], s.dpdu[2]}));
+    Store3(s.dpdv, XfVector(m, V3{s.dpdv[0], s.dpdv[1], s.dpdv[2]}));
+    Store3(s.dndu, XfNormal(mInv, V3{s.dndu[0], s.dndu[1], s.dndu[2]}));
+    Store3(s.dndv, XfNormal(mInv, V3{s.dndv[0], s.dndv[1], s.dndv[2]}));
+    if (DotN(sn, n) < 0.f) sn = -sn;  // FaceForward(ret.shading.n, ret.n), vecmath.h:1106-1108
+    Store3(s.n, sn);
+}
+
+// Sphere::InteractionFromIntersection(isect, wo, time), shapes.h:238-280.  pObj is what the engine
+// returns in Hit::{b0,b1,b2} for a sphere leaf; wo is in render space and need not be unit length.
+inline void SphereInteractionFromIntersection(const SphereShape &sp, const float pObj[3], const float wo[3],
+                                              float time, SurfaceHit *out) {
+    using namespace detail;
+    const float Pi = 3.14159265358979323846f;
+    V3 pHit{pObj[0], pObj[1], pObj[2]};
+    float phi = std::atan2(pHit.y, pHit.x);  // QuadricIntersection::phi, shapes.h:194-197
+    if (phi < 0) phi += 2 * Pi;
+    float u = phi / sp.phiMax;
+    float cosTheta = pHit.z / sp.radius;
+    float theta = std::acos(Clamp(cosTheta, -1, 1));  // SafeACos, math.h:350-353
+    float dTheta = sp.thetaZMax - sp.thetaZMin;
+    float v = (theta - sp.thetaZMin) / dTheta;
+    float zRadius = std::sqrt(pHit.x * pHit.x + pHit.y * pHit.y);
+    float cosPhi = pHit.x / zRadius, sinPhi = pHit.y / zRadius;
+    V3 dpdu{-sp.phiMax * pHit.y, sp.phiMax * pHit.x, 0};
+    float sinTheta = std::sqrt(std::max(0.f, 1 - cosTheta * cosTheta));  // SafeSqrt, math.h:276-279
+    V3 dpdv = dTheta * V3{pHit.z * cosPhi, pHit.z * sinPhi, -sp.radius * sinTheta};
+    V3 d2Pduu = (-sp.phiMax * sp.phiMax) * V3{pHit.x, pHit.y, 0};
+    V3 d2Pduv = (dTheta * pHit.z * sp.phiMax) * V3{-sinPhi, cosPhi, 0};
+    V3 d2Pdvv = -(dTheta * dTheta) * pHit;
+    float E = DotV(dpdu, dpdu), F = DotV(dpdu, dpdv), G = DotV(dpdv, dpdv);
+    V3 nn = Normalize(Cross(dpdu, dpdv));
+    float e = DotV(nn, d2Pduu), f = DotV(nn, d2Pduv), g = DotV(nn, d2Pdvv);
+    float EGF2 = DoP(E, G, F, F);
+    float invEGF2 = (EGF2 == 0) ? 0.f : 1 / EGF2;
+    V3 dndu = ((f * F - e * G) * invEGF2) * dpdu + ((e * F - f * E) * invEGF2) * dpdv;
+    V3 dndv = ((g * F - f * G) * invEGF2) * dpdu + ((f * F - g * E) * invEGF2) * dpdv;
+    V3 pError = Gamma(5) * Abs(pHit);
+    bool flipNormal = sp.reverseOrientation ^ sp.transformSwapsHandedness;
+    V3 woObject = XfVector(sp.objectFromRender, V3{wo[0], wo[1], wo[2]});
+
+    // SurfaceInteraction(pi, uv, wo, dpdu, dpdv, dndu, dndv, time, flipNormal), interaction.h:151-180
+    Store3(out->p, pHit);
+    Store3(out->pError, pError);
+    FromValueAndError(pHit.x, pError.x, &out->piLow[0], &out->piHigh[0]);
+    FromValueAndError(pHit.y, pError.y, &out->piLow[1], &out->piHigh[1]);
+    FromValueAndError(pHit.z, pError.z, &out->piLow[2], &out->piHigh[2]);
+    out->uv[0] = u, out->uv[1] = v;
+    Store3(out->wo, Normalize(woObject));  // Interaction(pi, n, uv, wo, time), interaction.h:30-32
+    out->time = time;
+    out->faceIndex = 0;
+    V3 n = nn;
+    if (flipNormal) n = -1.f * n;  // n *= -1
+    Store3(out->n, n);
+    Store3(out->dpdu, dpdu);
+    Store3(out->dpdv, dpdv);
+    Store3(out->dndu, dndu);
+    Store3(out->dndv, dndv);
+    Store3(out->shading.n, n);
+    Store3(out->shading.dpdu, dpdu);
+    Store3(out->shading.dpdv, dpdv);
+    Store3(out->shading.dndu, dndu);
+    Store3(out->shading.dndv, dndv);
+    TransformSurfaceHit(sp.renderFromObject, sp.objectFromRender, out);
 }
 
 // ---- the aggregate -------------------------------------------------------------------------

@@ -337,6 +337,29 @@ class Reference:
         self.lib.nnbvh_ref_sphere_bounds(_p(sphere28), _p(out))
         return out
 
+    def sphere_interaction(self, sphere28, reverse: bool, rays8):
+        """Sphere::Intersect per ray: (hit, tHit, 42 words = the 39 of triangle_interaction + wo)."""
+        sphere28 = np.ascontiguousarray(sphere28, dtype=np.float32)
+        rays8 = np.ascontiguousarray(rays8, dtype=np.float32)
+        n = rays8.shape[0]
+        hit = np.zeros(n, dtype=np.int32)
+        t_hit = np.zeros(n, dtype=np.float32)
+        out = np.zeros((n, 42), dtype=np.float32)
+        f = self.lib.nnbvh_ref_sphere_interaction
+        f.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_int64] + [ctypes.c_void_p] * 3
+        f(_p(sphere28), int(bool(reverse)), _p(rays8), n, _p(hit), _p(t_hit), _p(out))
+        return hit.astype(bool), t_hit, out
+
+    def interaction_wo(self, wo3):
+        """What Interaction's constructor stores for a given wo (interaction.h:30-32)."""
+        wo3 = np.ascontiguousarray(wo3, dtype=np.float32)
+        out = np.zeros_like(wo3)
+        f = self.lib.nnbvh_ref_interaction_wo
+        f.argtypes = [ctypes.c_void_p, ctypes.c_int64, ctypes.c_void_p]
+        f.restype = None
+        f(_p(wo3), wo3.shape[0], _p(out))
+        return out
+
     def export(self, scene, n_tris: int):
         n = self.lib.nnbvh_ref_scene_num_nodes(scene)
         nodes = np.zeros((n, 8), dtype=np.uint32)

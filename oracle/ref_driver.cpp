@@ -543,6 +543,27 @@ void nnbvh_ref_sphere_bounds(const float *sphere28, float *out6) {
     delete rs;
 }
 
+// 39 words of a SurfaceInteraction: pi.low xyz, pi.high xyz, n, uv, dpdu, dpdv, dndu, dndv,
+// shading.{n, dpdu, dpdv, dndu, dndv}, faceIndex (int).
+static void PutSurface39(const pbrt::SurfaceInteraction &si, float *o) {
+    auto put3 = [&o](float x, float y, float z) { *o++ = x, *o++ = y, *o++ = z; };
+    put3(si.pi.x.LowerBound(), si.pi.y.LowerBound(), si.pi.z.LowerBound());
+    put3(si.pi.x.UpperBound(), si.pi.y.UpperBound(), si.pi.z.UpperBound());
+    put3(si.n.x, si.n.y, si.n.z);
+    *o++ = si.uv.x, *o++ = si.uv.y;
+    put3(si.dpdu.x, si.dpdu.y, si.dpdu.z);
+    put3(si.dpdv.x, si.dpdv.y, si.dpdv.z);
+    put3(si.dndu.x, si.dndu.y, si.dndu.z);
+    put3(si.dndv.x, si.dndv.y, si.dndv.z);
+    put3(si.shading.n.x, si.shading.n.y, si.shading.n.z);
+    put3(si.shading.dpdu.x, si.shading.dpdu.y, si.shading.dpdu.z);
+    put3(si.shading.dpdv.x, si.shading.dpdv.y, si.shading.dpdv.z);
+    put3(si.shading.dndu.x, si.shading.dndu.y, si.shading.dndu.z);
+    put3(si.shading.dndv.x, si.shading.dndv.y, si.shading.dndv.z);
+    int fi = si.faceIndex;
+    std::memcpy(o, &fi, 4);
+}
+
 // Triangle::InteractionFromIntersection (shapes.h:884-1010) on a caller-supplied mesh: the host
 // step that turns an engine hit record {prim,t,b0,b1,b2} back into a SurfaceInteraction
 // (pins include/nnbvh_wavefront.hpp).  normals / tangents / uvs may be NULL.
@@ -582,25 +603,44 @@ int nnbvh_ref_triangle_interaction(const float *verts, int nVerts, const int *in
         const float *w = wo_time + 4 * i;
         pbrt::SurfaceInteraction si = pbrt::Triangle::InteractionFromIntersection(
             mesh, tri[i], ti, w[3], pbrt::Vector3f(w[0], w[1], w[2]));
-        float *o = out + 39 * i;
-        auto put3 = [&o](float x, float y, float z) { *o++ = x, *o++ = y, *o++ = z; };
-        put3(si.pi.x.LowerBound(), si.pi.y.LowerBound(), si.pi.z.LowerBound());
-        put3(si.pi.x.UpperBound(), si.pi.y.UpperBound(), si.pi.z.UpperBound());
-        put3(si.n.x, si.n.y, si.n.z);
-        *o++ = si.uv.x, *o++ = si.uv.y;
-        put3(si.dpdu.x, si.dpdu.y, si.dpdu.z);
-        put3(si.dpdv.x, si.dpdv.y, si.dpdv.z);
-        put3(si.dndu.x, si.dndu.y, si.dndu.z);
-        put3(si.dndv.x, si.dndv.y, si.dndv.z);
-        put3(si.shading.n.x, si.shading.n.y, si.shading.n.z);
-        put3(si.shading.dpdu.x, si.shading.dpdu.y, si.shading.dpdu.z);
-        put3(si.shading.dpdv.x, si.shading.dpdv.y, si.shading.dpdv.z);
-        put3(si.shading.dndu.x, si.shading.dndu.y, si.shading.dndu.z);
-        put3(si.shading.dndv.x, si.shading.dndv.y, si.shading.dndv.z);
-        int fi = si.faceIndex;
-        std::memcpy(o, &fi, 4);
+        PutSurface39(si, out + 39 * i);
     }
     return 0;
+}
+
+// Sphere::Intersect (shapes.h:130-139) = BasicIntersect + InteractionFromIntersection (:238-280) on
+// one sphere (28 floats, nnbvh_sphere) with the given reverseOrientation, for n rays
+// {o, tMax, d, time}.  hit[i] = 0/1; where 1: tHit[i] and out[42 i ..] = the 39 words above + the
+// interaction's wo.  Pins include/nnbvh_wavefront.hpp SphereInteractionFromIntersection.
+int nnbvh_ref_sphere_interaction(const float *sphere28, int reverseOrientation, const float *rays8,
+                                 int64_t n, int *hit, float *tHit, float *out) {
+    if (!g_inited)
+        nnbvh_ref_init(0);
+    pbrt::SquareMatrix<4> r = Matrix12(sphere28), o = Matrix12(sphere28 + 12);
+    pbrt::Transform renderFromObject(r, o), objectFromRender(o, r);
+    pbrt::Sphere sphere(&renderFromObject, &objectFromRender, reverseOrientation != 0, sphere28[24],
+                        sphere28[25], sphere28[26], sphere28[27]);
+    for (int64_t i = 0; i < n; ++i) {
+        const float *q = rays8 + 8 * i;
+        pstd::optional<pbrt::ShapeIntersection> si = sphere.Intersect(MakeRay(q), q[3]);
+        hit[i] = si.has_value();
+        if (!si)
+            continue;
+        tHit[i] = si->tHit;
+        PutSurface39(si->intr, out + 42 * i);
+        out[42 * i + 39] = si->intr.wo.x, out[42 * i + 40] = si->intr.wo.y, out[42 * i + 41] = si->intr.wo.z;
+    }
+    return 0;
+}
+
+// Interaction(pi, n, uv, wo, time) (interaction.h:30-32) keeps Normalize(wo): what a triangle
+// hit's SurfaceInteraction::wo holds for the wo = -ray.d it is given.
+void nnbvh_ref_interaction_wo(const float *wo3, int64_t n, float *out3) {
+    for (int64_t i = 0; i < n; ++i) {
+        pbrt::Interaction it(pbrt::Point3fi(), pbrt::Normal3f(), pbrt::Point2f(),
+                             pbrt::Vector3f(wo3[3 * i], wo3[3 * i + 1], wo3[3 * i + 2]), 0.f);
+        out3[3 * i] = it.wo.x, out3[3 * i + 1] = it.wo.y, out3[3 * i + 2] = it.wo.z;
+    }
 }
 
 // Loop subdivision through the reference (util/loopsubdiv.cpp) so that

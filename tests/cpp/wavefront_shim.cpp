@@ -102,6 +102,34 @@ int wf_interaction(const float *verts, int nVerts, const int *indices, int nTris
     return 0;
 }
 
+// Sphere::InteractionFromIntersection on the host: query i is pObj[3i..] (what the engine returns
+// for a sphere leaf) with woTime[4i..]; out42 = the 39 words + the interaction's wo.
+int wf_sphere_interaction(const float *sphere28, int reverseOrientation, const float *pObj,
+                          const float *woTime, int64_t n, float *out42) {
+    nnbvh_sphere s;
+    std::memcpy(&s, sphere28, sizeof s);
+    SphereShape shape = MakeSphereShape(s, reverseOrientation != 0);
+    for (int64_t i = 0; i < n; ++i) {
+        SurfaceHit h;
+        SphereInteractionFromIntersection(shape, pObj + 3 * i, woTime + 4 * i, woTime[4 * i + 3], &h);
+        Pack(h, out42 + 42 * i);
+        std::memcpy(out42 + 42 * i + 39, h.wo, 12);
+    }
+    return 0;
+}
+
+// The wo a triangle hit's interaction stores for the wo it is given
+void wf_interaction_wo(const float *verts9, const float *wo3, int64_t n, float *out3) {
+    int idx[3] = {0, 1, 2};
+    TriangleMeshView v;
+    v.vertexIndices = idx, v.p = verts9;
+    for (int64_t i = 0; i < n; ++i) {
+        SurfaceHit h;
+        InteractionFromIntersection(v, 0, 0.25f, 0.25f, 0.5f, 0.f, wo3 + 3 * i, &h);
+        std::memcpy(out3 + 3 * i, h.wo, 12);
+    }
+}
+
 void *wf_create(const float *verts, int nVerts, const int *indices, int nTris, const float *normals,
                 const float *uvs, int maxPrimsInNode, int splitMethod, int hostThreads) {
     try {

@@ -37,6 +37,9 @@ def shim():
     L.wf_destroy.argtypes = [ctypes.c_void_p]
     L.wf_interaction.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_int] + \
         [ctypes.c_void_p] * 3 + [ctypes.c_int] + [ctypes.c_void_p] * 3 + [ctypes.c_int64, ctypes.c_void_p]
+    L.wf_sphere_interaction.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p,
+                                        ctypes.c_int64, ctypes.c_void_p]
+    L.wf_interaction_wo.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int64, ctypes.c_void_p]
     L.wf_intersect_closest.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_int] + \
         [ctypes.c_void_p] * 5
     L.wf_intersect_shadow.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_int,
@@ -81,6 +84,76 @@ def test_interaction_matches_reference_live(shim, reference):
                                                   normals=c["n"], tangents=c["s"], uvs=c["uv"],
                                                   reverse_orientation=c["reverse"])
             _same(_interaction(shim, c), want, f"{name} seed {seed}")
+
+
+NAMES42 = NAMES39 + ["wo"] * 3
+
+
+def _sphere_interaction(L, sphere28, reverse, p_obj, rays):
+    """The host restatement on the engine's sphere hit records: pObj + (wo = -d, time)."""
+    n = rays.shape[0]
+    wt = np.ascontiguousarray(np.concatenate([-rays[:, 4:7], rays[:, 7:8]], axis=1), dtype=np.float32)
+    p_obj = np.ascontiguousarray(p_obj, dtype=np.float32)
+    s = np.ascontiguousarray(sphere28, dtype=np.float32)
+    out = np.zeros((n, 42), dtype=np.uint32)
+    assert L.wf_sphere_interaction(_p(s), int(bool(reverse)), _p(p_obj), _p(wt), n, _p(out)) == 0
+    return out
+
+
+def _same42(got, want, what):
+    bad = np.argwhere(got != want)
+    assert bad.size == 0, f"{what}: {len(bad)} words differ, first at ray {bad[0][0]} field {NAMES42[bad[0][1]]}"
+
+
+def test_sphere_interaction_matches_reference_golden(shim):
+    """Sphere::InteractionFromIntersection (shapes.h:238-280) + Transform::operator()(SurfaceInteraction)
+    (util/transform.cpp:229-261): all 42 words, bit for bit, for mirrored / clipped / reversed spheres."""
+    g = np.load(os.path.join(GOLDEN, "sphere_interaction.npz"))
+    total = 0
+    for i, s in enumerate(g["spheres"]):
+        hit = g["hit"][i]
+        got = _sphere_interaction(shim, s, g["reverse"][i], g["p_obj"][i], g["rays"][i])
+        _same42(got[hit], g["surf"][i][hit], f"sphere {i}")
+        total += int(hit.sum())
+    assert total > 2000
+
+
+def test_sphere_interaction_matches_reference_live(shim, reference, oracle):
+    from tools.make_golden import random_spheres, sphere_rays
+    rng = np.random.default_rng(77)
+    spheres = random_spheres(rng, 12)
+    spheres[::3, 0:12:4] *= -1          # first column of renderFromObject: a mirror
+    for i, s in enumerate(spheres):
+        m = np.eye(4)
+        m[:3] = s[:12].reshape(3, 4).astype(np.float64)
+        s[12:24] = np.linalg.inv(m)[:3].ravel()
+        rays = sphere_rays(rng, np.repeat(s[None], 300, 0))
+        hit, t_hit, want = reference.sphere_interaction(s, i % 2 == 1, rays)
+        p_obj = np.zeros((300, 3), dtype=np.float32)
+        for k in np.nonzero(hit)[0]:
+            h, o4 = oracle.sphere(rays[k], s)       # the record the engine returns (tests/test_spheres.py)
+            assert h and o4[:1].view(np.uint32)[0] == t_hit[k:k + 1].view(np.uint32)[0]
+            p_obj[k] = o4[1:]
+        got = _sphere_interaction(shim, s, i % 2 == 1, p_obj, rays)
+        _same42(got[hit], want.view(np.uint32)[hit], f"sphere {i}")
+
+
+def _normalize_f32(v):
+    """Normalize(Vector3f) (vecmath.h:948-961) in float32 steps."""
+    v = np.ascontiguousarray(v, dtype=np.float32)
+    ls = v[:, 0] * v[:, 0] + v[:, 1] * v[:, 1] + v[:, 2] * v[:, 2]
+    return v / np.sqrt(ls)[:, None]
+
+
+def test_interaction_stores_normalized_wo(shim):
+    """Interaction(pi, n, uv, wo, time) keeps Normalize(wo) (interaction.h:30-32)."""
+    g = np.load(os.path.join(GOLDEN, "sphere_interaction.npz"))
+    wo = np.ascontiguousarray(g["wo"])
+    v9 = np.array([0, 0, 0, 1, 0, 0, 0, 1, 0], dtype=np.float32)
+    out = np.zeros_like(wo)
+    shim.wf_interaction_wo(_p(v9), _p(wo), wo.shape[0], _p(out))
+    assert np.array_equal(out.view(np.uint32), g["wo_stored"].view(np.uint32))
+    assert np.array_equal(_normalize_f32(wo).view(np.uint32), g["wo_stored"].view(np.uint32))
 
 
 def test_backend_fails_loudly_without_gpu(shim):
@@ -156,7 +229,7 @@ def test_wavefront_queues_closest_and_shadow(shim, oracle, reference, where):
         assert len(hit) > N // 20
         assert np.array_equal(prim[hit], order[want[hit, 0]].astype(np.uint32))      # caller's primitive index
         assert np.array_equal(t_hit[hit].view(np.uint32), want[hit, 1])
-        assert np.array_equal(wo_t[hit, :3], -rays[hit, 4:7]) and np.array_equal(wo_t[hit, 3], rays[hit, 7])
+        assert np.array_equal(wo_t[hit, :3], _normalize_f32(-rays[hit, 4:7])) and np.array_equal(wo_t[hit, 3], rays[hit, 7])
         b = want[hit, 2:5].view(np.float32)
         ref_surf = reference.triangle_interaction(verts, idx, prim[hit].astype(np.int32), b, wo_t[hit],
                                                   normals=nrm, uvs=uv)

@@ -28,6 +28,10 @@ oracle/ref_driver.cpp; the fixtures are small so they can be committed.
                     triangles + 30 instances of 3 objects (one a single triangle): the reference's
                     top-level and per-object trees, TransformedPrimitive::Bounds, closest hits
                     (with the primitive inside the object), IntersectP (--only-instances).
+  sphere_interaction.npz  Sphere::Intersect = BasicIntersect + InteractionFromIntersection
+                    (shapes.h:130-139, :238-280) for 48 spheres x 64 rays: rotated / scaled /
+                    mirrored transforms, z-clipped, reverseOrientation; plus what Interaction's
+                    constructor stores as wo (--only-sphere-interaction).
 """
 import os
 import sys
@@ -371,6 +375,36 @@ def instanced(ref, rng):
     np.savez_compressed(os.path.join(OUT, "instanced.npz"), **out)
 
 
+def sphere_interaction(ref, rng):
+    n_s, n_r = 48, 64
+    spheres = random_spheres(rng, n_s)
+    for i in range(0, n_s, 4):               # mirrored: the transform swaps handedness
+        m = np.eye(4)
+        m[:3] = spheres[i, :12].reshape(3, 4).astype(np.float64)
+        m[:3, 0] *= -1
+        spheres[i, :12] = m[:3].ravel()
+        spheres[i, 12:24] = np.linalg.inv(m)[:3].ravel()
+    reverse = (np.arange(n_s) % 3 == 0)
+    rays = np.zeros((n_s, n_r, 8), dtype=np.float32)
+    hit = np.zeros((n_s, n_r), dtype=bool)
+    t_hit = np.zeros((n_s, n_r), dtype=np.float32)
+    p_obj = np.zeros((n_s, n_r, 3), dtype=np.float32)
+    surf = np.zeros((n_s, n_r, 42), dtype=np.float32)
+    for i in range(n_s):
+        rays[i] = sphere_rays(rng, np.repeat(spheres[i][None], n_r, 0))
+        hit[i], t_hit[i], surf[i] = ref.sphere_interaction(spheres[i], reverse[i], rays[i])
+        for k in range(n_r):
+            h, o4 = ref.sphere(rays[i, k], spheres[i])
+            assert h == hit[i, k]
+            if h:
+                p_obj[i, k] = o4[1:]
+    wo = rng.normal(size=(512, 3)).astype(np.float32) * np.exp(rng.uniform(-3, 3, (512, 1))).astype(np.float32)
+    print("sphere_interaction:", int(hit.sum()), "hits of", hit.size)
+    np.savez_compressed(os.path.join(OUT, "sphere_interaction.npz"), spheres=spheres, reverse=reverse, rays=rays,
+                        hit=hit, t_hit=t_hit, p_obj=p_obj, surf=surf.view(np.uint32), wo=wo,
+                        wo_stored=ref.interaction_wo(wo))
+
+
 if __name__ == "__main__":
     os.makedirs(OUT, exist_ok=True)
     ref = Reference(threads=1)
@@ -383,6 +417,9 @@ if __name__ == "__main__":
     if "--only-interaction" in sys.argv:
         interaction(ref)
         sys.exit(0)
+    if "--only-sphere-interaction" in sys.argv:
+        sphere_interaction(ref, np.random.default_rng(238))
+        sys.exit(0)
     if "--only-hlbvh" in sys.argv:
         hlbvh(ref)
         sys.exit(0)
@@ -394,3 +431,4 @@ if __name__ == "__main__":
     interaction(ref)
     sphere_vectors(ref, np.random.default_rng(147))
     instanced(ref, np.random.default_rng(112))
+    sphere_interaction(ref, np.random.default_rng(238))
