@@ -16,7 +16,10 @@
 // The engine returns {prim, t, b0, b1, b2}; the reference's consumers want a SurfaceInteraction.
 // InteractionFromIntersection() below restates Triangle::InteractionFromIntersection
 // (shapes.h:884-1010) on the host, operation for operation (compile with -ffp-contract=off):
-// tests/test_wavefront.py pins it bit for bit against the reference's own function.
+// tests/test_wavefront.py pins it bit for bit against the reference's own function.  A hit on a
+// sphere leaf comes back as {prim, t, pObj}: SphereInteractionFromIntersection() restates
+// Sphere::InteractionFromIntersection (shapes.h:238-280) and the Transform::operator()
+// (SurfaceInteraction) it ends with (util/transform.cpp:229-261), pinned the same way.
 //
 // No traversal or intersection arithmetic lives here; every query runs on the GPU.
 #ifndef NNBVH_WAVEFRONT_HPP
@@ -451,14 +454,26 @@ class GPUBVHWavefrontAggregate {
         : meshes_(std::move(meshes)), prims_(std::move(prims)),
           hostThreads_(hostThreads > 0 ? hostThreads
                                        : std::max(1u, std::thread::hardware_concurrency())) {
-        std::vector<float> tris9(9 * prims_.size());
-        for (size_t i = 0; i < prims_.size(); ++i) {
-            const TriangleMeshView &m = meshes_[prims_[i].meshIndex];
-            const int *v = &m.vertexIndices[3 * prims_[i].triIndex];
-            for (int k = 0; k < 3; ++k)
-                for (int c = 0; c < 3; ++c) tris9[9 * i + 3 * k + c] = m.p[3 * v[k] + c];
-        }
-        agg_.reset(new GPUBVHAggregate(tris9, maxPrimsInNode, sm, device));
+        agg_.reset(new GPUBVHAggregate(Soup(), maxPrimsInNode, sm, device));
+    }
+
+    // The same with `Shape "sphere"` primitives after the triangles: primitive prims.size() + k of the
+    // list is spheres[k] (full spheres and z-clipped ones; phimax < 360 is refused by the engine).
+    // sphereReverseOrientation[k]: the shape's ReverseOrientation flag (shapes.h:117-123), empty = none.
+    GPUBVHWavefrontAggregate(std::vector<TriangleMeshView> meshes, std::vector<PrimitiveRef> prims,
+                             std::vector<nnbvh_sphere> spheres, std::vector<uint8_t> sphereReverseOrientation,
+                             int maxPrimsInNode = 4,
+                             GPUBVHAggregate::SplitMethod sm = GPUBVHAggregate::SplitMethod::SAH,
+                             int device = -1, int hostThreads = 0)
+        : meshes_(std::move(meshes)), prims_(std::move(prims)), spheres_(std::move(spheres)),
+          hostThreads_(hostThreads > 0 ? hostThreads
+                                       : std::max(1u, std::thread::hardware_concurrency())) {
+        if (!sphereReverseOrientation.empty() && sphereReverseOrientation.size() != spheres_.size())
+            throw Error(NNBVH_ERR_INVALID, "one reverseOrientation flag per sphere");
+        agg_.reset(new GPUBVHAggregate(Soup(), spheres_, maxPrimsInNode, sm, device));
+        for (size_t k = 0; k < spheres_.size(); ++k)  // spheres_ is not resized after this: the pointers hold
+            shapes_.push_back(MakeSphereShape(spheres_[k], !sphereReverseOrientation.empty() &&
+                                                               sphereReverseOrientation[k] != 0));
     }
 
     Bounds3f Bounds() const { return agg_->Bounds(); }  // WavefrontAggregate::Bounds, integrator.h:35
@@ -482,9 +497,15 @@ class GPUBVHWavefrontAggregate {
                 return;
             }
             uint32_t prim = agg_->PrimitiveIndex(h.prim);
-            const PrimitiveRef &pr = prims_[prim];
             float wo[3] = {-d.x[i], -d.y[i], -d.z[i]};
             SurfaceHit sh;
+            if (prim >= prims_.size()) {  // a sphere leaf: {b0,b1,b2} = pObj (Sphere::Intersect, shapes.h:130-139)
+                const float pObj[3] = {h.b0, h.b1, h.b2};
+                SphereInteractionFromIntersection(shapes_[prim - prims_.size()], pObj, wo, d.t ? d.t[i] : 0.f, &sh);
+                sink.EnqueueWorkAfterIntersection(i, prim, h.t, sh);
+                return;
+            }
+            const PrimitiveRef &pr = prims_[prim];
             if (!InteractionFromIntersection(meshes_[pr.meshIndex], pr.triIndex, h.b0, h.b1, h.b2,
                                              d.t ? d.t[i] : 0.f, wo, &sh))
                 throw Error(NNBVH_ERR_INVALID, "hit on a triangle with a zero normal");
@@ -511,6 +532,17 @@ class GPUBVHWavefrontAggregate {
     }
 
   private:
+    // the triangles of the primitive list as 9 floats each
+    std::vector<float> Soup() const {
+        std::vector<float> tris9(9 * prims_.size());
+        for (size_t i = 0; i < prims_.size(); ++i) {
+            const TriangleMeshView &m = meshes_[prims_[i].meshIndex];
+            const int *v = &m.vertexIndices[3 * prims_[i].triIndex];
+            for (int k = 0; k < 3; ++k)
+                for (int c = 0; c < 3; ++c) tris9[9 * i + 3 * k + c] = m.p[3 * v[k] + c];
+        }
+        return tris9;
+    }
     static int Count(int maxRays, int size) {
         if (size < 0 || size > maxRays)
             throw Error(NNBVH_ERR_INVALID, "queue size exceeds maxRays");  // the queues are allocated for maxQueueSize
@@ -565,6 +597,8 @@ class GPUBVHWavefrontAggregate {
 
     std::vector<TriangleMeshView> meshes_;
     std::vector<PrimitiveRef> prims_;
+    std::vector<nnbvh_sphere> spheres_;
+    std::vector<SphereShape> shapes_;
     int hostThreads_;
     std::unique_ptr<GPUBVHAggregate> agg_;
     mutable std::vector<nnbvh_hit> hits_;

@@ -147,6 +147,30 @@ void *wf_create(const float *verts, int nVerts, const int *indices, int nTris, c
     }
 }
 
+// The same scene with nSpheres `Shape "sphere"` primitives (28 floats each, nnbvh_sphere) after the
+// triangles; reverse: one flag per sphere or NULL.
+void *wf_create_mixed(const float *verts, int nVerts, const int *indices, int nTris, const float *normals,
+                      const float *uvs, const float *spheres28, int nSpheres, const uint8_t *reverse,
+                      int maxPrimsInNode, int splitMethod, int hostThreads) {
+    try {
+        auto *s = new Scene;
+        s->mesh = MakeMesh(verts, nVerts, indices, nTris, normals, nullptr, uvs);
+        std::vector<GPUBVHWavefrontAggregate::PrimitiveRef> prims(nTris);
+        for (int i = 0; i < nTris; ++i) prims[i] = {0, i};
+        std::vector<nnbvh_sphere> sph(nSpheres);
+        std::memcpy(sph.data(), spheres28, sizeof(nnbvh_sphere) * (size_t)nSpheres);
+        std::vector<uint8_t> rev;
+        if (reverse) rev.assign(reverse, reverse + nSpheres);
+        s->agg.reset(new GPUBVHWavefrontAggregate(
+            {s->mesh.View(false)}, prims, sph, rev, maxPrimsInNode,
+            (nnbvh::GPUBVHAggregate::SplitMethod)splitMethod, -1, hostThreads));
+        return s;
+    } catch (const nnbvh::Error &e) {
+        g_what = e.what();
+        return nullptr;
+    }
+}
+
 void wf_destroy(void *scene) { delete (Scene *)scene; }
 
 // planes: ox oy oz dx dy dz time (7 pointers; host or device memory).  Returns the number of sink

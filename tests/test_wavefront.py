@@ -243,3 +243,71 @@ def test_wavefront_queues_closest_and_shadow(shim, oracle, reference, where):
         assert shim.wf_intersect_shadow(h, N, arr, 0, _p(found), 0) == 0
     finally:
         shim.wf_destroy(h)
+
+
+@pytest.mark.gpu
+def test_wavefront_closest_hits_on_spheres(shim, oracle, reference):
+    """A primitive list of triangles + `Shape "sphere"` entries behind the wavefront backend: sphere
+    leaves reach EnqueueWorkAfterIntersection with Sphere::Intersect's SurfaceInteraction
+    (shapes.h:130-139), triangles with Triangle::Intersect's, every word equal to the reference's."""
+    from tools.make_golden import random_spheres
+    rng = np.random.default_rng(91)
+    verts, idx, uv, nrm = _mesh(rng, V=2000, T=5000)
+    T, S = idx.shape[0], 60
+    sph = random_spheres(rng, S, scale=0.1, center_box=0.0)
+    for k in range(S):
+        m = np.eye(4)
+        m[:3] = sph[k, :12].reshape(3, 4)
+        m[:3, 3] = rng.random(3)
+        if k % 4 == 0:
+            m[:3, 0] *= -1                                   # swaps handedness
+        sph[k, :12] = m[:3].astype(np.float32).ravel()
+        sph[k, 12:24] = np.linalg.inv(m)[:3].astype(np.float32).ravel()
+    rev = (np.arange(S) % 3 == 0).astype(np.uint8)
+    shim.wf_create_mixed.restype = ctypes.c_void_p
+    shim.wf_create_mixed.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_int] + \
+        [ctypes.c_void_p] * 3 + [ctypes.c_int, ctypes.c_void_p] + [ctypes.c_int] * 3
+    h = shim.wf_create_mixed(_p(verts), verts.shape[0], _p(idx), T, _p(nrm), _p(uv), _p(sph), S, _p(rev), 4, 0, 4)
+    assert h, shim.wf_last_error()
+    try:
+        N = 100_000
+        rays = rand_rays(rng, N)
+        aim = rng.integers(0, S, N // 2)                     # half the rays aimed at a sphere
+        tgt = sph[aim][:, [3, 7, 11]] + rng.normal(size=(N // 2, 3)).astype(np.float32) * 0.05
+        rays[:N // 2, 4:7] = tgt - rays[:N // 2, :3]
+        rays[:, 7] = rng.random(N)
+        rays[:, 3] = np.inf
+        planes_np = [np.ascontiguousarray(rays[:, k]) for k in (0, 1, 2, 4, 5, 6, 7)]
+        arr = (ctypes.c_void_p * 7)(*[p.ctypes.data for p in planes_np])
+        kind = np.full(N, -1, dtype=np.int8)
+        prim = np.zeros(N, dtype=np.uint32)
+        t_hit = np.zeros(N, dtype=np.float32)
+        surf = np.zeros((N, 39), dtype=np.uint32)
+        wo_t = np.zeros((N, 4), dtype=np.float32)
+        assert shim.wf_intersect_closest(h, N, arr, N, _p(kind), _p(prim), _p(t_hit), _p(surf), _p(wo_t)) == N, \
+            shim.wf_last_error()
+
+        tris9 = verts[idx].reshape(T, 9)
+        sc = reference.scene_mixed(tris9, sph, 4, "sah")
+        _, order = reference.export(sc, T + S)
+        want = reference.intersect(sc, rays, parallel=False)
+        miss = want[:, 0] == 0xFFFFFFFF
+        assert np.array_equal(kind == 0, miss) and np.array_equal(kind == 1, ~miss)
+        hit = np.nonzero(~miss)[0]
+        assert np.array_equal(prim[hit], order[want[hit, 0]].astype(np.uint32))
+        assert np.array_equal(t_hit[hit].view(np.uint32), want[hit, 1])
+        on_tri = hit[prim[hit] < T]
+        on_sph = hit[prim[hit] >= T]
+        assert len(on_tri) > 1000 and len(on_sph) > 1000
+        ref_surf = reference.triangle_interaction(verts, idx, prim[on_tri].astype(np.int32),
+                                                  want[on_tri, 2:5].view(np.float32), wo_t[on_tri], normals=nrm, uvs=uv)
+        _same(surf[on_tri], ref_surf, "triangle hits")
+        got42 = np.concatenate([surf, wo_t[:, :3].view(np.uint32)], axis=1)
+        for k in np.unique(prim[on_sph] - T):
+            sel = on_sph[prim[on_sph] - T == k]
+            rhit, rt, r42 = reference.sphere_interaction(sph[k], rev[k], rays[sel])
+            assert rhit.all() and np.array_equal(rt.view(np.uint32), t_hit[sel].view(np.uint32))
+            _same42(got42[sel], r42.view(np.uint32), f"sphere {k}")
+        assert np.array_equal(wo_t[hit, 3], rays[hit, 7])
+    finally:
+        shim.wf_destroy(h)
