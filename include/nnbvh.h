@@ -230,6 +230,11 @@ int nnbvh_upload_scene_instanced(nnbvh_engine *e, const nnbvh_node *nodes, uint3
  * inside the hit object (NNBVH_MISS for a top-level triangle or a miss).  innerPrim may be NULL. */
 int nnbvh_intersect_closest_instanced(nnbvh_engine *e, const nnbvh_ray *rays, uint64_t n,
                                       nnbvh_hit *hits, uint32_t *innerPrim);
+/* The same over the wavefront queues' seven planes (wavefront/workitems.soa; tMax NULL = Infinity). */
+int nnbvh_intersect_closest_instanced_soa(nnbvh_engine *e, const float *ox, const float *oy,
+                                          const float *oz, const float *dx, const float *dy,
+                                          const float *dz, const float *tMax, uint64_t n,
+                                          nnbvh_hit *hits, uint32_t *innerPrim);
 
 /* BVHAggregate::Intersect (cpu/aggregates.cpp:529-579) for n rays. */
 int nnbvh_intersect_closest(nnbvh_engine *e, const nnbvh_ray *rays, uint64_t n,

@@ -208,6 +208,11 @@ class GPUBVHAggregate {
     void IntersectBatchInstanced(const nnbvh_ray *rays, uint64_t n, nnbvh_hit *hits, uint32_t *innerPrim) const {
         Check(nnbvh_intersect_closest_instanced(e_, rays, n, hits, innerPrim));
     }
+    void IntersectBatchInstancedSoA(const float *ox, const float *oy, const float *oz, const float *dx,
+                                    const float *dy, const float *dz, const float *tMax, uint64_t n,
+                                    nnbvh_hit *hits, uint32_t *innerPrim) const {
+        Check(nnbvh_intersect_closest_instanced_soa(e_, ox, oy, oz, dx, dy, dz, tMax, n, hits, innerPrim));
+    }
     // ordered top-level primitive (Hit::prim) -> instance index, or -1
     int32_t InstanceOf(uint32_t ordered) const { return instanceOf_.empty() ? -1 : instanceOf_[ordered]; }
     const std::vector<ObjectTree> &Objects() const { return objects_; }

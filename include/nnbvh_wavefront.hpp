@@ -432,6 +432,21 @@ inline void SphereInteractionFromIntersection(const SphereShape &sp, const float
     TransformSurfaceHit(sp.renderFromObject, sp.objectFromRender, out);
 }
 
+// TransformedPrimitive::Intersect (cpu/primitive.cpp:112-125) for a hit on triangle `triIndex` of an
+// object's mesh (object space): the object's own Intersect saw the ray renderFromPrimitive->ApplyInverse(r)
+// (its direction through mInv, transform.h:401-406), so the interaction's wo is minus that direction;
+// the result is carried back by renderFromPrimitive.  dRender: the render-space ray's direction.
+inline bool InstanceInteractionFromIntersection(const nnbvh_instance &in, const TriangleMeshView &mesh,
+                                                int triIndex, float b0, float b1, float b2, float time,
+                                                const float dRender[3], SurfaceHit *out) {
+    using namespace detail;
+    V3 dl = XfVector(in.primitiveFromRender, V3{dRender[0], dRender[1], dRender[2]});
+    const float wl[3] = {-dl.x, -dl.y, -dl.z};
+    if (!InteractionFromIntersection(mesh, triIndex, b0, b1, b2, time, wl, out)) return false;
+    TransformSurfaceHit(in.renderFromPrimitive, in.primitiveFromRender, out);
+    return true;
+}
+
 // ---- the aggregate -------------------------------------------------------------------------
 // The scene is one TriangleMesh-like soup per primitive list entry: primitive i of the list given
 // to the constructor is triangle `triIndex[i]` of mesh `meshIndex[i]` (Triangle::{meshIndex,
@@ -476,6 +491,23 @@ class GPUBVHWavefrontAggregate {
                                                                sphereReverseOrientation[k] != 0));
     }
 
+    // Object instances (TransformedPrimitive over a per-object BVHAggregate, cpu/primitive.cpp:112-130):
+    // objects[j] is object j's own primitive list -- triangles of `meshes`, given in the OBJECT's space --
+    // and primitive prims.size() + k of the top-level list is instances[k].
+    GPUBVHWavefrontAggregate(std::vector<TriangleMeshView> meshes, std::vector<PrimitiveRef> prims,
+                             std::vector<std::vector<PrimitiveRef>> objects, std::vector<nnbvh_instance> instances,
+                             int maxPrimsInNode = 4,
+                             GPUBVHAggregate::SplitMethod sm = GPUBVHAggregate::SplitMethod::SAH,
+                             int device = -1, int hostThreads = 0)
+        : meshes_(std::move(meshes)), prims_(std::move(prims)), objects_(std::move(objects)),
+          instances_(std::move(instances)),
+          hostThreads_(hostThreads > 0 ? hostThreads
+                                       : std::max(1u, std::thread::hardware_concurrency())) {
+        std::vector<std::vector<float>> objSoups;
+        for (const std::vector<PrimitiveRef> &o : objects_) objSoups.push_back(Soup(o));
+        agg_.reset(new GPUBVHAggregate(Soup(), objSoups, instances_, maxPrimsInNode, sm, device));
+    }
+
     Bounds3f Bounds() const { return agg_->Bounds(); }  // WavefrontAggregate::Bounds, integrator.h:35
     const GPUBVHAggregate &Aggregate() const { return *agg_; }
 
@@ -486,8 +518,13 @@ class GPUBVHWavefrontAggregate {
         const int n = Count(maxRays, q.size);
         if (n == 0) return;
         hits_.resize((size_t)n);
-        agg_->IntersectBatchSoA(q.ox, q.oy, q.oz, q.dx, q.dy, q.dz, /*tMax=*/nullptr, (uint64_t)n,
-                                hits_.data());
+        if (!instances_.empty()) {
+            inner_.resize((size_t)n);
+            agg_->IntersectBatchInstancedSoA(q.ox, q.oy, q.oz, q.dx, q.dy, q.dz, /*tMax=*/nullptr, (uint64_t)n,
+                                             hits_.data(), inner_.data());
+        } else
+            agg_->IntersectBatchSoA(q.ox, q.oy, q.oz, q.dx, q.dy, q.dz, /*tMax=*/nullptr, (uint64_t)n,
+                                    hits_.data());
         // wo = -ray.d needs the directions on the host; a queue in device memory is staged once.
         HostPlanes d(q.dx, q.dy, q.dz, q.time, n);
         ParallelFor(n, [&](int i) {
@@ -499,6 +536,16 @@ class GPUBVHWavefrontAggregate {
             uint32_t prim = agg_->PrimitiveIndex(h.prim);
             float wo[3] = {-d.x[i], -d.y[i], -d.z[i]};
             SurfaceHit sh;
+            if (prim >= prims_.size() && !instances_.empty()) {
+                const nnbvh_instance &in = instances_[prim - prims_.size()];
+                const PrimitiveRef &pr = objects_[in.object][agg_->Objects()[in.object].order[inner_[(size_t)i]]];
+                const float dir[3] = {d.x[i], d.y[i], d.z[i]};
+                if (!InstanceInteractionFromIntersection(in, meshes_[pr.meshIndex], pr.triIndex, h.b0, h.b1, h.b2,
+                                                         d.t ? d.t[i] : 0.f, dir, &sh))
+                    throw Error(NNBVH_ERR_INVALID, "hit on a triangle with a zero normal");
+                sink.EnqueueWorkAfterIntersection(i, prim, h.t, sh);
+                return;
+            }
             if (prim >= prims_.size()) {  // a sphere leaf: {b0,b1,b2} = pObj (Sphere::Intersect, shapes.h:130-139)
                 const float pObj[3] = {h.b0, h.b1, h.b2};
                 SphereInteractionFromIntersection(shapes_[prim - prims_.size()], pObj, wo, d.t ? d.t[i] : 0.f, &sh);
@@ -533,11 +580,12 @@ class GPUBVHWavefrontAggregate {
 
   private:
     // the triangles of the primitive list as 9 floats each
-    std::vector<float> Soup() const {
-        std::vector<float> tris9(9 * prims_.size());
-        for (size_t i = 0; i < prims_.size(); ++i) {
-            const TriangleMeshView &m = meshes_[prims_[i].meshIndex];
-            const int *v = &m.vertexIndices[3 * prims_[i].triIndex];
+    std::vector<float> Soup() const { return Soup(prims_); }
+    std::vector<float> Soup(const std::vector<PrimitiveRef> &prims) const {
+        std::vector<float> tris9(9 * prims.size());
+        for (size_t i = 0; i < prims.size(); ++i) {
+            const TriangleMeshView &m = meshes_[prims[i].meshIndex];
+            const int *v = &m.vertexIndices[3 * prims[i].triIndex];
             for (int k = 0; k < 3; ++k)
                 for (int c = 0; c < 3; ++c) tris9[9 * i + 3 * k + c] = m.p[3 * v[k] + c];
         }
@@ -599,9 +647,12 @@ class GPUBVHWavefrontAggregate {
     std::vector<PrimitiveRef> prims_;
     std::vector<nnbvh_sphere> spheres_;
     std::vector<SphereShape> shapes_;
+    std::vector<std::vector<PrimitiveRef>> objects_;
+    std::vector<nnbvh_instance> instances_;
     int hostThreads_;
     std::unique_ptr<GPUBVHAggregate> agg_;
     mutable std::vector<nnbvh_hit> hits_;
+    mutable std::vector<uint32_t> inner_;
     mutable std::vector<uint8_t> occ_;
 };
 

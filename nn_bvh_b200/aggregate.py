@@ -353,6 +353,15 @@ class GPUBVHAggregate:
                      capi.ptr(hits)))
         return hits
 
+    def IntersectBatchInstancedSoA(self, ox, oy, oz, dx, dy, dz, tMax=None, hits=None, inner=None):
+        """IntersectBatchInstanced over the wavefront queues' planes."""
+        n = int(ox.shape[0])
+        if hits is None:
+            hits, inner = np.zeros(n, dtype=HIT_DTYPE), np.zeros(n, dtype=np.uint32)
+        capi.check(capi.lib().nnbvh_intersect_closest_instanced_soa(
+            self._h, *(capi.ptr(a) for a in (ox, oy, oz, dx, dy, dz, tMax)), n, capi.ptr(hits), capi.ptr(inner)))
+        return hits, inner
+
     def IntersectCounters(self, rays, any_hit=False):
         """Results plus the reference's per-ray statistics (bvhNodesVisited,
         nTriTests).  numpy in, numpy out."""

@@ -1126,6 +1126,22 @@ extern "C" int nnbvh_intersect_closest_soa(nnbvh_engine *e, const float *ox, con
     return RunBatch(e, b);
 }
 
+extern "C" int nnbvh_intersect_closest_instanced_soa(nnbvh_engine *e, const float *ox, const float *oy,
+                                                     const float *oz, const float *dx, const float *dy,
+                                                     const float *dz, const float *tMax, uint64_t n,
+                                                     nnbvh_hit *hits, uint32_t *innerPrim) {
+    if (e && !e->hasInstances)
+        return SetError(NNBVH_ERR_INVALID, "nnbvh_intersect_closest_instanced_soa: the scene has no instances");
+    if (innerPrim && IsDevicePtr(innerPrim) != IsDevicePtr(hits))
+        return SetError(NNBVH_ERR_INVALID, "nnbvh_intersect_closest_instanced_soa: hits and innerPrim must live on the same side");
+    Batch b;
+    FillPlanes(b, ox, oy, oz, dx, dy, dz, tMax);
+    b.n = n;
+    b.out.hits = hits;
+    b.out.inner = innerPrim;
+    return RunBatch(e, b);
+}
+
 extern "C" int nnbvh_intersect_any_soa(nnbvh_engine *e, const float *ox, const float *oy,
                                        const float *oz, const float *dx, const float *dy,
                                        const float *dz, const float *tMax, uint64_t n,

@@ -350,6 +350,19 @@ class Reference:
         f(_p(sphere28), int(bool(reverse)), _p(rays8), n, _p(hit), _p(t_hit), _p(out))
         return hit.astype(bool), t_hit, out
 
+    def intersect_surface(self, scene, rays8):
+        """BVHAggregate::Intersect's SurfaceInteraction per ray: (hit, tHit, 42 words) on any scene handle."""
+        rays8 = np.ascontiguousarray(rays8, dtype=np.float32)
+        n = rays8.shape[0]
+        hit = np.zeros(n, dtype=np.int32)
+        t_hit = np.zeros(n, dtype=np.float32)
+        out = np.zeros((n, 42), dtype=np.float32)
+        f = self.lib.nnbvh_ref_intersect_surface
+        f.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int64] + [ctypes.c_void_p] * 3
+        f.restype = None
+        f(scene, _p(rays8), n, _p(hit), _p(t_hit), _p(out))
+        return hit.astype(bool), t_hit, out
+
     def interaction_wo(self, wo3):
         """What Interaction's constructor stores for a given wo (interaction.h:30-32)."""
         wo3 = np.ascontiguousarray(wo3, dtype=np.float32)

@@ -633,6 +633,25 @@ int nnbvh_ref_sphere_interaction(const float *sphere28, int reverseOrientation, 
     return 0;
 }
 
+// BVHAggregate::Intersect on any scene of this driver (triangles, triangles + spheres, triangles +
+// instances), returning the SurfaceInteraction itself: hit[i], tHit[i] and 42 words per ray (the 39
+// of PutSurface39 + wo).  The end-to-end pin for include/nnbvh_wavefront.hpp.
+void nnbvh_ref_intersect_surface(void *scene, const float *rays, int64_t n, int *hit, float *tHit,
+                                 float *out42) {
+    RefScene *s = (RefScene *)scene;
+    pbrt::Primitive top(s->agg);
+    for (int64_t i = 0; i < n; ++i) {
+        const float *r = rays + 8 * i;
+        pstd::optional<pbrt::ShapeIntersection> si = top.Intersect(MakeRay(r), r[3]);
+        hit[i] = si.has_value();
+        if (!si)
+            continue;
+        tHit[i] = si->tHit;
+        PutSurface39(si->intr, out42 + 42 * i);
+        out42[42 * i + 39] = si->intr.wo.x, out42[42 * i + 40] = si->intr.wo.y, out42[42 * i + 41] = si->intr.wo.z;
+    }
+}
+
 // Interaction(pi, n, uv, wo, time) (interaction.h:30-32) keeps Normalize(wo): what a triangle
 // hit's SurfaceInteraction::wo holds for the wo = -ray.d it is given.
 void nnbvh_ref_interaction_wo(const float *wo3, int64_t n, float *out3) {

@@ -58,6 +58,7 @@ void Pack(const SurfaceHit &h, float *o) {
 
 struct Scene {
     Mesh mesh;
+    std::vector<Mesh> objectMeshes;
     std::unique_ptr<GPUBVHWavefrontAggregate> agg;
 };
 
@@ -164,6 +165,70 @@ void *wf_create_mixed(const float *verts, int nVerts, const int *indices, int nT
         s->agg.reset(new GPUBVHWavefrontAggregate(
             {s->mesh.View(false)}, prims, sph, rev, maxPrimsInNode,
             (nnbvh::GPUBVHAggregate::SplitMethod)splitMethod, -1, hostThreads));
+        return s;
+    } catch (const nnbvh::Error &e) {
+        g_what = e.what();
+        return nullptr;
+    }
+}
+
+// A triangle soup (9 floats per triangle) as an indexed mesh without normals / uv
+Mesh SoupMesh(const float *tris9, int nTris) {
+    std::vector<int> idx(3 * (size_t)nTris);
+    for (size_t i = 0; i < idx.size(); ++i) idx[i] = (int)i;
+    return MakeMesh(tris9, 3 * nTris, idx.data(), nTris, nullptr, nullptr, nullptr);
+}
+
+nnbvh_instance MakeInstance(const float *m24, int object) {
+    nnbvh_instance in{};
+    std::memcpy(in.renderFromPrimitive, m24, 48);
+    std::memcpy(in.primitiveFromRender, m24 + 12, 48);
+    in.object = (uint32_t)object;
+    return in;
+}
+
+// TransformedPrimitive::Intersect's interaction on the host: query i hits triangle tri[i] of the object's
+// soup with barycentrics b[3i..], for the render-space ray direction / time dTime[4i..].
+int wf_instance_interaction(const float *inst24, const float *soup9, int nTris, const int *tri,
+                            const float *b, const float *dTime, int64_t n, float *out42) {
+    Mesh m = SoupMesh(soup9, nTris);
+    TriangleMeshView v = m.View(false);
+    nnbvh_instance in = MakeInstance(inst24, 0);
+    for (int64_t i = 0; i < n; ++i) {
+        SurfaceHit h;
+        if (!InstanceInteractionFromIntersection(in, v, tri[i], b[3 * i], b[3 * i + 1], b[3 * i + 2],
+                                                 dTime[4 * i + 3], dTime + 4 * i, &h))
+            return -1;
+        Pack(h, out42 + 42 * i);
+        std::memcpy(out42 + 42 * i + 39, h.wo, 12);
+    }
+    return 0;
+}
+
+// Top-level soup + objects (soups in object space, concatenated; objStart[j] .. objStart[j+1]) +
+// instances (24 floats: renderFromPrimitive, primitiveFromRender; instObject[k]).
+void *wf_create_instanced(const float *top9, int nTop, const float *obj9, const int *objStart, int nObjects,
+                          const float *inst24, const int *instObject, int nInst, int maxPrimsInNode,
+                          int splitMethod, int hostThreads) {
+    try {
+        auto *s = new Scene;
+        using Ref = GPUBVHWavefrontAggregate::PrimitiveRef;
+        s->mesh = SoupMesh(top9, nTop);
+        std::vector<TriangleMeshView> views{s->mesh.View(false)};
+        std::vector<Ref> prims(nTop);
+        for (int i = 0; i < nTop; ++i) prims[i] = {0, i};
+        std::vector<std::vector<Ref>> objects(nObjects);
+        s->objectMeshes.reserve(nObjects);
+        for (int j = 0; j < nObjects; ++j) {
+            int n = objStart[j + 1] - objStart[j];
+            s->objectMeshes.push_back(SoupMesh(obj9 + 9 * (size_t)objStart[j], n));
+            views.push_back(s->objectMeshes.back().View(false));
+            for (int i = 0; i < n; ++i) objects[j].push_back(Ref{j + 1, i});
+        }
+        std::vector<nnbvh_instance> inst(nInst);
+        for (int k = 0; k < nInst; ++k) inst[k] = MakeInstance(inst24 + 24 * (size_t)k, instObject[k]);
+        s->agg.reset(new GPUBVHWavefrontAggregate(views, prims, objects, inst, maxPrimsInNode,
+                                                  (nnbvh::GPUBVHAggregate::SplitMethod)splitMethod, -1, hostThreads));
         return s;
     } catch (const nnbvh::Error &e) {
         g_what = e.what();

@@ -105,6 +105,15 @@ def test_instanced_scene_gpu_matches_reference_golden(gold):
     assert np.array_equal(np.ascontiguousarray(hits).view(np.uint32).reshape(-1, 5), gold["hits"])
     assert np.array_equal(inner, gold["inner"])
     assert np.array_equal(agg.IntersectPBatch(gold["rays"]), gold["occ"])
+    # the wavefront queues' planes (tMax plane given / NULL = Infinity)
+    r = gold["rays"]
+    pl = [np.ascontiguousarray(r[:, k]) for k in (0, 1, 2, 4, 5, 6, 3)]
+    h2, i2 = agg.IntersectBatchInstancedSoA(*pl)
+    assert np.array_equal(np.ascontiguousarray(h2).view(np.uint32).reshape(-1, 5), gold["hits"]) and np.array_equal(i2, gold["inner"])
+    inf = np.isinf(r[:, 3])
+    h3, i3 = agg.IntersectBatchInstancedSoA(*pl[:6])
+    assert inf.sum() > 100 and np.array_equal(np.ascontiguousarray(h3).view(np.uint32).reshape(-1, 5)[inf], gold["hits"][inf])
+    assert np.array_equal(i3[inf], gold["inner"][inf])
     # the plain closest entry point works too (no inner plane)
     assert np.array_equal(np.ascontiguousarray(agg.IntersectBatch(gold["rays"])).view(np.uint32).reshape(-1, 5), gold["hits"])
 

@@ -311,3 +311,106 @@ def test_wavefront_closest_hits_on_spheres(shim, oracle, reference):
         assert np.array_equal(wo_t[hit, 3], rays[hit, 7])
     finally:
         shim.wf_destroy(h)
+
+
+# ---- instances (TransformedPrimitive::Intersect, cpu/primitive.cpp:112-125) --------------------------------
+def _instance_interactions(L, inst24, inst_object, objs, obj_orders, order, n_top, rays, hits, inner):
+    """The host restatement on the engine's records of instance hits -> (ray indices, 42 words each)."""
+    L.wf_instance_interaction.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int] + [ctypes.c_void_p] * 3 + \
+        [ctypes.c_int64, ctypes.c_void_p]
+    on_inst = np.nonzero(inner != 0xFFFFFFFF)[0]
+    k_of = order[hits[on_inst, 0]] - n_top
+    got = np.zeros((len(on_inst), 42), dtype=np.uint32)
+    for k in np.unique(k_of):
+        m = k_of == k
+        sel, j = on_inst[m], int(inst_object[k])
+        tri = np.ascontiguousarray(obj_orders[j][inner[sel]], dtype=np.int32)
+        b = np.ascontiguousarray(hits[sel, 2:5]).view(np.float32)
+        d_time = np.ascontiguousarray(np.concatenate([rays[sel, 4:7], rays[sel, 7:8]], axis=1), dtype=np.float32)
+        out = np.zeros((len(sel), 42), dtype=np.uint32)
+        soup = np.ascontiguousarray(objs[j], dtype=np.float32)
+        assert L.wf_instance_interaction(_p(np.ascontiguousarray(inst24[k])), _p(soup), len(soup), _p(tri), _p(b),
+                                         _p(d_time), len(sel), _p(out)) == 0
+        got[m] = out
+    return on_inst, got
+
+
+def test_instance_interaction_matches_reference_golden(shim):
+    g = np.load(os.path.join(GOLDEN, "instanced_surface.npz"))
+    J = int(g["n_objects"])
+    objs, orders = [g[f"obj{j}"] for j in range(J)], [g[f"obj{j}_order"] for j in range(J)]
+    idx, got = _instance_interactions(shim, g["inst24"], g["inst_object"], objs, orders, g["order"], len(g["top"]),
+                                      g["rays"], g["hits"], g["inner"])
+    assert len(idx) > 800
+    _same42(got, g["surf"][idx], "instance hits")
+
+
+def test_instance_interaction_matches_reference_live(shim, reference):
+    from tools.make_golden import instanced_scene
+    rng = np.random.default_rng(58)
+    top, objs, inst, io = instanced_scene(rng, T=600, K=20, obj_sizes=(200, 1, 700))
+    inst[::3, 1:12:4] *= -1                 # second column of renderFromPrimitive: mirrored instances
+    for k in range(len(inst)):
+        m = np.eye(4)
+        m[:3] = inst[k, :12].reshape(3, 4).astype(np.float64)
+        inst[k, 12:] = np.linalg.inv(m)[:3].ravel()
+    sc = reference.scene_instanced(top, objs, inst, io, 4, "sah")
+    rays = rand_rays(rng, 8000)
+    rays[:, 3] = np.inf
+    rays[:, 4:7] *= np.exp(rng.uniform(-1, 1, (8000, 1))).astype(np.float32)
+    rays[:, 7] = rng.random(8000)
+    hits, inner = reference.intersect_instanced(sc["handle"], rays)
+    _, _, surf = reference.intersect_surface(sc["handle"], rays)
+    idx, got = _instance_interactions(shim, inst, io, objs, sc["obj_orders"], sc["order"], len(top), rays, hits, inner)
+    assert len(idx) > 500
+    _same42(got, surf.view(np.uint32)[idx], "instance hits")
+
+
+@pytest.mark.gpu
+def test_wavefront_closest_hits_on_instances(shim, reference):
+    """An instanced scene behind the wavefront backend: top-level triangles and TransformedPrimitive
+    instances; every ray's kind / tHit / SurfaceInteraction (42 words) equals BVHAggregate::Intersect's."""
+    from tools.make_golden import instanced_scene
+    rng = np.random.default_rng(63)
+    top, objs, inst, io = instanced_scene(rng, T=4000, K=60, obj_sizes=(1500, 1, 3000))
+    inst[::4, 0:12:4] *= -1
+    for k in range(len(inst)):
+        m = np.eye(4)
+        m[:3] = inst[k, :12].reshape(3, 4).astype(np.float64)
+        m[:3, :3] *= 0.6
+        inst[k, :12] = m[:3].ravel()
+        inst[k, 12:] = np.linalg.inv(m)[:3].ravel()
+    obj_all = np.ascontiguousarray(np.concatenate(objs), dtype=np.float32)
+    start = np.concatenate([[0], np.cumsum([len(o) for o in objs])]).astype(np.int32)
+    shim.wf_create_instanced.restype = ctypes.c_void_p
+    shim.wf_create_instanced.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int,
+                                         ctypes.c_void_p, ctypes.c_void_p] + [ctypes.c_int] * 4
+    top = np.ascontiguousarray(top, dtype=np.float32)
+    h = shim.wf_create_instanced(_p(top), len(top), _p(obj_all), _p(start), len(objs), _p(inst), _p(io), len(inst), 4, 0, 4)
+    assert h, shim.wf_last_error()
+    try:
+        N = 60_000
+        rays = rand_rays(rng, N)
+        rays[:, 3] = np.inf
+        rays[:, 7] = rng.random(N)
+        planes_np = [np.ascontiguousarray(rays[:, k]) for k in (0, 1, 2, 4, 5, 6, 7)]
+        arr = (ctypes.c_void_p * 7)(*[p.ctypes.data for p in planes_np])
+        kind = np.full(N, -1, dtype=np.int8)
+        prim = np.zeros(N, dtype=np.uint32)
+        t_hit = np.zeros(N, dtype=np.float32)
+        surf = np.zeros((N, 39), dtype=np.uint32)
+        wo_t = np.zeros((N, 4), dtype=np.float32)
+        assert shim.wf_intersect_closest(h, N, arr, N, _p(kind), _p(prim), _p(t_hit), _p(surf), _p(wo_t)) == N, \
+            shim.wf_last_error()
+        sc = reference.scene_instanced(top, objs, inst, io, 4, "sah")
+        whits, winner = reference.intersect_instanced(sc["handle"], rays)
+        rhit, rt, r42 = reference.intersect_surface(sc["handle"], rays)
+        assert np.array_equal(kind == 1, rhit) and np.array_equal(kind == 0, ~rhit)
+        hit = np.nonzero(rhit)[0]
+        assert (winner[hit] != 0xFFFFFFFF).sum() > 3000 and (winner[hit] == 0xFFFFFFFF).sum() > 3000
+        assert np.array_equal(prim[hit], sc["order"][whits[hit, 0]].astype(np.uint32))
+        assert np.array_equal(t_hit[hit].view(np.uint32), rt[hit].view(np.uint32))
+        got42 = np.concatenate([surf, wo_t[:, :3].view(np.uint32)], axis=1)
+        _same42(got42[hit], r42.view(np.uint32)[hit], "instanced scene")
+    finally:
+        shim.wf_destroy(h)

@@ -32,6 +32,10 @@ oracle/ref_driver.cpp; the fixtures are small so they can be committed.
                     (shapes.h:130-139, :238-280) for 48 spheres x 64 rays: rotated / scaled /
                     mirrored transforms, z-clipped, reverseOrientation; plus what Interaction's
                     constructor stores as wo (--only-sphere-interaction).
+  instanced_surface.npz  BVHAggregate::Intersect's SurfaceInteraction on an instanced scene (some
+                    instances mirrored, ray directions not normalised): TransformedPrimitive::Intersect's
+                    (*renderFromPrimitive)(si->intr) (cpu/primitive.cpp:112-125), 42 words per ray
+                    (--only-instanced-surface).
 """
 import os
 import sys
@@ -405,6 +409,34 @@ def sphere_interaction(ref, rng):
                         wo_stored=ref.interaction_wo(wo))
 
 
+def instanced_surface(ref, rng):
+    top, objs, inst, io = instanced_scene(rng, T=800, K=24, obj_sizes=(300, 1, 500))
+    for k in range(0, len(inst), 5):         # mirrored instances: the transform swaps handedness
+        m = np.eye(4)
+        m[:3] = inst[k, :12].reshape(3, 4).astype(np.float64)
+        m[:3, 1] *= -1
+        inst[k, :12] = m[:3].ravel()
+        inst[k, 12:] = np.linalg.inv(m)[:3].ravel()
+    sc = ref.scene_instanced(top, objs, inst, io, 4, "sah")
+    N = 3000
+    rays = np.zeros((N, 8), dtype=np.float32)
+    rays[:, :3] = rng.random((N, 3)) * 1.5 - 0.25
+    d = rng.normal(size=(N, 3))
+    rays[:, 4:7] = d / np.linalg.norm(d, axis=1, keepdims=True) * np.exp(rng.uniform(-1, 1, (N, 1)))
+    rays[:, 3] = np.inf
+    rays[:, 7] = rng.random(N)
+    hits, inner = ref.intersect_instanced(sc["handle"], rays)
+    hit, t_hit, surf = ref.intersect_surface(sc["handle"], rays)
+    assert np.array_equal(hit, hits[:, 0] != 0xFFFFFFFF)
+    print("instanced_surface: instance hits", int((inner != 0xFFFFFFFF).sum()), "of", int(hit.sum()), "hits")
+    out = dict(top=top, inst24=inst, inst_object=io, rays=rays, hits=hits, inner=inner, order=sc["order"],
+               t_hit=t_hit, surf=surf.view(np.uint32), n_objects=np.int32(len(objs)))
+    for j, o in enumerate(objs):
+        out[f"obj{j}"] = o
+        out[f"obj{j}_order"] = sc["obj_orders"][j]
+    np.savez_compressed(os.path.join(OUT, "instanced_surface.npz"), **out)
+
+
 if __name__ == "__main__":
     os.makedirs(OUT, exist_ok=True)
     ref = Reference(threads=1)
@@ -420,6 +452,9 @@ if __name__ == "__main__":
     if "--only-sphere-interaction" in sys.argv:
         sphere_interaction(ref, np.random.default_rng(238))
         sys.exit(0)
+    if "--only-instanced-surface" in sys.argv:
+        instanced_surface(ref, np.random.default_rng(415))
+        sys.exit(0)
     if "--only-hlbvh" in sys.argv:
         hlbvh(ref)
         sys.exit(0)
@@ -432,3 +467,4 @@ if __name__ == "__main__":
     sphere_vectors(ref, np.random.default_rng(147))
     instanced(ref, np.random.default_rng(112))
     sphere_interaction(ref, np.random.default_rng(238))
+    instanced_surface(ref, np.random.default_rng(415))
