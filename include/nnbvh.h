@@ -106,8 +106,8 @@ int nnbvh_build_bvh_bounds(const float *bounds6, uint32_t nPrims, int32_t maxPri
  * What `Shape "sphere"` hands to Sphere::Sphere (shapes.h:117-128): both transforms (rows 0..2 of
  * the 4x4 matrices, row-major; row 3 must be 0 0 0 1) and radius / zmin / zmax / phimax as the
  * scene file gives them (the constructor's clamping is applied by the library).  Spheres with
- * phimax < 360 are rejected (NNBVH_ERR_INVALID): their clipping test compares std::atan2's
- * result (shapes.h:194-203), which the device cannot reproduce bit for bit. */
+ * phimax < 360 compare std::atan2's result (shapes.h:196-203): the device follows glibc's
+ * single-precision algorithm (csrc/atan2_host.cuh), bit for bit the libm of this image. */
 typedef struct nnbvh_sphere {
     float renderFromObject[12];
     float objectFromRender[12];
@@ -289,6 +289,9 @@ int nnbvh_test_boxes(nnbvh_engine *e, const nnbvh_ray *rays, const float *boxes6
  * out4[i] = {tHit, pObj.x, pObj.y, pObj.z} where hit[i] != 0. */
 int nnbvh_test_spheres(nnbvh_engine *e, const nnbvh_ray *rays, const nnbvh_sphere *spheres,
                        uint64_t n, uint8_t *hit, float *out4);
+/* The device's std::atan2(float, float) -- the host libm's algorithm restated, which the phimax
+ * clipping test of a partial sphere compares (shapes.h:196-203) -- on n (y, x) pairs.  Host pointers. */
+int nnbvh_test_atan2(nnbvh_engine *e, const float *y, const float *x, uint64_t n, float *out);
 
 const char *nnbvh_last_error(void);
 const char *nnbvh_version(void);

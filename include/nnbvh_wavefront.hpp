@@ -473,7 +473,7 @@ class GPUBVHWavefrontAggregate {
     }
 
     // The same with `Shape "sphere"` primitives after the triangles: primitive prims.size() + k of the
-    // list is spheres[k] (full spheres and z-clipped ones; phimax < 360 is refused by the engine).
+    // list is spheres[k] (full, z-clipped or phimax-clipped).
     // sphereReverseOrientation[k]: the shape's ReverseOrientation flag (shapes.h:117-123), empty = none.
     GPUBVHWavefrontAggregate(std::vector<TriangleMeshView> meshes, std::vector<PrimitiveRef> prims,
                              std::vector<nnbvh_sphere> spheres, std::vector<uint8_t> sphereReverseOrientation,

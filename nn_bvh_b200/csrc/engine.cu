@@ -453,16 +453,12 @@ static int MakeSphereDev(const nnbvh_sphere &s, uint32_t index, SphereDev *out) 
             return SetError(NNBVH_ERR_INVALID, "sphere %u: non-finite transform", index);
     if (!(s.radius > 0.f) || !std::isfinite(s.radius))
         return SetError(NNBVH_ERR_INVALID, "sphere %u: radius %g", index, (double)s.radius);
-    // Clamp(phiMax, 0, 360) < 360 clips by std::atan2's value (shapes.h:194-203): not reproducible here
-    if (!(s.phiMax >= 360.f))
-        return SetError(NNBVH_ERR_INVALID, "sphere %u: phimax %g < 360 is not supported (the clipping "
-                                           "test depends on std::atan2 bit for bit)", index, (double)s.phiMax);
     auto clamp = [](float v, float lo, float hi) { return v < lo ? lo : (v > hi ? hi : v); };
     for (int k = 0; k < 12; ++k) out->m[k] = s.objectFromRender[k];
     out->radius = s.radius;
     out->zMin = clamp(std::min(s.zMin, s.zMax), -s.radius, s.radius);
     out->zMax = clamp(std::max(s.zMin, s.zMax), -s.radius, s.radius);
-    out->pad = 0.f;
+    out->phiMax = (3.14159265358979323846f / 180) * clamp(s.phiMax, 0.f, 360.f);  // Radians(), util/math.h:261-263
     return NNBVH_OK;
 }
 
@@ -1265,7 +1261,29 @@ __global__ void TestSpheresKernel(const float4 *__restrict__ rays, const SphereD
     hit[i] = ok ? 1 : 0;
     out[i] = ok ? make_float4(sh.t, sh.px, sh.py, sh.pz) : make_float4(0.f, 0.f, 0.f, 0.f);
 }
+__global__ void TestAtan2Kernel(const float *__restrict__ y, const float *__restrict__ x, uint64_t n,
+                                float *__restrict__ out) {
+    const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) out[i] = Atan2fHost(y[i], x[i]);
+}
 }  // namespace nnbvh
+
+extern "C" int nnbvh_test_atan2(nnbvh_engine *e, const float *y, const float *x, uint64_t n, float *out) {
+    if (!e || !y || !x || !out) return SetError(NNBVH_ERR_INVALID, "nnbvh_test_atan2: NULL argument");
+    if (n == 0) return NNBVH_OK;
+    CU(cudaSetDevice(e->device));
+    float *d = nullptr;
+    CU(cudaMalloc(&d, n * 12));
+    CU(cudaMemcpy(d, y, n * 4, cudaMemcpyHostToDevice));
+    CU(cudaMemcpy(d + n, x, n * 4, cudaMemcpyHostToDevice));
+    TestAtan2Kernel<<<(unsigned)((n + 255) / 256), 256, 0, e->stream>>>(d, d + n, n, d + 2 * n);
+    ++e->launches;
+    CU(cudaGetLastError());
+    CU(cudaStreamSynchronize(e->stream));
+    CU(cudaMemcpy(out, d + 2 * n, n * 4, cudaMemcpyDeviceToHost));
+    cudaFree(d);
+    return NNBVH_OK;
+}
 
 extern "C" int nnbvh_test_spheres(nnbvh_engine *e, const nnbvh_ray *rays, const nnbvh_sphere *spheres,
                                   uint64_t n, uint8_t *hit, float *out4) {

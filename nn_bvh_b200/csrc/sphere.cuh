@@ -13,14 +13,16 @@
 // path, so this file follows the host branches.  std::min / std::max are spelled out as the
 // comparisons libstdc++ performs, so NaNs take the same side.
 //
-// Supported: full or z-clipped spheres.  phiMax < 360 needs std::atan2 bit for bit
-// (shapes.h:194,216) and is rejected at upload.  For phiMax = 360 the test `phi > phiMax` can
-// never hold: phiMax = Radians(360) rounds to the float 2*Pi, and phi <= 2*Pi by construction.
+// Supported: full, z-clipped and phi-clipped spheres.  phiMax < 360 compares std::atan2's value
+// (shapes.h:196-203, :218-222): atan2_host.cuh follows the host libm's algorithm for it.  For
+// phiMax = 360 the test `phi > phiMax` can never hold (phiMax = Radians(360) rounds to the float
+// 2*Pi, and phi <= 2*Pi by construction), so full spheres skip the atan2.
 #pragma once
 
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include "atan2_host.cuh"
 #include "exact_math.cuh"
 #include "internal.h"
 
@@ -107,11 +109,22 @@ __device__ __forceinline__ Ival Sqrt(Ival i) {  // :1070-1072 with util/float.h:
 }
 
 // SphereDev: 64 bytes, one per sphere: rows 0..2 of objectFromRender, then radius and the
-// constructor's clamped zMin / zMax (shapes.h:117-128).
+// constructor's clamped zMin / zMax and phiMax in radians (shapes.h:117-128).
 struct alignas(64) SphereDev {
     float m[12];
-    float radius, zMin, zMax, pad;
+    float radius, zMin, zMax, phiMax;
 };
+constexpr float kTwoPiF = 2 * 3.14159265358979323846f;  // 2 * Pi as the reference's float expression
+
+// The clipping test of shapes.h:202-203 / :221-222 on a refined hit point.
+__device__ __forceinline__ bool SphereClipped(float radius, float zMin, float zMax, float phiMax, float px, float py,
+                                              float pz) {
+    if ((zMin > -radius && pz < zMin) || (zMax < radius && pz > zMax)) return true;
+    if (!(phiMax < kTwoPiF)) return false;
+    float phi = Atan2fHost(py, px);
+    if (phi < 0) phi = Add(phi, kTwoPiF);
+    return phi > phiMax;
+}
 static_assert(sizeof(SphereDev) == 64, "SphereDev must be 64 bytes");
 
 struct SphereHit {
@@ -137,7 +150,7 @@ __device__ __noinline__ bool SphereTest(const SphereDev *__restrict__ sp, float 
                                         float rdx, float rdy, float rdz, float tMax, SphereHit *out) {
     const float4 r0 = __ldg(reinterpret_cast<const float4 *>(sp)), r1 = __ldg(reinterpret_cast<const float4 *>(sp) + 1),
                  r2 = __ldg(reinterpret_cast<const float4 *>(sp) + 2), r3 = __ldg(reinterpret_cast<const float4 *>(sp) + 3);
-    const float radius = r3.x, zMin = r3.y, zMax = r3.z;
+    const float radius = r3.x, zMin = r3.y, zMax = r3.z, phiMax = r3.w;
     const float g3 = GammaF(3);
     Ival oix, oiy, oiz, dix, diy, diz;
     {   // Transform::operator()(Point3fi), exact input; Float(p.x) is the midpoint of [x, x]
@@ -192,13 +205,13 @@ __device__ __noinline__ bool SphereTest(const SphereDev *__restrict__ sp, float 
     const float ox = Mid(oix), oy = Mid(oiy), oz = Mid(oiz), dx = Mid(dix), dy = Mid(diy), dz = Mid(diz);
     float px, py, pz;
     SpherePoint(radius, ox, oy, oz, dx, dy, dz, Mid(tShape), &px, &py, &pz);
-    // clipping (:202-222); `phi > phiMax` cannot hold for phiMax = 360 (see the header)
-    if ((zMin > -radius && pz < zMin) || (zMax < radius && pz > zMax)) {
+    // clipping (:202-222)
+    if (SphereClipped(radius, zMin, zMax, phiMax, px, py, pz)) {
         if (tShape.lo == t1.lo && tShape.hi == t1.hi) return false;
         if (t1.hi > tMax) return false;
         tShape = t1;
         SpherePoint(radius, ox, oy, oz, dx, dy, dz, Mid(tShape), &px, &py, &pz);
-        if ((zMin > -radius && pz < zMin) || (zMax < radius && pz > zMax)) return false;
+        if (SphereClipped(radius, zMin, zMax, phiMax, px, py, pz)) return false;
     }
     out->t = Mid(tShape);
     out->px = px, out->py = py, out->pz = pz;

@@ -697,7 +697,7 @@ inline Interval Sqrt(Interval i) { return {SqrtRoundDown(i.low), SqrtRoundUp(i.h
 // nnbvh_sphere as 28 floats: renderFromObject[12], objectFromRender[12], radius, zMin, zMax, phiMax.
 struct SphereCtx {
     const float *m;  // objectFromRender rows 0..2 (row 3 = 0 0 0 1)
-    float radius, zMin, zMax;
+    float radius, zMin, zMax, phiMax;
 };
 inline float Clamp(float v, float lo, float hi) { return v < lo ? lo : (v > hi ? hi : v); }
 inline SphereCtx MakeSphereCtx(const float *s28) {  // Sphere::Sphere, shapes.h:117-128
@@ -706,11 +706,13 @@ inline SphereCtx MakeSphereCtx(const float *s28) {  // Sphere::Sphere, shapes.h:
     c.radius = s28[24];
     c.zMin = Clamp(std::min(s28[25], s28[26]), -c.radius, c.radius);
     c.zMax = Clamp(std::max(s28[25], s28[26]), -c.radius, c.radius);
+    c.phiMax = (3.14159265358979323846f / 180) * Clamp(s28[27], 0, 360);  // Radians(), util/math.h:261-263
     return c;
 }
 
-// phiMax is 360 for every sphere this restatement accepts: `phi > phiMax` (shapes.h:203) is then
-// never true -- Radians(360) rounds to the float 2*Pi and phi <= 2*Pi by construction.
+// phi comes from std::atan2 as in the reference (shapes.h:196-198): this checker links the same libm.
+// For phiMax = 360 `phi > phiMax` (shapes.h:203) is never true -- Radians(360) rounds to the float 2*Pi
+// and phi <= 2*Pi by construction.
 inline bool SphereBasicIntersect(const SphereCtx &sp, const float *ray8, float tMax, float *tOut, float *pObj) {
     const float *m = sp.m;
     const float g3 = Gamma(3);
@@ -771,7 +773,11 @@ inline bool SphereBasicIntersect(const SphereCtx &sp, const float *ray8, float t
             p[0] = 1e-5f * sp.radius;
     };
     auto clipped = [&](const float *p) {
-        return (sp.zMin > -sp.radius && p[2] < sp.zMin) || (sp.zMax < sp.radius && p[2] > sp.zMax);
+        float phi = std::atan2(p[1], p[0]);
+        if (phi < 0)
+            phi += 2 * 3.14159265358979323846f;
+        return (sp.zMin > -sp.radius && p[2] < sp.zMin) || (sp.zMax < sp.radius && p[2] > sp.zMax) ||
+               phi > sp.phiMax;
     };
     float pHit[3];
     point(tShapeHit, pHit);
@@ -1099,6 +1105,13 @@ void nnbvh_oracle_instance_bounds(const float *renderFromPrimitive12, const floa
 
 int32_t nnbvh_oracle_sphere(const float *ray8, const float *sphere28, float *out4) {
     return SphereBasicIntersect(MakeSphereCtx(sphere28), ray8, ray8[3], &out4[0], &out4[1]) ? 1 : 0;
+}
+
+// std::atan2(float, float) of the libm this checker (and oracle/_ref) links: what Sphere::BasicIntersect
+// compares with phiMax (shapes.h:196-203).
+void nnbvh_oracle_atan2f(const float *y, const float *x, int64_t n, float *out) {
+    for (int64_t i = 0; i < n; ++i)
+        out[i] = std::atan2(y[i], x[i]);
 }
 
 void nnbvh_oracle_sphere_bounds(const float *sphere28, float *out6) {

@@ -164,6 +164,17 @@ class Oracle:
         hit = self.lib.nnbvh_oracle_sphere(_p(ray8), _p(sphere28), _p(out))
         return bool(hit), out
 
+    def atan2f(self, y, x):
+        """The host libm's atan2f, elementwise."""
+        y = np.ascontiguousarray(y, dtype=np.float32)
+        x = np.ascontiguousarray(x, dtype=np.float32)
+        out = np.zeros_like(y)
+        f = self.lib.nnbvh_oracle_atan2f
+        f.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int64, ctypes.c_void_p]
+        f.restype = None
+        f(_p(y), _p(x), y.size, _p(out))
+        return out
+
     def sphere_bounds(self, sphere28):
         sphere28 = np.ascontiguousarray(sphere28, dtype=np.float32)
         out = np.zeros(6, dtype=np.float32)

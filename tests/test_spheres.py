@@ -15,7 +15,7 @@ import os
 import numpy as np
 import pytest
 
-from conftest import GOLDEN, rand_rays
+from conftest import GOLDEN, ROOT, rand_rays
 
 MISS = 0xFFFFFFFF
 
@@ -121,19 +121,43 @@ def test_mixed_scene_trees_and_traversal_match_reference_live(oracle, reference,
                           reference.intersect_p(sc, rays, parallel=False))
 
 
-def test_partial_phi_spheres_are_rejected_loudly():
-    """phimax < 360 clips by std::atan2's value: the library refuses instead of approximating."""
-    import nn_bvh_b200 as nb
-    from nn_bvh_b200 import capi
-    sph = nb.make_spheres(np.eye(4)[None], 1.0, phi_max=180.0)
-    # the check sits in the upload path, which needs a device; without one creation already fails loudly
-    import torch
-    if not torch.cuda.is_available():
-        with pytest.raises(capi.NnbvhError):
-            nb.GPUBVHAggregate(None, 4, "sah", spheres=sph)
-        return
-    with pytest.raises(capi.NnbvhError, match="phimax"):
-        nb.GPUBVHAggregate(None, 4, "sah", spheres=sph)
+@pytest.fixture(scope="module")
+def gold_phi():
+    return np.load(os.path.join(GOLDEN, "sphere_phi.npz"))
+
+
+def test_oracle_partial_phi_matches_reference_golden(oracle, gold_phi):
+    """phimax < 360: the clipping test compares std::atan2's value (shapes.h:196-203, :218-222)."""
+    g = gold_phi
+    for i in range(len(g["rays"])):
+        h, o4 = oracle.sphere(g["rays"][i], g["spheres"][i])
+        assert h == bool(g["hit"][i]), i
+        if h:
+            assert np.array_equal(o4.view(np.uint32), g["out"][i].view(np.uint32)), i
+    assert 1000 < g["hit"][2500:].sum() < 1400           # the boundary cases fall on both sides
+
+
+def test_oracle_partial_phi_matches_reference_live(oracle, reference):
+    from tools.make_golden import phi_boundary_rays, phi_spheres, sphere_rays
+    rng = np.random.default_rng(303)
+    sph = phi_spheres(rng, 3000)
+    sph[2000:, 25], sph[2000:, 26] = -sph[2000:, 24], sph[2000:, 24]
+    sph[2000:, 27] = rng.uniform(1, 359, 1000).astype(np.float32)
+    rays = np.concatenate([sphere_rays(rng, sph[:2000]), phi_boundary_rays(rng, sph[2000:])])
+    for i in range(len(rays)):
+        a, b = reference.sphere(rays[i], sph[i]), oracle.sphere(rays[i], sph[i])
+        assert a[0] == b[0] and (not a[0] or np.array_equal(a[1].view(np.uint32), b[1].view(np.uint32))), i
+
+
+def test_atan2_restatement_matches_host_libm(tmp_path):
+    """tools/atan2_check.c: the host twin of csrc/atan2_host.cuh against this machine's atan2f on 3e7
+    inputs (arbitrary bit patterns and pairs in [-1,1]^2); 1e9 were run when the file was written."""
+    import subprocess
+    exe = str(tmp_path / "atan2_check")
+    subprocess.check_call(["gcc", "-O2", "-ffp-contract=off", "-fno-builtin", "-o", exe,
+                           os.path.join(ROOT, "tools", "atan2_check.c"), "-lm"])
+    out = subprocess.run([exe, "30000000"], capture_output=True, text=True)
+    assert out.returncode == 0 and "bad=0" in out.stdout, out.stdout[-600:]
 
 
 # ---------------------------------------------------------------------------- GPU
@@ -262,3 +286,72 @@ def test_reference_scenes_with_their_spheres(oracle, name):
     assert np.array_equal(occ[sub], oracle.intersect_p_mixed(nodes, agg.ordered_tris9, agg.ordered_sphere_index,
                                                             s28, rays[sub]))
     assert np.array_equal(occ != 0, got[:, 0] != MISS)   # tMax = inf: occluded <=> a closest hit exists
+
+
+
+def _atan2_inputs(rng, n):
+    """(y, x): arbitrary bit patterns, pairs in [-1,1]^2, huge / tiny ratios, zeros, infinities, x = 1."""
+    y = rng.integers(0, 2 ** 32, n, dtype=np.uint64).astype(np.uint32).view(np.float32).copy()
+    x = rng.integers(0, 2 ** 32, n, dtype=np.uint64).astype(np.uint32).view(np.float32).copy()
+    q = n // 4
+    y[:q], x[:q] = rng.uniform(-1, 1, q), rng.uniform(-1, 1, q)
+    y[q:2 * q] = (rng.normal(size=q) * np.exp2(rng.uniform(-40, 40, q))).astype(np.float32)
+    x[q:2 * q] = (rng.normal(size=q) * np.exp2(rng.uniform(-40, 40, q))).astype(np.float32)
+    sp = np.array([0.0, -0.0, 1.0, -1.0, np.inf, -np.inf, np.nan, 1e-45, -1e-45, 3.4e38], dtype=np.float32)
+    y[2 * q:2 * q + 100], x[2 * q:2 * q + 100] = np.repeat(sp, 10), np.tile(sp, 10)
+    x[2 * q + 100:2 * q + 5000] = 1.0
+    return y, x
+
+
+@pytest.mark.gpu
+def test_device_atan2_matches_host_libm(oracle):
+    import nn_bvh_b200 as nb
+    from nn_bvh_b200 import capi
+    agg = nb.GPUBVHAggregate(None)
+    y, x = _atan2_inputs(np.random.default_rng(8), 8_000_000)
+    got = np.zeros_like(y)
+    capi.check(capi.lib().nnbvh_test_atan2(agg._h, capi.ptr(y), capi.ptr(x), y.size, capi.ptr(got)))
+    want = oracle.atan2f(y, x)
+    nan = np.isnan(want)
+    assert np.array_equal(np.isnan(got), nan)
+    assert np.array_equal(got.view(np.uint32)[~nan], want.view(np.uint32)[~nan])
+
+
+@pytest.mark.gpu
+def test_device_partial_phi_spheres_match_reference_golden(gold_phi):
+    import nn_bvh_b200 as nb
+    from nn_bvh_b200 import capi
+    agg = nb.GPUBVHAggregate(None)
+    rays, sph = np.ascontiguousarray(gold_phi["rays"]), np.ascontiguousarray(gold_phi["spheres"])
+    n = len(rays)
+    hit = np.zeros(n, dtype=np.uint8)
+    out = np.zeros((n, 4), dtype=np.float32)
+    capi.check(capi.lib().nnbvh_test_spheres(agg._h, capi.ptr(rays), capi.ptr(sph), n, capi.ptr(hit), capi.ptr(out)))
+    assert np.array_equal(hit, gold_phi["hit"])
+    assert np.array_equal(out.view(np.uint32), gold_phi["out"].view(np.uint32))
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("kernel", [0, 1])
+def test_mixed_scene_with_partial_phi_spheres_matches_oracle(oracle, kernel):
+    """Triangles + spheres clipped in z and in phi behind the traversal kernels (StepKernel, BasicKernel)."""
+    import nn_bvh_b200 as nb
+    rng = np.random.default_rng(29 + kernel)
+    tris, sph = _mixed_scene(rng, 20_000, 400, 0.012)
+    sph[:, 27] = rng.uniform(20, 400, len(sph)).astype(np.float32)
+    agg = nb.GPUBVHAggregate(tris, 4, "sah", kernel=kernel, spheres=sph.view(nb.SPHERE_DTYPE).reshape(-1))
+    N = 300_000
+    rays = rand_rays(rng, N)
+    aim = rng.integers(0, len(sph), N // 2)                      # half the rays aimed at a sphere
+    rays[:N // 2, 4:7] = sph[aim][:, [3, 7, 11]] + rng.normal(size=(N // 2, 3)).astype(np.float32) * 0.02 - rays[:N // 2, :3]
+    rays[N // 2::2, 3] = rng.random(len(rays[N // 2::2]))
+    nodes, so = agg.nodes.view(np.uint32).reshape(-1, 8), agg.ordered_sphere_index
+    want = oracle.intersect_mixed(nodes, agg.ordered_tris9, so, sph, rays)
+    got = np.ascontiguousarray(agg.IntersectBatch(rays)).view(np.uint32).reshape(-1, 5)
+    assert np.array_equal(got, want)
+    hit = want[:, 0] != MISS
+    assert (so[want[hit, 0]] >= 0).sum() > 20_000
+    full = sph.copy()
+    full[:, 27] = 360
+    assert (oracle.intersect_mixed(nodes, agg.ordered_tris9, so, full, rays) != want).any(axis=1).sum() > 5000   # the clip matters
+    assert np.array_equal(agg.IntersectPBatch(rays), oracle.intersect_p_mixed(nodes, agg.ordered_tris9, so, sph, rays))

@@ -123,6 +123,7 @@ def test_sphere_interaction_matches_reference_live(shim, reference, oracle):
     rng = np.random.default_rng(77)
     spheres = random_spheres(rng, 12)
     spheres[::3, 0:12:4] *= -1          # first column of renderFromObject: a mirror
+    spheres[1::2, 27] = rng.uniform(60, 350, len(spheres[1::2])).astype(np.float32)     # u = phi / phiMax
     for i, s in enumerate(spheres):
         m = np.eye(4)
         m[:3] = s[:12].reshape(3, 4).astype(np.float64)

@@ -32,6 +32,9 @@ oracle/ref_driver.cpp; the fixtures are small so they can be committed.
                     (shapes.h:130-139, :238-280) for 48 spheres x 64 rays: rotated / scaled /
                     mirrored transforms, z-clipped, reverseOrientation; plus what Interaction's
                     constructor stores as wo (--only-sphere-interaction).
+  sphere_phi.npz    Sphere::BasicIntersect for 4000 (ray, sphere) pairs with phimax < 360 (the std::atan2
+                    clipping test, shapes.h:196-203), 1500 of them aimed within 1e-7 .. 1e-3 (relative)
+                    of the phi = phimax boundary (--only-sphere-phi).
   instanced_surface.npz  BVHAggregate::Intersect's SurfaceInteraction on an instanced scene (some
                     instances mirrored, ray directions not normalised): TransformedPrimitive::Intersect's
                     (*renderFromPrimitive)(si->intr) (cpu/primitive.cpp:112-125), 42 words per ray
@@ -437,6 +440,52 @@ def instanced_surface(ref, rng):
     np.savez_compressed(os.path.join(OUT, "instanced_surface.npz"), **out)
 
 
+def phi_spheres(rng, n):
+    """random_spheres with phimax in (-20, 400) (clamped by the constructor) and a few exact values."""
+    s = random_spheres(rng, n)
+    s[:, 27] = rng.uniform(-20, 400, n).astype(np.float32)
+    s[::7, 27] = rng.choice([0, 90, 180, 270, 359.99, 360], len(s[::7]))
+    return s
+
+
+def phi_boundary_rays(rng, spheres):
+    """One ray per sphere whose first hit lies at phi = phimax * (1 +- 1e-7 .. 1e-3)."""
+    n = len(spheres)
+    rays = np.zeros((n, 8), dtype=np.float32)
+    for i, s in enumerate(spheres):
+        m = np.eye(4)
+        m[:3] = s[:12].reshape(3, 4).astype(np.float64)
+        r = float(s[24])
+        phi = np.radians(np.clip(float(s[27]), 0, 360)) * (1 + rng.choice([-1, 1]) * 10 ** rng.uniform(-7, -3))
+        ct = rng.uniform(-0.9, 0.9)
+        st = np.sqrt(1 - ct * ct)
+        p_obj = np.array([r * st * np.cos(phi), r * st * np.sin(phi), r * ct])
+        o_obj = p_obj * rng.uniform(1.5, 4)                   # outside, on the hit point's normal: first hit is p
+        o = m[:3, :3] @ o_obj + m[:3, 3]
+        p = m[:3, :3] @ p_obj + m[:3, 3]
+        d = p - o
+        if i % 2:
+            d /= np.linalg.norm(d)
+        rays[i, :3], rays[i, 4:7], rays[i, 3], rays[i, 7] = o, d, np.inf, rng.random()
+    return rays
+
+
+def sphere_phi(ref, rng):
+    n, nb = 2500, 1500
+    spheres = phi_spheres(rng, n + nb)
+    spheres[n:, 25], spheres[n:, 26] = -spheres[n:, 24], spheres[n:, 24]      # boundary cases: no z clipping
+    spheres[n:, 27] = rng.uniform(5, 355, nb).astype(np.float32)
+    rays = np.concatenate([sphere_rays(rng, spheres[:n]), phi_boundary_rays(rng, spheres[n:])])
+    hit = np.zeros(n + nb, dtype=np.uint8)
+    out = np.zeros((n + nb, 4), dtype=np.float32)
+    for i in range(n + nb):
+        h, o4 = ref.sphere(rays[i], spheres[i])
+        hit[i] = h
+        out[i] = o4 if h else 0
+    print("sphere_phi: hits", int(hit[:n].sum()), "of", n, "; boundary hits", int(hit[n:].sum()), "of", nb)
+    np.savez_compressed(os.path.join(OUT, "sphere_phi.npz"), spheres=spheres, rays=rays, hit=hit, out=out)
+
+
 if __name__ == "__main__":
     os.makedirs(OUT, exist_ok=True)
     ref = Reference(threads=1)
@@ -455,6 +504,9 @@ if __name__ == "__main__":
     if "--only-instanced-surface" in sys.argv:
         instanced_surface(ref, np.random.default_rng(415))
         sys.exit(0)
+    if "--only-sphere-phi" in sys.argv:
+        sphere_phi(ref, np.random.default_rng(196))
+        sys.exit(0)
     if "--only-hlbvh" in sys.argv:
         hlbvh(ref)
         sys.exit(0)
@@ -468,3 +520,4 @@ if __name__ == "__main__":
     instanced(ref, np.random.default_rng(112))
     sphere_interaction(ref, np.random.default_rng(238))
     instanced_surface(ref, np.random.default_rng(415))
+    sphere_phi(ref, np.random.default_rng(196))
