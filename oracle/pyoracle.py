@@ -374,6 +374,52 @@ class Reference:
         f(scene, _p(rays8), n, _p(hit), _p(t_hit), _p(out))
         return hit.astype(bool), t_hit, out
 
+    # ---- the reference's own wavefront queues (oracle/ref_queues.cpp) ----
+    def ray_queue(self, rays8, max_queue_size=None):
+        """A real pbrt::RayQueue filled by PushCameraRay -> (handle, [7 plane addresses], size)."""
+        rays8 = np.ascontiguousarray(rays8, dtype=np.float32).reshape(-1, 8)
+        L = self.lib
+        L.nnbvh_ref_rayqueue_create.restype = ctypes.c_void_p
+        L.nnbvh_ref_rayqueue_create.argtypes = [ctypes.c_int]
+        L.nnbvh_ref_rayqueue_push.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int]
+        L.nnbvh_ref_rayqueue_planes.argtypes = [ctypes.c_void_p, ctypes.c_void_p]
+        q = ctypes.c_void_p(L.nnbvh_ref_rayqueue_create(max_queue_size or len(rays8)))
+        L.nnbvh_ref_rayqueue_push(q, _p(rays8), len(rays8))
+        planes = (ctypes.c_void_p * 7)()
+        size = L.nnbvh_ref_rayqueue_planes(q, planes)
+        return q, [int(a) for a in planes], size
+
+    def ray_queue_get(self, q, i):
+        out = np.zeros(8, dtype=np.float32)
+        self.lib.nnbvh_ref_rayqueue_get.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p]
+        self.lib.nnbvh_ref_rayqueue_get.restype = None
+        self.lib.nnbvh_ref_rayqueue_get(q, i, _p(out))
+        return out
+
+    def ray_queue_destroy(self, q):
+        self.lib.nnbvh_ref_rayqueue_destroy.argtypes = [ctypes.c_void_p]
+        self.lib.nnbvh_ref_rayqueue_destroy.restype = None
+        self.lib.nnbvh_ref_rayqueue_destroy(q)
+
+    def shadow_queue(self, rays8, max_queue_size=None):
+        """A real pbrt::ShadowRayQueue filled by Push -> (handle, [8 plane addresses], size)."""
+        rays8 = np.ascontiguousarray(rays8, dtype=np.float32).reshape(-1, 8)
+        L = self.lib
+        L.nnbvh_ref_shadowqueue_create.restype = ctypes.c_void_p
+        L.nnbvh_ref_shadowqueue_create.argtypes = [ctypes.c_int]
+        L.nnbvh_ref_shadowqueue_push.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int]
+        L.nnbvh_ref_shadowqueue_planes.argtypes = [ctypes.c_void_p, ctypes.c_void_p]
+        q = ctypes.c_void_p(L.nnbvh_ref_shadowqueue_create(max_queue_size or len(rays8)))
+        L.nnbvh_ref_shadowqueue_push(q, _p(rays8), len(rays8))
+        planes = (ctypes.c_void_p * 8)()
+        size = L.nnbvh_ref_shadowqueue_planes(q, planes)
+        return q, [int(a) for a in planes], size
+
+    def shadow_queue_destroy(self, q):
+        self.lib.nnbvh_ref_shadowqueue_destroy.argtypes = [ctypes.c_void_p]
+        self.lib.nnbvh_ref_shadowqueue_destroy.restype = None
+        self.lib.nnbvh_ref_shadowqueue_destroy(q)
+
     def interaction_wo(self, wo3):
         """What Interaction's constructor stores for a given wo (interaction.h:30-32)."""
         wo3 = np.ascontiguousarray(wo3, dtype=np.float32)

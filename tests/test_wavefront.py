@@ -185,8 +185,41 @@ def _mesh(rng, V=4000, T=12000):
     return verts, np.ascontiguousarray(idx), uv, n
 
 
+def _plane(addr, n):
+    return np.ctypeslib.as_array((ctypes.c_float * n).from_address(addr))
+
+
+def test_queue_views_are_the_reference_queue_planes(reference):
+    """RayQueueView / ShadowRayQueueView name the arrays of the reference's OWN queue types: a real
+    pbrt::RayQueue (WorkQueue<RayWorkItem>, workitems.h:330-343) and ShadowRayQueue (:165-172, :386), with
+    SOA<> generated by the reference's soac, filled through PushCameraRay / Push.  Plane k of the view holds
+    component k of ray i at index i -- nothing to gather or repack."""
+    rng = np.random.default_rng(12)
+    N = 5000
+    rays = rand_rays(rng, N)
+    rays[:, 7] = rng.random(N)
+    rays[:, 3] = rng.random(N)
+    q, planes, size = reference.ray_queue(rays, max_queue_size=N + 100)
+    try:
+        assert size == N and len(set(planes)) == 7
+        for k, col in enumerate((0, 1, 2, 4, 5, 6, 7)):            # ox oy oz dx dy dz time
+            assert np.array_equal(_plane(planes[k], N).view(np.uint32), rays[:, col].view(np.uint32)), k
+        for i in (0, 1, N // 2, N - 1):                            # what (*rayQ)[i].ray gives the reference's loop
+            got = reference.ray_queue_get(q, i)
+            assert np.array_equal(got[[0, 1, 2, 4, 5, 6, 7]], rays[i, [0, 1, 2, 4, 5, 6, 7]])
+    finally:
+        reference.ray_queue_destroy(q)
+    q, planes, size = reference.shadow_queue(rays)
+    try:
+        assert size == N and len(set(planes)) == 8
+        for k, col in enumerate((0, 1, 2, 4, 5, 6, 7, 3)):         # ... time tMax
+            assert np.array_equal(_plane(planes[k], N).view(np.uint32), rays[:, col].view(np.uint32)), k
+    finally:
+        reference.shadow_queue_destroy(q)
+
+
 @pytest.mark.gpu
-@pytest.mark.parametrize("where", ["host", "device"])
+@pytest.mark.parametrize("where", ["host", "device", "reference_queue"])
 def test_wavefront_queues_closest_and_shadow(shim, oracle, reference, where):
     import torch
     rng = np.random.default_rng(34)
@@ -200,12 +233,17 @@ def test_wavefront_queues_closest_and_shadow(shim, oracle, reference, where):
         rays[:, 7] = rng.random(N)                     # ray.time travels to the interaction
         rays[N // 2:, 3] = rng.random(N - N // 2)      # shadow tMax
         planes_np = [np.ascontiguousarray(rays[:, k]) for k in (0, 1, 2, 4, 5, 6, 7, 3)]
+        ref_q = None
         if where == "device":
             keep = [torch.from_numpy(p).cuda() for p in planes_np]
             ptrs = [t.data_ptr() for t in keep]
+        elif where == "reference_queue":   # the memory of the reference's own RayQueue / ShadowRayQueue
+            ref_q = (reference.ray_queue(rays), reference.shadow_queue(rays))
+            ptrs = ref_q[0][1] + [None]
         else:
             ptrs = [p.ctypes.data for p in planes_np]
         arr = (ctypes.c_void_p * 8)(*ptrs)
+        arr_s = (ctypes.c_void_p * 8)(*ref_q[1][1]) if ref_q else arr
 
         kind = np.full(N, -1, dtype=np.int8)
         prim = np.zeros(N, dtype=np.uint32)
@@ -238,12 +276,15 @@ def test_wavefront_queues_closest_and_shadow(shim, oracle, reference, where):
 
         found = np.full(N, 7, dtype=np.uint8)
         for tr in (0, 1):
-            assert shim.wf_intersect_shadow(h, N, arr, N, _p(found), tr) == N, shim.wf_last_error()
+            assert shim.wf_intersect_shadow(h, N, arr_s, N, _p(found), tr) == N, shim.wf_last_error()
             assert np.array_equal(found, oracle.intersect_p(nodes, tris9[order], rays))
         # an empty queue is a no-op
-        assert shim.wf_intersect_shadow(h, N, arr, 0, _p(found), 0) == 0
+        assert shim.wf_intersect_shadow(h, N, arr_s, 0, _p(found), 0) == 0
     finally:
         shim.wf_destroy(h)
+        if ref_q:
+            reference.ray_queue_destroy(ref_q[0][0])
+            reference.shadow_queue_destroy(ref_q[1][0])
 
 
 @pytest.mark.gpu
