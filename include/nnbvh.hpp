@@ -20,6 +20,7 @@
 
 #include <algorithm>
 #include <cstddef>
+#include <cmath>
 #include <cstdint>
 #include <limits>
 #include <memory>
@@ -58,6 +59,24 @@ struct Hit {
 struct Bounds3f {
     float pMin[3], pMax[3];
 };
+
+// nnbvh_sphere takes phimax in degrees, as `Shape "sphere"` gives it; Sphere keeps
+// phiMax = Radians(Clamp(phimax, 0, 360)) (shapes.h:117-128, util/math.h:261-263).  A binding that only has
+// the Sphere object recovers a degree value that maps to the SAME float: float(Degrees(phiMax)) or one of
+// its neighbours (the two grids have nearly the same spacing; a preimage exists because phiMax came from one).
+inline float SpherePhiMaxDegrees(float phiMaxRadians) {
+    const float kPi = 3.14159265358979323846f;
+    auto radians = [kPi](float deg) { return (kPi / 180) * (deg < 0 ? 0.f : (deg > 360 ? 360.f : deg)); };
+    float deg = (180 / kPi) * phiMaxRadians;
+    if (radians(deg) == phiMaxRadians) return deg;
+    float up = deg, down = deg;
+    for (int k = 0; k < 16; ++k) {
+        up = std::nextafter(up, 1e9f), down = std::nextafter(down, -1e9f);
+        if (radians(up) == phiMaxRadians) return up;
+        if (radians(down) == phiMaxRadians) return down;
+    }
+    return deg;  // not produced by Radians(float): the closest value
+}
 
 inline nnbvh_ray MakeRay(const Ray &r, float tMax) {
     return nnbvh_ray{r.o[0], r.o[1], r.o[2], tMax, r.d[0], r.d[1], r.d[2], r.time};

@@ -1,4 +1,4 @@
-// integration/pbrt/compile_check.cpp -- type-checks gpubvh_wavefront.h against the reference's real headers
+// integration/pbrt/compile_check.cpp -- type-checks gpubvh.h and gpubvh_wavefront.h against the reference's real headers
 // (tests/test_integration_compile.py; -fsyntax-only).  The friend declarations the adapter needs are
 // replaced here by opening the three classes' private sections.
 #include <algorithm>
@@ -18,6 +18,15 @@
 #include <pbrt/shapes.h>
 #undef private
 #include "gpubvh_wavefront.h"
+
+// what CreateAccelerator (cpu/aggregates.cpp:1163-1178) would do with it
+pbrt::GPUBVHAggregate *MakeAccelerator(std::vector<pbrt::Primitive> prims, const pbrt::ParameterDictionary &dict) {
+    pbrt::GPUBVHAggregate *accel = pbrt::GPUBVHAggregate::Create(std::move(prims), dict);
+    pbrt::Ray ray(pbrt::Point3f(0, 0, 0), pbrt::Vector3f(0, 0, 1));
+    if (accel->IntersectP(ray, pbrt::Infinity))
+        (void)accel->Intersect(ray, pbrt::Infinity)->intr.p();
+    return accel;
+}
 
 // what wavefront/integrator.cpp:157-170 would do with it
 pbrt::WavefrontAggregate *MakeAggregate(std::vector<pbrt::Primitive> prims, int maxQueueSize) {

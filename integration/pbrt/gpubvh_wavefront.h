@@ -14,20 +14,14 @@
 // `soac` generates -- by tests/test_integration_compile.py (type-checked: every `override` below must
 // match WavefrontAggregate's signature).  It cannot be linked here: that needs all of pbrt.
 //
-// Friend access it needs in the reference (three one-line patches):
-//   cpu/primitive.h:58  class GeometricPrimitive { friend class GPUBVHWavefrontAggregate; ...
-//   cpu/primitive.h:76  class SimplePrimitive    { friend class GPUBVHWavefrontAggregate; ...
-//   shapes.h:1179       class Triangle           { friend class GPUBVHWavefrontAggregate; ...
-// (the compile check opens them with `#define private public` instead of patching).
+// The primitive list, the hit -> ShapeIntersection step and the friend access that step needs live in
+// gpubvh.h (pbrt::GPUBVHAggregate); this class adds the queue plumbing.
 //
-// Contract: SimplePrimitive / alpha-free GeometricPrimitive over Triangle.  Sphere and
-// TransformedPrimitive entries map to nnbvh_sphere / nnbvh_instance as INTEGRATION.md 2.1 says.
+// Contract: SimplePrimitive / alpha-free GeometricPrimitive over Triangle or Sphere.  TransformedPrimitive
+// entries map to nnbvh_instance as INTEGRATION.md 2.1 says.
 #ifndef NNBVH_INTEGRATION_PBRT_GPUBVH_WAVEFRONT_H
 #define NNBVH_INTEGRATION_PBRT_GPUBVH_WAVEFRONT_H
 
-#include <pbrt/cpu/aggregates.h>
-#include <pbrt/cpu/primitive.h>
-#include <pbrt/shapes.h>
 #include <pbrt/util/parallel.h>
 #include <pbrt/wavefront/integrator.h>
 #include <pbrt/wavefront/intersect.h>
@@ -35,7 +29,7 @@
 #include <memory>
 #include <vector>
 
-#include <nnbvh.hpp>
+#include "gpubvh.h"
 
 namespace pbrt {
 
@@ -44,30 +38,9 @@ class GPUBVHWavefrontAggregate : public WavefrontAggregate {
     // prims: the list CPUAggregate would hand to CreateAccelerator (cpu/aggregates.cpp:1163-1178).
     GPUBVHWavefrontAggregate(std::vector<Primitive> prims, int maxPrimsInNode,
                              BVHAggregate::SplitMethod splitMethod, int maxQueueSize, int device = -1)
-        : primitives(std::move(prims)), hits(maxQueueSize), occluded(maxQueueSize) {
-        std::vector<float> tris9;
-        tris9.reserve(9 * primitives.size());
-        for (const Primitive &p : primitives) {
-            Parts parts = PartsOf(p);
-            if (!parts.tri)
-                ErrorExit("gpubvh: only (alpha-free) triangle primitives are supported");
-            const TriangleMesh *mesh = parts.tri->GetMesh();
-            const int *v = &mesh->vertexIndices[3 * parts.tri->triIndex];
-            for (int k = 0; k < 3; ++k) {
-                Point3f q = mesh->p[v[k]];
-                tris9.push_back(q.x), tris9.push_back(q.y), tris9.push_back(q.z);
-            }
-        }
-        // BVHAggregate::SplitMethod { SAH, HLBVH, Middle, EqualCounts } (cpu/aggregates.h:33) has the
-        // library's numbering
-        agg = std::make_unique<nnbvh::GPUBVHAggregate>(
-            tris9, maxPrimsInNode, nnbvh::GPUBVHAggregate::SplitMethod((int)splitMethod), device);
-    }
+        : host(std::move(prims), maxPrimsInNode, splitMethod, device), hits(maxQueueSize), occluded(maxQueueSize) {}
 
-    Bounds3f Bounds() const override {
-        nnbvh::Bounds3f b = agg->Bounds();
-        return Bounds3f(Point3f(b.pMin[0], b.pMin[1], b.pMin[2]), Point3f(b.pMax[0], b.pMax[1], b.pMax[2]));
-    }
+    Bounds3f Bounds() const override { return host.Bounds(); }
 
     // CPUAggregate::IntersectClosest, wavefront/aggregate.cpp:34-58
     void IntersectClosest(int maxRays, const RayQueue *rayQ, EscapedRayQueue *escapedRayQ,
@@ -78,7 +51,7 @@ class GPUBVHWavefrontAggregate : public WavefrontAggregate {
         if (n == 0)
             return;
         // SOA<RayWorkItem> keeps ray.o.x[], ray.o.y[] ... as separate float arrays: no repack
-        agg->IntersectBatchSoA(rayQ->ray.o.x, rayQ->ray.o.y, rayQ->ray.o.z, rayQ->ray.d.x, rayQ->ray.d.y,
+        host.Engine().IntersectBatchSoA(rayQ->ray.o.x, rayQ->ray.o.y, rayQ->ray.o.z, rayQ->ray.d.x, rayQ->ray.d.y,
                                rayQ->ray.d.z, /*tMax=*/nullptr, (uint64_t)n, hits.data());
         ParallelFor(0, n, [=](int index) {
             const RayWorkItem r = (*rayQ)[index];
@@ -86,7 +59,7 @@ class GPUBVHWavefrontAggregate : public WavefrontAggregate {
             if (h.prim == NNBVH_MISS)
                 EnqueueWorkAfterMiss(r, mediumSampleQ, escapedRayQ);
             else {
-                ShapeIntersection si = Resolve(h, r.ray);
+                ShapeIntersection si = host.Resolve(h, r.ray);
                 EnqueueWorkAfterIntersection(r, r.ray.medium, si.tHit, si.intr, mediumSampleQ, nextRayQ,
                                              hitAreaLightQ, basicMtlQ, universalMtlQ);
             }
@@ -100,7 +73,7 @@ class GPUBVHWavefrontAggregate : public WavefrontAggregate {
         if (n == 0)
             return;
         const ShadowRayQueue *q = shadowRayQueue;
-        agg->IntersectPBatchSoA(q->ray.o.x, q->ray.o.y, q->ray.o.z, q->ray.d.x, q->ray.d.y, q->ray.d.z, q->tMax,
+        host.Engine().IntersectPBatchSoA(q->ray.o.x, q->ray.o.y, q->ray.o.z, q->ray.d.x, q->ray.d.y, q->ray.d.z, q->tMax,
                                 (uint64_t)n, occluded.data());
         ParallelFor(0, n, [=](int index) {
             RecordShadowRayResult((*shadowRayQueue)[index], pixelSampleState, occluded[index] != 0);
@@ -117,7 +90,7 @@ class GPUBVHWavefrontAggregate : public WavefrontAggregate {
             TraceTransmittance(
                 w, pixelSampleState,
                 [&](Ray ray, Float tMax) -> TransmittanceTraceResult {
-                    si = IntersectOne(ray, tMax);
+                    si = host.Intersect(ray, tMax);
                     if (!si)
                         return TransmittanceTraceResult{false, Point3f(), Material()};
                     return TransmittanceTraceResult{true, si->intr.p(), si->intr.material};
@@ -137,7 +110,7 @@ class GPUBVHWavefrontAggregate : public WavefrontAggregate {
                 Ray r = base.SpawnRayTo(w.p1);
                 if (r.d == Vector3f(0, 0, 0))
                     break;
-                pstd::optional<ShapeIntersection> si = IntersectOne(r, 1);
+                pstd::optional<ShapeIntersection> si = host.Intersect(r, 1);
                 if (!si)
                     break;
                 base = si->intr;
@@ -152,50 +125,8 @@ class GPUBVHWavefrontAggregate : public WavefrontAggregate {
         });
     }
 
-    // {prim, t, b0, b1, b2} -> what Primitive::Intersect would have returned
-    // (SimplePrimitive / GeometricPrimitive::Intersect, cpu/primitive.cpp:50-84, :100-110)
-    ShapeIntersection Resolve(const nnbvh_hit &h, const Ray &ray) const {
-        Parts parts = PartsOf(primitives[agg->PrimitiveIndex(h.prim)]);
-        SurfaceInteraction intr = Triangle::InteractionFromIntersection(
-            parts.tri->GetMesh(), parts.tri->triIndex, TriangleIntersection{h.b0, h.b1, h.b2, h.t}, ray.time,
-            -ray.d);
-        intr.SetIntersectionProperties(parts.material, parts.areaLight, parts.mediumInterface, ray.medium);
-        return ShapeIntersection{intr, h.t};
-    }
-
   private:
-    struct Parts {
-        const Triangle *tri = nullptr;
-        Material material;
-        Light areaLight;
-        const MediumInterface *mediumInterface = nullptr;
-    };
-    static Parts PartsOf(const Primitive &p) {
-        Parts out;
-        if (const SimplePrimitive *sp = p.CastOrNullptr<SimplePrimitive>()) {
-            out.tri = sp->shape.CastOrNullptr<Triangle>();
-            out.material = sp->material;
-        } else if (const GeometricPrimitive *gp = p.CastOrNullptr<GeometricPrimitive>()) {
-            if (!gp->alpha)
-                out.tri = gp->shape.CastOrNullptr<Triangle>();
-            out.material = gp->material;
-            out.areaLight = gp->areaLight;
-            out.mediumInterface = &gp->mediumInterface;
-        }
-        return out;
-    }
-    // one ray through the batch entry point (the data-dependent loops above)
-    pstd::optional<ShapeIntersection> IntersectOne(const Ray &ray, Float tMax) const {
-        nnbvh_ray r{ray.o.x, ray.o.y, ray.o.z, tMax, ray.d.x, ray.d.y, ray.d.z, ray.time};
-        nnbvh_hit h;
-        agg->IntersectBatch(&r, 1, &h);
-        if (h.prim == NNBVH_MISS)
-            return {};
-        return Resolve(h, ray);
-    }
-
-    std::vector<Primitive> primitives;  // caller's order: hit.prim -> primitives[agg->PrimitiveIndex(prim)]
-    std::unique_ptr<nnbvh::GPUBVHAggregate> agg;
+    GPUBVHAggregate host;
     mutable std::vector<nnbvh_hit> hits;  // one IntersectClosest / IntersectShadow is in flight at a time
     mutable std::vector<uint8_t> occluded;
 };

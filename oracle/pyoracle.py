@@ -20,6 +20,7 @@ import numpy as np
 HERE = os.path.dirname(os.path.abspath(__file__))
 ORACLE_SO = os.path.join(HERE, "_build", "libnnbvh_oracle.so")
 REF_SO = os.path.join(HERE, "_ref", "libnnbvh_ref.so")
+BINDING_SO = os.path.join(HERE, "_ref", "libnnbvh_ref_binding.so")
 MISS = 0xFFFFFFFF
 
 SPLIT = {"sah": 0, "hlbvh": 1, "middle": 2, "equal": 3}
@@ -27,7 +28,7 @@ SPLIT = {"sah": 0, "hlbvh": 1, "middle": 2, "equal": 3}
 
 def build(ref: bool = True) -> None:
     """Compile the restatement (always) and oracle/_ref (when /root/reference exists)."""
-    targets = ["oracle"] + (["ref"] if ref else [])
+    targets = ["oracle"] + (["ref", "binding"] if ref else [])
     subprocess.check_call(["make", "-s", "-C", HERE, "-j8"] + targets)
 
 
@@ -213,10 +214,10 @@ class Reference:
 
     _inited = False
 
-    def __init__(self, threads: int = 0):
-        if not ref_available():
-            raise FileNotFoundError(REF_SO)
-        L = self.lib = ctypes.CDLL(REF_SO)
+    def __init__(self, threads: int = 0, so: str = REF_SO):
+        if not os.path.exists(so):
+            raise FileNotFoundError(so)
+        L = self.lib = ctypes.CDLL(so)
         L.nnbvh_ref_scene_create.restype = ctypes.c_void_p
         L.nnbvh_ref_scene_create.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p,
                                              ctypes.c_int, ctypes.c_int, ctypes.c_int]
@@ -507,3 +508,60 @@ class Reference:
         self.lib.nnbvh_ref_free(oi)
         self.lib.nnbvh_ref_free(ov)
         return idx, v
+
+
+def binding_available() -> bool:
+    return os.path.exists(BINDING_SO)
+
+
+class Binding(Reference):
+    """oracle/_ref/libnnbvh_ref_binding.so: the reference driver plus integration/pbrt/gpubvh.h over
+    libnnbvh.so -- pbrt::GPUBVHAggregate built on the very Primitive list a reference scene holds."""
+
+    def __init__(self, threads: int = 1):
+        super().__init__(threads, so=BINDING_SO)
+        L = self.lib
+        L.nnbvh_binding_last_error.restype = ctypes.c_char_p
+        L.nnbvh_binding_create.restype = ctypes.c_void_p
+        L.nnbvh_binding_create.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_int]
+        L.nnbvh_binding_destroy.argtypes = [ctypes.c_void_p]
+        L.nnbvh_binding_destroy.restype = None
+        for f in (L.nnbvh_binding_intersect_surface, L.nnbvh_binding_intersect_surface_batch):
+            f.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int64] + [ctypes.c_void_p] * 3
+        L.nnbvh_binding_intersect_p.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int64, ctypes.c_void_p]
+        L.nnbvh_binding_bounds.argtypes = [ctypes.c_void_p, ctypes.c_void_p]
+        L.nnbvh_binding_bounds.restype = None
+
+    def create(self, scene, max_prims: int = 4, split: str = "sah"):
+        h = self.lib.nnbvh_binding_create(scene, max_prims, SPLIT[split])
+        if not h:
+            raise RuntimeError(self.lib.nnbvh_binding_last_error().decode())
+        return ctypes.c_void_p(h)
+
+    def destroy(self, b):
+        self.lib.nnbvh_binding_destroy(b)
+
+    def surface(self, b, rays8, batch: bool):
+        rays8 = np.ascontiguousarray(rays8, dtype=np.float32)
+        n = rays8.shape[0]
+        hit = np.zeros(n, dtype=np.int32)
+        t_hit = np.zeros(n, dtype=np.float32)
+        out = np.zeros((n, 42), dtype=np.float32)
+        f = self.lib.nnbvh_binding_intersect_surface_batch if batch else self.lib.nnbvh_binding_intersect_surface
+        rc = f(b, _p(rays8), n, _p(hit), _p(t_hit), _p(out))
+        if rc:
+            raise RuntimeError(self.lib.nnbvh_binding_last_error().decode())
+        return hit.astype(bool), t_hit, out
+
+    def intersect_p_binding(self, b, rays8):
+        rays8 = np.ascontiguousarray(rays8, dtype=np.float32)
+        occ = np.zeros(rays8.shape[0], dtype=np.uint8)
+        rc = self.lib.nnbvh_binding_intersect_p(b, _p(rays8), rays8.shape[0], _p(occ))
+        if rc:
+            raise RuntimeError(self.lib.nnbvh_binding_last_error().decode())
+        return occ
+
+    def bounds(self, b):
+        out = np.zeros(6, dtype=np.float32)
+        self.lib.nnbvh_binding_bounds(b, _p(out))
+        return out

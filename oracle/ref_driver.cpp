@@ -113,6 +113,7 @@ struct RefScene {
     std::vector<RefSphere *> spheres;  // primitives nTris .. nTris + spheres.size() - 1 of the list
     pbrt::TriangleMesh *mesh = nullptr;
     pbrt::BVHAggregate *agg = nullptr;
+    std::vector<pbrt::Primitive> primList;  // the list BVHAggregate was given, in the caller's order
     int nTris = 0;
     int nNodes = 0;
     std::vector<int> orderedToOrig;  // ordered prim index -> original triangle
@@ -220,6 +221,7 @@ void *nnbvh_ref_scene_create_mixed(const float *verts, int nVerts, const int *in
     }
     s->nTris = nTris;
     const int nPrims = nTris + nSpheres;
+    s->primList = prims;
     s->agg = new pbrt::BVHAggregate(std::move(prims), maxPrimsInNode,
                                     (pbrt::BVHAggregate::SplitMethod)splitMethod);
     s->nNodes = CountNodes(reinterpret_cast<const NodeMirror *>(s->agg->nodes));
@@ -730,3 +732,94 @@ int nnbvh_ref_stats(int64_t *nodesVisited, int64_t *triTests, int64_t *triHits) 
 }
 
 }  // extern "C"
+
+// ---- the reference-side binding, run on the reference's own primitives --------------------------------
+// Compiled only into oracle/_ref/libnnbvh_ref_binding.so (which links libnnbvh.so): pbrt::GPUBVHAggregate of
+// integration/pbrt/gpubvh.h is constructed over the SAME std::vector<Primitive> a BVHAggregate of this
+// driver got, so its Intersect / IntersectP / Resolve can be compared with BVHAggregate's, interaction
+// for interaction (tests/test_binding.py; needs a GPU).
+#ifdef NNBVH_WITH_BINDING
+#include "../integration/pbrt/gpubvh.h"
+
+namespace {
+thread_local std::string g_bindingError;
+void PutSurface42(const pbrt::SurfaceInteraction &intr, float *o) {
+    PutSurface39(intr, o);
+    o[39] = intr.wo.x, o[40] = intr.wo.y, o[41] = intr.wo.z;
+}
+}  // namespace
+
+extern "C" {
+const char *nnbvh_binding_last_error(void) { return g_bindingError.c_str(); }
+
+void *nnbvh_binding_create(void *scene, int maxPrimsInNode, int splitMethod) {
+    RefScene *s = (RefScene *)scene;
+    try {
+        return new pbrt::GPUBVHAggregate(s->primList, maxPrimsInNode,
+                                         (pbrt::BVHAggregate::SplitMethod)splitMethod);
+    } catch (const nnbvh::Error &e) {
+        g_bindingError = e.what();
+        return nullptr;
+    }
+}
+void nnbvh_binding_destroy(void *b) { delete (pbrt::GPUBVHAggregate *)b; }
+
+// Primitive's single-ray surface: Intersect(ray, tMax) per ray
+int nnbvh_binding_intersect_surface(void *binding, const float *rays, int64_t n, int *hit, float *tHit,
+                                    float *out42) {
+    const pbrt::GPUBVHAggregate *b = (const pbrt::GPUBVHAggregate *)binding;
+    try {
+        for (int64_t i = 0; i < n; ++i) {
+            const float *r = rays + 8 * i;
+            pstd::optional<pbrt::ShapeIntersection> si = b->Intersect(MakeRay(r), r[3]);
+            hit[i] = si.has_value();
+            if (!si)
+                continue;
+            tHit[i] = si->tHit;
+            PutSurface42(si->intr, out42 + 42 * i);
+        }
+    } catch (const nnbvh::Error &e) {
+        g_bindingError = e.what();
+        return e.code;
+    }
+    return 0;
+}
+// The batch surface: one IntersectBatch, then Resolve per hit
+int nnbvh_binding_intersect_surface_batch(void *binding, const float *rays, int64_t n, int *hit,
+                                          float *tHit, float *out42) {
+    const pbrt::GPUBVHAggregate *b = (const pbrt::GPUBVHAggregate *)binding;
+    try {
+        std::vector<nnbvh_hit> hits((size_t)n);
+        b->Engine().IntersectBatch(reinterpret_cast<const nnbvh_ray *>(rays), (uint64_t)n, hits.data());
+        for (int64_t i = 0; i < n; ++i) {
+            hit[i] = hits[i].prim != NNBVH_MISS;
+            if (!hit[i])
+                continue;
+            pbrt::ShapeIntersection si = b->Resolve(hits[i], MakeRay(rays + 8 * i));
+            tHit[i] = si.tHit;
+            PutSurface42(si.intr, out42 + 42 * i);
+        }
+    } catch (const nnbvh::Error &e) {
+        g_bindingError = e.what();
+        return e.code;
+    }
+    return 0;
+}
+int nnbvh_binding_intersect_p(void *binding, const float *rays, int64_t n, uint8_t *occluded) {
+    const pbrt::GPUBVHAggregate *b = (const pbrt::GPUBVHAggregate *)binding;
+    try {
+        for (int64_t i = 0; i < n; ++i)
+            occluded[i] = b->IntersectP(MakeRay(rays + 8 * i), rays[8 * i + 3]) ? 1 : 0;
+    } catch (const nnbvh::Error &e) {
+        g_bindingError = e.what();
+        return e.code;
+    }
+    return 0;
+}
+void nnbvh_binding_bounds(void *binding, float *out6) {
+    pbrt::Bounds3f b = ((const pbrt::GPUBVHAggregate *)binding)->Bounds();
+    out6[0] = b.pMin.x, out6[1] = b.pMin.y, out6[2] = b.pMin.z;
+    out6[3] = b.pMax.x, out6[4] = b.pMax.y, out6[5] = b.pMax.z;
+}
+}  // extern "C"
+#endif  // NNBVH_WITH_BINDING

@@ -119,6 +119,11 @@ int wf_sphere_interaction(const float *sphere28, int reverseOrientation, const f
     return 0;
 }
 
+// nnbvh::SpherePhiMaxDegrees on n values
+void wf_phimax_degrees(const float *radians, int64_t n, float *degrees) {
+    for (int64_t i = 0; i < n; ++i) degrees[i] = nnbvh::SpherePhiMaxDegrees(radians[i]);
+}
+
 // The wo a triangle hit's interaction stores for the wo it is given
 void wf_interaction_wo(const float *verts9, const float *wo3, int64_t n, float *out3) {
     int idx[3] = {0, 1, 2};

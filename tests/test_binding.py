@@ -1,0 +1,73 @@
+"""tests/test_binding.py -- the reference-side binding, RUN on the reference's own primitives.
+
+oracle/_ref/libnnbvh_ref_binding.so holds the unmodified reference translation units, the driver, and
+integration/pbrt/gpubvh.h (pbrt::GPUBVHAggregate, the class a maintainer adds as the "gpubvh" accelerator) linked
+against libnnbvh.so.  The binding is constructed over the very std::vector<Primitive> -- SimplePrimitive over
+Triangle and over Sphere -- that the reference's BVHAggregate of the same scene got, and every
+ShapeIntersection it returns (tHit and the SurfaceInteraction: pi with its error interval, n, uv, dpdu/dpdv,
+dndu/dndv, the shading frame, faceIndex, wo) is compared with BVHAggregate::Intersect's, bit for bit; likewise
+IntersectP and Bounds.  This is the drop-in claim itself: same inputs, the reference's types on both sides.
+"""
+import numpy as np
+import pytest
+
+from conftest import rand_rays
+
+
+@pytest.fixture(scope="module")
+def binding():
+    from oracle import pyoracle
+    if not pyoracle.binding_available():
+        pytest.skip("oracle/_ref/libnnbvh_ref_binding.so not built (no /root/reference on this machine)")
+    return pyoracle.Binding(threads=1)
+
+
+def _scene(rng, T, S):
+    from tools.make_golden import random_spheres
+    c = rng.random((T, 1, 3), dtype=np.float32)
+    tris = ((c + np.float32(0.03) * (rng.random((T, 3, 3), dtype=np.float32) * 2 - 1)).reshape(T, 9)
+            + np.float32(0)).astype(np.float32)
+    sph = random_spheres(rng, S, scale=0.1, center_box=0.0)
+    for k in range(S):
+        m = np.eye(4)
+        m[:3] = sph[k, :12].reshape(3, 4)
+        m[:3, 3] = rng.random(3)
+        if k % 4 == 0:
+            m[:3, 0] *= -1
+        sph[k, :12] = m[:3].astype(np.float32).ravel()
+        sph[k, 12:24] = np.linalg.inv(m)[:3].astype(np.float32).ravel()
+    sph[1::3, 27] = rng.uniform(40, 350, len(sph[1::3])).astype(np.float32)       # phimax-clipped ones
+    return tris, sph
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("split", ["sah", "hlbvh"])
+def test_binding_returns_the_reference_shape_intersections(binding, split):
+    rng = np.random.default_rng(71)
+    tris, sph = _scene(rng, 6000, 50)
+    sc = binding.scene_mixed(tris, sph, 4, split)
+    b = binding.create(sc, 4, split)
+    try:
+        N = 40_000
+        rays = rand_rays(rng, N)
+        aim = rng.integers(0, len(sph), N // 2)
+        rays[:N // 2, 4:7] = sph[aim][:, [3, 7, 11]] + rng.normal(size=(N // 2, 3)).astype(np.float32) * 0.05 \
+            - rays[:N // 2, :3]
+        rays[:, 7] = rng.random(N)
+        rays[N // 2::2, 3] = rng.random(len(rays[N // 2::2])) * 1.5          # finite tMax on a quarter
+        whit, wt, w42 = binding.intersect_surface(sc, rays)                   # BVHAggregate::Intersect
+        assert 0.2 * N < whit.sum() < 0.9 * N
+        ghit, gt, g42 = binding.surface(b, rays, batch=True)                  # IntersectBatch + Resolve
+        assert np.array_equal(ghit, whit)
+        assert np.array_equal(gt.view(np.uint32)[whit], wt.view(np.uint32)[whit])
+        bad = np.argwhere(g42.view(np.uint32)[whit] != w42.view(np.uint32)[whit])
+        assert bad.size == 0, f"{len(bad)} words differ, first {bad[0]}"
+        n1 = 1500                                                             # Primitive's single-ray surface
+        shit, st, s42 = binding.surface(b, rays[:n1], batch=False)
+        assert np.array_equal(shit, whit[:n1]) and np.array_equal(s42.view(np.uint32)[shit], w42.view(np.uint32)[:n1][shit])
+        assert np.array_equal(binding.intersect_p_binding(b, rays[-n1:]),
+                              binding.intersect_p(sc, rays[-n1:], parallel=False))
+        nodes, _ = binding.export(sc, len(tris) + len(sph))
+        assert np.array_equal(binding.bounds(b).view(np.uint32), nodes[0, :6])   # BVHAggregate::Bounds = root box
+    finally:
+        binding.destroy(b)

@@ -139,6 +139,20 @@ def test_sphere_interaction_matches_reference_live(shim, reference, oracle):
         _same42(got[hit], want.view(np.uint32)[hit], f"sphere {i}")
 
 
+def test_phimax_degrees_round_trip(shim):
+    """A binding that only sees Sphere::phiMax (radians) gets back a `phimax` that the constructor maps to the
+    same float (nnbvh::SpherePhiMaxDegrees)."""
+    rng = np.random.default_rng(4)
+    deg = np.concatenate([rng.uniform(0, 360, 200_000), [0, 90, 180, 270, 359.99, 360, 1e-3, 45.5]]).astype(np.float32)
+    k = np.float32(np.float32(3.14159265358979323846) / np.float32(180))
+    rad = (k * deg).astype(np.float32)
+    out = np.zeros_like(rad)
+    shim.wf_phimax_degrees.argtypes = [ctypes.c_void_p, ctypes.c_int64, ctypes.c_void_p]
+    shim.wf_phimax_degrees.restype = None
+    shim.wf_phimax_degrees(_p(rad), rad.size, _p(out))
+    assert np.array_equal((k * np.clip(out, 0, 360)).astype(np.float32).view(np.uint32), rad.view(np.uint32))
+
+
 def _normalize_f32(v):
     """Normalize(Vector3f) (vecmath.h:948-961) in float32 steps."""
     v = np.ascontiguousarray(v, dtype=np.float32)
