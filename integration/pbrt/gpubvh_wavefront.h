@@ -11,8 +11,11 @@
 // aggregate (wavefront/integrator.cpp:157-170).
 //
 // This file is compiled against the reference's real headers -- including the SOA queue types its
-// `soac` generates -- by tests/test_integration_compile.py (type-checked: every `override` below must
-// match WavefrontAggregate's signature).  It cannot be linked here: that needs all of pbrt.
+// `soac` generates -- by tests/test_integration_compile.py, and RUN by tests/test_binding.py: inside
+// oracle/_ref/libnnbvh_ref_binding.so it is called through the WavefrontAggregate interface with the
+// reference's own RayQueue / EscapedRayQueue / ShadowRayQueue / SOA<PixelSampleState>, beside
+// CPUAggregate's loops over the reference BVHAggregate, and leaves the same queues and radiance behind.
+// (Materials are null there: the full integrator around it needs all of pbrt.)
 //
 // The primitive list, the hit -> ShapeIntersection step and the friend access that step needs live in
 // gpubvh.h (pbrt::GPUBVHAggregate); this class adds the queue plumbing.

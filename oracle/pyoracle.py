@@ -565,3 +565,29 @@ class Binding(Reference):
         out = np.zeros(6, dtype=np.float32)
         self.lib.nnbvh_binding_bounds(b, _p(out))
         return out
+
+    def wavefront_closest(self, scene, rays8, use_binding: bool, max_prims: int = 4, split: str = "sah"):
+        """One IntersectClosest over a real RayQueue -> (kind per ray: 0 escaped / 1 continued, continued rays)."""
+        rays8 = np.ascontiguousarray(rays8, dtype=np.float32)
+        n = rays8.shape[0]
+        kind = np.full(n, -2, dtype=np.int8)
+        nxt = np.zeros((n, 8), dtype=np.float32)
+        f = self.lib.nnbvh_binding_wavefront_closest
+        f.argtypes = [ctypes.c_void_p] + [ctypes.c_int] * 3 + [ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p]
+        rc = f(scene, max_prims, SPLIT[split], int(use_binding), _p(rays8), n, _p(kind), _p(nxt))
+        if rc:
+            raise RuntimeError(self.lib.nnbvh_binding_last_error().decode())
+        return kind, nxt
+
+    def wavefront_shadow(self, scene, rays8, use_binding: bool, max_prims: int = 4, split: str = "sah"):
+        """One IntersectShadow over a real ShadowRayQueue -> PixelSampleState::L[.][0] per ray."""
+        rays8 = np.ascontiguousarray(rays8, dtype=np.float32)
+        n = rays8.shape[0]
+        out = np.zeros(n, dtype=np.float32)
+        f = self.lib.nnbvh_binding_wavefront_shadow
+        f.argtypes = [ctypes.c_void_p] + [ctypes.c_int] * 3 + [ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p]
+        rc = f(scene, max_prims, SPLIT[split], int(use_binding), _p(rays8), n, _p(out))
+        if rc:
+            raise RuntimeError(self.lib.nnbvh_binding_last_error().decode())
+        return out
+

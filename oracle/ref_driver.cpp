@@ -740,6 +740,7 @@ int nnbvh_ref_stats(int64_t *nodesVisited, int64_t *triTests, int64_t *triHits) 
 // for interaction (tests/test_binding.py; needs a GPU).
 #ifdef NNBVH_WITH_BINDING
 #include "../integration/pbrt/gpubvh.h"
+#include "../integration/pbrt/gpubvh_wavefront.h"
 
 namespace {
 thread_local std::string g_bindingError;
@@ -816,6 +817,109 @@ int nnbvh_binding_intersect_p(void *binding, const float *rays, int64_t n, uint8
     }
     return 0;
 }
+// ---- the wavefront subclass, run with the reference's own queues ----
+// One IntersectClosest over a real RayQueue filled by PushCameraRay (pixelIndex = ray index), either by
+// pbrt::GPUBVHWavefrontAggregate (useBinding) or by CPUAggregate::IntersectClosest's loop
+// (wavefront/aggregate.cpp:42-57) over the reference BVHAggregate.  The scene's materials are null, so
+// every hit takes EnqueueWorkAfterIntersection's `!material` branch (wavefront/intersect.h:101-109): the
+// ray intr.SpawnRay(r.ray.d) -- pi's error bounds, n -- goes to nextRayQ; misses go to escapedRayQ.
+// kind[i]: 0 escaped, 1 continued, -1 lost; nextRays8[i] = the continued ray {o, 0, d, time}.
+int nnbvh_binding_wavefront_closest(void *scene, int maxPrimsInNode, int splitMethod, int useBinding,
+                                    const float *rays, int n, int8_t *kind, float *nextRays8) {
+    RefScene *s = (RefScene *)scene;
+    pbrt::Allocator alloc;
+    pbrt::RayQueue rayQ(n, alloc), nextQ(n, alloc);
+    pbrt::EscapedRayQueue escapedQ(n, alloc);
+    pbrt::SampledWavelengths lambda = pbrt::SampledWavelengths::SampleUniform(0.5f);
+    for (int i = 0; i < n; ++i)
+        rayQ.PushCameraRay(MakeRay(rays + 8 * (size_t)i), lambda, i);
+    try {
+        if (useBinding) {
+            pbrt::GPUBVHWavefrontAggregate agg(s->primList, maxPrimsInNode,
+                                               (pbrt::BVHAggregate::SplitMethod)splitMethod, n);
+            const pbrt::WavefrontAggregate &w = agg;  // through the reference's interface
+            w.IntersectClosest(n, &rayQ, &escapedQ, nullptr, nullptr, nullptr, nullptr, &nextQ);
+        } else {
+            pbrt::Primitive aggregate(s->agg);
+            const pbrt::RayQueue *rq = &rayQ;
+            pbrt::EscapedRayQueue *eq = &escapedQ;
+            pbrt::RayQueue *nq = &nextQ;
+            pbrt::ParallelFor(0, rayQ.Size(), [=](int index) {
+                const pbrt::RayWorkItem r = (*rq)[index];
+                pstd::optional<pbrt::ShapeIntersection> si = aggregate.Intersect(r.ray, pbrt::Infinity);
+                if (!si)
+                    pbrt::EnqueueWorkAfterMiss(r, nullptr, eq);
+                else
+                    pbrt::EnqueueWorkAfterIntersection(r, r.ray.medium, si->tHit, si->intr, nullptr, nq, nullptr,
+                                                       nullptr, nullptr);
+            });
+        }
+    } catch (const nnbvh::Error &e) {
+        g_bindingError = e.what();
+        return e.code;
+    }
+    for (int i = 0; i < n; ++i)
+        kind[i] = -1;
+    for (int j = 0; j < escapedQ.Size(); ++j)
+        kind[escapedQ.pixelIndex[j]] = 0;
+    for (int j = 0; j < nextQ.Size(); ++j) {
+        pbrt::RayWorkItem r = nextQ[j];
+        kind[r.pixelIndex] = 1;
+        float *o = nextRays8 + 8 * (size_t)r.pixelIndex;
+        o[0] = r.ray.o.x, o[1] = r.ray.o.y, o[2] = r.ray.o.z, o[3] = 0;
+        o[4] = r.ray.d.x, o[5] = r.ray.d.y, o[6] = r.ray.d.z, o[7] = r.ray.time;
+    }
+    return 0;
+}
+
+// One IntersectShadow over a real ShadowRayQueue: the radiance RecordShadowRayResult (wavefront/intersect.h:31-46)
+// leaves in SOA<PixelSampleState>::L, first wavelength, per ray (Ld = i % 7 + 1 on the way in).
+int nnbvh_binding_wavefront_shadow(void *scene, int maxPrimsInNode, int splitMethod, int useBinding,
+                                   const float *rays, int n, float *L0) {
+    RefScene *s = (RefScene *)scene;
+    pbrt::Allocator alloc;
+    pbrt::ShadowRayQueue shadowQ(n, alloc);
+    pbrt::SOA<pbrt::PixelSampleState> pss(n, alloc);
+    pbrt::SampledWavelengths lambda = pbrt::SampledWavelengths::SampleUniform(0.5f);
+    for (int i = 0; i < n; ++i) {
+        const float *r = rays + 8 * (size_t)i;
+        pbrt::ShadowRayWorkItem w;
+        w.ray = MakeRay(r);
+        w.tMax = r[3];
+        w.lambda = lambda;
+        w.Ld = pbrt::SampledSpectrum(float(i % 7 + 1));
+        w.r_u = w.r_l = pbrt::SampledSpectrum(1.f);
+        w.pixelIndex = i;
+        shadowQ.Push(w);
+        pss.L[i] = pbrt::SampledSpectrum(0.f);
+    }
+    try {
+        if (useBinding) {
+            pbrt::GPUBVHWavefrontAggregate agg(s->primList, maxPrimsInNode,
+                                               (pbrt::BVHAggregate::SplitMethod)splitMethod, n);
+            const pbrt::WavefrontAggregate &w = agg;
+            w.IntersectShadow(n, &shadowQ, &pss);
+        } else {
+            pbrt::Primitive aggregate(s->agg);
+            pbrt::ShadowRayQueue *sq = &shadowQ;
+            pbrt::SOA<pbrt::PixelSampleState> *ps = &pss;
+            pbrt::ParallelFor(0, shadowQ.Size(), [=](int index) {  // aggregate.cpp:63-67
+                const pbrt::ShadowRayWorkItem w = (*sq)[index];
+                bool hit = aggregate.IntersectP(w.ray, w.tMax);
+                pbrt::RecordShadowRayResult(w, ps, hit);
+            });
+        }
+    } catch (const nnbvh::Error &e) {
+        g_bindingError = e.what();
+        return e.code;
+    }
+    for (int i = 0; i < n; ++i) {
+        pbrt::SampledSpectrum L = pss.L[i];
+        L0[i] = L[0];
+    }
+    return 0;
+}
+
 void nnbvh_binding_bounds(void *binding, float *out6) {
     pbrt::Bounds3f b = ((const pbrt::GPUBVHAggregate *)binding)->Bounds();
     out6[0] = b.pMin.x, out6[1] = b.pMin.y, out6[2] = b.pMin.z;

@@ -71,3 +71,30 @@ def test_binding_returns_the_reference_shape_intersections(binding, split):
         assert np.array_equal(binding.bounds(b).view(np.uint32), nodes[0, :6])   # BVHAggregate::Bounds = root box
     finally:
         binding.destroy(b)
+
+
+@pytest.mark.gpu
+def test_wavefront_subclass_runs_on_the_reference_queues(binding):
+    """pbrt::GPUBVHWavefrontAggregate (integration/pbrt/gpubvh_wavefront.h) called through the reference's
+    WavefrontAggregate interface with the reference's own RayQueue / EscapedRayQueue / ShadowRayQueue /
+    SOA<PixelSampleState>, beside CPUAggregate's loops (wavefront/aggregate.cpp:42-67) over the reference
+    BVHAggregate on the same queues.  What the reference's consumers leave behind must be identical: which
+    rays escaped, the ray EnqueueWorkAfterIntersection spawned for every hit (intr.SpawnRay: pi's error
+    bounds and n), and the radiance RecordShadowRayResult added per pixel."""
+    rng = np.random.default_rng(5)
+    T, N = 8000, 50_000
+    c = rng.random((T, 1, 3), dtype=np.float32)
+    tris = ((c + np.float32(0.03) * (rng.random((T, 3, 3), dtype=np.float32) * 2 - 1)).reshape(T, 9)
+            + np.float32(0)).astype(np.float32)
+    sc = binding.scene(tris, 4, "sah")
+    rays = rand_rays(rng, N)
+    rays[:, 7] = rng.random(N)
+    want_kind, want_next = binding.wavefront_closest(sc, rays, use_binding=False)
+    assert set(np.unique(want_kind)) == {0, 1} and 0.1 * N < (want_kind == 1).sum() < 0.6 * N
+    kind, nxt = binding.wavefront_closest(sc, rays, use_binding=True)
+    assert np.array_equal(kind, want_kind)
+    assert np.array_equal(nxt.view(np.uint32)[kind == 1], want_next.view(np.uint32)[kind == 1])
+    rays[N // 2:, 3] = rng.random(N - N // 2)
+    want_L = binding.wavefront_shadow(sc, rays, use_binding=False)
+    assert 0.05 * N < (want_L == 0).sum() < 0.6 * N
+    assert np.array_equal(binding.wavefront_shadow(sc, rays, use_binding=True), want_L)
