@@ -81,6 +81,20 @@ struct Sink {
     }
     void RecordShadowRayResult(int i, bool found) { shadow[i] = found, ++calls; }
 };
+// A triangle soup (9 floats per triangle) as an indexed mesh without normals / uv
+Mesh SoupMesh(const float *tris9, int nTris) {
+    std::vector<int> idx(3 * (size_t)nTris);
+    for (size_t i = 0; i < idx.size(); ++i) idx[i] = (int)i;
+    return MakeMesh(tris9, 3 * nTris, idx.data(), nTris, nullptr, nullptr, nullptr);
+}
+
+nnbvh_instance MakeInstance(const float *m24, int object) {
+    nnbvh_instance in{};
+    std::memcpy(in.renderFromPrimitive, m24, 48);
+    std::memcpy(in.primitiveFromRender, m24 + 12, 48);
+    in.object = (uint32_t)object;
+    return in;
+}
 }  // namespace
 
 extern "C" {
@@ -175,21 +189,6 @@ void *wf_create_mixed(const float *verts, int nVerts, const int *indices, int nT
         g_what = e.what();
         return nullptr;
     }
-}
-
-// A triangle soup (9 floats per triangle) as an indexed mesh without normals / uv
-Mesh SoupMesh(const float *tris9, int nTris) {
-    std::vector<int> idx(3 * (size_t)nTris);
-    for (size_t i = 0; i < idx.size(); ++i) idx[i] = (int)i;
-    return MakeMesh(tris9, 3 * nTris, idx.data(), nTris, nullptr, nullptr, nullptr);
-}
-
-nnbvh_instance MakeInstance(const float *m24, int object) {
-    nnbvh_instance in{};
-    std::memcpy(in.renderFromPrimitive, m24, 48);
-    std::memcpy(in.primitiveFromRender, m24 + 12, 48);
-    in.object = (uint32_t)object;
-    return in;
 }
 
 // TransformedPrimitive::Intersect's interaction on the host: query i hits triangle tri[i] of the object's
