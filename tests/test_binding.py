@@ -98,3 +98,27 @@ def test_wavefront_subclass_runs_on_the_reference_queues(binding):
     want_L = binding.wavefront_shadow(sc, rays, use_binding=False)
     assert 0.05 * N < (want_L == 0).sum() < 0.6 * N
     assert np.array_equal(binding.wavefront_shadow(sc, rays, use_binding=True), want_L)
+
+
+def test_reference_loops_over_reference_queues_are_consistent(binding):
+    """The checker's half of the test above, without a GPU: CPUAggregate's loops over real queues agree with the
+    reference's per-ray answers (escaped <=> no hit, the continued ray keeps d / time and starts on the surface,
+    an unoccluded shadow ray adds Ld / 2)."""
+    rng = np.random.default_rng(15)
+    T, N = 3000, 20_000
+    c = rng.random((T, 1, 3), dtype=np.float32)
+    tris = ((c + np.float32(0.04) * (rng.random((T, 3, 3), dtype=np.float32) * 2 - 1)).reshape(T, 9)
+            + np.float32(0)).astype(np.float32)
+    sc = binding.scene(tris, 4, "sah")
+    rays = rand_rays(rng, N)
+    rays[:, 7] = rng.random(N)
+    kind, nxt = binding.wavefront_closest(sc, rays, use_binding=False)
+    hit, _, s42 = binding.intersect_surface(sc, rays)
+    assert np.array_equal(kind == 1, hit) and np.array_equal(kind == 0, ~hit) and hit.sum() > 2000
+    assert np.array_equal(nxt[hit][:, 4:8], rays[hit][:, 4:8])
+    p = (s42[:, 0:3] + s42[:, 3:6]) / 2
+    assert np.abs(nxt[hit, :3] - p[hit]).max() < 1e-5
+    rays[N // 2:, 3] = rng.random(N - N // 2)
+    L = binding.wavefront_shadow(sc, rays, use_binding=False)
+    occ = binding.intersect_p(sc, rays, parallel=False)
+    assert np.array_equal(L, np.where(occ != 0, 0, (np.arange(N) % 7 + 1) / 2).astype(np.float32))
