@@ -13,7 +13,9 @@
 //    the ordered primitive list is the final permutation of the array: no
 //    shared counter is needed, and disjoint spans can be built by different
 //    threads with a bit-identical result (the reference's own parallel build is
-//    NOT deterministic, :359-370).
+//    NOT deterministic, :359-370).  Large children are forked while threads are
+//    spare; a large span's own passes run on a Team (below) with results that
+//    equal the serial ones bit for bit.
 //  * Nodes are emitted straight into pre-order position: a subtree over n
 //    primitives gets a private slab of 2n-1 slots, is built there in pre-order,
 //    and slabs are compacted afterwards (offsets fixed up) -- no pointer tree.
@@ -81,6 +83,7 @@ struct Item {  // BVHPrimitive, aggregates.cpp:91-100
 };
 
 constexpr int kBuckets = 12;
+constexpr size_t kForkMin = 32 * 1024;  // smallest span worth a thread of its own
 
 inline int BucketOf(const Aabb &cb, const Item &it, int dim) {
     int b = kBuckets * cb.Rel(it.Mid(dim), dim);
@@ -93,6 +96,7 @@ struct Ctx {
     int maxLeaf;
     int split;
     std::atomic<bool> *overflow;
+    std::atomic<int> *spare;  // threads that may still be started (nThreads - 1 at the beginning)
 };
 
 void WriteBox(nnbvh_node &nd, const Aabb &b) {
@@ -102,16 +106,120 @@ void WriteBox(nnbvh_node &nd, const Aabb &b) {
     }
 }
 
+// ---- several threads on ONE large span ----------------------------------------------------------------
+// Near the root a span is too large to leave to one thread (and SAH's first splits are often lopsided, so
+// forking the children does not help yet).  Its passes are reductions whose serial results can be
+// reproduced exactly from per-chunk partial results combined in chunk order: std::min / std::max keep the
+// LEFTMOST of equal values (that covers -0 / +0) and never take a NaN, which is associative; counts are
+// integers.  The partition is libstdc++'s two-pointer scheme (bits/stl_algo.h __partition, bidirectional):
+// with m = the number of elements satisfying the predicate, the i-th failing element of [0, m) from the left
+// is exchanged with the i-th satisfying element of [m, n) from the right -- positions that can be listed
+// per chunk and exchanged independently.  So the permutation, hence the tree, stays bit-identical.
+class Team {
+  public:
+    Team(const Ctx &c, int want) : c_(c) {
+        while (want > 0) {
+            int cur = c.spare->load();
+            int take = std::min(cur, want);
+            if (take <= 0) break;
+            if (c.spare->compare_exchange_weak(cur, cur - take)) {
+                extra_ = take;
+                break;
+            }
+        }
+    }
+    ~Team() { Release(); }
+    void Release() {
+        if (extra_) c_.spare->fetch_add(extra_);
+        extra_ = 0;
+    }
+    int Size() const { return extra_ + 1; }
+    template <typename F>
+    void Run(F body) const {  // body(t) for t in [0, Size())
+        std::vector<std::thread> th;
+        for (int t = 1; t <= extra_; ++t) th.emplace_back([&body, t] { body(t); });
+        body(0);
+        for (std::thread &x : th) x.join();
+    }
+
+  private:
+    const Ctx &c_;
+    int extra_ = 0;
+};
+constexpr size_t kTeamMin = 128 * 1024;  // smallest span that gets a team
+
+inline void Chunk(size_t n, int t, int T, size_t *b, size_t *e) {
+    *b = n * (size_t)t / (size_t)T;
+    *e = n * (size_t)(t + 1) / (size_t)T;
+}
+
+// Union of the boxes and of the centroids of a[0..n)
+void TeamBounds(const Team &team, const Item *a, size_t n, Aabb *bounds, Aabb *cb) {
+    const int T = team.Size();
+    std::vector<Aabb> pb(T), pc(T);
+    team.Run([&](int t) {
+        size_t b, e;
+        Chunk(n, t, T, &b, &e);
+        Aabb bb, cc;
+        for (size_t i = b; i < e; ++i) {
+            bb.Grow(a[i].box);
+            float m[3] = {a[i].Mid(0), a[i].Mid(1), a[i].Mid(2)};
+            cc.Grow(m);
+        }
+        pb[t] = bb, pc[t] = cc;
+    });
+    for (int t = 0; t < T; ++t) bounds->Grow(pb[t]), cb->Grow(pc[t]);
+}
+
+// std::partition(a, a + n, pred) with the same resulting permutation; returns the partition point.
+template <typename Pred>
+size_t TeamPartition(const Team &team, Item *a, size_t n, Pred pred) {
+    const int T = team.Size();
+    std::vector<uint8_t> flag(n);
+    std::vector<size_t> cnt(T);
+    team.Run([&](int t) {
+        size_t b, e, k = 0;
+        Chunk(n, t, T, &b, &e);
+        for (size_t i = b; i < e; ++i) k += (flag[i] = pred(a[i]) ? 1 : 0);
+        cnt[t] = k;
+    });
+    size_t m = 0;
+    for (int t = 0; t < T; ++t) m += cnt[t];
+    std::vector<std::vector<uint32_t>> fl(T), tr(T);  // failing in [0, m), satisfying in [m, n): ascending
+    team.Run([&](int t) {
+        size_t b, e;
+        Chunk(n, t, T, &b, &e);
+        for (size_t i = b; i < std::min(e, m); ++i)
+            if (!flag[i]) fl[t].push_back((uint32_t)i);
+        for (size_t i = std::max(b, m); i < e; ++i)
+            if (flag[i]) tr[t].push_back((uint32_t)i);
+    });
+    std::vector<size_t> fo(T + 1, 0), to(T + 1, 0);
+    for (int t = 0; t < T; ++t) fo[t + 1] = fo[t] + fl[t].size(), to[t + 1] = to[t] + tr[t].size();
+    const size_t k = fo[T];  // == to[T]
+    std::vector<uint32_t> R(k);
+    team.Run([&](int t) { std::copy(tr[t].begin(), tr[t].end(), R.begin() + to[t]); });
+    team.Run([&](int t) {  // the i-th failing element from the left <-> the i-th satisfying one from the right
+        for (size_t j = 0; j < fl[t].size(); ++j) std::swap(a[fl[t][j]], a[R[k - 1 - (fo[t] + j)]]);
+    });
+    return m;
+}
+
 // Chooses the split of span [s, s+n) exactly as buildRecursive does and
-// permutes it; returns mid (0 => make a leaf).
-size_t SplitSpan(const Ctx &c, size_t s, size_t n, const Aabb &bounds, int *axisOut) {
+// permutes it; returns mid (0 => make a leaf).  team / cbPre: several threads on this span, with the
+// centroid bounds already known.
+size_t SplitSpan(const Ctx &c, size_t s, size_t n, const Aabb &bounds, int *axisOut, const Team *team = nullptr,
+                 const Aabb *cbPre = nullptr) {
     Item *a = c.items + s;
     if (bounds.Area() == 0 || n == 1) return 0;  // :205
     Aabb cb;
-    for (size_t i = 0; i < n; ++i) {
-        float m[3] = {a[i].Mid(0), a[i].Mid(1), a[i].Mid(2)};
-        cb.Grow(m);
-    }
+    if (cbPre)
+        cb = *cbPre;
+    else
+        for (size_t i = 0; i < n; ++i) {
+            float m[3] = {a[i].Mid(0), a[i].Mid(1), a[i].Mid(2)};
+            cb.Grow(m);
+        }
     int dim = cb.WidestAxis();
     *axisOut = dim;
     if (cb.hi[dim] == cb.lo[dim]) return 0;  // :225
@@ -123,7 +231,8 @@ size_t SplitSpan(const Ctx &c, size_t s, size_t n, const Aabb &bounds, int *axis
     if (c.split == NNBVH_SPLIT_EQUAL_COUNTS) return median();
     if (c.split == NNBVH_SPLIT_MIDDLE) {  // :240-253, falls through to EqualCounts
         float pmid = (cb.lo[dim] + cb.hi[dim]) / 2;
-        Item *m = std::partition(a, a + n, [=](const Item &x) { return x.Mid(dim) < pmid; });
+        auto below = [=](const Item &x) { return x.Mid(dim) < pmid; };
+        Item *m = team ? a + TeamPartition(*team, a, n, below) : std::partition(a, a + n, below);
         if (m != a && m != a + n) return size_t(m - a);
         return median();
     }
@@ -131,11 +240,32 @@ size_t SplitSpan(const Ctx &c, size_t s, size_t n, const Aabb &bounds, int *axis
     if (n <= 2) return median();
     int count[kBuckets] = {};
     Aabb bb[kBuckets];
-    for (size_t i = 0; i < n; ++i) {
-        int b = BucketOf(cb, a[i], dim);
-        ++count[b];
-        bb[b].Grow(a[i].box);
-    }
+    if (team) {
+        const int T = team->Size();
+        struct Part {
+            int count[kBuckets] = {};
+            Aabb bb[kBuckets];
+        };
+        std::vector<Part> part(T);
+        team->Run([&](int t) {
+            size_t b0, e0;
+            Chunk(n, t, T, &b0, &e0);
+            Part p;
+            for (size_t i = b0; i < e0; ++i) {
+                int b = BucketOf(cb, a[i], dim);
+                ++p.count[b];
+                p.bb[b].Grow(a[i].box);
+            }
+            part[t] = p;
+        });
+        for (int t = 0; t < T; ++t)
+            for (int b = 0; b < kBuckets; ++b) count[b] += part[t].count[b], bb[b].Grow(part[t].bb[b]);
+    } else
+        for (size_t i = 0; i < n; ++i) {
+            int b = BucketOf(cb, a[i], dim);
+            ++count[b];
+            bb[b].Grow(a[i].box);
+        }
     float cost[kBuckets - 1] = {};
     {
         int below = 0;
@@ -163,7 +293,8 @@ size_t SplitSpan(const Ctx &c, size_t s, size_t n, const Aabb &bounds, int *axis
     float leafCost = n;
     bestCost = 1.f / 2.f + bestCost / bounds.Area();
     if (n > (size_t)c.maxLeaf || bestCost < leafCost) {
-        Item *m = std::partition(a, a + n, [&](const Item &x) { return BucketOf(cb, x, dim) <= best; });
+        auto inLeft = [&](const Item &x) { return BucketOf(cb, x, dim) <= best; };
+        Item *m = team ? a + TeamPartition(*team, a, n, inLeft) : std::partition(a, a + n, inLeft);
         return size_t(m - a);
     }
     return 0;
@@ -171,14 +302,24 @@ size_t SplitSpan(const Ctx &c, size_t s, size_t n, const Aabb &bounds, int *axis
 
 // Builds the subtree over span [s, s+n) in pre-order into c.slab starting at
 // slot `at`; returns the number of nodes written.  Offsets are slab-absolute.
-// `par` = remaining levels at which children may run on a fresh thread.
-uint32_t BuildSpan(const Ctx &c, size_t s, size_t n, uint32_t at, int par) {
+// `par`: children of this span may run on a fresh thread (while c.spare lasts).
+uint32_t BuildSpan(const Ctx &c, size_t s, size_t n, uint32_t at, bool par) {
     nnbvh_node &nd = c.slab[at];
     std::memset(&nd, 0, sizeof(nd));
     Aabb bounds;
-    for (size_t i = 0; i < n; ++i) bounds.Grow(c.items[s + i].box);
     int axis = 0;
-    size_t mid = SplitSpan(c, s, n, bounds, &axis);
+    size_t mid;
+    {
+        Team team(c, par && n >= kTeamMin ? 63 : 0);  // whatever is spare right now
+        if (team.Size() > 1) {
+            Aabb cb;
+            TeamBounds(team, c.items + s, n, &bounds, &cb);
+            mid = SplitSpan(c, s, n, bounds, &axis, &team, &cb);
+        } else {
+            for (size_t i = 0; i < n; ++i) bounds.Grow(c.items[s + i].box);
+            mid = SplitSpan(c, s, n, bounds, &axis);
+        }
+    }  // the slots go back before the children start
     if (mid == 0) {
         // SplitSpan returns 0 only for "make a leaf": the median split has
         // mid >= 1, Middle guards it, and a SAH partition with an empty side
@@ -190,13 +331,19 @@ uint32_t BuildSpan(const Ctx &c, size_t s, size_t n, uint32_t at, int par) {
         return 1;
     }
     uint32_t nl, nr;
-    if (par > 0 && n > 64 * 1024) {
+    // A fork pays only when BOTH children are large: SAH splits near the root are often lopsided (a few
+    // thousand primitives against the rest), and then the large child simply keeps the whole thread budget.
+    const bool bigL = mid > kForkMin, bigR = n - mid > kForkMin;
+    if (par && bigL && bigR && c.spare->fetch_sub(1) > 0) {
         // Right child into a private region sized for the worst case, moved
         // down next to the left subtree afterwards.
         uint32_t rightAt = at + 1 + (uint32_t)(2 * mid - 1);
         uint32_t nrT = 0;
-        std::thread t([&] { nrT = BuildSpan(c, s + mid, n - mid, rightAt, par - 1); });
-        nl = BuildSpan(c, s, mid, at + 1, par - 1);
+        std::thread t([&] {
+            nrT = BuildSpan(c, s + mid, n - mid, rightAt, true);
+            c.spare->fetch_add(1);  // the slot is free again as soon as this subtree is done
+        });
+        nl = BuildSpan(c, s, mid, at + 1, true);
         t.join();
         nr = nrT;
         uint32_t dst = at + 1 + nl;
@@ -207,8 +354,9 @@ uint32_t BuildSpan(const Ctx &c, size_t s, size_t n, uint32_t at, int par) {
                 if (c.slab[i].nPrimitives == 0) c.slab[i].offset -= shift;
         }
     } else {
-        nl = BuildSpan(c, s, mid, at + 1, 0);
-        nr = BuildSpan(c, s + mid, n - mid, at + 1 + nl, 0);
+        if (par && bigL && bigR) c.spare->fetch_add(1);  // no slot was free: undo the probe
+        nl = BuildSpan(c, s, mid, at + 1, par && bigL);
+        nr = BuildSpan(c, s + mid, n - mid, at + 1 + nl, par && bigR);
     }
     // InitInterior, :113-120: bounds = Union(c0, c1)
     const nnbvh_node &L = c.slab[at + 1], &R = c.slab[at + 1 + nl];
@@ -447,9 +595,9 @@ static int BuildFromBoxes(const std::vector<float> &box, uint32_t nPrims, int32_
     std::atomic<bool> overflow{false};
     c.overflow = &overflow;
     int nt = nThreads > 0 ? nThreads : (int)std::thread::hardware_concurrency();
-    int par = 0;
-    while ((1 << par) < nt) ++par;
-    uint32_t total = BuildSpan(c, 0, nPrims, 0, par);
+    std::atomic<int> spare{std::max(0, nt - 1)};
+    c.spare = &spare;
+    uint32_t total = BuildSpan(c, 0, nPrims, 0, nt > 1);
     if (overflow.load())
         return SetError(NNBVH_ERR_INVALID, "nnbvh_build_bvh: a leaf holds >= 65536 primitives "
                                            "(the reference CHECKs nPrimitives < 65536)");

@@ -256,6 +256,13 @@ class Reference:
         h = self.lib.nnbvh_ref_scene_create(_p(verts), 3 * T, _p(idx), T, max_prims, SPLIT[split])
         return ctypes.c_void_p(h)
 
+    def build_seconds(self, scene) -> float:
+        """Wall time of the BVHAggregate constructor that made this scene."""
+        f = self.lib.nnbvh_ref_scene_build_seconds
+        f.restype = ctypes.c_double
+        f.argtypes = [ctypes.c_void_p]
+        return f(scene)
+
     def scene_mixed(self, tris9, spheres28, max_prims: int = 4, split: str = "sah"):
         """BVHAggregate over [triangles..., spheres...] (SimplePrimitive each)."""
         tris9 = np.ascontiguousarray(tris9, dtype=np.float32).reshape(-1, 9)

@@ -18,6 +18,7 @@
 
 #include <algorithm>
 #include <atomic>
+#include <chrono>
 #include <cstdint>
 #include <cstdio>
 #include <cstdlib>
@@ -114,6 +115,7 @@ struct RefScene {
     pbrt::TriangleMesh *mesh = nullptr;
     pbrt::BVHAggregate *agg = nullptr;
     std::vector<pbrt::Primitive> primList;  // the list BVHAggregate was given, in the caller's order
+    double buildSeconds = 0;                // wall time of the BVHAggregate constructor alone
     int nTris = 0;
     int nNodes = 0;
     std::vector<int> orderedToOrig;  // ordered prim index -> original triangle
@@ -222,8 +224,10 @@ void *nnbvh_ref_scene_create_mixed(const float *verts, int nVerts, const int *in
     s->nTris = nTris;
     const int nPrims = nTris + nSpheres;
     s->primList = prims;
+    auto t0 = std::chrono::steady_clock::now();
     s->agg = new pbrt::BVHAggregate(std::move(prims), maxPrimsInNode,
                                     (pbrt::BVHAggregate::SplitMethod)splitMethod);
+    s->buildSeconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
     s->nNodes = CountNodes(reinterpret_cast<const NodeMirror *>(s->agg->nodes));
     s->orderedToOrig.resize(nPrims);
     s->origToOrdered.resize(nPrims);
@@ -237,6 +241,10 @@ void *nnbvh_ref_scene_create_mixed(const float *verts, int nVerts, const int *in
     return s;
 }
 
+// Wall time of BVHAggregate::BVHAggregate (build + flatten) for this scene, seconds.
+double nnbvh_ref_scene_build_seconds(void *scene) {
+    return ((RefScene *)scene)->buildSeconds;
+}
 int nnbvh_ref_scene_num_nodes(void *scene) {
     return ((RefScene *)scene)->nNodes;
 }

@@ -51,6 +51,25 @@ def test_host_builder_matches_oracle_and_threads(oracle):
     assert nb.tree_stack_depth(n1) <= 64
 
 
+@pytest.mark.parametrize("split", ["sah", "middle", "equal"])
+def test_host_builder_teams_and_forks_are_deterministic(oracle, split):
+    """Large spans are worked on by several threads (chunked reductions, the two-pointer partition replayed from
+    per-chunk position lists) and large children are forked: the tree must not depend on the thread count.
+    The soup is lopsided (a dense cluster in a sparse room) and full of -0.0 / +0.0 coordinates, whose order
+    decides which zero std::min keeps."""
+    import nn_bvh_b200 as nb
+    rng = np.random.default_rng(17)
+    tris = np.concatenate([soup(rng, 150_000, 0.002) * np.float32(0.05), soup(rng, 150_000, 0.02)]).astype(np.float32)
+    tris[rng.random(tris.shape) < 0.02] = 0.0
+    tris[rng.random(tris.shape) < 0.02] = -0.0
+    tris = tris[rng.permutation(len(tris))]
+    on, oo = oracle.build_bvh(tris, 4, split)
+    for threads in (1, 3, 8):
+        n, o = nb.build_bvh(tris, 4, split, threads=threads)
+        assert np.array_equal(n.view(np.uint32).reshape(-1, 8), on), threads
+        assert np.array_equal(o, oo.astype(np.uint32)), threads
+
+
 def test_builder_edge_cases():
     import nn_bvh_b200 as nb
     one = np.array([[0, 0, 0, 1, 0, 0, 0, 1, 0]], np.float32)
