@@ -53,6 +53,7 @@ class GPUBVHWavefrontAggregate : public WavefrontAggregate {
         const int n = rayQ->Size();
         if (n == 0)
             return;
+        CHECK_LE((size_t)n, hits.size());  // the queues are allocated for maxQueueSize
         // SOA<RayWorkItem> keeps ray.o.x[], ray.o.y[] ... as separate float arrays: no repack
         host.Engine().IntersectBatchSoA(rayQ->ray.o.x, rayQ->ray.o.y, rayQ->ray.o.z, rayQ->ray.d.x, rayQ->ray.d.y,
                                rayQ->ray.d.z, /*tMax=*/nullptr, (uint64_t)n, hits.data());
@@ -75,6 +76,7 @@ class GPUBVHWavefrontAggregate : public WavefrontAggregate {
         const int n = shadowRayQueue->Size();
         if (n == 0)
             return;
+        CHECK_LE((size_t)n, occluded.size());
         const ShadowRayQueue *q = shadowRayQueue;
         host.Engine().IntersectPBatchSoA(q->ray.o.x, q->ray.o.y, q->ray.o.z, q->ray.d.x, q->ray.d.y, q->ray.d.z, q->tMax,
                                 (uint64_t)n, occluded.data());
