@@ -564,6 +564,16 @@ int BuildHLBVHHost(const std::vector<float> &box, uint32_t nTris, int maxLeaf, i
 
 using namespace nnbvh;
 
+// body(begin, end) over [0, n) on up to nt threads (independent elements: no ordering involved)
+template <typename F>
+static void ForRanges(size_t n, int nt, F body) {
+    nt = (int)std::min<size_t>(std::max(1, std::min(nt, 64)), n / (64 * 1024) + 1);
+    std::vector<std::thread> th;
+    for (int t = 1; t < nt; ++t) th.emplace_back([=] { body(n * (size_t)t / nt, n * (size_t)(t + 1) / nt); });
+    body(0, n / nt);
+    for (std::thread &x : th) x.join();
+}
+
 static int BuildFromBoxes(const std::vector<float> &box, uint32_t nPrims, int32_t maxPrimsInNode,
                           int32_t splitMethod, int32_t nThreads, nnbvh_node *nodesOut,
                           uint32_t *nNodesOut, uint32_t *orderOut) {
@@ -576,17 +586,20 @@ static int BuildFromBoxes(const std::vector<float> &box, uint32_t nPrims, int32_
         return BuildHLBVHHost(box, nPrims, std::min(255, (int)maxPrimsInNode), nt, nodesOut,
                               nNodesOut, orderOut);
     }
+    const int nt = nThreads > 0 ? nThreads : (int)std::thread::hardware_concurrency();
     std::vector<Item> items(nPrims);
-    for (uint32_t i = 0; i < nPrims; ++i) {
-        const float *b6 = &box[6 * (size_t)i];
-        Aabb b;
-        for (int k = 0; k < 3; ++k) {
-            b.lo[k] = b6[k];
-            b.hi[k] = b6[3 + k];
+    ForRanges(nPrims, nt, [&](size_t b0, size_t e0) {
+        for (size_t i = b0; i < e0; ++i) {
+            const float *b6 = &box[6 * i];
+            Aabb b;
+            for (int k = 0; k < 3; ++k) {
+                b.lo[k] = b6[k];
+                b.hi[k] = b6[3 + k];
+            }
+            items[i].index = i;
+            items[i].box = b;
         }
-        items[i].index = i;
-        items[i].box = b;
-    }
+    });
     Ctx c;
     c.items = items.data();
     c.slab = nodesOut;
@@ -594,7 +607,6 @@ static int BuildFromBoxes(const std::vector<float> &box, uint32_t nPrims, int32_
     c.split = splitMethod;
     std::atomic<bool> overflow{false};
     c.overflow = &overflow;
-    int nt = nThreads > 0 ? nThreads : (int)std::thread::hardware_concurrency();
     std::atomic<int> spare{std::max(0, nt - 1)};
     c.spare = &spare;
     uint32_t total = BuildSpan(c, 0, nPrims, 0, nt > 1);
@@ -615,7 +627,9 @@ extern "C" int nnbvh_build_bvh(const float *triVerts9, uint32_t nTris, int32_t m
     if (nTris > (1u << 30))
         return SetError(NNBVH_ERR_INVALID, "nnbvh_build_bvh: too many triangles");
     std::vector<float> box(6 * (size_t)nTris);
-    for (uint32_t i = 0; i < nTris; ++i) TriBox(triVerts9 + 9 * (size_t)i, &box[6 * (size_t)i]);
+    ForRanges(nTris, nThreads > 0 ? nThreads : (int)std::thread::hardware_concurrency(), [&](size_t b0, size_t e0) {
+        for (size_t i = b0; i < e0; ++i) TriBox(triVerts9 + 9 * i, &box[6 * i]);
+    });
     return BuildFromBoxes(box, nTris, maxPrimsInNode, splitMethod, nThreads, nodesOut, nNodesOut, orderOut);
 }
 
