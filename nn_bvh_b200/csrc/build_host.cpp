@@ -310,7 +310,7 @@ uint32_t BuildSpan(const Ctx &c, size_t s, size_t n, uint32_t at, bool par) {
     int axis = 0;
     size_t mid;
     {
-        Team team(c, par && n >= kTeamMin ? 63 : 0);  // whatever is spare right now
+        Team team(c, par && n >= kTeamMin ? 15 : 0);  // what is spare right now (the passes are memory-bound)
         if (team.Size() > 1) {
             Aabb cb;
             TeamBounds(team, c.items + s, n, &bounds, &cb);
