@@ -814,6 +814,109 @@ inline void SphereBounds(const float *s28, float *out6) {
         out6[k] = bt.mn[k], out6[3 + k] = bt.mx[k];
 }
 
+// ---- GeometricPrimitive with an alpha texture (cpu/primitive.cpp:50-84) ------------------------------
+// Only constant alpha values are restated (FloatConstantTexture, textures.h:269-283): image and procedural
+// textures are outside this path.
+// MurmurHash64A, util/hash.h:19-70 (the tail switch is unused here: 24 bytes)
+inline uint64_t MurmurHash64A(const unsigned char *key, size_t len, uint64_t seed) {
+    const uint64_t m = 0xc6a4a7935bd1e995ull;
+    const int r = 47;
+    uint64_t h = seed ^ (len * m);
+    const unsigned char *end = key + 8 * (len / 8);
+    while (key != end) {
+        uint64_t k;
+        std::memcpy(&k, key, sizeof(uint64_t));
+        key += 8;
+        k *= m;
+        k ^= k >> r;
+        k *= m;
+        h ^= k;
+        h *= m;
+    }
+    h ^= h >> r;
+    h *= m;
+    h ^= h >> r;
+    return h;
+}
+// HashFloat(r.o, r.d), util/hash.h:98-112: Point3f and Vector3f copied back to back, seed 0
+inline float HashFloatOD(const float *o, const float *d) {
+    uint64_t buf[3];
+    std::memcpy((char *)buf, o, 12);
+    std::memcpy((char *)buf + 12, d, 12);
+    return uint32_t(MurmurHash64A((const unsigned char *)buf, 24, 0)) * 0x1p-32f;
+}
+// The origin of si->intr.SpawnRay(r.d) for a hit (b0,b1,b2) on triangle p (no shading normals):
+// Triangle::InteractionFromIntersection's pHit / pError / n (shapes.h:924-941), Point3fi(pHit, pError)
+// (util/math.h:829-838), OffsetRayOrigin (ray.h:75-92).  The orientation of n does not matter: Abs(n)
+// scales the offset and Dot(w, n) < 0 flips it back.
+inline void SpawnOrigin(const float *p, float b0, float b1, float b2, const float *w, float *po) {
+    const float *p0 = p, *p1 = p + 3, *p2 = p + 6;
+    float dp02[3], dp12[3];
+    for (int k = 0; k < 3; ++k)
+        dp02[k] = p0[k] - p2[k], dp12[k] = p1[k] - p2[k];
+    float n[3] = {DifferenceOfProducts(dp02[1], dp12[2], dp02[2], dp12[1]),
+                  DifferenceOfProducts(dp02[2], dp12[0], dp02[0], dp12[2]),
+                  DifferenceOfProducts(dp02[0], dp12[1], dp02[1], dp12[0])};
+    float len = std::sqrt(n[0] * n[0] + n[1] * n[1] + n[2] * n[2]);
+    for (int k = 0; k < 3; ++k)
+        n[k] = n[k] / len;
+    const float g7 = Gamma(7);
+    float mid[3], err[3];
+    for (int k = 0; k < 3; ++k) {
+        float pHit = b0 * p0[k] + b1 * p1[k] + b2 * p2[k];
+        float pErr = g7 * (std::abs(b0 * p0[k]) + std::abs(b1 * p1[k]) + std::abs(b2 * p2[k]));
+        Interval pi = Interval::FromValueAndError(pHit, pErr);
+        mid[k] = pi.Midpoint();           // Point3f(pi)
+        err[k] = (pi.high - pi.low) / 2;  // pi.Error()
+    }
+    auto sumOfProducts = [](float a, float b, float c, float d) {  // util/math.h:577-583
+        float cd = c * d;
+        float sum = std::fma(a, b, cd);
+        float error = std::fma(c, d, -cd);
+        return sum + error;
+    };
+    // Dot(Normal3f, Vector3f), vecmath.h:1057-1069
+    float d = std::fma(std::abs(n[0]), err[0], sumOfProducts(std::abs(n[1]), err[1], std::abs(n[2]), err[2]));
+    float offset[3] = {d * n[0], d * n[1], d * n[2]};
+    if (std::fma(w[0], n[0], sumOfProducts(w[1], n[1], w[2], n[2])) < 0)
+        for (int k = 0; k < 3; ++k)
+            offset[k] = -offset[k];
+    for (int k = 0; k < 3; ++k) {
+        po[k] = mid[k] + offset[k];
+        if (offset[k] > 0)
+            po[k] = NextFloatUp(po[k]);
+        else if (offset[k] < 0)
+            po[k] = NextFloatDown(po[k]);
+    }
+}
+inline RayCtx MakeRayCtx(const float *o, const float *d) {
+    float r8[8] = {o[0], o[1], o[2], 0, d[0], d[1], d[2], 0};
+    return MakeRayCtx(r8);
+}
+// GeometricPrimitive::Intersect over a Triangle with constant alpha a.
+inline bool GeometricAlphaIntersect(const float *o, const float *d, float tMax, const float *p, float a,
+                                    float *tOut, float *b0, float *b1, float *b2, int depth = 0) {
+    RayCtx r = MakeRayCtx(o, d);
+    float t, c0, c1, c2;
+    if (!TriangleIntersect(r, tMax, p, &t, &c0, &c1, &c2))
+        return false;
+    if (a < 1) {
+        float u = (a <= 0) ? 1.f : HashFloatOD(o, d);
+        if (u > a) {  // ignore this intersection and trace a new ray (against this primitive only)
+            if (depth > 64)
+                return false;
+            float on[3], tn;
+            SpawnOrigin(p, c0, c1, c2, d, on);
+            if (!GeometricAlphaIntersect(on, d, tMax - t, p, a, &tn, b0, b1, b2, depth + 1))
+                return false;
+            *tOut = tn + t;  // siNext->tHit += si->tHit
+            return true;
+        }
+    }
+    *tOut = t, *b0 = c0, *b1 = c1, *b2 = c2;
+    return true;
+}
+
 // ---- TransformedPrimitive (cpu/primitive.cpp:112-130) ------------------------------------------
 // Ray Transform::ApplyInverse(const Ray &r, Float *tMax), util/transform.h:416-430, with
 // Point3fi Transform::ApplyInverse(const Point3fi &) on an exact point (util/transform.cpp:263-303) and
@@ -864,7 +967,8 @@ template <bool ANY>
 inline bool Traverse(const nnbvh_oracle_node *nodes, const float *tris, const float *ray8,
                      uint32_t *hit5, uint32_t *nodesVisitedOut, uint32_t *triTestsOut,
                      const int32_t *sphereOf = nullptr, const float *spheres28 = nullptr,
-                     const InstancedScene *inst = nullptr, uint32_t *innerOut = nullptr) {
+                     const InstancedScene *inst = nullptr, uint32_t *innerOut = nullptr,
+                     const float *alphaOf = nullptr) {
     RayCtx r = MakeRayCtx(ray8);
     float tMax = ray8[3];
     uint32_t hitPrim = 0xFFFFFFFFu, hitInner = 0xFFFFFFFFu;
@@ -932,8 +1036,10 @@ inline bool Traverse(const nnbvh_oracle_node *nodes, const float *tris, const fl
                             continue;
                         }
                         ++triTests;
-                        if (TriangleIntersect(r, tMax, tris + 9 * (size_t)prim, &t, &b0, &b1,
-                                              &b2)) {
+                        if (alphaOf && alphaOf[prim] < 1
+                                ? GeometricAlphaIntersect(ray8, ray8 + 4, tMax, tris + 9 * (size_t)prim, alphaOf[prim],
+                                                          &t, &b0, &b1, &b2)
+                                : TriangleIntersect(r, tMax, tris + 9 * (size_t)prim, &t, &b0, &b1, &b2)) {
                             if (ANY) {
                                 any = true;
                                 goto done;
@@ -1065,6 +1171,36 @@ void nnbvh_oracle_intersectP_mixed(const nnbvh_oracle_node *nodes, const float *
                           ? 1
                           : 0;
     });
+}
+
+// Triangles behind GeometricPrimitives with a constant alpha each (orderedAlpha[i] >= 1: none).  Closest hits
+// or, with occluded != NULL, IntersectP (which is Intersect(...).has_value() for such primitives).
+void nnbvh_oracle_intersect_alpha(const nnbvh_oracle_node *nodes, const float *orderedTris9,
+                                  const float *orderedAlpha, const float *rays8, int64_t n, uint32_t *hits5,
+                                  uint8_t *occluded, int32_t nThreads) {
+    ParallelRays(n, nThreads, [&](int64_t i) {
+        if (occluded)
+            occluded[i] = Traverse<true>(nodes, orderedTris9, rays8 + 8 * i, nullptr, nullptr, nullptr, nullptr,
+                                         nullptr, nullptr, nullptr, orderedAlpha)
+                              ? 1
+                              : 0;
+        else
+            Traverse<false>(nodes, orderedTris9, rays8 + 8 * i, hits5 + 5 * i, nullptr, nullptr, nullptr, nullptr,
+                            nullptr, nullptr, orderedAlpha);
+    });
+}
+// Origin of the ray GeometricPrimitive::Intersect re-traces after an ignored hit, and tHit; 0 = miss.
+int32_t nnbvh_oracle_spawn_origin(const float *ray8, const float *p9, float *out4) {
+    RayCtx r = MakeRayCtx(ray8);
+    float t, b0, b1, b2;
+    if (!TriangleIntersect(r, ray8[3], p9, &t, &b0, &b1, &b2))
+        return 0;
+    SpawnOrigin(p9, b0, b1, b2, ray8 + 4, out4);
+    out4[3] = t;
+    return 1;
+}
+float nnbvh_oracle_hash_float(const float *o3, const float *d3) {
+    return HashFloatOD(o3, d3);
 }
 
 void nnbvh_oracle_intersect_instanced(const nnbvh_oracle_node *nodes, const float *orderedTris9,

@@ -165,6 +165,34 @@ class Oracle:
         hit = self.lib.nnbvh_oracle_sphere(_p(ray8), _p(sphere28), _p(out))
         return bool(hit), out
 
+    def spawn_origin(self, ray8, p9):
+        """(hit, [o.xyz of intr.SpawnRay(ray.d), tHit]) for one (ray, triangle) pair."""
+        out = np.zeros(4, dtype=np.float32)
+        f = self.lib.nnbvh_oracle_spawn_origin
+        f.argtypes = [ctypes.c_void_p] * 3
+        hit = f(_p(np.ascontiguousarray(ray8, dtype=np.float32)), _p(np.ascontiguousarray(p9, dtype=np.float32)), _p(out))
+        return bool(hit), out
+
+    def intersect_alpha(self, nodes, ordered_tris9, ordered_alpha, rays8, any_hit=False, threads=0):
+        """Triangles behind GeometricPrimitives with constant alpha: hits5, or occluded with any_hit."""
+        rays8 = np.ascontiguousarray(rays8, dtype=np.float32).reshape(-1, 8)
+        n = rays8.shape[0]
+        hits = np.zeros((n, 5), dtype=np.uint32)
+        occ = np.zeros(n, dtype=np.uint8)
+        f = self.lib.nnbvh_oracle_intersect_alpha
+        f.restype = None
+        f.argtypes = [ctypes.c_void_p] * 4 + [ctypes.c_int64, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int32]
+        a = np.ascontiguousarray(ordered_alpha, dtype=np.float32)
+        t = np.ascontiguousarray(ordered_tris9, dtype=np.float32)
+        f(_p(nodes), _p(t), _p(a), _p(rays8), n, _p(hits), _p(occ) if any_hit else None, threads)
+        return occ if any_hit else hits
+
+    def hash_float(self, o3, d3) -> float:
+        f = self.lib.nnbvh_oracle_hash_float
+        f.restype = ctypes.c_float
+        f.argtypes = [ctypes.c_void_p, ctypes.c_void_p]
+        return f(_p(np.ascontiguousarray(o3, dtype=np.float32)), _p(np.ascontiguousarray(d3, dtype=np.float32)))
+
     def atan2f(self, y, x):
         """The host libm's atan2f, elementwise."""
         y = np.ascontiguousarray(y, dtype=np.float32)
@@ -255,6 +283,33 @@ class Reference:
         idx = np.arange(3 * T, dtype=np.int32)
         h = self.lib.nnbvh_ref_scene_create(_p(verts), 3 * T, _p(idx), T, max_prims, SPLIT[split])
         return ctypes.c_void_p(h)
+
+    def spawn_origin(self, ray8, p9):
+        """(hit, [o.xyz of intr.SpawnRay(ray.d), tHit]) for one (ray, triangle) pair."""
+        out = np.zeros(4, dtype=np.float32)
+        f = self.lib.nnbvh_ref_spawn_origin
+        f.argtypes = [ctypes.c_void_p] * 3
+        hit = f(_p(np.ascontiguousarray(ray8, dtype=np.float32)), _p(np.ascontiguousarray(p9, dtype=np.float32)), _p(out))
+        return bool(hit), out
+
+    def scene_alpha(self, tris9, alpha, max_prims: int = 4, split: str = "sah"):
+        """BVHAggregate over triangles behind GeometricPrimitives with a constant alpha each (>= 1: none)."""
+        tris9 = np.ascontiguousarray(tris9, dtype=np.float32).reshape(-1, 9)
+        alpha = np.ascontiguousarray(alpha, dtype=np.float32)
+        T = tris9.shape[0]
+        verts = tris9.reshape(-1, 3)
+        idx = np.arange(3 * T, dtype=np.int32)
+        f = self.lib.nnbvh_ref_scene_create_alpha
+        f.restype = ctypes.c_void_p
+        f.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_int,
+                      ctypes.c_int]
+        return ctypes.c_void_p(f(_p(verts), 3 * T, _p(idx), T, _p(alpha), max_prims, SPLIT[split]))
+
+    def hash_float(self, o3, d3) -> float:
+        f = self.lib.nnbvh_ref_hash_float
+        f.restype = ctypes.c_float
+        f.argtypes = [ctypes.c_void_p, ctypes.c_void_p]
+        return f(_p(np.ascontiguousarray(o3, dtype=np.float32)), _p(np.ascontiguousarray(d3, dtype=np.float32)))
 
     def build_seconds(self, scene) -> float:
         """Wall time of the BVHAggregate constructor that made this scene."""

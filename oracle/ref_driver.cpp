@@ -39,6 +39,8 @@
 #define private public
 #include <pbrt/pbrt.h>
 #include <pbrt/cpu/aggregates.h>
+#include <pbrt/textures.h>
+#include <pbrt/util/hash.h>
 #include <pbrt/cpu/primitive.h>
 #include <pbrt/materials.h>
 #include <pbrt/options.h>
@@ -245,6 +247,81 @@ void *nnbvh_ref_scene_create_mixed(const float *verts, int nVerts, const int *in
 double nnbvh_ref_scene_build_seconds(void *scene) {
     return ((RefScene *)scene)->buildSeconds;
 }
+// Triangles behind GeometricPrimitives with a constant alpha texture each (cpu/primitive.cpp:32-84):
+// alpha[i] < 1 -> GeometricPrimitive(shape, no material, no light, no media, FloatConstantTexture(alpha[i])),
+// else SimplePrimitive.  alpha = 0 primitives stay in the list (pbrt's scene loader would drop them).
+void *nnbvh_ref_scene_create_alpha(const float *verts, int nVerts, const int *indices, int nTris,
+                                   const float *alpha, int maxPrimsInNode, int splitMethod) {
+    if (!g_inited)
+        nnbvh_ref_init(0);
+    auto *s = new RefScene;
+    std::vector<int> idx(indices, indices + 3 * (size_t)nTris);
+    std::vector<pbrt::Point3f> p(nVerts);
+    for (int i = 0; i < nVerts; ++i)
+        p[i] = pbrt::Point3f(verts[3 * i], verts[3 * i + 1], verts[3 * i + 2]);
+    std::vector<int> face(nTris);
+    for (int i = 0; i < nTris; ++i)
+        face[i] = i;
+    pbrt::Allocator alloc;
+    s->mesh = alloc.new_object<pbrt::TriangleMesh>(pbrt::Transform(), false, idx, p,
+                                                   std::vector<pbrt::Vector3f>(),
+                                                   std::vector<pbrt::Normal3f>(),
+                                                   std::vector<pbrt::Point2f>(), face, alloc);
+    pstd::vector<pbrt::Shape> shapes = pbrt::Triangle::CreateTriangles(s->mesh, alloc);
+    std::vector<pbrt::Primitive> prims;
+    prims.reserve(nTris);
+    for (int i = 0; i < nTris; ++i) {
+        if (alpha[i] < 1) {
+            pbrt::FloatTexture tex(alloc.new_object<pbrt::FloatConstantTexture>(alpha[i]));
+            prims.push_back(pbrt::Primitive(alloc.new_object<pbrt::GeometricPrimitive>(
+                shapes[i], pbrt::Material(nullptr), pbrt::Light(nullptr), pbrt::MediumInterface(), tex)));
+        } else
+            prims.push_back(pbrt::Primitive(
+                alloc.new_object<pbrt::SimplePrimitive>(shapes[i], pbrt::Material(nullptr))));
+    }
+    s->nTris = nTris;
+    s->primList = prims;
+    s->agg = new pbrt::BVHAggregate(std::move(prims), maxPrimsInNode,
+                                    (pbrt::BVHAggregate::SplitMethod)splitMethod);
+    s->nNodes = CountNodes(reinterpret_cast<const NodeMirror *>(s->agg->nodes));
+    s->orderedToOrig.resize(nTris);
+    s->origToOrdered.resize(nTris);
+    for (int i = 0; i < nTris; ++i) {
+        const pbrt::Primitive &pr = s->agg->primitives[i];
+        pbrt::Shape sh = pr.Is<pbrt::SimplePrimitive>() ? pr.Cast<pbrt::SimplePrimitive>()->shape
+                                                        : pr.Cast<pbrt::GeometricPrimitive>()->shape;
+        int orig = sh.Cast<pbrt::Triangle>()->triIndex;
+        s->orderedToOrig[i] = orig;
+        s->origToOrdered[orig] = i;
+    }
+    return s;
+}
+// Origin of si->intr.SpawnRay(r.d) (cpu/primitive.cpp:63) after Triangle::Intersect on one triangle
+// (p9), and tHit; returns 0 when the ray misses.
+int nnbvh_ref_spawn_origin(const float *ray8, const float *p9, float *out4) {
+    if (!g_inited)
+        nnbvh_ref_init(0);
+    std::vector<int> idx{0, 1, 2};
+    std::vector<pbrt::Point3f> p{pbrt::Point3f(p9[0], p9[1], p9[2]), pbrt::Point3f(p9[3], p9[4], p9[5]),
+                                 pbrt::Point3f(p9[6], p9[7], p9[8])};
+    pbrt::Allocator alloc;
+    pbrt::TriangleMesh *mesh = alloc.new_object<pbrt::TriangleMesh>(
+        pbrt::Transform(), false, idx, p, std::vector<pbrt::Vector3f>(), std::vector<pbrt::Normal3f>(),
+        std::vector<pbrt::Point2f>(), std::vector<int>(), alloc);
+    pstd::vector<pbrt::Shape> shapes = pbrt::Triangle::CreateTriangles(mesh, alloc);
+    pbrt::Ray ray = MakeRay(ray8);
+    pstd::optional<pbrt::ShapeIntersection> si = shapes[0].Intersect(ray, ray8[3]);
+    if (!si)
+        return 0;
+    pbrt::Ray next = si->intr.SpawnRay(ray.d);
+    out4[0] = next.o.x, out4[1] = next.o.y, out4[2] = next.o.z, out4[3] = si->tHit;
+    return 1;
+}
+// HashFloat(Point3f, Vector3f) as GeometricPrimitive::Intersect calls it (cpu/primitive.cpp:60)
+float nnbvh_ref_hash_float(const float *o, const float *d) {
+    return pbrt::HashFloat(pbrt::Point3f(o[0], o[1], o[2]), pbrt::Vector3f(d[0], d[1], d[2]));
+}
+
 int nnbvh_ref_scene_num_nodes(void *scene) {
     return ((RefScene *)scene)->nNodes;
 }

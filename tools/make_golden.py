@@ -35,6 +35,10 @@ oracle/ref_driver.cpp; the fixtures are small so they can be committed.
   sphere_phi.npz    Sphere::BasicIntersect for 4000 (ray, sphere) pairs with phimax < 360 (the std::atan2
                     clipping test, shapes.h:196-203), 1500 of them aimed within 1e-7 .. 1e-3 (relative)
                     of the phi = phimax boundary (--only-sphere-phi).
+  alpha.npz         GeometricPrimitive with a constant alpha texture (cpu/primitive.cpp:50-84): HashFloat(o, d)
+                    for 2000 pairs, the origin of intr.SpawnRay(r.d) for the hits of tri_vectors.npz, and a
+                    4000-triangle scene (half the triangles with alpha in [0,1), a tenth with alpha 0): the
+                    reference's tree, closest hits and IntersectP (--only-alpha).
   instanced_surface.npz  BVHAggregate::Intersect's SurfaceInteraction on an instanced scene (some
                     instances mirrored, ray directions not normalised): TransformedPrimitive::Intersect's
                     (*renderFromPrimitive)(si->intr) (cpu/primitive.cpp:112-125), 42 words per ray
@@ -486,6 +490,39 @@ def sphere_phi(ref, rng):
     np.savez_compressed(os.path.join(OUT, "sphere_phi.npz"), spheres=spheres, rays=rays, hit=hit, out=out)
 
 
+def alpha(ref, rng):
+    od = rng.normal(size=(2000, 6)).astype(np.float32) * np.exp(rng.uniform(-3, 3, (2000, 1))).astype(np.float32)
+    hashes = np.array([ref.hash_float(v[:3], v[3:]) for v in od], dtype=np.float32)
+    tv = np.load(os.path.join(OUT, "tri_vectors.npz"))
+    n = len(tv["rays"])
+    spawn_hit = np.zeros(n, dtype=np.uint8)
+    spawn = np.zeros((n, 4), dtype=np.float32)
+    for i in range(n):
+        h, o4 = ref.spawn_origin(tv["rays"][i], tv["tris"][i])
+        spawn_hit[i] = h
+        spawn[i] = o4 if h else 0
+    T = 4000
+    c = rng.random((T, 1, 3), dtype=np.float32)
+    tris = as_pbrt_stores((c + np.float32(0.05) * (rng.random((T, 3, 3), dtype=np.float32) * 2 - 1)).reshape(T, 9))
+    a = np.ones(T, dtype=np.float32)
+    a[::2] = rng.random(len(a[::2])).astype(np.float32)
+    a[::10] = 0.0
+    sc = ref.scene_alpha(tris, a, 4, "sah")
+    nodes, order = ref.export(sc, T)
+    N = 8192
+    rays = np.zeros((N, 8), dtype=np.float32)
+    rays[:, :3] = rng.random((N, 3)) * 1.5 - 0.25
+    d = rng.normal(size=(N, 3))
+    rays[:, 4:7] = d / np.linalg.norm(d, axis=1, keepdims=True)
+    rays[:, 3] = np.inf
+    rays[N // 2:, 3] = rng.random(N - N // 2)
+    hits = ref.intersect(sc, rays, parallel=False)
+    occ = ref.intersect_p(sc, rays, parallel=False)
+    print("alpha: spawn hits", int(spawn_hit.sum()), "; scene hits", int((hits[:, 0] != 0xFFFFFFFF).sum()), "occluded", int(occ.sum()))
+    np.savez_compressed(os.path.join(OUT, "alpha.npz"), od=od, hashes=hashes, spawn_hit=spawn_hit, spawn=spawn,
+                        tris=tris, alpha=a, nodes=nodes, order=order, rays=rays, hits=hits, occ=occ)
+
+
 if __name__ == "__main__":
     os.makedirs(OUT, exist_ok=True)
     ref = Reference(threads=1)
@@ -507,6 +544,9 @@ if __name__ == "__main__":
     if "--only-sphere-phi" in sys.argv:
         sphere_phi(ref, np.random.default_rng(196))
         sys.exit(0)
+    if "--only-alpha" in sys.argv:
+        alpha(ref, np.random.default_rng(606))
+        sys.exit(0)
     if "--only-hlbvh" in sys.argv:
         hlbvh(ref)
         sys.exit(0)
@@ -521,3 +561,4 @@ if __name__ == "__main__":
     sphere_interaction(ref, np.random.default_rng(238))
     instanced_surface(ref, np.random.default_rng(415))
     sphere_phi(ref, np.random.default_rng(196))
+    alpha(ref, np.random.default_rng(606))
