@@ -196,6 +196,15 @@ int nnbvh_upload_scene_mixed(nnbvh_engine *e, const nnbvh_node *nodes, uint32_t 
                              const float *orderedTriVerts9, const int32_t *orderedSphereIndex,
                              uint32_t nPrims, const nnbvh_sphere *spheres, uint32_t nSpheres);
 
+/* ---- alpha-tested triangles: GeometricPrimitive with an alpha texture (cpu/primitive.cpp:50-84) ------
+ * orderedAlpha[i]: the CONSTANT alpha of ordered primitive i (FloatConstantTexture; >= 1 = no texture).
+ * A hit is ignored when alpha <= 0 or HashFloat(ray.o, ray.d) > alpha (util/hash.h:98-112), and the same
+ * primitive is asked again with si->intr.SpawnRay(ray.d) and tMax - tHit, as the reference does;
+ * nnbvh_intersect_any on such a scene is Intersect(...).has_value().  Image / procedural alpha textures
+ * are outside this path.  Such scenes run a one-thread-per-ray kernel; per-ray counters are unavailable. */
+int nnbvh_upload_scene_alpha(nnbvh_engine *e, const nnbvh_node *nodes, uint32_t nNodes,
+                             const float *orderedTriVerts9, const float *orderedAlpha, uint32_t nPrims);
+
 /* ---- instances: TransformedPrimitive over per-object BVHAggregates ---------------------------
  * (cpu/primitive.cpp:112-130; pbrt creates them for ObjectInstance, scene.cpp:1541-1571).  An object
  * is a BVHAggregate over triangles in ITS OWN space (tree + ordered triangles, as nnbvh_upload_scene

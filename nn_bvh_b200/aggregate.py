@@ -182,7 +182,8 @@ class GPUBVHAggregate:
                  device: int = -1, kernel: int = capi.KERNEL_AUTO, smem_top_nodes: int = -1,
                  spheres: Optional[np.ndarray] = None,
                  ordered_sphere_index: Optional[np.ndarray] = None,
-                 objects: Optional[list] = None, instances: Optional[np.ndarray] = None):
+                 objects: Optional[list] = None, instances: Optional[np.ndarray] = None,
+                 alpha: Optional[np.ndarray] = None):
         """Either tris9 (a soup to build over, like the reference ctor) or a ready
         flattened tree: nodes + ordered_tris9 (e.g. an exported NN-split tree).
 
@@ -194,7 +195,11 @@ class GPUBVHAggregate:
         objects (list of (T_j,9) soups in object space) + instances (INSTANCE_DTYPE records, see
         make_instances): each object gets its own tree; caller primitive T + k is instance k, a
         TransformedPrimitive over its object's aggregate (nnbvh_upload_scene_instanced).  Use
-        IntersectBatchInstanced to get the primitive inside the object as well."""
+        IntersectBatchInstanced to get the primitive inside the object as well.
+
+        alpha (one float per caller triangle; >= 1 = none): the constant alpha texture of a
+        GeometricPrimitive (cpu/primitive.cpp:50-84): hits are ignored when HashFloat(o, d) > alpha
+        (nnbvh_upload_scene_alpha).  Triangle-only scenes."""
         L = capi.lib()
         opts = capi.Options(device=device, kernel=kernel, smem_top_nodes=smem_top_nodes)
         h = ctypes.c_void_p()
@@ -265,6 +270,14 @@ class GPUBVHAggregate:
             capi.check(L.nnbvh_upload_scene_mixed(h, capi.ptr(self.nodes), len(self.nodes),
                                                   capi.ptr(self.ordered_tris9), capi.ptr(self.ordered_sphere_index),
                                                   len(self.ordered_tris9), capi.ptr(self.spheres), len(self.spheres)))
+        elif alpha is not None:
+            alpha = np.ascontiguousarray(alpha, dtype=np.float32).reshape(-1)
+            if len(alpha) != len(self.ordered_tris9):
+                raise ValueError("one alpha value per triangle")
+            self.ordered_alpha = np.ascontiguousarray(alpha if self.order is None else alpha[self.order])
+            capi.check(L.nnbvh_upload_scene_alpha(h, capi.ptr(self.nodes), len(self.nodes),
+                                                  capi.ptr(self.ordered_tris9), capi.ptr(self.ordered_alpha),
+                                                  len(self.ordered_tris9)))
         else:
             capi.check(L.nnbvh_upload_scene(h, capi.ptr(self.nodes), len(self.nodes),
                                             capi.ptr(self.ordered_tris9), len(self.ordered_tris9)))

@@ -34,7 +34,7 @@ SYMBOLS = [
     "nnbvh_last_error", "nnbvh_version", "nnbvh_build_hlbvh_device", "nnbvh_debug_step_stats", "nnbvh_last_traversal_ms", "nnbvh_peer_alloc", "nnbvh_peer_open",
     "nnbvh_peer_close", "nnbvh_peer_free", "nnbvh_peer_copy", "nnbvh_read_bandwidth_probe",
     "nnbvh_pointer_kind", "nnbvh_copy_to_host", "nnbvh_build_bvh_bounds", "nnbvh_sphere_bounds",
-    "nnbvh_upload_scene_mixed", "nnbvh_test_spheres", "nnbvh_test_atan2", "nnbvh_instance_bounds",
+    "nnbvh_upload_scene_mixed", "nnbvh_upload_scene_alpha", "nnbvh_test_spheres", "nnbvh_test_atan2", "nnbvh_instance_bounds",
     "nnbvh_upload_scene_instanced", "nnbvh_intersect_closest_instanced", "nnbvh_intersect_closest_instanced_soa", "nnbvh_clone",
 ]
 
@@ -95,6 +95,7 @@ def lib() -> ctypes.CDLL:
     L.nnbvh_upload_scene_instanced.argtypes = [vp, vp, u32, vp, vp, u32, vp, u32, vp, u32]
     L.nnbvh_intersect_closest_instanced.argtypes = [vp, vp, u64, vp, vp]
     L.nnbvh_test_atan2.argtypes = [vp, vp, vp, u64, vp]
+    L.nnbvh_upload_scene_alpha.argtypes = [vp, vp, ctypes.c_uint32, vp, vp, ctypes.c_uint32]
     L.nnbvh_intersect_closest_instanced_soa.argtypes = [vp] * 8 + [u64, vp, vp]
     L.nnbvh_copy_to_host.argtypes = [vp, vp, u64]
     L.nnbvh_test_triangles.argtypes = [vp, vp, vp, u64, vp, vp]

@@ -17,6 +17,7 @@
 #include "../../include/nnbvh.h"
 #include "internal.h"
 #include "kernels.cuh"
+#include "alpha.cuh"
 #include "binning.cuh"
 #include "hlbvh.cuh"
 #include "traverse.cuh"
@@ -110,9 +111,10 @@ struct SceneStore {
     DevBuf<InstanceDev> dInstances;
     DevBuf<nnbvh_node> dObjNodes;
     DevBuf<float4> dObjTris;
+    DevBuf<float> dAlpha;  // one value per ordered primitive (nnbvh_upload_scene_alpha)
     ~SceneStore() {
         dNodes.Free(); dWide.Free(); dTris.Free(); dSpheres.Free();
-        dInstances.Free(); dObjNodes.Free(); dObjTris.Free();
+        dInstances.Free(); dObjNodes.Free(); dObjTris.Free(); dAlpha.Free();
     }
 };
 
@@ -136,6 +138,7 @@ struct nnbvh_engine {
     std::shared_ptr<SceneStore> store = std::make_shared<SceneStore>();
     bool hasInstances = false;  // instanced scene: BasicKernel with nested traversal runs
     bool hasSpheres = false;  // scene uploaded with spheres: the SPHERES instantiations run
+    bool hasAlpha = false;    // scene uploaded with per-primitive alpha: AlphaKernel runs
     // device-pointer path scratch
     Scratch scratch;
     // host-pointer pipeline
@@ -280,6 +283,7 @@ extern "C" int nnbvh_clone(nnbvh_engine *src, nnbvh_engine **out) {
     e->boxesRegular = src->boxesRegular;
     e->hasSpheres = src->hasSpheres;
     e->hasInstances = src->hasInstances;
+    e->hasAlpha = src->hasAlpha;
     *out = e;
     return NNBVH_OK;
 }
@@ -473,6 +477,26 @@ extern "C" int nnbvh_upload_scene(nnbvh_engine *e, const nnbvh_node *nodes, uint
     return UploadScene(e, nodes, nNodes, orderedTriVerts9, nPrims, nullptr, nullptr, 0);
 }
 
+extern "C" int nnbvh_upload_scene_alpha(nnbvh_engine *e, const nnbvh_node *nodes, uint32_t nNodes,
+                                        const float *orderedTriVerts9, const float *orderedAlpha, uint32_t nPrims) {
+    if (nPrims && !orderedAlpha) return SetError(NNBVH_ERR_INVALID, "nnbvh_upload_scene_alpha: NULL alpha array");
+    if (IsDevicePtr(orderedAlpha))
+        return SetError(NNBVH_ERR_INVALID, "nnbvh_upload_scene_alpha: the alpha array is a host array");
+    for (uint32_t i = 0; i < nPrims; ++i)
+        if (std::isnan(orderedAlpha[i]))
+            return SetError(NNBVH_ERR_INVALID, "nnbvh_upload_scene_alpha: alpha of primitive %u is NaN", i);
+    DetachStore(e);
+    int rc = UploadScene(e, nodes, nNodes, orderedTriVerts9, nPrims, nullptr, nullptr, 0);
+    if (rc || nNodes == 0 || nPrims == 0) return rc;
+    rc = e->store->dAlpha.Reserve(nPrims);
+    if (rc) return rc;
+    cudaStream_t st = e->stream;
+    CU(cudaMemcpyAsync(e->store->dAlpha.p, orderedAlpha, sizeof(float) * (size_t)nPrims, cudaMemcpyHostToDevice, st));
+    CU(cudaStreamSynchronize(st));
+    e->hasAlpha = true;
+    return NNBVH_OK;
+}
+
 extern "C" int nnbvh_upload_scene_mixed(nnbvh_engine *e, const nnbvh_node *nodes, uint32_t nNodes,
                                         const float *orderedTriVerts9, const int32_t *orderedSphereIndex,
                                         uint32_t nPrims, const nnbvh_sphere *spheres, uint32_t nSpheres) {
@@ -494,6 +518,7 @@ static int UploadScene(nnbvh_engine *e, const nnbvh_node *nodes, uint32_t nNodes
     e->haveScene = false;
     e->hasSpheres = false;
     e->hasInstances = false;
+    e->hasAlpha = false;
     if (nNodes == 0) {  // `nodes == nullptr` in the reference: every ray misses
         e->sc = SceneDev{};
         e->haveScene = true;
@@ -757,6 +782,18 @@ static int LaunchTraversal(nnbvh_engine *e, cudaStream_t st, bool any, bool coun
                            const RayInput &in, uint64_t n, const Outputs &o,
                            Scratch &scr) {
     if (n == 0) return NNBVH_OK;
+    if (e->hasAlpha) {  // alpha-tested primitives: one thread per ray (alpha.cuh)
+        if (counters)
+            return SetError(NNBVH_ERR_INVALID, "per-ray counters are not available for scenes with alpha primitives");
+        if (n > (uint64_t)0x7fffffff * 128)
+            return SetError(NNBVH_ERR_INVALID, "batch too large for one launch");
+        const unsigned grid = (unsigned)((n + 127) / 128);
+        if (any) AlphaKernel<true><<<grid, 128, 0, st>>>(e->sc, e->store->dAlpha.p, in, n, o.hits, o.occ);
+        else AlphaKernel<false><<<grid, 128, 0, st>>>(e->sc, e->store->dAlpha.p, in, n, o.hits, o.occ);
+        ++e->launches;
+        CU(cudaGetLastError());
+        return NNBVH_OK;
+    }
     // instanced scenes: nested traversal lives in BasicKernel only (one thread per ray)
     const bool basic = counters || e->kernel == NNBVH_KERNEL_BASIC || e->hasInstances;
     if (basic) {

@@ -1,0 +1,55 @@
+"""tests/test_zz_alpha_gpu.py -- alpha-tested primitives on the device (csrc/alpha.cuh, nnbvh_upload_scene_alpha).
+
+The device kernel was written after this round's GPU budget was spent: it compiles for sm_100a (and leaves the SASS
+of every other kernel unchanged), its arithmetic is the oracle's (tests/test_alpha.py pins that to the reference), but
+it has NOT yet been run on a GPU.  Until it has, these tests are expected-to-fail-or-pass (xfail, non-strict): a pass
+shows up as XPASS.  The file sorts last so that nothing else runs after a kernel nobody has executed yet.
+"""
+import os
+
+import numpy as np
+import pytest
+
+from conftest import GOLDEN, rand_rays
+
+MISS = 0xFFFFFFFF
+UNRUN = pytest.mark.xfail(reason="AlphaKernel has not been run on a GPU yet (written after the round's GPU budget)",
+                          strict=False)
+
+
+@pytest.mark.gpu
+@UNRUN
+def test_alpha_scene_gpu_matches_reference_golden():
+    import nn_bvh_b200 as nb
+    g = np.load(os.path.join(GOLDEN, "alpha.npz"))
+    order = g["order"].astype(np.uint32)
+    agg = nb.GPUBVHAggregate(nodes=g["nodes"].view(nb.NODE_DTYPE).reshape(-1), ordered_tris9=g["tris"][order],
+                             order=order, alpha=g["alpha"])
+    hits = np.ascontiguousarray(agg.IntersectBatch(g["rays"])).view(np.uint32).reshape(-1, 5)
+    assert np.array_equal(hits, g["hits"])
+    assert np.array_equal(agg.IntersectPBatch(g["rays"]), g["occ"])
+
+
+@pytest.mark.gpu
+@UNRUN
+def test_alpha_scene_gpu_matches_oracle_at_size(oracle):
+    import nn_bvh_b200 as nb
+    rng = np.random.default_rng(44)
+    T, N = 60_000, 400_000
+    c = rng.random((T, 1, 3), dtype=np.float32)
+    tris = ((c + np.float32(0.02) * (rng.random((T, 3, 3), dtype=np.float32) * 2 - 1)).reshape(T, 9)
+            + np.float32(0)).astype(np.float32)
+    a = rng.random(T).astype(np.float32)
+    a[::3] = 1.0
+    a[1::9] = 0.0
+    agg = nb.GPUBVHAggregate(tris, 4, "sah", alpha=a)
+    rays = rand_rays(rng, N)
+    rays[N // 2:, 3] = rng.random(N - N // 2)
+    rays[::5, 4:7] *= np.float32(3.7)                      # HashFloat sees d as given
+    nodes = agg.nodes.view(np.uint32).reshape(-1, 8)
+    want = oracle.intersect_alpha(nodes, agg.ordered_tris9, agg.ordered_alpha, rays)
+    got = np.ascontiguousarray(agg.IntersectBatch(rays)).view(np.uint32).reshape(-1, 5)
+    assert np.array_equal(got, want)
+    assert (oracle.intersect(nodes, agg.ordered_tris9, rays) != want).any(axis=1).sum() > 10_000
+    assert np.array_equal(agg.IntersectPBatch(rays),
+                          oracle.intersect_alpha(nodes, agg.ordered_tris9, agg.ordered_alpha, rays, any_hit=True))
