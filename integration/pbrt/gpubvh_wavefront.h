@@ -85,49 +85,52 @@ class GPUBVHWavefrontAggregate : public WavefrontAggregate {
         });
     }
 
-    // CPUAggregate::IntersectShadowTr, wavefront/aggregate.cpp:70-92.  Scenes without media reduce to
-    // IntersectShadow; with media the walk over interfaces is data dependent and goes ray by ray.
+    // What CPUAggregate::IntersectShadowTr does (wavefront/aggregate.cpp:70-92): TraceTransmittance
+    // (wavefront/intersect.h:165-240) walks a shadow ray across medium interfaces.  How many surfaces a ray
+    // crosses depends on what it meets, so the walk goes ray by ray through the single-ray entry point.
     void IntersectShadowTr(int maxRays, ShadowRayQueue *shadowRayQueue,
                            SOA<PixelSampleState> *pixelSampleState) const override {
-        ParallelFor(0, shadowRayQueue->Size(), [=](int index) {
-            const ShadowRayWorkItem w = (*shadowRayQueue)[index];
-            pstd::optional<ShapeIntersection> si;
-            TraceTransmittance(
-                w, pixelSampleState,
-                [&](Ray ray, Float tMax) -> TransmittanceTraceResult {
-                    si = host.Intersect(ray, tMax);
-                    if (!si)
-                        return TransmittanceTraceResult{false, Point3f(), Material()};
-                    return TransmittanceTraceResult{true, si->intr.p(), si->intr.material};
-                },
-                [&](Point3f p) -> Ray { return si->intr.SpawnRayTo(p); });
-        });
+        auto walk = [=](int index) {
+            pstd::optional<ShapeIntersection> last;  // the surface the walk currently stands on
+            auto trace = [&](Ray ray, Float tMax) {
+                last = host.Intersect(ray, tMax);
+                TransmittanceTraceResult res{last.has_value(), Point3f(), Material()};
+                if (last) {
+                    res.pHit = last->intr.p();
+                    res.material = last->intr.material;
+                }
+                return res;
+            };
+            auto spawnTo = [&](Point3f target) { return last->intr.SpawnRayTo(target); };
+            TraceTransmittance((*shadowRayQueue)[index], pixelSampleState, trace, spawnTo);
+        };
+        ParallelFor(0, shadowRayQueue->Size(), walk);
     }
 
-    // CPUAggregate::IntersectOneRandom, wavefront/aggregate.cpp:94-124
+    // What CPUAggregate::IntersectOneRandom does (wavefront/aggregate.cpp:94-124): between p0 and p1 every
+    // surface of the probe's material is a candidate of weight 1 for the subsurface exit point; the reservoir
+    // is seeded by Hash(p0, p1).
     void IntersectOneRandom(int maxRays, SubsurfaceScatterQueue *subsurfaceScatterQueue) const override {
-        ParallelFor(0, subsurfaceScatterQueue->Size(), [=](int index) {
-            const SubsurfaceScatterWorkItem &w = (*subsurfaceScatterQueue)[index];
-            uint64_t seed = Hash(w.p0, w.p1);
-            WeightedReservoirSampler<SubsurfaceInteraction> wrs(seed);
-            Interaction base(w.p0, 0.f, Medium());
-            while (true) {
-                Ray r = base.SpawnRayTo(w.p1);
-                if (r.d == Vector3f(0, 0, 0))
+        SubsurfaceScatterQueue *q = subsurfaceScatterQueue;
+        auto probe = [=](int index) {
+            const SubsurfaceScatterWorkItem &item = (*q)[index];
+            WeightedReservoirSampler<SubsurfaceInteraction> reservoir(Hash(item.p0, item.p1));
+            for (Interaction from(item.p0, 0.f, Medium());;) {
+                Ray segment = from.SpawnRayTo(item.p1);
+                if (segment.d == Vector3f(0, 0, 0))
                     break;
-                pstd::optional<ShapeIntersection> si = host.Intersect(r, 1);
-                if (!si)
+                pstd::optional<ShapeIntersection> next = host.Intersect(segment, 1);
+                if (!next)
                     break;
-                base = si->intr;
-                if (si->intr.material == w.material)
-                    wrs.Add(SubsurfaceInteraction(si->intr), 1.f);
+                if (next->intr.material == item.material)
+                    reservoir.Add(SubsurfaceInteraction(next->intr), 1.f);
+                from = next->intr;
             }
-            if (wrs.HasSample()) {
-                subsurfaceScatterQueue->reservoirPDF[index] = wrs.SampleProbability();
-                subsurfaceScatterQueue->ssi[index] = wrs.GetSample();
-            } else
-                subsurfaceScatterQueue->reservoirPDF[index] = 0;
-        });
+            q->reservoirPDF[index] = reservoir.HasSample() ? reservoir.SampleProbability() : Float(0);
+            if (reservoir.HasSample())
+                q->ssi[index] = reservoir.GetSample();
+        };
+        ParallelFor(0, q->Size(), probe);
     }
 
   private:
