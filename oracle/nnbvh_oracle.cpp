@@ -1199,6 +1199,17 @@ int32_t nnbvh_oracle_spawn_origin(const float *ray8, const float *p9, float *out
     out4[3] = t;
     return 1;
 }
+// GeometricPrimitive::Intersect over one triangle with a constant alpha; out4 = {tHit, b0, b1, b2}; 0 = no hit.
+int32_t nnbvh_oracle_alpha_triangle(const float *ray8, const float *p9, float alpha, float *out4) {
+    if (alpha < 1)
+        return GeometricAlphaIntersect(ray8, ray8 + 4, ray8[3], p9, alpha, &out4[0], &out4[1], &out4[2], &out4[3]) ? 1 : 0;
+    RayCtx r = MakeRayCtx(ray8);
+    return TriangleIntersect(r, ray8[3], p9, &out4[0], &out4[1], &out4[2], &out4[3]) ? 1 : 0;
+}
+// Transform::ApplyInverse(Ray, &tMax) (util/transform.h:416-430) with mInv = primitiveFromRender; local8 = {o, tMax, d, time}
+void nnbvh_oracle_instance_ray(const float *primitiveFromRender12, const float *ray8, float *local8) {
+    InstanceRay(primitiveFromRender12, ray8, local8);
+}
 float nnbvh_oracle_hash_float(const float *o3, const float *d3) {
     return HashFloatOD(o3, d3);
 }

@@ -12,3 +12,6 @@ g++ -std=c++17 -O2 -ffp-contract=off -fPIC -shared -I"$ROOT/include" \
     -o "$HERE/libwavefront_shim.so" "$HERE/wavefront_shim.cpp" \
     -L"$ROOT/nn_bvh_b200" -lnnbvh -Wl,-rpath,'$ORIGIN/../../nn_bvh_b200' -pthread
 echo "built $HERE/libwavefront_shim.so"
+g++ -std=c++17 -O2 -ffp-contract=off -fPIC -shared -w -I"$HERE/cuda_stub" \
+    -o "$HERE/libdevice_twin.so" "$HERE/device_twin.cpp"
+echo "built $HERE/libdevice_twin.so"

@@ -1,0 +1,80 @@
+// tests/cpp/device_twin.cpp -- the DEVICE math headers compiled for the host (tests/test_device_twin.py).
+//
+// nn_bvh_b200/csrc/{exact_math,sphere,atan2_host,alpha_math}.cuh are included unchanged, with
+// tests/cpp/cuda_stub/cuda_runtime.h supplying IEEE-exact host equivalents of the CUDA intrinsics.  The CPU
+// suite then runs the device source -- the same statements the GPU executes -- on the reference's golden
+// vectors and against the checker, so a slip in the device text is caught without a GPU.
+#include <algorithm>
+
+#include "../../nn_bvh_b200/csrc/alpha_math.cuh"
+#include "../../nn_bvh_b200/csrc/atan2_host.cuh"
+#include "../../nn_bvh_b200/csrc/exact_math.cuh"
+#include "../../nn_bvh_b200/csrc/sphere.cuh"
+
+using namespace nnbvh;
+
+namespace {
+RayConst RayOf(const float *r) { return MakeRayConst(r[0], r[1], r[2], r[4], r[5], r[6]); }
+// what MakeSphereDev (engine.cu) stores: Sphere::Sphere's clamped values (shapes.h:117-128)
+SphereDev SphereOf(const float *s28) {
+    SphereDev d;
+    for (int k = 0; k < 12; ++k) d.m[k] = s28[12 + k];
+    auto clamp = [](float v, float lo, float hi) { return v < lo ? lo : (v > hi ? hi : v); };
+    const float r = s28[24];
+    d.radius = r;
+    d.zMin = clamp(std::min(s28[25], s28[26]), -r, r);
+    d.zMax = clamp(std::max(s28[25], s28[26]), -r, r);
+    d.phiMax = (3.14159265358979323846f / 180) * clamp(s28[27], 0.f, 360.f);
+    return d;
+}
+}  // namespace
+
+extern "C" {
+
+// out4 = {t, b0, b1, b2}
+int dt_triangle(const float *ray8, const float *p, float *out4) {
+    if (TriangleDegenerate(p[0], p[1], p[2], p[3], p[4], p[5], p[6], p[7], p[8])) return 0;
+    return TriangleTest(RayOf(ray8), ray8[3], p[0], p[1], p[2], p[3], p[4], p[5], p[6], p[7], p[8], &out4[0], &out4[1],
+                        &out4[2], &out4[3])
+               ? 1
+               : 0;
+}
+int dt_box(const float *ray8, const float *box6) { return SlabTest(RayOf(ray8), box6, ray8[3]) ? 1 : 0; }
+// out4 = {tHit, pObj}
+int dt_sphere(const float *ray8, const float *sphere28, float *out4) {
+    SphereDev sd = SphereOf(sphere28);
+    SphereHit h;
+    if (!SphereTest(&sd, ray8[0], ray8[1], ray8[2], ray8[4], ray8[5], ray8[6], ray8[3], &h)) return 0;
+    out4[0] = h.t, out4[1] = h.px, out4[2] = h.py, out4[3] = h.pz;
+    return 1;
+}
+void dt_atan2(const float *y, const float *x, int64_t n, float *out) {
+    for (int64_t i = 0; i < n; ++i) out[i] = Atan2fHost(y[i], x[i]);
+}
+float dt_hash_float(const float *o, const float *d) { return HashFloatOD(o[0], o[1], o[2], d[0], d[1], d[2]); }
+// out4 = {origin of intr.SpawnRay(ray.d), tHit}
+int dt_spawn_origin(const float *ray8, const float *p, float *out4) {
+    float t, b0, b1, b2;
+    if (!dt_triangle(ray8, p, out4)) return 0;
+    t = out4[0], b0 = out4[1], b1 = out4[2], b2 = out4[3];
+    SpawnOrigin(p, p + 3, p + 6, b0, b1, b2, ray8[4], ray8[5], ray8[6], out4);
+    out4[3] = t;
+    return 1;
+}
+// GeometricPrimitive::Intersect over one triangle with constant alpha; out4 = {t, b0, b1, b2}
+int dt_alpha_triangle(const float *ray8, const float *p, float alpha, float *out4) {
+    if (TriangleDegenerate(p[0], p[1], p[2], p[3], p[4], p[5], p[6], p[7], p[8])) return 0;
+    if (!(alpha < 1)) return dt_triangle(ray8, p, out4);
+    return AlphaTriangleTest(RayOf(ray8), ray8[3], p, p + 3, p + 6, alpha, &out4[0], &out4[1], &out4[2], &out4[3]) ? 1 : 0;
+}
+// Transform::ApplyInverse(Ray, &tMax) as InstanceRay does it; local8 = {o, tMax, d, time}
+void dt_instance_ray(const float *primitiveFromRender12, const float *ray8, float *local8) {
+    InstanceDev in{};
+    for (int k = 0; k < 12; ++k) in.mInv[k] = primitiveFromRender12[k];
+    float o[3], d[3], t;
+    InstanceRay(&in, ray8[0], ray8[1], ray8[2], ray8[4], ray8[5], ray8[6], ray8[3], o, d, &t);
+    local8[0] = o[0], local8[1] = o[1], local8[2] = o[2], local8[3] = t;
+    local8[4] = d[0], local8[5] = d[1], local8[6] = d[2], local8[7] = ray8[7];
+}
+
+}  // extern "C"

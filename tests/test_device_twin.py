@@ -1,0 +1,119 @@
+"""tests/test_device_twin.py -- the device math SOURCE, run on the host.
+
+tests/cpp/device_twin.cpp includes nn_bvh_b200/csrc/{exact_math,sphere,atan2_host,alpha_math}.cuh unchanged and
+compiles them with g++ against tests/cpp/cuda_stub/cuda_runtime.h, where every CUDA intrinsic they use has an
+IEEE-754 equivalent (_rn operations = plain operations under -ffp-contract=off, __fmaf_rn = std::fma, bit casts =
+memcpy).  So the statements the GPU executes -- the watertight triangle test, the slab test, Sphere::BasicIntersect
+in interval arithmetic, glibc's atan2f, Transform::ApplyInverse(Ray), the alpha test's hash / spawned origin /
+re-trace -- run here on the reference's golden vectors and beside the checker, bit for bit, without a GPU.
+What this cannot show is that the GPU's instructions are IEEE-exact; the -m gpu tests do.
+"""
+import ctypes
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+from conftest import GOLDEN, ROOT, rand_rays
+
+
+def _p(a):
+    return a.ctypes.data_as(ctypes.c_void_p)
+
+
+@pytest.fixture(scope="module")
+def twin():
+    subprocess.check_call(["sh", os.path.join(ROOT, "tests", "cpp", "build.sh")], stdout=subprocess.DEVNULL)
+    L = ctypes.CDLL(os.path.join(ROOT, "tests", "cpp", "libdevice_twin.so"))
+    for f in (L.dt_triangle, L.dt_sphere, L.dt_spawn_origin):
+        f.argtypes = [ctypes.c_void_p] * 3
+    L.dt_box.argtypes = [ctypes.c_void_p] * 2
+    L.dt_atan2.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int64, ctypes.c_void_p]
+    L.dt_atan2.restype = None
+    L.dt_hash_float.argtypes = [ctypes.c_void_p] * 2
+    L.dt_hash_float.restype = ctypes.c_float
+    L.dt_alpha_triangle.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_float, ctypes.c_void_p]
+    L.dt_instance_ray.argtypes = [ctypes.c_void_p] * 3
+    L.dt_instance_ray.restype = None
+    return L
+
+
+def _pairs(L, fn, rays, other, gold_hit, gold_out):
+    rays, other = np.ascontiguousarray(rays), np.ascontiguousarray(other)
+    n_hit = 0
+    for i in range(len(rays)):
+        out = np.zeros(4, dtype=np.float32)
+        h = fn(_p(rays[i]), _p(other[i]), _p(out))
+        assert bool(h) == bool(gold_hit[i]), i
+        if h:
+            n_hit += 1
+            assert np.array_equal(out.view(np.uint32), gold_out[i].view(np.uint32)), i
+    return n_hit
+
+
+def test_device_triangle_and_box_source_on_reference_golden(twin, golden):
+    tv = golden["tri_vectors"]
+    assert _pairs(twin, twin.dt_triangle, tv["rays"], tv["tris"], tv["hit"], tv["out"]) > 3000
+    bv = golden["box_vectors"]
+    rays, boxes = np.ascontiguousarray(bv["rays"]), np.ascontiguousarray(bv["boxes"])
+    got = np.array([twin.dt_box(_p(rays[i]), _p(boxes[i])) for i in range(len(rays))], dtype=np.uint8)
+    assert np.array_equal(got, bv["hit"].astype(np.uint8)) and 1000 < got.sum() < 5500
+
+
+@pytest.mark.parametrize("name", ["sphere_vectors", "sphere_phi"])
+def test_device_sphere_source_on_reference_golden(twin, name):
+    g = np.load(os.path.join(GOLDEN, name + ".npz"))
+    assert _pairs(twin, twin.dt_sphere, g["rays"], g["spheres"], g["hit"], g["out"]) > 1500
+
+
+def test_device_atan2_source_matches_host_libm(twin, oracle):
+    from test_spheres import _atan2_inputs
+    y, x = _atan2_inputs(np.random.default_rng(21), 2_000_000)
+    got = np.zeros_like(y)
+    twin.dt_atan2(_p(y), _p(x), y.size, _p(got))
+    want = oracle.atan2f(y, x)
+    nan = np.isnan(want)
+    assert np.array_equal(np.isnan(got), nan)
+    assert np.array_equal(got.view(np.uint32)[~nan], want.view(np.uint32)[~nan])
+
+
+def test_device_alpha_source_on_reference_golden(twin, oracle, golden):
+    g = np.load(os.path.join(GOLDEN, "alpha.npz"))
+    od = np.ascontiguousarray(g["od"])
+    got = np.array([twin.dt_hash_float(_p(v[:3].copy()), _p(v[3:].copy())) for v in od], dtype=np.float32)
+    assert np.array_equal(got.view(np.uint32), g["hashes"].view(np.uint32))
+    tv = golden["tri_vectors"]
+    assert _pairs(twin, twin.dt_spawn_origin, tv["rays"], tv["tris"], g["spawn_hit"], g["spawn"]) > 3000
+    # GeometricPrimitive::Intersect over one triangle: the device loop against the checker's recursion
+    rng = np.random.default_rng(9)
+    rays, tris = np.ascontiguousarray(tv["rays"]), np.ascontiguousarray(tv["tris"])
+    alpha = rng.random(len(rays)).astype(np.float32)
+    alpha[::5] = 0.0
+    alpha[1::5] = 1.0
+    ignored = 0
+    for i in range(len(rays)):
+        a, b = np.zeros(4, dtype=np.float32), np.zeros(4, dtype=np.float32)
+        h = twin.dt_alpha_triangle(_p(rays[i]), _p(tris[i]), float(alpha[i]), _p(a))
+        w = oracle.lib.nnbvh_oracle_alpha_triangle(_p(rays[i]), _p(tris[i]), ctypes.c_float(float(alpha[i])), _p(b))
+        assert bool(h) == bool(w), i
+        if h:
+            assert np.array_equal(a.view(np.uint32), b.view(np.uint32)), i
+        ignored += bool(tv["hit"][i]) and not h
+    assert ignored > 800            # the alpha test did remove hits
+
+
+def test_device_instance_ray_source_matches_checker(twin, oracle):
+    from tools.make_golden import instanced_scene
+    rng = np.random.default_rng(31)
+    _, _, inst, _ = instanced_scene(rng, T=10, K=200, obj_sizes=(5,))
+    rays = rand_rays(rng, 4000)
+    rays[2000:, 3] = rng.random(2000)
+    oracle.lib.nnbvh_oracle_instance_ray.argtypes = [ctypes.c_void_p] * 3
+    oracle.lib.nnbvh_oracle_instance_ray.restype = None
+    for i in range(len(rays)):
+        m = np.ascontiguousarray(inst[i % len(inst), 12:])
+        a, b = np.zeros(8, dtype=np.float32), np.zeros(8, dtype=np.float32)
+        twin.dt_instance_ray(_p(m), _p(rays[i]), _p(a))
+        oracle.lib.nnbvh_oracle_instance_ray(_p(m), _p(rays[i]), _p(b))
+        assert np.array_equal(a.view(np.uint32), b.view(np.uint32)), i
