@@ -242,6 +242,9 @@ BasicKernel(SceneDev sc, RayInput in, uint64_t n, nnbvh_hit *__restrict__ hits,
     }
 }
 
+// Everything below uses warp intrinsics, shared memory and PTX: device compilation only (the host twin of
+// tests/cpp/device_twin.cpp stops here).
+#ifdef __CUDACC__
 // ---------------------------------------------------------------------------
 // WideKernel
 // ---------------------------------------------------------------------------
@@ -482,5 +485,7 @@ __global__ void __launch_bounds__(256, MINB) WideKernel(WideParams p) {
         }
     }
 }
+
+#endif  // __CUDACC__
 
 }  // namespace nnbvh

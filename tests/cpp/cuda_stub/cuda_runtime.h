@@ -58,3 +58,9 @@ template <typename T>
 inline T __ldg(const T *p) {
     return *p;
 }
+
+// One "thread" at a time: the twin sets these and calls a __global__ function as an ordinary function.
+struct TwinDim3 {
+    unsigned x = 0, y = 0, z = 0;
+};
+inline thread_local TwinDim3 blockIdx, threadIdx, blockDim;

@@ -6,6 +6,9 @@
 // vectors and against the checker, so a slip in the device text is caught without a GPU.
 #include <algorithm>
 
+#include <vector>
+
+#include "../../nn_bvh_b200/csrc/alpha.cuh"
 #include "../../nn_bvh_b200/csrc/alpha_math.cuh"
 #include "../../nn_bvh_b200/csrc/atan2_host.cuh"
 #include "../../nn_bvh_b200/csrc/exact_math.cuh"
@@ -27,9 +30,77 @@ SphereDev SphereOf(const float *s28) {
     d.phiMax = (3.14159265358979323846f / 180) * clamp(s28[27], 0.f, 360.f);
     return d;
 }
+
+// What PackTrisKernel / BuildWideLayout (engine.cu) put on the device for the one-thread-per-ray kernels: three
+// float4 per ordered primitive, the flags in the first one's .w; `special` >= 0 marks a sphere / instance slot.
+std::vector<float4> Pack(const nnbvh_node *nodes, uint32_t nNodes, const float *tris9, uint32_t nPrims,
+                         const int32_t *special, uint32_t specialFlag) {
+    std::vector<uint8_t> last(nPrims, 0);
+    for (uint32_t i = 0; i < nNodes; ++i)
+        if (nodes[i].nPrimitives > 0) last[(uint32_t)nodes[i].offset + nodes[i].nPrimitives - 1] = 1;
+    std::vector<float4> out(3 * (size_t)nPrims);
+    for (uint32_t i = 0; i < nPrims; ++i) {
+        if (special && special[i] >= 0) {
+            out[3 * (size_t)i] = make_float4(__uint_as_float((uint32_t)special[i]), 0.f, 0.f,
+                                             __uint_as_float(specialFlag | (last[i] ? kTriLast : 0u)));
+            out[3 * (size_t)i + 1] = out[3 * (size_t)i + 2] = make_float4(0.f, 0.f, 0.f, 0.f);
+            continue;
+        }
+        const float *v = tris9 + 9 * (size_t)i;
+        uint32_t flags = 0;
+        if (TriangleDegenerate(v[0], v[1], v[2], v[3], v[4], v[5], v[6], v[7], v[8])) flags |= kTriDegenerate;
+        if (last[i]) flags |= kTriLast;
+        out[3 * (size_t)i] = make_float4(v[0], v[1], v[2], __uint_as_float(flags));
+        out[3 * (size_t)i + 1] = make_float4(v[3], v[4], v[5], 0.f);
+        out[3 * (size_t)i + 2] = make_float4(v[6], v[7], v[8], 0.f);
+    }
+    return out;
+}
+
+// Runs kernel(i) for every "thread" i < n, 128 to a block, as the engine launches the one-thread-per-ray kernels.
+template <typename F>
+void ForThreads(int64_t n, F kernel) {
+    blockDim.x = 128;
+    for (int64_t i = 0; i < n; ++i) {
+        blockIdx.x = (unsigned)(i / 128), threadIdx.x = (unsigned)(i % 128);
+        kernel();
+    }
+}
 }  // namespace
 
 extern "C" {
+
+// BasicKernel / AlphaKernel over a whole tree, one simulated thread per ray.  spheres28: NULL or the sphere
+// table with sphereOf[i] (-1 = triangle); alpha: NULL or one value per ordered primitive.  hits5: n x 5 words
+// or, with occluded != NULL, the any-hit answers.
+void dt_traverse(const void *nodes, uint32_t nNodes, const float *orderedTris9, uint32_t nPrims,
+                 const int32_t *sphereOf, const float *spheres28, uint32_t nSpheres, const float *alpha,
+                 const float *rays8, int64_t n, uint32_t *hits5, uint8_t *occluded) {
+    const nnbvh_node *nd = (const nnbvh_node *)nodes;
+    std::vector<float4> packed = Pack(nd, nNodes, orderedTris9, nPrims, spheres28 ? sphereOf : nullptr, kPrimSphere);
+    std::vector<SphereDev> sph(nSpheres);
+    for (uint32_t k = 0; k < nSpheres; ++k) sph[k] = SphereOf(spheres28 + 28 * (size_t)k);
+    SceneDev sc{};
+    sc.nodes = nd;
+    sc.tris = packed.data();
+    sc.nNodes = nNodes;
+    sc.nPrims = nPrims;
+    sc.spheres = spheres28 ? sph.data() : nullptr;
+    RayInput in{};
+    in.aos = reinterpret_cast<const float4 *>(rays8);
+    nnbvh_hit *hits = reinterpret_cast<nnbvh_hit *>(hits5);
+    const uint64_t un = (uint64_t)n;
+    if (alpha) {
+        if (occluded) ForThreads(n, [&] { AlphaKernel<true>(sc, alpha, in, un, hits, occluded); });
+        else ForThreads(n, [&] { AlphaKernel<false>(sc, alpha, in, un, hits, occluded); });
+    } else if (spheres28) {
+        if (occluded) ForThreads(n, [&] { BasicKernel<true, false, true>(sc, in, un, hits, occluded, nullptr, nullptr); });
+        else ForThreads(n, [&] { BasicKernel<false, false, true>(sc, in, un, hits, occluded, nullptr, nullptr); });
+    } else {
+        if (occluded) ForThreads(n, [&] { BasicKernel<true, false>(sc, in, un, hits, occluded, nullptr, nullptr); });
+        else ForThreads(n, [&] { BasicKernel<false, false>(sc, in, un, hits, occluded, nullptr, nullptr); });
+    }
+}
 
 // out4 = {t, b0, b1, b2}
 int dt_triangle(const float *ray8, const float *p, float *out4) {

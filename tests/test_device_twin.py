@@ -117,3 +117,49 @@ def test_device_instance_ray_source_matches_checker(twin, oracle):
         twin.dt_instance_ray(_p(m), _p(rays[i]), _p(a))
         oracle.lib.nnbvh_oracle_instance_ray(_p(m), _p(rays[i]), _p(b))
         assert np.array_equal(a.view(np.uint32), b.view(np.uint32)), i
+
+
+def _traverse(L, nodes, ordered_tris9, rays, sphere_of=None, spheres=None, alpha=None, any_hit=False):
+    L.dt_traverse.argtypes = [ctypes.c_void_p, ctypes.c_uint32, ctypes.c_void_p, ctypes.c_uint32, ctypes.c_void_p,
+                              ctypes.c_void_p, ctypes.c_uint32, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int64,
+                              ctypes.c_void_p, ctypes.c_void_p]
+    L.dt_traverse.restype = None
+    nodes = np.ascontiguousarray(nodes)
+    t = np.ascontiguousarray(ordered_tris9, dtype=np.float32)
+    rays = np.ascontiguousarray(rays, dtype=np.float32)
+    n = len(rays)
+    hits = np.zeros((n, 5), dtype=np.uint32)
+    occ = np.zeros(n, dtype=np.uint8)
+    so = None if sphere_of is None else np.ascontiguousarray(sphere_of, dtype=np.int32)
+    sp = None if spheres is None else np.ascontiguousarray(spheres, dtype=np.float32)
+    al = None if alpha is None else np.ascontiguousarray(alpha, dtype=np.float32)
+    L.dt_traverse(_p(nodes), len(nodes), _p(t), len(t), None if so is None else _p(so), None if sp is None else _p(sp),
+                  0 if sp is None else len(sp), None if al is None else _p(al), _p(rays), n, _p(hits),
+                  _p(occ) if any_hit else None)
+    return occ if any_hit else hits
+
+
+def test_device_kernels_whole_traversal_on_reference_golden(twin, golden):
+    """BasicKernel and AlphaKernel themselves -- the one-thread-per-ray kernels, called as ordinary functions with
+    blockIdx / threadIdx set per ray -- over the reference's trees: closest hits and IntersectP equal the reference's."""
+    g = golden["scene_small"]
+    for split in ("sah", "middle"):
+        order = g[f"{split}_order"]
+        ot = g["tris"][order]
+        assert np.array_equal(_traverse(twin, g[f"{split}_nodes"], ot, g["rays"]), g[f"{split}_hits"])
+        assert np.array_equal(_traverse(twin, g[f"{split}_nodes"], ot, g["rays"], any_hit=True), g[f"{split}_occ"])
+    a = np.load(os.path.join(GOLDEN, "alpha.npz"))
+    order = a["order"]
+    assert np.array_equal(_traverse(twin, a["nodes"], a["tris"][order], a["rays"], alpha=a["alpha"][order]), a["hits"])
+    assert np.array_equal(_traverse(twin, a["nodes"], a["tris"][order], a["rays"], alpha=a["alpha"][order], any_hit=True),
+                          a["occ"])
+    s = np.load(os.path.join(GOLDEN, "sphere_vectors.npz"))
+    T = len(s["mixed_tris"])
+    order = s["mixed_order"]
+    so = np.where(order >= T, order - T, -1).astype(np.int32)
+    ot = np.zeros((len(order), 9), dtype=np.float32)
+    ot[order < T] = s["mixed_tris"][order[order < T]]
+    assert np.array_equal(_traverse(twin, s["mixed_nodes"], ot, s["mixed_rays"], sphere_of=so, spheres=s["mixed_spheres"]),
+                          s["mixed_hits"])
+    assert np.array_equal(_traverse(twin, s["mixed_nodes"], ot, s["mixed_rays"], sphere_of=so, spheres=s["mixed_spheres"],
+                                    any_hit=True), s["mixed_occ"])

@@ -1,8 +1,8 @@
 """tests/test_zz_alpha_gpu.py -- alpha-tested primitives on the device (csrc/alpha.cuh, nnbvh_upload_scene_alpha).
 
 The device kernel was written after this round's GPU budget was spent: it compiles for sm_100a (and leaves the SASS
-of every other kernel unchanged), its arithmetic is the oracle's (tests/test_alpha.py pins that to the reference), but
-it has NOT yet been run on a GPU.  Until it has, these tests are expected-to-fail-or-pass (xfail, non-strict): a pass
+of every other kernel unchanged), its source -- arithmetic and traversal loop -- reproduces the reference's golden
+answers when compiled for the host (tests/test_device_twin.py), but it has NOT yet been run on a GPU.  Until it has, these tests are expected-to-fail-or-pass (xfail, non-strict): a pass
 shows up as XPASS.  The file sorts last so that nothing else runs after a kernel nobody has executed yet.
 """
 import os
