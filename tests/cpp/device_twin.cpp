@@ -148,4 +148,48 @@ void dt_instance_ray(const float *primitiveFromRender12, const float *ray8, floa
     local8[4] = d[0], local8[5] = d[1], local8[6] = d[2], local8[7] = ray8[7];
 }
 
+// BasicKernel<ANY, false, false, INST = true> over an instanced scene (the layout nnbvh_upload_scene_instanced builds):
+// inst24[k] = {renderFromPrimitive, primitiveFromRender}, instObject[k]; object j's tree is objNodes[objNodeBase[j] ..
+// objNodeBase[j+1]) and its ordered triangles objTris9[objPrimBase[j] .. objPrimBase[j+1]).
+void dt_traverse_instanced(const void *nodes, uint32_t nNodes, const float *orderedTris9, uint32_t nPrims,
+                           const int32_t *instanceOf, const float *inst24, const int32_t *instObject, uint32_t nInst,
+                           const void *objNodes, const int32_t *objNodeBase, const float *objTris9,
+                           const int32_t *objPrimBase, uint32_t nObjects, const float *rays8, int64_t n,
+                           uint32_t *hits5, uint32_t *inner, uint8_t *occluded) {
+    const nnbvh_node *nd = (const nnbvh_node *)nodes, *on = (const nnbvh_node *)objNodes;
+    std::vector<float4> packed = Pack(nd, nNodes, orderedTris9, nPrims, instanceOf, kPrimInstance);
+    std::vector<float4> objPacked;
+    for (uint32_t j = 0; j < nObjects; ++j) {
+        const uint32_t nb = (uint32_t)objNodeBase[j], ne = (uint32_t)objNodeBase[j + 1];
+        const uint32_t pb = (uint32_t)objPrimBase[j], pe = (uint32_t)objPrimBase[j + 1];
+        std::vector<float4> one = Pack(on + nb, ne - nb, objTris9 + 9 * (size_t)pb, pe - pb, nullptr, 0);
+        objPacked.insert(objPacked.end(), one.begin(), one.end());
+    }
+    std::vector<InstanceDev> inst(nInst);
+    for (uint32_t k = 0; k < nInst; ++k) {
+        for (int c = 0; c < 12; ++c) inst[k].mInv[c] = inst24[24 * (size_t)k + 12 + c];
+        const int j = instObject[k];
+        inst[k].nodeBase = (uint32_t)objNodeBase[j];
+        inst[k].primBase = (uint32_t)objPrimBase[j];
+        inst[k].nNodes = (uint32_t)(objNodeBase[j + 1] - objNodeBase[j]);
+        inst[k].pad = 0;
+    }
+    SceneDev sc{};
+    sc.nodes = nd;
+    sc.tris = packed.data();
+    sc.nNodes = nNodes;
+    sc.nPrims = nPrims;
+    sc.instances = inst.data();
+    sc.objNodes = on;
+    sc.objTris = objPacked.data();
+    RayInput in{};
+    in.aos = reinterpret_cast<const float4 *>(rays8);
+    nnbvh_hit *hits = reinterpret_cast<nnbvh_hit *>(hits5);
+    const uint64_t un = (uint64_t)n;
+    if (occluded)
+        ForThreads(n, [&] { BasicKernel<true, false, false, true>(sc, in, un, hits, occluded, nullptr, nullptr, nullptr); });
+    else
+        ForThreads(n, [&] { BasicKernel<false, false, false, true>(sc, in, un, hits, occluded, nullptr, nullptr, inner); });
+}
+
 }  // extern "C"

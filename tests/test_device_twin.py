@@ -163,3 +163,30 @@ def test_device_kernels_whole_traversal_on_reference_golden(twin, golden):
                           s["mixed_hits"])
     assert np.array_equal(_traverse(twin, s["mixed_nodes"], ot, s["mixed_rays"], sphere_of=so, spheres=s["mixed_spheres"],
                                     any_hit=True), s["mixed_occ"])
+
+
+def test_device_instanced_kernel_on_reference_golden(twin):
+    """BasicKernel with the two-level traversal (InstanceRay + InnerTraverse) over the reference's instanced golden
+    scene: hit records, the primitive inside the object and IntersectP."""
+    g = np.load(os.path.join(GOLDEN, "instanced.npz"))
+    f = twin.dt_traverse_instanced
+    f.restype = None
+    f.argtypes = [ctypes.c_void_p, ctypes.c_uint32, ctypes.c_void_p, ctypes.c_uint32, ctypes.c_void_p, ctypes.c_void_p,
+                  ctypes.c_void_p, ctypes.c_uint32, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p,
+                  ctypes.c_uint32, ctypes.c_void_p, ctypes.c_int64, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p]
+    c = lambda k, dt: np.ascontiguousarray(g[k], dtype=dt)
+    nodes, tris, inst_of = c("sc_nodes", np.uint32), c("sc_ordered_tris9", np.float32), c("sc_instance_of", np.int32)
+    inst24, inst_obj = c("sc_inst24", np.float32), c("sc_inst_object", np.int32)
+    obj_nodes, obj_tris = c("sc_obj_nodes", np.uint32), c("sc_obj_tris", np.float32)
+    J = int(g["n_objects"])
+    nbase = np.ascontiguousarray(np.concatenate([g["sc_obj_node_base"], [len(obj_nodes)]]), dtype=np.int32)
+    pbase = np.ascontiguousarray(np.concatenate([g["sc_obj_prim_base"], [len(obj_tris)]]), dtype=np.int32)
+    rays = c("rays", np.float32)
+    n = len(rays)
+    hits, inner, occ = np.zeros((n, 5), np.uint32), np.zeros(n, np.uint32), np.zeros(n, np.uint8)
+    args = (_p(nodes), len(nodes), _p(tris), len(tris), _p(inst_of), _p(inst24), _p(inst_obj), len(inst24), _p(obj_nodes),
+            _p(nbase), _p(obj_tris), _p(pbase), J, _p(rays), n)
+    f(*args, _p(hits), _p(inner), None)
+    assert np.array_equal(hits, g["hits"]) and np.array_equal(inner, g["inner"])
+    f(*args, _p(hits), _p(inner), _p(occ))
+    assert np.array_equal(occ, g["occ"])
