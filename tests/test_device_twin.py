@@ -190,3 +190,28 @@ def test_device_instanced_kernel_on_reference_golden(twin):
     assert np.array_equal(hits, g["hits"]) and np.array_equal(inner, g["inner"])
     f(*args, _p(hits), _p(inner), _p(occ))
     assert np.array_equal(occ, g["occ"])
+
+
+def test_device_alpha_kernel_matches_checker_at_size(twin, oracle):
+    """The seeded scene of tests/test_zz_alpha_gpu.py (smaller ray count), AlphaKernel's source on the host against
+    the checker: product-built tree, unnormalised directions, finite tMax, alpha in {0, (0,1), 1}."""
+    import nn_bvh_b200 as nb
+    rng = np.random.default_rng(44)
+    T, N = 60_000, 80_000
+    c = rng.random((T, 1, 3), dtype=np.float32)
+    tris = ((c + np.float32(0.02) * (rng.random((T, 3, 3), dtype=np.float32) * 2 - 1)).reshape(T, 9)
+            + np.float32(0)).astype(np.float32)
+    a = rng.random(T).astype(np.float32)
+    a[::3] = 1.0
+    a[1::9] = 0.0
+    nodes, order = nb.build_bvh(tris, 4, "sah")
+    nodes_u = nodes.view(np.uint32).reshape(-1, 8)
+    ot, oa = tris[order], a[order]
+    rays = rand_rays(rng, N)
+    rays[N // 2:, 3] = rng.random(N - N // 2)
+    rays[::5, 4:7] *= np.float32(3.7)
+    want = oracle.intersect_alpha(nodes_u, ot, oa, rays)
+    assert np.array_equal(_traverse(twin, nodes_u, ot, rays, alpha=oa), want)
+    assert (oracle.intersect(nodes_u, ot, rays) != want).any(axis=1).sum() > 2000
+    assert np.array_equal(_traverse(twin, nodes_u, ot, rays, alpha=oa, any_hit=True),
+                          oracle.intersect_alpha(nodes_u, ot, oa, rays, any_hit=True))
