@@ -148,6 +148,27 @@ void dt_instance_ray(const float *primitiveFromRender12, const float *ray8, floa
     local8[4] = d[0], local8[5] = d[1], local8[6] = d[2], local8[7] = ray8[7];
 }
 
+// BasicKernel<ANY, COUNT = true>: the reference's per-ray statistics (bvhNodesVisited, nTriTests) on a triangle scene
+void dt_traverse_counters(const void *nodes, uint32_t nNodes, const float *orderedTris9, uint32_t nPrims,
+                          const float *rays8, int64_t n, int anyHit, uint32_t *nodesVisited, uint32_t *triTests) {
+    const nnbvh_node *nd = (const nnbvh_node *)nodes;
+    std::vector<float4> packed = Pack(nd, nNodes, orderedTris9, nPrims, nullptr, 0);
+    SceneDev sc{};
+    sc.nodes = nd;
+    sc.tris = packed.data();
+    sc.nNodes = nNodes;
+    sc.nPrims = nPrims;
+    RayInput in{};
+    in.aos = reinterpret_cast<const float4 *>(rays8);
+    std::vector<nnbvh_hit> hits((size_t)n);
+    std::vector<uint8_t> occ((size_t)n);
+    const uint64_t un = (uint64_t)n;
+    if (anyHit)
+        ForThreads(n, [&] { BasicKernel<true, true>(sc, in, un, hits.data(), occ.data(), nodesVisited, triTests); });
+    else
+        ForThreads(n, [&] { BasicKernel<false, true>(sc, in, un, hits.data(), occ.data(), nodesVisited, triTests); });
+}
+
 // BasicKernel<ANY, false, false, INST = true> over an instanced scene (the layout nnbvh_upload_scene_instanced builds):
 // inst24[k] = {renderFromPrimitive, primitiveFromRender}, instObject[k]; object j's tree is objNodes[objNodeBase[j] ..
 // objNodeBase[j+1]) and its ordered triangles objTris9[objPrimBase[j] .. objPrimBase[j+1]).

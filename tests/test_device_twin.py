@@ -215,3 +215,23 @@ def test_device_alpha_kernel_matches_checker_at_size(twin, oracle):
     assert (oracle.intersect(nodes_u, ot, rays) != want).any(axis=1).sum() > 2000
     assert np.array_equal(_traverse(twin, nodes_u, ot, rays, alpha=oa, any_hit=True),
                           oracle.intersect_alpha(nodes_u, ot, oa, rays, any_hit=True))
+
+
+def test_device_kernel_counters_on_reference_golden(twin, golden):
+    """BasicKernel's COUNT instantiation: the totals of bvhNodesVisited / nTriTests the reference itself reported."""
+    g = golden["scene_small"]
+    f = twin.dt_traverse_counters
+    f.restype = None
+    f.argtypes = [ctypes.c_void_p, ctypes.c_uint32, ctypes.c_void_p, ctypes.c_uint32, ctypes.c_void_p, ctypes.c_int64,
+                  ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p]
+    for split in ("sah", "equal"):
+        nodes = np.ascontiguousarray(g[f"{split}_nodes"])
+        ot = np.ascontiguousarray(g["tris"][g[f"{split}_order"]], dtype=np.float32)
+        rays = np.ascontiguousarray(g["rays"], dtype=np.float32)
+        n = len(rays)
+        tot = []
+        for any_hit in (0, 1):
+            nv, tt = np.zeros(n, np.uint32), np.zeros(n, np.uint32)
+            f(_p(nodes), len(nodes), _p(ot), len(ot), _p(rays), n, any_hit, _p(nv), _p(tt))
+            tot += [int(nv.sum()), int(tt.sum())]
+        assert tuple(tot) == tuple(int(v) for v in g[f"{split}_stats"])
