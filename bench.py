@@ -9,8 +9,9 @@ diffuse-bounce rays through BVHAggregate::Intersect (closest hit) plus `--rays`
 shadow rays through IntersectP (any hit) -- BASELINE.json configs[1] (default
 8M + 8M).  The conference scene is missing from the reference tree
 (.MISSING_LARGE_BLOBS:12); the workload is its stand-in, the reference's own
-bathroom scene (592k triangles) from scene_cache/, else a procedural room, and
-config.workload says which.
+bathroom scene (592 188 triangles) from scene_cache/ (exported by
+__graft_entry__.build()).  A missing scene file is an error unless
+--allow-procedural is given; config.workload names what was really traced.
 
 value  : whole-job Mrays/s, rays resident in HBM, CUDA-event timed (max over ranks).
 e2e    : same metric through the C ABI with pinned HOST buffers (H2D/D2H inside).
@@ -46,6 +47,9 @@ def parse():
     ap.add_argument("--rays", type=int, default=8 << 20, help="rays per kind per step per GPU")
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="budget of the cpu_baseline leg")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--allow-procedural", action="store_true",
+                    help="trace a procedural stand-in when scene_cache/<scene> is missing (NOT a BASELINE.json "
+                         "config; without this flag a missing scene is an error)")
     ap.add_argument("--exchange", default="peer", choices=["peer", "nccl"],
                     help="N>1: how hit records reach rank 0: copy engines into a peer-mapped window, or an NCCL gather")
     return ap.parse_args()
@@ -106,7 +110,10 @@ def load_workload(args, trace, rank):
     import nn_bvh_b200 as nb
     from nn_bvh_b200 import rays as R
     from nn_bvh_b200 import scenes
-    tris, cam, name = scenes.load(args.scene)
+    try:
+        tris, cam, name = scenes.load(args.scene, allow_procedural=args.allow_procedural)
+    except FileNotFoundError as e:
+        raise SystemExit(f"bench.py: {e}")
     nodes, order = nb.build_bvh(tris, 4, "sah")     # reference defaults (aggregates.cpp:727,742)
     ordered = tris[order]
     return dict(tris=tris, cam=cam, nodes=nodes, order=order, ordered=ordered, name=name)

@@ -3,8 +3,9 @@
 Geometry comes from scene_cache/<name>.tris.npy, exported once from the
 reference's shipped scenes by tools/export_scenes.py (the GPU box has no
 /root/reference; the cache travels with the working tree).  When a cache file
-is missing a deterministic procedural stand-in of similar size is generated and
-the returned name says so -- a bench line always names what it really traced.
+is missing load() raises; only with allow_procedural=True is a deterministic
+procedural stand-in of similar size generated, and the returned name says so -- a
+bench line always names what it really traced.
 
 Nothing here intersects anything: this is input preparation for
 GPUBVHAggregate (the reference's equivalent is its parser + CreateAggregate,
@@ -126,7 +127,7 @@ def load_spheres(name: str):
                         np.array([s["phimax"] for s in sph], dtype=np.float32))
 
 
-def load(name: str, allow_procedural: bool = True):
+def load(name: str, allow_procedural: bool = False):
     """-> (tris9 float32 (T,9), camera dict, workload name actually loaded)."""
     path = os.path.join(CACHE, name + ".tris.npy")
     if os.path.exists(path):
@@ -142,6 +143,9 @@ def load(name: str, allow_procedural: bool = True):
         tris = synthetic_soup(n)
         return tris, _camera_from_meta({}, tris), f"synthetic:{n}"
     if not allow_procedural:
-        raise FileNotFoundError(path)
+        raise FileNotFoundError(
+            f"{path} is missing: run `python -c 'import __graft_entry__ as g; g.export_scenes()'` where "
+            "/root/reference exists (build() does), or pass allow_procedural=True / --allow-procedural "
+            "to trace a procedural stand-in that is NOT a BASELINE.json config")
     tris, cam = procedural_room()
     return tris, cam, f"procedural_room(stand-in for {name}: scene_cache missing)"

@@ -256,6 +256,9 @@ def test_reference_scenes_with_their_spheres(oracle, name):
     from inside (scene files: killeroo-simple-v4.pbrt:28, crown.pbrt:108)."""
     import nn_bvh_b200 as nb
     from nn_bvh_b200 import rays as raygen, scenes
+    if not os.path.exists(os.path.join(ROOT, "scene_cache", name + ".tris.npy")):
+        pytest.skip(f"scene_cache/{name} not present on this machine (build() exports it where "
+                    "/root/reference exists)")
     tris, cam, loaded = scenes.load(name, allow_procedural=False)
     sph = scenes.load_spheres(name)
     assert sph is not None and len(sph) == 1

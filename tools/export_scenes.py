@@ -4,8 +4,8 @@
 Runs only where /root/reference exists (this container).  Writes
 scene_cache/<name>.tris.npy ((T,9) float32, world space) and <name>.json
 (camera, counts).  scene_cache/ is git-ignored but travels to the GPU box with
-the gpurun snapshot, exactly like built .so files; nn_bvh_b200.scenes falls back
-to procedural geometry when a cache file is absent.
+the gpurun snapshot, exactly like built .so files; __graft_entry__.build() calls
+main() for every cache file that is missing.
 
 killeroos needs loop subdivision: it is done by the reference's own
 LoopSubdivide through oracle/_ref (tools may use the oracle; the product may not).
