@@ -253,6 +253,26 @@ int nnbvh_intersect_closest(nnbvh_engine *e, const nnbvh_ray *rays, uint64_t n,
 int nnbvh_intersect_any(nnbvh_engine *e, const nnbvh_ray *rays, uint64_t n,
                         uint8_t *occluded);
 
+/* nnbvh_intersect_closest for callers that cannot allocate: code under CUDA graph capture, tight
+ * serving loops, harnesses that forbid cudaMalloc.  NO COUNTERPART IN THE REFERENCE.
+ * Same kernels and bit-identical results as nnbvh_intersect_closest
+ * with device pointers, but the per-launch scratch (ray cursors, the list of rays deferred to the
+ * exact slab test) lives in a file-scope `static __device__` array inside the library -- 256 B +
+ * 4 B x NNBVH_NOALLOC_MAX_RAYS per GPU that loads the library, held until the process exits -- so
+ * the call makes no cudaMalloc / cudaFree or any allocating library call: one cudaMemsetAsync and
+ * the two traversal launches on the engine's stream, asynchronously.
+ *   - raysDev / hitsDev must be DEVICE pointers (host buffers would need staging memory);
+ *   - n > NNBVH_NOALLOC_MAX_RAYS fails with NNBVH_ERR_INVALID (split the batch, or use
+ *     nnbvh_intersect_closest); no ray-ordering pre-pass runs (it needs O(n) buffers);
+ *   - triangle and sphere scenes only (alpha / instanced scenes: NNBVH_ERR_INVALID);
+ *   - every call on a device shares the one array: calls that OVERLAP on the GPU (different
+ *     streams, engines or threads without ordering between them) race; calls ordered on one
+ *     stream are safe, the library clears what must start at zero at the start of each call;
+ *   - the array's address is resolved and the kernels are loaded by nnbvh_create. */
+#define NNBVH_NOALLOC_MAX_RAYS (1u << 20)
+int nnbvh_intersect_closest_noalloc(nnbvh_engine *e, const nnbvh_ray *raysDev, uint64_t n,
+                                    nnbvh_hit *hitsDev);
+
 /* SoA forms for the wavefront queues (SOA<RayWorkItem>, wavefront/workitems.soa;
  * wavefront/aggregate.cpp:34-68).  tMax may be NULL (= Infinity). */
 int nnbvh_intersect_closest_soa(nnbvh_engine *e, const float *ox, const float *oy,

@@ -287,6 +287,12 @@ class GPUBVHAggregate {
     void IntersectPBatch(const nnbvh_ray *rays, uint64_t n, uint8_t *occluded) const {
         Check(nnbvh_intersect_any(e_, rays, n, occluded));
     }
+    // IntersectBatch for callers that cannot allocate (CUDA graph capture, serving loops): DEVICE pointers,
+    // n <= NNBVH_NOALLOC_MAX_RAYS, scratch in the library's static device array; calls that overlap on the
+    // GPU race (nnbvh.h nnbvh_intersect_closest_noalloc; no counterpart in the reference).
+    void IntersectBatchNoAlloc(const nnbvh_ray *raysDev, uint64_t n, nnbvh_hit *hitsDev) const {
+        Check(nnbvh_intersect_closest_noalloc(e_, raysDev, n, hitsDev));
+    }
     // The wavefront queues' SoA layout (SOA<RayWorkItem>, wavefront/workitems.soa); tMax may be null.
     void IntersectBatchSoA(const float *ox, const float *oy, const float *oz, const float *dx,
                            const float *dy, const float *dz, const float *tMax, uint64_t n,

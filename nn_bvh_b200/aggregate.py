@@ -338,6 +338,13 @@ class GPUBVHAggregate:
         capi.check(capi.lib().nnbvh_intersect_closest(self._h, capi.ptr(rays), n, capi.ptr(hits)))
         return hits
 
+    def IntersectBatchNoAlloc(self, rays, hits, n=None):
+        """IntersectBatch for device tensors through nnbvh_intersect_closest_noalloc: at most
+        capi.NOALLOC_MAX_RAYS rays, scratch in the library's static device array, no allocation."""
+        n = self._count(rays, n)
+        capi.check(capi.lib().nnbvh_intersect_closest_noalloc(self._h, capi.ptr(rays), n, capi.ptr(hits)))
+        return hits
+
     def IntersectBatchInstanced(self, rays, hits=None, inner=None, n=None):
         """Instanced scenes: (hits, inner) with inner[i] = ordered primitive inside the hit object
         (MISS for a top-level triangle or a miss)."""

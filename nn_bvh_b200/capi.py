@@ -16,6 +16,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(HERE, "libnnbvh.so")
 
 MISS = 0xFFFFFFFF
+NOALLOC_MAX_RAYS = 1 << 20   # NNBVH_NOALLOC_MAX_RAYS
 KERNEL_AUTO, KERNEL_BASIC, KERNEL_WIDE, KERNEL_STEP = 0, 1, 2, 3
 SPLIT = {"sah": 0, "hlbvh": 1, "middle": 2, "equal": 3}
 
@@ -36,6 +37,7 @@ SYMBOLS = [
     "nnbvh_pointer_kind", "nnbvh_copy_to_host", "nnbvh_build_bvh_bounds", "nnbvh_sphere_bounds",
     "nnbvh_upload_scene_mixed", "nnbvh_upload_scene_alpha", "nnbvh_test_spheres", "nnbvh_test_atan2", "nnbvh_instance_bounds",
     "nnbvh_upload_scene_instanced", "nnbvh_intersect_closest_instanced", "nnbvh_intersect_closest_instanced_soa", "nnbvh_clone",
+    "nnbvh_intersect_closest_noalloc",
 ]
 
 
@@ -72,6 +74,7 @@ def lib() -> ctypes.CDLL:
     L.nnbvh_upload_scene.argtypes = [vp, vp, u32, vp, u32]
     L.nnbvh_intersect_closest.argtypes = [vp, vp, u64, vp]
     L.nnbvh_intersect_any.argtypes = [vp, vp, u64, vp]
+    L.nnbvh_intersect_closest_noalloc.argtypes = [vp, vp, u64, vp]
     L.nnbvh_intersect_closest_soa.argtypes = [vp] * 8 + [u64, vp]
     L.nnbvh_intersect_any_soa.argtypes = [vp] * 8 + [u64, vp]
     L.nnbvh_intersect_counters.argtypes = [vp, vp, u64, i32, vp, vp, vp, vp]

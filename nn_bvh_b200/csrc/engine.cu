@@ -12,6 +12,7 @@
 #include <cstring>
 #include <deque>
 #include <memory>
+#include <mutex>
 #include <vector>
 
 #include "../../include/nnbvh.h"
@@ -165,6 +166,10 @@ struct nnbvh_engine {
     uint32_t binMinNodes = 1u << 18; // nor for scenes the L1s hold anyway (measured: killeroos loses 11-14 %)
 };
 
+// nnbvh_intersect_closest_noalloc's set-up (end of this file): resolves the device address of the
+// file-scope scratch array for `device`, which must be current.  Called by nnbvh_create.
+static int NoAllocSetup(int device);
+
 extern "C" const char *nnbvh_last_error(void) { return g_err; }
 extern "C" const char *nnbvh_version(void) { return "nnbvh-b200 0.1 (sm_100a)"; }
 
@@ -237,6 +242,8 @@ extern "C" int nnbvh_create(const nnbvh_options *opts, nnbvh_engine **out) {
         CU(cudaEventCreateWithFlags(&s.done, cudaEventDisableTiming));
         CU(cudaMalloc(&s.scratch.cursor, kCursorWords * sizeof(unsigned long long)));
     }
+    int rcSetup = NoAllocSetup(dev);
+    if (rcSetup) return rcSetup;
     *out = e;
     return NNBVH_OK;
 }
@@ -1571,5 +1578,104 @@ extern "C" int nnbvh_read_bandwidth_probe(nnbvh_engine *e, uint64_t bytes, uint3
     cudaFree(buf);
     cudaFree(sink);
     *gbs = (float)((double)nChunks * 32.0 * iters / (ms * 1e-3) / 1e9);
+    return NNBVH_OK;
+}
+
+// ---------------------------------------------------------------------------
+// nnbvh_intersect_closest_noalloc: the closest-hit StepKernel path for callers that cannot allocate
+// (CUDA graph capture, serving loops, harnesses that forbid cudaMalloc).  No counterpart in the
+// reference.
+//
+// The StepKernel path needs per-launch scratch: the ray cursors / deferred-ray count (kCursorWords
+// 64-bit words) and the list of rays deferred to the exact slab test (one uint32 per ray).  The
+// ordinary entry points keep them in cudaMalloc'ed buffers that grow on demand (Scratch); this one
+// keeps them in ONE file-scope device array of fixed size, so it calls nothing that allocates:
+// cudaMemsetAsync of the cursor words, two kernel launches.  Every GPU that loads libnnbvh.so holds
+// the array (256 B + 4 B x NNBVH_NOALLOC_MAX_RAYS = 4 MiB + 256 B) until the process exits.
+//
+// All calls on one device share the array: calls that overlap on the GPU (two streams, two engines,
+// two threads) race on the cursors.  Calls ordered on one stream are safe; the cursor words are
+// cleared at the start of each call, the deferred list needs no clearing (only entries below the
+// freshly counted nDeferred are read).
+// ---------------------------------------------------------------------------
+namespace nnbvh {
+constexpr size_t kNoAllocDeferredAt = 256;  // bytes: cursor words first, the deferred list after them
+static_assert(kCursorWords * sizeof(unsigned long long) <= kNoAllocDeferredAt, "cursor words fit the header");
+static __device__ __align__(256) unsigned char g_noAllocScratch[kNoAllocDeferredAt +
+                                                                sizeof(uint32_t) * (size_t)NNBVH_NOALLOC_MAX_RAYS];
+// In host code `g_noAllocScratch` is only a stand-in for the symbol, NOT a device address: the address
+// is asked for once per device (cudaGetSymbolAddress, that device current) and kept here.
+constexpr int kNoAllocMaxDevices = 64;
+static void *g_noAllocPtr[kNoAllocMaxDevices] = {};
+}  // namespace nnbvh
+
+static int NoAllocSetup(int device) {
+    if (device < 0 || device >= kNoAllocMaxDevices) return NNBVH_OK;  // the entry point reports it
+    static std::mutex mu;
+    std::lock_guard<std::mutex> lock(mu);
+    if (g_noAllocPtr[device]) return NNBVH_OK;
+    void *ptr = nullptr;
+    CU(cudaGetSymbolAddress(&ptr, g_noAllocScratch));
+    if (!ptr) return SetError(NNBVH_ERR_CUDA, "cudaGetSymbolAddress(g_noAllocScratch) returned NULL on device %d", device);
+    // Load the kernels the entry point launches now (CUDA loads functions lazily on first use, and
+    // that load may allocate): default instantiations; an engine created with NNBVH_WIDE_MINB set
+    // loads its own on its first ordinary batch.
+    cudaFuncAttributes fa;
+    CU(cudaFuncGetAttributes(&fa, StepKernel<false, false, 5>));
+    CU(cudaFuncGetAttributes(&fa, StepKernel<false, true, 5>));
+    CU(cudaFuncGetAttributes(&fa, StepKernel<false, false, 4, false, true>));
+    CU(cudaFuncGetAttributes(&fa, StepKernel<false, true, 4, false, true>));
+    g_noAllocPtr[device] = ptr;
+    return NNBVH_OK;
+}
+
+extern "C" int nnbvh_intersect_closest_noalloc(nnbvh_engine *e, const nnbvh_ray *raysDev, uint64_t n,
+                                               nnbvh_hit *hitsDev) {
+    if (!e) return SetError(NNBVH_ERR_INVALID, "nnbvh_intersect_closest_noalloc: engine is NULL");
+    if (!e->haveScene) return SetError(NNBVH_ERR_NOSCENE, "no scene uploaded");
+    if (n == 0) return NNBVH_OK;
+    if (n > (uint64_t)NNBVH_NOALLOC_MAX_RAYS)
+        return SetError(NNBVH_ERR_INVALID, "nnbvh_intersect_closest_noalloc: %llu rays exceed NNBVH_NOALLOC_MAX_RAYS = %u "
+                        "(the static scratch array holds one deferred-list entry per ray); split the batch or "
+                        "use nnbvh_intersect_closest", (unsigned long long)n, (unsigned)NNBVH_NOALLOC_MAX_RAYS);
+    if (!raysDev || !hitsDev) return SetError(NNBVH_ERR_INVALID, "nnbvh_intersect_closest_noalloc: NULL rays / hits");
+    if (e->hasAlpha || e->hasInstances)
+        return SetError(NNBVH_ERR_INVALID, "nnbvh_intersect_closest_noalloc: scenes with alpha-tested or instanced "
+                                           "primitives run other kernels; use nnbvh_intersect_closest");
+    if (e->device < 0 || e->device >= kNoAllocMaxDevices || !g_noAllocPtr[e->device])
+        return SetError(NNBVH_ERR_CUDA, "nnbvh_intersect_closest_noalloc: no scratch address for device %d", e->device);
+    CU(cudaSetDevice(e->device));
+    if (!IsDevicePtr(raysDev) || !IsDevicePtr(hitsDev))
+        return SetError(NNBVH_ERR_INVALID, "nnbvh_intersect_closest_noalloc: rays and hits must be device pointers "
+                                           "(staging host buffers would need an allocation)");
+    unsigned char *base = static_cast<unsigned char *>(g_noAllocPtr[e->device]);
+    unsigned long long *cursor = reinterpret_cast<unsigned long long *>(base);
+    uint32_t *deferred = reinterpret_cast<uint32_t *>(base + kNoAllocDeferredAt);
+    cudaStream_t st = e->stream;
+    CU(cudaMemsetAsync(cursor, 0, kCursorWords * sizeof(unsigned long long), st));
+    StepParams sp{};
+    sp.sc = e->sc;
+    sp.in.aos = reinterpret_cast<const float4 *>(raysDev);
+    sp.n = n;
+    sp.hits = hitsDev;
+    sp.refillBelow = (uint32_t)std::min(32, std::max(1, e->refillBelow));
+    sp.leafQuorum = (uint32_t)std::min(32, std::max(1, e->leafQuorum));
+    sp.popLoop = (uint32_t)(e->popLoop != 0);
+    sp.sphereQuorum = (uint32_t)std::min(32, std::max(1, e->sphereQuorum));
+    if (e->boxesRegular && !e->exactOnly) {  // fast-slab launch; rays it cannot take go to the deferred list
+        sp.cursor = cursor;
+        sp.deferred = deferred;
+        sp.nDeferred = reinterpret_cast<uint32_t *>(cursor + 2);
+        LaunchStep<false, false>(e, st, sp);
+        ++e->launches;
+        sp.perm = deferred;
+        sp.nPtr = sp.nDeferred;
+        sp.deferred = nullptr;
+        sp.nDeferred = nullptr;
+    }
+    sp.cursor = cursor + 1;
+    LaunchStep<false, true>(e, st, sp);  // exact launch over the deferred rays (or over all of them)
+    ++e->launches;
+    CU(cudaGetLastError());
     return NNBVH_OK;
 }
