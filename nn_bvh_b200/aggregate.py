@@ -208,6 +208,13 @@ class GPUBVHAggregate:
         self.spheres = None
         self.ordered_sphere_index = None
         self.instances = None
+        has_sph = spheres is not None and len(spheres) > 0
+        has_inst = instances is not None and len(instances) > 0
+        if alpha is not None and (has_sph or has_inst):
+            raise ValueError("alpha-tested triangles cannot be combined with spheres or instances in one scene "
+                             "(nnbvh_upload_scene_alpha takes triangle-only lists)")
+        if has_sph and nodes is not None and ordered_sphere_index is None:
+            raise ValueError("a ready tree with spheres needs ordered_sphere_index (-1 = triangle)")
         if instances is not None and len(instances):
             if spheres is not None and len(spheres):
                 raise ValueError("a scene holds either spheres or instances")

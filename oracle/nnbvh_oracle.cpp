@@ -6,7 +6,7 @@
 // file:line it follows (paths relative to /root/reference/src/pbrt).
 //
 // Parity status: PINNED against the unmodified reference built into
-// oracle/_ref/libnnbvh_ref.so (tests/test_oracle_vs_ref.py) and against the
+// oracle/_ref/libnnbvh_ref.so (tests/test_oracle.py::test_oracle_vs_reference_live) and against the
 // golden vectors under tests/golden/ generated from that library.
 //
 // Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline /

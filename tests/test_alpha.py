@@ -5,7 +5,7 @@ is ignored when HashFloat(r.o, r.d) > alpha (always, for alpha <= 0), and the pr
 si->intr.SpawnRay(r.d); IntersectP is Intersect(...).has_value().  The oracle restates it for constant alpha
 values -- MurmurHash64A / HashFloat (util/hash.h), the triangle interaction's pHit / pError / n and
 OffsetRayOrigin (shapes.h:924-941, ray.h:75-92) -- and is pinned here to the reference, golden and live.
-The device side (csrc/alpha.cuh) is checked against this oracle in tests/test_zz_alpha_gpu.py.
+The device side (csrc/alpha.cuh) is checked against this oracle in tests/test_alpha_gpu.py.
 """
 import os
 

@@ -1,9 +1,8 @@
-"""tests/test_zz_alpha_gpu.py -- alpha-tested primitives on the device (csrc/alpha.cuh, nnbvh_upload_scene_alpha).
+"""tests/test_alpha_gpu.py -- alpha-tested primitives on the device (csrc/alpha.cuh, nnbvh_upload_scene_alpha).
 
-The device kernel was written after this round's GPU budget was spent: it compiles for sm_100a (and leaves the SASS
-of every other kernel unchanged), its source -- arithmetic and traversal loop -- reproduces the reference's golden
-answers when compiled for the host (tests/test_device_twin.py), but it has NOT yet been run on a GPU.  Until it has, these tests are expected-to-fail-or-pass (xfail, non-strict): a pass
-shows up as XPASS.  The file sorts last so that nothing else runs after a kernel nobody has executed yet.
+AlphaKernel through the C ABI against the reference's golden answers (tests/golden/alpha.npz, produced by the
+reference's own GeometricPrimitive, tools/make_golden.py) and against the oracle at size.  First run on a B200 in
+round 2 (gpurun_out r02a: both tests passed as XPASS under the round-1 xfail marks, which are gone).
 """
 import os
 
@@ -13,12 +12,9 @@ import pytest
 from conftest import GOLDEN, rand_rays
 
 MISS = 0xFFFFFFFF
-UNRUN = pytest.mark.xfail(reason="AlphaKernel has not been run on a GPU yet (written after the round's GPU budget)",
-                          strict=False)
 
 
 @pytest.mark.gpu
-@UNRUN
 def test_alpha_scene_gpu_matches_reference_golden():
     import nn_bvh_b200 as nb
     g = np.load(os.path.join(GOLDEN, "alpha.npz"))
@@ -31,7 +27,6 @@ def test_alpha_scene_gpu_matches_reference_golden():
 
 
 @pytest.mark.gpu
-@UNRUN
 def test_alpha_scene_gpu_matches_oracle_at_size(oracle):
     import nn_bvh_b200 as nb
     rng = np.random.default_rng(44)

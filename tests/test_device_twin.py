@@ -193,7 +193,7 @@ def test_device_instanced_kernel_on_reference_golden(twin):
 
 
 def test_device_alpha_kernel_matches_checker_at_size(twin, oracle):
-    """The seeded scene of tests/test_zz_alpha_gpu.py (smaller ray count), AlphaKernel's source on the host against
+    """The seeded scene of tests/test_alpha_gpu.py (smaller ray count), AlphaKernel's source on the host against
     the checker: product-built tree, unnormalised directions, finite tMax, alpha in {0, (0,1), 1}."""
     import nn_bvh_b200 as nb
     rng = np.random.default_rng(44)
