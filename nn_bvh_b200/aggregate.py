@@ -290,6 +290,25 @@ class GPUBVHAggregate:
                                             capi.ptr(self.ordered_tris9), len(self.ordered_tris9)))
 
     @classmethod
+    def FromDevice(cls, nodes_dev, n_nodes: int, ordered_tris9_dev, n_prims: int, device: int = -1,
+                   kernel: int = capi.KERNEL_AUTO):
+        """An aggregate over a flattened tree and ordered triangles that already live in DEVICE memory
+        (torch tensors or raw addresses): e.g. a scene one rank built and broadcast over NCCL, so that the
+        other ranks neither rebuild nor re-read it.  nnbvh_upload_scene validates the tree and
+        derives the wide layout as for host arrays.  `nodes` / `ordered_tris9` stay None on this object."""
+        self = object.__new__(cls)
+        L = capi.lib()
+        opts = capi.Options(device=device, kernel=kernel, smem_top_nodes=-1)
+        h = ctypes.c_void_p()
+        capi.check(L.nnbvh_create(ctypes.byref(opts), ctypes.byref(h)))
+        self._h = h
+        self.spheres = self.ordered_sphere_index = self.instances = None
+        self.nodes = self.ordered_tris9 = self.order = None
+        capi.check(L.nnbvh_upload_scene(h, capi.ptr(nodes_dev), int(n_nodes), capi.ptr(ordered_tris9_dev),
+                                        int(n_prims)))
+        return self
+
+    @classmethod
     def Create(cls, tris9, parameters: Optional[dict] = None, **kw):
         """BVHAggregate::Create (cpu/aggregates.cpp:725-744): "splitmethod" (default
         "sah"), "maxnodeprims" (default 4)."""
@@ -318,6 +337,8 @@ class GPUBVHAggregate:
 
     # ---- BVHAggregate surface -------------------------------------------------
     def Bounds(self):
+        if self.nodes is None:
+            raise RuntimeError("Bounds(): this aggregate was made from device arrays (FromDevice) and keeps no host tree")
         if len(self.nodes) == 0:
             raise RuntimeError("Bounds() of an empty aggregate (the reference CHECK(nodes)s)")
         return self.nodes[0]["bounds"].copy()

@@ -146,3 +146,45 @@ def random_rays(n: int, seed: int = 6, lo=-0.25, hi=1.25) -> np.ndarray:
     r["d"] = np.stack([rad * np.cos(phi), rad * np.sin(phi), z], 1).astype(np.float32)
     r["tMax"] = np.inf
     return r
+
+
+# ---- config 5 on the device: ray i is a pure function of its GLOBAL index ------------------------
+def _hash01(idx, stream: int):
+    """splitmix64-style hash of (global index, stream) -> float32 in [0,1) with 24 random bits.
+    idx: int64 torch tensor (any device)."""
+    import torch
+
+    def w(v):   # python int -> the int64 with the same low 64 bits
+        v &= (1 << 64) - 1
+        return v - (1 << 64) if v >= (1 << 63) else v
+
+    def lsr(v, k):   # logical shift right on int64
+        return (v >> k) & ((1 << (64 - k)) - 1)
+
+    x = idx * -7046029254386353131 + w((stream + 1) * 0xBF58476D1CE4E5B9)   # wraps mod 2^64
+    x = (x ^ lsr(x, 30)) * -4658895280553007687
+    x = (x ^ lsr(x, 27)) * -7723592293110705685
+    x = x ^ lsr(x, 31)
+    return (lsr(x, 40) & 0xFFFFFF).to(torch.float32) * (1.0 / 16777216.0)
+
+
+def hashed_random_rays(a: int, b: int, device, lo: float = -0.25, hi: float = 1.25):
+    """Config 5's rays [a, b) of the global batch as an (b-a, 8) float32 torch tensor on `device`:
+    o ~ U[lo,hi)^3, d uniform on the sphere, tMax = inf.  Every world size and every
+    sharding sees the same ray for the same global index, so checksums are comparable across N."""
+    import torch
+    out = torch.empty((b - a, 8), dtype=torch.float32, device=device)
+    step = 1 << 24
+    for s in range(a, b, step):
+        e = min(b, s + step)
+        idx = torch.arange(s, e, dtype=torch.int64, device=device)
+        o = out[s - a:e - a]
+        for k in range(3):
+            o[:, k] = _hash01(idx, k) * (hi - lo) + lo
+        z = 1 - 2 * _hash01(idx, 3)
+        phi = (2 * np.pi) * _hash01(idx, 4)
+        rad = torch.sqrt(torch.clamp(1 - z * z, min=0))
+        o[:, 4], o[:, 5], o[:, 6] = rad * torch.cos(phi), rad * torch.sin(phi), z
+        o[:, 3] = float("inf")
+        o[:, 7] = 0
+    return out

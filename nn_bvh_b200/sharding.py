@@ -124,6 +124,7 @@ class PeerWindow:
         self._capi, self._ct = capi, ctypes
         L = capi.lib()
         self.world, self.rank, self.dst = dist.get_world_size(group), dist.get_rank(group), dst
+        self._group = group
         self.n_total, self.tail, self.dtype = n_total, tuple(tail), dtype
         self.row_bytes = torch.empty((), dtype=dtype).element_size()
         for t in self.tail:
@@ -172,23 +173,33 @@ class PeerWindow:
             at = 0
         elif at < 0 or at + local.shape[0] > b - a:
             raise ValueError(f"rank {self.rank}: rows [{at}, {at + local.shape[0]}) outside a shard of {b - a}")
+        src = local.contiguous()           # a temporary only for a non-contiguous input
+        src.record_stream(self.stream)     # the caching allocator must not reuse the block before the copy has read it
         self._ready.record(producer)
         self.stream.wait_event(self._ready)
         self._capi.check(self._capi.lib().nnbvh_peer_copy(
-            self._ct.c_void_p(self.base + (a + at) * self.row_bytes), self._capi.ptr(local.contiguous()),
+            self._ct.c_void_p(self.base + (a + at) * self.row_bytes), self._capi.ptr(src),
             local.shape[0] * self.row_bytes, self._ct.c_void_p(self.stream.cuda_stream)))
         self._done.record(self.stream)
 
     def wait_on(self, stream: "torch.cuda.Stream"):
+        """Make `stream` wait for THIS rank's last delivery.  It orders nothing across ranks: before
+        rank `dst` reads `tensor` every rank must have waited for its own delivery and the ranks must
+        have met (dist.barrier(), or any collective ordered after the wait) -- bench.py's barrier()."""
         stream.wait_event(self._done)
 
-    def close(self):
+    def close(self, collective: bool = True):
+        """Collective (default): every rank of the group calls it.  The mappings are closed before the owner
+        frees the allocation (freeing exported memory that a peer still maps is undefined).
+        collective=False: no barrier -- the caller orders the non-owners' close before the owner's."""
         L = self._capi.lib()
         torch.cuda.synchronize()
-        if self.base:
-            if self._owner:
-                self.tensor = None
-                L.nnbvh_peer_free(self._ct.c_void_p(self.base))
-            else:
-                L.nnbvh_peer_close(self._ct.c_void_p(self.base))
+        if self.base and not self._owner:
+            L.nnbvh_peer_close(self._ct.c_void_p(self.base))
+            self.base = 0
+        if self.world > 1 and collective:
+            dist.barrier(self._group)
+        if self.base and self._owner:
+            self.tensor = None
+            L.nnbvh_peer_free(self._ct.c_void_p(self.base))
             self.base = 0

@@ -25,37 +25,9 @@ import torch.distributed as dist
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 
 
-def hash01(idx: torch.Tensor, stream: int) -> torch.Tensor:
-    """splitmix64-style hash of (global index, stream) -> float32 in [0,1) with 24 random bits."""
-    def w(v):   # python int -> the int64 with the same low 64 bits
-        v &= (1 << 64) - 1
-        return v - (1 << 64) if v >= (1 << 63) else v
-    x = idx * -7046029254386353131 + w((stream + 1) * 0xBF58476D1CE4E5B9)   # wraps mod 2^64
-    def lsr(v, k):   # logical shift right on int64
-        return (v >> k) & ((1 << (64 - k)) - 1)
-    x = (x ^ lsr(x, 30)) * -4658895280553007687
-    x = (x ^ lsr(x, 27)) * -7723592293110705685
-    x = x ^ lsr(x, 31)
-    return (lsr(x, 40) & 0xFFFFFF).to(torch.float32) * (1.0 / 16777216.0)
-
-
 def gen_rays(a: int, b: int, dev) -> torch.Tensor:
-    """rays [a, b): o ~ U[-0.25,1.25)^3, d uniform on the sphere, tMax = inf."""
-    out = torch.empty((b - a, 8), dtype=torch.float32, device=dev)
-    step = 1 << 24
-    for s in range(a, b, step):
-        e = min(b, s + step)
-        idx = torch.arange(s, e, dtype=torch.int64, device=dev)
-        o = out[s - a:e - a]
-        for k in range(3):
-            o[:, k] = hash01(idx, k) * 1.5 - 0.25
-        z = 1 - 2 * hash01(idx, 3)
-        phi = (2 * np.pi) * hash01(idx, 4)
-        rad = torch.sqrt(torch.clamp(1 - z * z, min=0))
-        o[:, 4], o[:, 5], o[:, 6] = rad * torch.cos(phi), rad * torch.sin(phi), z
-        o[:, 3] = float("inf")
-        o[:, 7] = 0
-    return out
+    from nn_bvh_b200 import rays as R
+    return R.hashed_random_rays(a, b, dev)
 
 
 def main():
