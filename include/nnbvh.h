@@ -13,6 +13,15 @@
  * device pointers; device pointers are detected with cudaPointerGetAttributes
  * and used in place.  There is NO CPU fallback: without a CUDA device every
  * compute entry point fails with NNBVH_ERR_CUDA.
+ *
+ * Threading: an nnbvh_engine is NOT re-entrant.  It owns one launch stream, one set of scratch
+ * buffers and one host-pointer pipeline (slots of staging buffers), and it serialises its batches;
+ * calls on ONE engine must not overlap in time -- callers with several threads give each thread its
+ * own engine (nnbvh_clone shares the uploaded scene) or take a lock (integration/pbrt/gpubvh.h does
+ * for the single-ray Primitive surface).  DIFFERENT engines may be used from different threads at
+ * once.  nnbvh_last_error() is per thread.  The host builders (nnbvh_build_bvh*) are self-contained
+ * and may run concurrently.  nnbvh_intersect_closest_noalloc additionally shares one static scratch
+ * array between all engines of a device (see its comment).
  */
 #ifndef NNBVH_H
 #define NNBVH_H

@@ -91,11 +91,17 @@ class GPUBVHAggregate {
         return Bounds3f(Point3f(b.pMin[0], b.pMin[1], b.pMin[2]), Point3f(b.pMax[0], b.pMax[1], b.pMax[2]));
     }
 
-    // The single-ray surface a Primitive must have: a batch of one
+    // The single-ray surface a Primitive must have: a batch of one.  An nnbvh_engine serialises its
+    // batches and is NOT re-entrant (include/nnbvh.h, "Threading"), while pbrt calls Primitive::Intersect
+    // from every ParallelFor worker: the single-ray calls take a lock.  Correctness only -- anything that
+    // has more than a handful of rays uses Engine()'s batch calls (the wavefront subclass does).
     pstd::optional<ShapeIntersection> Intersect(const Ray &ray, Float tMax = Infinity) const {
         nnbvh_ray r{ray.o.x, ray.o.y, ray.o.z, tMax, ray.d.x, ray.d.y, ray.d.z, ray.time};
         nnbvh_hit h;
-        agg->IntersectBatch(&r, 1, &h);
+        {
+            std::lock_guard<std::mutex> lock(singleRay);
+            agg->IntersectBatch(&r, 1, &h);
+        }
         if (h.prim == NNBVH_MISS)
             return {};
         return Resolve(h, ray);
@@ -103,7 +109,10 @@ class GPUBVHAggregate {
     bool IntersectP(const Ray &ray, Float tMax = Infinity) const {
         nnbvh_ray r{ray.o.x, ray.o.y, ray.o.z, tMax, ray.d.x, ray.d.y, ray.d.z, ray.time};
         uint8_t occluded = 0;
-        agg->IntersectPBatch(&r, 1, &occluded);
+        {
+            std::lock_guard<std::mutex> lock(singleRay);
+            agg->IntersectPBatch(&r, 1, &occluded);
+        }
         return occluded != 0;
     }
 
@@ -170,6 +179,7 @@ class GPUBVHAggregate {
     std::vector<Primitive> primitives;  // the caller's list
     std::vector<int> slot;              // library primitive index (triangles, then spheres) -> index in it
     std::unique_ptr<nnbvh::GPUBVHAggregate> agg;
+    mutable std::mutex singleRay;
 };
 
 }  // namespace pbrt

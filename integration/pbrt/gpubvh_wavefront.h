@@ -25,7 +25,9 @@
 #ifndef NNBVH_INTEGRATION_PBRT_GPUBVH_WAVEFRONT_H
 #define NNBVH_INTEGRATION_PBRT_GPUBVH_WAVEFRONT_H
 
+#include <pbrt/materials.h>
 #include <pbrt/util/parallel.h>
+#include <pbrt/util/sampling.h>
 #include <pbrt/wavefront/integrator.h>
 #include <pbrt/wavefront/intersect.h>
 
@@ -85,58 +87,172 @@ class GPUBVHWavefrontAggregate : public WavefrontAggregate {
         });
     }
 
-    // What CPUAggregate::IntersectShadowTr does (wavefront/aggregate.cpp:70-92): TraceTransmittance
-    // (wavefront/intersect.h:165-240) walks a shadow ray across medium interfaces.  How many surfaces a ray
-    // crosses depends on what it meets, so the walk goes ray by ray through the single-ray entry point.
+    // CPUAggregate::IntersectShadowTr (wavefront/aggregate.cpp:70-92), batched.  The reference walks each shadow
+    // ray across the medium interfaces it meets with TraceTransmittance (wavefront/intersect.h:165-275), asking for
+    // one closest hit per segment.  Here every still-walking ray's NEXT segment goes to the GPU in one batch per
+    // round (as the reference's own GPU backend does per ray inside one launch, gpu/optix.cu:268-296):
+    //   round k: each live walk is REPLAYED from its start by the reference's unmodified TraceTransmittance, whose
+    //   `trace` callback answers the first k segments from the hits of the earlier rounds; when it asks for a
+    //   segment nobody has traced yet, the segment is recorded and the callback answers "opaque surface", which
+    //   ends that replay with T_ray = 0 and therefore WITHOUT touching pixelSampleState (intersect.h:263-274).
+    //   The replay that gets through with known segments only is the real one and records its radiance once.
+    // TraceTransmittance is deterministic in its inputs (its RNG is seeded from the ray, :181), so every replay
+    // repeats the same prefix; a walk over s surfaces costs s + 1 rounds and O(s^2) host steps, s being 1-3 in
+    // practice.  GPU batches per call = 1 + the longest walk's surface count, not one per segment per ray.
     void IntersectShadowTr(int maxRays, ShadowRayQueue *shadowRayQueue,
                            SOA<PixelSampleState> *pixelSampleState) const override {
-        auto walk = [=](int index) {
-            pstd::optional<ShapeIntersection> last;  // the surface the walk currently stands on
-            auto trace = [&](Ray ray, Float tMax) {
-                last = host.Intersect(ray, tMax);
-                TransmittanceTraceResult res{last.has_value(), Point3f(), Material()};
-                if (last) {
-                    res.pHit = last->intr.p();
-                    res.material = last->intr.material;
-                }
-                return res;
-            };
-            auto spawnTo = [&](Point3f target) { return last->intr.SpawnRayTo(target); };
-            TraceTransmittance((*shadowRayQueue)[index], pixelSampleState, trace, spawnTo);
+        const int n = shadowRayQueue->Size();
+        if (n == 0)
+            return;
+        struct Walk {
+            std::vector<nnbvh_hit> known;  // hits of the segments traced so far, in walk order
+            nnbvh_ray query;               // the next segment, when the last replay stopped for it
+            bool done = false;
         };
-        ParallelFor(0, shadowRayQueue->Size(), walk);
+        std::vector<Walk> walks((size_t)n);
+        std::vector<int> live((size_t)n);
+        for (int i = 0; i < n; ++i)
+            live[i] = i;
+        std::vector<nnbvh_ray> rays;
+        std::vector<nnbvh_hit> segHits;
+        lastTrBatches = 0;
+        while (!live.empty()) {
+            const int m = (int)live.size();
+            ParallelFor(0, m, [&](int j) {
+                Walk &w = walks[live[j]];
+                size_t asked = 0;
+                bool pending = false;
+                pstd::optional<ShapeIntersection> last;  // the surface the walk currently stands on
+                auto trace = [&](Ray ray, Float tMax) {
+                    if (asked < w.known.size()) {
+                        const nnbvh_hit &h = w.known[asked++];
+                        last.reset();
+                        if (h.prim != NNBVH_MISS)
+                            last = host.Resolve(h, ray);
+                        return TransmittanceTraceResult{last.has_value(), last ? last->intr.p() : Point3f(),
+                                                        last ? last->intr.material : Material()};
+                    }
+                    w.query = nnbvh_ray{ray.o.x, ray.o.y, ray.o.z, tMax, ray.d.x, ray.d.y, ray.d.z, ray.time};
+                    pending = true;
+                    return TransmittanceTraceResult{true, Point3f(), OpaqueSentinel()};  // ends this replay, no side effect
+                };
+                auto spawnTo = [&](Point3f target) { return last->intr.SpawnRayTo(target); };
+                TraceTransmittance((*shadowRayQueue)[live[j]], pixelSampleState, trace, spawnTo);
+                w.done = !pending;
+            });
+            std::vector<int> next;
+            next.reserve(live.size());
+            for (int i : live)
+                if (!walks[i].done)
+                    next.push_back(i);
+            live.swap(next);
+            if (live.empty())
+                break;
+            rays.resize(live.size());
+            segHits.resize(live.size());
+            for (size_t j = 0; j < live.size(); ++j)
+                rays[j] = walks[live[j]].query;
+            host.Engine().IntersectBatch(rays.data(), (uint64_t)rays.size(), segHits.data());
+            ++lastTrBatches;
+            for (size_t j = 0; j < live.size(); ++j)
+                walks[live[j]].known.push_back(segHits[j]);
+        }
     }
 
-    // What CPUAggregate::IntersectOneRandom does (wavefront/aggregate.cpp:94-124): between p0 and p1 every
-    // surface of the probe's material is a candidate of weight 1 for the subsurface exit point; the reservoir
-    // is seeded by Hash(p0, p1).
+    // CPUAggregate::IntersectOneRandom (wavefront/aggregate.cpp:94-124), batched the same way (the reference's GPU
+    // backend: gpu/optix.cu:480-573).  Between p0 and p1 every surface of the probe's material is a candidate of
+    // weight 1 for the subsurface exit point; the reservoir is seeded by Hash(p0, p1).  The probe loop is short
+    // enough to be kept as a per-probe state (the interaction the probe stands on + its reservoir) that advances
+    // by one segment per round; one closest-hit batch over the still-walking probes per round.
     void IntersectOneRandom(int maxRays, SubsurfaceScatterQueue *subsurfaceScatterQueue) const override {
         SubsurfaceScatterQueue *q = subsurfaceScatterQueue;
-        auto probe = [=](int index) {
-            const SubsurfaceScatterWorkItem &item = (*q)[index];
-            WeightedReservoirSampler<SubsurfaceInteraction> reservoir(Hash(item.p0, item.p1));
-            for (Interaction from(item.p0, 0.f, Medium());;) {
-                Ray segment = from.SpawnRayTo(item.p1);
-                if (segment.d == Vector3f(0, 0, 0))
-                    break;
-                pstd::optional<ShapeIntersection> next = host.Intersect(segment, 1);
-                if (!next)
-                    break;
-                if (next->intr.material == item.material)
-                    reservoir.Add(SubsurfaceInteraction(next->intr), 1.f);
-                from = next->intr;
-            }
-            q->reservoirPDF[index] = reservoir.HasSample() ? reservoir.SampleProbability() : Float(0);
-            if (reservoir.HasSample())
-                q->ssi[index] = reservoir.GetSample();
+        const int n = q->Size();
+        if (n == 0)
+            return;
+        struct Probe {
+            Interaction from;
+            WeightedReservoirSampler<SubsurfaceInteraction> reservoir;
+            Ray segment;
+            bool live = true;
         };
-        ParallelFor(0, q->Size(), probe);
+        std::vector<Probe> probes((size_t)n);
+        ParallelFor(0, n, [&](int i) {
+            const SubsurfaceScatterWorkItem &item = (*q)[i];
+            probes[i].from = Interaction(item.p0, 0.f, Medium());
+            probes[i].reservoir.Seed(Hash(item.p0, item.p1));
+        });
+        std::vector<int> live((size_t)n);
+        for (int i = 0; i < n; ++i)
+            live[i] = i;
+        std::vector<nnbvh_ray> rays;
+        std::vector<nnbvh_hit> segHits;
+        lastOneRandomBatches = 0;
+        while (true) {
+            // the next segment of every live probe (`if (r.d == 0) break`, aggregate.cpp:104-106)
+            std::vector<int> next;
+            next.reserve(live.size());
+            for (int i : live) {
+                Probe &p = probes[i];
+                p.segment = p.from.SpawnRayTo(Point3f(q->p1[i]));
+                if (p.segment.d == Vector3f(0, 0, 0))
+                    p.live = false;
+                else
+                    next.push_back(i);
+            }
+            live.swap(next);
+            if (live.empty())
+                break;
+            rays.resize(live.size());
+            segHits.resize(live.size());
+            for (size_t j = 0; j < live.size(); ++j) {
+                const Ray &r = probes[live[j]].segment;
+                rays[j] = nnbvh_ray{r.o.x, r.o.y, r.o.z, 1.f, r.d.x, r.d.y, r.d.z, r.time};
+            }
+            host.Engine().IntersectBatch(rays.data(), (uint64_t)rays.size(), segHits.data());
+            ++lastOneRandomBatches;
+            ParallelFor(0, (int64_t)live.size(), [&](int64_t j) {
+                Probe &p = probes[live[j]];
+                if (segHits[j].prim == NNBVH_MISS) {
+                    p.live = false;
+                    return;
+                }
+                ShapeIntersection si = host.Resolve(segHits[j], p.segment);
+                p.from = si.intr;
+                if (si.intr.material == Material(q->material[live[j]]))
+                    p.reservoir.Add(SubsurfaceInteraction(si.intr), 1.f);
+            });
+            next.clear();
+            for (int i : live)
+                if (probes[i].live)
+                    next.push_back(i);
+            live.swap(next);
+        }
+        ParallelFor(0, n, [&](int i) {
+            Probe &p = probes[i];
+            q->reservoirPDF[i] = p.reservoir.HasSample() ? p.reservoir.SampleProbability() : Float(0);
+            if (p.reservoir.HasSample())
+                q->ssi[i] = p.reservoir.GetSample();
+        });
     }
 
+    // GPU batches the last IntersectShadowTr / IntersectOneRandom call issued (tests: <= longest walk + 1)
+    int LastShadowTrBatches() const { return lastTrBatches; }
+    int LastOneRandomBatches() const { return lastOneRandomBatches; }
+
   private:
+    // A Material that is only ever compared with null: TraceTransmittance reads `result.hit && result.material`
+    // (wavefront/intersect.h:192) and never dereferences it.
+    static Material OpaqueSentinel() {
+        static DiffuseMaterial *const tagOnly = reinterpret_cast<DiffuseMaterial *>(uintptr_t(64));
+        return Material(tagOnly);
+    }
+
     GPUBVHAggregate host;
-    mutable std::vector<nnbvh_hit> hits;  // one IntersectClosest / IntersectShadow is in flight at a time
+    // One call of this aggregate is in flight at a time (the wavefront render loop is sequential,
+    // wavefront/integrator.cpp); the batch buffers and counters below rely on it.
+    mutable std::vector<nnbvh_hit> hits;
     mutable std::vector<uint8_t> occluded;
+    mutable int lastTrBatches = 0, lastOneRandomBatches = 0;
 };
 
 }  // namespace pbrt

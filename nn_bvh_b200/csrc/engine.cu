@@ -63,6 +63,28 @@ struct DevBuf {
     }
 };
 
+// A cudaMalloc'ed temporary that is freed on every return path.
+template <typename T>
+struct DevTmp {
+    T *p = nullptr;
+    DevTmp() = default;
+    DevTmp(const DevTmp &) = delete;
+    DevTmp &operator=(const DevTmp &) = delete;
+    ~DevTmp() {
+        if (p) cudaFree(p);
+    }
+    cudaError_t Alloc(size_t n) { return cudaMalloc(&p, std::max<size_t>(n, 1) * sizeof(T)); }
+};
+
+// Known-answer hooks: host array -> device temporary and back, ordered on the engine's stream (a blocking
+// cudaMemcpy on the legacy stream is not ordered with a cudaStreamNonBlocking stream).
+template <typename T>
+static cudaError_t StageIn(DevTmp<T> &d, const void *host, size_t count, cudaStream_t st) {
+    cudaError_t ce = d.Alloc(count);
+    if (ce != cudaSuccess) return ce;
+    return cudaMemcpyAsync(d.p, host, count * sizeof(T), cudaMemcpyHostToDevice, st);
+}
+
 // Per-launch device scratch: the persistent kernel's ray cursor and the binning buffers.
 constexpr int kCursorWords = 8;
 struct Scratch {
@@ -91,6 +113,8 @@ struct Scratch {
 struct Slot {
     cudaStream_t stream = nullptr;
     cudaEvent_t done = nullptr;
+    cudaEvent_t k0 = nullptr, k1 = nullptr;  // around the chunk's kernels (pooled: created once per slot)
+    bool timed = false;                      // k0/k1 hold a chunk whose time has not been added yet
     DevBuf<nnbvh_ray> rays;
     DevBuf<float> soa;       // 7 planes for the SoA entry points
     DevBuf<nnbvh_hit> hits;
@@ -187,32 +211,29 @@ extern "C" int nnbvh_create(const nnbvh_options *opts, nnbvh_engine **out) {
         return SetError(NNBVH_ERR_CUDA, "nnbvh_create: no CUDA device (%s); this library has "
                                         "no CPU fallback",
                         ce == cudaSuccess ? "device count 0" : cudaGetErrorString(ce));
-    nnbvh_engine *e = new nnbvh_engine;
+    // owned until handed to the caller: every early return below destroys what was created so far
+    struct Destroyer {
+        void operator()(nnbvh_engine *p) const { nnbvh_destroy(p); }
+    };
+    std::unique_ptr<nnbvh_engine, Destroyer> owner(new nnbvh_engine);
+    nnbvh_engine *e = owner.get();
     int dev = opts ? opts->device : -1;
     if (dev < 0) CU(cudaGetDevice(&dev));
-    if (dev >= nDev) {
-        delete e;
-        return SetError(NNBVH_ERR_INVALID, "nnbvh_create: device %d of %d", dev, nDev);
-    }
+    if (dev >= nDev) return SetError(NNBVH_ERR_INVALID, "nnbvh_create: device %d of %d", dev, nDev);
     e->device = dev;
     CU(cudaSetDevice(dev));
     cudaDeviceProp prop;
     CU(cudaGetDeviceProperties(&prop, dev));
-    if (prop.major < 10) {
-        delete e;
+    if (prop.major < 10)
         return SetError(NNBVH_ERR_CUDA, "nnbvh_create: device %d is sm_%d%d; this library is "
                                         "built for sm_100a only", dev, prop.major, prop.minor);
-    }
     e->numSMs = prop.multiProcessorCount;
     e->maxSmemOptin = (int)prop.sharedMemPerBlockOptin;
     e->kernel = opts ? opts->kernel : NNBVH_KERNEL_AUTO;
     e->smemTopNodes = opts ? opts->smem_top_nodes : -1;
     e->kernel = EnvInt("NNBVH_KERNEL", e->kernel);
-    if (e->kernel < NNBVH_KERNEL_AUTO || e->kernel > NNBVH_KERNEL_STEP) {
-        int k = e->kernel;
-        delete e;
-        return SetError(NNBVH_ERR_INVALID, "nnbvh_create: unknown kernel %d", k);
-    }
+    if (e->kernel < NNBVH_KERNEL_AUTO || e->kernel > NNBVH_KERNEL_STEP)
+        return SetError(NNBVH_ERR_INVALID, "nnbvh_create: unknown kernel %d", e->kernel);
     e->smemTopNodes = EnvInt("NNBVH_SMEM_NODES", e->smemTopNodes);
     e->wideMinB = EnvInt("NNBVH_WIDE_MINB", e->wideMinB);
     e->refillBelow = EnvInt("NNBVH_REFILL_BELOW", e->refillBelow);
@@ -240,11 +261,13 @@ extern "C" int nnbvh_create(const nnbvh_options *opts, nnbvh_engine **out) {
     for (Slot &s : e->slots) {
         CU(cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking));
         CU(cudaEventCreateWithFlags(&s.done, cudaEventDisableTiming));
+        CU(cudaEventCreate(&s.k0));
+        CU(cudaEventCreate(&s.k1));
         CU(cudaMalloc(&s.scratch.cursor, kCursorWords * sizeof(unsigned long long)));
     }
     int rcSetup = NoAllocSetup(dev);
     if (rcSetup) return rcSetup;
-    *out = e;
+    *out = owner.release();
     return NNBVH_OK;
 }
 
@@ -259,6 +282,8 @@ extern "C" void nnbvh_destroy(nnbvh_engine *e) {
         s.rays.Free(); s.soa.Free(); s.hits.Free(); s.occ.Free(); s.cnt.Free(); s.inner.Free();
         s.scratch.Free();
         if (s.done) cudaEventDestroy(s.done);
+        if (s.k0) cudaEventDestroy(s.k0);
+        if (s.k1) cudaEventDestroy(s.k1);
         if (s.stream) cudaStreamDestroy(s.stream);
     }
     if (e->evA) cudaEventDestroy(e->evA);
@@ -563,21 +588,22 @@ static int UploadScene(nnbvh_engine *e, const nnbvh_node *nodes, uint32_t nNodes
     if (!wide.empty())
         CU(cudaMemcpyAsync(e->store->dWide.p, wide.data(), sizeof(WideNode) * wide.size(),
                            cudaMemcpyHostToDevice, st));
-    // triangles: stage raw floats + leaf-end flags, pack on the device
-    float *dRaw = nullptr;
-    uint8_t *dLast = nullptr;
+    // triangles: stage raw floats + leaf-end flags, pack on the device (temporaries freed on every return path)
+    DevTmp<float> dRaw;
+    DevTmp<uint8_t> dLast;
+    DevTmp<int32_t> dSphereOf;
     const float *src = orderedTriVerts9;
     if (!IsDevicePtr(orderedTriVerts9)) {
-        CU(cudaMalloc(&dRaw, sizeof(float) * 9 * (size_t)nPrims));
-        CU(cudaMemcpyAsync(dRaw, orderedTriVerts9, sizeof(float) * 9 * (size_t)nPrims,
+        CU(dRaw.Alloc(9 * (size_t)nPrims));
+        CU(cudaMemcpyAsync(dRaw.p, orderedTriVerts9, sizeof(float) * 9 * (size_t)nPrims,
                            cudaMemcpyHostToDevice, st));
-        src = dRaw;
+        src = dRaw.p;
     }
-    CU(cudaMalloc(&dLast, nPrims));
-    CU(cudaMemcpyAsync(dLast, last.data(), nPrims, cudaMemcpyHostToDevice, st));
-    int32_t *dSphereOf = nullptr;
+    CU(dLast.Alloc(nPrims));
+    CU(cudaMemcpyAsync(dLast.p, last.data(), nPrims, cudaMemcpyHostToDevice, st));
+    std::vector<SphereDev> sd;  // outlives the asynchronous copy below
     if (sphereOf) {
-        std::vector<SphereDev> sd(nSpheres);
+        sd.resize(nSpheres);
         for (uint32_t i = 0; i < nSpheres; ++i) {
             rc = MakeSphereDev(spheres[i], i, &sd[i]);
             if (rc) break;
@@ -587,32 +613,28 @@ static int UploadScene(nnbvh_engine *e, const nnbvh_node *nodes, uint32_t nNodes
                 rc = SetError(NNBVH_ERR_INVALID, "primitive %u refers to sphere %d of %u", i, sphereOf[i], nSpheres);
         if (!rc) rc = e->store->dSpheres.Reserve(nSpheres);
         if (rc) {
-            if (dRaw) cudaFree(dRaw);
-            cudaFree(dLast);
+            cudaStreamSynchronize(st);  // the staged copies read host vectors of this frame
             return rc;
         }
         CU(cudaMemcpyAsync(e->store->dSpheres.p, sd.data(), sizeof(SphereDev) * nSpheres, cudaMemcpyHostToDevice, st));
-        CU(cudaMalloc(&dSphereOf, sizeof(int32_t) * (size_t)nPrims));
-        CU(cudaMemcpyAsync(dSphereOf, sphereOf, sizeof(int32_t) * (size_t)nPrims, cudaMemcpyHostToDevice, st));
-        CU(cudaStreamSynchronize(st));  // sd goes out of scope
+        CU(dSphereOf.Alloc(nPrims));
+        CU(cudaMemcpyAsync(dSphereOf.p, sphereOf, sizeof(int32_t) * (size_t)nPrims, cudaMemcpyHostToDevice, st));
     } else if (instanceOf) {
         for (uint32_t i = 0; i < nPrims; ++i)
             if (instanceOf[i] >= (int32_t)nInstances) {
-                if (dRaw) cudaFree(dRaw);
-                cudaFree(dLast);
+                cudaStreamSynchronize(st);
                 return SetError(NNBVH_ERR_INVALID, "primitive %u refers to instance %d of %u", i, instanceOf[i], nInstances);
             }
-        CU(cudaMalloc(&dSphereOf, sizeof(int32_t) * (size_t)nPrims));
-        CU(cudaMemcpyAsync(dSphereOf, instanceOf, sizeof(int32_t) * (size_t)nPrims, cudaMemcpyHostToDevice, st));
+        CU(dSphereOf.Alloc(nPrims));
+        CU(cudaMemcpyAsync(dSphereOf.p, instanceOf, sizeof(int32_t) * (size_t)nPrims, cudaMemcpyHostToDevice, st));
     }
-    PackTrisKernel<<<(nPrims + 255) / 256, 256, 0, st>>>(src, dLast, dSphereOf, instanceOf ? kPrimInstance : kPrimSphere,
+    PackTrisKernel<<<(nPrims + 255) / 256, 256, 0, st>>>(src, dLast.p, dSphereOf.p, instanceOf ? kPrimInstance : kPrimSphere,
                                                         nPrims, e->store->dTris.p);
     ++e->launches;
-    CU(cudaGetLastError());
-    CU(cudaStreamSynchronize(st));
-    if (dRaw) cudaFree(dRaw);
-    cudaFree(dLast);
-    if (dSphereOf) cudaFree(dSphereOf);
+    cudaError_t launchErr = cudaGetLastError();
+    cudaError_t syncErr = cudaStreamSynchronize(st);  // before the temporaries (and `h`, `wide`, `last`, `sd`) go away
+    CU(launchErr);
+    CU(syncErr);
     SceneDev sc{};
     sc.nodes = e->store->dNodes.p;
     sc.wide = e->store->dWide.p;
@@ -704,20 +726,24 @@ extern "C" int nnbvh_upload_scene_instanced(nnbvh_engine *e, const nnbvh_node *n
     if (!rc) rc = e->store->dObjTris.Reserve(3 * (size_t)nObjPrims);
     if (!rc) rc = e->store->dInstances.Reserve(nInstances);
     if (rc) return rc;
-    float *dRaw = nullptr;
-    uint8_t *dLast = nullptr;
-    CU(cudaMalloc(&dRaw, sizeof(float) * allTris.size()));
-    CU(cudaMalloc(&dLast, nObjPrims));
-    CU(cudaMemcpyAsync(dRaw, allTris.data(), sizeof(float) * allTris.size(), cudaMemcpyHostToDevice, st));
-    CU(cudaMemcpyAsync(dLast, allLast.data(), nObjPrims, cudaMemcpyHostToDevice, st));
-    CU(cudaMemcpyAsync(e->store->dObjNodes.p, allNodes.data(), sizeof(nnbvh_node) * allNodes.size(), cudaMemcpyHostToDevice, st));
-    CU(cudaMemcpyAsync(e->store->dInstances.p, id.data(), sizeof(InstanceDev) * nInstances, cudaMemcpyHostToDevice, st));
-    PackTrisKernel<<<(nObjPrims + 255) / 256, 256, 0, st>>>(dRaw, dLast, nullptr, 0u, nObjPrims, e->store->dObjTris.p);
-    ++e->launches;
-    CU(cudaGetLastError());
-    CU(cudaStreamSynchronize(st));
-    cudaFree(dRaw);
-    cudaFree(dLast);
+    {
+        DevTmp<float> dRaw;
+        DevTmp<uint8_t> dLast;
+        cudaError_t ce = dRaw.Alloc(allTris.size());
+        if (ce == cudaSuccess) ce = dLast.Alloc(nObjPrims);
+        if (ce == cudaSuccess) ce = cudaMemcpyAsync(dRaw.p, allTris.data(), sizeof(float) * allTris.size(), cudaMemcpyHostToDevice, st);
+        if (ce == cudaSuccess) ce = cudaMemcpyAsync(dLast.p, allLast.data(), nObjPrims, cudaMemcpyHostToDevice, st);
+        if (ce == cudaSuccess) ce = cudaMemcpyAsync(e->store->dObjNodes.p, allNodes.data(), sizeof(nnbvh_node) * allNodes.size(), cudaMemcpyHostToDevice, st);
+        if (ce == cudaSuccess) ce = cudaMemcpyAsync(e->store->dInstances.p, id.data(), sizeof(InstanceDev) * nInstances, cudaMemcpyHostToDevice, st);
+        if (ce == cudaSuccess) {
+            PackTrisKernel<<<(nObjPrims + 255) / 256, 256, 0, st>>>(dRaw.p, dLast.p, nullptr, 0u, nObjPrims, e->store->dObjTris.p);
+            ++e->launches;
+            ce = cudaGetLastError();
+        }
+        cudaError_t se = cudaStreamSynchronize(st);  // the copies read this frame's vectors; the temporaries go away
+        CU(ce);
+        CU(se);
+    }
     // the top level: triangles and instance slots
     rc = UploadScene(e, nodes, nNodes, orderedTriVerts9, nPrims, nullptr, nullptr, 0, orderedInstanceIndex, nInstances);
     if (rc) return rc;
@@ -1017,13 +1043,18 @@ static int RunBatch(nnbvh_engine *e, const Batch &b) {
 
     // ---- host buffers: chunked H2D -> kernel -> D2H over kSlots streams ----
     const uint64_t chunk = std::max<uint64_t>(b.soa ? e->chunkRaysSoa : e->chunkRays, 1024);
-    std::vector<cudaEvent_t> k0, k1;  // kernel timing events, one pair per chunk
-    int idx = 0;
-    int rcOut = NNBVH_OK;
-    for (uint64_t off = 0; off < b.n && rcOut == NNBVH_OK; off += chunk, ++idx) {
-        Slot &s = e->slots[idx % e->nSlots];
-        const uint64_t m = std::min(chunk, b.n - off);
-        CU(cudaEventSynchronize(s.done));  // slot buffers free again
+    float total = 0.f;
+    // a slot's pooled event pair holds the previous chunk's kernel time until the slot is taken again
+    auto collect = [&](Slot &s) {
+        if (!s.timed) return;
+        float ms = 0.f;
+        if (cudaEventElapsedTime(&ms, s.k0, s.k1) == cudaSuccess) total += ms;
+        s.timed = false;
+    };
+    // one chunk: everything asynchronous on the slot's stream; any error leaves the loop
+    auto issue = [&](Slot &s, uint64_t off, uint64_t m) -> int {
+        CU(cudaEventSynchronize(s.done));  // slot buffers (and its event pair) free again
+        collect(s);
         RayInput in{};
         if (b.soa) {
             if (raysDev) {
@@ -1072,15 +1103,11 @@ static int RunBatch(nnbvh_engine *e, const Batch &b) {
                 o.triTests = s.cnt.p + chunk;
             }
         }
-        cudaEvent_t a, z;
-        CU(cudaEventCreate(&a));
-        CU(cudaEventCreate(&z));
-        k0.push_back(a);
-        k1.push_back(z);
-        CU(cudaEventRecord(a, s.stream));
-        rcOut = LaunchTraversal(e, s.stream, b.any, b.counters, in, m, o, s.scratch);
-        if (rcOut) break;
-        CU(cudaEventRecord(z, s.stream));
+        CU(cudaEventRecord(s.k0, s.stream));
+        int rc = LaunchTraversal(e, s.stream, b.any, b.counters, in, m, o, s.scratch);
+        if (rc) return rc;
+        CU(cudaEventRecord(s.k1, s.stream));
+        s.timed = true;
         if (!outDev) {
             if (b.any) CU(cudaMemcpyAsync(b.out.occ + off, o.occ, m, cudaMemcpyDeviceToHost, s.stream));
             else CU(cudaMemcpyAsync(b.out.hits + off, o.hits, sizeof(nnbvh_hit) * m,
@@ -1095,14 +1122,18 @@ static int RunBatch(nnbvh_engine *e, const Batch &b) {
                                cudaMemcpyDeviceToHost, s.stream));
         }
         CU(cudaEventRecord(s.done, s.stream));
-    }
-    for (Slot &s : e->slots) CU(cudaStreamSynchronize(s.stream));
-    float total = 0.f;
-    for (size_t i = 0; i < k1.size(); ++i) {
-        float ms = 0.f;
-        if (cudaEventElapsedTime(&ms, k0[i], k1[i]) == cudaSuccess) total += ms;
-        cudaEventDestroy(k0[i]);
-        cudaEventDestroy(k1[i]);
+        return NNBVH_OK;
+    };
+    int rcOut = NNBVH_OK;
+    int idx = 0;
+    for (uint64_t off = 0; off < b.n && rcOut == NNBVH_OK; off += chunk, ++idx)
+        rcOut = issue(e->slots[idx % e->nSlots], off, std::min(chunk, b.n - off));
+    // Also on an error: nothing may still be copying into the caller's buffers when this returns.
+    for (Slot &s : e->slots) {
+        cudaError_t ce = cudaStreamSynchronize(s.stream);
+        if (ce != cudaSuccess && rcOut == NNBVH_OK)
+            rcOut = SetError(NNBVH_ERR_CUDA, "cudaStreamSynchronize failed: %s", cudaGetErrorString(ce));
+        collect(s);
     }
     cudaGetLastError();
     e->lastMs = total;
@@ -1252,22 +1283,22 @@ extern "C" int nnbvh_test_triangles(nnbvh_engine *e, const nnbvh_ray *rays, cons
         return SetError(NNBVH_ERR_INVALID, "nnbvh_test_triangles: NULL argument");
     if (n == 0) return NNBVH_OK;
     CU(cudaSetDevice(e->device));
-    float4 *dR = nullptr;
-    float *dT = nullptr, *dO = nullptr;
-    uint8_t *dH = nullptr;
-    CU(cudaMalloc(&dR, n * 32));
-    CU(cudaMalloc(&dT, n * 36));
-    CU(cudaMalloc(&dO, n * 16));
-    CU(cudaMalloc(&dH, n));
-    CU(cudaMemcpy(dR, rays, n * 32, cudaMemcpyHostToDevice));
-    CU(cudaMemcpy(dT, tris9, n * 36, cudaMemcpyHostToDevice));
-    TestTrianglesKernel<<<(unsigned)((n + 127) / 128), 128, 0, e->stream>>>(dR, dT, n, dH, dO);
+    cudaStream_t st = e->stream;
+    DevTmp<float4> dR;
+    DevTmp<float> dT, dO;
+    DevTmp<uint8_t> dH;
+    CU(StageIn(dR, rays, 2 * n, st));
+    CU(StageIn(dT, tris9, 9 * n, st));
+    CU(dO.Alloc(4 * n));
+    CU(dH.Alloc(n));
+    TestTrianglesKernel<<<(unsigned)((n + 127) / 128), 128, 0, st>>>(dR.p, dT.p, n, dH.p, dO.p);
     ++e->launches;
-    CU(cudaGetLastError());
-    CU(cudaStreamSynchronize(e->stream));
-    CU(cudaMemcpy(hit, dH, n, cudaMemcpyDeviceToHost));
-    CU(cudaMemcpy(out4, dO, n * 16, cudaMemcpyDeviceToHost));
-    cudaFree(dR); cudaFree(dT); cudaFree(dO); cudaFree(dH);
+    cudaError_t ce = cudaGetLastError();
+    if (ce == cudaSuccess) ce = cudaMemcpyAsync(hit, dH.p, n, cudaMemcpyDeviceToHost, st);
+    if (ce == cudaSuccess) ce = cudaMemcpyAsync(out4, dO.p, n * 16, cudaMemcpyDeviceToHost, st);
+    cudaError_t se = cudaStreamSynchronize(st);  // before the temporaries are freed, error or not
+    CU(ce);
+    CU(se);
     return NNBVH_OK;
 }
 
@@ -1277,20 +1308,20 @@ extern "C" int nnbvh_test_boxes(nnbvh_engine *e, const nnbvh_ray *rays, const fl
         return SetError(NNBVH_ERR_INVALID, "nnbvh_test_boxes: NULL argument");
     if (n == 0) return NNBVH_OK;
     CU(cudaSetDevice(e->device));
-    float4 *dR = nullptr;
-    float *dB = nullptr;
-    uint8_t *dH = nullptr;
-    CU(cudaMalloc(&dR, n * 32));
-    CU(cudaMalloc(&dB, n * 24));
-    CU(cudaMalloc(&dH, n));
-    CU(cudaMemcpy(dR, rays, n * 32, cudaMemcpyHostToDevice));
-    CU(cudaMemcpy(dB, boxes6, n * 24, cudaMemcpyHostToDevice));
-    TestBoxesKernel<<<(unsigned)((n + 127) / 128), 128, 0, e->stream>>>(dR, dB, n, dH);
+    cudaStream_t st = e->stream;
+    DevTmp<float4> dR;
+    DevTmp<float> dB;
+    DevTmp<uint8_t> dH;
+    CU(StageIn(dR, rays, 2 * n, st));
+    CU(StageIn(dB, boxes6, 6 * n, st));
+    CU(dH.Alloc(n));
+    TestBoxesKernel<<<(unsigned)((n + 127) / 128), 128, 0, st>>>(dR.p, dB.p, n, dH.p);
     ++e->launches;
-    CU(cudaGetLastError());
-    CU(cudaStreamSynchronize(e->stream));
-    CU(cudaMemcpy(hit, dH, n, cudaMemcpyDeviceToHost));
-    cudaFree(dR); cudaFree(dB); cudaFree(dH);
+    cudaError_t ce = cudaGetLastError();
+    if (ce == cudaSuccess) ce = cudaMemcpyAsync(hit, dH.p, n, cudaMemcpyDeviceToHost, st);
+    cudaError_t se = cudaStreamSynchronize(st);
+    CU(ce);
+    CU(se);
     return NNBVH_OK;
 }
 
@@ -1316,16 +1347,20 @@ extern "C" int nnbvh_test_atan2(nnbvh_engine *e, const float *y, const float *x,
     if (!e || !y || !x || !out) return SetError(NNBVH_ERR_INVALID, "nnbvh_test_atan2: NULL argument");
     if (n == 0) return NNBVH_OK;
     CU(cudaSetDevice(e->device));
-    float *d = nullptr;
-    CU(cudaMalloc(&d, n * 12));
-    CU(cudaMemcpy(d, y, n * 4, cudaMemcpyHostToDevice));
-    CU(cudaMemcpy(d + n, x, n * 4, cudaMemcpyHostToDevice));
-    TestAtan2Kernel<<<(unsigned)((n + 255) / 256), 256, 0, e->stream>>>(d, d + n, n, d + 2 * n);
-    ++e->launches;
-    CU(cudaGetLastError());
-    CU(cudaStreamSynchronize(e->stream));
-    CU(cudaMemcpy(out, d + 2 * n, n * 4, cudaMemcpyDeviceToHost));
-    cudaFree(d);
+    cudaStream_t st = e->stream;
+    DevTmp<float> d;
+    CU(d.Alloc(3 * n));
+    cudaError_t ce = cudaMemcpyAsync(d.p, y, n * 4, cudaMemcpyHostToDevice, st);
+    if (ce == cudaSuccess) ce = cudaMemcpyAsync(d.p + n, x, n * 4, cudaMemcpyHostToDevice, st);
+    if (ce == cudaSuccess) {
+        TestAtan2Kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(d.p, d.p + n, n, d.p + 2 * n);
+        ++e->launches;
+        ce = cudaGetLastError();
+    }
+    if (ce == cudaSuccess) ce = cudaMemcpyAsync(out, d.p + 2 * n, n * 4, cudaMemcpyDeviceToHost, st);
+    cudaError_t se = cudaStreamSynchronize(st);
+    CU(ce);
+    CU(se);
     return NNBVH_OK;
 }
 
@@ -1340,22 +1375,24 @@ extern "C" int nnbvh_test_spheres(nnbvh_engine *e, const nnbvh_ray *rays, const 
         int rc = MakeSphereDev(spheres[i], (uint32_t)i, &sd[i]);
         if (rc) return rc;
     }
-    float4 *dR = nullptr, *dO = nullptr;
-    SphereDev *dS = nullptr;
-    uint8_t *dH = nullptr;
-    CU(cudaMalloc(&dR, n * 32));
-    CU(cudaMalloc(&dS, n * sizeof(SphereDev)));
-    CU(cudaMalloc(&dH, n));
-    CU(cudaMalloc(&dO, n * 16));
-    CU(cudaMemcpy(dR, rays, n * 32, cudaMemcpyHostToDevice));
-    CU(cudaMemcpy(dS, sd.data(), n * sizeof(SphereDev), cudaMemcpyHostToDevice));
-    TestSpheresKernel<<<(unsigned)((n + 127) / 128), 128, 0, e->stream>>>(dR, dS, n, dH, dO);
-    ++e->launches;
-    CU(cudaGetLastError());
-    CU(cudaStreamSynchronize(e->stream));
-    CU(cudaMemcpy(hit, dH, n, cudaMemcpyDeviceToHost));
-    CU(cudaMemcpy(out4, dO, n * 16, cudaMemcpyDeviceToHost));
-    cudaFree(dR); cudaFree(dS); cudaFree(dH); cudaFree(dO);
+    cudaStream_t st = e->stream;
+    DevTmp<float4> dR, dO;
+    DevTmp<SphereDev> dS;
+    DevTmp<uint8_t> dH;
+    CU(StageIn(dR, rays, 2 * n, st));
+    cudaError_t ce = StageIn(dS, sd.data(), n, st);
+    if (ce == cudaSuccess) ce = dH.Alloc(n);
+    if (ce == cudaSuccess) ce = dO.Alloc(n);
+    if (ce == cudaSuccess) {
+        TestSpheresKernel<<<(unsigned)((n + 127) / 128), 128, 0, st>>>(dR.p, dS.p, n, dH.p, dO.p);
+        ++e->launches;
+        ce = cudaGetLastError();
+    }
+    if (ce == cudaSuccess) ce = cudaMemcpyAsync(hit, dH.p, n, cudaMemcpyDeviceToHost, st);
+    if (ce == cudaSuccess) ce = cudaMemcpyAsync(out4, dO.p, n * 16, cudaMemcpyDeviceToHost, st);
+    cudaError_t se = cudaStreamSynchronize(st);  // `sd` and the temporaries outlive every copy
+    CU(ce);
+    CU(se);
     return NNBVH_OK;
 }
 

@@ -58,6 +58,29 @@ __device__ __forceinline__ float Sel3(int k, float x, float y, float z) {
     return k == 0 ? x : (k == 1 ? y : z);
 }
 
+// c ? a : b as ONE select instruction (SASS FSEL).  Written in PTX for the device because, left to
+// itself, the compiler turned the nine permutation selects of the triangle test into nine divergent
+// branch regions (lanes of a warp hold rays with different kz): 20 % of the leaf phase's issue slots
+// (profiles/r02c: 0x3ef0-0x4270 of StepKernel<0,0,5>).
+__device__ __forceinline__ float SelF(bool c, float a, float b) {
+#ifdef __CUDA_ARCH__
+    float r;
+    asm("{ .reg .pred p; setp.ne.u32 p, %3, 0; selp.f32 %0, %1, %2, p; }" : "=f"(r) : "f"(a), "f"(b), "r"((unsigned)c));
+    return r;
+#else
+    return c ? a : b;
+#endif
+}
+
+// Permute(v, kx, ky, kz) of shapes.cpp:186-196 with kx = (kz + 1) % 3, ky = (kx + 1) % 3:
+// kz = 0 -> (a1, a2, a0); kz = 1 -> (a2, a0, a1); kz = 2 -> (a0, a1, a2).
+__device__ __forceinline__ void Permute3(int kz, float a0, float a1, float a2, float *x, float *y, float *z) {
+    const bool k0 = kz == 0, k1 = kz == 1;
+    *x = SelF(k0, a1, SelF(k1, a2, a0));
+    *y = SelF(k0, a2, SelF(k1, a0, a1));
+    *z = SelF(k0, a0, SelF(k1, a1, a2));
+}
+
 __device__ __forceinline__ RayConst MakeRayConst(float ox, float oy, float oz, float dx,
                                                  float dy, float dz) {
     RayConst r;
@@ -141,11 +164,11 @@ __device__ __forceinline__ bool TriangleTest(const RayConst &r, float tMax, floa
     float a0 = Sub(p0x, r.ox), a1 = Sub(p0y, r.oy), a2 = Sub(p0z, r.oz);
     float c0 = Sub(p1x, r.ox), c1 = Sub(p1y, r.oy), c2 = Sub(p1z, r.oz);
     float e0_ = Sub(p2x, r.ox), e1_ = Sub(p2y, r.oy), e2_ = Sub(p2z, r.oz);
-    // :186-196 permute
-    float p0tx = Sel3(r.kx, a0, a1, a2), p0ty = Sel3(r.ky, a0, a1, a2), p0tz = Sel3(r.kz, a0, a1, a2);
-    float p1tx = Sel3(r.kx, c0, c1, c2), p1ty = Sel3(r.ky, c0, c1, c2), p1tz = Sel3(r.kz, c0, c1, c2);
-    float p2tx = Sel3(r.kx, e0_, e1_, e2_), p2ty = Sel3(r.ky, e0_, e1_, e2_),
-          p2tz = Sel3(r.kz, e0_, e1_, e2_);
+    // :186-196 permute (kx, ky follow from kz; branch-free)
+    float p0tx, p0ty, p0tz, p1tx, p1ty, p1tz, p2tx, p2ty, p2tz;
+    Permute3(r.kz, a0, a1, a2, &p0tx, &p0ty, &p0tz);
+    Permute3(r.kz, c0, c1, c2, &p1tx, &p1ty, &p1tz);
+    Permute3(r.kz, e0_, e1_, e2_, &p2tx, &p2ty, &p2tz);
     // :202-207 shear (separate multiply and add)
     p0tx = Add(p0tx, Mul(r.Sx, p0tz));
     p0ty = Add(p0ty, Mul(r.Sy, p0tz));

@@ -211,7 +211,12 @@ __global__ void __launch_bounds__(256, MINB) StepKernel(StepParams p) {
                 st[3] += 32 - __popc(nm | lm);
             }
             if (alive && cur >= 0) {
-                bool needPop = true;
+                // `descend`: the lane moves to a child of `cur`; otherwise it pops.  The child selection is
+                // written with selects and ONE predicated push, not as the reference's if / else-if chain:
+                // lanes of a warp take different arms at almost every node, and as branches the arms ran
+                // one after the other with 3-10 lanes each -- a third of the node step's issue slots
+                // (profiles/r02c, 0x2190-0x24c0 of StepKernel<0,0,5>).
+                bool descend = false;
                 if (curT < tMax) {  // the reference's `tMin < raytMax` for this node, made now
                     const unsigned char *np = wideBase + (size_t)(unsigned)cur * sizeof(WideNode);
                     const F8 a = Ldg256(np), b = Ldg256(np + 32);
@@ -263,23 +268,19 @@ __global__ void __launch_bounds__(256, MINB) StepKernel(StepParams p) {
                         stFar = (tFar <= xFar) && (xFar > 0.f);
                     }
                     const bool goNear = stNear && (tNear < tMax);
-                    if (goNear) {
-                        // The far child is stacked whenever its tMax-independent test passes: tMax
-                        // can GROW by an ulp before the pop (shapes.cpp:239-247), see DESIGN.md.
-                        if (stFar) {
-                            stack[sp] = ((unsigned long long)__float_as_uint(tFar) << 32) | (unsigned)refFar;
-                            ++sp;
-                        }
-                        cur = refNear;
-                        curT = tNear;  // tNear < tMax already established: next step passes
-                        needPop = false;
-                    } else if (stFar && (tFar < tMax)) {
-                        cur = refFar;
-                        curT = tFar;
-                        needPop = false;
-                    }
+                    const bool goFar = stFar && (tFar < tMax);
+                    // The far child is stacked whenever its tMax-independent test passes: tMax
+                    // can GROW by an ulp before the pop (shapes.cpp:239-247), see DESIGN.md.
+                    const bool push = goNear && stFar;
+                    if (push) stack[sp] = ((unsigned long long)__float_as_uint(tFar) << 32) | (unsigned)refFar;
+                    sp += push ? 1 : 0;
+                    // near child if it passes (tNear < tMax already established: next step passes), else the
+                    // far child if it does (aggregates.cpp:560-569); with neither, the values are dead
+                    cur = goNear ? refNear : (goFar ? refFar : cur);
+                    curT = goNear ? tNear : tFar;
+                    descend = goNear || goFar;
                 }
-                if (needPop) {
+                if (!descend) {
                     // aggregates.cpp:570-574.  Entries whose box test fails against the current tMax
                     // (`curT < tMax` false) are discarded here rather than one per iteration: the
                     // reference pops them one by one with the same outcome, and tMax cannot change

@@ -603,13 +603,17 @@ class Binding(Reference):
     def destroy(self, b):
         self.lib.nnbvh_binding_destroy(b)
 
-    def surface(self, b, rays8, batch: bool):
+    def surface(self, b, rays8, batch: bool, parallel: bool = False):
+        """parallel: the single-ray calls are made from pbrt's ParallelFor workers (set_threads > 1) at once."""
         rays8 = np.ascontiguousarray(rays8, dtype=np.float32)
         n = rays8.shape[0]
         hit = np.zeros(n, dtype=np.int32)
         t_hit = np.zeros(n, dtype=np.float32)
         out = np.zeros((n, 42), dtype=np.float32)
         f = self.lib.nnbvh_binding_intersect_surface_batch if batch else self.lib.nnbvh_binding_intersect_surface
+        if parallel:
+            f = self.lib.nnbvh_binding_intersect_surface_parallel
+            f.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int64] + [ctypes.c_void_p] * 3
         rc = f(b, _p(rays8), n, _p(hit), _p(t_hit), _p(out))
         if rc:
             raise RuntimeError(self.lib.nnbvh_binding_last_error().decode())
@@ -653,3 +657,33 @@ class Binding(Reference):
             raise RuntimeError(self.lib.nnbvh_binding_last_error().decode())
         return out
 
+
+    def wavefront_shadow_tr(self, scene, rays8, use_binding: bool, max_prims: int = 4, split: str = "sah"):
+        """One IntersectShadowTr over a real ShadowRayQueue -> (PixelSampleState::L[.][0] per ray, closest-hit
+        queries per ray (reference leg only, else zeros), GPU batches issued (binding leg only))."""
+        rays8 = np.ascontiguousarray(rays8, dtype=np.float32)
+        n = rays8.shape[0]
+        out = np.zeros(n, dtype=np.float32)
+        seg = np.zeros(n, dtype=np.int32)
+        batches = ctypes.c_int(0)
+        f = self.lib.nnbvh_binding_wavefront_shadow_tr
+        f.argtypes = [ctypes.c_void_p] + [ctypes.c_int] * 3 + [ctypes.c_void_p, ctypes.c_int] + [ctypes.c_void_p] * 3
+        rc = f(scene, max_prims, SPLIT[split], int(use_binding), _p(rays8), n, _p(out), _p(seg), ctypes.byref(batches))
+        if rc:
+            raise RuntimeError(self.lib.nnbvh_binding_last_error().decode())
+        return out, seg, batches.value
+
+    def wavefront_one_random(self, scene, seg6, use_binding: bool, max_prims: int = 4, split: str = "sah"):
+        """One IntersectOneRandom over a real SubsurfaceScatterQueue of probes p0 -> p1 ((n,6)) ->
+        (reservoirPDF per probe, chosen interaction's p and n (n,6), GPU batches issued (binding leg only))."""
+        seg6 = np.ascontiguousarray(seg6, dtype=np.float32)
+        n = seg6.shape[0]
+        pdf = np.zeros(n, dtype=np.float32)
+        pn = np.zeros((n, 6), dtype=np.float32)
+        batches = ctypes.c_int(0)
+        f = self.lib.nnbvh_binding_wavefront_one_random
+        f.argtypes = [ctypes.c_void_p] + [ctypes.c_int] * 3 + [ctypes.c_void_p, ctypes.c_int] + [ctypes.c_void_p] * 3
+        rc = f(scene, max_prims, SPLIT[split], int(use_binding), _p(seg6), n, _p(pdf), _p(pn), ctypes.byref(batches))
+        if rc:
+            raise RuntimeError(self.lib.nnbvh_binding_last_error().decode())
+        return pdf, pn, batches.value

@@ -870,6 +870,29 @@ int nnbvh_binding_intersect_surface(void *binding, const float *rays, int64_t n,
     }
     return 0;
 }
+// The same from pbrt's ParallelFor workers at once: what an integrator that holds the binding as its
+// Primitive does.  nnbvh_engine is not re-entrant; the binding's single-ray calls take a lock.
+int nnbvh_binding_intersect_surface_parallel(void *binding, const float *rays, int64_t n, int *hit, float *tHit,
+                                             float *out42) {
+    const pbrt::GPUBVHAggregate *b = (const pbrt::GPUBVHAggregate *)binding;
+    std::atomic<int> failed{0};
+    pbrt::ParallelFor(0, n, [&](int64_t i) {
+        try {
+            const float *r = rays + 8 * i;
+            pstd::optional<pbrt::ShapeIntersection> si = b->Intersect(MakeRay(r), r[3]);
+            hit[i] = si.has_value();
+            if (!si)
+                return;
+            tHit[i] = si->tHit;
+            PutSurface42(si->intr, out42 + 42 * i);
+        } catch (const nnbvh::Error &e) {
+            failed = e.code;
+        }
+    });
+    if (failed)
+        g_bindingError = "a single-ray call failed in a worker thread";
+    return failed;
+}
 // The batch surface: one IntersectBatch, then Resolve per hit
 int nnbvh_binding_intersect_surface_batch(void *binding, const float *rays, int64_t n, int *hit,
                                           float *tHit, float *out42) {
@@ -1001,6 +1024,143 @@ int nnbvh_binding_wavefront_shadow(void *scene, int maxPrimsInNode, int splitMet
     for (int i = 0; i < n; ++i) {
         pbrt::SampledSpectrum L = pss.L[i];
         L0[i] = L[0];
+    }
+    return 0;
+}
+
+// One IntersectShadowTr over a real ShadowRayQueue.  Materials and media are null in these scenes, so every
+// surface is a transparent interface: TraceTransmittance (wavefront/intersect.h:165-275) walks each ray from
+// surface to surface with intr.SpawnRayTo(pLight) until nothing is left before the light, and adds Ld to
+// PixelSampleState::L.  useBinding: pbrt::GPUBVHWavefrontAggregate (one GPU batch per round of segments);
+// else CPUAggregate::IntersectShadowTr's loop (wavefront/aggregate.cpp:70-92) over the reference BVHAggregate.
+// segments[i] = closest-hit queries the reference's walk of ray i made (CPU leg only; may be NULL).
+int nnbvh_binding_wavefront_shadow_tr(void *scene, int maxPrimsInNode, int splitMethod, int useBinding,
+                                      const float *rays, int n, float *L0, int *segments, int *gpuBatches) {
+    RefScene *s = (RefScene *)scene;
+    pbrt::Allocator alloc;
+    pbrt::ShadowRayQueue shadowQ(n, alloc);
+    pbrt::SOA<pbrt::PixelSampleState> pss(n, alloc);
+    pbrt::SampledWavelengths lambda = pbrt::SampledWavelengths::SampleUniform(0.5f);
+    for (int i = 0; i < n; ++i) {
+        const float *r = rays + 8 * (size_t)i;
+        pbrt::ShadowRayWorkItem w;
+        w.ray = MakeRay(r);
+        w.tMax = r[3];
+        w.lambda = lambda;
+        w.Ld = pbrt::SampledSpectrum(float(i % 7 + 1));
+        w.r_u = w.r_l = pbrt::SampledSpectrum(1.f);
+        w.pixelIndex = i;
+        shadowQ.Push(w);
+        pss.L[i] = pbrt::SampledSpectrum(0.f);
+    }
+    if (gpuBatches)
+        *gpuBatches = 0;
+    try {
+        if (useBinding) {
+            pbrt::GPUBVHWavefrontAggregate agg(s->primList, maxPrimsInNode,
+                                               (pbrt::BVHAggregate::SplitMethod)splitMethod, n);
+            const pbrt::WavefrontAggregate &w = agg;
+            w.IntersectShadowTr(n, &shadowQ, &pss);
+            if (gpuBatches)
+                *gpuBatches = agg.LastShadowTrBatches();
+        } else {
+            pbrt::Primitive aggregate(s->agg);
+            pbrt::ShadowRayQueue *sq = &shadowQ;
+            pbrt::SOA<pbrt::PixelSampleState> *ps = &pss;
+            pbrt::ParallelFor(0, shadowQ.Size(), [=](int index) {  // aggregate.cpp:72-91
+                const pbrt::ShadowRayWorkItem w = (*sq)[index];
+                pstd::optional<pbrt::ShapeIntersection> si;
+                int asked = 0;
+                pbrt::TraceTransmittance(
+                    w, ps,
+                    [&](pbrt::Ray ray, pbrt::Float tMax) -> pbrt::TransmittanceTraceResult {
+                        ++asked;
+                        si = aggregate.Intersect(ray, tMax);
+                        if (!si)
+                            return pbrt::TransmittanceTraceResult{false, pbrt::Point3f(), pbrt::Material()};
+                        return pbrt::TransmittanceTraceResult{true, si->intr.p(), si->intr.material};
+                    },
+                    [&](pbrt::Point3f p) -> pbrt::Ray { return si->intr.SpawnRayTo(p); });
+                if (segments)
+                    segments[index] = asked;
+            });
+        }
+    } catch (const nnbvh::Error &e) {
+        g_bindingError = e.what();
+        return e.code;
+    }
+    for (int i = 0; i < n; ++i) {
+        pbrt::SampledSpectrum L = pss.L[i];
+        L0[i] = L[0];
+    }
+    return 0;
+}
+
+// One IntersectOneRandom over a real SubsurfaceScatterQueue: probes p0 -> p1 (seg6[i] = p0.xyz, p1.xyz), the
+// probe's material null like every surface's, so each surface between the two points is a candidate.
+// Out per probe: reservoirPDF and, where it is non-zero, the chosen SubsurfaceInteraction's p() and n.
+int nnbvh_binding_wavefront_one_random(void *scene, int maxPrimsInNode, int splitMethod, int useBinding,
+                                       const float *seg6, int n, float *pdf, float *pn6, int *gpuBatches) {
+    RefScene *s = (RefScene *)scene;
+    pbrt::Allocator alloc;
+    pbrt::SubsurfaceScatterQueue q(n, alloc);
+    pbrt::SampledWavelengths lambda = pbrt::SampledWavelengths::SampleUniform(0.5f);
+    for (int i = 0; i < n; ++i) {
+        const float *p = seg6 + 6 * (size_t)i;
+        q.Push(pbrt::Point3f(p[0], p[1], p[2]), pbrt::Point3f(p[3], p[4], p[5]), 0, pbrt::Material(),
+               pbrt::TabulatedBSSRDF(), lambda, pbrt::SampledSpectrum(1.f), pbrt::SampledSpectrum(1.f),
+               pbrt::MediumInterface(), 1.f, i);
+    }
+    if (gpuBatches)
+        *gpuBatches = 0;
+    try {
+        if (useBinding) {
+            pbrt::GPUBVHWavefrontAggregate agg(s->primList, maxPrimsInNode,
+                                               (pbrt::BVHAggregate::SplitMethod)splitMethod, n);
+            const pbrt::WavefrontAggregate &w = agg;
+            w.IntersectOneRandom(n, &q);
+            if (gpuBatches)
+                *gpuBatches = agg.LastOneRandomBatches();
+        } else {
+            pbrt::Primitive aggregate(s->agg);
+            pbrt::SubsurfaceScatterQueue *sq = &q;
+            pbrt::ParallelFor(0, q.Size(), [=](int index) {  // aggregate.cpp:96-123
+                const pbrt::SubsurfaceScatterWorkItem &w = (*sq)[index];
+                uint64_t seed = pbrt::Hash(w.p0, w.p1);
+                pbrt::WeightedReservoirSampler<pbrt::SubsurfaceInteraction> wrs(seed);
+                pbrt::Interaction base(w.p0, 0.f, pbrt::Medium());
+                while (true) {
+                    pbrt::Ray r = base.SpawnRayTo(w.p1);
+                    if (r.d == pbrt::Vector3f(0, 0, 0))
+                        break;
+                    pstd::optional<pbrt::ShapeIntersection> si = aggregate.Intersect(r, 1);
+                    if (!si)
+                        break;
+                    base = si->intr;
+                    if (si->intr.material == w.material)
+                        wrs.Add(pbrt::SubsurfaceInteraction(si->intr), 1.f);
+                }
+                if (wrs.HasSample()) {
+                    sq->reservoirPDF[index] = wrs.SampleProbability();
+                    sq->ssi[index] = wrs.GetSample();
+                } else
+                    sq->reservoirPDF[index] = 0;
+            });
+        }
+    } catch (const nnbvh::Error &e) {
+        g_bindingError = e.what();
+        return e.code;
+    }
+    for (int i = 0; i < n; ++i) {
+        pdf[i] = q.reservoirPDF[i];
+        float *o = pn6 + 6 * (size_t)i;
+        for (int k = 0; k < 6; ++k)
+            o[k] = 0;
+        if (pdf[i] != 0) {
+            pbrt::SubsurfaceInteraction ssi = q.ssi[i];
+            pbrt::Point3f p = ssi.p();
+            o[0] = p.x, o[1] = p.y, o[2] = p.z, o[3] = ssi.n.x, o[4] = ssi.n.y, o[5] = ssi.n.z;
+        }
     }
     return 0;
 }

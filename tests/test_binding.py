@@ -122,3 +122,76 @@ def test_reference_loops_over_reference_queues_are_consistent(binding):
     L = binding.wavefront_shadow(sc, rays, use_binding=False)
     occ = binding.intersect_p(sc, rays, parallel=False)
     assert np.array_equal(L, np.where(occ != 0, 0, (np.arange(N) % 7 + 1) / 2).astype(np.float32))
+
+
+def _walk_scene(rng, T=6000, N=20_000):
+    c = rng.random((T, 1, 3), dtype=np.float32)
+    tris = ((c + np.float32(0.05) * (rng.random((T, 3, 3), dtype=np.float32) * 2 - 1)).reshape(T, 9)
+            + np.float32(0)).astype(np.float32)
+    rays = rand_rays(rng, N)
+    # shadow rays as the integrator makes them: d = pLight - o (unnormalised), tMax = 1 - ShadowEpsilon
+    target = rng.random((N, 3)).astype(np.float32) * 1.5 - 0.25
+    rays[:, 4:7] = target - rays[:, :3]
+    rays[:, 3] = np.float32(0.9999)
+    rays[:, 7] = rng.random(N)
+    rays[::97, 4:7] = 0.0          # degenerate: the walk does not start (`while (ray.d != 0)`)
+    seg6 = np.concatenate([rays[:, :3], target], axis=1).astype(np.float32)
+    return tris, rays, seg6
+
+
+def test_reference_transmittance_and_subsurface_loops_walk_several_surfaces():
+    """CPU half of the test below: CPUAggregate::IntersectShadowTr / IntersectOneRandom (wavefront/aggregate.cpp:70-124)
+    over the reference BVHAggregate.  With null materials every surface is an interface, so the walks cross several
+    surfaces -- the multi-round case the batched binding has to reproduce -- and run on several host threads."""
+    from oracle import pyoracle
+    if not pyoracle.binding_available():
+        pytest.skip("oracle/_ref/libnnbvh_ref_binding.so not built (no /root/reference on this machine)")
+    b = pyoracle.Binding(threads=4)
+    rng = np.random.default_rng(23)
+    tris, rays, seg6 = _walk_scene(rng, 3000, 5000)
+    sc = b.scene(tris, 4, "sah")
+    L, seg, _ = b.wavefront_shadow_tr(sc, rays, use_binding=False)
+    assert seg.max() >= 4 and (seg[::97] == 0).all() and (seg[1::97] >= 1).all()
+    # nothing is opaque and there is no medium: every walk reaches the light with T_ray = 1 -> L = Ld / 2
+    assert np.array_equal(L, ((np.arange(len(rays)) % 7 + 1) / 2).astype(np.float32))
+    pdf, pn, _ = b.wavefront_one_random(sc, seg6, use_binding=False)
+    assert 0.2 * len(pdf) < (pdf > 0).sum() and (pdf[pdf > 0] <= 1).all() and (pdf[pdf > 0] < 1).sum() > 100
+    b.set_threads(1)
+
+
+@pytest.mark.gpu
+def test_batched_shadow_tr_and_one_random_match_the_reference_loops():
+    """pbrt::GPUBVHWavefrontAggregate::IntersectShadowTr / IntersectOneRandom -- one GPU batch per ROUND of segments
+    (integration/pbrt/gpubvh_wavefront.h) -- through the WavefrontAggregate interface on the reference's queues,
+    with pbrt's ParallelFor on 4 host threads, against CPUAggregate's loops on the same queues: the same radiance in
+    SOA<PixelSampleState>, the same reservoir probabilities and chosen SubsurfaceInteractions, and no more GPU
+    batches than the longest walk has segments (round-1: one single-ray GPU batch per segment per ray, from
+    unsynchronised worker threads)."""
+    from oracle import pyoracle
+    if not pyoracle.binding_available():
+        pytest.skip("oracle/_ref/libnnbvh_ref_binding.so not built (no /root/reference on this machine)")
+    b = pyoracle.Binding(threads=4)
+    rng = np.random.default_rng(29)
+    tris, rays, seg6 = _walk_scene(rng)
+    sc = b.scene(tris, 4, "sah")
+    want_L, seg, _ = b.wavefront_shadow_tr(sc, rays, use_binding=False)
+    got_L, _, batches = b.wavefront_shadow_tr(sc, rays, use_binding=True)
+    assert np.array_equal(got_L, want_L)
+    assert seg.max() >= 4 and batches == seg.max()
+    want_pdf, want_pn, _ = b.wavefront_one_random(sc, seg6, use_binding=False)
+    got_pdf, got_pn, batches = b.wavefront_one_random(sc, seg6, use_binding=True)
+    assert np.array_equal(got_pdf, want_pdf) and np.array_equal(got_pn.view(np.uint32), want_pn.view(np.uint32))
+    assert (want_pdf > 0).sum() > 2000 and 2 <= batches <= 64
+    # the single-ray surface used concurrently: Primitive::Intersect from 4 ParallelFor workers at once (the
+    # engine is not re-entrant; the binding's single-ray calls take a lock)
+    bb = b.create(sc, 4, "sah")
+    try:
+        sub = rays[:2000][(rays[:2000, 4:7] != 0).any(axis=1)]   # d = 0 "hits" with tHit = NaN on both sides; the NaN's
+        whit, wt, w42 = b.intersect_surface(sc, sub)             # sign / payload is the host's vs the device's
+        ghit, gt, g42 = b.surface(bb, sub, batch=False, parallel=True)
+        assert np.array_equal(ghit, whit) and np.array_equal(gt.view(np.uint32)[whit], wt.view(np.uint32)[whit])
+        bad = np.argwhere(g42.view(np.uint32)[whit] != w42.view(np.uint32)[whit])
+        assert bad.size == 0, f"{len(bad)} words differ: rows {np.unique(bad[:, 0])[:8]} columns {np.unique(bad[:, 1])}"
+    finally:
+        b.destroy(bb)
+        b.set_threads(1)
