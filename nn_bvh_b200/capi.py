@@ -13,7 +13,7 @@ import os
 import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libnnbvh.so")
+LIB_PATH = os.environ.get("NNBVH_LIB") or os.path.join(HERE, "libnnbvh.so")   # NNBVH_LIB: an A/B build (tools/)
 
 MISS = 0xFFFFFFFF
 NOALLOC_MAX_RAYS = 1 << 20   # NNBVH_NOALLOC_MAX_RAYS

@@ -4,7 +4,7 @@
 # Device code: --fmad=false (plus explicit _rn intrinsics in exact_math.cuh).
 set -e
 HERE="$(cd "$(dirname "$0")" && pwd)"
-OUT="$HERE/../libnnbvh.so"
+OUT="${NNBVH_OUT:-$HERE/../libnnbvh.so}"
 NVCC="${NVCC:-/usr/local/cuda/bin/nvcc}"
 "$NVCC" -std=c++17 -O3 -lineinfo --fmad=false -prec-div=true -prec-sqrt=true -ftz=false \
     -gencode arch=compute_100a,code=sm_100a \

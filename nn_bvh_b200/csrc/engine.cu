@@ -172,8 +172,11 @@ struct nnbvh_engine {
     Slot slots[kMaxSlots];
     // tuning knobs (env overridable, see nnbvh_create)
     int wideMinB = 5;        // CTAs/SM the traversal kernel is compiled for
-    int refillBelow = 20;
-    int leafQuorum = 12;
+    // StepKernel lane policy; -1 = by scene size (StepKnobs): the optimum moved down when the node step's child
+    // selection became branch-free (r02e-g sweeps: bathroom +3.5 / +2.4 / +8.7 % bounce / shadow / primary at
+    // quorum 8, refill 12; the latency-bound scenes -- crown, the synthetic soups -- prefer 10 / 16)
+    int refillBelow = -1;
+    int leafQuorum = -1;
     int stepStats = 0;       // NNBVH_STEP_STATS=1: run the counting instantiation of StepKernel
     unsigned long long *dStats = nullptr;
     int popLoop = 1;         // StepKernel: discard culled stack entries inside the pop
@@ -193,6 +196,16 @@ struct nnbvh_engine {
 // nnbvh_intersect_closest_noalloc's set-up (end of this file): resolves the device address of the
 // file-scope scratch array for `device`, which must be current.  Called by nnbvh_create.
 static int NoAllocSetup(int device);
+
+// refillBelow / leafQuorum of the StepKernel for the uploaded scene (see nnbvh_engine)
+static void StepKnobs(const nnbvh_engine *e, uint32_t *refillBelow, uint32_t *leafQuorum) {
+    const size_t sceneBytes = sizeof(WideNode) * (size_t)e->sc.nWide + 48 * (size_t)e->sc.nPrims;
+    const bool cacheResident = sceneBytes < ((size_t)96 << 20);  // fits the L2 with room for the ray / hit streams
+    const int rb = e->refillBelow > 0 ? e->refillBelow : (cacheResident ? 12 : 16);
+    const int lq = e->leafQuorum > 0 ? e->leafQuorum : (cacheResident ? 8 : 10);
+    *refillBelow = (uint32_t)std::min(32, std::max(1, rb));
+    *leafQuorum = (uint32_t)std::min(32, std::max(1, lq));
+}
 
 extern "C" const char *nnbvh_last_error(void) { return g_err; }
 extern "C" const char *nnbvh_version(void) { return "nnbvh-b200 0.1 (sm_100a)"; }
@@ -939,8 +952,7 @@ static int LaunchTraversal(nnbvh_engine *e, cudaStream_t st, bool any, bool coun
             sp.occluded = o.occ;
             sp.perm = perm;
             sp.permOn = permOn;
-            sp.refillBelow = (uint32_t)std::min(32, std::max(1, e->refillBelow));
-            sp.leafQuorum = (uint32_t)std::min(32, std::max(1, e->leafQuorum));
+            StepKnobs(e, &sp.refillBelow, &sp.leafQuorum);
             sp.popLoop = (uint32_t)(e->popLoop != 0);
             sp.sphereQuorum = (uint32_t)std::min(32, std::max(1, e->sphereQuorum));
             if (e->stepStats) {
@@ -988,8 +1000,8 @@ static int LaunchTraversal(nnbvh_engine *e, cudaStream_t st, bool any, bool coun
         p.occluded = o.occ;
         p.cursor = cursor;
         p.smemNodes = smemNodes;
-        p.refillBelow = (uint32_t)std::min(32, std::max(1, e->refillBelow));
-        p.leafQuorum = (uint32_t)std::min(32, std::max(1, e->leafQuorum));
+        p.refillBelow = (uint32_t)std::min(32, std::max(1, e->refillBelow > 0 ? e->refillBelow : 20));
+        p.leafQuorum = (uint32_t)std::min(32, std::max(1, e->leafQuorum > 0 ? e->leafQuorum : 12));
         int rc = any ? LaunchWide<true>(e, st, p, smemNodes * (uint32_t)sizeof(WideNode))
                      : LaunchWide<false>(e, st, p, smemNodes * (uint32_t)sizeof(WideNode));
         if (rc) return rc;
@@ -1695,8 +1707,7 @@ extern "C" int nnbvh_intersect_closest_noalloc(nnbvh_engine *e, const nnbvh_ray 
     sp.in.aos = reinterpret_cast<const float4 *>(raysDev);
     sp.n = n;
     sp.hits = hitsDev;
-    sp.refillBelow = (uint32_t)std::min(32, std::max(1, e->refillBelow));
-    sp.leafQuorum = (uint32_t)std::min(32, std::max(1, e->leafQuorum));
+    StepKnobs(e, &sp.refillBelow, &sp.leafQuorum);
     sp.popLoop = (uint32_t)(e->popLoop != 0);
     sp.sphereQuorum = (uint32_t)std::min(32, std::max(1, e->sphereQuorum));
     if (e->boxesRegular && !e->exactOnly) {  // fast-slab launch; rays it cannot take go to the deferred list

@@ -95,6 +95,9 @@ __device__ __forceinline__ RayConst ToRayConst(const StepRay &s) {
 
 constexpr float kNegInf = -__builtin_huge_valf();
 
+template <bool ANY> struct StackWord { typedef unsigned long long type; };
+template <> struct StackWord<true> { typedef unsigned type; };
+
 template <bool ANY, bool EXACT, int MINB, bool STATS = false, bool SPHERES = false>
 __global__ void __launch_bounds__(256, MINB) StepKernel(StepParams p) {
     // STATS: [0] phase-A iterations, [1] lanes at a node, [2] lanes parked at a leaf, [3] lanes without
@@ -114,8 +117,11 @@ __global__ void __launch_bounds__(256, MINB) StepKernel(StepParams p) {
     HitRegs hit{NNBVH_MISS, 0.f, 0.f, 0.f, 0.f};
     int cur = 0, sp = 0;
     float curT = 0.f;
-    // stack entry = {ref, tEntry} packed into 64 bits (one STL.64 / LDL.64 per push / pop)
-    unsigned long long stack[kMaxStack];
+    // stack entry = {ref, tEntry} packed into 64 bits (one STL.64 / LDL.64 per push / pop).
+    // ANY: IntersectP never shrinks tMax (aggregates.cpp:581-624), so `tMin < raytMax` of a child can be
+    // settled for good when its parent is fetched: only children that pass it are entered or stacked, the
+    // entry is the bare 32-bit ref, nothing is re-validated at a pop and no lane carries curT.
+    typename StackWord<ANY>::type stack[kMaxStack];
     bool exhausted = false;
     // SPHERES: a lane that steps onto a sphere slot waits (sphWait) until `sphereQuorum` lanes of its warp
     // wait at spheres or no lane can do anything else: Sphere::BasicIntersect is ~20x a triangle test, and
@@ -217,7 +223,7 @@ __global__ void __launch_bounds__(256, MINB) StepKernel(StepParams p) {
                 // one after the other with 3-10 lanes each -- a third of the node step's issue slots
                 // (profiles/r02c, 0x2190-0x24c0 of StepKernel<0,0,5>).
                 bool descend = false;
-                if (curT < tMax) {  // the reference's `tMin < raytMax` for this node, made now
+                if (ANY || curT < tMax) {  // the reference's `tMin < raytMax` for this node, made now
                     const unsigned char *np = wideBase + (size_t)(unsigned)cur * sizeof(WideNode);
                     const F8 a = Ldg256(np), b = Ldg256(np + 32);
                     // WideNode: lo0 xyz, hi0 xyz, lo1 xy | lo1 z, hi1 xyz, ref0, ref1, axis, pad
@@ -271,13 +277,16 @@ __global__ void __launch_bounds__(256, MINB) StepKernel(StepParams p) {
                     const bool goFar = stFar && (tFar < tMax);
                     // The far child is stacked whenever its tMax-independent test passes: tMax
                     // can GROW by an ulp before the pop (shapes.cpp:239-247), see DESIGN.md.
-                    const bool push = goNear && stFar;
-                    if (push) stack[sp] = ((unsigned long long)__float_as_uint(tFar) << 32) | (unsigned)refFar;
+                    const bool push = goNear && (ANY ? goFar : stFar);
+                    if (push) {
+                        if (ANY) stack[sp] = (unsigned)refFar;
+                        else stack[sp] = ((unsigned long long)__float_as_uint(tFar) << 32) | (unsigned)refFar;
+                    }
                     sp += push ? 1 : 0;
                     // near child if it passes (tNear < tMax already established: next step passes), else the
                     // far child if it does (aggregates.cpp:560-569); with neither, the values are dead
                     cur = goNear ? refNear : (goFar ? refFar : cur);
-                    curT = goNear ? tNear : tFar;
+                    if (!ANY) curT = goNear ? tNear : tFar;
                     descend = goNear || goFar;
                 }
                 if (!descend) {
@@ -286,14 +295,22 @@ __global__ void __launch_bounds__(256, MINB) StepKernel(StepParams p) {
                     // reference pops them one by one with the same outcome, and tMax cannot change
                     // between this pop and the lane's next step.
                     bool got = false;
-                    while (sp > 0) {
-                        --sp;
-                        const unsigned long long e = stack[sp];
-                        cur = (int)(unsigned)e;
-                        curT = __uint_as_float((unsigned)(e >> 32));
-                        if (curT < tMax || !p.popLoop) {
+                    if (ANY) {
+                        if (sp > 0) {
+                            --sp;
+                            cur = (int)(unsigned)stack[sp];
                             got = true;
-                            break;
+                        }
+                    } else {
+                        while (sp > 0) {
+                            --sp;
+                            const unsigned long long e = stack[sp];
+                            cur = (int)(unsigned)e;
+                            curT = __uint_as_float((unsigned)(e >> 32));
+                            if (curT < tMax || !p.popLoop) {
+                                got = true;
+                                break;
+                            }
                         }
                     }
                     if (!got) {
@@ -309,7 +326,7 @@ __global__ void __launch_bounds__(256, MINB) StepKernel(StepParams p) {
         // ---- phase B: every parked lane tests ONE triangle of its leaf ----
         if (STATS) {
             const unsigned parked = __ballot_sync(0xffffffffu, alive && cur < 0);
-            const unsigned testing = __ballot_sync(0xffffffffu, alive && cur < 0 && curT < tMax);
+            const unsigned testing = __ballot_sync(0xffffffffu, alive && cur < 0 && (ANY || curT < tMax));
             st[4] += 1;
             st[5] += __popc(parked);
             st[6] += __popc(testing);
@@ -324,8 +341,8 @@ __global__ void __launch_bounds__(256, MINB) StepKernel(StepParams p) {
         }
         if (alive && cur < 0 && (!(SPHERES && sphWait) || doSphere)) {
             bool needPop = true;
-            if ((SPHERES && sphWait) || curT < tMax) {  // box test of the leaf node, made when the lane steps onto it
-                curT = kNegInf;  // ... and only then: later triangles of this leaf skip it (:547-555)
+            if (ANY || (SPHERES && sphWait) || curT < tMax) {  // box test of the leaf node, made when the lane steps onto it
+                if (!ANY) curT = kNegInf;  // ... and only then: later triangles of this leaf skip it (:547-555)
                 const uint32_t prim = (uint32_t)cur & 0x7fffffffu;
                 const float4 *tp = tris + 3 * (size_t)prim;
                 const float4 v0 = __ldg(tp), v1 = __ldg(tp + 1), v2 = __ldg(tp + 2);
@@ -377,14 +394,22 @@ __global__ void __launch_bounds__(256, MINB) StepKernel(StepParams p) {
             }
             if (needPop) {  // :556-558; culled entries are skipped as in phase A
                 bool got = false;
-                while (sp > 0) {
-                    --sp;
-                    const unsigned long long e = stack[sp];
-                    cur = (int)(unsigned)e;
-                    curT = __uint_as_float((unsigned)(e >> 32));
-                    if (curT < tMax || !p.popLoop) {
+                if (ANY) {
+                    if (sp > 0) {
+                        --sp;
+                        cur = (int)(unsigned)stack[sp];
                         got = true;
-                        break;
+                    }
+                } else {
+                    while (sp > 0) {
+                        --sp;
+                        const unsigned long long e = stack[sp];
+                        cur = (int)(unsigned)e;
+                        curT = __uint_as_float((unsigned)(e >> 32));
+                        if (curT < tMax || !p.popLoop) {
+                            got = true;
+                            break;
+                        }
                     }
                 }
                 if (!got) {
