@@ -40,6 +40,7 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
 METRIC = "Mrays/s closest-hit+shadow"
+OUT = sys.stdout   # replaced by the real stdout in __main__ (see _quiet_stdout)
 UNIT = "Mrays/s"
 
 
@@ -62,9 +63,17 @@ def parse():
     ap.add_argument("--c5-tris", type=int, default=10_000_000)
     ap.add_argument("--c5-rays", type=int, default=256 << 20, help="config 5: rays of the ONE batch all ranks share")
     ap.add_argument("--c5-steps", type=int, default=5, help="config 5: at most this many timed steps")
-    ap.add_argument("--c5-chunks", default="0.4,0.3,0.2,0.1",
+    ap.add_argument("--c5-chunks", default="0.5,0.5",
                     help="config 5, N>1: fractions of a rank's shard traced and delivered one after another "
                          "(a chunk's delivery overlaps the next chunk's traversal)")
+    ap.add_argument("--c5-rank0-share", type=float, default=1.0,
+                    help="config 5, N>1: rank 0's share of the batch relative to the other ranks' (1 = equal)")
+    ap.add_argument("--c5-copy-streams", type=int, default=4,
+                    help="config 5, N>1: copy engines a rank's delivery is spread over")
+    ap.add_argument("--c5-lanes", type=int, default=2, choices=[1, 2],
+                    help="config 5, N>1: chunks alternate between this many engines / streams (nnbvh_clone), so that "
+                         "one chunk's ray-ordering pre-pass and first CTAs fill the SMs the previous chunk's "
+                         "persistent CTAs free as it drains")
     ap.add_argument("--exchange", default="peer", choices=["peer", "nccl"],
                     help="N>1: how hit records reach rank 0: copy engines into a peer-mapped window, or an NCCL gather")
     return ap.parse_args()
@@ -279,7 +288,7 @@ def run_reference(args):
             "cpu_baseline": {"value": val, "unit": UNIT, "cores": cpu.cores, "kind": cpu.kind,
                              "sample": sample},
             "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-    print(json.dumps(line), flush=True)
+    print(json.dumps(line), file=OUT, flush=True)
 
 
 
@@ -381,7 +390,7 @@ def run_ours(args):
                         "gpu_launches": c5["gpu_launches"], "roofline": c5["roofline"]}
             line.setdefault("configs", {})["synthetic10M"] = c5
     if rank == 0:
-        print(json.dumps(line), flush=True)
+        print(json.dumps(line), file=OUT, flush=True)
     if world > 1:
         dist.destroy_process_group()
 
@@ -709,24 +718,40 @@ def run_config5(args, world, rank, local, dev):
     del d_nodes, d_tris
     torch.cuda.empty_cache()
 
-    lo, hi = sharding.shard_range(NR, rank, world)
+    # rank 0 also takes in every other rank's records over its NVLink ports: it may trace a smaller share
+    ranges = sharding.weighted_ranges(NR, [args.c5_rank0_share if r == 0 and world > 1 else 1.0 for r in range(world)])
+    lo, hi = ranges[rank]
     n_loc = hi - lo
     rays = R.hashed_random_rays(lo, hi, dev)
     hits = torch.zeros((n_loc, 5), dtype=torch.int32, device=dev)
     stream = torch.cuda.Stream(device=dev)
     torch.cuda.set_stream(stream)
     agg.set_stream(stream.cuda_stream)
-    win = sharding.PeerWindow(NR, (5,), torch.int32, dst=0) if world > 1 else None
+    win = sharding.PeerWindow(NR, (5,), torch.int32, dst=0, copy_streams=args.c5_copy_streams, ranges=ranges) if world > 1 else None
+    if win is not None and rank == 0:
+        hits = win.tensor[lo:hi]   # rank 0 traces straight into its slice of the window: nothing to deliver
     fr = [float(x) for x in args.c5_chunks.split(",")] if world > 1 else [1.0]
     cum = np.cumsum([0.0] + fr) / sum(fr)
     bounds = sorted(set(int(round(c * n_loc)) for c in cum))
+    # lanes: chunk c runs on engine / stream c % lanes (a clone shares the uploaded scene)
+    lanes = [(agg, stream)]
+    if world > 1 and args.c5_lanes == 2 and len(bounds) > 2:
+        stream2 = torch.cuda.Stream(device=dev)
+        agg2 = agg.clone()
+        agg2.set_stream(stream2.cuda_stream)
+        lanes.append((agg2, stream2))
+    lane_done = torch.cuda.Event()
     setup_s = time.perf_counter() - t_setup
 
     def step():
-        for s0, s1 in zip(bounds[:-1], bounds[1:]):
-            agg.IntersectBatch(rays[s0:s1], hits=hits[s0:s1], n=s1 - s0)
-            if win is not None:
-                win.deliver(hits[s0:s1], stream, at=s0)
+        for c, (s0, s1) in enumerate(zip(bounds[:-1], bounds[1:])):
+            a, st = lanes[c % len(lanes)]
+            a.IntersectBatch(rays[s0:s1], hits=hits[s0:s1], n=s1 - s0)
+            if win is not None and rank != 0:
+                win.deliver(hits[s0:s1], st, at=s0)
+        if len(lanes) > 1:
+            lane_done.record(lanes[1][1])
+            stream.wait_event(lane_done)
         if win is not None:
             win.wait_on(stream)   # the step ends when this rank's records are on rank 0
 
@@ -740,15 +765,17 @@ def run_config5(args, world, rank, local, dev):
     for _ in range(warm):
         step()
     barrier()
-    l0 = agg.launch_count()
+    l0 = sum(a.launch_count() for a, _ in lanes)
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
     ev0.record(stream)
+    if len(lanes) > 1:
+        lanes[1][1].wait_event(ev0)
     for _ in range(steps):
         step()
     ev1.record(stream)
     barrier()
-    launches = agg.launch_count() - l0
+    launches = sum(a.launch_count() for a, _ in lanes) - l0
     t = torch.tensor([ev0.elapsed_time(ev1)], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -796,9 +823,10 @@ def run_config5(args, world, rank, local, dev):
                            f"{world} rank(s)", "metric": "Mrays/s closest-hit", "value": NR * steps / (total_ms / 1e3) / 1e6,
                "unit": UNIT, "scaling": "strong", "n_gpus": world, "steps": steps, "warmup": warm,
                "ms_per_step": total_ms / steps, "triangles": T, "bvh_nodes": M, "rays_total": NR,
-               "rays_per_rank": n_loc, "gpu_launches": int(launches),
+               "rays_per_rank": [b - a for a, b in ranges], "gpu_launches": int(launches),
                "exchange": (None if world == 1 else
-                            f"each rank traces its shard in {len(bounds) - 1} chunks (fractions {args.c5_chunks}) and "
+                            f"each rank traces its shard in {len(bounds) - 1} chunks (fractions {args.c5_chunks}) "
+                            f"alternating between {len(lanes)} engine(s) / stream(s), and "
                             "delivers every chunk's hit records into rank 0's peer-mapped window with a copy engine "
                             "over NVLink while the next chunk is traced; the step ends when all records are on rank 0 "
                             f"({NR * 20 / 1e9:.1f} GB)"),
@@ -809,15 +837,27 @@ def run_config5(args, world, rank, local, dev):
                             "expected": exp, "ok": (checksum == exp) if exp else None,
                             "gathered_records_match": gathered_ok},
                "kernel_only_ms": traversal_ms, "roofline": roofline}
+    del rays, hits
     if win is not None:
         win.close()
-    del rays, hits
-    agg.close()
+        win = None
+    for a, _ in reversed(lanes):
+        a.close()
     torch.cuda.empty_cache()
     return out
 
 
+def _quiet_stdout():
+    """stdout must carry exactly ONE JSON line: whatever a library prints to file descriptor 1 (NCCL's version
+    banner does, whatever NCCL_DEBUG_FILE says) goes to stderr instead; the line is written to the real stdout."""
+    sys.stdout.flush()
+    real = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
+    return real
+
+
 if __name__ == "__main__":
+    OUT = _quiet_stdout()
     a = parse()
     if a.impl == "reference":
         run_reference(a)

@@ -224,8 +224,8 @@ int nnbvh_upload_scene_alpha(nnbvh_engine *e, const nnbvh_node *nodes, uint32_t 
  * traversed there.  A hit on an instance is {prim = the instance's top-level slot, t and b0,b1,b2 of
  * the inner triangle in the instance ray's parametrisation} -- what TransformedPrimitive::Intersect
  * returns -- plus, from nnbvh_intersect_closest_instanced, the ordered primitive inside the object.
- * First version: such scenes run the one-thread-per-ray kernel (nested traversal), and a scene holds
- * either spheres or instances. */
+ * Such scenes run the one-thread-per-ray kernel (nested traversal).  Spheres and alpha-tested triangles
+ * beside instances: nnbvh_upload_scene_general. */
 typedef struct nnbvh_object {
     const nnbvh_node *nodes;
     uint32_t nNodes;
@@ -253,6 +253,34 @@ int nnbvh_intersect_closest_instanced_soa(nnbvh_engine *e, const float *ox, cons
                                           const float *oz, const float *dx, const float *dy,
                                           const float *dz, const float *tMax, uint64_t n,
                                           nnbvh_hit *hits, uint32_t *innerPrim);
+
+/* ---- general scenes: any mix of primitive kinds in ONE list -----------------------------------
+ * What pbrt hands to one BVHAggregate (scene.cpp:1352-1591): SimplePrimitive / GeometricPrimitive over
+ * Triangle or Sphere, GeometricPrimitive with a constant alpha texture over Triangle, TransformedPrimitive
+ * over per-object aggregates -- all in the same std::vector<Primitive> (cpu/primitive.cpp:50-130).
+ * Per ordered primitive i: orderedSphereIndex[i] >= 0 -> sphere, orderedInstanceIndex[i] >= 0 -> instance
+ * (never both), else the triangle orderedTriVerts9[9 i ..] with orderedAlpha[i] (>= 1 or a NULL array: no
+ * alpha test).  Index arrays of kinds that do not occur may be NULL.  Hit records are those of the
+ * specialised uploads: triangle {prim, t, b}, sphere {prim, tHit, pObj}, instance {prim = top-level slot,
+ * inner triangle's t, b} (+ innerPrim from nnbvh_intersect_closest_instanced).  A description with at most
+ * one extra kind is routed to that kind's own upload and kernel; a real mix runs a one-thread-per-ray
+ * kernel, and per-ray counters are unavailable for it. */
+typedef struct nnbvh_scene_desc {
+    const nnbvh_node *nodes;
+    uint32_t nNodes;
+    const float *orderedTriVerts9;
+    uint32_t nPrims;
+    const int32_t *orderedSphereIndex;
+    const nnbvh_sphere *spheres;
+    uint32_t nSpheres;
+    const int32_t *orderedInstanceIndex;
+    const nnbvh_instance *instances;
+    uint32_t nInstances;
+    const nnbvh_object *objects;
+    uint32_t nObjects;
+    const float *orderedAlpha;
+} nnbvh_scene_desc;
+int nnbvh_upload_scene_general(nnbvh_engine *e, const nnbvh_scene_desc *d);
 
 /* BVHAggregate::Intersect (cpu/aggregates.cpp:529-579) for n rays. */
 int nnbvh_intersect_closest(nnbvh_engine *e, const nnbvh_ray *rays, uint64_t n,

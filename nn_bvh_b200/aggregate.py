@@ -290,6 +290,75 @@ class GPUBVHAggregate:
                                             capi.ptr(self.ordered_tris9), len(self.ordered_tris9)))
 
     @classmethod
+    def General(cls, tris9=None, alpha=None, spheres=None, objects=None, instances=None,
+                max_prims_in_node: int = 4, split_method: str = "sah", *, tree: Optional[dict] = None,
+                device: int = -1):
+        """ONE primitive list holding any mix of kinds (nnbvh_upload_scene_general): caller primitive ids are
+        triangles 0..T-1 (alpha[i] < 1: constant-alpha GeometricPrimitive), then spheres, then instances --
+        the order pbrt's scene code appends them in.  objects: (T_j,9) soups in object space.
+        tree: instead of building here, a ready flattened tree as a dict(nodes, ordered_tris9, sphere_of,
+        instance_of, ordered_alpha, objects=[dict(nodes, ordered_tris9)], order) -- e.g. the reference's own."""
+        self = object.__new__(cls)
+        L = capi.lib()
+        opts = capi.Options(device=device, kernel=capi.KERNEL_AUTO, smem_top_nodes=-1)
+        h = ctypes.c_void_p()
+        capi.check(L.nnbvh_create(ctypes.byref(opts), ctypes.byref(h)))
+        self._h = h
+        self.spheres = None if spheres is None else np.ascontiguousarray(spheres).view(SPHERE_DTYPE).reshape(-1)
+        self.instances = None if instances is None else np.ascontiguousarray(instances).view(INSTANCE_DTYPE).reshape(-1)
+        S = 0 if self.spheres is None else len(self.spheres)
+        K = 0 if self.instances is None else len(self.instances)
+        if tree is None:
+            tris9 = (np.zeros((0, 9), dtype=np.float32) if tris9 is None
+                     else np.ascontiguousarray(tris9, dtype=np.float32).reshape(-1, 9))
+            T = len(tris9)
+            objs = []
+            for soup in (objects or []):
+                soup = np.ascontiguousarray(soup, dtype=np.float32).reshape(-1, 9)
+                on, oo = build_bvh(soup, max_prims_in_node, split_method)
+                objs.append(dict(nodes=on, order=oo, ordered_tris9=np.ascontiguousarray(soup[oo])))
+            parts = [triangle_bounds(tris9)]
+            if S:
+                parts.append(sphere_bounds(self.spheres))
+            if K:
+                roots = np.stack([objs[j]["nodes"][0]["bounds"] for j in self.instances["object"]])
+                parts.append(instance_bounds(self.instances, roots))
+            nodes, order = build_bvh_bounds(np.concatenate(parts), max_prims_in_node, split_method)
+            o64 = order.astype(np.int64)
+            ordered = np.zeros((len(order), 9), dtype=np.float32)
+            is_tri = o64 < T
+            ordered[is_tri] = tris9[o64[is_tri]]
+            oa = np.ones(len(order), dtype=np.float32)
+            if alpha is not None:
+                oa[is_tri] = np.asarray(alpha, dtype=np.float32).reshape(-1)[o64[is_tri]]
+            tree = dict(nodes=nodes, order=order, ordered_tris9=ordered, ordered_alpha=oa, objects=objs,
+                        sphere_of=np.where((o64 >= T) & (o64 < T + S), o64 - T, -1).astype(np.int32),
+                        instance_of=np.where(o64 >= T + S, o64 - T - S, -1).astype(np.int32))
+        self.nodes = np.ascontiguousarray(tree["nodes"]).view(NODE_DTYPE).reshape(-1)
+        self.ordered_tris9 = np.ascontiguousarray(tree["ordered_tris9"], dtype=np.float32).reshape(-1, 9)
+        self.order = tree.get("order")
+        self.ordered_sphere_index = np.ascontiguousarray(tree["sphere_of"], dtype=np.int32)
+        self.ordered_instance_index = np.ascontiguousarray(tree["instance_of"], dtype=np.int32)
+        self.ordered_alpha = np.ascontiguousarray(tree["ordered_alpha"], dtype=np.float32)
+        self.objects = [dict(nodes=np.ascontiguousarray(o["nodes"]).view(NODE_DTYPE).reshape(-1),
+                             ordered_tris9=np.ascontiguousarray(o["ordered_tris9"], dtype=np.float32).reshape(-1, 9))
+                        for o in tree.get("objects", [])]
+        objs_c = (_Object * max(1, len(self.objects)))()
+        for j, o in enumerate(self.objects):
+            objs_c[j] = _Object(o["nodes"].ctypes.data, len(o["nodes"]), o["ordered_tris9"].ctypes.data,
+                                len(o["ordered_tris9"]))
+        d = capi.SceneDesc(self.nodes.ctypes.data, len(self.nodes), self.ordered_tris9.ctypes.data,
+                           len(self.ordered_tris9),
+                           self.ordered_sphere_index.ctypes.data if S else None,
+                           self.spheres.ctypes.data if S else None, S,
+                           self.ordered_instance_index.ctypes.data if K else None,
+                           self.instances.ctypes.data if K else None, K,
+                           ctypes.cast(objs_c, ctypes.c_void_p) if K else None, len(self.objects) if K else 0,
+                           self.ordered_alpha.ctypes.data)
+        capi.check(L.nnbvh_upload_scene_general(h, ctypes.byref(d)))
+        return self
+
+    @classmethod
     def FromDevice(cls, nodes_dev, n_nodes: int, ordered_tris9_dev, n_prims: int, device: int = -1,
                    kernel: int = capi.KERNEL_AUTO):
         """An aggregate over a flattened tree and ordered triangles that already live in DEVICE memory

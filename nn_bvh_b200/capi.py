@@ -37,13 +37,22 @@ SYMBOLS = [
     "nnbvh_pointer_kind", "nnbvh_copy_to_host", "nnbvh_build_bvh_bounds", "nnbvh_sphere_bounds",
     "nnbvh_upload_scene_mixed", "nnbvh_upload_scene_alpha", "nnbvh_test_spheres", "nnbvh_test_atan2", "nnbvh_instance_bounds",
     "nnbvh_upload_scene_instanced", "nnbvh_intersect_closest_instanced", "nnbvh_intersect_closest_instanced_soa", "nnbvh_clone",
-    "nnbvh_intersect_closest_noalloc",
+    "nnbvh_intersect_closest_noalloc", "nnbvh_upload_scene_general",
 ]
 
 
 class Options(ctypes.Structure):
     _fields_ = [("device", ctypes.c_int32), ("kernel", ctypes.c_int32),
                 ("smem_top_nodes", ctypes.c_int32), ("reserved", ctypes.c_int32 * 5)]
+
+
+class SceneDesc(ctypes.Structure):           # nnbvh_scene_desc
+    _fields_ = [("nodes", ctypes.c_void_p), ("nNodes", ctypes.c_uint32),
+                ("orderedTriVerts9", ctypes.c_void_p), ("nPrims", ctypes.c_uint32),
+                ("orderedSphereIndex", ctypes.c_void_p), ("spheres", ctypes.c_void_p), ("nSpheres", ctypes.c_uint32),
+                ("orderedInstanceIndex", ctypes.c_void_p), ("instances", ctypes.c_void_p),
+                ("nInstances", ctypes.c_uint32), ("objects", ctypes.c_void_p), ("nObjects", ctypes.c_uint32),
+                ("orderedAlpha", ctypes.c_void_p)]
 
 
 class NnbvhError(RuntimeError):
@@ -75,6 +84,7 @@ def lib() -> ctypes.CDLL:
     L.nnbvh_intersect_closest.argtypes = [vp, vp, u64, vp]
     L.nnbvh_intersect_any.argtypes = [vp, vp, u64, vp]
     L.nnbvh_intersect_closest_noalloc.argtypes = [vp, vp, u64, vp]
+    L.nnbvh_upload_scene_general.argtypes = [vp, vp]
     L.nnbvh_intersect_closest_soa.argtypes = [vp] * 8 + [u64, vp]
     L.nnbvh_intersect_any_soa.argtypes = [vp] * 8 + [u64, vp]
     L.nnbvh_intersect_counters.argtypes = [vp, vp, u64, i32, vp, vp, vp, vp]

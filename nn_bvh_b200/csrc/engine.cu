@@ -164,6 +164,7 @@ struct nnbvh_engine {
     bool hasInstances = false;  // instanced scene: BasicKernel with nested traversal runs
     bool hasSpheres = false;  // scene uploaded with spheres: the SPHERES instantiations run
     bool hasAlpha = false;    // scene uploaded with per-primitive alpha: AlphaKernel runs
+    bool general = false;     // nnbvh_upload_scene_general with more than one special kind: BasicKernel<.., 1, 1, 1> runs
     // device-pointer path scratch
     Scratch scratch;
     // host-pointer pipeline
@@ -187,7 +188,7 @@ struct nnbvh_engine {
     int exactOnly = 0;       // skip the fast-slab launch (debug / A-B knob)
     int binMode = 2;         // 0 = off, 1 = always, 2 = per batch, decided on the device (>= binMinRays)
     int binThreshold = 8;    // mode 2: sort when the average warp holds more distinct keys than this
-    int binCellBits = 5;     // origin grid (1<<bits)^3
+    int binCellBits = -1;    // origin grid (1<<bits)^3; -1 = 5 for cache-resident scenes, 7 beyond (r02i: crown +3.5 %, 10 M soup +3.9 %)
     int binDirBits = 3;      // octahedral direction grid (1<<bits)^2
     uint64_t binMinRays = 1u << 21;  // the pre-pass is ~17 launches: not worth it under ~2 Mi rays
     uint32_t binMinNodes = 1u << 18; // nor for scenes the L1s hold anyway (measured: killeroos loses 11-14 %)
@@ -260,7 +261,7 @@ extern "C" int nnbvh_create(const nnbvh_options *opts, nnbvh_engine **out) {
     e->binMode = EnvInt("NNBVH_BIN", e->binMode);
     e->binThreshold = EnvInt("NNBVH_BIN_THRESHOLD", e->binThreshold);
     e->exactOnly = EnvInt("NNBVH_EXACT_ONLY", e->exactOnly);
-    e->binCellBits = std::min(8, std::max(0, EnvInt("NNBVH_BIN_CELL_BITS", e->binCellBits)));
+    e->binCellBits = std::min(8, std::max(-1, EnvInt("NNBVH_BIN_CELL_BITS", e->binCellBits)));
     e->binDirBits = std::min(4, std::max(0, EnvInt("NNBVH_BIN_DIR_BITS", e->binDirBits)));
     e->binMinRays = (uint64_t)EnvInt("NNBVH_BIN_MIN_RAYS", (int)e->binMinRays);
     e->binMinNodes = (uint32_t)EnvInt("NNBVH_BIN_MIN_NODES", (int)e->binMinNodes);
@@ -329,6 +330,7 @@ extern "C" int nnbvh_clone(nnbvh_engine *src, nnbvh_engine **out) {
     e->hasSpheres = src->hasSpheres;
     e->hasInstances = src->hasInstances;
     e->hasAlpha = src->hasAlpha;
+    e->general = src->general;
     *out = e;
     return NNBVH_OK;
 }
@@ -388,16 +390,18 @@ static bool IsDevicePtr(const void *p) {
 }
 
 // in9: nPrims*9 floats (ordered); last: 1 where the primitive ends its leaf.
-// special (optional): >= 0 marks a sphere / instance slot (specialFlag says which), the value is its
-// index in the sphere / instance table.
+// sphereOf / instanceOf (each optional): >= 0 marks a sphere / instance slot, the value is its index in the
+// sphere / instance table.
 __global__ void PackTrisKernel(const float *__restrict__ in9, const uint8_t *__restrict__ last,
-                               const int32_t *__restrict__ special, uint32_t specialFlag, uint32_t nPrims,
-                               float4 *__restrict__ out) {
+                               const int32_t *__restrict__ sphereOf, const int32_t *__restrict__ instanceOf,
+                               uint32_t nPrims, float4 *__restrict__ out) {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= nPrims) return;
-    if (special && special[i] >= 0) {
-        out[3 * (size_t)i + 0] = make_float4(__uint_as_float((uint32_t)special[i]), 0.f, 0.f,
-                                             __uint_as_float(specialFlag | (last[i] ? kTriLast : 0u)));
+    const int32_t sph = sphereOf ? sphereOf[i] : -1, inst = instanceOf ? instanceOf[i] : -1;
+    if (sph >= 0 || inst >= 0) {
+        const uint32_t flag = inst >= 0 ? kPrimInstance : kPrimSphere;
+        out[3 * (size_t)i + 0] = make_float4(__uint_as_float((uint32_t)(inst >= 0 ? inst : sph)), 0.f, 0.f,
+                                             __uint_as_float(flag | (last[i] ? kTriLast : 0u)));
         out[3 * (size_t)i + 1] = make_float4(0.f, 0.f, 0.f, 0.f);
         out[3 * (size_t)i + 2] = make_float4(0.f, 0.f, 0.f, 0.f);
         return;
@@ -564,6 +568,7 @@ static int UploadScene(nnbvh_engine *e, const nnbvh_node *nodes, uint32_t nNodes
     e->hasSpheres = false;
     e->hasInstances = false;
     e->hasAlpha = false;
+    e->general = false;
     if (nNodes == 0) {  // `nodes == nullptr` in the reference: every ray misses
         e->sc = SceneDev{};
         e->haveScene = true;
@@ -615,6 +620,7 @@ static int UploadScene(nnbvh_engine *e, const nnbvh_node *nodes, uint32_t nNodes
     CU(dLast.Alloc(nPrims));
     CU(cudaMemcpyAsync(dLast.p, last.data(), nPrims, cudaMemcpyHostToDevice, st));
     std::vector<SphereDev> sd;  // outlives the asynchronous copy below
+    DevTmp<int32_t> dInstanceOf;
     if (sphereOf) {
         sd.resize(nSpheres);
         for (uint32_t i = 0; i < nSpheres; ++i) {
@@ -632,17 +638,18 @@ static int UploadScene(nnbvh_engine *e, const nnbvh_node *nodes, uint32_t nNodes
         CU(cudaMemcpyAsync(e->store->dSpheres.p, sd.data(), sizeof(SphereDev) * nSpheres, cudaMemcpyHostToDevice, st));
         CU(dSphereOf.Alloc(nPrims));
         CU(cudaMemcpyAsync(dSphereOf.p, sphereOf, sizeof(int32_t) * (size_t)nPrims, cudaMemcpyHostToDevice, st));
-    } else if (instanceOf) {
-        for (uint32_t i = 0; i < nPrims; ++i)
-            if (instanceOf[i] >= (int32_t)nInstances) {
-                cudaStreamSynchronize(st);
-                return SetError(NNBVH_ERR_INVALID, "primitive %u refers to instance %d of %u", i, instanceOf[i], nInstances);
-            }
-        CU(dSphereOf.Alloc(nPrims));
-        CU(cudaMemcpyAsync(dSphereOf.p, instanceOf, sizeof(int32_t) * (size_t)nPrims, cudaMemcpyHostToDevice, st));
     }
-    PackTrisKernel<<<(nPrims + 255) / 256, 256, 0, st>>>(src, dLast.p, dSphereOf.p, instanceOf ? kPrimInstance : kPrimSphere,
-                                                        nPrims, e->store->dTris.p);
+    if (instanceOf) {
+        for (uint32_t i = 0; i < nPrims; ++i)
+            if (instanceOf[i] >= (int32_t)nInstances || (instanceOf[i] >= 0 && sphereOf && sphereOf[i] >= 0)) {
+                cudaStreamSynchronize(st);
+                return SetError(NNBVH_ERR_INVALID, "primitive %u refers to instance %d of %u%s", i, instanceOf[i], nInstances,
+                                instanceOf[i] < (int32_t)nInstances ? " and to a sphere as well" : "");
+            }
+        CU(dInstanceOf.Alloc(nPrims));
+        CU(cudaMemcpyAsync(dInstanceOf.p, instanceOf, sizeof(int32_t) * (size_t)nPrims, cudaMemcpyHostToDevice, st));
+    }
+    PackTrisKernel<<<(nPrims + 255) / 256, 256, 0, st>>>(src, dLast.p, dSphereOf.p, dInstanceOf.p, nPrims, e->store->dTris.p);
     ++e->launches;
     cudaError_t launchErr = cudaGetLastError();
     cudaError_t syncErr = cudaStreamSynchronize(st);  // before the temporaries (and `h`, `wide`, `last`, `sd`) go away
@@ -688,17 +695,11 @@ extern "C" int nnbvh_instance_bounds(const nnbvh_instance *in, const float *obje
     return NNBVH_OK;
 }
 
-extern "C" int nnbvh_upload_scene_instanced(nnbvh_engine *e, const nnbvh_node *nodes, uint32_t nNodes,
-                                            const float *orderedTriVerts9, const int32_t *orderedInstanceIndex,
-                                            uint32_t nPrims, const nnbvh_instance *instances, uint32_t nInstances,
-                                            const nnbvh_object *objects, uint32_t nObjects) {
-    if (!e) return SetError(NNBVH_ERR_INVALID, "nnbvh_upload_scene_instanced: engine is NULL");
-    if (!instances || !objects || !orderedInstanceIndex || nInstances == 0 || nObjects == 0)
-        return SetError(NNBVH_ERR_INVALID, "nnbvh_upload_scene_instanced: NULL / empty instance or object table");
-    CU(cudaSetDevice(e->device));
-    DetachStore(e);
+// The objects of an instanced scene: validate each tree, lay trees and triangles back to back on the device,
+// fill the instance table.  `e`'s device is current.
+static int UploadObjects(nnbvh_engine *e, const nnbvh_instance *instances, uint32_t nInstances,
+                         const nnbvh_object *objects, uint32_t nObjects) {
     cudaStream_t st = e->stream;
-    // the objects: validate each tree, lay trees and triangles back to back
     std::vector<nnbvh_node> allNodes;
     std::vector<float> allTris;
     std::vector<uint8_t> allLast;
@@ -739,24 +740,36 @@ extern "C" int nnbvh_upload_scene_instanced(nnbvh_engine *e, const nnbvh_node *n
     if (!rc) rc = e->store->dObjTris.Reserve(3 * (size_t)nObjPrims);
     if (!rc) rc = e->store->dInstances.Reserve(nInstances);
     if (rc) return rc;
-    {
-        DevTmp<float> dRaw;
-        DevTmp<uint8_t> dLast;
-        cudaError_t ce = dRaw.Alloc(allTris.size());
-        if (ce == cudaSuccess) ce = dLast.Alloc(nObjPrims);
-        if (ce == cudaSuccess) ce = cudaMemcpyAsync(dRaw.p, allTris.data(), sizeof(float) * allTris.size(), cudaMemcpyHostToDevice, st);
-        if (ce == cudaSuccess) ce = cudaMemcpyAsync(dLast.p, allLast.data(), nObjPrims, cudaMemcpyHostToDevice, st);
-        if (ce == cudaSuccess) ce = cudaMemcpyAsync(e->store->dObjNodes.p, allNodes.data(), sizeof(nnbvh_node) * allNodes.size(), cudaMemcpyHostToDevice, st);
-        if (ce == cudaSuccess) ce = cudaMemcpyAsync(e->store->dInstances.p, id.data(), sizeof(InstanceDev) * nInstances, cudaMemcpyHostToDevice, st);
-        if (ce == cudaSuccess) {
-            PackTrisKernel<<<(nObjPrims + 255) / 256, 256, 0, st>>>(dRaw.p, dLast.p, nullptr, 0u, nObjPrims, e->store->dObjTris.p);
-            ++e->launches;
-            ce = cudaGetLastError();
-        }
-        cudaError_t se = cudaStreamSynchronize(st);  // the copies read this frame's vectors; the temporaries go away
-        CU(ce);
-        CU(se);
+    DevTmp<float> dRaw;
+    DevTmp<uint8_t> dLast;
+    cudaError_t ce = dRaw.Alloc(allTris.size());
+    if (ce == cudaSuccess) ce = dLast.Alloc(nObjPrims);
+    if (ce == cudaSuccess) ce = cudaMemcpyAsync(dRaw.p, allTris.data(), sizeof(float) * allTris.size(), cudaMemcpyHostToDevice, st);
+    if (ce == cudaSuccess) ce = cudaMemcpyAsync(dLast.p, allLast.data(), nObjPrims, cudaMemcpyHostToDevice, st);
+    if (ce == cudaSuccess) ce = cudaMemcpyAsync(e->store->dObjNodes.p, allNodes.data(), sizeof(nnbvh_node) * allNodes.size(), cudaMemcpyHostToDevice, st);
+    if (ce == cudaSuccess) ce = cudaMemcpyAsync(e->store->dInstances.p, id.data(), sizeof(InstanceDev) * nInstances, cudaMemcpyHostToDevice, st);
+    if (ce == cudaSuccess) {
+        PackTrisKernel<<<(nObjPrims + 255) / 256, 256, 0, st>>>(dRaw.p, dLast.p, nullptr, nullptr, nObjPrims, e->store->dObjTris.p);
+        ++e->launches;
+        ce = cudaGetLastError();
     }
+    cudaError_t se = cudaStreamSynchronize(st);  // the copies read this frame's vectors; the temporaries go away
+    CU(ce);
+    CU(se);
+    return NNBVH_OK;
+}
+
+extern "C" int nnbvh_upload_scene_instanced(nnbvh_engine *e, const nnbvh_node *nodes, uint32_t nNodes,
+                                            const float *orderedTriVerts9, const int32_t *orderedInstanceIndex,
+                                            uint32_t nPrims, const nnbvh_instance *instances, uint32_t nInstances,
+                                            const nnbvh_object *objects, uint32_t nObjects) {
+    if (!e) return SetError(NNBVH_ERR_INVALID, "nnbvh_upload_scene_instanced: engine is NULL");
+    if (!instances || !objects || !orderedInstanceIndex || nInstances == 0 || nObjects == 0)
+        return SetError(NNBVH_ERR_INVALID, "nnbvh_upload_scene_instanced: NULL / empty instance or object table");
+    CU(cudaSetDevice(e->device));
+    DetachStore(e);
+    int rc = UploadObjects(e, instances, nInstances, objects, nObjects);
+    if (rc) return rc;
     // the top level: triangles and instance slots
     rc = UploadScene(e, nodes, nNodes, orderedTriVerts9, nPrims, nullptr, nullptr, 0, orderedInstanceIndex, nInstances);
     if (rc) return rc;
@@ -764,6 +777,65 @@ extern "C" int nnbvh_upload_scene_instanced(nnbvh_engine *e, const nnbvh_node *n
     e->sc.objNodes = e->store->dObjNodes.p;
     e->sc.objTris = e->store->dObjTris.p;
     e->hasInstances = true;
+    return NNBVH_OK;
+}
+
+// One primitive list holding any mix of triangles (some with a constant alpha), spheres and instances
+// (cpu/primitive.cpp:50-130 behind one BVHAggregate, as scene.cpp:1352-1591 builds it).  A description that
+// uses at most one of the three extras takes that extra's own path (StepKernel for spheres, ...); a real
+// mix runs the general instantiation of BasicKernel (one thread per ray, nested traversal, alpha re-trace).
+extern "C" int nnbvh_upload_scene_general(nnbvh_engine *e, const nnbvh_scene_desc *d) {
+    if (!e || !d) return SetError(NNBVH_ERR_INVALID, "nnbvh_upload_scene_general: NULL argument");
+    const bool sph = d->nSpheres > 0, inst = d->nInstances > 0;
+    bool alpha = false;
+    if (d->orderedAlpha) {
+        if (IsDevicePtr(d->orderedAlpha))
+            return SetError(NNBVH_ERR_INVALID, "nnbvh_upload_scene_general: the alpha array is a host array");
+        for (uint32_t i = 0; i < d->nPrims; ++i) {
+            if (std::isnan(d->orderedAlpha[i]))
+                return SetError(NNBVH_ERR_INVALID, "nnbvh_upload_scene_general: alpha of primitive %u is NaN", i);
+            alpha |= d->orderedAlpha[i] < 1;
+        }
+    }
+    if (sph && (!d->spheres || !d->orderedSphereIndex))
+        return SetError(NNBVH_ERR_INVALID, "nnbvh_upload_scene_general: NULL sphere table / index");
+    if (inst && (!d->instances || !d->objects || !d->orderedInstanceIndex || d->nObjects == 0))
+        return SetError(NNBVH_ERR_INVALID, "nnbvh_upload_scene_general: NULL / empty instance or object table");
+    if ((sph && (IsDevicePtr(d->orderedSphereIndex) || IsDevicePtr(d->spheres))) ||
+        (inst && (IsDevicePtr(d->orderedInstanceIndex) || IsDevicePtr(d->instances))))
+        return SetError(NNBVH_ERR_INVALID, "nnbvh_upload_scene_general: tables and index arrays are host arrays");
+    const int kinds = (int)sph + (int)inst + (int)alpha;
+    if (kinds <= 1) {  // the specialised paths
+        if (sph) return nnbvh_upload_scene_mixed(e, d->nodes, d->nNodes, d->orderedTriVerts9, d->orderedSphereIndex,
+                                                 d->nPrims, d->spheres, d->nSpheres);
+        if (inst) return nnbvh_upload_scene_instanced(e, d->nodes, d->nNodes, d->orderedTriVerts9, d->orderedInstanceIndex,
+                                                      d->nPrims, d->instances, d->nInstances, d->objects, d->nObjects);
+        if (alpha) return nnbvh_upload_scene_alpha(e, d->nodes, d->nNodes, d->orderedTriVerts9, d->orderedAlpha, d->nPrims);
+        return nnbvh_upload_scene(e, d->nodes, d->nNodes, d->orderedTriVerts9, d->nPrims);
+    }
+    CU(cudaSetDevice(e->device));
+    DetachStore(e);
+    int rc = NNBVH_OK;
+    if (inst) rc = UploadObjects(e, d->instances, d->nInstances, d->objects, d->nObjects);
+    if (rc) return rc;
+    rc = UploadScene(e, d->nodes, d->nNodes, d->orderedTriVerts9, d->nPrims, sph ? d->orderedSphereIndex : nullptr,
+                     d->spheres, d->nSpheres, inst ? d->orderedInstanceIndex : nullptr, d->nInstances);
+    if (rc || d->nNodes == 0) return rc;
+    // alpha: always present on this path (1 = none), so the kernel needs no NULL test
+    std::vector<float> a(d->nPrims, 1.f);
+    if (alpha) a.assign(d->orderedAlpha, d->orderedAlpha + d->nPrims);
+    rc = e->store->dAlpha.Reserve(d->nPrims);
+    if (rc) return rc;
+    CU(cudaMemcpyAsync(e->store->dAlpha.p, a.data(), sizeof(float) * (size_t)d->nPrims, cudaMemcpyHostToDevice, e->stream));
+    CU(cudaStreamSynchronize(e->stream));
+    e->sc.alpha = e->store->dAlpha.p;
+    if (inst) {
+        e->sc.instances = e->store->dInstances.p;
+        e->sc.objNodes = e->store->dObjNodes.p;
+        e->sc.objTris = e->store->dObjTris.p;
+    }
+    e->hasSpheres = false;  // the flags of the specialised paths stay off: `general` selects the kernel
+    e->general = true;
     return NNBVH_OK;
 }
 
@@ -828,6 +900,18 @@ static int LaunchTraversal(nnbvh_engine *e, cudaStream_t st, bool any, bool coun
                            const RayInput &in, uint64_t n, const Outputs &o,
                            Scratch &scr) {
     if (n == 0) return NNBVH_OK;
+    if (e->general) {  // triangles + spheres + instances + alpha in one list: BasicKernel's general instantiation
+        if (counters)
+            return SetError(NNBVH_ERR_INVALID, "per-ray counters are not available for general (mixed-kind) scenes");
+        if (n > (uint64_t)0x7fffffff * 128)
+            return SetError(NNBVH_ERR_INVALID, "batch too large for one launch");
+        const unsigned grid = (unsigned)((n + 127) / 128);
+        if (any) BasicKernel<true, false, true, true, true><<<grid, 128, 0, st>>>(e->sc, in, n, o.hits, o.occ, nullptr, nullptr, o.inner);
+        else BasicKernel<false, false, true, true, true><<<grid, 128, 0, st>>>(e->sc, in, n, o.hits, o.occ, nullptr, nullptr, o.inner);
+        ++e->launches;
+        CU(cudaGetLastError());
+        return NNBVH_OK;
+    }
     if (e->hasAlpha) {  // alpha-tested primitives: one thread per ray (alpha.cuh)
         if (counters)
             return SetError(NNBVH_ERR_INVALID, "per-ray counters are not available for scenes with alpha primitives");
@@ -885,7 +969,8 @@ static int LaunchTraversal(nnbvh_engine *e, cudaStream_t st, bool any, bool coun
         if ((e->binMode == 1 || (e->binMode == 2 && stepKernel && e->sc.nNodes >= e->binMinNodes)) &&
             n >= e->binMinRays && n < 0xffffffffull && e->sc.nNodes) {
             BinParams bp;
-            bp.cellBits = (uint32_t)e->binCellBits;
+            const size_t sceneBytes = sizeof(WideNode) * (size_t)e->sc.nWide + 48 * (size_t)e->sc.nPrims;
+            bp.cellBits = (uint32_t)(e->binCellBits >= 0 ? e->binCellBits : (sceneBytes < ((size_t)96 << 20) ? 5 : 7));
             bp.dirBits = (uint32_t)e->binDirBits;
             for (int k = 0; k < 3; ++k) {
                 float ext = e->sc.rootBox[3 + k] - e->sc.rootBox[k];
@@ -1168,7 +1253,7 @@ extern "C" int nnbvh_intersect_closest(nnbvh_engine *e, const nnbvh_ray *rays, u
 
 extern "C" int nnbvh_intersect_closest_instanced(nnbvh_engine *e, const nnbvh_ray *rays, uint64_t n,
                                                  nnbvh_hit *hits, uint32_t *innerPrim) {
-    if (e && !e->hasInstances)
+    if (e && !e->hasInstances && !(e->general && e->sc.instances))
         return SetError(NNBVH_ERR_INVALID, "nnbvh_intersect_closest_instanced: the scene has no instances");
     Batch b;
     b.rays = rays;
@@ -1213,7 +1298,7 @@ extern "C" int nnbvh_intersect_closest_instanced_soa(nnbvh_engine *e, const floa
                                                      const float *oz, const float *dx, const float *dy,
                                                      const float *dz, const float *tMax, uint64_t n,
                                                      nnbvh_hit *hits, uint32_t *innerPrim) {
-    if (e && !e->hasInstances)
+    if (e && !e->hasInstances && !(e->general && e->sc.instances))
         return SetError(NNBVH_ERR_INVALID, "nnbvh_intersect_closest_instanced_soa: the scene has no instances");
     if (innerPrim && IsDevicePtr(innerPrim) != IsDevicePtr(hits))
         return SetError(NNBVH_ERR_INVALID, "nnbvh_intersect_closest_instanced_soa: hits and innerPrim must live on the same side");
@@ -1688,7 +1773,7 @@ extern "C" int nnbvh_intersect_closest_noalloc(nnbvh_engine *e, const nnbvh_ray 
                         "(the static scratch array holds one deferred-list entry per ray); split the batch or "
                         "use nnbvh_intersect_closest", (unsigned long long)n, (unsigned)NNBVH_NOALLOC_MAX_RAYS);
     if (!raysDev || !hitsDev) return SetError(NNBVH_ERR_INVALID, "nnbvh_intersect_closest_noalloc: NULL rays / hits");
-    if (e->hasAlpha || e->hasInstances)
+    if (e->hasAlpha || e->hasInstances || e->general)
         return SetError(NNBVH_ERR_INVALID, "nnbvh_intersect_closest_noalloc: scenes with alpha-tested or instanced "
                                            "primitives run other kernels; use nnbvh_intersect_closest");
     if (e->device < 0 || e->device >= kNoAllocMaxDevices || !g_noAllocPtr[e->device])

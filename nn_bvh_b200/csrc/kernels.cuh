@@ -23,6 +23,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include "alpha_math.cuh"
 #include "exact_math.cuh"
 #include "internal.h"
 #include "sphere.cuh"
@@ -43,6 +44,8 @@ struct SceneDev {
     const InstanceDev *instances;
     const nnbvh_node *objNodes;
     const float4 *objTris;
+    // general scenes (nnbvh_upload_scene_general): constant alpha per ordered top-level primitive, >= 1 = none
+    const float *alpha;
 };
 
 struct RayInput {
@@ -90,7 +93,7 @@ __device__ __noinline__ bool InnerTraverse(const SceneDev &sc, uint32_t instance
                               HitRegs &hit, uint32_t prim, float &tMax, uint32_t &nodesVisited,
                               uint32_t &triTests);
 
-template <bool ANY, bool COUNT, bool SPHERES, bool INST = false>
+template <bool ANY, bool COUNT, bool SPHERES, bool INST = false, bool ALPHA = false>
 __device__ __forceinline__ bool LeafTest(const float4 *__restrict__ tris, uint32_t first,
                                          const RayConst &rc, float &tMax, HitRegs &hit,
                                          uint32_t &triTests, const SphereDev *__restrict__ spheres,
@@ -131,8 +134,17 @@ __device__ __forceinline__ bool LeafTest(const float4 *__restrict__ tris, uint32
         if (COUNT) ++triTests;
         if (!(flags & kTriDegenerate)) {
             float t, b0, b1, b2;
-            if (TriangleTest(rc, tMax, v0.x, v0.y, v0.z, v1.x, v1.y, v1.z, v2.x, v2.y, v2.z, &t,
-                             &b0, &b1, &b2)) {
+            bool got;
+            if (ALPHA) {
+                // GeometricPrimitive::Intersect with a constant alpha texture (cpu/primitive.cpp:50-84; alpha.cuh)
+                const float a = __ldg(sc->alpha + prim);
+                const float p0[3] = {v0.x, v0.y, v0.z}, p1[3] = {v1.x, v1.y, v1.z}, p2[3] = {v2.x, v2.y, v2.z};
+                got = a < 1 ? AlphaTriangleTest(rc, tMax, p0, p1, p2, a, &t, &b0, &b1, &b2)
+                            : TriangleTest(rc, tMax, v0.x, v0.y, v0.z, v1.x, v1.y, v1.z, v2.x, v2.y, v2.z, &t, &b0, &b1, &b2);
+            } else {
+                got = TriangleTest(rc, tMax, v0.x, v0.y, v0.z, v1.x, v1.y, v1.z, v2.x, v2.y, v2.z, &t, &b0, &b1, &b2);
+            }
+            if (got) {
                 if (ANY) return true;
                 hit.prim = prim;
                 hit.inner = NNBVH_MISS;
@@ -152,7 +164,7 @@ __device__ __forceinline__ bool LeafTest(const float4 *__restrict__ tris, uint32
 // BVHAggregate::Intersect / IntersectP (cpu/aggregates.cpp:529-624) over 32-byte reference nodes, in
 // the reference's statement order.  primBase: added to leaf offsets (objects' triangles lie back to
 // back).  Returns true when ANY found a hit.
-template <bool ANY, bool COUNT, bool SPHERES, bool INST>
+template <bool ANY, bool COUNT, bool SPHERES, bool INST, bool ALPHA = false>
 __device__ __forceinline__ bool TraverseRef(const nnbvh_node *__restrict__ nodes, const float4 *__restrict__ tris,
                                             uint32_t primBase, const SceneDev &sc, const RayConst &rc, float &tMax,
                                             HitRegs &hit, uint32_t &nodesVisited, uint32_t &triTests) {
@@ -169,7 +181,7 @@ __device__ __forceinline__ bool TraverseRef(const nnbvh_node *__restrict__ nodes
         uint32_t nPrims = meta & 0xffffu, axis = (meta >> 16) & 0xffu;
         if (SlabTest(rc, box, tMax)) {
             if (nPrims > 0) {
-                if (LeafTest<ANY, COUNT, SPHERES, INST>(tris + 3 * (size_t)primBase, (uint32_t)offset, rc, tMax, hit,
+                if (LeafTest<ANY, COUNT, SPHERES, INST, ALPHA>(tris + 3 * (size_t)primBase, (uint32_t)offset, rc, tMax, hit,
                                                         triTests, sc.spheres, &sc, &nodesVisited))
                     return true;
                 if (sp == 0) break;
@@ -216,7 +228,9 @@ __device__ __noinline__ bool InnerTraverse(const SceneDev &sc, uint32_t instance
 // ---------------------------------------------------------------------------
 // BasicKernel: cpu/aggregates.cpp:529-624 per thread.
 // ---------------------------------------------------------------------------
-template <bool ANY, bool COUNT, bool SPHERES = false, bool INST = false>
+// SPHERES, INST, ALPHA all true = the general instantiation: any mix of triangles (with or without a constant
+// alpha), spheres and instances in ONE primitive list (nnbvh_upload_scene_general).
+template <bool ANY, bool COUNT, bool SPHERES = false, bool INST = false, bool ALPHA = false>
 __global__ void __launch_bounds__(128)
 BasicKernel(SceneDev sc, RayInput in, uint64_t n, nnbvh_hit *__restrict__ hits,
             uint8_t *__restrict__ occluded, uint32_t *__restrict__ nodesVisitedOut,
@@ -230,7 +244,7 @@ BasicKernel(SceneDev sc, RayInput in, uint64_t n, nnbvh_hit *__restrict__ hits,
     bool any = false;
     uint32_t nodesVisited = 0, triTests = 0;
     if (sc.nNodes)
-        any = TraverseRef<ANY, COUNT, SPHERES, INST>(sc.nodes, sc.tris, 0u, sc, rc, tMax, hit, nodesVisited, triTests);
+        any = TraverseRef<ANY, COUNT, SPHERES, INST, ALPHA>(sc.nodes, sc.tris, 0u, sc, rc, tMax, hit, nodesVisited, triTests);
     if (ANY) occluded[i] = any ? 1 : 0;
     else {
         StoreHit(hits, i, hit);

@@ -26,6 +26,22 @@ def shard_range(n: int, rank: int, world: int) -> tuple[int, int]:
     return (rank * n) // world, ((rank + 1) * n) // world
 
 
+def weighted_ranges(n: int, weights) -> list:
+    """Contiguous slices of [0, n) in rank order with sizes proportional to `weights` (one per rank): the
+    slices tile [0, n) exactly (equal weights: sizes differ by at most one, like shard_range).  Used when one rank has other work
+    in the step -- rank 0 of a sharded batch takes every other rank's hit records in over its NVLink
+    ports while it traces -- and should trace a smaller share."""
+    w = [float(x) for x in weights]
+    if not w or min(w) < 0 or sum(w) <= 0:
+        raise ValueError("weights must be non-negative and not all zero")
+    tot, acc, cuts = sum(w), 0.0, [0]
+    for x in w:
+        acc += x
+        cuts.append(int(round(n * acc / tot)))
+    cuts[-1] = n
+    return [(cuts[i], max(cuts[i], cuts[i + 1])) for i in range(len(w))]
+
+
 def max_shard(n: int, world: int) -> int:
     return max(shard_range(n, r, world)[1] - shard_range(n, r, world)[0] for r in range(world))
 
@@ -118,7 +134,8 @@ class PeerWindow:
     rows: (n_total,) + tail of `dtype`; equal or ragged shards (shard_range).  `tensor` is the
     array on `dst` (None elsewhere).  GPU only; the gloo tests cover gather_records instead."""
 
-    def __init__(self, n_total: int, tail: tuple, dtype: torch.dtype, dst: int = 0, group=None):
+    def __init__(self, n_total: int, tail: tuple, dtype: torch.dtype, dst: int = 0, group=None,
+                 copy_streams: int = 1, ranges=None):
         import ctypes
         from . import capi
         self._capi, self._ct = capi, ctypes
@@ -126,6 +143,8 @@ class PeerWindow:
         self.world, self.rank, self.dst = dist.get_world_size(group), dist.get_rank(group), dst
         self._group = group
         self.n_total, self.tail, self.dtype = n_total, tuple(tail), dtype
+        # ranges: [(a, b)] per rank (weighted_ranges); default = equal contiguous slices (shard_range)
+        self.ranges = list(ranges) if ranges is not None else [shard_range(n_total, r, self.world) for r in range(self.world)]
         self.row_bytes = torch.empty((), dtype=dtype).element_size()
         for t in self.tail:
             self.row_bytes *= t
@@ -157,16 +176,20 @@ class PeerWindow:
                      "data": (self.base, False), "version": 3, "strides": None}
             holder = type("PeerWindowMemory", (), {"__cuda_array_interface__": iface})()
             self.tensor = torch.as_tensor(holder, device=torch.device("cuda", torch.cuda.current_device()))
-        self.stream = torch.cuda.Stream()
+        # copy_streams > 1: a delivery is split into that many pieces on as many streams, i.e. copy engines
+        # (one engine does not fill an NVLink 5 port: 2.7 GB took 8.6 ms = 312 GB/s, r02k)
+        self.streams = [torch.cuda.Stream() for _ in range(max(1, copy_streams))]
+        self.stream = self.streams[0]
         self._ready = torch.cuda.Event()
-        self._done = torch.cuda.Event()
+        self._dones = [torch.cuda.Event() for _ in self.streams]
+        self._done = self._dones[0]
 
     def deliver(self, local: torch.Tensor, producer: "torch.cuda.Stream", at: int = None):
         """Enqueue the copy of this rank's slice, ordered after everything `producer` holds now.
         Returns at once; wait_on(stream) makes a stream wait for the delivery.
         at: deliver `local` as rows [at, at + len(local)) of this rank's shard (a batch traced in chunks
         delivers each chunk while the next one is traced); None = the whole shard."""
-        a, b = shard_range(self.n_total, self.rank, self.world)
+        a, b = self.ranges[self.rank]
         if at is None:
             if local.shape[0] != b - a:
                 raise ValueError(f"rank {self.rank}: local result has {local.shape[0]} rows, shard has {b - a}")
@@ -174,19 +197,27 @@ class PeerWindow:
         elif at < 0 or at + local.shape[0] > b - a:
             raise ValueError(f"rank {self.rank}: rows [{at}, {at + local.shape[0]}) outside a shard of {b - a}")
         src = local.contiguous()           # a temporary only for a non-contiguous input
-        src.record_stream(self.stream)     # the caching allocator must not reuse the block before the copy has read it
         self._ready.record(producer)
-        self.stream.wait_event(self._ready)
-        self._capi.check(self._capi.lib().nnbvh_peer_copy(
-            self._ct.c_void_p(self.base + (a + at) * self.row_bytes), self._capi.ptr(src),
-            local.shape[0] * self.row_bytes, self._ct.c_void_p(self.stream.cuda_stream)))
-        self._done.record(self.stream)
+        rows = local.shape[0]
+        k = len(self.streams) if rows >= (1 << 16) else 1
+        for i in range(k):
+            r0, r1 = rows * i // k, rows * (i + 1) // k
+            st = self.streams[i]
+            src.record_stream(st)          # the caching allocator must not reuse the block before the copy has read it
+            st.wait_event(self._ready)
+            if r1 > r0:
+                self._capi.check(self._capi.lib().nnbvh_peer_copy(
+                    self._ct.c_void_p(self.base + (a + at + r0) * self.row_bytes),
+                    self._ct.c_void_p(src.data_ptr() + r0 * self.row_bytes),
+                    (r1 - r0) * self.row_bytes, self._ct.c_void_p(st.cuda_stream)))
+            self._dones[i].record(st)
 
     def wait_on(self, stream: "torch.cuda.Stream"):
         """Make `stream` wait for THIS rank's last delivery.  It orders nothing across ranks: before
         rank `dst` reads `tensor` every rank must have waited for its own delivery and the ranks must
         have met (dist.barrier(), or any collective ordered after the wait) -- bench.py's barrier()."""
-        stream.wait_event(self._done)
+        for ev in self._dones:
+            stream.wait_event(ev)
 
     def close(self, collective: bool = True):
         """Collective (default): every rank of the group calls it.  The mappings are closed before the owner

@@ -384,6 +384,61 @@ class Reference:
                               obj_tris=np.ascontiguousarray(np.concatenate(obj_tris)),
                               obj_prim_base=np.array(pbase[:-1], dtype=np.int32)))
 
+    def scene_general(self, tris9, alpha, spheres28, obj_soups, inst24, inst_object, max_prims: int = 4,
+                      split: str = "sah"):
+        """BVHAggregate over ONE list: triangles (GeometricPrimitive with constant alpha where alpha < 1), then
+        spheres, then TransformedPrimitive instances of per-object aggregates.  Returns the handle and the
+        reference's trees / orders in the layout nnbvh_upload_scene_general takes."""
+        tris9 = np.ascontiguousarray(tris9, dtype=np.float32).reshape(-1, 9)
+        T = tris9.shape[0]
+        alpha = np.ascontiguousarray(alpha, dtype=np.float32).reshape(-1)
+        spheres28 = np.ascontiguousarray(spheres28, dtype=np.float32).reshape(-1, 28)
+        S = len(spheres28)
+        obj_soups = [np.ascontiguousarray(o, dtype=np.float32).reshape(-1, 9) for o in obj_soups]
+        obj_all = np.ascontiguousarray(np.concatenate(obj_soups))
+        start = np.concatenate([[0], np.cumsum([len(o) for o in obj_soups])]).astype(np.int32)
+        inst24 = np.ascontiguousarray(inst24, dtype=np.float32).reshape(-1, 24)
+        inst_object = np.ascontiguousarray(inst_object, dtype=np.int32)
+        K = len(inst24)
+        L = self.lib
+        f = L.nnbvh_ref_scene_create_general
+        f.restype = ctypes.c_void_p
+        f.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p,
+                      ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_int,
+                      ctypes.c_int]
+        h = ctypes.c_void_p(f(_p(tris9), T, _p(alpha), _p(spheres28), S, _p(obj_all), _p(start), len(obj_soups),
+                              _p(inst24), _p(inst_object), K, max_prims, SPLIT[split]))
+        nodes, order = self.export(h, T + S + K)
+        L.nnbvh_ref_scene_object_num_nodes.argtypes = [ctypes.c_void_p, ctypes.c_int]
+        L.nnbvh_ref_scene_export_object.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p]
+        objects = []
+        for j, soup in enumerate(obj_soups):
+            m = L.nnbvh_ref_scene_object_num_nodes(h, j)
+            nd = np.zeros((m, 8), dtype=np.uint32)
+            od = np.zeros(len(soup), dtype=np.int32)
+            L.nnbvh_ref_scene_export_object(h, j, _p(nd), _p(od))
+            objects.append(dict(nodes=nd, order=od, ordered_tris9=np.ascontiguousarray(soup[od])))
+        ordered = np.zeros((T + S + K, 9), dtype=np.float32)
+        is_tri = order < T
+        ordered[is_tri] = tris9[order[is_tri]]
+        ordered_alpha = np.ones(T + S + K, dtype=np.float32)
+        ordered_alpha[is_tri] = alpha[order[is_tri]]
+        return dict(handle=h, nodes=nodes, order=order, ordered_tris9=ordered, ordered_alpha=ordered_alpha,
+                    sphere_of=np.where((order >= T) & (order < T + S), order - T, -1).astype(np.int32),
+                    instance_of=np.where(order >= T + S, order - T - S, -1).astype(np.int32), objects=objects)
+
+    def intersect_general(self, handle, rays8):
+        """BVHAggregate::Intersect over a scene_general handle -> (hits (n,5) uint32, inner (n,) uint32)."""
+        rays8 = np.ascontiguousarray(rays8, dtype=np.float32).reshape(-1, 8)
+        n = rays8.shape[0]
+        hits = np.zeros((n, 5), dtype=np.uint32)
+        inner = np.zeros(n, dtype=np.uint32)
+        f = self.lib.nnbvh_ref_intersect_general
+        f.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int64, ctypes.c_void_p, ctypes.c_void_p]
+        f.restype = None
+        f(handle, _p(rays8), n, _p(hits), _p(inner))
+        return hits, inner
+
     def intersect_instanced(self, handle, rays8):
         rays8 = np.ascontiguousarray(rays8, dtype=np.float32).reshape(-1, 8)
         n = rays8.shape[0]

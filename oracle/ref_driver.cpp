@@ -598,6 +598,158 @@ void nnbvh_ref_intersect_instanced(void *scene, const float *rays, int64_t n, ui
     }
 }
 
+// ---- general scenes: every primitive kind of the path in ONE list ------------------------------------------
+// Primitive list: triangles 0..nTris-1 (GeometricPrimitive with FloatConstantTexture(alpha[i]) where alpha[i] < 1,
+// else SimplePrimitive), spheres nTris..nTris+nSpheres-1 (SimplePrimitive, tagged), instances after them
+// (TransformedPrimitive over per-object BVHAggregates whose triangles carry the object's tag).
+constexpr int kObjectTagBase = 1 << 24;
+void *nnbvh_ref_scene_create_general(const float *tris9, int nTris, const float *alpha, const float *spheres28,
+                                     int nSpheres, const float *objTris9, const int *objStart, int nObjects,
+                                     const float *inst24, const int *instObject, int nInstances,
+                                     int maxPrimsInNode, int splitMethod) {
+    if (!g_inited)
+        nnbvh_ref_init(0);
+    auto *s = new RefScene;
+    pbrt::Allocator alloc;
+    auto makeMesh = [&](const float *t9, int n) {
+        std::vector<int> idx(3 * (size_t)n), face(n);
+        std::vector<pbrt::Point3f> p(3 * (size_t)n);
+        for (int i = 0; i < 3 * n; ++i) {
+            idx[i] = i;
+            p[i] = pbrt::Point3f(t9[3 * i], t9[3 * i + 1], t9[3 * i + 2]);
+        }
+        for (int i = 0; i < n; ++i)
+            face[i] = i;
+        return alloc.new_object<pbrt::TriangleMesh>(pbrt::Transform(), false, idx, p, std::vector<pbrt::Vector3f>(),
+                                                    std::vector<pbrt::Normal3f>(), std::vector<pbrt::Point2f>(), face,
+                                                    alloc);
+    };
+    for (int j = 0; j < nObjects; ++j) {
+        auto *o = new RefObject;
+        o->nTris = objStart[j + 1] - objStart[j];
+        o->mesh = makeMesh(objTris9 + 9 * (size_t)objStart[j], o->nTris);
+        std::vector<pbrt::Primitive> prims;
+        for (pbrt::Shape sh : pbrt::Triangle::CreateTriangles(o->mesh, alloc))
+            prims.push_back(pbrt::Primitive(alloc.new_object<pbrt::SimplePrimitive>(sh, TagMaterial(kObjectTagBase + j))));
+        o->agg = new pbrt::BVHAggregate(std::move(prims), maxPrimsInNode, (pbrt::BVHAggregate::SplitMethod)splitMethod);
+        o->nNodes = CountNodes(reinterpret_cast<const NodeMirror *>(o->agg->nodes));
+        o->orderedToOrig.resize(o->nTris);
+        o->origToOrdered.resize(o->nTris);
+        for (int i = 0; i < o->nTris; ++i) {
+            int orig = o->agg->primitives[i].Cast<pbrt::SimplePrimitive>()->shape.Cast<pbrt::Triangle>()->triIndex;
+            o->orderedToOrig[i] = orig;
+            o->origToOrdered[orig] = i;
+        }
+        s->objects.push_back(o);
+    }
+    s->mesh = makeMesh(tris9, nTris);
+    pstd::vector<pbrt::Shape> shapes = pbrt::Triangle::CreateTriangles(s->mesh, alloc);
+    std::vector<pbrt::Primitive> prims;
+    for (int i = 0; i < nTris; ++i) {
+        if (alpha && alpha[i] < 1) {
+            pbrt::FloatTexture tex(alloc.new_object<pbrt::FloatConstantTexture>(alpha[i]));
+            prims.push_back(pbrt::Primitive(alloc.new_object<pbrt::GeometricPrimitive>(
+                shapes[i], pbrt::Material(nullptr), pbrt::Light(nullptr), pbrt::MediumInterface(), tex)));
+        } else
+            prims.push_back(pbrt::Primitive(alloc.new_object<pbrt::SimplePrimitive>(shapes[i], pbrt::Material(nullptr))));
+    }
+    for (int k = 0; k < nSpheres; ++k) {
+        s->spheres.push_back(MakeSphere(spheres28 + 28 * (size_t)k));
+        prims.push_back(pbrt::Primitive(alloc.new_object<pbrt::SimplePrimitive>(pbrt::Shape(s->spheres.back()->shape),
+                                                                                TagMaterial(nTris + k))));
+    }
+    std::map<const void *, int> instIndex;
+    for (int k = 0; k < nInstances; ++k) {
+        auto *in = new RefInstance;
+        in->renderFromPrimitive = pbrt::Transform(Matrix12(inst24 + 24 * (size_t)k), Matrix12(inst24 + 24 * (size_t)k + 12));
+        in->object = instObject[k];
+        in->prim = new pbrt::TransformedPrimitive(pbrt::Primitive(s->objects[in->object]->agg), &in->renderFromPrimitive);
+        instIndex[in->prim] = k;
+        prims.push_back(pbrt::Primitive(in->prim));
+        s->instances.push_back(in);
+    }
+    s->nTris = nTris;
+    const int nPrims = nTris + nSpheres + nInstances;
+    s->primList = prims;
+    s->agg = new pbrt::BVHAggregate(std::move(prims), maxPrimsInNode, (pbrt::BVHAggregate::SplitMethod)splitMethod);
+    s->nNodes = CountNodes(reinterpret_cast<const NodeMirror *>(s->agg->nodes));
+    s->orderedToOrig.resize(nPrims);
+    s->origToOrdered.resize(nPrims);
+    for (int i = 0; i < nPrims; ++i) {
+        pbrt::Primitive p = s->agg->primitives[i];
+        int orig;
+        if (p.Is<pbrt::TransformedPrimitive>())
+            orig = nTris + nSpheres + instIndex[p.Cast<pbrt::TransformedPrimitive>()];
+        else if (p.Is<pbrt::GeometricPrimitive>())
+            orig = p.Cast<pbrt::GeometricPrimitive>()->shape.Cast<pbrt::Triangle>()->triIndex;
+        else {
+            const pbrt::SimplePrimitive *sp = p.Cast<pbrt::SimplePrimitive>();
+            orig = sp->shape.Is<pbrt::Triangle>() ? sp->shape.Cast<pbrt::Triangle>()->triIndex : TagOf(sp->material);
+        }
+        s->orderedToOrig[i] = orig;
+        s->origToOrdered[orig] = i;
+    }
+    return s;
+}
+
+// BVHAggregate::Intersect over a general scene: hits5 / inner as nnbvh_ref_intersect_instanced, sphere hits as
+// nnbvh_ref_intersect ({prim, tHit, pObj}).
+void nnbvh_ref_intersect_general(void *scene, const float *rays, int64_t n, uint32_t *hits, uint32_t *inner) {
+    RefScene *s = (RefScene *)scene;
+    pbrt::Primitive top(s->agg);
+    const int nSph = (int)s->spheres.size();
+    for (int64_t i = 0; i < n; ++i) {
+        const float *r = rays + 8 * i;
+        pbrt::Ray ray = MakeRay(r);
+        pstd::optional<pbrt::ShapeIntersection> si = top.Intersect(ray, r[3]);
+        uint32_t *h = hits + 5 * i;
+        inner[i] = 0xFFFFFFFFu;
+        h[0] = 0xFFFFFFFFu;
+        h[1] = h[2] = h[3] = h[4] = 0;
+        if (!si)
+            continue;
+        float t = si->tHit, b[3] = {0, 0, 0};
+        int tag = TagOf(si->intr.material), face = si->intr.faceIndex;
+        if (tag < 0) {  // a top-level triangle
+            h[0] = (uint32_t)s->origToOrdered[face];
+            const int *v = &s->mesh->vertexIndices[3 * face];
+            const pbrt::Point3f p0 = s->mesh->p[v[0]], p1 = s->mesh->p[v[1]], p2 = s->mesh->p[v[2]];
+            // barycentrics as nnbvh_ref_intersect recovers them (b and t do not depend on tMax, shapes.cpp:245-247);
+            // an alpha-rejected hit is re-traced against the same flat triangle, i.e. in practice skipped
+            if (auto ti = pbrt::IntersectTriangle(ray, pbrt::Infinity, p0, p1, p2))
+                b[0] = ti->b0, b[1] = ti->b1, b[2] = ti->b2;
+        } else if (tag < kObjectTagBase) {  // a sphere
+            h[0] = (uint32_t)s->origToOrdered[tag];
+            pstd::optional<pbrt::QuadricIntersection> qi = s->spheres[tag - s->nTris]->shape->BasicIntersect(ray, pbrt::Infinity);
+            if (qi)
+                b[0] = qi->pObj.x, b[1] = qi->pObj.y, b[2] = qi->pObj.z;
+        } else {  // a triangle of an object: find the instance
+            const int obj = tag - kObjectTagBase;
+            int found = -1;
+            for (size_t k = 0; k < s->instances.size() && found < 0; ++k) {
+                if (s->instances[k]->object != obj)
+                    continue;
+                auto sk = s->instances[k]->prim->Intersect(ray, pbrt::Infinity);
+                if (sk && sk->tHit == t && sk->intr.faceIndex == face)
+                    found = (int)k;
+            }
+            if (found < 0) {
+                h[0] = 0xFFFFFFFEu;  // cannot happen; makes a test fail loudly
+                continue;
+            }
+            RefObject *o = s->objects[obj];
+            h[0] = (uint32_t)s->origToOrdered[s->nTris + nSph + found];
+            inner[i] = (uint32_t)o->origToOrdered[face];
+            pbrt::Ray local = s->instances[found]->renderFromPrimitive.ApplyInverse(ray, nullptr);
+            const int *v = &o->mesh->vertexIndices[3 * face];
+            if (auto ti = pbrt::IntersectTriangle(local, pbrt::Infinity, o->mesh->p[v[0]], o->mesh->p[v[1]], o->mesh->p[v[2]]))
+                b[0] = ti->b0, b[1] = ti->b1, b[2] = ti->b2;
+        }
+        std::memcpy(&h[1], &t, 4);
+        std::memcpy(&h[2], b, 12);
+    }
+}
+
 // TransformedPrimitive::Bounds() of instance k (cpu/primitive.h:94).
 void nnbvh_ref_instance_bounds(void *scene, int k, float *out6) {
     pbrt::Bounds3f b = ((RefScene *)scene)->instances[k]->prim->Bounds();

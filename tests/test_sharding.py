@@ -85,3 +85,17 @@ def test_sharded_trace_matches_single_process(tmp_path, world, n):
     port = _free_port()
     mp.spawn(_worker, args=(world, port, n, str(tmp_path)), nprocs=world, join=True)
     assert os.path.exists(tmp_path / f"ok_{world}_{n}")
+
+
+def test_weighted_ranges_tile_the_batch():
+    from nn_bvh_b200 import sharding
+    for n, w in ((100, [0.5, 1, 1, 1]), (10, [1, 1, 1]), (7, [0, 1]), (268435456, [0.7] + [1.0] * 7), (3, [1] * 8)):
+        r = sharding.weighted_ranges(n, w)
+        assert len(r) == len(w) and r[0][0] == 0 and r[-1][1] == n
+        assert all(a <= b for a, b in r) and all(r[i][1] == r[i + 1][0] for i in range(len(r) - 1))
+    eq = sharding.weighted_ranges(1000, [1] * 7)
+    assert max(b - a for a, b in eq) - min(b - a for a, b in eq) <= 1
+    small = sharding.weighted_ranges(1 << 20, [0.5, 1, 1, 1])
+    assert abs((small[0][1] - small[0][0]) * 2 - (small[1][1] - small[1][0])) <= 2
+    with pytest.raises(ValueError):
+        sharding.weighted_ranges(10, [0, 0])
