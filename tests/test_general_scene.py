@@ -123,3 +123,28 @@ def test_general_description_with_one_kind_takes_that_kinds_path(reference):
     c = nb.GPUBVHAggregate.General(tris)
     d = nb.GPUBVHAggregate(tris, 4, "sah")
     assert np.array_equal(np.ascontiguousarray(c.IntersectBatch(rays)).view(np.uint32), np.ascontiguousarray(d.IntersectBatch(rays)).view(np.uint32))
+
+
+@pytest.mark.gpu
+def test_general_scene_matches_the_reference_golden():
+    """The same claim without oracle/_ref: answers the reference produced here (tools/make_golden.py --only-general)."""
+    import os
+    import nn_bvh_b200 as nb
+    from conftest import GOLDEN
+    from nn_bvh_b200.aggregate import INSTANCE_DTYPE, SPHERE_DTYPE
+    g = np.load(os.path.join(GOLDEN, "general.npz"))
+    spheres = np.ascontiguousarray(g["spheres28"]).view(SPHERE_DTYPE).reshape(-1)
+    instances = np.zeros(len(g["inst24"]), dtype=INSTANCE_DTYPE)
+    instances["renderFromPrimitive"], instances["primitiveFromRender"] = g["inst24"][:, :12], g["inst24"][:, 12:]
+    instances["object"] = g["inst_object"]
+    objects, nb_, tb_ = [], 0, 0
+    for nn, nt in zip(g["obj_node_count"], g["obj_tri_count"]):
+        objects.append(dict(nodes=g["obj_nodes"][nb_:nb_ + nn], ordered_tris9=g["obj_tris"][tb_:tb_ + nt]))
+        nb_, tb_ = nb_ + nn, tb_ + nt
+    tree = dict(nodes=g["nodes"], order=g["order"], ordered_tris9=g["ordered_tris9"], ordered_alpha=g["ordered_alpha"],
+                sphere_of=g["sphere_of"], instance_of=g["instance_of"], objects=objects)
+    agg = nb.GPUBVHAggregate.General(spheres=spheres, instances=instances, tree=tree)
+    hits, inner = agg.IntersectBatchInstanced(g["rays"])
+    assert np.array_equal(np.ascontiguousarray(hits).view(np.uint32).reshape(-1, 5), g["hits"])
+    assert np.array_equal(inner, g["inner"])
+    assert np.array_equal(agg.IntersectPBatch(g["rays"]), g["occ"])

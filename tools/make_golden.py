@@ -523,9 +523,36 @@ def alpha(ref, rng):
                         tris=tris, alpha=a, nodes=nodes, order=order, rays=rays, hits=hits, occ=occ)
 
 
+def general(ref, rng):
+    """tests/golden/general.npz: ONE list with triangles, constant-alpha triangles, spheres and instances -- the
+    reference's tree over it and BVHAggregate::Intersect / IntersectP answers (tests/test_general_scene.py)."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from test_general_scene import _rays, _scene
+    tris, alpha, sph, soups, inst24, inst_obj = _scene(rng, 1500, 16, 2, 10)
+    g = ref.scene_general(tris, alpha, sph, soups, inst24, inst_obj, 4, "sah")
+    rays = _rays(rng, 8192, sph, inst24)
+    hits, inner = ref.intersect_general(g["handle"], rays)
+    occ = ref.intersect_p(g["handle"], rays, parallel=False)
+    T, S = len(tris), len(sph)
+    k = g["order"][hits[hits[:, 0] != 0xFFFFFFFF, 0]]
+    print("general: hits on triangles", int((k < T).sum()), "spheres", int(((k >= T) & (k < T + S)).sum()),
+          "instances", int((k >= T + S).sum()), "occluded", int(occ.sum()))
+    np.savez_compressed(os.path.join(OUT, "general.npz"), nodes=g["nodes"], order=g["order"],
+                        ordered_tris9=g["ordered_tris9"], ordered_alpha=g["ordered_alpha"], sphere_of=g["sphere_of"],
+                        instance_of=g["instance_of"], spheres28=sph, inst24=inst24, inst_object=inst_obj,
+                        obj_nodes=np.concatenate([o["nodes"] for o in g["objects"]]),
+                        obj_node_count=np.array([len(o["nodes"]) for o in g["objects"]], dtype=np.int32),
+                        obj_tris=np.concatenate([o["ordered_tris9"] for o in g["objects"]]),
+                        obj_tri_count=np.array([len(o["ordered_tris9"]) for o in g["objects"]], dtype=np.int32),
+                        rays=rays, hits=hits, inner=inner, occ=occ)
+
+
 if __name__ == "__main__":
     os.makedirs(OUT, exist_ok=True)
     ref = Reference(threads=1)
+    if "--only-general" in sys.argv:
+        general(ref, np.random.default_rng(211))
+        sys.exit(0)
     if "--only-instances" in sys.argv:
         instanced(ref, np.random.default_rng(112))
         sys.exit(0)
