@@ -180,6 +180,7 @@ struct nnbvh_engine {
     int leafQuorum = -1;
     int stepStats = 0;       // NNBVH_STEP_STATS=1: run the counting instantiation of StepKernel
     unsigned long long *dStats = nullptr;
+    int gridRaysPerLane = 0; // StepKernel: shrink the persistent grid for small batches (StepGrid); 0 = never
     int popLoop = 1;         // StepKernel: discard culled stack entries inside the pop
     int sphereQuorum = 12;   // StepKernel with sphere leaves: lanes waiting at spheres before their tests run
     uint64_t chunkRays = 1u << 19;
@@ -253,6 +254,7 @@ extern "C" int nnbvh_create(const nnbvh_options *opts, nnbvh_engine **out) {
     e->refillBelow = EnvInt("NNBVH_REFILL_BELOW", e->refillBelow);
     e->leafQuorum = EnvInt("NNBVH_LEAF_QUORUM", e->leafQuorum);
     e->popLoop = EnvInt("NNBVH_POP_LOOP", e->popLoop);
+    e->gridRaysPerLane = EnvInt("NNBVH_GRID_RAYS_PER_LANE", e->gridRaysPerLane);
     e->sphereQuorum = EnvInt("NNBVH_SPHERE_QUORUM", e->sphereQuorum);
     e->stepStats = EnvInt("NNBVH_STEP_STATS", 0);
     e->chunkRays = (uint64_t)EnvInt("NNBVH_CHUNK_RAYS", (int)e->chunkRays);
@@ -874,23 +876,36 @@ static int LaunchWide(nnbvh_engine *e, cudaStream_t st, const WideParams &p, uin
     }
 }
 
+// Grid of the persistent StepKernel: numSMs x MINB CTAs, fewer for small batches so that every lane still gets
+// `raysPerLane` rays to refill from (a warp that holds one ray per lane for its whole life has nothing to
+// replace finished rays with: NNBVH_GRID_RAYS_PER_LANE, 0 = always the full grid).
+static unsigned StepGrid(const nnbvh_engine *e, int minB, uint64_t n) {
+    const unsigned full = (unsigned)(e->numSMs * minB);
+    if (e->gridRaysPerLane <= 0) return full;
+    const uint64_t want = (n + 256ull * (uint64_t)e->gridRaysPerLane - 1) / (256ull * (uint64_t)e->gridRaysPerLane);
+    return (unsigned)std::min<uint64_t>(full, std::max<uint64_t>(want, (uint64_t)e->numSMs));
+}
+
 template <bool ANY, bool EXACT>
 static void LaunchStep(nnbvh_engine *e, cudaStream_t st, const StepParams &p) {
+    const uint64_t n = p.nPtr ? 0 : p.n;  // the exact launch over the deferred list does not know its size on the host
     if (e->hasSpheres) {  // sphere leaves: one instantiation, 4 CTAs/SM (the sphere test wants registers)
-        StepKernel<ANY, EXACT, 4, false, true><<<e->numSMs * 4, 256, 0, st>>>(p);
+        StepKernel<ANY, EXACT, 4, false, true><<<p.nPtr ? e->numSMs * 4 : StepGrid(e, 4, n), 256, 0, st>>>(p);
         return;
     }
     if (p.stats && !EXACT) {  // NNBVH_STEP_STATS=1: lane-occupancy counters (diagnostic build of the kernel)
         StepKernel<ANY, false, 5, true><<<e->numSMs * 5, 256, 0, st>>>(p);
         return;
     }
-    switch (e->wideMinB) {
-    case 1: StepKernel<ANY, EXACT, 1><<<e->numSMs * 1, 256, 0, st>>>(p); break;
-    case 2: StepKernel<ANY, EXACT, 2><<<e->numSMs * 2, 256, 0, st>>>(p); break;
-    case 3: StepKernel<ANY, EXACT, 3><<<e->numSMs * 3, 256, 0, st>>>(p); break;
-    case 4: StepKernel<ANY, EXACT, 4><<<e->numSMs * 4, 256, 0, st>>>(p); break;
-    case 6: StepKernel<ANY, EXACT, 6><<<e->numSMs * 6, 256, 0, st>>>(p); break;
-    default: StepKernel<ANY, EXACT, 5><<<e->numSMs * 5, 256, 0, st>>>(p); break;
+    const int minB = (e->wideMinB >= 1 && e->wideMinB <= 6) ? e->wideMinB : 5;
+    const unsigned grid = p.nPtr ? (unsigned)(e->numSMs * minB) : StepGrid(e, minB, n);
+    switch (minB) {
+    case 1: StepKernel<ANY, EXACT, 1><<<grid, 256, 0, st>>>(p); break;
+    case 2: StepKernel<ANY, EXACT, 2><<<grid, 256, 0, st>>>(p); break;
+    case 3: StepKernel<ANY, EXACT, 3><<<grid, 256, 0, st>>>(p); break;
+    case 4: StepKernel<ANY, EXACT, 4><<<grid, 256, 0, st>>>(p); break;
+    case 6: StepKernel<ANY, EXACT, 6><<<grid, 256, 0, st>>>(p); break;
+    default: StepKernel<ANY, EXACT, 5><<<grid, 256, 0, st>>>(p); break;
     }
 }
 

@@ -208,7 +208,33 @@ __device__ __forceinline__ bool TriangleTest(const RayConst &r, float tMax, floa
     float invDet = Div(1.f, det);
     float b0 = Mul(e0, invDet), b1 = Mul(e1, invDet), b2 = Mul(e2, invDet);
     float t = Mul(tScaled, invDet);
-    // :250-269 conservative t > deltaT
+    // :250-269 conservative t > deltaT.  Only the OUTCOME of `t <= deltaT` is observable, and for almost every
+    // accepted hit t exceeds deltaT by orders of magnitude, so a cheap upper bound U >= deltaT decides first:
+    //   deltaX, deltaY <= 2 g5 M,  deltaE <= 2 M^2 (g2 + 4 g5),  deltaZ <= g3 M      (M = largest |coordinate|)
+    //   deltaT <= 3 |invDet| M (2 g3 maxE + 2 (g2 + 4 g5) M^2)
+    // evaluated in float with a 1 % margin that covers the ~30 roundings of both expressions; t > U implies
+    // t > deltaT.  Anything else -- t close to the bound, NaN, magnitudes near overflow (W >= 1e37) or so small
+    // that products inside either expression are denormal or underflow (W <= 1e-30: a denormal's rounding error
+    // is not relative, and |invDet| can blow it up) -- takes the reference's expression verbatim.  The final
+    // `* |invDet|` is monotone in both expressions, so it needs no guard of its own.
+    {
+        const float M = fmaxf(fmaxf(fmaxf(fmaxf(fabsf(p0tx), fabsf(p1tx)), fabsf(p2tx)),
+                                    fmaxf(fmaxf(fabsf(p0ty), fabsf(p1ty)), fabsf(p2ty))),
+                              fmaxf(fmaxf(fabsf(p0tz), fabsf(p1tz)), fabsf(p2tz)));
+        const float mE = fmaxf(fmaxf(fabsf(e0), fabsf(e1)), fabsf(e2));
+        constexpr float c1 = 1.01f * 6.f * GammaF(3), c2 = 1.01f * 6.f * (GammaF(2) + 4.f * GammaF(5));
+        // W bounds every intermediate of the reference's expression before its final `* |invDet|`: while W is far
+        // from overflow none of them is inf (deltaT = inf rejects whatever t is, and must keep doing so)
+        const float W = Mul(M, Add(Mul(c1, mE), Mul(c2, Mul(M, M))));
+        const float U = Mul(fabsf(invDet), W);
+        if (t > U && W > 1e-30f && W < 1e37f) {
+            *tOut = t;
+            *b0Out = b0;
+            *b1Out = b1;
+            *b2Out = b2;
+            return true;
+        }
+    }
     float maxZt = Max3First(fabsf(p0tz), fabsf(p1tz), fabsf(p2tz));
     float deltaZ = Mul(GammaF(3), maxZt);
     float maxXt = Max3First(fabsf(p0tx), fabsf(p1tx), fabsf(p2tx));

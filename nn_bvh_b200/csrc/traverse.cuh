@@ -33,6 +33,9 @@
 #include "internal.h"
 #include "kernels.cuh"
 
+#ifndef NNBVH_PREFETCH_AHEAD
+#define NNBVH_PREFETCH_AHEAD 0  // refill: L2-prefetch the rays this many permutation entries ahead of the cursor (0 = off)
+#endif
 #ifndef NNBVH_SPC
 #define NNBVH_SPC 4  // node steps per look at the leaf quorum (unrolled)
 #endif
@@ -142,6 +145,16 @@ __global__ void __launch_bounds__(256, MINB) StepKernel(StepParams p) {
             base = __shfl_sync(0xffffffffu, base, 0);
             if (base + nWant >= nRays) exhausted = true;
             if (STATS) st[7] += 1;
+            if (NNBVH_PREFETCH_AHEAD > 0 && perm && p.in.aos) {
+                // Through the sorted permutation a refill reads rays from random places of the caller's array:
+                // DRAM latency with the whole warp waiting.  Every refill touches the rays a later refill (of any
+                // warp) will take, NNBVH_PREFETCH_AHEAD entries ahead of the cursor, so that they wait in the L2.
+                const uint64_t ja = base + NNBVH_PREFETCH_AHEAD + lane;
+                if (ja < nRays) {
+                    const uint32_t ia = __ldg(perm + ja);
+                    asm volatile("prefetch.global.L2 [%0];" ::"l"(p.in.aos + 2 * (size_t)ia));
+                }
+            }
             if (!alive) {
                 uint64_t j = base + __popc(want & ((1u << lane) - 1));
                 if (j < nRays) {

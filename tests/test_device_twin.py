@@ -235,3 +235,39 @@ def test_device_kernel_counters_on_reference_golden(twin, golden):
             f(_p(nodes), len(nodes), _p(ot), len(ot), _p(rays), n, any_hit, _p(nv), _p(tt))
             tot += [int(nv.sum()), int(tt.sum())]
         assert tuple(tot) == tuple(int(v) for v in g[f"{split}_stats"])
+
+
+def test_device_triangle_delta_t_shortcut_never_changes_the_outcome(twin, oracle):
+    """exact_math.cuh decides `t <= deltaT` (shapes.cpp:250-269) with a cheap upper bound first and falls back to
+    the reference's expression.  Rays that start within a few error bounds of the triangle -- t of the order of
+    deltaT, across 40 orders of magnitude of scene scale -- must give the verbatim answer (hit flag and t, b bits)."""
+    rng = np.random.default_rng(977)
+    n = 30000
+    rays = np.zeros((n, 8), dtype=np.float32)
+    tris = np.zeros((n, 9), dtype=np.float32)
+    accepted = rejected = 0
+    for i in range(n):
+        scale = 10.0 ** rng.uniform(-21, 18)      # down to where the products go denormal, up to overflow
+        tri = (rng.normal(size=(3, 3)) * scale).astype(np.float32)
+        if i % 5 == 0:
+            tri += np.float32(scale * 10.0 ** rng.uniform(0, 6))        # far from the origin: large |coordinates|, small edges
+        b = rng.dirichlet([1, 1, 1])
+        p = (b[:, None] * tri.astype(np.float64)).sum(0)
+        d = rng.normal(size=3)
+        d /= np.linalg.norm(d)
+        d *= 10.0 ** rng.uniform(-3, 3)                                 # unnormalised directions too
+        eps = np.abs(p).max() * 10.0 ** rng.uniform(-9, -3) if i % 3 else np.abs(p).max() * 10.0 ** rng.uniform(-7.5, -5.5)
+        o = p - d / np.linalg.norm(d) * eps
+        rays[i, :3], rays[i, 4:7], rays[i, 3] = o, d, np.inf
+        tris[i] = tri.ravel()
+    for i in range(n):
+        got = np.zeros(4, dtype=np.float32)
+        h = twin.dt_triangle(_p(rays[i]), _p(tris[i]), _p(got))
+        wh, want = oracle.triangle(rays[i], tris[i])
+        assert bool(h) == bool(wh), (i, rays[i], tris[i])
+        if wh:
+            accepted += 1
+            assert np.array_equal(got.view(np.uint32), np.asarray(want, dtype=np.float32).view(np.uint32)), i
+        else:
+            rejected += 1
+    assert accepted > 5000 and rejected > 5000
