@@ -183,6 +183,7 @@ struct nnbvh_engine {
     int gridRaysPerLane = 0; // StepKernel: shrink the persistent grid for small batches (StepGrid); 0 = never
     int popLoop = 1;         // StepKernel: discard culled stack entries inside the pop
     int sphereQuorum = 12;   // StepKernel with sphere leaves: lanes waiting at spheres before their tests run
+    int chunkRamp = 1;       // host-pointer pipeline: small chunks at both ends of a call (RunBatch)
     uint64_t chunkRays = 1u << 19;
     uint64_t chunkRaysSoa = 1u << 20;  // SoA planes are 4 bytes per ray each: larger chunks per copy
     // ray binning pre-pass (binning.cuh)
@@ -257,6 +258,7 @@ extern "C" int nnbvh_create(const nnbvh_options *opts, nnbvh_engine **out) {
     e->gridRaysPerLane = EnvInt("NNBVH_GRID_RAYS_PER_LANE", e->gridRaysPerLane);
     e->sphereQuorum = EnvInt("NNBVH_SPHERE_QUORUM", e->sphereQuorum);
     e->stepStats = EnvInt("NNBVH_STEP_STATS", 0);
+    e->chunkRamp = EnvInt("NNBVH_CHUNK_RAMP", e->chunkRamp);
     e->chunkRays = (uint64_t)EnvInt("NNBVH_CHUNK_RAYS", (int)e->chunkRays);
     e->chunkRaysSoa = (uint64_t)EnvInt("NNBVH_CHUNK_RAYS_SOA", (int)e->chunkRaysSoa);
     e->nSlots = std::min((int)nnbvh_engine::kMaxSlots, std::max(1, EnvInt("NNBVH_SLOTS", e->nSlots)));
@@ -1236,10 +1238,24 @@ static int RunBatch(nnbvh_engine *e, const Batch &b) {
         CU(cudaEventRecord(s.done, s.stream));
         return NNBVH_OK;
     };
+    // Chunk schedule.  The first chunk's upload and the last chunk's kernel + download are the part of a call
+    // that nothing overlaps, so the schedule ramps up (chunk/4, chunk/2, chunk, ...) and down again at the end
+    // (NNBVH_CHUNK_RAMP=0: equal chunks).
     int rcOut = NNBVH_OK;
     int idx = 0;
-    for (uint64_t off = 0; off < b.n && rcOut == NNBVH_OK; off += chunk, ++idx)
-        rcOut = issue(e->slots[idx % e->nSlots], off, std::min(chunk, b.n - off));
+    const uint64_t small = std::max<uint64_t>(chunk / 4, 1024);
+    for (uint64_t off = 0; off < b.n && rcOut == NNBVH_OK; ++idx) {
+        uint64_t m = chunk;
+        if (e->chunkRamp) {
+            if (idx == 0) m = small;
+            else if (idx == 1) m = std::max<uint64_t>(chunk / 2, 1024);
+            const uint64_t left = b.n - off;
+            if (left < 2 * chunk) m = std::min(m, std::max(small, (left + 1) / 2));  // ... halving towards the end
+        }
+        m = std::min(m, b.n - off);
+        rcOut = issue(e->slots[idx % e->nSlots], off, m);
+        off += m;
+    }
     // Also on an error: nothing may still be copying into the caller's buffers when this returns.
     for (Slot &s : e->slots) {
         cudaError_t ce = cudaStreamSynchronize(s.stream);

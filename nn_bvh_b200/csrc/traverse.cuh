@@ -36,6 +36,9 @@
 #ifndef NNBVH_PREFETCH_AHEAD
 #define NNBVH_PREFETCH_AHEAD 0  // refill: L2-prefetch the rays this many permutation entries ahead of the cursor (0 = off)
 #endif
+#ifndef NNBVH_PREFETCH_TRI
+#define NNBVH_PREFETCH_TRI 0  // 1: L1-prefetch the first triangle when a lane steps onto a leaf; 2: both of its lines
+#endif
 #ifndef NNBVH_SPC
 #define NNBVH_SPC 4  // node steps per look at the leaf quorum (unrolled)
 #endif
@@ -332,6 +335,17 @@ __global__ void __launch_bounds__(256, MINB) StepKernel(StepParams p) {
                         else StoreHit(p.hits, rayIdx, hit);
                     }
                 }
+#if NNBVH_PREFETCH_TRI
+                // the lane has just stepped onto a leaf: it will wait there for the quorum, and its first triangle
+                // can travel to the L1 meanwhile
+                if (alive && cur < 0) {
+                    const float4 *tp = tris + 3 * (size_t)((uint32_t)cur & 0x7fffffffu);
+                    asm volatile("prefetch.global.L1 [%0];" ::"l"(tp));
+#if NNBVH_PREFETCH_TRI > 1
+                    asm volatile("prefetch.global.L1 [%0];" ::"l"(tp + 2));
+#endif
+                }
+#endif
             }
             }
         }
