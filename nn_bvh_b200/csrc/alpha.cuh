@@ -31,8 +31,9 @@ template <bool ANY>
 __global__ void __launch_bounds__(128)
 AlphaKernel(SceneDev sc, const float *__restrict__ alpha, RayInput in, uint64_t n, nnbvh_hit *__restrict__ hits,
             uint8_t *__restrict__ occluded) {
-    const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
+    const uint64_t j = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= n) return;
+    const uint64_t i = OrderedRay(in, j);
     const RayRegs rr = LoadRay(in, i);
     const RayConst rc = MakeRayConst(rr.ox, rr.oy, rr.oz, rr.dx, rr.dy, rr.dz);
     float tMax = rr.tMax;

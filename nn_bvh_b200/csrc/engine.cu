@@ -912,19 +912,103 @@ static void LaunchStep(nnbvh_engine *e, cudaStream_t st, const StepParams &p) {
 }
 
 
+// The ray-ordering pre-pass (binning.cuh): a permutation of the batch that keeps warps coherent, or nothing
+// when the batch is too small / the mode says so.  cursor: the batch's zeroed scratch words (3, 4: sample
+// statistics, 5: the device-side "sorted" flag).  *perm stays NULL when no sort was enqueued; *permOn is the
+// device flag the kernels read (mode 2 decides per batch on the device).
+static int OrderRays(nnbvh_engine *e, cudaStream_t st, const RayInput &in, uint64_t n, Scratch &scr,
+                     unsigned long long *cursor, bool deviceDecides, uint32_t minNodes, const uint32_t **permOut,
+                     const uint32_t **permOnOut) {
+    const uint32_t *perm = nullptr, *permOn = nullptr;
+    *permOut = *permOnOut = nullptr;
+    if (!((e->binMode == 1 || (e->binMode == 2 && deviceDecides && e->sc.nNodes >= minNodes)) &&
+          n >= e->binMinRays && n < 0xffffffffull && e->sc.nNodes))
+        return NNBVH_OK;
+    {
+    BinParams bp;
+    const size_t sceneBytes = sizeof(WideNode) * (size_t)e->sc.nWide + 48 * (size_t)e->sc.nPrims;
+    bp.cellBits = (uint32_t)(e->binCellBits >= 0 ? e->binCellBits : (sceneBytes < ((size_t)96 << 20) ? 5 : 7));
+    bp.dirBits = (uint32_t)e->binDirBits;
+    for (int k = 0; k < 3; ++k) {
+        float ext = e->sc.rootBox[3 + k] - e->sc.rootBox[k];
+        bp.lo[k] = e->sc.rootBox[k];
+        bp.scale[k] = ext > 0.f ? (float)(1u << bp.cellBits) / ext : 0.f;
+    }
+    const int keyBits = (int)(3 * bp.cellBits + 2 * bp.dirBits);
+    const uint32_t nSortBlk = (uint32_t)((n + kSortTile - 1) / kSortTile);
+    constexpr int kBinRadixBits = 7;  // 21-bit default key = 3 passes; runs of 16 pairs per digit
+    const uint32_t nHist = (1u << kBinRadixBits) * nSortBlk, nTiles = (nHist + kScanTile - 1) / kScanTile;
+    int rc = scr.keys.Reserve(n);
+    if (!rc) rc = scr.keys2.Reserve(n);
+    if (!rc) rc = scr.perm.Reserve(n);
+    if (!rc) rc = scr.perm2.Reserve(n);
+    if (!rc) rc = scr.hist.Reserve(nHist);
+    if (!rc) rc = scr.tileSums.Reserve(nTiles);
+    if (rc) return rc;
+    uint32_t *flag = reinterpret_cast<uint32_t *>(cursor + 5);
+    if (!scr.hFlag) {
+        CU(cudaHostAlloc(&scr.hFlag, sizeof(uint32_t), cudaHostAllocDefault));
+        *scr.hFlag = 1u;
+    }
+    const uint32_t lastFlag = *const_cast<volatile uint32_t *>(scr.hFlag);
+    scr.coherentRun = lastFlag ? 0 : std::min(scr.coherentRun + 1, 1 << 20);
+    const bool enqueueSort = e->binMode == 1 || scr.coherentRun < 2;
+    BinSampleKernel<<<kBinSamples, 32, 0, st>>>(bp, in, n, cursor + 3);
+    BinDecideKernel<<<1, 1, 0, st>>>(cursor + 3, (uint32_t)e->binThreshold,
+                                     e->binMode == 1 ? 1u : 0u, flag);
+    CU(cudaMemcpyAsync(scr.hFlag, flag, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+    e->launches += 2;
+    uint32_t *kIn = scr.keys.p, *kOut = scr.keys2.p, *vIn = nullptr, *vOut = scr.perm.p;
+    if (enqueueSort) {
+        BinKeyKernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(bp, in, n, scr.keys.p, flag);
+        ++e->launches;
+    }
+    for (int shift = 0; enqueueSort && shift < keyBits; shift += kBinRadixBits) {
+        RadixCountKernel<kBinRadixBits><<<nSortBlk, 256, 0, st>>>(kIn, (uint32_t)n, shift, scr.hist.p, flag);
+        BinTileSumKernel<<<nTiles, 1024, 0, st>>>(scr.hist.p, nHist, scr.tileSums.p, flag);
+        BinTileScanKernel<<<nTiles, 1024, 0, st>>>(scr.hist.p, nHist, scr.tileSums.p, flag);
+        const bool lastPass = shift + kBinRadixBits >= keyBits;  // only the permutation is read afterwards
+        RadixScatterKernel<kBinRadixBits><<<nSortBlk, 256, 0, st>>>(kIn, vIn, (uint32_t)n, shift, scr.hist.p,
+                                                                   lastPass ? nullptr : kOut, vOut, flag);
+        e->launches += 4;
+        std::swap(kIn, kOut);
+        uint32_t *done = vOut;
+        vOut = (done == scr.perm.p) ? scr.perm2.p : scr.perm.p;
+        vIn = done;
+    }
+    CU(cudaGetLastError());
+    if (enqueueSort) {
+        perm = vIn;
+        permOn = flag;
+    }
+    }
+    *permOut = perm;
+    *permOnOut = permOn;
+    return NNBVH_OK;
+}
+
 // All pointers are device pointers here.
 static int LaunchTraversal(nnbvh_engine *e, cudaStream_t st, bool any, bool counters,
                            const RayInput &in, uint64_t n, const Outputs &o,
                            Scratch &scr) {
     if (n == 0) return NNBVH_OK;
+    // One thread per ray (general / alpha / instanced scenes): the same ray order helps there too -- the lanes of a
+    // warp then walk neighbouring rays -- so those kernels pull their ray through the permutation as well.
+    RayInput inO = in;
+    if ((e->general || e->hasAlpha || e->hasInstances) && !counters && e->kernel != NNBVH_KERNEL_BASIC) {
+        CU(cudaMemsetAsync(scr.cursor, 0, kCursorWords * sizeof(unsigned long long), st));
+        // (no node-count floor here: an instanced scene's top level is small, its objects are not)
+        int rc = OrderRays(e, st, in, n, scr, scr.cursor, true, 0u, &inO.perm, &inO.permOn);
+        if (rc) return rc;
+    }
     if (e->general) {  // triangles + spheres + instances + alpha in one list: BasicKernel's general instantiation
         if (counters)
             return SetError(NNBVH_ERR_INVALID, "per-ray counters are not available for general (mixed-kind) scenes");
         if (n > (uint64_t)0x7fffffff * 128)
             return SetError(NNBVH_ERR_INVALID, "batch too large for one launch");
         const unsigned grid = (unsigned)((n + 127) / 128);
-        if (any) BasicKernel<true, false, true, true, true><<<grid, 128, 0, st>>>(e->sc, in, n, o.hits, o.occ, nullptr, nullptr, o.inner);
-        else BasicKernel<false, false, true, true, true><<<grid, 128, 0, st>>>(e->sc, in, n, o.hits, o.occ, nullptr, nullptr, o.inner);
+        if (any) BasicKernel<true, false, true, true, true><<<grid, 128, 0, st>>>(e->sc, inO, n, o.hits, o.occ, nullptr, nullptr, o.inner);
+        else BasicKernel<false, false, true, true, true><<<grid, 128, 0, st>>>(e->sc, inO, n, o.hits, o.occ, nullptr, nullptr, o.inner);
         ++e->launches;
         CU(cudaGetLastError());
         return NNBVH_OK;
@@ -935,8 +1019,8 @@ static int LaunchTraversal(nnbvh_engine *e, cudaStream_t st, bool any, bool coun
         if (n > (uint64_t)0x7fffffff * 128)
             return SetError(NNBVH_ERR_INVALID, "batch too large for one launch");
         const unsigned grid = (unsigned)((n + 127) / 128);
-        if (any) AlphaKernel<true><<<grid, 128, 0, st>>>(e->sc, e->store->dAlpha.p, in, n, o.hits, o.occ);
-        else AlphaKernel<false><<<grid, 128, 0, st>>>(e->sc, e->store->dAlpha.p, in, n, o.hits, o.occ);
+        if (any) AlphaKernel<true><<<grid, 128, 0, st>>>(e->sc, e->store->dAlpha.p, inO, n, o.hits, o.occ);
+        else AlphaKernel<false><<<grid, 128, 0, st>>>(e->sc, e->store->dAlpha.p, inO, n, o.hits, o.occ);
         ++e->launches;
         CU(cudaGetLastError());
         return NNBVH_OK;
@@ -953,8 +1037,8 @@ static int LaunchTraversal(nnbvh_engine *e, cudaStream_t st, bool any, bool coun
                 if (any) BasicKernel<true, true, false, true><<<grid, 128, 0, st>>>(e->sc, in, n, o.hits, o.occ, nv, tt, o.inner);
                 else BasicKernel<false, true, false, true><<<grid, 128, 0, st>>>(e->sc, in, n, o.hits, o.occ, nv, tt, o.inner);
             } else {
-                if (any) BasicKernel<true, false, false, true><<<grid, 128, 0, st>>>(e->sc, in, n, o.hits, o.occ, nv, tt, o.inner);
-                else BasicKernel<false, false, false, true><<<grid, 128, 0, st>>>(e->sc, in, n, o.hits, o.occ, nv, tt, o.inner);
+                if (any) BasicKernel<true, false, false, true><<<grid, 128, 0, st>>>(e->sc, inO, n, o.hits, o.occ, nv, tt, o.inner);
+                else BasicKernel<false, false, false, true><<<grid, 128, 0, st>>>(e->sc, inO, n, o.hits, o.occ, nv, tt, o.inner);
             }
         } else if (e->hasSpheres) {
             if (counters) {
@@ -979,68 +1063,12 @@ static int LaunchTraversal(nnbvh_engine *e, cudaStream_t st, bool any, bool coun
         unsigned long long *cursor = scr.cursor;
         CU(cudaMemsetAsync(cursor, 0, kCursorWords * sizeof(unsigned long long), st));
         // ---- binning pre-pass: a ray order that keeps warps coherent (binning.cuh) ----
-        // binMode 1: always sort; 2: the device decides per batch (StepKernel only, which reads
-        // the flag); 0: off.
+        // binMode 1: always sort; 2: the device decides per batch (the kernels read the flag); 0: off.
         const uint32_t *perm = nullptr, *permOn = nullptr;
         const bool stepKernel = e->kernel != NNBVH_KERNEL_WIDE || e->hasSpheres;  // WideKernel has no sphere leaves
-        if ((e->binMode == 1 || (e->binMode == 2 && stepKernel && e->sc.nNodes >= e->binMinNodes)) &&
-            n >= e->binMinRays && n < 0xffffffffull && e->sc.nNodes) {
-            BinParams bp;
-            const size_t sceneBytes = sizeof(WideNode) * (size_t)e->sc.nWide + 48 * (size_t)e->sc.nPrims;
-            bp.cellBits = (uint32_t)(e->binCellBits >= 0 ? e->binCellBits : (sceneBytes < ((size_t)96 << 20) ? 5 : 7));
-            bp.dirBits = (uint32_t)e->binDirBits;
-            for (int k = 0; k < 3; ++k) {
-                float ext = e->sc.rootBox[3 + k] - e->sc.rootBox[k];
-                bp.lo[k] = e->sc.rootBox[k];
-                bp.scale[k] = ext > 0.f ? (float)(1u << bp.cellBits) / ext : 0.f;
-            }
-            const int keyBits = (int)(3 * bp.cellBits + 2 * bp.dirBits);
-            const uint32_t nSortBlk = (uint32_t)((n + kSortTile - 1) / kSortTile);
-            constexpr int kBinRadixBits = 7;  // 21-bit default key = 3 passes; runs of 16 pairs per digit
-            const uint32_t nHist = (1u << kBinRadixBits) * nSortBlk, nTiles = (nHist + kScanTile - 1) / kScanTile;
-            int rc = scr.keys.Reserve(n);
-            if (!rc) rc = scr.keys2.Reserve(n);
-            if (!rc) rc = scr.perm.Reserve(n);
-            if (!rc) rc = scr.perm2.Reserve(n);
-            if (!rc) rc = scr.hist.Reserve(nHist);
-            if (!rc) rc = scr.tileSums.Reserve(nTiles);
+        {
+            int rc = OrderRays(e, st, in, n, scr, cursor, stepKernel, e->binMinNodes, &perm, &permOn);
             if (rc) return rc;
-            uint32_t *flag = reinterpret_cast<uint32_t *>(cursor + 5);
-            if (!scr.hFlag) {
-                CU(cudaHostAlloc(&scr.hFlag, sizeof(uint32_t), cudaHostAllocDefault));
-                *scr.hFlag = 1u;
-            }
-            const uint32_t lastFlag = *const_cast<volatile uint32_t *>(scr.hFlag);
-            scr.coherentRun = lastFlag ? 0 : std::min(scr.coherentRun + 1, 1 << 20);
-            const bool enqueueSort = e->binMode == 1 || scr.coherentRun < 2;
-            BinSampleKernel<<<kBinSamples, 32, 0, st>>>(bp, in, n, cursor + 3);
-            BinDecideKernel<<<1, 1, 0, st>>>(cursor + 3, (uint32_t)e->binThreshold,
-                                             e->binMode == 1 ? 1u : 0u, flag);
-            CU(cudaMemcpyAsync(scr.hFlag, flag, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
-            e->launches += 2;
-            uint32_t *kIn = scr.keys.p, *kOut = scr.keys2.p, *vIn = nullptr, *vOut = scr.perm.p;
-            if (enqueueSort) {
-                BinKeyKernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(bp, in, n, scr.keys.p, flag);
-                ++e->launches;
-            }
-            for (int shift = 0; enqueueSort && shift < keyBits; shift += kBinRadixBits) {
-                RadixCountKernel<kBinRadixBits><<<nSortBlk, 256, 0, st>>>(kIn, (uint32_t)n, shift, scr.hist.p, flag);
-                BinTileSumKernel<<<nTiles, 1024, 0, st>>>(scr.hist.p, nHist, scr.tileSums.p, flag);
-                BinTileScanKernel<<<nTiles, 1024, 0, st>>>(scr.hist.p, nHist, scr.tileSums.p, flag);
-                const bool lastPass = shift + kBinRadixBits >= keyBits;  // only the permutation is read afterwards
-                RadixScatterKernel<kBinRadixBits><<<nSortBlk, 256, 0, st>>>(kIn, vIn, (uint32_t)n, shift, scr.hist.p,
-                                                                           lastPass ? nullptr : kOut, vOut, flag);
-                e->launches += 4;
-                std::swap(kIn, kOut);
-                uint32_t *done = vOut;
-                vOut = (done == scr.perm.p) ? scr.perm2.p : scr.perm.p;
-                vIn = done;
-            }
-            CU(cudaGetLastError());
-            if (enqueueSort) {
-                perm = vIn;
-                permOn = flag;
-            }
         }
         if (stepKernel) {
             // ---- StepKernel: fast-slab launch, then the exact launch over the deferred rays ----

@@ -51,7 +51,14 @@ struct SceneDev {
 struct RayInput {
     const float4 *aos;  // 2 float4 per ray, or NULL for SoA
     const float *ox, *oy, *oz, *dx, *dy, *dz, *tMax;
+    // one-thread-per-ray kernels: optional ray order (binning.cuh); thread j takes ray perm[j] when the
+    // device flag *permOn (or a NULL permOn) says the batch was sorted.  Results go to the ray's own slot.
+    const uint32_t *perm, *permOn;
 };
+
+__device__ __forceinline__ uint64_t OrderedRay(const RayInput &in, uint64_t j) {
+    return (in.perm && (!in.permOn || __ldg(in.permOn))) ? (uint64_t)__ldg(in.perm + j) : j;
+}
 
 struct RayRegs {
     float ox, oy, oz, tMax, dx, dy, dz;
@@ -235,8 +242,9 @@ __global__ void __launch_bounds__(128)
 BasicKernel(SceneDev sc, RayInput in, uint64_t n, nnbvh_hit *__restrict__ hits,
             uint8_t *__restrict__ occluded, uint32_t *__restrict__ nodesVisitedOut,
             uint32_t *__restrict__ triTestsOut, uint32_t *__restrict__ innerOut = nullptr) {
-    uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
+    const uint64_t j = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= n) return;
+    const uint64_t i = OrderedRay(in, j);
     RayRegs rr = LoadRay(in, i);
     RayConst rc = MakeRayConst(rr.ox, rr.oy, rr.oz, rr.dx, rr.dy, rr.dz);
     float tMax = rr.tMax;

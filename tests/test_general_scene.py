@@ -148,3 +148,48 @@ def test_general_scene_matches_the_reference_golden():
     assert np.array_equal(np.ascontiguousarray(hits).view(np.uint32).reshape(-1, 5), g["hits"])
     assert np.array_equal(inner, g["inner"])
     assert np.array_equal(agg.IntersectPBatch(g["rays"]), g["occ"])
+
+
+@pytest.mark.gpu
+def test_ray_ordering_does_not_change_one_thread_per_ray_results(reference, monkeypatch):
+    """Batches of >= 2 Mi rays go through the ray-ordering pre-pass on the general / alpha / instanced paths too
+    (thread j traces ray perm[j], the record goes to the ray's own slot): forced on and off, same records; and a
+    strided subset equals the reference."""
+    import nn_bvh_b200 as nb
+    from nn_bvh_b200.aggregate import INSTANCE_DTYPE, SPHERE_DTYPE
+    rng = np.random.default_rng(107)
+    tris, alpha, sph, soups, inst24, inst_obj = _scene(rng, 4000, 30, 3, 20)
+    ref = reference.scene_general(tris, alpha, sph, soups, inst24, inst_obj, 4, "sah")
+    spheres = np.ascontiguousarray(sph).view(SPHERE_DTYPE).reshape(-1)
+    instances = np.zeros(len(inst24), dtype=INSTANCE_DTYPE)
+    instances["renderFromPrimitive"], instances["primitiveFromRender"] = inst24[:, :12], inst24[:, 12:]
+    instances["object"] = inst_obj
+    import torch
+    N = (2 << 20) + 12345
+    rays = _rays(rng, N, sph, inst24)
+    d_rays = torch.from_numpy(rays).cuda()      # resident rays: one launch over the whole batch (host arrays are chunked)
+    d_hits = torch.zeros((N, 5), dtype=torch.int32, device="cuda")
+    d_inner = torch.zeros(N, dtype=torch.int32, device="cuda")
+    d_occ = torch.zeros(N, dtype=torch.uint8, device="cuda")
+    out = {}
+    for mode in ("0", "1"):
+        monkeypatch.setenv("NNBVH_BIN", mode)
+        agg = nb.GPUBVHAggregate.General(spheres=spheres, instances=instances, tree=ref)
+        agg.IntersectBatchInstanced(d_rays, hits=d_hits, inner=d_inner, n=N)
+        agg.IntersectPBatch(d_rays, occluded=d_occ, n=N)
+        torch.cuda.synchronize()
+        out[mode] = (d_hits.cpu().numpy().view(np.uint32).copy(), d_inner.cpu().numpy().view(np.uint32).copy(),
+                     d_occ.cpu().numpy().copy(), agg.launch_count())
+        agg.close()
+        al = nb.GPUBVHAggregate(tris, 4, "sah", alpha=alpha)          # the alpha-only path
+        al.IntersectBatch(d_rays, hits=d_hits, n=N)
+        torch.cuda.synchronize()
+        out["a" + mode] = d_hits.cpu().numpy().view(np.uint32).copy()
+        al.close()
+    assert out["1"][3] > out["0"][3] + 10                               # the sort really ran
+    for k in range(3):
+        assert np.array_equal(out["0"][k], out["1"][k])
+    assert np.array_equal(out["a0"], out["a1"])
+    sub = np.ascontiguousarray(rays[::97])
+    want, want_inner = reference.intersect_general(ref["handle"], sub)
+    assert np.array_equal(out["1"][0][::97], want) and np.array_equal(out["1"][1][::97], want_inner)
