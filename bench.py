@@ -63,7 +63,7 @@ def parse():
     ap.add_argument("--c5-tris", type=int, default=10_000_000)
     ap.add_argument("--c5-rays", type=int, default=256 << 20, help="config 5: rays of the ONE batch all ranks share")
     ap.add_argument("--c5-steps", type=int, default=5, help="config 5: at most this many timed steps")
-    ap.add_argument("--c5-chunks", default="0.5,0.5",
+    ap.add_argument("--c5-chunks", default="0.4,0.4,0.2",
                     help="config 5, N>1: fractions of a rank's shard traced and delivered one after another "
                          "(a chunk's delivery overlaps the next chunk's traversal)")
     ap.add_argument("--c5-rank0-share", type=float, default=1.0,

@@ -39,6 +39,9 @@
 #ifndef NNBVH_PREFETCH_TRI
 #define NNBVH_PREFETCH_TRI 0  // 1: L1-prefetch the first triangle when a lane steps onto a leaf; 2: both of its lines
 #endif
+#ifndef NNBVH_ANY_ORDER
+#define NNBVH_ANY_ORDER 1
+#endif
 #ifndef NNBVH_SPC
 #define NNBVH_SPC 4  // node steps per look at the leaf quorum (unrolled)
 #endif
@@ -245,7 +248,14 @@ __global__ void __launch_bounds__(256, MINB) StepKernel(StepParams p) {
                     // WideNode: lo0 xyz, hi0 xyz, lo1 xy | lo1 z, hi1 xyz, ref0, ref1, axis, pad
                     const int ref0 = __float_as_int(b.v[4]), ref1 = __float_as_int(b.v[5]);
                     const unsigned axis = __float_as_uint(b.v[6]);
-                    const bool secondFirst = (ry.neg >> axis) & 1u;  // aggregates.cpp:561
+                    // aggregates.cpp:561.  IntersectP's answer does not depend on the visit order (no tMax update,
+                    // any accepted primitive ends the ray): NNBVH_ANY_ORDER 0 = child 0 first, 2 = the child whose
+                    // box is entered first (smaller tEntry), 1 = the reference's order (default).
+#if NNBVH_ANY_ORDER == 0
+                    const bool secondFirst = ANY ? false : (bool)((ry.neg >> axis) & 1u);
+#else
+                    const bool secondFirst = (ry.neg >> axis) & 1u;
+#endif
                     const int refNear = secondFirst ? ref1 : ref0, refFar = secondFirst ? ref0 : ref1;
                     float tNear, tFar;
                     bool stNear, stFar;
