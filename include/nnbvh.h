@@ -224,8 +224,11 @@ int nnbvh_upload_scene_alpha(nnbvh_engine *e, const nnbvh_node *nodes, uint32_t 
  * traversed there.  A hit on an instance is {prim = the instance's top-level slot, t and b0,b1,b2 of
  * the inner triangle in the instance ray's parametrisation} -- what TransformedPrimitive::Intersect
  * returns -- plus, from nnbvh_intersect_closest_instanced, the ordered primitive inside the object.
- * Such scenes run the one-thread-per-ray kernel (nested traversal).  Spheres and alpha-tested triangles
- * beside instances: nnbvh_upload_scene_general. */
+ * Such scenes run the product kernel (StepKernel with instance slots: the objects' nodes and triangles are
+ * appended to the top level's device arrays and the second level is entered as a pushed sub-state);
+ * per-ray counters, NNBVH_INST_STEP=0 and scenes whose combined stack depth exceeds 64 entries run the
+ * one-thread-per-ray kernel.  Spheres and alpha-tested triangles beside instances:
+ * nnbvh_upload_scene_general. */
 typedef struct nnbvh_object {
     const nnbvh_node *nodes;
     uint32_t nNodes;

@@ -137,9 +137,10 @@ struct SceneStore {
     DevBuf<nnbvh_node> dObjNodes;
     DevBuf<float4> dObjTris;
     DevBuf<float> dAlpha;  // one value per ordered primitive (nnbvh_upload_scene_alpha)
+    DevBuf<InstanceStep> dInstStep;  // instanced scenes on the StepKernel
     ~SceneStore() {
         dNodes.Free(); dWide.Free(); dTris.Free(); dSpheres.Free();
-        dInstances.Free(); dObjNodes.Free(); dObjTris.Free(); dAlpha.Free();
+        dInstances.Free(); dObjNodes.Free(); dObjTris.Free(); dAlpha.Free(); dInstStep.Free();
     }
 };
 
@@ -165,6 +166,7 @@ struct nnbvh_engine {
     bool hasSpheres = false;  // scene uploaded with spheres: the SPHERES instantiations run
     bool hasAlpha = false;    // scene uploaded with per-primitive alpha: AlphaKernel runs
     bool general = false;     // nnbvh_upload_scene_general with more than one special kind: BasicKernel<.., 1, 1, 1> runs
+    bool instStepOK = false;  // instanced scene laid out for StepKernel<..., INST> (outer + 1 + inner stack depth <= 64)
     // device-pointer path scratch
     Scratch scratch;
     // host-pointer pipeline
@@ -180,6 +182,7 @@ struct nnbvh_engine {
     int leafQuorum = -1;
     int stepStats = 0;       // NNBVH_STEP_STATS=1: run the counting instantiation of StepKernel
     unsigned long long *dStats = nullptr;
+    int instStep = 1;        // instanced scenes: 1 = StepKernel<..., INST>, 0 = the one-thread-per-ray BasicKernel
     int gridRaysPerLane = 0; // StepKernel: shrink the persistent grid for small batches (StepGrid); 0 = never
     int popLoop = 1;         // StepKernel: discard culled stack entries inside the pop
     int sphereQuorum = 12;   // StepKernel with sphere leaves: lanes waiting at spheres before their tests run
@@ -256,6 +259,7 @@ extern "C" int nnbvh_create(const nnbvh_options *opts, nnbvh_engine **out) {
     e->leafQuorum = EnvInt("NNBVH_LEAF_QUORUM", e->leafQuorum);
     e->popLoop = EnvInt("NNBVH_POP_LOOP", e->popLoop);
     e->gridRaysPerLane = EnvInt("NNBVH_GRID_RAYS_PER_LANE", e->gridRaysPerLane);
+    e->instStep = EnvInt("NNBVH_INST_STEP", e->instStep);
     e->sphereQuorum = EnvInt("NNBVH_SPHERE_QUORUM", e->sphereQuorum);
     e->stepStats = EnvInt("NNBVH_STEP_STATS", 0);
     e->chunkRamp = EnvInt("NNBVH_CHUNK_RAMP", e->chunkRamp);
@@ -335,6 +339,7 @@ extern "C" int nnbvh_clone(nnbvh_engine *src, nnbvh_engine **out) {
     e->hasInstances = src->hasInstances;
     e->hasAlpha = src->hasAlpha;
     e->general = src->general;
+    e->instStepOK = src->instStepOK;
     *out = e;
     return NNBVH_OK;
 }
@@ -519,10 +524,25 @@ static int MakeSphereDev(const nnbvh_sphere &s, uint32_t index, SphereDev *out) 
     return NNBVH_OK;
 }
 
+// The objects of an instanced scene as StepKernel<..., INST> wants them: WideNodes and triangles that UploadScene
+// appends to the top level's arrays (refs are relative to the start of the object level until it rebases them).
+struct ObjectLevel {
+    std::vector<WideNode> wide;
+    std::vector<float> tris9;
+    std::vector<uint8_t> last;
+    std::vector<uint32_t> wideStart, primStart;  // per object: where it starts in `wide` / in the triangles
+    std::vector<int32_t> rootRef;                // per object, relative to the object level
+    std::vector<float> rootBox;                  // 6 floats per object
+    std::vector<uint32_t> objectOf;              // per instance
+    uint32_t maxDepth = 0;                       // deepest traversal stack any object needs
+    bool regular = true;                         // every box finite with lo <= hi
+};
+
 static int UploadScene(nnbvh_engine *e, const nnbvh_node *nodes, uint32_t nNodes,
                        const float *orderedTriVerts9, uint32_t nPrims, const int32_t *sphereOf,
                        const nnbvh_sphere *spheres, uint32_t nSpheres,
-                       const int32_t *instanceOf = nullptr, uint32_t nInstances = 0);
+                       const int32_t *instanceOf = nullptr, uint32_t nInstances = 0,
+                       ObjectLevel *objs = nullptr);
 
 extern "C" int nnbvh_upload_scene(nnbvh_engine *e, const nnbvh_node *nodes, uint32_t nNodes,
                                   const float *orderedTriVerts9, uint32_t nPrims) {
@@ -565,7 +585,7 @@ extern "C" int nnbvh_upload_scene_mixed(nnbvh_engine *e, const nnbvh_node *nodes
 static int UploadScene(nnbvh_engine *e, const nnbvh_node *nodes, uint32_t nNodes,
                        const float *orderedTriVerts9, uint32_t nPrims, const int32_t *sphereOf,
                        const nnbvh_sphere *spheres, uint32_t nSpheres, const int32_t *instanceOf,
-                       uint32_t nInstances) {
+                       uint32_t nInstances, ObjectLevel *objs) {
     if (!e) return SetError(NNBVH_ERR_INVALID, "nnbvh_upload_scene: engine is NULL");
     CU(cudaSetDevice(e->device));
     e->haveScene = false;
@@ -573,6 +593,7 @@ static int UploadScene(nnbvh_engine *e, const nnbvh_node *nodes, uint32_t nNodes
     e->hasInstances = false;
     e->hasAlpha = false;
     e->general = false;
+    e->instStepOK = false;
     if (nNodes == 0) {  // `nodes == nullptr` in the reference: every ray misses
         e->sc = SceneDev{};
         e->haveScene = true;
@@ -599,11 +620,33 @@ static int UploadScene(nnbvh_engine *e, const nnbvh_node *nodes, uint32_t nNodes
     const uint32_t topCap = 2048;  // 128 KiB of WideNodes at most in shared memory
     int rc = BuildWideLayout(h, nPrims, topCap, wide, last, &rootRef, &topNodes);
     if (rc) return rc;
+    // Instanced scenes on the StepKernel: the objects' WideNodes follow the top level's, their triangles follow
+    // the top level's triangles; refs become absolute.
+    const uint32_t nWideTop = (uint32_t)wide.size();
+    uint32_t nObjPrims = 0;
+    bool stepInstances = false;
+    if (objs) {
+        uint32_t depthTop = 0;
+        rc = nnbvh_tree_stack_depth(h.data(), nNodes, &depthTop);
+        if (rc) return rc;
+        nObjPrims = (uint32_t)objs->last.size();
+        stepInstances = depthTop + 1 + objs->maxDepth <= (uint32_t)kMaxStack &&
+                        (uint64_t)nPrims + nObjPrims < 0x80000000ull;
+        if (stepInstances) {
+            if (!objs->regular) e->boxesRegular = false;
+            wide.reserve(nWideTop + objs->wide.size());
+            for (WideNode w : objs->wide) {
+                w.ref0 = w.ref0 >= 0 ? w.ref0 + (int32_t)nWideTop : (int32_t)(0x80000000u | (((uint32_t)w.ref0 & 0x7fffffffu) + nPrims));
+                w.ref1 = w.ref1 >= 0 ? w.ref1 + (int32_t)nWideTop : (int32_t)(0x80000000u | (((uint32_t)w.ref1 & 0x7fffffffu) + nPrims));
+                wide.push_back(w);
+            }
+        } else nObjPrims = 0;
+    }
     rc = e->store->dNodes.Reserve(nNodes);
     if (rc) return rc;
     rc = e->store->dWide.Reserve(wide.size());
     if (rc) return rc;
-    rc = e->store->dTris.Reserve(3 * (size_t)nPrims);
+    rc = e->store->dTris.Reserve(3 * ((size_t)nPrims + nObjPrims));
     if (rc) return rc;
     CU(cudaMemcpyAsync(e->store->dNodes.p, h.data(), sizeof(nnbvh_node) * (size_t)nNodes,
                        cudaMemcpyHostToDevice, st));
@@ -655,6 +698,32 @@ static int UploadScene(nnbvh_engine *e, const nnbvh_node *nodes, uint32_t nNodes
     }
     PackTrisKernel<<<(nPrims + 255) / 256, 256, 0, st>>>(src, dLast.p, dSphereOf.p, dInstanceOf.p, nPrims, e->store->dTris.p);
     ++e->launches;
+    DevTmp<float> dObjRaw;
+    DevTmp<uint8_t> dObjLast;
+    std::vector<InstanceStep> steps;  // outlives the asynchronous copy
+    if (stepInstances) {
+        CU(dObjRaw.Alloc(objs->tris9.size()));
+        CU(dObjLast.Alloc(nObjPrims));
+        CU(cudaMemcpyAsync(dObjRaw.p, objs->tris9.data(), sizeof(float) * objs->tris9.size(), cudaMemcpyHostToDevice, st));
+        CU(cudaMemcpyAsync(dObjLast.p, objs->last.data(), nObjPrims, cudaMemcpyHostToDevice, st));
+        PackTrisKernel<<<(nObjPrims + 255) / 256, 256, 0, st>>>(dObjRaw.p, dObjLast.p, nullptr, nullptr, nObjPrims,
+                                                                 e->store->dTris.p + 3 * (size_t)nPrims);
+        ++e->launches;
+        steps.resize(objs->objectOf.size());
+        for (size_t k = 0; k < steps.size(); ++k) {
+            const uint32_t j = objs->objectOf[k];
+            for (int c = 0; c < 6; ++c) steps[k].rootBox[c] = objs->rootBox[6 * j + c];
+            const int32_t r = objs->rootRef[j];
+            steps[k].rootRef = r >= 0 ? r + (int32_t)nWideTop : (int32_t)(0x80000000u | (((uint32_t)r & 0x7fffffffu) + nPrims));
+            steps[k].primBase = nPrims + objs->primStart[j];
+        }
+        rc = e->store->dInstStep.Reserve(steps.size());
+        if (rc) {
+            cudaStreamSynchronize(st);
+            return rc;
+        }
+        CU(cudaMemcpyAsync(e->store->dInstStep.p, steps.data(), sizeof(InstanceStep) * steps.size(), cudaMemcpyHostToDevice, st));
+    }
     cudaError_t launchErr = cudaGetLastError();
     cudaError_t syncErr = cudaStreamSynchronize(st);  // before the temporaries (and `h`, `wide`, `last`, `sd`) go away
     CU(launchErr);
@@ -670,6 +739,8 @@ static int UploadScene(nnbvh_engine *e, const nnbvh_node *nodes, uint32_t nNodes
     sc.rootRef = rootRef;
     sc.topNodes = topNodes;
     sc.spheres = sphereOf ? e->store->dSpheres.p : nullptr;
+    sc.instStep = stepInstances ? e->store->dInstStep.p : nullptr;
+    e->instStepOK = stepInstances;
     e->sc = sc;
     e->hasSpheres = sphereOf != nullptr;
     e->haveScene = true;
@@ -702,7 +773,7 @@ extern "C" int nnbvh_instance_bounds(const nnbvh_instance *in, const float *obje
 // The objects of an instanced scene: validate each tree, lay trees and triangles back to back on the device,
 // fill the instance table.  `e`'s device is current.
 static int UploadObjects(nnbvh_engine *e, const nnbvh_instance *instances, uint32_t nInstances,
-                         const nnbvh_object *objects, uint32_t nObjects) {
+                         const nnbvh_object *objects, uint32_t nObjects, ObjectLevel *lvl) {
     cudaStream_t st = e->stream;
     std::vector<nnbvh_node> allNodes;
     std::vector<float> allTris;
@@ -721,6 +792,30 @@ static int UploadObjects(nnbvh_engine *e, const nnbvh_instance *instances, uint3
         if (rc) return rc;
         nodeBase[j] = (uint32_t)allNodes.size();
         primBase[j] = (uint32_t)allLast.size();
+        {   // the object in the StepKernel's layout: refs relative to the start of the object level
+            const uint32_t w0 = (uint32_t)lvl->wide.size(), p0 = primBase[j];
+            auto rel = [&](int32_t r) {
+                return r >= 0 ? r + (int32_t)w0 : (int32_t)(0x80000000u | (((uint32_t)r & 0x7fffffffu) + p0));
+            };
+            lvl->wideStart.push_back(w0);
+            lvl->primStart.push_back(p0);
+            for (WideNode w : wide) {
+                w.ref0 = rel(w.ref0);
+                w.ref1 = rel(w.ref1);
+                lvl->wide.push_back(w);
+            }
+            lvl->rootRef.push_back(rel(rootRef));
+            for (int c = 0; c < 6; ++c) lvl->rootBox.push_back(h[0].bounds[c]);
+            uint32_t depth = 0;
+            rc = nnbvh_tree_stack_depth(h.data(), o.nNodes, &depth);
+            if (rc) return rc;
+            lvl->maxDepth = std::max(lvl->maxDepth, depth);
+            for (const nnbvh_node &nd : h)
+                for (int c = 0; c < 3; ++c) {
+                    const float lo = nd.bounds[c], hi = nd.bounds[3 + c];
+                    if (!(std::isfinite(lo) && std::isfinite(hi) && lo <= hi)) lvl->regular = false;
+                }
+        }
         allNodes.insert(allNodes.end(), h.begin(), h.end());
         allTris.insert(allTris.end(), o.orderedTriVerts9, o.orderedTriVerts9 + 9 * (size_t)o.nPrims);
         allLast.insert(allLast.end(), last.begin(), last.end());
@@ -734,11 +829,14 @@ static int UploadObjects(nnbvh_engine *e, const nnbvh_instance *instances, uint3
                 return SetError(NNBVH_ERR_INVALID, "instance %u: non-finite transform", k);
             id[k].mInv[c] = in.primitiveFromRender[c];
         }
+        lvl->objectOf.push_back(in.object);
         id[k].nodeBase = nodeBase[in.object];
         id[k].primBase = primBase[in.object];
         id[k].nNodes = objects[in.object].nNodes;
         id[k].pad = 0;
     }
+    lvl->tris9 = allTris;
+    lvl->last = allLast;
     const uint32_t nObjPrims = (uint32_t)allLast.size();
     int rc = e->store->dObjNodes.Reserve(allNodes.size());
     if (!rc) rc = e->store->dObjTris.Reserve(3 * (size_t)nObjPrims);
@@ -772,10 +870,11 @@ extern "C" int nnbvh_upload_scene_instanced(nnbvh_engine *e, const nnbvh_node *n
         return SetError(NNBVH_ERR_INVALID, "nnbvh_upload_scene_instanced: NULL / empty instance or object table");
     CU(cudaSetDevice(e->device));
     DetachStore(e);
-    int rc = UploadObjects(e, instances, nInstances, objects, nObjects);
+    ObjectLevel lvl;
+    int rc = UploadObjects(e, instances, nInstances, objects, nObjects, &lvl);
     if (rc) return rc;
-    // the top level: triangles and instance slots
-    rc = UploadScene(e, nodes, nNodes, orderedTriVerts9, nPrims, nullptr, nullptr, 0, orderedInstanceIndex, nInstances);
+    // the top level: triangles and instance slots (+ the objects appended in the StepKernel's layout)
+    rc = UploadScene(e, nodes, nNodes, orderedTriVerts9, nPrims, nullptr, nullptr, 0, orderedInstanceIndex, nInstances, &lvl);
     if (rc) return rc;
     e->sc.instances = e->store->dInstances.p;
     e->sc.objNodes = e->store->dObjNodes.p;
@@ -820,7 +919,8 @@ extern "C" int nnbvh_upload_scene_general(nnbvh_engine *e, const nnbvh_scene_des
     CU(cudaSetDevice(e->device));
     DetachStore(e);
     int rc = NNBVH_OK;
-    if (inst) rc = UploadObjects(e, d->instances, d->nInstances, d->objects, d->nObjects);
+    ObjectLevel lvl;  // general scenes run BasicKernel: the StepKernel layout of the objects is not uploaded
+    if (inst) rc = UploadObjects(e, d->instances, d->nInstances, d->objects, d->nObjects, &lvl);
     if (rc) return rc;
     rc = UploadScene(e, d->nodes, d->nNodes, d->orderedTriVerts9, d->nPrims, sph ? d->orderedSphereIndex : nullptr,
                      d->spheres, d->nSpheres, inst ? d->orderedInstanceIndex : nullptr, d->nInstances);
@@ -893,6 +993,10 @@ static void LaunchStep(nnbvh_engine *e, cudaStream_t st, const StepParams &p) {
     const uint64_t n = p.nPtr ? 0 : p.n;  // the exact launch over the deferred list does not know its size on the host
     if (e->hasSpheres) {  // sphere leaves: one instantiation, 4 CTAs/SM (the sphere test wants registers)
         StepKernel<ANY, EXACT, 4, false, true><<<p.nPtr ? e->numSMs * 4 : StepGrid(e, 4, n), 256, 0, st>>>(p);
+        return;
+    }
+    if (e->hasInstances) {  // instance slots: one instantiation, 4 CTAs/SM (the lane carries the instance state)
+        StepKernel<ANY, EXACT, 4, false, false, true><<<p.nPtr ? e->numSMs * 4 : StepGrid(e, 4, n), 256, 0, st>>>(p);
         return;
     }
     if (p.stats && !EXACT) {  // NNBVH_STEP_STATS=1: lane-occupancy counters (diagnostic build of the kernel)
@@ -995,7 +1099,8 @@ static int LaunchTraversal(nnbvh_engine *e, cudaStream_t st, bool any, bool coun
     // One thread per ray (general / alpha / instanced scenes): the same ray order helps there too -- the lanes of a
     // warp then walk neighbouring rays -- so those kernels pull their ray through the permutation as well.
     RayInput inO = in;
-    if ((e->general || e->hasAlpha || e->hasInstances) && !counters && e->kernel != NNBVH_KERNEL_BASIC) {
+    if ((e->general || e->hasAlpha || (e->hasInstances && !(e->instStepOK && e->instStep && e->kernel != NNBVH_KERNEL_WIDE))) &&
+        !counters && e->kernel != NNBVH_KERNEL_BASIC) {
         CU(cudaMemsetAsync(scr.cursor, 0, kCursorWords * sizeof(unsigned long long), st));
         // (no node-count floor here: an instanced scene's top level is small, its objects are not)
         int rc = OrderRays(e, st, in, n, scr, scr.cursor, true, 0u, &inO.perm, &inO.permOn);
@@ -1025,8 +1130,10 @@ static int LaunchTraversal(nnbvh_engine *e, cudaStream_t st, bool any, bool coun
         CU(cudaGetLastError());
         return NNBVH_OK;
     }
-    // instanced scenes: nested traversal lives in BasicKernel only (one thread per ray)
-    const bool basic = counters || e->kernel == NNBVH_KERNEL_BASIC || e->hasInstances;
+    // instanced scenes: StepKernel<..., INST> when the combined stack depth fits (NNBVH_INST_STEP=0: BasicKernel);
+    // counters and deeper scenes run the one-thread-per-ray kernel with its per-level stacks
+    const bool instStep = e->hasInstances && e->instStepOK && e->instStep && e->kernel != NNBVH_KERNEL_WIDE;
+    const bool basic = counters || e->kernel == NNBVH_KERNEL_BASIC || (e->hasInstances && !instStep);
     if (basic) {
         if (n > (uint64_t)0x7fffffff * 128)
             return SetError(NNBVH_ERR_INVALID, "batch too large for one launch");
@@ -1065,9 +1172,10 @@ static int LaunchTraversal(nnbvh_engine *e, cudaStream_t st, bool any, bool coun
         // ---- binning pre-pass: a ray order that keeps warps coherent (binning.cuh) ----
         // binMode 1: always sort; 2: the device decides per batch (the kernels read the flag); 0: off.
         const uint32_t *perm = nullptr, *permOn = nullptr;
-        const bool stepKernel = e->kernel != NNBVH_KERNEL_WIDE || e->hasSpheres;  // WideKernel has no sphere leaves
+        const bool stepKernel = e->kernel != NNBVH_KERNEL_WIDE || e->hasSpheres || instStep;  // WideKernel: triangles only
         {
-            int rc = OrderRays(e, st, in, n, scr, cursor, stepKernel, e->binMinNodes, &perm, &permOn);
+            // (an instanced scene's top level is small, its objects are not: no node-count floor there)
+            int rc = OrderRays(e, st, in, n, scr, cursor, stepKernel, instStep ? 0u : e->binMinNodes, &perm, &permOn);
             if (rc) return rc;
         }
         if (stepKernel) {
@@ -1080,6 +1188,7 @@ static int LaunchTraversal(nnbvh_engine *e, cudaStream_t st, bool any, bool coun
             sp.n = n;
             sp.hits = o.hits;
             sp.occluded = o.occ;
+            sp.inner = (instStep && !any) ? o.inner : nullptr;
             sp.perm = perm;
             sp.permOn = permOn;
             StepKnobs(e, &sp.refillBelow, &sp.leafQuorum);

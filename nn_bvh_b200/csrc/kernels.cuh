@@ -46,6 +46,9 @@ struct SceneDev {
     const float4 *objTris;
     // general scenes (nnbvh_upload_scene_general): constant alpha per ordered top-level primitive, >= 1 = none
     const float *alpha;
+    // instanced scenes on the StepKernel: per instance the object's root box, root ref and first triangle in the
+    // COMBINED arrays (the objects' WideNodes / triangles follow the top level's in `wide` / `tris`)
+    const InstanceStep *instStep;
 };
 
 struct RayInput {

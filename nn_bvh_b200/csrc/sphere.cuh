@@ -227,6 +227,14 @@ struct alignas(64) InstanceDev {
 };
 static_assert(sizeof(InstanceDev) == 64, "InstanceDev must be 64 bytes");
 
+// What StepKernel<..., INST> reads when a lane enters an instance (two float4 loads).
+struct alignas(32) InstanceStep {
+    float rootBox[6];   // bounds of the object's root node (the reference tests it first, aggregates.cpp:543)
+    int32_t rootRef;    // WideNode index (>= 0) or leaf ref (< 0) of the object's root, absolute
+    uint32_t primBase;  // first triangle of the object in the combined triangle array
+};
+static_assert(sizeof(InstanceStep) == 32, "InstanceStep must be 32 bytes");
+
 // Ray Transform::ApplyInverse(const Ray &r, Float *tMax) (util/transform.h:416-430) with
 // Point3fi Transform::ApplyInverse(const Point3fi &) on an exact point (util/transform.cpp:263-303).
 __device__ __noinline__ void InstanceRay(const InstanceDev *__restrict__ in, float rox, float roy, float roz,

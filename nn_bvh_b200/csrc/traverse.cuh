@@ -64,6 +64,7 @@ struct StepParams {
     uint32_t popLoop;             // 1: discard culled stack entries inside the pop (default)
     uint32_t sphereQuorum;        // SPHERES: run the sphere tests when this many lanes wait at sphere slots
     unsigned long long *stats;    // STATS instantiation only: 8 lane-occupancy counters
+    uint32_t *inner;              // INST, closest hit: optional plane, ordered primitive inside the hit object
 };
 
 struct F8 {
@@ -107,7 +108,15 @@ constexpr float kNegInf = -__builtin_huge_valf();
 template <bool ANY> struct StackWord { typedef unsigned long long type; };
 template <> struct StackWord<true> { typedef unsigned type; };
 
-template <bool ANY, bool EXACT, int MINB, bool STATS = false, bool SPHERES = false>
+// INST: the top-level list holds TransformedPrimitive slots (kPrimInstance).  The objects' WideNodes and triangles
+// live in the SAME arrays as the top level (refs are absolute), so entering an instance is: transform the ray
+// (InstanceRay = Transform::ApplyInverse(Ray, &tMax)), test the object's root box, push a sentinel holding where
+// the outer traversal continues (and its tMax), and carry on with `cur` = the object's root; leaving it -- when the
+// stack is back at the sentinel -- re-derives the outer ray's constants from the ray in memory.  A ray whose
+// TRANSFORMED direction does not qualify for the fast slab is handed to the exact launch as a whole.
+constexpr int kPopMark = 0x7fffffff;  // sentinel: "the instance was the last primitive of its leaf: pop"
+
+template <bool ANY, bool EXACT, int MINB, bool STATS = false, bool SPHERES = false, bool INST = false>
 __global__ void __launch_bounds__(256, MINB) StepKernel(StepParams p) {
     // STATS: [0] phase-A iterations, [1] lanes at a node, [2] lanes parked at a leaf, [3] lanes without
     // a ray, [4] phase-B passes, [5] lanes parked there, [6] lanes that ran a triangle test, [7] refills
@@ -137,8 +146,82 @@ __global__ void __launch_bounds__(256, MINB) StepKernel(StepParams p) {
     // run for one or two lanes at a time it was most of the kernel (crown's environment shell: every
     // escaping ray tests it once).  Waiting changes nothing a ray can observe: its own state is frozen.
     bool sphWait = false;
+    // INST: >= 0 while the lane is inside an instance (the instance's top-level slot); stack entries below spBase
+    // belong to the outer traversal, stack[spBase - 1] is the sentinel
+    int instSlot = -1, spBase = 0;
+    uint32_t instPrimBase = 0;
+    bool instHit = false;
 
     const unsigned leafQuorum = p.leafQuorum;
+
+    auto fastSlabSafe = [](const RayConst &rc) {  // finite, non-zero invDir and finite origin <=> the fast slab is exact
+        const float big = __int_as_float(0x7f800000);
+        const bool okInv = fabsf(rc.ix) < big && fabsf(rc.iy) < big && fabsf(rc.iz) < big &&
+                           rc.ix != 0.f && rc.iy != 0.f && rc.iz != 0.f;
+        const bool okOrg = fabsf(rc.ox) < big && fabsf(rc.oy) < big && fabsf(rc.oz) < big;
+        return okInv && okOrg;
+    };
+    auto setRay = [&](const RayConst &rc) {
+        ry.ox = rc.ox; ry.oy = rc.oy; ry.oz = rc.oz;
+        ry.ix = rc.ix; ry.iy = rc.iy; ry.iz = rc.iz;
+        ry.Sx = rc.Sx; ry.Sy = rc.Sy; ry.Sz = rc.Sz;
+        ry.kz = rc.kz;
+        ry.neg = (unsigned)rc.negx | ((unsigned)rc.negy << 1) | ((unsigned)rc.negz << 2);
+    };
+    auto finish = [&]() {  // the ray is done: its record goes out
+        alive = false;
+        if (ANY) p.occluded[rayIdx] = 0;
+        else {
+            StoreHit(p.hits, rayIdx, hit);
+            if (INST && p.inner) p.inner[rayIdx] = hit.inner;
+        }
+    };
+    // INST: the pop of both phases.  Entries above spBase are the current level's; with none left inside an instance
+    // the sentinel is taken: TransformedPrimitive::Intersect has returned, BVHAggregate::Intersect sets
+    // tMax = tHit when it brought a hit (aggregates.cpp:549-553) and goes on with the leaf's next primitive.
+    auto popInst = [&]() {
+        while (true) {
+            bool got = false;
+            if (ANY) {
+                if (sp > spBase) {
+                    --sp;
+                    cur = (int)(unsigned)stack[sp];
+                    got = true;
+                }
+            } else {
+                while (sp > spBase) {
+                    --sp;
+                    const unsigned long long e = (unsigned long long)stack[sp];
+                    cur = (int)(unsigned)e;
+                    curT = __uint_as_float((unsigned)(e >> 32));
+                    if (curT < tMax || !p.popLoop) {
+                        got = true;
+                        break;
+                    }
+                }
+            }
+            if (got) return;
+            if (instSlot < 0) {
+                finish();
+                return;
+            }
+            --sp;  // the sentinel
+            const unsigned long long e = (unsigned long long)stack[sp];
+            const int outerNext = (int)(unsigned)e;
+            const RayRegs rr = LoadRay(p.in, rayIdx);
+            setRay(MakeRayConst(rr.ox, rr.oy, rr.oz, rr.dx, rr.dy, rr.dz));
+            if (ANY) tMax = rr.tMax;
+            else tMax = instHit ? hit.t : __uint_as_float((unsigned)(e >> 32));
+            instSlot = -1;
+            spBase = 0;
+            instHit = false;
+            if (outerNext != kPopMark) {
+                cur = outerNext;  // the next primitive of the outer leaf: no box test again
+                if (!ANY) curT = kNegInf;
+                return;
+            }
+        }
+    };
 
     while (true) {
         // ---- refill: finished lanes take the next rays from the global cursor ----
@@ -189,6 +272,12 @@ __global__ void __launch_bounds__(256, MINB) StepKernel(StepParams p) {
                         tMax = rr.tMax;
                         hit.prim = NNBVH_MISS;
                         hit.t = hit.b0 = hit.b1 = hit.b2 = 0.f;
+                        if (INST) {
+                            hit.inner = NNBVH_MISS;
+                            instSlot = -1;
+                            spBase = 0;
+                            instHit = false;
+                        }
                         sp = 0;
                         // Root: the reference tests the root's own box first (aggregates.cpp:543);
                         // nodes == nullptr -> miss (:531).  Exact cascade, once per ray.
@@ -205,7 +294,10 @@ __global__ void __launch_bounds__(256, MINB) StepKernel(StepParams p) {
                             curT = tRoot;
                             alive = true;
                         } else if (ANY) p.occluded[idx] = 0;
-                        else StoreHit(p.hits, idx, hit);
+                        else {
+                            StoreHit(p.hits, idx, hit);
+                            if (INST && p.inner) p.inner[idx] = NNBVH_MISS;
+                        }
                     }
                 }
             }
@@ -315,7 +407,9 @@ __global__ void __launch_bounds__(256, MINB) StepKernel(StepParams p) {
                     if (!ANY) curT = goNear ? tNear : tFar;
                     descend = goNear || goFar;
                 }
-                if (!descend) {
+                if (INST && !descend) {
+                    popInst();
+                } else if (!descend) {
                     // aggregates.cpp:570-574.  Entries whose box test fails against the current tMax
                     // (`curT < tMax` false) are discarded here rather than one per iteration: the
                     // reference pops them one by one with the same outcome, and tMax cannot change
@@ -385,7 +479,47 @@ __global__ void __launch_bounds__(256, MINB) StepKernel(StepParams p) {
                 const float4 v0 = __ldg(tp), v1 = __ldg(tp + 1), v2 = __ldg(tp + 2);
                 const uint32_t flags = __float_as_uint(v0.w);
                 bool found = false;
-                if (SPHERES && (flags & kPrimSphere) && !sphWait) {
+                if (INST && (flags & kPrimInstance)) {
+                    // TransformedPrimitive::Intersect / IntersectP (cpu/primitive.cpp:112-130): the ray in the
+                    // instance's space, the object's aggregate traversed there with the shortened tMax
+                    const uint32_t k = __float_as_uint(v0.x);
+                    const RayRegs rr = LoadRay(p.in, rayIdx);
+                    float o[3], d[3], tLocal;
+                    InstanceRay(sc.instances + k, rr.ox, rr.oy, rr.oz, rr.dx, rr.dy, rr.dz, tMax, o, d, &tLocal);
+                    const RayConst rc = MakeRayConst(o[0], o[1], o[2], d[0], d[1], d[2]);
+                    if (!EXACT && !fastSlabSafe(rc)) {
+                        // this instance's ray needs the verbatim slab cascade: the exact launch traces the ray again
+                        const uint32_t pos = atomicAdd(p.nDeferred, 1u);
+                        p.deferred[pos] = rayIdx;
+                        alive = false;
+                        needPop = false;
+                    } else {
+                        const float4 *is = reinterpret_cast<const float4 *>(sc.instStep + k);
+                        const float4 b0 = __ldg(is), b1 = __ldg(is + 1);  // rootBox[6], rootRef, primBase
+                        float tRoot = 0.f;
+                        const bool rootOk = SlabStatic(rc, rc.negx ? b0.w : b0.x, rc.negx ? b0.x : b0.w,
+                                                       rc.negy ? b1.x : b0.y, rc.negy ? b0.y : b1.x,
+                                                       rc.negz ? b1.y : b0.z, rc.negz ? b0.z : b1.y, &tRoot);
+                        if (rootOk && tRoot < tLocal) {
+                            const int outerNext = (flags & kTriLast) ? kPopMark : cur + 1;
+                            if (ANY) stack[sp] = (unsigned)outerNext;
+                            else stack[sp] = ((unsigned long long)__float_as_uint(tMax) << 32) | (unsigned)outerNext;
+                            ++sp;
+                            spBase = sp;
+                            instSlot = (int)prim;
+                            instPrimBase = __float_as_uint(b1.w);
+                            instHit = false;
+                            setRay(rc);
+                            tMax = tLocal;
+                            cur = __float_as_int(b1.z);
+                            if (!ANY) curT = tRoot;
+                            needPop = false;
+                        } else if (!(flags & kTriLast)) {
+                            cur = cur + 1;  // the instance is missed as a whole: next primitive of the leaf
+                            needPop = false;
+                        }
+                    }
+                } else if (SPHERES && (flags & kPrimSphere) && !sphWait) {
                     sphWait = true;  // first arrival: wait for company (see above); nothing else moves
                     needPop = false;
                 } else if (SPHERES && (flags & kPrimSphere)) {
@@ -411,6 +545,11 @@ __global__ void __launch_bounds__(256, MINB) StepKernel(StepParams p) {
                                      &t, &b0, &b1, &b2)) {
                         found = true;
                         hit.prim = prim;
+                        if (INST) {  // inside an instance: its top-level slot + the primitive inside the object
+                            hit.inner = instSlot >= 0 ? prim - instPrimBase : NNBVH_MISS;
+                            hit.prim = instSlot >= 0 ? (uint32_t)instSlot : prim;
+                            instHit = instSlot >= 0;
+                        }
                         hit.t = t;
                         hit.b0 = b0;
                         hit.b1 = b1;
@@ -418,7 +557,9 @@ __global__ void __launch_bounds__(256, MINB) StepKernel(StepParams p) {
                         tMax = t;
                     }
                 }
-                if (SPHERES && sphWait) {
+                if (INST && (flags & kPrimInstance)) {
+                    // handled above
+                } else if (SPHERES && sphWait) {
                     // parked at the sphere slot: `cur` stays
                 } else if (ANY && found) {  // first accepted primitive ends the ray (:598-601)
                     alive = false;
@@ -429,7 +570,9 @@ __global__ void __launch_bounds__(256, MINB) StepKernel(StepParams p) {
                     needPop = false;
                 }
             }
-            if (needPop) {  // :556-558; culled entries are skipped as in phase A
+            if (INST && needPop) {
+                popInst();
+            } else if (needPop) {  // :556-558; culled entries are skipped as in phase A
                 bool got = false;
                 if (ANY) {
                     if (sp > 0) {

@@ -93,9 +93,13 @@ def _oracle_scene(agg):
                 obj_prim_base=np.array(pb_[:-1], dtype=np.int32))
 
 
+# inst_step 1: StepKernel<..., INST> (the objects' nodes and triangles appended to the top level's arrays, the second
+# level entered as a pushed sub-state); 0: the one-thread-per-ray BasicKernel with nested traversal
 @pytest.mark.gpu
-def test_instanced_scene_gpu_matches_reference_golden(gold):
+@pytest.mark.parametrize("inst_step", ["1", "0"])
+def test_instanced_scene_gpu_matches_reference_golden(gold, inst_step, monkeypatch):
     import nn_bvh_b200 as nb
+    monkeypatch.setenv("NNBVH_INST_STEP", inst_step)
     J = int(gold["n_objects"])
     inst = nb.make_instances(gold["inst24"][:, :12].reshape(-1, 3, 4), gold["inst_object"], gold["inst24"][:, 12:])
     assert np.array_equal(inst["renderFromPrimitive"], gold["inst24"][:, :12])
@@ -119,9 +123,11 @@ def test_instanced_scene_gpu_matches_reference_golden(gold):
 
 
 @pytest.mark.gpu
-def test_instanced_scene_gpu_matches_oracle_at_size(oracle):
+@pytest.mark.parametrize("inst_step", ["1", "0"])
+def test_instanced_scene_gpu_matches_oracle_at_size(oracle, inst_step, monkeypatch):
     import torch
     import nn_bvh_b200 as nb
+    monkeypatch.setenv("NNBVH_INST_STEP", inst_step)
     from tools.make_golden import instanced_scene
     rng = np.random.default_rng(21)
     top, objs, inst24, io = instanced_scene(rng, T=20_000, K=400, obj_sizes=(3000, 1, 12_000, 500))

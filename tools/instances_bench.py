@@ -45,8 +45,9 @@ dr = torch.from_numpy(rays).cuda()
 hits = torch.zeros((n, 5), dtype=torch.int32, device="cuda")
 inner = torch.zeros(n, dtype=torch.int32, device="cuda")
 ref = None
-for mode in ("0", "2"):
+for step, mode in (("0", "0"), ("0", "2"), ("1", "0"), ("1", "2")):
     os.environ["NNBVH_BIN"] = mode
+    os.environ["NNBVH_INST_STEP"] = step
     agg = nb.GPUBVHAggregate(floor, 4, "sah", objects=[obj], instances=inst)
     best = 1e9
     for it in range(4):
@@ -57,6 +58,6 @@ for mode in ("0", "2"):
     h = hits.cpu().numpy()
     if ref is None:
         ref = h
-    print(f"instances {K} x {len(obj)} triangles, {n} rays, NNBVH_BIN={mode}: {n / best / 1e3:8.1f} Mrays/s "
+    print(f"instances {K} x {len(obj)} triangles, {n} rays, {'StepKernel<INST>' if step == '1' else 'BasicKernel<INST>'}, NNBVH_BIN={mode}: {n / best / 1e3:8.1f} Mrays/s "
           f"({best:.2f} ms incl. pre-pass), hit fraction {(h[:, 0] != -1).mean():.3f}, same records as unsorted: {np.array_equal(h, ref)}")
     agg.close()
