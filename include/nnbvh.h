@@ -266,8 +266,9 @@ int nnbvh_intersect_closest_instanced_soa(nnbvh_engine *e, const float *ox, cons
  * alpha test).  Index arrays of kinds that do not occur may be NULL.  Hit records are those of the
  * specialised uploads: triangle {prim, t, b}, sphere {prim, tHit, pObj}, instance {prim = top-level slot,
  * inner triangle's t, b} (+ innerPrim from nnbvh_intersect_closest_instanced).  A description with at most
- * one extra kind is routed to that kind's own upload and kernel; a real mix runs a one-thread-per-ray
- * kernel, and per-ray counters are unavailable for it. */
+ * one extra kind is routed to that kind's own upload and kernel; a real mix runs the general
+ * instantiation of the product kernel (sphere leaves + instance slots + alpha test), and per-ray
+ * counters are unavailable for it. */
 typedef struct nnbvh_scene_desc {
     const nnbvh_node *nodes;
     uint32_t nNodes;

@@ -167,6 +167,7 @@ struct nnbvh_engine {
     bool hasAlpha = false;    // scene uploaded with per-primitive alpha: AlphaKernel runs
     bool general = false;     // nnbvh_upload_scene_general with more than one special kind: BasicKernel<.., 1, 1, 1> runs
     bool instStepOK = false;  // instanced scene laid out for StepKernel<..., INST> (outer + 1 + inner stack depth <= 64)
+    bool generalStepOK = false;  // general scene that the StepKernel's general instantiation can run
     // device-pointer path scratch
     Scratch scratch;
     // host-pointer pipeline
@@ -340,6 +341,7 @@ extern "C" int nnbvh_clone(nnbvh_engine *src, nnbvh_engine **out) {
     e->hasAlpha = src->hasAlpha;
     e->general = src->general;
     e->instStepOK = src->instStepOK;
+    e->generalStepOK = src->generalStepOK;
     *out = e;
     return NNBVH_OK;
 }
@@ -594,6 +596,7 @@ static int UploadScene(nnbvh_engine *e, const nnbvh_node *nodes, uint32_t nNodes
     e->hasAlpha = false;
     e->general = false;
     e->instStepOK = false;
+    e->generalStepOK = false;
     if (nNodes == 0) {  // `nodes == nullptr` in the reference: every ray misses
         e->sc = SceneDev{};
         e->haveScene = true;
@@ -919,11 +922,12 @@ extern "C" int nnbvh_upload_scene_general(nnbvh_engine *e, const nnbvh_scene_des
     CU(cudaSetDevice(e->device));
     DetachStore(e);
     int rc = NNBVH_OK;
-    ObjectLevel lvl;  // general scenes run BasicKernel: the StepKernel layout of the objects is not uploaded
+    ObjectLevel lvl;
     if (inst) rc = UploadObjects(e, d->instances, d->nInstances, d->objects, d->nObjects, &lvl);
     if (rc) return rc;
     rc = UploadScene(e, d->nodes, d->nNodes, d->orderedTriVerts9, d->nPrims, sph ? d->orderedSphereIndex : nullptr,
-                     d->spheres, d->nSpheres, inst ? d->orderedInstanceIndex : nullptr, d->nInstances);
+                     d->spheres, d->nSpheres, inst ? d->orderedInstanceIndex : nullptr, d->nInstances,
+                     inst ? &lvl : nullptr);
     if (rc || d->nNodes == 0) return rc;
     // alpha: always present on this path (1 = none), so the kernel needs no NULL test
     std::vector<float> a(d->nPrims, 1.f);
@@ -940,6 +944,7 @@ extern "C" int nnbvh_upload_scene_general(nnbvh_engine *e, const nnbvh_scene_des
     }
     e->hasSpheres = false;  // the flags of the specialised paths stay off: `general` selects the kernel
     e->general = true;
+    e->generalStepOK = !inst || e->instStepOK;  // the objects fit the StepKernel's combined stack
     return NNBVH_OK;
 }
 
@@ -991,6 +996,10 @@ static unsigned StepGrid(const nnbvh_engine *e, int minB, uint64_t n) {
 template <bool ANY, bool EXACT>
 static void LaunchStep(nnbvh_engine *e, cudaStream_t st, const StepParams &p) {
     const uint64_t n = p.nPtr ? 0 : p.n;  // the exact launch over the deferred list does not know its size on the host
+    if (e->general) {  // every primitive kind in one list: spheres + instance slots + constant alpha, 3 CTAs/SM
+        StepKernel<ANY, EXACT, 3, false, true, true, true><<<p.nPtr ? e->numSMs * 3 : StepGrid(e, 3, n), 256, 0, st>>>(p);
+        return;
+    }
     if (e->hasSpheres) {  // sphere leaves: one instantiation, 4 CTAs/SM (the sphere test wants registers)
         StepKernel<ANY, EXACT, 4, false, true><<<p.nPtr ? e->numSMs * 4 : StepGrid(e, 4, n), 256, 0, st>>>(p);
         return;
@@ -1099,14 +1108,19 @@ static int LaunchTraversal(nnbvh_engine *e, cudaStream_t st, bool any, bool coun
     // One thread per ray (general / alpha / instanced scenes): the same ray order helps there too -- the lanes of a
     // warp then walk neighbouring rays -- so those kernels pull their ray through the permutation as well.
     RayInput inO = in;
-    if ((e->general || e->hasAlpha || (e->hasInstances && !(e->instStepOK && e->instStep && e->kernel != NNBVH_KERNEL_WIDE))) &&
+    const bool generalStepEarly = e->general && e->generalStepOK && e->instStep && !counters &&
+                                  e->kernel != NNBVH_KERNEL_BASIC && e->kernel != NNBVH_KERNEL_WIDE;
+    if (((e->general && !generalStepEarly) || e->hasAlpha ||
+         (e->hasInstances && !(e->instStepOK && e->instStep && e->kernel != NNBVH_KERNEL_WIDE))) &&
         !counters && e->kernel != NNBVH_KERNEL_BASIC) {
         CU(cudaMemsetAsync(scr.cursor, 0, kCursorWords * sizeof(unsigned long long), st));
         // (no node-count floor here: an instanced scene's top level is small, its objects are not)
         int rc = OrderRays(e, st, in, n, scr, scr.cursor, true, 0u, &inO.perm, &inO.permOn);
         if (rc) return rc;
     }
-    if (e->general) {  // triangles + spheres + instances + alpha in one list: BasicKernel's general instantiation
+    const bool generalStep = e->general && e->generalStepOK && e->instStep && !counters &&
+                             e->kernel != NNBVH_KERNEL_BASIC && e->kernel != NNBVH_KERNEL_WIDE;
+    if (e->general && !generalStep) {  // triangles + spheres + instances + alpha in one list: BasicKernel's general instantiation
         if (counters)
             return SetError(NNBVH_ERR_INVALID, "per-ray counters are not available for general (mixed-kind) scenes");
         if (n > (uint64_t)0x7fffffff * 128)
@@ -1132,7 +1146,7 @@ static int LaunchTraversal(nnbvh_engine *e, cudaStream_t st, bool any, bool coun
     }
     // instanced scenes: StepKernel<..., INST> when the combined stack depth fits (NNBVH_INST_STEP=0: BasicKernel);
     // counters and deeper scenes run the one-thread-per-ray kernel with its per-level stacks
-    const bool instStep = e->hasInstances && e->instStepOK && e->instStep && e->kernel != NNBVH_KERNEL_WIDE;
+    const bool instStep = generalStep || (e->hasInstances && e->instStepOK && e->instStep && e->kernel != NNBVH_KERNEL_WIDE);
     const bool basic = counters || e->kernel == NNBVH_KERNEL_BASIC || (e->hasInstances && !instStep);
     if (basic) {
         if (n > (uint64_t)0x7fffffff * 128)

@@ -116,7 +116,10 @@ template <> struct StackWord<true> { typedef unsigned type; };
 // TRANSFORMED direction does not qualify for the fast slab is handed to the exact launch as a whole.
 constexpr int kPopMark = 0x7fffffff;  // sentinel: "the instance was the last primitive of its leaf: pop"
 
-template <bool ANY, bool EXACT, int MINB, bool STATS = false, bool SPHERES = false, bool INST = false>
+// ALPHA: sc.alpha holds a constant alpha per TOP-LEVEL ordered primitive (>= 1: none); a triangle with alpha < 1 is
+// tested as GeometricPrimitive::Intersect does (alpha_math.cuh) with the ray as the caller gave it (read again:
+// the lane keeps no direction).  SPHERES + INST + ALPHA together = the general instantiation.
+template <bool ANY, bool EXACT, int MINB, bool STATS = false, bool SPHERES = false, bool INST = false, bool ALPHA = false>
 __global__ void __launch_bounds__(256, MINB) StepKernel(StepParams p) {
     // STATS: [0] phase-A iterations, [1] lanes at a node, [2] lanes parked at a leaf, [3] lanes without
     // a ray, [4] phase-B passes, [5] lanes parked there, [6] lanes that ran a triangle test, [7] refills
@@ -532,6 +535,7 @@ __global__ void __launch_bounds__(256, MINB) StepKernel(StepParams p) {
                                    rr.dz, tMax, &sh)) {
                         found = true;
                         hit.prim = prim;
+                        if (INST) hit.inner = NNBVH_MISS;
                         hit.t = sh.t;
                         hit.b0 = sh.px;
                         hit.b1 = sh.py;
@@ -541,8 +545,18 @@ __global__ void __launch_bounds__(256, MINB) StepKernel(StepParams p) {
                 } else if (!(flags & kTriDegenerate)) {
                     RayConst rc = ToRayConst(ry);
                     float t, b0, b1, b2;
-                    if (TriangleTest(rc, tMax, v0.x, v0.y, v0.z, v1.x, v1.y, v1.z, v2.x, v2.y, v2.z,
-                                     &t, &b0, &b1, &b2)) {
+                    bool got;
+                    const float a = (ALPHA && (!INST || instSlot < 0)) ? __ldg(sc.alpha + prim) : 1.f;
+                    if (ALPHA && a < 1) {
+                        const RayRegs rr = LoadRay(p.in, rayIdx);  // HashFloat(r.o, r.d) and the re-trace want d
+                        rc.dx = rr.dx; rc.dy = rr.dy; rc.dz = rr.dz;
+                        const float q0[3] = {v0.x, v0.y, v0.z}, q1[3] = {v1.x, v1.y, v1.z}, q2[3] = {v2.x, v2.y, v2.z};
+                        got = AlphaTriangleTest(rc, tMax, q0, q1, q2, a, &t, &b0, &b1, &b2);
+                    } else {
+                        got = TriangleTest(rc, tMax, v0.x, v0.y, v0.z, v1.x, v1.y, v1.z, v2.x, v2.y, v2.z,
+                                           &t, &b0, &b1, &b2);
+                    }
+                    if (got) {
                         found = true;
                         hit.prim = prim;
                         if (INST) {  // inside an instance: its top-level slot + the primitive inside the object

@@ -61,10 +61,13 @@ def _rays(rng, N, sph, inst24):
     return rays
 
 
+# kernel "1": StepKernel's general instantiation (spheres + instance slots + alpha); "0": BasicKernel's
 @pytest.mark.gpu
+@pytest.mark.parametrize("kernel", ["1", "0"])
 @pytest.mark.parametrize("split", ["sah", "middle"])
-def test_one_list_with_every_primitive_kind_matches_the_reference(reference, split):
+def test_one_list_with_every_primitive_kind_matches_the_reference(reference, split, kernel, monkeypatch):
     import nn_bvh_b200 as nb
+    monkeypatch.setenv("NNBVH_INST_STEP", kernel)
     from nn_bvh_b200.aggregate import INSTANCE_DTYPE, SPHERE_DTYPE
     rng = np.random.default_rng(101)
     tris, alpha, sph, soups, inst24, inst_obj = _scene(rng)
@@ -126,9 +129,11 @@ def test_general_description_with_one_kind_takes_that_kinds_path(reference):
 
 
 @pytest.mark.gpu
-def test_general_scene_matches_the_reference_golden():
+@pytest.mark.parametrize("kernel", ["1", "0"])
+def test_general_scene_matches_the_reference_golden(kernel, monkeypatch):
     """The same claim without oracle/_ref: answers the reference produced here (tools/make_golden.py --only-general)."""
     import os
+    monkeypatch.setenv("NNBVH_INST_STEP", kernel)
     import nn_bvh_b200 as nb
     from conftest import GOLDEN
     from nn_bvh_b200.aggregate import INSTANCE_DTYPE, SPHERE_DTYPE
@@ -172,6 +177,7 @@ def test_ray_ordering_does_not_change_one_thread_per_ray_results(reference, monk
     d_inner = torch.zeros(N, dtype=torch.int32, device="cuda")
     d_occ = torch.zeros(N, dtype=torch.uint8, device="cuda")
     out = {}
+    monkeypatch.setenv("NNBVH_INST_STEP", "0")          # BasicKernel's general instantiation (one thread per ray)
     for mode in ("0", "1"):
         monkeypatch.setenv("NNBVH_BIN", mode)
         agg = nb.GPUBVHAggregate.General(spheres=spheres, instances=instances, tree=ref)
