@@ -210,7 +210,8 @@ int nnbvh_upload_scene_mixed(nnbvh_engine *e, const nnbvh_node *nodes, uint32_t 
  * A hit is ignored when alpha <= 0 or HashFloat(ray.o, ray.d) > alpha (util/hash.h:98-112), and the same
  * primitive is asked again with si->intr.SpawnRay(ray.d) and tMax - tHit, as the reference does;
  * nnbvh_intersect_any on such a scene is Intersect(...).has_value().  Image / procedural alpha textures
- * are outside this path.  Such scenes run a one-thread-per-ray kernel; per-ray counters are unavailable. */
+ * are outside this path.  Such scenes run the product kernel with the alpha test in its leaf phase
+ * (NNBVH_INST_STEP=0: a one-thread-per-ray kernel); per-ray counters are unavailable. */
 int nnbvh_upload_scene_alpha(nnbvh_engine *e, const nnbvh_node *nodes, uint32_t nNodes,
                              const float *orderedTriVerts9, const float *orderedAlpha, uint32_t nPrims);
 

@@ -568,6 +568,7 @@ extern "C" int nnbvh_upload_scene_alpha(nnbvh_engine *e, const nnbvh_node *nodes
     cudaStream_t st = e->stream;
     CU(cudaMemcpyAsync(e->store->dAlpha.p, orderedAlpha, sizeof(float) * (size_t)nPrims, cudaMemcpyHostToDevice, st));
     CU(cudaStreamSynchronize(st));
+    e->sc.alpha = e->store->dAlpha.p;
     e->hasAlpha = true;
     return NNBVH_OK;
 }
@@ -1004,6 +1005,10 @@ static void LaunchStep(nnbvh_engine *e, cudaStream_t st, const StepParams &p) {
         StepKernel<ANY, EXACT, 4, false, true><<<p.nPtr ? e->numSMs * 4 : StepGrid(e, 4, n), 256, 0, st>>>(p);
         return;
     }
+    if (e->hasAlpha) {  // constant-alpha triangles: the alpha test inside the leaf phase, 4 CTAs/SM
+        StepKernel<ANY, EXACT, 4, false, false, false, true><<<p.nPtr ? e->numSMs * 4 : StepGrid(e, 4, n), 256, 0, st>>>(p);
+        return;
+    }
     if (e->hasInstances) {  // instance slots: one instantiation, 4 CTAs/SM (the lane carries the instance state)
         StepKernel<ANY, EXACT, 4, false, false, true><<<p.nPtr ? e->numSMs * 4 : StepGrid(e, 4, n), 256, 0, st>>>(p);
         return;
@@ -1110,7 +1115,9 @@ static int LaunchTraversal(nnbvh_engine *e, cudaStream_t st, bool any, bool coun
     RayInput inO = in;
     const bool generalStepEarly = e->general && e->generalStepOK && e->instStep && !counters &&
                                   e->kernel != NNBVH_KERNEL_BASIC && e->kernel != NNBVH_KERNEL_WIDE;
-    if (((e->general && !generalStepEarly) || e->hasAlpha ||
+    const bool alphaStepEarly = e->hasAlpha && e->instStep && !counters && e->kernel != NNBVH_KERNEL_BASIC &&
+                                e->kernel != NNBVH_KERNEL_WIDE;
+    if (((e->general && !generalStepEarly) || (e->hasAlpha && !alphaStepEarly) ||
          (e->hasInstances && !(e->instStepOK && e->instStep && e->kernel != NNBVH_KERNEL_WIDE))) &&
         !counters && e->kernel != NNBVH_KERNEL_BASIC) {
         CU(cudaMemsetAsync(scr.cursor, 0, kCursorWords * sizeof(unsigned long long), st));
@@ -1132,7 +1139,9 @@ static int LaunchTraversal(nnbvh_engine *e, cudaStream_t st, bool any, bool coun
         CU(cudaGetLastError());
         return NNBVH_OK;
     }
-    if (e->hasAlpha) {  // alpha-tested primitives: one thread per ray (alpha.cuh)
+    const bool alphaStep = e->hasAlpha && e->instStep && !counters && e->kernel != NNBVH_KERNEL_BASIC &&
+                           e->kernel != NNBVH_KERNEL_WIDE;
+    if (e->hasAlpha && !alphaStep) {  // alpha-tested primitives: one thread per ray (alpha.cuh)
         if (counters)
             return SetError(NNBVH_ERR_INVALID, "per-ray counters are not available for scenes with alpha primitives");
         if (n > (uint64_t)0x7fffffff * 128)
@@ -1186,7 +1195,7 @@ static int LaunchTraversal(nnbvh_engine *e, cudaStream_t st, bool any, bool coun
         // ---- binning pre-pass: a ray order that keeps warps coherent (binning.cuh) ----
         // binMode 1: always sort; 2: the device decides per batch (the kernels read the flag); 0: off.
         const uint32_t *perm = nullptr, *permOn = nullptr;
-        const bool stepKernel = e->kernel != NNBVH_KERNEL_WIDE || e->hasSpheres || instStep;  // WideKernel: triangles only
+        const bool stepKernel = e->kernel != NNBVH_KERNEL_WIDE || e->hasSpheres || instStep || alphaStep;  // WideKernel: triangles only
         {
             // (an instanced scene's top level is small, its objects are not: no node-count floor there)
             int rc = OrderRays(e, st, in, n, scr, cursor, stepKernel, instStep ? 0u : e->binMinNodes, &perm, &permOn);

@@ -14,9 +14,12 @@ from conftest import GOLDEN, rand_rays
 MISS = 0xFFFFFFFF
 
 
+# kernel "1": StepKernel<..., ALPHA> (the alpha test inside the product kernel's leaf phase); "0": AlphaKernel
 @pytest.mark.gpu
-def test_alpha_scene_gpu_matches_reference_golden():
+@pytest.mark.parametrize("kernel", ["1", "0"])
+def test_alpha_scene_gpu_matches_reference_golden(kernel, monkeypatch):
     import nn_bvh_b200 as nb
+    monkeypatch.setenv("NNBVH_INST_STEP", kernel)
     g = np.load(os.path.join(GOLDEN, "alpha.npz"))
     order = g["order"].astype(np.uint32)
     agg = nb.GPUBVHAggregate(nodes=g["nodes"].view(nb.NODE_DTYPE).reshape(-1), ordered_tris9=g["tris"][order],
@@ -27,8 +30,10 @@ def test_alpha_scene_gpu_matches_reference_golden():
 
 
 @pytest.mark.gpu
-def test_alpha_scene_gpu_matches_oracle_at_size(oracle):
+@pytest.mark.parametrize("kernel", ["1", "0"])
+def test_alpha_scene_gpu_matches_oracle_at_size(oracle, kernel, monkeypatch):
     import nn_bvh_b200 as nb
+    monkeypatch.setenv("NNBVH_INST_STEP", kernel)
     rng = np.random.default_rng(44)
     T, N = 60_000, 400_000
     c = rng.random((T, 1, 3), dtype=np.float32)
