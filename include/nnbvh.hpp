@@ -237,6 +237,113 @@ class GPUBVHAggregate {
     const std::vector<ObjectTree> &Objects() const { return objects_; }
     const std::vector<int32_t> &OrderedInstanceIndex() const { return instanceOf_; }
 
+    // ONE primitive list with every kind the library traverses, in the CALLER's order (so the tree is the
+    // one BVHAggregate builds from the same std::vector<Primitive>): triangles, optionally with a constant
+    // alpha (GeometricPrimitive over a FloatConstantTexture, cpu/primitive.cpp:50-84), spheres, and
+    // TransformedPrimitive instances (cpu/primitive.cpp:112-130) of objects whose trees are already built --
+    // by BuildObject() below, or by the reference itself (a BVHAggregate's flattened nodes have
+    // nnbvh_node's layout; integration/pbrt/gpubvh.h hands them over as they are).
+    struct GeneralList {
+        enum Kind : uint8_t { kTriangle = 0, kSphere = 1, kInstance = 2 };
+        std::vector<uint8_t> kind;       // per caller primitive
+        std::vector<uint32_t> index;     // ... and its index in tris9 / spheres / instances
+        std::vector<float> tris9;
+        std::vector<float> alpha;        // empty, or one constant per triangle of tris9 (>= 1: no alpha test)
+        std::vector<nnbvh_sphere> spheres;
+        std::vector<nnbvh_instance> instances;
+        std::vector<ObjectTree> objects;
+    };
+    static ObjectTree BuildObject(const std::vector<float> &tris9, int maxPrimsInNode = 1,
+                                  SplitMethod splitMethod = SplitMethod::SAH, int buildThreads = 0) {
+        const uint32_t n = (uint32_t)(tris9.size() / 9);
+        ObjectTree o;
+        o.nodes.resize(2 * (size_t)std::max(n, 1u));
+        o.order.resize(n);
+        uint32_t nNodes = 0;
+        Check(nnbvh_build_bvh(tris9.data(), n, maxPrimsInNode, (int)splitMethod, buildThreads, o.nodes.data(),
+                              &nNodes, o.order.data()));
+        o.nodes.resize(nNodes);
+        o.orderedTris9.resize(9 * (size_t)n);
+        for (uint32_t i = 0; i < n; ++i)
+            for (int k = 0; k < 9; ++k) o.orderedTris9[9 * (size_t)i + k] = tris9[9 * (size_t)o.order[i] + k];
+        return o;
+    }
+    GPUBVHAggregate(GeneralList list, int maxPrimsInNode = 1, SplitMethod splitMethod = SplitMethod::SAH,
+                    int device = -1, int buildThreads = 0) {
+        const uint32_t nPrims = (uint32_t)list.kind.size();
+        const uint32_t nTris = (uint32_t)(list.tris9.size() / 9);
+        CreateEngine(device);
+        if (list.index.size() != nPrims || (!list.alpha.empty() && list.alpha.size() != nTris))
+            FailWith(NNBVH_ERR_INVALID, "GPUBVHAggregate: GeneralList arrays disagree in length");
+        if (nPrims == 0) {
+            Upload();
+            return;
+        }
+        std::vector<float> bounds(6 * (size_t)nPrims);
+        for (uint32_t i = 0; i < nPrims; ++i) {
+            float *b = &bounds[6 * (size_t)i];
+            const uint32_t k = list.index[i];
+            if (list.kind[i] == GeneralList::kTriangle) {  // Triangle::Bounds, shapes.cpp:294-301
+                if (k >= nTris) FailWith(NNBVH_ERR_INVALID, "GPUBVHAggregate: triangle index out of range");
+                const float *p = &list.tris9[9 * (size_t)k];
+                for (int a = 0; a < 3; ++a) {
+                    b[a] = std::min(std::min(p[a], p[3 + a]), p[6 + a]);
+                    b[3 + a] = std::max(std::max(p[a], p[3 + a]), p[6 + a]);
+                }
+            } else if (list.kind[i] == GeneralList::kSphere) {  // Sphere::Bounds, shapes.cpp:37-40
+                if (k >= list.spheres.size()) FailWith(NNBVH_ERR_INVALID, "GPUBVHAggregate: sphere index out of range");
+                if (int rc = nnbvh_sphere_bounds(&list.spheres[k], b)) Fail(rc);
+            } else if (list.kind[i] == GeneralList::kInstance) {  // TransformedPrimitive::Bounds, cpu/primitive.h:94
+                if (k >= list.instances.size() || list.instances[k].object >= list.objects.size() ||
+                    list.objects[list.instances[k].object].nodes.empty())
+                    FailWith(NNBVH_ERR_INVALID, "GPUBVHAggregate: instance or its object is missing");
+                if (int rc = nnbvh_instance_bounds(&list.instances[k],
+                                                   list.objects[list.instances[k].object].nodes[0].bounds, b))
+                    Fail(rc);
+            } else
+                FailWith(NNBVH_ERR_INVALID, "GPUBVHAggregate: unknown primitive kind");
+        }
+        nodes_.resize(2 * (size_t)nPrims - 1);
+        order_.resize(nPrims);
+        uint32_t nNodes = 0;
+        if (int rc = nnbvh_build_bvh_bounds(bounds.data(), nPrims, maxPrimsInNode, (int)splitMethod, buildThreads,
+                                            nodes_.data(), &nNodes, order_.data())) Fail(rc);
+        nodes_.resize(nNodes);
+        ordered_.assign(9 * (size_t)nPrims, 0.f);
+        if (!list.spheres.empty()) sphereOf_.assign(nPrims, -1);
+        if (!list.instances.empty()) instanceOf_.assign(nPrims, -1);
+        if (!list.alpha.empty()) alpha_.assign(nPrims, 1.f);
+        for (uint32_t i = 0; i < nPrims; ++i) {
+            const uint32_t src = order_[i], k = list.index[src];
+            if (list.kind[src] == GeneralList::kSphere)
+                sphereOf_[i] = (int32_t)k;
+            else if (list.kind[src] == GeneralList::kInstance)
+                instanceOf_[i] = (int32_t)k;
+            else {
+                for (int a = 0; a < 9; ++a) ordered_[9 * (size_t)i + a] = list.tris9[9 * (size_t)k + a];
+                if (!alpha_.empty()) alpha_[i] = list.alpha[k];
+            }
+        }
+        spheres_ = std::move(list.spheres);
+        instances_ = std::move(list.instances);
+        objects_ = std::move(list.objects);
+        std::vector<nnbvh_object> objs(objects_.size());
+        for (size_t j = 0; j < objects_.size(); ++j)
+            objs[j] = nnbvh_object{objects_[j].nodes.data(), (uint32_t)objects_[j].nodes.size(),
+                                   objects_[j].orderedTris9.data(), (uint32_t)(objects_[j].orderedTris9.size() / 9)};
+        nnbvh_scene_desc d{};
+        d.nodes = nodes_.data(), d.nNodes = (uint32_t)nodes_.size();
+        d.orderedTriVerts9 = ordered_.data(), d.nPrims = nPrims;
+        d.orderedSphereIndex = sphereOf_.empty() ? nullptr : sphereOf_.data();
+        d.spheres = spheres_.data(), d.nSpheres = (uint32_t)spheres_.size();
+        d.orderedInstanceIndex = instanceOf_.empty() ? nullptr : instanceOf_.data();
+        d.instances = instances_.data(), d.nInstances = (uint32_t)instances_.size();
+        d.objects = objs.data(), d.nObjects = instances_.empty() ? 0u : (uint32_t)objs.size();
+        d.orderedAlpha = alpha_.empty() ? nullptr : alpha_.data();
+        if (int rc = nnbvh_upload_scene_general(e_, &d)) Fail(rc);
+    }
+    bool HasInstances() const { return !instances_.empty(); }
+
     // A ready flattened tree (e.g. an NN-split tree exported in LinearBVHNode layout).
     GPUBVHAggregate(std::vector<nnbvh_node> nodes, std::vector<float> orderedTris9,
                     std::vector<uint32_t> order = {}, int device = -1)
@@ -330,7 +437,7 @@ class GPUBVHAggregate {
     struct CloneTag {};
     GPUBVHAggregate(CloneTag, const GPUBVHAggregate &o)
         : nodes_(o.nodes_), ordered_(o.ordered_), order_(o.order_), sphereOf_(o.sphereOf_), spheres_(o.spheres_),
-          instanceOf_(o.instanceOf_), instances_(o.instances_), objects_(o.objects_) {
+          instanceOf_(o.instanceOf_), instances_(o.instances_), objects_(o.objects_), alpha_(o.alpha_) {
         Check(nnbvh_clone(o.e_, &e_));
     }
     void CreateEngine(int device) {
@@ -373,6 +480,7 @@ class GPUBVHAggregate {
     std::vector<int32_t> instanceOf_;     // per ordered top-level primitive: -1 triangle, else instance index
     std::vector<nnbvh_instance> instances_;
     std::vector<ObjectTree> objects_;
+    std::vector<float> alpha_;            // per ordered primitive: the constant alpha (general lists), or empty
     nnbvh_engine *e_ = nullptr;
 };
 

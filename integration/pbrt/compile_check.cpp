@@ -1,6 +1,6 @@
 // integration/pbrt/compile_check.cpp -- type-checks gpubvh.h and gpubvh_wavefront.h against the reference's real headers
 // (tests/test_integration_compile.py; -fsyntax-only).  The friend declarations the adapter needs are
-// replaced here by opening the three classes' private sections.
+// replaced here by opening the classes' private sections.
 #include <algorithm>
 #include <atomic>
 #include <cstdint>
@@ -14,6 +14,7 @@
 #include <vector>
 #define private public
 #include <pbrt/pbrt.h>
+#include <pbrt/cpu/aggregates.h>
 #include <pbrt/cpu/primitive.h>
 #include <pbrt/shapes.h>
 #undef private

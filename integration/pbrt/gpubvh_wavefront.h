@@ -43,7 +43,7 @@ class GPUBVHWavefrontAggregate : public WavefrontAggregate {
     // prims: the list CPUAggregate would hand to CreateAccelerator (cpu/aggregates.cpp:1163-1178).
     GPUBVHWavefrontAggregate(std::vector<Primitive> prims, int maxPrimsInNode,
                              BVHAggregate::SplitMethod splitMethod, int maxQueueSize, int device = -1)
-        : host(std::move(prims), maxPrimsInNode, splitMethod, device), hits(maxQueueSize), occluded(maxQueueSize) {}
+        : host(std::move(prims), maxPrimsInNode, splitMethod, device), hits(maxQueueSize), inner(maxQueueSize, NNBVH_MISS), occluded(maxQueueSize) {}
 
     Bounds3f Bounds() const override { return host.Bounds(); }
 
@@ -57,15 +57,15 @@ class GPUBVHWavefrontAggregate : public WavefrontAggregate {
             return;
         CHECK_LE((size_t)n, hits.size());  // the queues are allocated for maxQueueSize
         // SOA<RayWorkItem> keeps ray.o.x[], ray.o.y[] ... as separate float arrays: no repack
-        host.Engine().IntersectBatchSoA(rayQ->ray.o.x, rayQ->ray.o.y, rayQ->ray.o.z, rayQ->ray.d.x, rayQ->ray.d.y,
-                               rayQ->ray.d.z, /*tMax=*/nullptr, (uint64_t)n, hits.data());
+        host.IntersectBatchSoA(rayQ->ray.o.x, rayQ->ray.o.y, rayQ->ray.o.z, rayQ->ray.d.x, rayQ->ray.d.y,
+                               rayQ->ray.d.z, /*tMax=*/nullptr, (uint64_t)n, hits.data(), inner.data());
         ParallelFor(0, n, [=](int index) {
             const RayWorkItem r = (*rayQ)[index];
             const nnbvh_hit &h = hits[index];
             if (h.prim == NNBVH_MISS)
                 EnqueueWorkAfterMiss(r, mediumSampleQ, escapedRayQ);
             else {
-                ShapeIntersection si = host.Resolve(h, r.ray);
+                ShapeIntersection si = host.Resolve(h, inner[index], r.ray);
                 EnqueueWorkAfterIntersection(r, r.ray.medium, si.tHit, si.intr, mediumSampleQ, nextRayQ,
                                              hitAreaLightQ, basicMtlQ, universalMtlQ);
             }
@@ -106,6 +106,7 @@ class GPUBVHWavefrontAggregate : public WavefrontAggregate {
             return;
         struct Walk {
             std::vector<nnbvh_hit> known;  // hits of the segments traced so far, in walk order
+            std::vector<uint32_t> knownInner;  // ... and the primitive inside the object, for instance hits
             nnbvh_ray query;               // the next segment, when the last replay stopped for it
             bool done = false;
         };
@@ -115,6 +116,7 @@ class GPUBVHWavefrontAggregate : public WavefrontAggregate {
             live[i] = i;
         std::vector<nnbvh_ray> rays;
         std::vector<nnbvh_hit> segHits;
+        std::vector<uint32_t> segInner;
         lastTrBatches = 0;
         while (!live.empty()) {
             const int m = (int)live.size();
@@ -125,10 +127,11 @@ class GPUBVHWavefrontAggregate : public WavefrontAggregate {
                 pstd::optional<ShapeIntersection> last;  // the surface the walk currently stands on
                 auto trace = [&](Ray ray, Float tMax) {
                     if (asked < w.known.size()) {
-                        const nnbvh_hit &h = w.known[asked++];
+                        const nnbvh_hit &h = w.known[asked];
+                        const uint32_t in = w.knownInner[asked++];
                         last.reset();
                         if (h.prim != NNBVH_MISS)
-                            last = host.Resolve(h, ray);
+                            last = host.Resolve(h, in, ray);
                         return TransmittanceTraceResult{last.has_value(), last ? last->intr.p() : Point3f(),
                                                         last ? last->intr.material : Material()};
                     }
@@ -152,10 +155,13 @@ class GPUBVHWavefrontAggregate : public WavefrontAggregate {
             segHits.resize(live.size());
             for (size_t j = 0; j < live.size(); ++j)
                 rays[j] = walks[live[j]].query;
-            host.Engine().IntersectBatch(rays.data(), (uint64_t)rays.size(), segHits.data());
+            segInner.assign(live.size(), NNBVH_MISS);
+            host.IntersectBatch(rays.data(), (uint64_t)rays.size(), segHits.data(), segInner.data());
             ++lastTrBatches;
-            for (size_t j = 0; j < live.size(); ++j)
+            for (size_t j = 0; j < live.size(); ++j) {
                 walks[live[j]].known.push_back(segHits[j]);
+                walks[live[j]].knownInner.push_back(segInner[j]);
+            }
         }
     }
 
@@ -186,6 +192,7 @@ class GPUBVHWavefrontAggregate : public WavefrontAggregate {
             live[i] = i;
         std::vector<nnbvh_ray> rays;
         std::vector<nnbvh_hit> segHits;
+        std::vector<uint32_t> segInner;
         lastOneRandomBatches = 0;
         while (true) {
             // the next segment of every live probe (`if (r.d == 0) break`, aggregate.cpp:104-106)
@@ -208,7 +215,8 @@ class GPUBVHWavefrontAggregate : public WavefrontAggregate {
                 const Ray &r = probes[live[j]].segment;
                 rays[j] = nnbvh_ray{r.o.x, r.o.y, r.o.z, 1.f, r.d.x, r.d.y, r.d.z, r.time};
             }
-            host.Engine().IntersectBatch(rays.data(), (uint64_t)rays.size(), segHits.data());
+            segInner.assign(live.size(), NNBVH_MISS);
+            host.IntersectBatch(rays.data(), (uint64_t)rays.size(), segHits.data(), segInner.data());
             ++lastOneRandomBatches;
             ParallelFor(0, (int64_t)live.size(), [&](int64_t j) {
                 Probe &p = probes[live[j]];
@@ -216,7 +224,7 @@ class GPUBVHWavefrontAggregate : public WavefrontAggregate {
                     p.live = false;
                     return;
                 }
-                ShapeIntersection si = host.Resolve(segHits[j], p.segment);
+                ShapeIntersection si = host.Resolve(segHits[j], segInner[j], p.segment);
                 p.from = si.intr;
                 if (si.intr.material == Material(q->material[live[j]]))
                     p.reservoir.Add(SubsurfaceInteraction(si.intr), 1.f);
@@ -251,6 +259,7 @@ class GPUBVHWavefrontAggregate : public WavefrontAggregate {
     // One call of this aggregate is in flight at a time (the wavefront render loop is sequential,
     // wavefront/integrator.cpp); the batch buffers and counters below rely on it.
     mutable std::vector<nnbvh_hit> hits;
+    mutable std::vector<uint32_t> inner;  // primitive inside the object, for hits on instances
     mutable std::vector<uint8_t> occluded;
     mutable int lastTrBatches = 0, lastOneRandomBatches = 0;
 };

@@ -384,6 +384,11 @@ class Reference:
                               obj_tris=np.ascontiguousarray(np.concatenate(obj_tris)),
                               obj_prim_base=np.array(pbase[:-1], dtype=np.int32)))
 
+    def tag_materials(self, on: bool):
+        """Scenes created while off hold null materials only (needed by the wavefront queue harnesses); the
+        intersect_* calls that name the primitive hit need the tags."""
+        self.lib.nnbvh_ref_tag_materials(int(on))
+
     def scene_general(self, tris9, alpha, spheres28, obj_soups, inst24, inst_object, max_prims: int = 4,
                       split: str = "sah"):
         """BVHAggregate over ONE list: triangles (GeometricPrimitive with constant alpha where alpha < 1), then

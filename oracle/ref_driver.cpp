@@ -90,7 +90,10 @@ RefSphere *MakeSphere(const float *s28) {
 }
 // SimplePrimitive::Intersect copies its Material handle into the interaction without looking at it
 // (cpu/primitive.cpp:105-108): a fake pointer value carries the primitive's index through.
+bool g_tagMaterials = true;  // nnbvh_ref_tag_materials(0): null materials instead, for the queue harnesses below
 pbrt::Material TagMaterial(int index) {
+    if (!g_tagMaterials)
+        return pbrt::Material(nullptr);
     return pbrt::Material((pbrt::DiffuseMaterial *)(uintptr_t)(16 * (uintptr_t)(index + 1)));
 }
 int TagOf(pbrt::Material m) {
@@ -603,6 +606,11 @@ void nnbvh_ref_intersect_instanced(void *scene, const float *rays, int64_t n, ui
 // else SimplePrimitive), spheres nTris..nTris+nSpheres-1 (SimplePrimitive, tagged), instances after them
 // (TransformedPrimitive over per-object BVHAggregates whose triangles carry the object's tag).
 constexpr int kObjectTagBase = 1 << 24;
+// Scenes created while this is off carry null materials everywhere (EnqueueWorkAfterIntersection's `!material`
+// branch, wavefront/intersect.h:101-109, must not meet a tag); nnbvh_ref_intersect* cannot name the primitive
+// hit in such a scene, nnbvh_ref_intersect_surface and the queue harnesses can be used.
+void nnbvh_ref_tag_materials(int on) { g_tagMaterials = on != 0; }
+
 void *nnbvh_ref_scene_create_general(const float *tris9, int nTris, const float *alpha, const float *spheres28,
                                      int nSpheres, const float *objTris9, const int *objStart, int nObjects,
                                      const float *inst24, const int *instObject, int nInstances,
@@ -1051,12 +1059,13 @@ int nnbvh_binding_intersect_surface_batch(void *binding, const float *rays, int6
     const pbrt::GPUBVHAggregate *b = (const pbrt::GPUBVHAggregate *)binding;
     try {
         std::vector<nnbvh_hit> hits((size_t)n);
-        b->Engine().IntersectBatch(reinterpret_cast<const nnbvh_ray *>(rays), (uint64_t)n, hits.data());
+        std::vector<uint32_t> inner((size_t)n, NNBVH_MISS);
+        b->IntersectBatch(reinterpret_cast<const nnbvh_ray *>(rays), (uint64_t)n, hits.data(), inner.data());
         for (int64_t i = 0; i < n; ++i) {
             hit[i] = hits[i].prim != NNBVH_MISS;
             if (!hit[i])
                 continue;
-            pbrt::ShapeIntersection si = b->Resolve(hits[i], MakeRay(rays + 8 * i));
+            pbrt::ShapeIntersection si = b->Resolve(hits[i], inner[i], MakeRay(rays + 8 * i));
             tHit[i] = si.tHit;
             PutSurface42(si.intr, out42 + 42 * i);
         }

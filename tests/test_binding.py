@@ -195,3 +195,49 @@ def test_batched_shadow_tr_and_one_random_match_the_reference_loops():
     finally:
         b.destroy(bb)
         b.set_threads(1)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("split", ["sah", "middle"])
+def test_binding_over_one_list_with_every_primitive_kind(binding, split):
+    """pbrt::GPUBVHAggregate over the list the reference's general scene holds: SimplePrimitive over Triangle and
+    Sphere, GeometricPrimitive with a constant alpha, TransformedPrimitive over per-object BVHAggregates (whose
+    flattened trees go to the device as the reference built them).  Every ShapeIntersection -- for an instance the
+    object-space interaction carried back by renderFromPrimitive, cpu/primitive.cpp:112-130 -- IntersectP and the
+    wavefront subclass's IntersectClosest over the reference's queues must equal the reference's."""
+    from test_general_scene import _rays, _scene as general_scene
+    rng = np.random.default_rng(83)
+    tris, alpha, sph, soups, inst24, inst_obj = general_scene(rng)
+    binding.tag_materials(False)        # null materials: the queue harness takes EnqueueWorkAfterIntersection's !material branch
+    try:
+        sc = binding.scene_general(tris, alpha, sph, soups, inst24, inst_obj, 4, split)["handle"]
+    finally:
+        binding.tag_materials(True)
+    b = binding.create(sc, 4, split)
+    try:
+        N = 60_000
+        rays = _rays(rng, N, sph, inst24)
+        rays[:, 7] = rng.random(N)
+        whit, wt, w42 = binding.intersect_surface(sc, rays)                   # BVHAggregate::Intersect
+        assert 0.2 * N < whit.sum() < 0.9 * N
+        ghit, gt, g42 = binding.surface(b, rays, batch=True)                  # one batch + Resolve per hit
+        assert np.array_equal(ghit, whit)
+        assert np.array_equal(gt.view(np.uint32)[whit], wt.view(np.uint32)[whit])
+        bad = np.argwhere(g42.view(np.uint32)[whit] != w42.view(np.uint32)[whit])
+        assert bad.size == 0, f"{len(bad)} words differ, first {bad[0]}"
+        n1 = 1500                                                             # Primitive's single-ray surface
+        shit, st, s42 = binding.surface(b, rays[N // 4:N // 4 + n1], batch=False)      # rays aimed at instances
+        assert np.array_equal(shit, whit[N // 4:N // 4 + n1])
+        assert np.array_equal(s42.view(np.uint32)[shit], w42.view(np.uint32)[N // 4:N // 4 + n1][shit])
+        assert np.array_equal(binding.intersect_p_binding(b, rays[-n1:]),
+                              binding.intersect_p(sc, rays[-n1:], parallel=False))
+        nodes, _ = binding.export(sc, len(tris) + len(sph) + len(inst24))
+        assert np.array_equal(binding.bounds(b).view(np.uint32), nodes[0, :6])
+        sub = rays[:20_000].copy()
+        sub[:, 3] = np.inf                                                    # the queues carry no tMax
+        want_kind, want_next = binding.wavefront_closest(sc, sub, use_binding=False, split=split)
+        kind, nxt = binding.wavefront_closest(sc, sub, use_binding=True, split=split)
+        assert np.array_equal(kind, want_kind) and (kind == 1).sum() > 4000
+        assert np.array_equal(nxt.view(np.uint32)[kind == 1], want_next.view(np.uint32)[kind == 1])
+    finally:
+        binding.destroy(b)
