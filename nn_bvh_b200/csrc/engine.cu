@@ -185,7 +185,6 @@ struct nnbvh_engine {
     unsigned long long *dStats = nullptr;
     int instStep = 1;        // instanced scenes: 1 = StepKernel<..., INST>, 0 = the one-thread-per-ray BasicKernel
     int gridRaysPerLane = 0; // StepKernel: shrink the persistent grid for small batches (StepGrid); 0 = never
-    int popLoop = 1;         // StepKernel: discard culled stack entries inside the pop
     int sphereQuorum = 12;   // StepKernel with sphere leaves: lanes waiting at spheres before their tests run
     int chunkRamp = 1;       // host-pointer pipeline: small chunks at both ends of a call (RunBatch)
     uint64_t chunkRays = 1u << 19;
@@ -258,7 +257,6 @@ extern "C" int nnbvh_create(const nnbvh_options *opts, nnbvh_engine **out) {
     e->wideMinB = EnvInt("NNBVH_WIDE_MINB", e->wideMinB);
     e->refillBelow = EnvInt("NNBVH_REFILL_BELOW", e->refillBelow);
     e->leafQuorum = EnvInt("NNBVH_LEAF_QUORUM", e->leafQuorum);
-    e->popLoop = EnvInt("NNBVH_POP_LOOP", e->popLoop);
     e->gridRaysPerLane = EnvInt("NNBVH_GRID_RAYS_PER_LANE", e->gridRaysPerLane);
     e->instStep = EnvInt("NNBVH_INST_STEP", e->instStep);
     e->sphereQuorum = EnvInt("NNBVH_SPHERE_QUORUM", e->sphereQuorum);
@@ -497,7 +495,7 @@ static int BuildWideLayout(const std::vector<nnbvh_node> &nodes, uint32_t nPrims
         w.ref0 = refOf(i + 1);
         w.ref1 = refOf((uint32_t)nodes[i].offset);
         w.axis = nodes[i].axis;
-        w.pad = 0;
+        w.axisBit = 1 << nodes[i].axis;
     }
     *rootRef = refOf(0);
     return NNBVH_OK;
@@ -1215,7 +1213,6 @@ static int LaunchTraversal(nnbvh_engine *e, cudaStream_t st, bool any, bool coun
             sp.perm = perm;
             sp.permOn = permOn;
             StepKnobs(e, &sp.refillBelow, &sp.leafQuorum);
-            sp.popLoop = (uint32_t)(e->popLoop != 0);
             sp.sphereQuorum = (uint32_t)std::min(32, std::max(1, e->sphereQuorum));
             if (e->stepStats) {
                 if (!e->dStats) {
@@ -1984,7 +1981,6 @@ extern "C" int nnbvh_intersect_closest_noalloc(nnbvh_engine *e, const nnbvh_ray 
     sp.n = n;
     sp.hits = hitsDev;
     StepKnobs(e, &sp.refillBelow, &sp.leafQuorum);
-    sp.popLoop = (uint32_t)(e->popLoop != 0);
     sp.sphereQuorum = (uint32_t)std::min(32, std::max(1, e->sphereQuorum));
     if (e->boxesRegular && !e->exactOnly) {  // fast-slab launch; rays it cannot take go to the deferred list
         sp.cursor = cursor;

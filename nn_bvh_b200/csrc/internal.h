@@ -29,7 +29,7 @@ struct alignas(64) WideNode {
     float lo1[3], hi1[3];  // child 1 box
     int32_t ref0, ref1;
     int32_t axis;
-    int32_t pad;
+    int32_t axisBit;  // 1 << axis: StepKernel's near/far choice is one AND with the ray's sign bits
 };
 static_assert(sizeof(WideNode) == 64, "WideNode must be 64 bytes");
 

@@ -6,13 +6,14 @@
 // lanes active, L1 at 75 %).
 //
 //  * Persistent warps pull rays from a global cursor; finished lanes are refilled.
-//  * Every lane carries (cur, curT): the node or leaf it is AT and the box-entry distance
-//    that was computed when its parent was fetched.  `curT < tMax` -- the only part of
-//    Bounds3f::IntersectP that depends on the shrinking tMax (util/vecmath.h:1607) -- is
-//    evaluated when the lane steps onto `cur`, which is the moment the reference tests it.
-//  * One step per lane per iteration, straight-line: a lane whose entry fails the test, or
-//    whose node has no passing child, pops ONE entry and re-validates next iteration, so no
-//    lane ever loops while its 31 neighbours wait.
+//  * Every lane carries `cur`, the node or leaf it is AT.  Both boxes of a node are tested when the node
+//    is fetched; `tEntry < tMax` -- the only part of Bounds3f::IntersectP that depends on the shrinking
+//    tMax (util/vecmath.h:1607) -- is evaluated at the moment the lane steps onto a child: at once for
+//    the child it descends to, at the pop for the stacked one (the entry carries its tEntry), which is
+//    the moment the reference tests it.  tMax only changes while the lane is parked at a leaf, so a lane
+//    at a node never has to look at it again.
+//  * One step per lane per iteration, straight-line: a lane whose node has no passing child pops ONE
+//    entry with a predicated load; entries that fail the test (rare) are dropped in a side arm.
 //  * A 64-byte node is fetched with two 256-bit loads (LDG.E.ENL2.256): half the L1
 //    wavefronts of four LDG.128.
 //  * Fast slab (EXACT=false): for rays whose invDir is finite and non-zero and whose origin
@@ -61,7 +62,6 @@ struct StepParams {
     uint32_t *deferred;           // EXACT=false: indices of rays needing the exact slab test
     uint32_t *nDeferred;
     uint32_t refillBelow, leafQuorum;
-    uint32_t popLoop;             // 1: discard culled stack entries inside the pop (default)
     uint32_t sphereQuorum;        // SPHERES: run the sphere tests when this many lanes wait at sphere slots
     unsigned long long *stats;    // STATS instantiation only: 8 lane-occupancy counters
     uint32_t *inner;              // INST, closest hit: optional plane, ordered primitive inside the hit object
@@ -132,16 +132,17 @@ __global__ void __launch_bounds__(256, MINB) StepKernel(StepParams p) {
     const uint32_t *__restrict__ perm = (p.perm && (!p.permOn || __ldg(p.permOn))) ? p.perm : nullptr;
 
     uint32_t rayIdx = 0;
-    bool alive = false;
     StepRay ry{};
     float tMax = 0.f;
     HitRegs hit{NNBVH_MISS, 0.f, 0.f, 0.f, 0.f};
-    int cur = 0, sp = 0;
-    float curT = 0.f;
+    // kDead: the lane has no ray.  A lane is at an interior node when cur >= 0 and parked at a leaf slot when
+    // cur < kDead (bit 31 + the ordered primitive, which is never 0x7fffffff): one compare each, no flag to carry.
+    constexpr int kDead = -1;
+    int cur = kDead, sp = 0;
     // stack entry = {ref, tEntry} packed into 64 bits (one STL.64 / LDL.64 per push / pop).
     // ANY: IntersectP never shrinks tMax (aggregates.cpp:581-624), so `tMin < raytMax` of a child can be
     // settled for good when its parent is fetched: only children that pass it are entered or stacked, the
-    // entry is the bare 32-bit ref, nothing is re-validated at a pop and no lane carries curT.
+    // entry is the bare 32-bit ref and nothing is re-validated at a pop.
     typename StackWord<ANY>::type stack[kMaxStack];
     bool exhausted = false;
     // SPHERES: a lane that steps onto a sphere slot waits (sphWait) until `sphereQuorum` lanes of its warp
@@ -172,11 +173,58 @@ __global__ void __launch_bounds__(256, MINB) StepKernel(StepParams p) {
         ry.neg = (unsigned)rc.negx | ((unsigned)rc.negy << 1) | ((unsigned)rc.negz << 2);
     };
     auto finish = [&]() {  // the ray is done: its record goes out
-        alive = false;
+        cur = kDead;
         if (ANY) p.occluded[rayIdx] = 0;
         else {
             StoreHit(p.hits, rayIdx, hit);
             if (INST && p.inner) p.inner[rayIdx] = hit.inner;
+        }
+    };
+    // The pop of both phases (aggregates.cpp:556-558, :570-574) for the lanes that `want` it.  Closest hit: ONE
+    // predicated load in the straight line, not a branch -- as a branch it ran with ~4 lanes per warp after every
+    // node step and, with its reconvergence, was 14 % of the kernel's issued instructions (profiles/r02q,
+    // 0x21f0-0x2470 and 0x4930-0x4a30 of StepKernel<0,0,5>).  An entry whose box test fails against the current
+    // tMax (`tEntry < tMax` false: the reference pops those one by one with the same outcome) and the end of the
+    // ray are the rare arm.  Any hit keeps the branch: its entries are bare refs, nothing is re-validated, and the
+    // predicated form measured 2 % slower there (profiles/r02_experiments.txt).
+    auto popOne = [&](const bool want) {
+        if (ANY) {
+            if (want) {
+                if (sp > 0) {
+                    --sp;
+                    cur = (int)(unsigned)stack[sp];
+                } else {
+                    cur = kDead;
+                    p.occluded[rayIdx] = 0;
+                }
+            }
+            return;
+        }
+        const bool pop = want && sp > 0;
+        float tEntry = 0.f;
+        // `if (pop) { e = stack[--sp]; ... }` compiles to a branch around the load; as a predicated ld.local the
+        // registers simply keep their values in the other lanes.  entry = {ref (low word), tEntry bits (high word)}
+#pragma nv_diag_suppress 549  // `stack` is written before any pop can happen (sp > 0)
+        const size_t top = __cvta_generic_to_local(&stack[sp - 1]);  // not dereferenced unless pop
+#pragma nv_diag_default 549
+        asm volatile("{\n .reg .pred q;\n setp.ne.s32 q, %3, 0;\n @q ld.local.v2.b32 {%0, %1}, [%2];\n}"
+                     : "+r"(cur), "+f"(tEntry) : "l"(top), "r"((int)pop) : "memory");
+        sp -= pop ? 1 : 0;
+        if ((want && !pop) || (pop && !(tEntry < tMax))) {
+            bool got = false;
+            while (sp > 0) {
+                --sp;
+                const unsigned long long e = (unsigned long long)stack[sp];
+                cur = (int)(unsigned)e;
+                if (__uint_as_float((unsigned)(e >> 32)) < tMax) {
+                    got = true;
+                    break;
+                }
+            }
+            if (!got) {
+                cur = kDead;
+                StoreHit(p.hits, rayIdx, hit);
+            }
         }
     };
     // INST: the pop of both phases.  Entries above spBase are the current level's; with none left inside an instance
@@ -196,8 +244,7 @@ __global__ void __launch_bounds__(256, MINB) StepKernel(StepParams p) {
                     --sp;
                     const unsigned long long e = (unsigned long long)stack[sp];
                     cur = (int)(unsigned)e;
-                    curT = __uint_as_float((unsigned)(e >> 32));
-                    if (curT < tMax || !p.popLoop) {
+                    if (__uint_as_float((unsigned)(e >> 32)) < tMax) {
                         got = true;
                         break;
                     }
@@ -220,7 +267,6 @@ __global__ void __launch_bounds__(256, MINB) StepKernel(StepParams p) {
             instHit = false;
             if (outerNext != kPopMark) {
                 cur = outerNext;  // the next primitive of the outer leaf: no box test again
-                if (!ANY) curT = kNegInf;
                 return;
             }
         }
@@ -228,7 +274,7 @@ __global__ void __launch_bounds__(256, MINB) StepKernel(StepParams p) {
 
     while (true) {
         // ---- refill: finished lanes take the next rays from the global cursor ----
-        unsigned liveMask = __ballot_sync(0xffffffffu, alive);
+        unsigned liveMask = __ballot_sync(0xffffffffu, cur != kDead);
         if (!exhausted && (unsigned)__popc(liveMask) < p.refillBelow) {
             unsigned want = ~liveMask;
             unsigned nWant = __popc(want);
@@ -247,7 +293,7 @@ __global__ void __launch_bounds__(256, MINB) StepKernel(StepParams p) {
                     asm volatile("prefetch.global.L2 [%0];" ::"l"(p.in.aos + 2 * (size_t)ia));
                 }
             }
-            if (!alive) {
+            if (cur == kDead) {
                 uint64_t j = base + __popc(want & ((1u << lane) - 1));
                 if (j < nRays) {
                     uint32_t idx = perm ? __ldg(perm + j) : (uint32_t)j;
@@ -294,8 +340,6 @@ __global__ void __launch_bounds__(256, MINB) StepKernel(StepParams p) {
                         }
                         if (rootOk && tRoot < tMax) {
                             cur = sc.rootRef;
-                            curT = tRoot;
-                            alive = true;
                         } else if (ANY) p.occluded[idx] = 0;
                         else {
                             StoreHit(p.hits, idx, hit);
@@ -304,7 +348,7 @@ __global__ void __launch_bounds__(256, MINB) StepKernel(StepParams p) {
                     }
                 }
             }
-            liveMask = __ballot_sync(0xffffffffu, alive);
+            liveMask = __ballot_sync(0xffffffffu, cur != kDead);
         }
         if (liveMask == 0) {
             if (exhausted) break;
@@ -313,9 +357,9 @@ __global__ void __launch_bounds__(256, MINB) StepKernel(StepParams p) {
 
         // ---- phase A: interior nodes, one step per lane per iteration ----
         while (true) {
-            const bool atNode = alive && cur >= 0;
+            const bool atNode = cur >= 0;
             const unsigned nodeMask = __ballot_sync(0xffffffffu, atNode);
-            const unsigned leafMask = __ballot_sync(0xffffffffu, alive && cur < 0 && !(SPHERES && sphWait));
+            const unsigned leafMask = __ballot_sync(0xffffffffu, cur < kDead && !(SPHERES && sphWait));
             if (nodeMask == 0 || (unsigned)__popc(leafMask) >= leafQuorum) break;
             // NNBVH_SPC node steps between two looks at the leaf quorum: the two ballots, the popc
             // and the compares were 7 % of the issued instructions at one step per look.  A lane that
@@ -323,33 +367,33 @@ __global__ void __launch_bounds__(256, MINB) StepKernel(StepParams p) {
 #pragma unroll
             for (int u = 0; u < NNBVH_SPC; ++u) {
             if (STATS) {  // per node step, not per look
-                const unsigned nm = __ballot_sync(0xffffffffu, alive && cur >= 0);
-                const unsigned lm = __ballot_sync(0xffffffffu, alive && cur < 0);
+                const unsigned nm = __ballot_sync(0xffffffffu, cur >= 0);
+                const unsigned lm = __ballot_sync(0xffffffffu, cur < kDead);
                 st[0] += 1;
                 st[1] += __popc(nm);
                 st[2] += __popc(lm);
                 st[3] += 32 - __popc(nm | lm);
             }
-            if (alive && cur >= 0) {
+            if (cur >= 0) {
                 // `descend`: the lane moves to a child of `cur`; otherwise it pops.  The child selection is
                 // written with selects and ONE predicated push, not as the reference's if / else-if chain:
                 // lanes of a warp take different arms at almost every node, and as branches the arms ran
                 // one after the other with 3-10 lanes each -- a third of the node step's issue slots
                 // (profiles/r02c, 0x2190-0x24c0 of StepKernel<0,0,5>).
                 bool descend = false;
-                if (ANY || curT < tMax) {  // the reference's `tMin < raytMax` for this node, made now
+                {
                     const unsigned char *np = wideBase + (size_t)(unsigned)cur * sizeof(WideNode);
                     const F8 a = Ldg256(np), b = Ldg256(np + 32);
-                    // WideNode: lo0 xyz, hi0 xyz, lo1 xy | lo1 z, hi1 xyz, ref0, ref1, axis, pad
+                    // WideNode: lo0 xyz, hi0 xyz, lo1 xy | lo1 z, hi1 xyz, ref0, ref1, axis, 1 << axis
                     const int ref0 = __float_as_int(b.v[4]), ref1 = __float_as_int(b.v[5]);
-                    const unsigned axis = __float_as_uint(b.v[6]);
+                    const unsigned axisBit = __float_as_uint(b.v[7]);  // 1 << axis
                     // aggregates.cpp:561.  IntersectP's answer does not depend on the visit order (no tMax update,
                     // any accepted primitive ends the ray): NNBVH_ANY_ORDER 0 = child 0 first, 2 = the child whose
                     // box is entered first (smaller tEntry), 1 = the reference's order (default).
 #if NNBVH_ANY_ORDER == 0
-                    const bool secondFirst = ANY ? false : (bool)((ry.neg >> axis) & 1u);
+                    const bool secondFirst = ANY ? false : (ry.neg & axisBit) != 0;
 #else
-                    const bool secondFirst = (ry.neg >> axis) & 1u;
+                    const bool secondFirst = (ry.neg & axisBit) != 0;
 #endif
                     const int refNear = secondFirst ? ref1 : ref0, refFar = secondFirst ? ref0 : ref1;
                     float tNear, tFar;
@@ -407,45 +451,17 @@ __global__ void __launch_bounds__(256, MINB) StepKernel(StepParams p) {
                     // near child if it passes (tNear < tMax already established: next step passes), else the
                     // far child if it does (aggregates.cpp:560-569); with neither, the values are dead
                     cur = goNear ? refNear : (goFar ? refFar : cur);
-                    if (!ANY) curT = goNear ? tNear : tFar;
                     descend = goNear || goFar;
                 }
                 if (INST && !descend) {
                     popInst();
-                } else if (!descend) {
-                    // aggregates.cpp:570-574.  Entries whose box test fails against the current tMax
-                    // (`curT < tMax` false) are discarded here rather than one per iteration: the
-                    // reference pops them one by one with the same outcome, and tMax cannot change
-                    // between this pop and the lane's next step.
-                    bool got = false;
-                    if (ANY) {
-                        if (sp > 0) {
-                            --sp;
-                            cur = (int)(unsigned)stack[sp];
-                            got = true;
-                        }
-                    } else {
-                        while (sp > 0) {
-                            --sp;
-                            const unsigned long long e = stack[sp];
-                            cur = (int)(unsigned)e;
-                            curT = __uint_as_float((unsigned)(e >> 32));
-                            if (curT < tMax || !p.popLoop) {
-                                got = true;
-                                break;
-                            }
-                        }
-                    }
-                    if (!got) {
-                        alive = false;
-                        if (ANY) p.occluded[rayIdx] = 0;
-                        else StoreHit(p.hits, rayIdx, hit);
-                    }
+                } else {
+                    popOne(!descend);
                 }
 #if NNBVH_PREFETCH_TRI
                 // the lane has just stepped onto a leaf: it will wait there for the quorum, and its first triangle
                 // can travel to the L1 meanwhile
-                if (alive && cur < 0) {
+                if (cur < kDead) {
                     const float4 *tp = tris + 3 * (size_t)((uint32_t)cur & 0x7fffffffu);
                     asm volatile("prefetch.global.L1 [%0];" ::"l"(tp));
 #if NNBVH_PREFETCH_TRI > 1
@@ -459,8 +475,8 @@ __global__ void __launch_bounds__(256, MINB) StepKernel(StepParams p) {
 
         // ---- phase B: every parked lane tests ONE triangle of its leaf ----
         if (STATS) {
-            const unsigned parked = __ballot_sync(0xffffffffu, alive && cur < 0);
-            const unsigned testing = __ballot_sync(0xffffffffu, alive && cur < 0 && (ANY || curT < tMax));
+            const unsigned parked = __ballot_sync(0xffffffffu, cur < kDead);
+            const unsigned testing = parked;
             st[4] += 1;
             st[5] += __popc(parked);
             st[6] += __popc(testing);
@@ -469,14 +485,13 @@ __global__ void __launch_bounds__(256, MINB) StepKernel(StepParams p) {
         if (SPHERES) {
             const unsigned sphMask = __ballot_sync(0xffffffffu, sphWait);
             if (sphMask) {
-                const unsigned other = __ballot_sync(0xffffffffu, alive && !sphWait);
+                const unsigned other = __ballot_sync(0xffffffffu, cur != kDead && !sphWait);
                 doSphere = (unsigned)__popc(sphMask) >= p.sphereQuorum || other == 0;
             }
         }
-        if (alive && cur < 0 && (!(SPHERES && sphWait) || doSphere)) {
+        if (cur < kDead && (!(SPHERES && sphWait) || doSphere)) {
             bool needPop = true;
-            if (ANY || (SPHERES && sphWait) || curT < tMax) {  // box test of the leaf node, made when the lane steps onto it
-                if (!ANY) curT = kNegInf;  // ... and only then: later triangles of this leaf skip it (:547-555)
+            {  // the leaf node's own `tMin < raytMax` was settled when the lane stepped onto it (:547-555)
                 const uint32_t prim = (uint32_t)cur & 0x7fffffffu;
                 const float4 *tp = tris + 3 * (size_t)prim;
                 const float4 v0 = __ldg(tp), v1 = __ldg(tp + 1), v2 = __ldg(tp + 2);
@@ -494,7 +509,7 @@ __global__ void __launch_bounds__(256, MINB) StepKernel(StepParams p) {
                         // this instance's ray needs the verbatim slab cascade: the exact launch traces the ray again
                         const uint32_t pos = atomicAdd(p.nDeferred, 1u);
                         p.deferred[pos] = rayIdx;
-                        alive = false;
+                        cur = kDead;
                         needPop = false;
                     } else {
                         const float4 *is = reinterpret_cast<const float4 *>(sc.instStep + k);
@@ -515,7 +530,6 @@ __global__ void __launch_bounds__(256, MINB) StepKernel(StepParams p) {
                             setRay(rc);
                             tMax = tLocal;
                             cur = __float_as_int(b1.z);
-                            if (!ANY) curT = tRoot;
                             needPop = false;
                         } else if (!(flags & kTriLast)) {
                             cur = cur + 1;  // the instance is missed as a whole: next primitive of the leaf
@@ -576,7 +590,7 @@ __global__ void __launch_bounds__(256, MINB) StepKernel(StepParams p) {
                 } else if (SPHERES && sphWait) {
                     // parked at the sphere slot: `cur` stays
                 } else if (ANY && found) {  // first accepted primitive ends the ray (:598-601)
-                    alive = false;
+                    cur = kDead;
                     needPop = false;
                     p.occluded[rayIdx] = 1;
                 } else if (!(flags & kTriLast)) {
@@ -586,31 +600,8 @@ __global__ void __launch_bounds__(256, MINB) StepKernel(StepParams p) {
             }
             if (INST && needPop) {
                 popInst();
-            } else if (needPop) {  // :556-558; culled entries are skipped as in phase A
-                bool got = false;
-                if (ANY) {
-                    if (sp > 0) {
-                        --sp;
-                        cur = (int)(unsigned)stack[sp];
-                        got = true;
-                    }
-                } else {
-                    while (sp > 0) {
-                        --sp;
-                        const unsigned long long e = stack[sp];
-                        cur = (int)(unsigned)e;
-                        curT = __uint_as_float((unsigned)(e >> 32));
-                        if (curT < tMax || !p.popLoop) {
-                            got = true;
-                            break;
-                        }
-                    }
-                }
-                if (!got) {
-                    alive = false;
-                    if (ANY) p.occluded[rayIdx] = 0;
-                    else StoreHit(p.hits, rayIdx, hit);
-                }
+            } else {  // :556-558; culled entries are skipped as in phase A
+                popOne(needPop);
             }
         }
     }

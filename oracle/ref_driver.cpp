@@ -695,6 +695,8 @@ void *nnbvh_ref_scene_create_general(const float *tris9, int nTris, const float 
             orig = sp->shape.Is<pbrt::Triangle>() ? sp->shape.Cast<pbrt::Triangle>()->triIndex : TagOf(sp->material);
         }
         s->orderedToOrig[i] = orig;
+        if (orig < 0)  // a sphere of a scene made with nnbvh_ref_tag_materials(0): it cannot be named
+            continue;
         s->origToOrdered[orig] = i;
     }
     return s;
