@@ -47,6 +47,10 @@
 #define NNBVH_SPC 4  // node steps per look at the leaf quorum (unrolled)
 #endif
 
+// popOne takes the address of the top stack entry before the first push has been written (it is not
+// dereferenced then): nvcc's "used before its value is set" does not apply
+#pragma nv_diag_suppress 549
+
 namespace nnbvh {
 
 struct StepParams {
@@ -134,7 +138,12 @@ __global__ void __launch_bounds__(256, MINB) StepKernel(StepParams p) {
     uint32_t rayIdx = 0;
     StepRay ry{};
     float tMax = 0.f;
-    HitRegs hit{NNBVH_MISS, 0.f, 0.f, 0.f, 0.f};
+    // Closest hit: no lane carries its hit record.  Every accepted hit is written to the ray's output slot at once
+    // (a later, closer one overwrites it: 1.2 writes per ray on bathroom) and tMax IS the record's t; what stays in
+    // registers is one bit, kHasHit of ry.neg, so that a ray that ends without a hit stores the miss record.
+    // Five registers less in the node loop (at 48 per thread the compiler kept the record in local memory there).
+    constexpr unsigned kHasHit = 0x80000000u;
+    const HitRegs kMissRecord{NNBVH_MISS, 0.f, 0.f, 0.f, 0.f};
     // kDead: the lane has no ray.  A lane is at an interior node when cur >= 0 and parked at a leaf slot when
     // cur < kDead (bit 31 + the ordered primitive, which is never 0x7fffffff): one compare each, no flag to carry.
     constexpr int kDead = -1;
@@ -170,15 +179,21 @@ __global__ void __launch_bounds__(256, MINB) StepKernel(StepParams p) {
         ry.ix = rc.ix; ry.iy = rc.iy; ry.iz = rc.iz;
         ry.Sx = rc.Sx; ry.Sy = rc.Sy; ry.Sz = rc.Sz;
         ry.kz = rc.kz;
-        ry.neg = (unsigned)rc.negx | ((unsigned)rc.negy << 1) | ((unsigned)rc.negz << 2);
+        ry.neg = (ry.neg & kHasHit) | (unsigned)rc.negx | ((unsigned)rc.negy << 1) | ((unsigned)rc.negz << 2);
     };
-    auto finish = [&]() {  // the ray is done: its record goes out
+    auto finish = [&]() {  // the ray is done: a hit's record is already out
         cur = kDead;
         if (ANY) p.occluded[rayIdx] = 0;
-        else {
-            StoreHit(p.hits, rayIdx, hit);
-            if (INST && p.inner) p.inner[rayIdx] = hit.inner;
+        else if (!(ry.neg & kHasHit)) {
+            StoreHit(p.hits, rayIdx, kMissRecord);
+            if (INST && p.inner) p.inner[rayIdx] = NNBVH_MISS;
         }
+    };
+    auto accept = [&](uint32_t prim, uint32_t inner, float t, float b0, float b1, float b2) {
+        StoreHit(p.hits, rayIdx, HitRegs{prim, t, b0, b1, b2});
+        if (INST && p.inner) p.inner[rayIdx] = inner;
+        ry.neg |= kHasHit;
+        tMax = t;
     };
     // The pop of both phases (aggregates.cpp:556-558, :570-574) for the lanes that `want` it.  Closest hit: ONE
     // predicated load in the straight line, not a branch -- as a branch it ran with ~4 lanes per warp after every
@@ -204,9 +219,7 @@ __global__ void __launch_bounds__(256, MINB) StepKernel(StepParams p) {
         float tEntry = 0.f;
         // `if (pop) { e = stack[--sp]; ... }` compiles to a branch around the load; as a predicated ld.local the
         // registers simply keep their values in the other lanes.  entry = {ref (low word), tEntry bits (high word)}
-#pragma nv_diag_suppress 549  // `stack` is written before any pop can happen (sp > 0)
         const size_t top = __cvta_generic_to_local(&stack[sp - 1]);  // not dereferenced unless pop
-#pragma nv_diag_default 549
         asm volatile("{\n .reg .pred q;\n setp.ne.s32 q, %3, 0;\n @q ld.local.v2.b32 {%0, %1}, [%2];\n}"
                      : "+r"(cur), "+f"(tEntry) : "l"(top), "r"((int)pop) : "memory");
         sp -= pop ? 1 : 0;
@@ -221,10 +234,7 @@ __global__ void __launch_bounds__(256, MINB) StepKernel(StepParams p) {
                     break;
                 }
             }
-            if (!got) {
-                cur = kDead;
-                StoreHit(p.hits, rayIdx, hit);
-            }
+            if (!got) finish();
         }
     };
     // INST: the pop of both phases.  Entries above spBase are the current level's; with none left inside an instance
@@ -261,7 +271,7 @@ __global__ void __launch_bounds__(256, MINB) StepKernel(StepParams p) {
             const RayRegs rr = LoadRay(p.in, rayIdx);
             setRay(MakeRayConst(rr.ox, rr.oy, rr.oz, rr.dx, rr.dy, rr.dz));
             if (ANY) tMax = rr.tMax;
-            else tMax = instHit ? hit.t : __uint_as_float((unsigned)(e >> 32));
+            else tMax = instHit ? tMax : __uint_as_float((unsigned)(e >> 32));  // the hit's t is the inner tMax
             instSlot = -1;
             spBase = 0;
             instHit = false;
@@ -319,10 +329,7 @@ __global__ void __launch_bounds__(256, MINB) StepKernel(StepParams p) {
                         ry.kz = rc.kz;
                         ry.neg = (unsigned)rc.negx | ((unsigned)rc.negy << 1) | ((unsigned)rc.negz << 2);
                         tMax = rr.tMax;
-                        hit.prim = NNBVH_MISS;
-                        hit.t = hit.b0 = hit.b1 = hit.b2 = 0.f;
                         if (INST) {
-                            hit.inner = NNBVH_MISS;
                             instSlot = -1;
                             spBase = 0;
                             instHit = false;
@@ -342,7 +349,7 @@ __global__ void __launch_bounds__(256, MINB) StepKernel(StepParams p) {
                             cur = sc.rootRef;
                         } else if (ANY) p.occluded[idx] = 0;
                         else {
-                            StoreHit(p.hits, idx, hit);
+                            StoreHit(p.hits, idx, kMissRecord);
                             if (INST && p.inner) p.inner[idx] = NNBVH_MISS;
                         }
                     }
@@ -548,13 +555,7 @@ __global__ void __launch_bounds__(256, MINB) StepKernel(StepParams p) {
                     if (SphereTest(sc.spheres + __float_as_uint(v0.x), rr.ox, rr.oy, rr.oz, rr.dx, rr.dy,
                                    rr.dz, tMax, &sh)) {
                         found = true;
-                        hit.prim = prim;
-                        if (INST) hit.inner = NNBVH_MISS;
-                        hit.t = sh.t;
-                        hit.b0 = sh.px;
-                        hit.b1 = sh.py;
-                        hit.b2 = sh.pz;
-                        tMax = sh.t;
+                        if (!ANY) accept(prim, NNBVH_MISS, sh.t, sh.px, sh.py, sh.pz);
                     }
                 } else if (!(flags & kTriDegenerate)) {
                     RayConst rc = ToRayConst(ry);
@@ -572,17 +573,13 @@ __global__ void __launch_bounds__(256, MINB) StepKernel(StepParams p) {
                     }
                     if (got) {
                         found = true;
-                        hit.prim = prim;
-                        if (INST) {  // inside an instance: its top-level slot + the primitive inside the object
-                            hit.inner = instSlot >= 0 ? prim - instPrimBase : NNBVH_MISS;
-                            hit.prim = instSlot >= 0 ? (uint32_t)instSlot : prim;
-                            instHit = instSlot >= 0;
+                        if (ANY) {
+                        } else if (INST && instSlot >= 0) {  // inside an instance: its top-level slot + the primitive inside the object
+                            accept((uint32_t)instSlot, prim - instPrimBase, t, b0, b1, b2);
+                            instHit = true;
+                        } else {
+                            accept(prim, NNBVH_MISS, t, b0, b1, b2);
                         }
-                        hit.t = t;
-                        hit.b0 = b0;
-                        hit.b1 = b1;
-                        hit.b2 = b2;
-                        tMax = t;
                     }
                 }
                 if (INST && (flags & kPrimInstance)) {
