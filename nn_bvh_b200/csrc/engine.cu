@@ -1224,6 +1224,8 @@ static int LaunchTraversal(nnbvh_engine *e, cudaStream_t st, bool any, bool coun
             uint32_t *nDef = reinterpret_cast<uint32_t *>(cursor + 2);
             const bool timed = st == e->stream;  // the device-pointer path; chunk streams are not timed
             if (timed) CU(cudaEventRecord(e->evC, st));
+            // any hit: the kernel only writes the occluded rays' 1s (no store left in its node loop)
+            if (any) CU(cudaMemsetAsync(o.occ, 0, n, st));
             if (e->boxesRegular && !e->exactOnly) {
                 int rc = scr.deferred.Reserve(n);
                 if (rc) return rc;

@@ -59,7 +59,7 @@ struct StepParams {
     uint64_t n;                   // rays (or capacity of `perm` when nPtr is used)
     const uint32_t *nPtr;         // if set: number of entries of `perm` to process, on the device
     nnbvh_hit *hits;
-    uint8_t *occluded;
+    uint8_t *occluded;            // any hit: ZEROED by the caller before the launch; the kernel only writes the 1s
     unsigned long long *cursor;   // zeroed before launch
     const uint32_t *perm;         // optional ray order; results go to slot perm[j]
     const uint32_t *permOn;       // optional device flag: 0 = ignore perm (binning decided not to sort)
@@ -183,8 +183,9 @@ __global__ void __launch_bounds__(256, MINB) StepKernel(StepParams p) {
     };
     auto finish = [&]() {  // the ray is done: a hit's record is already out
         cur = kDead;
-        if (ANY) p.occluded[rayIdx] = 0;
-        else if (!(ry.neg & kHasHit)) {
+        if (ANY) {
+            // occluded[] is zeroed before the launch (StepParams::occluded): an unoccluded ray just ends
+        } else if (!(ry.neg & kHasHit)) {
             StoreHit(p.hits, rayIdx, kMissRecord);
             if (INST && p.inner) p.inner[rayIdx] = NNBVH_MISS;
         }
@@ -209,8 +210,7 @@ __global__ void __launch_bounds__(256, MINB) StepKernel(StepParams p) {
                     --sp;
                     cur = (int)(unsigned)stack[sp];
                 } else {
-                    cur = kDead;
-                    p.occluded[rayIdx] = 0;
+                    cur = kDead;  // unoccluded: occluded[] was zeroed before the launch
                 }
             }
             return;
@@ -347,8 +347,8 @@ __global__ void __launch_bounds__(256, MINB) StepKernel(StepParams p) {
                         }
                         if (rootOk && tRoot < tMax) {
                             cur = sc.rootRef;
-                        } else if (ANY) p.occluded[idx] = 0;
-                        else {
+                        } else if (ANY) {
+                        } else {
                             StoreHit(p.hits, idx, kMissRecord);
                             if (INST && p.inner) p.inner[idx] = NNBVH_MISS;
                         }
