@@ -216,13 +216,13 @@ __global__ void __launch_bounds__(256, MINB) StepKernel(StepParams p) {
             return;
         }
         const bool pop = want && sp > 0;
-        float tEntry = 0.f;
+        float tEntry;  // written by the load; only looked at under `pop`
         // `if (pop) { e = stack[--sp]; ... }` compiles to a branch around the load; as a predicated ld.local the
         // registers simply keep their values in the other lanes.  entry = {ref (low word), tEntry bits (high word)}
         const size_t top = __cvta_generic_to_local(&stack[sp - 1]);  // not dereferenced unless pop
-        asm volatile("{\n .reg .pred q;\n setp.ne.s32 q, %3, 0;\n @q ld.local.v2.b32 {%0, %1}, [%2];\n}"
-                     : "+r"(cur), "+f"(tEntry) : "l"(top), "r"((int)pop) : "memory");
-        sp -= pop ? 1 : 0;
+        asm volatile("{\n .reg .pred q;\n setp.ne.s32 q, %4, 0;\n @q ld.local.v2.b32 {%0, %1}, [%3];\n"
+                     " @q add.s32 %2, %2, -1;\n}"
+                     : "+r"(cur), "=f"(tEntry), "+r"(sp) : "l"(top), "r"((int)pop) : "memory");
         if ((want && !pop) || (pop && !(tEntry < tMax))) {
             bool got = false;
             while (sp > 0) {
@@ -453,8 +453,8 @@ __global__ void __launch_bounds__(256, MINB) StepKernel(StepParams p) {
                     if (push) {
                         if (ANY) stack[sp] = (unsigned)refFar;
                         else stack[sp] = ((unsigned long long)__float_as_uint(tFar) << 32) | (unsigned)refFar;
+                        ++sp;
                     }
-                    sp += push ? 1 : 0;
                     // near child if it passes (tNear < tMax already established: next step passes), else the
                     // far child if it does (aggregates.cpp:560-569); with neither, the values are dead
                     cur = goNear ? refNear : (goFar ? refFar : cur);
