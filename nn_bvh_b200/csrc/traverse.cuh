@@ -43,6 +43,9 @@
 #ifndef NNBVH_ANY_ORDER
 #define NNBVH_ANY_ORDER 1
 #endif
+#ifndef NNBVH_ANY_PRED_POP
+#define NNBVH_ANY_PRED_POP 0  // 1: any hit pops with a predicated load too -- measured 1-2 % slower than the branch (r02zk)
+#endif
 #ifndef NNBVH_SPC
 #define NNBVH_SPC 4  // node steps per look at the leaf quorum (unrolled)
 #endif
@@ -205,6 +208,13 @@ __global__ void __launch_bounds__(256, MINB) StepKernel(StepParams p) {
     // predicated form measured 2 % slower there (profiles/r02_experiments.txt).
     auto popOne = [&](const bool want) {
         if (ANY) {
+#if NNBVH_ANY_PRED_POP
+            const bool pop = want && sp > 0;
+            cur = (want && !pop) ? kDead : cur;  // unoccluded: occluded[] was zeroed before the launch
+            const size_t top = __cvta_generic_to_local(&stack[sp - 1]);  // not dereferenced unless pop
+            asm volatile("{\n .reg .pred q;\n setp.ne.s32 q, %3, 0;\n @q ld.local.b32 %0, [%2];\n @q add.s32 %1, %1, -1;\n}"
+                         : "+r"(cur), "+r"(sp) : "l"(top), "r"((int)pop) : "memory");
+#else
             if (want) {
                 if (sp > 0) {
                     --sp;
@@ -213,6 +223,7 @@ __global__ void __launch_bounds__(256, MINB) StepKernel(StepParams p) {
                     cur = kDead;  // unoccluded: occluded[] was zeroed before the launch
                 }
             }
+#endif
             return;
         }
         const bool pop = want && sp > 0;
