@@ -12,8 +12,8 @@
 //    the child it descends to, at the pop for the stacked one (the entry carries its tEntry), which is
 //    the moment the reference tests it.  tMax only changes while the lane is parked at a leaf, so a lane
 //    at a node never has to look at it again.
-//  * One step per lane per iteration, straight-line: a lane whose node has no passing child pops ONE
-//    entry with a predicated load; entries that fail the test (rare) are dropped in a side arm.
+//  * One step per lane per iteration, straight-line: a lane whose node has no passing child pops (a
+//    branch; entries that fail the test against the current tMax are dropped inside that pop).
 //  * A 64-byte node is fetched with two 256-bit loads (LDG.E.ENL2.256): half the L1
 //    wavefronts of four LDG.128.
 //  * Fast slab (EXACT=false): for rays whose invDir is finite and non-zero and whose origin
@@ -45,6 +45,9 @@
 #endif
 #ifndef NNBVH_ANY_PRED_POP
 #define NNBVH_ANY_PRED_POP 0  // 1: any hit pops with a predicated load too -- measured 1-2 % slower than the branch (r02zk)
+#endif
+#ifndef NNBVH_CLOSEST_PRED_POP
+#define NNBVH_CLOSEST_PRED_POP 0  // 1: closest hit pops with a predicated ld.local in the step's straight line -- measured 1-4 % slower than the branch (r02zl)
 #endif
 #ifndef NNBVH_SPC
 #define NNBVH_SPC 4  // node steps per look at the leaf quorum (unrolled)
@@ -199,13 +202,12 @@ __global__ void __launch_bounds__(256, MINB) StepKernel(StepParams p) {
         ry.neg |= kHasHit;
         tMax = t;
     };
-    // The pop of both phases (aggregates.cpp:556-558, :570-574) for the lanes that `want` it.  Closest hit: ONE
-    // predicated load in the straight line, not a branch -- as a branch it ran with ~4 lanes per warp after every
-    // node step and, with its reconvergence, was 14 % of the kernel's issued instructions (profiles/r02q,
-    // 0x21f0-0x2470 and 0x4930-0x4a30 of StepKernel<0,0,5>).  An entry whose box test fails against the current
-    // tMax (`tEntry < tMax` false: the reference pops those one by one with the same outcome) and the end of the
-    // ray are the rare arm.  Any hit keeps the branch: its entries are bare refs, nothing is re-validated, and the
-    // predicated form measured 2 % slower there (profiles/r02_experiments.txt).
+    // The pop of both phases (aggregates.cpp:556-558, :570-574) for the lanes that `want` it: a branch.  Closest
+    // hit: entries whose box test fails against the current tMax (`tEntry < tMax` false) are discarded inside the
+    // pop -- the reference pops those one by one with the same outcome.  The same pop written as ONE predicated
+    // ld.local in the step's straight line (NNBVH_CLOSEST_PRED_POP / NNBVH_ANY_PRED_POP = 1; stale entries and the
+    // ray's end in a rare arm) issues 5 % fewer instructions and measured 1-4 % SLOWER for both kinds of ray
+    // (profiles/r02_experiments.txt: the load's latency then sits in every lane's step), so it stays off.
     auto popOne = [&](const bool want) {
         if (ANY) {
 #if NNBVH_ANY_PRED_POP
@@ -226,6 +228,22 @@ __global__ void __launch_bounds__(256, MINB) StepKernel(StepParams p) {
 #endif
             return;
         }
+#if !NNBVH_CLOSEST_PRED_POP
+        if (want) {
+            bool got = false;
+            while (sp > 0) {
+                --sp;
+                const unsigned long long e = (unsigned long long)stack[sp];
+                cur = (int)(unsigned)e;
+                if (__uint_as_float((unsigned)(e >> 32)) < tMax) {
+                    got = true;
+                    break;
+                }
+            }
+            if (!got) finish();
+        }
+        return;
+#endif
         const bool pop = want && sp > 0;
         float tEntry;  // written by the load; only looked at under `pop`
         // `if (pop) { e = stack[--sp]; ... }` compiles to a branch around the load; as a predicated ld.local the
