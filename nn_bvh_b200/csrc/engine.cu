@@ -186,6 +186,7 @@ struct nnbvh_engine {
     int instStep = 1;        // instanced scenes: 1 = StepKernel<..., INST>, 0 = the one-thread-per-ray BasicKernel
     int gridRaysPerLane = 0; // StepKernel: shrink the persistent grid for small batches (StepGrid); 0 = never
     int sphereQuorum = 12;   // StepKernel with sphere leaves: lanes waiting at spheres before their tests run
+    int stepBlock = 256;     // StepKernel<.., 5>: threads per CTA (a multiple of 32 up to 256; 192 = 7 CTAs / 42 warps per SM)
     int chunkRamp = 1;       // host-pointer pipeline: small chunks at both ends of a call (RunBatch)
     uint64_t chunkRays = 1u << 19;
     uint64_t chunkRaysSoa = 1u << 20;  // SoA planes are 4 bytes per ray each: larger chunks per copy
@@ -256,6 +257,7 @@ extern "C" int nnbvh_create(const nnbvh_options *opts, nnbvh_engine **out) {
     e->smemTopNodes = EnvInt("NNBVH_SMEM_NODES", e->smemTopNodes);
     e->wideMinB = EnvInt("NNBVH_WIDE_MINB", e->wideMinB);
     e->refillBelow = EnvInt("NNBVH_REFILL_BELOW", e->refillBelow);
+    e->stepBlock = std::min(256, std::max(32, EnvInt("NNBVH_STEP_BLOCK", e->stepBlock) & ~31));
     e->leafQuorum = EnvInt("NNBVH_LEAF_QUORUM", e->leafQuorum);
     e->gridRaysPerLane = EnvInt("NNBVH_GRID_RAYS_PER_LANE", e->gridRaysPerLane);
     e->instStep = EnvInt("NNBVH_INST_STEP", e->instStep);
@@ -1023,7 +1025,18 @@ static void LaunchStep(nnbvh_engine *e, cudaStream_t st, const StepParams &p) {
     case 3: StepKernel<ANY, EXACT, 3><<<grid, 256, 0, st>>>(p); break;
     case 4: StepKernel<ANY, EXACT, 4><<<grid, 256, 0, st>>>(p); break;
     case 6: StepKernel<ANY, EXACT, 6><<<grid, 256, 0, st>>>(p); break;
-    default: StepKernel<ANY, EXACT, 5><<<grid, 256, 0, st>>>(p); break;
+    default: {
+        // The kernel has no block-level state (warps are independent): at its 48 registers an SM holds 1365 threads,
+        // i.e. 5 CTAs of 256 (40 warps) or 7 of 192 (42 warps).  NNBVH_STEP_BLOCK selects the CTA size.
+        const unsigned block = (unsigned)e->stepBlock;
+        if (block == 256 || p.nPtr || e->gridRaysPerLane > 0) {
+            StepKernel<ANY, EXACT, 5><<<grid, 256, 0, st>>>(p);
+        } else {
+            const unsigned perSM = std::min(32u, 1344u / block);
+            StepKernel<ANY, EXACT, 5><<<(unsigned)e->numSMs * perSM, block, 0, st>>>(p);
+        }
+        break;
+    }
     }
 }
 
