@@ -49,6 +49,9 @@
 #ifndef NNBVH_CLOSEST_PRED_POP
 #define NNBVH_CLOSEST_PRED_POP 0  // 1: closest hit pops with a predicated ld.local in the step's straight line -- measured 1-4 % slower than the branch (r02zl)
 #endif
+#ifndef NNBVH_STACK_CACHE
+#define NNBVH_STACK_CACHE 0  // 1: closest hit (no instances) keeps the top stack entry in two registers
+#endif
 #ifndef NNBVH_SPC
 #define NNBVH_SPC 4  // node steps per look at the leaf quorum (unrolled)
 #endif
@@ -154,6 +157,13 @@ __global__ void __launch_bounds__(256, MINB) StepKernel(StepParams p) {
     // cur < kDead (bit 31 + the ordered primitive, which is never 0x7fffffff): one compare each, no flag to carry.
     constexpr int kDead = -1;
     int cur = kDead, sp = 0;
+    // NNBVH_STACK_CACHE: the newest stack entry lives in (topRef, topT) and only goes to local memory when a second one
+    // is pushed on top of it; a pop that follows a push touches no memory.  (The stack is a third of the L1's sector
+    // traffic)  Closest hit without instances only: the instance code addresses stack[] directly.
+    constexpr bool CACHE = NNBVH_STACK_CACHE && !NNBVH_CLOSEST_PRED_POP && !ANY && !INST;
+    constexpr int kNone = -1;  // no ref has this value (kDead)
+    int topRef = kNone;
+    float topT = 0.f;
     // stack entry = {ref, tEntry} packed into 64 bits (one STL.64 / LDL.64 per push / pop).
     // ANY: IntersectP never shrinks tMax (aggregates.cpp:581-624), so `tMin < raytMax` of a child can be
     // settled for good when its parent is fetched: only children that pass it are entered or stacked, the
@@ -229,6 +239,31 @@ __global__ void __launch_bounds__(256, MINB) StepKernel(StepParams p) {
             return;
         }
 #if !NNBVH_CLOSEST_PRED_POP
+        if (CACHE) {
+            if (want) {
+                bool got = false;
+                while (true) {
+                    float t;
+                    if (topRef != kNone) {
+                        cur = topRef;
+                        t = topT;
+                        topRef = kNone;
+                    } else if (sp > 0) {
+                        --sp;
+                        const unsigned long long e = (unsigned long long)stack[sp];
+                        cur = (int)(unsigned)e;
+                        t = __uint_as_float((unsigned)(e >> 32));
+                    } else
+                        break;
+                    if (t < tMax) {
+                        got = true;
+                        break;
+                    }
+                }
+                if (!got) finish();
+            }
+            return;
+        }
         if (want) {
             bool got = false;
             while (sp > 0) {
@@ -364,6 +399,7 @@ __global__ void __launch_bounds__(256, MINB) StepKernel(StepParams p) {
                             instHit = false;
                         }
                         sp = 0;
+                        topRef = kNone;
                         // Root: the reference tests the root's own box first (aggregates.cpp:543);
                         // nodes == nullptr -> miss (:531).  Exact cascade, once per ray.
                         float tRoot = 0.f;
@@ -479,7 +515,16 @@ __global__ void __launch_bounds__(256, MINB) StepKernel(StepParams p) {
                     // The far child is stacked whenever its tMax-independent test passes: tMax
                     // can GROW by an ulp before the pop (shapes.cpp:239-247), see DESIGN.md.
                     const bool push = goNear && (ANY ? goFar : stFar);
-                    if (push) {
+                    if (CACHE) {
+                        if (push) {
+                            if (topRef != kNone) {
+                                stack[sp] = ((unsigned long long)__float_as_uint(topT) << 32) | (unsigned)topRef;
+                                ++sp;
+                            }
+                            topRef = refFar;
+                            topT = tFar;
+                        }
+                    } else if (push) {
                         if (ANY) stack[sp] = (unsigned)refFar;
                         else stack[sp] = ((unsigned long long)__float_as_uint(tFar) << 32) | (unsigned)refFar;
                         ++sp;
