@@ -186,6 +186,8 @@ struct nnbvh_engine {
     int instStep = 1;        // instanced scenes: 1 = StepKernel<..., INST>, 0 = the one-thread-per-ray BasicKernel
     int gridRaysPerLane = 0; // StepKernel: shrink the persistent grid for small batches (StepGrid); 0 = never
     int sphereQuorum = 12;   // StepKernel with sphere leaves: lanes waiting at spheres before their tests run
+    int l2PersistMB = 0;     // NNBVH_L2_PERSIST_MB: L2 set-aside for the wide nodes (access-policy window on the launch stream); 0 = off
+    size_t l2PersistBytes = 0, l2MaxWindow = 0;
     int stepBlock = 256;     // StepKernel<.., 5>: threads per CTA (a multiple of 32 up to 256; 192 = 7 CTAs / 42 warps per SM)
     int chunkRamp = 1;       // host-pointer pipeline: small chunks at both ends of a call (RunBatch)
     uint64_t chunkRays = 1u << 19;
@@ -257,6 +259,16 @@ extern "C" int nnbvh_create(const nnbvh_options *opts, nnbvh_engine **out) {
     e->smemTopNodes = EnvInt("NNBVH_SMEM_NODES", e->smemTopNodes);
     e->wideMinB = EnvInt("NNBVH_WIDE_MINB", e->wideMinB);
     e->refillBelow = EnvInt("NNBVH_REFILL_BELOW", e->refillBelow);
+    e->l2PersistMB = std::max(0, EnvInt("NNBVH_L2_PERSIST_MB", e->l2PersistMB));
+    if (e->l2PersistMB > 0) {
+        int maxPersist = 0, maxWin = 0;
+        CU(cudaDeviceGetAttribute(&maxPersist, cudaDevAttrMaxPersistingL2CacheSize, e->device));
+        CU(cudaDeviceGetAttribute(&maxWin, cudaDevAttrMaxAccessPolicyWindowSize, e->device));
+        e->l2PersistBytes = std::min((size_t)e->l2PersistMB << 20, (size_t)std::max(0, maxPersist));
+        e->l2MaxWindow = (size_t)std::max(0, maxWin);
+        if (e->l2PersistBytes) CU(cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, e->l2PersistBytes));
+        if (getenv("NNBVH_VERBOSE")) fprintf(stderr, "nnbvh: L2 persisting max %d B, window max %d B, set-aside %zu B\n", maxPersist, maxWin, e->l2PersistBytes);
+    }
     e->stepBlock = std::min(256, std::max(32, EnvInt("NNBVH_STEP_BLOCK", e->stepBlock) & ~31));
     e->leafQuorum = EnvInt("NNBVH_LEAF_QUORUM", e->leafQuorum);
     e->gridRaysPerLane = EnvInt("NNBVH_GRID_RAYS_PER_LANE", e->gridRaysPerLane);
@@ -1121,6 +1133,16 @@ static int LaunchTraversal(nnbvh_engine *e, cudaStream_t st, bool any, bool coun
                            const RayInput &in, uint64_t n, const Outputs &o,
                            Scratch &scr) {
     if (n == 0) return NNBVH_OK;
+    if (e->l2PersistBytes && e->l2MaxWindow && e->sc.nWide) {  // experiment: keep the wide nodes in the L2's set-aside
+        cudaStreamAttrValue v{};
+        const size_t bytes = std::min(sizeof(WideNode) * (size_t)e->sc.nWide, e->l2MaxWindow);
+        v.accessPolicyWindow.base_ptr = const_cast<WideNode *>(e->sc.wide);
+        v.accessPolicyWindow.num_bytes = bytes;
+        v.accessPolicyWindow.hitRatio = (float)std::min(1.0, (double)e->l2PersistBytes / (double)bytes);
+        v.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
+        v.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
+        CU(cudaStreamSetAttribute(st, cudaStreamAttributeAccessPolicyWindow, &v));
+    }
     // One thread per ray (general / alpha / instanced scenes): the same ray order helps there too -- the lanes of a
     // warp then walk neighbouring rays -- so those kernels pull their ray through the permutation as well.
     RayInput inO = in;
