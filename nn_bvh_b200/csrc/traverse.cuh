@@ -49,6 +49,9 @@
 #ifndef NNBVH_CLOSEST_PRED_POP
 #define NNBVH_CLOSEST_PRED_POP 0  // 1: closest hit pops with a predicated ld.local in the step's straight line -- measured 1-4 % slower than the branch (r02zl)
 #endif
+#ifndef NNBVH_L1_NOALLOC
+#define NNBVH_L1_NOALLOC 0  // 1: triangle loads bypass L1 allocation (ld.global.nc.L1::no_allocate); 2: the refill's ray loads too
+#endif
 #ifndef NNBVH_STACK_CACHE
 #define NNBVH_STACK_CACHE 0  // 1: closest hit (no instances) keeps the top stack entry in two registers
 #endif
@@ -61,6 +64,15 @@
 #pragma nv_diag_suppress 549
 
 namespace nnbvh {
+
+// A 16-byte read-only load that does not allocate in the L1 (data with no reuse inside the SM: a triangle is tested
+// once per visit, a ray is read once) -- the L1 is shared with the lanes' stacks and the nodes.
+__device__ __forceinline__ float4 LdgNoAllocate(const float4 *p) {
+    float4 v;
+    asm("ld.global.nc.L1::no_allocate.v4.f32 {%0, %1, %2, %3}, [%4];"
+        : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p));
+    return v;
+}
 
 struct StepParams {
     SceneDev sc;
@@ -371,7 +383,17 @@ __global__ void __launch_bounds__(256, MINB) StepKernel(StepParams p) {
                 uint64_t j = base + __popc(want & ((1u << lane) - 1));
                 if (j < nRays) {
                     uint32_t idx = perm ? __ldg(perm + j) : (uint32_t)j;
+#if NNBVH_L1_NOALLOC >= 2
+                    RayRegs rr;
+                    if (p.in.aos) {
+                        const float4 a = LdgNoAllocate(p.in.aos + 2 * (size_t)idx), b = LdgNoAllocate(p.in.aos + 2 * (size_t)idx + 1);
+                        rr.ox = a.x; rr.oy = a.y; rr.oz = a.z; rr.tMax = a.w;
+                        rr.dx = b.x; rr.dy = b.y; rr.dz = b.z;
+                    } else
+                        rr = LoadRay(p.in, idx);
+#else
                     RayRegs rr = LoadRay(p.in, idx);
+#endif
                     RayConst rc = MakeRayConst(rr.ox, rr.oy, rr.oz, rr.dx, rr.dy, rr.dz);
                     bool defer = false;
                     if (!EXACT) {
@@ -575,7 +597,11 @@ __global__ void __launch_bounds__(256, MINB) StepKernel(StepParams p) {
             {  // the leaf node's own `tMin < raytMax` was settled when the lane stepped onto it (:547-555)
                 const uint32_t prim = (uint32_t)cur & 0x7fffffffu;
                 const float4 *tp = tris + 3 * (size_t)prim;
+#if NNBVH_L1_NOALLOC >= 1
+                const float4 v0 = LdgNoAllocate(tp), v1 = LdgNoAllocate(tp + 1), v2 = LdgNoAllocate(tp + 2);
+#else
                 const float4 v0 = __ldg(tp), v1 = __ldg(tp + 1), v2 = __ldg(tp + 2);
+#endif
                 const uint32_t flags = __float_as_uint(v0.w);
                 bool found = false;
                 if (INST && (flags & kPrimInstance)) {
