@@ -287,11 +287,14 @@ typedef struct nnbvh_scene_desc {
 } nnbvh_scene_desc;
 int nnbvh_upload_scene_general(nnbvh_engine *e, const nnbvh_scene_desc *d);
 
-/* BVHAggregate::Intersect (cpu/aggregates.cpp:529-579) for n rays. */
+/* BVHAggregate::Intersect (cpu/aggregates.cpp:529-579) for n rays.  hits[i] is final when the call's work on
+ * the stream has completed; while it runs, a ray's slot may hold the record of a hit that a closer one later
+ * replaces (the kernel writes a record when a hit is accepted). */
 int nnbvh_intersect_closest(nnbvh_engine *e, const nnbvh_ray *rays, uint64_t n,
                             nnbvh_hit *hits);
 
-/* BVHAggregate::IntersectP (cpu/aggregates.cpp:581-624) for n rays: occluded[i] = 0/1. */
+/* BVHAggregate::IntersectP (cpu/aggregates.cpp:581-624) for n rays: occluded[i] = 0/1 (all n bytes are written:
+ * zeroed first, then the occluded rays' 1s). */
 int nnbvh_intersect_any(nnbvh_engine *e, const nnbvh_ray *rays, uint64_t n,
                         uint8_t *occluded);
 
